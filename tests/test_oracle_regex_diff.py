@@ -1,0 +1,157 @@
+"""Differential pinning of the oracle's java.util.regex restatement.
+
+No JVM exists in this image, and the reference has no regex fixtures, so the oracle's matcher is
+pinned against two independent backtracking engines on the syntax they share with Java after
+translation: CPython `re` (3.12: possessive quantifiers and atomic groups included) and the
+third-party `regex` module (V1: nested sets / intersections). Java-only behaviour
+(`.`/`$` line terminators, \\Z vs \\z, ASCII \\b, illegal `{,n}`) is covered by explicit cases.
+"""
+import random
+import re
+
+import pytest
+import regex as rx
+
+from rxgen import Gen, gen_text
+
+
+def py_search(pat: str, text: str) -> bool:
+    return re.search(pat, text, re.ASCII) is not None
+
+
+def test_random_differential_vs_cpython(oracle):
+    rng = random.Random(20261106)
+    n_checked = 0
+    for it in range(2500):
+        g = Gen(rng)
+        j, p = g.regex()
+        try:
+            cre = re.compile(p, re.ASCII)
+        except re.error:
+            continue
+        try:
+            o = oracle.Regex(j)
+        except (oracle.OracleSyntaxError, oracle.OracleUnsupported) as e:
+            raise AssertionError(f"oracle rejected {j!r} ({e}) but CPython accepted {p!r}")
+        o_noopt = oracle.Regex(j)
+        o_noopt.set_first_opt(False)
+        for _ in range(12):
+            t = gen_text(rng)
+            if t == "" and "\\B" in j:
+                continue  # CPython < 3.13: \B never matches the empty string; Java's Bound(NONE) does
+            exp = cre.search(t) is not None
+            got = o.find(t)
+            assert got == exp, f"java={j!r} py={p!r} text={t!r} oracle={got} cpython={exp}"
+            assert o_noopt.find(t) == exp, f"first-char opt changed the result for {j!r} on {t!r}"
+            n_checked += 1
+    assert n_checked > 20000
+
+
+def test_spans_vs_cpython(oracle):
+    rng = random.Random(99)
+    for it in range(800):
+        g = Gen(rng)
+        j, p = g.regex()
+        try:
+            cre = re.compile(p, re.ASCII)
+        except re.error:
+            continue
+        o = oracle.Regex(j)
+        for _ in range(6):
+            t = gen_text(rng)
+            if t == "" and "\\B" in j:
+                continue
+            m = cre.search(t)
+            sp = o.span(t)
+            assert (sp is None) == (m is None)
+            if m is not None:
+                assert sp == m.span(), f"java={j!r} text={t!r} oracle={sp} cpython={m.span()}"
+
+
+@pytest.mark.parametrize("pat,text,exp", [
+    # '.' excludes \n \r      (SURVEY §8c-J)
+    ("a.b", "a\rb", False), ("a.b", "ab", False), ("a.b", "a b", False), ("a.b", "a b", False),
+    ("a.b", "axb", True), ("(?s)a.b", "a\rb", True), ("(?d)a.b", "a\rb", True),
+    # '$' / \Z before a final terminator; \z absolute
+    ("a$", "a\r", True), ("a$", "a", True), ("a$", "a ", True), ("a$", "a\r\r", False),
+    ("a\\Z", "a\r", True), ("a\\z", "a\r", False), ("a\\z", "a", True), ("a$\\r", "a\r", True),
+    ("(?d)a$", "a\r", False),
+    ("^a", "a", True), ("^a", "ba", False), ("(?m)^a", "b\ra", True), ("(?m)^$", "", False), ("^$", "", True),
+    ("(?m)a$", "a\rb", True), ("a$", "a\rb", False),
+    # \b is ASCII-word based since JDK 19
+    ("\\bERROR\\b", "éERROR", True), ("\\bERROR\\b", "xERROR", False), ("\\bERROR\\b", "ERROR_", False),
+    ("\\bERROR\\b", "[ERROR]", True), ("\\B", "", True), ("\\b", "", False),
+    # case-insensitive is ASCII only without (?u)
+    ("(?i)error", "ERROR", True), ("(?i)é", "É", False), ("(?i)[a-c]x", "BX", True), ("(?i)[^a]", "A", False),
+    ("a(?i)b", "aB", True), ("a(?i)b", "AB", False), ("(a(?i)b)c", "aBC", False), ("(?i:a)b", "Ab", True),
+    # classes
+    ("[a-d[m-p]]", "n", True), ("[a-z&&[def]]", "e", True), ("[a-z&&[def]]", "a", False),
+    ("[a-z&&[^bc]]", "b", False), ("[a-z&&[^bc]]", "d", True), ("[]a]", "]", True), ("[^]a]", "]", False),
+    ("[a-]", "-", True), ("[\\w&&[^\\d]]", "5", False), ("[\\w&&[^\\d]]", "q", True),
+    ("\\p{Alpha}", "é", False), ("\\p{Alpha}", "q", True), ("\\P{Alpha}", "1", True), ("\\p{Punct}", "!", True),
+    ("\\p{XDigit}+", "fF09", True), ("\\h", "\t", True), ("\\v", "\r", True), ("\\R", "\r", True),
+    # escapes
+    ("\\Qa.b\\E", "a.b", True), ("\\Qa.b\\E", "axb", False), ("\\x41", "A", True), ("\\u0041", "A", True),
+    ("\\x{1F600}", "\U0001F600", True), ("\\uD83D\\uDE00", "\U0001F600", True), ("\\0101", "A", True),
+    ("\\cA", "\x01", True), ("\\e", "\x1b", True), ("\\t", "\t", True), ("\\$", "$", True),
+    # quantifiers
+    ("a{2,3}?b", "aaab", True), ("a*+a", "aaa", False), ("(?>a*)a", "aaa", False), ("(ab)*+ab", "abab", False),
+    ("(a|ab)(c|bcd)(d*)", "abcd", True), ("x{0}y", "y", True), ("(a*)*b", "aaab", True), ("(a|b)*?c", "abc", True),
+    # groups / backrefs / lookaround
+    ("(\\w+) \\1", "hello hello", True), ("(\\w+) \\1", "hello world", False), ("(?<w>a+)-\\k<w>", "aa-aa", True),
+    ("(?i)(a)\\1", "aA", True), ("(a)|\\1b", "b", False),
+    ("(?<=foo)bar", "foobar", True), ("(?<!foo)bar", "foobar", False), ("(?<=fo{1,2})bar", "foobar", True),
+    ("foo(?=bar)", "foobar", True), ("foo(?!bar)", "foobar", False), ("(?=(a+))a*b\\1", "baaabac", True),
+    # code points vs bytes
+    ("^.$", "é", True), ("^.$", "\U0001F600", True), ("^..$", "\U0001F600", False), ("[^a]", "é", True),
+    ("é+", "éé", True), ("[à-ÿ]", "é", True),
+])
+def test_java_specific_cases(oracle, pat, text, exp):
+    assert oracle.Regex(pat).find(text) == exp
+
+
+@pytest.mark.parametrize("bad", [
+    "a{,2}", "a{", "{", "*a", "+", "?", "(a", "a)", "[a", "a**", "\\", "[z-a]", "a{3,2}", "(?<n>a)(?<n>b)",
+    "\\k<nope>", "(?<=a*)b", "\\y", "\\1", "(?<1a>x)", "a{2", "(?z)a",
+])
+def test_syntax_errors(oracle, bad):
+    with pytest.raises(oracle.OracleSyntaxError):
+        oracle.Regex(bad)
+
+
+@pytest.mark.parametrize("pat", ["\\X", "\\G", "\\p{L}", "(?u)a", "(?U)\\w", "\\b{g}", "\\N{DIGIT ONE}"])
+def test_declared_unsupported(oracle, pat):
+    with pytest.raises(oracle.OracleUnsupported):
+        oracle.Regex(pat)
+
+
+def test_vs_regex_module_sets(oracle):
+    """Nested sets / intersections against the `regex` module (V1 semantics)."""
+    rng = random.Random(5)
+    pats = ["[a-d[m-p]]+", "[a-z&&[def]]+", "[a-z&&[^bc]]+", "[\\w&&[^\\d_]]+", "[^a-y&&[^z]]", "[a-c&&[b-d]&&[c-e]]"]
+    for p in pats:
+        o = oracle.Regex(p)
+        c = rx.compile("(?V1)" + p, rx.ASCII)
+        for _ in range(300):
+            t = "".join(rng.choice("abcdefmnopyz_19 ") for _ in range(rng.randint(0, 6)))
+            assert o.find(t) == (c.search(t) is not None), (p, t)
+
+
+def test_context_regexes_vs_cpython(oracle):
+    """ContextAnalysisService.java:27-34 on realistic lines."""
+    rng = random.Random(11)
+    words = ["ERROR", "error", "Fatal", "CRITICAL", "severe", "WARN", "warning", "Warnings", "xERROR", "ERRORS",
+             "at", "\tat", "  at", "com.foo.Bar$1.run(Bar.java:12)", "NullPointerException", "OutOfMemoryError",
+             "Errors", "exception", "MyError:", "(x)", "()", " ", "INFO", "foo", "-", "\r"]
+    pats = [("\\b(ERROR|FATAL|CRITICAL|SEVERE)\\b", True), ("\\b(WARN|WARNING)\\b", True),
+            ("^\\s*at\\s+[\\w\\.\\$]+\\(.*\\)\\s*$", False), ("\\b\\w*Exception\\b|\\b\\w*Error\\b", False)]
+    for p, ci in pats:
+        o = oracle.Regex(p, oracle.F_CASE_INSENSITIVE if ci else 0)
+        pyp = p.replace(".*", "[^\\n\\r\\x85\\u2028\\u2029]*")
+        pyp = pyp[:-1] + "(?=[\\r\\x85\\u2028\\u2029]?\\Z)" if pyp.endswith("$") else pyp
+        c = re.compile(pyp, re.ASCII | (re.I if ci else 0))
+        for _ in range(2000):
+            t = " ".join(rng.choice(words) for _ in range(rng.randint(0, 5)))
+            if rng.random() < 0.3:
+                t = rng.choice(["\tat ", "   at ", "at "]) + t
+            assert o.find(t) == (c.search(t) is not None), (p, t)
