@@ -1,0 +1,167 @@
+/* liblogparser_b200.so — C ABI of the B200-native hot path of podmortem/log-parser.
+ *
+ * The reference (Java 21 / Quarkus) has no FFI today; this is the seam SURVEY.md §8b cuts into
+ * AnalysisService.analyze(): everything between `data.getLogs().split("\\r?\\n")`
+ * (AnalysisService.java:53) and the end of the N x P scan/score loop (AnalysisService.java:113)
+ * runs behind these entry points. The JVM keeps Parse.java, PatternService.java, the
+ * scoring.* configuration, FrequencyTrackingService's state/clock and the JSON assembly.
+ * Java binds these symbols with Panama FFM; no JNI glue, no callbacks.
+ *
+ * Plain pointers and sizes only. All strings are NUL-terminated UTF-8. The library copies what
+ * it needs from every input before returning. There is NO CPU fallback: every entry point that
+ * computes fails with LP_ERR_CUDA when no CUDA device is usable.
+ */
+#ifndef LOGPARSER_B200_H
+#define LOGPARSER_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LP_OK 0
+#define LP_ERR_INVALID (-1)       /* bad argument                                              */
+#define LP_ERR_SYNTAX (-2)        /* java.util.regex.PatternSyntaxException (AS:64,70,80)      */
+#define LP_ERR_UNSUPPORTED (-3)   /* legal Java regex syntax this build does not implement     */
+#define LP_ERR_CUDA (-4)          /* no device / CUDA runtime failure                          */
+#define LP_ERR_LIMIT (-5)         /* input exceeds a documented limit                          */
+#define LP_ERR_BACKTRACK (-6)     /* backtracking verifier ran out of its step/stack budget    */
+
+typedef struct lp_ctx lp_ctx;
+typedef struct lp_result lp_result;
+
+/* The nine scoring.* keys (src/main/resources/application.properties:5-20; defaults
+ * ScoringService.java:38-51, ContextAnalysisService.java:24, FrequencyTrackingService.java:27-34). */
+typedef struct lp_scoring_cfg {
+    double decay_constant;         /* scoring.proximity.decay-constant            10.0 */
+    int32_t max_window;            /* scoring.proximity.max-window                100  */
+    int32_t time_window_hours;     /* scoring.frequency.time-window-hours         1    */
+    double early_bonus_threshold;  /* scoring.chronological.early-bonus-threshold 0.2  */
+    double max_early_bonus;        /* scoring.chronological.max-early-bonus       2.5  */
+    double penalty_threshold;      /* scoring.chronological.penalty-threshold     0.5  */
+    double max_context_factor;     /* scoring.context.max-context-factor          2.5  */
+    double frequency_threshold;    /* scoring.frequency.threshold                 10.0 */
+    double max_penalty;            /* scoring.frequency.max-penalty               0.8  */
+    /* Optional exp(-d/decay_constant) for d = 0..max_window computed by the caller (Math.exp on
+     * the JVM) so proximity terms are bit-identical to ScoringService.java:177; NULL = libm exp. */
+    const double* decay_lut;
+} lp_scoring_cfg;
+
+typedef struct lp_secondary_desc {      /* SecondaryPattern: SS:172-178, 319 */
+    const char* regex;
+    double weight;
+    int32_t proximity_window;
+} lp_secondary_desc;
+
+typedef struct lp_sequence_desc {       /* SequencePattern / SequenceEvent: SS:207-258 */
+    const char* const* event_regex;
+    uint32_t n_events;
+    double bonus_multiplier;
+} lp_sequence_desc;
+
+/* One Pattern of a PatternSet, flattened in (set, pattern) load order (AS:91-92). */
+typedef struct lp_pattern_desc {
+    const char* id;                 /* NULL/blank: not frequency-tracked (FTS:42-44,65-67)        */
+    const char* primary_regex;      /* primaryPattern.regex (AS:62-65)                            */
+    double confidence;              /* primaryPattern.confidence (SS:65)                          */
+    double severity_multiplier;     /* SEVERITY_MULTIPLIERS lookup done by the caller (SS:30-36,68-69) */
+    int32_t has_context;            /* 0: contextExtraction == null (AS:137-139)                  */
+    int32_t lines_before;           /* contextExtraction.linesBefore (AS:142)                     */
+    int32_t lines_after;            /* contextExtraction.linesAfter  (AS:148)                     */
+    uint32_t n_secondaries;
+    const lp_secondary_desc* secondaries;
+    uint32_t n_sequences;
+    const lp_sequence_desc* sequences;
+} lp_pattern_desc;
+
+/* Column views of one analysis result; pointers stay valid until lp_result_free(). */
+typedef struct lp_result_view {
+    uint64_t n_logs;
+    uint64_t n_events;              /* all logs, grouped by log in input order                    */
+    const uint64_t* log_n_lines;    /* [n_logs]  logLines.length per log (AS:53,170)              */
+    const uint64_t* log_event_begin;/* [n_logs+1] events of log k are [begin[k], begin[k+1])      */
+    const uint32_t* line;           /* [n_events] 1-based line number within its log (AS:101)     */
+    const uint32_t* pattern;        /* [n_events] flat pattern index (AS:102)                     */
+    const double* score;            /* [n_events] MatchedEvent.score (AS:106-107)                 */
+    const uint32_t* rank;           /* [n_events] position when sorted by score desc, ties by     */
+                                    /*   discovery order, within the event's log (extension)      */
+    const double* factors;          /* [n_events*7] base,sev,chrono,prox,temporal,ctx,penalty; NULL unless LP_OPT_FACTORS */
+    const uint64_t* freq_delta;     /* [n_patterns] events per pattern in this call (FTS:41-56)   */
+    uint64_t n_patterns;
+    const uint32_t* line_start;     /* [total_lines+1] byte offsets, NULL unless LP_OPT_LINE_OFFSETS */
+    const uint32_t* line_end;       /* [total_lines]                                              */
+    uint64_t total_lines;
+} lp_result_view;
+
+enum {
+    LP_OPT_FACTORS = 1,        /* also return the seven factors per event                        */
+    LP_OPT_LINE_OFFSETS = 2,   /* also return line_start/line_end for context slicing (AS:132-156) */
+    LP_OPT_NO_RANK = 4         /* skip the ranking sort                                          */
+};
+
+/* ---- lifecycle ------------------------------------------------------------------------- */
+/* Carries the scoring.* values into the library and binds it to one CUDA device
+ * (replaces the @ConfigProperty injection of SS:38-51, CAS:24, FTS:27-34). NULL on failure. */
+lp_ctx* lp_create(const lp_scoring_cfg* cfg, int device);
+void lp_destroy(lp_ctx* ctx);
+/* Thread-local message for the last failing call on this thread. */
+const char* lp_last_error(void);
+const char* lp_version(void);
+
+/* Replaces the per-request compile block AS:56-86 (and the static context regexes CAS:27-34):
+ * compiles every primary / secondary / sequence-event regex once and uploads the device
+ * tables. On LP_ERR_SYNTAX / LP_ERR_UNSUPPORTED, *bad_pattern (if not NULL) receives the flat
+ * index of the offending pattern. Not concurrent with lp_analyze* on the same ctx. */
+int lp_load_patterns(lp_ctx* ctx, const lp_pattern_desc* patterns, size_t n_patterns, int64_t* bad_pattern);
+
+/* ---- the hot path ------------------------------------------------------------------------ */
+/* Replaces AS:53-113 for one request: split, scan, score. `log` is host memory (UTF-8 of
+ * PodFailureData.logs). prior_count[p] = matches of pattern p already inside the sliding
+ * frequency window at request start (FTS state stays on the JVM); NULL = all zero. */
+int lp_analyze(lp_ctx* ctx, const uint8_t* log, size_t len, const uint64_t* prior_count,
+               int options, lp_result** out);
+
+/* Same, with the log already resident in device memory (`d_log` is a device pointer). */
+int lp_analyze_device(lp_ctx* ctx, const uint8_t* d_log, size_t len, const uint64_t* prior_count,
+                      int options, lp_result** out);
+
+/* A batch of independent requests, processed as the reference would process them one after the
+ * other in input order (frequency state carried from log k to log k+1). `logs` is the plain
+ * concatenation of the logs; log k is bytes [offsets[k], offsets[k+1]). Total size < 4 GiB. */
+int lp_analyze_batch(lp_ctx* ctx, const uint8_t* logs, const uint64_t* offsets, size_t n_logs,
+                     const uint64_t* prior_count, int options, lp_result** out);
+int lp_analyze_batch_device(lp_ctx* ctx, const uint8_t* d_logs, const uint64_t* offsets, size_t n_logs,
+                            const uint64_t* prior_count, int options, lp_result** out);
+
+/* Two-phase form for sharding a batch over several GPUs (one process per GPU): phase 1 scans
+ * this rank's logs and returns its per-pattern event counts; the host exchanges counts between
+ * ranks (NCCL all-gather) and passes the exclusive prefix over lower ranks (+ the window's
+ * prior counts) to phase 2, which scores. lp_analyze_batch* == scan followed by score. */
+int lp_batch_scan_device(lp_ctx* ctx, const uint8_t* d_logs, const uint64_t* offsets, size_t n_logs,
+                         int options, uint64_t* counts_out /* [n_patterns] */);
+int lp_batch_score(lp_ctx* ctx, const uint64_t* prior_count, lp_result** out);
+
+int lp_result_get(const lp_result* r, lp_result_view* view);
+void lp_result_free(lp_result* r);
+
+/* ---- measurement ------------------------------------------------------------------------- */
+typedef struct lp_timings {
+    float total_ms;        /* first to last kernel of the last lp_analyze* call (CUDA events)     */
+    float scan_ms;         /* the line-split + prefilter kernel (the dominant streaming kernel)   */
+    float verify_ms;       /* candidate confirmation + DFA / backtracking verification            */
+    float score_ms;        /* sorting, event assembly, scoring, ranking                           */
+    float h2d_ms;          /* host->device copy of the log (lp_analyze / lp_analyze_batch only)   */
+    uint64_t kernel_launches;   /* kernels of this library launched by the last call             */
+    uint64_t scan_bytes;        /* algorithmic bytes of the scan kernel: B + 4(N+1) + 8M          */
+    uint64_t candidates;        /* gram-filter hits handed to confirmation                        */
+    uint64_t verify_tasks;      /* (line, regex) pairs verified                                   */
+} lp_timings;
+int lp_get_timings(const lp_ctx* ctx, lp_timings* out);
+/* The cudaStream_t all kernels and copies of this context are issued on (for callers that order
+ * their own work or CUDA events against it). */
+void* lp_stream(const lp_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LOGPARSER_B200_H */

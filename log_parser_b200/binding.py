@@ -1,0 +1,387 @@
+"""ctypes binding of liblogparser_b200.so — the same calls, in the same order, that the Java 21
+host makes through Panama FFM. There is no Python/CPU fallback: if the shared
+library is missing or no CUDA device is usable, the calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from dataclasses import dataclass
+from typing import Optional, Sequence
+
+import numpy as np
+
+from .model import PatternSpec, ScoringConfig, severity_multiplier
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "liblogparser_b200.so")
+
+LP_OK, LP_ERR_INVALID, LP_ERR_SYNTAX, LP_ERR_UNSUPPORTED, LP_ERR_CUDA, LP_ERR_LIMIT, LP_ERR_BACKTRACK = 0, -1, -2, -3, -4, -5, -6
+OPT_FACTORS, OPT_LINE_OFFSETS, OPT_NO_RANK = 1, 2, 4
+
+
+class LpError(RuntimeError):
+    def __init__(self, code: int, msg: str, bad_pattern: int = -1):
+        super().__init__(f"[{code}] {msg}")
+        self.code = code
+        self.bad_pattern = bad_pattern
+
+
+class PatternSyntaxError(LpError):
+    """java.util.regex.PatternSyntaxException (AnalysisService.java:64,70,80 -> HTTP 500)."""
+
+
+class UnsupportedRegexError(LpError):
+    pass
+
+
+class ScoringCfg(C.Structure):
+    _fields_ = [
+        ("decay_constant", C.c_double), ("max_window", C.c_int32), ("time_window_hours", C.c_int32),
+        ("early_bonus_threshold", C.c_double), ("max_early_bonus", C.c_double), ("penalty_threshold", C.c_double),
+        ("max_context_factor", C.c_double), ("frequency_threshold", C.c_double), ("max_penalty", C.c_double),
+        ("decay_lut", C.POINTER(C.c_double)),
+    ]
+
+
+class SecondaryDesc(C.Structure):
+    _fields_ = [("regex", C.c_char_p), ("weight", C.c_double), ("proximity_window", C.c_int32)]
+
+
+class SequenceDesc(C.Structure):
+    _fields_ = [("event_regex", C.POINTER(C.c_char_p)), ("n_events", C.c_uint32), ("bonus_multiplier", C.c_double)]
+
+
+class PatternDesc(C.Structure):
+    _fields_ = [
+        ("id", C.c_char_p), ("primary_regex", C.c_char_p), ("confidence", C.c_double),
+        ("severity_multiplier", C.c_double), ("has_context", C.c_int32), ("lines_before", C.c_int32),
+        ("lines_after", C.c_int32), ("n_secondaries", C.c_uint32), ("secondaries", C.POINTER(SecondaryDesc)),
+        ("n_sequences", C.c_uint32), ("sequences", C.POINTER(SequenceDesc)),
+    ]
+
+
+class ResultView(C.Structure):
+    _fields_ = [
+        ("n_logs", C.c_uint64), ("n_events", C.c_uint64), ("log_n_lines", C.POINTER(C.c_uint64)),
+        ("log_event_begin", C.POINTER(C.c_uint64)), ("line", C.POINTER(C.c_uint32)), ("pattern", C.POINTER(C.c_uint32)),
+        ("score", C.POINTER(C.c_double)), ("rank", C.POINTER(C.c_uint32)), ("factors", C.POINTER(C.c_double)),
+        ("freq_delta", C.POINTER(C.c_uint64)), ("n_patterns", C.c_uint64), ("line_start", C.POINTER(C.c_uint32)),
+        ("line_end", C.POINTER(C.c_uint32)), ("total_lines", C.c_uint64),
+    ]
+
+
+class Timings(C.Structure):
+    _fields_ = [
+        ("total_ms", C.c_float), ("scan_ms", C.c_float), ("verify_ms", C.c_float), ("score_ms", C.c_float),
+        ("h2d_ms", C.c_float), ("kernel_launches", C.c_uint64), ("scan_bytes", C.c_uint64),
+        ("candidates", C.c_uint64), ("verify_tasks", C.c_uint64),
+    ]
+
+
+# every symbol include/logparser_b200.h declares
+EXPORTS = [
+    "lp_create", "lp_destroy", "lp_last_error", "lp_version", "lp_load_patterns", "lp_analyze", "lp_analyze_device",
+    "lp_analyze_batch", "lp_analyze_batch_device", "lp_batch_scan_device", "lp_batch_score", "lp_result_get",
+    "lp_result_free", "lp_get_timings", "lp_stream",
+]
+
+_lib = None
+
+
+def load_library() -> C.CDLL:
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(SO_PATH):
+        raise ImportError(
+            f"{SO_PATH} is missing: build it with `python -m log_parser_b200.build` "
+            "(the B200 path has no CPU fallback)")
+    L = C.CDLL(SO_PATH)
+    vp, u8p, u64p = C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64)
+    L.lp_create.restype = vp
+    L.lp_create.argtypes = [C.POINTER(ScoringCfg), C.c_int]
+    L.lp_destroy.argtypes = [vp]
+    L.lp_last_error.restype = C.c_char_p
+    L.lp_version.restype = C.c_char_p
+    L.lp_load_patterns.argtypes = [vp, C.POINTER(PatternDesc), C.c_size_t, C.POINTER(C.c_int64)]
+    L.lp_analyze.argtypes = [vp, u8p, C.c_size_t, u64p, C.c_int, C.POINTER(vp)]
+    L.lp_analyze_device.argtypes = [vp, u8p, C.c_size_t, u64p, C.c_int, C.POINTER(vp)]
+    L.lp_analyze_batch.argtypes = [vp, u8p, u64p, C.c_size_t, u64p, C.c_int, C.POINTER(vp)]
+    L.lp_analyze_batch_device.argtypes = [vp, u8p, u64p, C.c_size_t, u64p, C.c_int, C.POINTER(vp)]
+    L.lp_batch_scan_device.argtypes = [vp, u8p, u64p, C.c_size_t, C.c_int, u64p]
+    L.lp_batch_score.argtypes = [vp, u64p, C.POINTER(vp)]
+    L.lp_result_get.argtypes = [vp, C.POINTER(ResultView)]
+    L.lp_result_free.argtypes = [vp]
+    L.lp_get_timings.argtypes = [vp, C.POINTER(Timings)]
+    L.lp_stream.restype = vp
+    L.lp_stream.argtypes = [vp]
+    # host-compiler introspection (CPU-only test tier)
+    L.lp_debug_rx_compile.restype = vp
+    L.lp_debug_rx_compile.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_char_p, C.c_size_t, C.POINTER(C.c_int)]
+    L.lp_debug_rx_free.argtypes = [vp]
+    L.lp_debug_rx_is_dfa.argtypes = [vp]
+    L.lp_debug_rx_states.restype = C.c_uint32
+    L.lp_debug_rx_states.argtypes = [vp]
+    L.lp_debug_rx_match.argtypes = [vp, C.c_char_p, C.c_size_t]
+    L.lp_debug_rx_literals.restype = C.c_size_t
+    L.lp_debug_rx_literals.argtypes = [vp, C.c_char_p, C.c_size_t]
+    _lib = L
+    return L
+
+
+def _last_error() -> str:
+    return load_library().lp_last_error().decode("utf-8", "replace")
+
+
+def _raise(code: int, bad: int = -1):
+    msg = _last_error()
+    if code == LP_ERR_SYNTAX:
+        raise PatternSyntaxError(code, msg, bad)
+    if code == LP_ERR_UNSUPPORTED:
+        raise UnsupportedRegexError(code, msg, bad)
+    raise LpError(code, msg, bad)
+
+
+class PatternTable:
+    """lp_pattern_desc[] built from PatternSpec objects in (set, pattern) load order."""
+
+    def __init__(self, patterns: Sequence[PatternSpec]):
+        self.n = len(patterns)
+        self._keep = []
+        self.arr = (PatternDesc * max(1, self.n))()
+        for i, p in enumerate(patterns):
+            secs = (SecondaryDesc * max(1, len(p.secondaries)))()
+            for j, s in enumerate(p.secondaries):
+                secs[j] = SecondaryDesc(s.regex.encode("utf-8"), s.weight, s.proximity_window)
+            seqs = (SequenceDesc * max(1, len(p.sequences)))()
+            for j, s in enumerate(p.sequences):
+                ev = (C.c_char_p * max(1, len(s.events)))(*[e.encode("utf-8") for e in s.events])
+                self._keep.append(ev)
+                seqs[j] = SequenceDesc(C.cast(ev, C.POINTER(C.c_char_p)), len(s.events), s.bonus_multiplier)
+            self._keep += [secs, seqs]
+            self.arr[i] = PatternDesc(
+                None if p.id is None else p.id.encode("utf-8"), p.primary_regex.encode("utf-8"), p.confidence,
+                severity_multiplier(p.severity), 1 if p.has_context else 0,
+                p.lines_before if p.has_context else 0, p.lines_after if p.has_context else 0,
+                len(p.secondaries), C.cast(secs, C.POINTER(SecondaryDesc)),
+                len(p.sequences), C.cast(seqs, C.POINTER(SequenceDesc)))
+
+
+@dataclass
+class Result:
+    n_logs: int
+    log_n_lines: np.ndarray       # uint64 [n_logs]
+    log_event_begin: np.ndarray   # uint64 [n_logs+1]
+    line: np.ndarray              # uint32, 1-based within the log
+    pattern: np.ndarray           # uint32 flat pattern index
+    score: np.ndarray             # float64
+    rank: np.ndarray              # uint32
+    freq_delta: np.ndarray        # uint64 [n_patterns]
+    factors: Optional[np.ndarray] = None
+    line_start: Optional[np.ndarray] = None
+    line_end: Optional[np.ndarray] = None
+
+    @property
+    def n_lines(self) -> int:
+        return int(self.log_n_lines[0])
+
+    @property
+    def n_events(self) -> int:
+        return int(self.line.shape[0])
+
+
+def _arr(ptr, n, dtype):
+    if n == 0 or not ptr:
+        return np.zeros(0, dtype)
+    return np.ctypeslib.as_array(ptr, (n,)).astype(dtype, copy=True)
+
+
+class LogParser:
+    """One lp_ctx: scoring.* configuration + loaded pattern set bound to one CUDA device."""
+
+    def __init__(self, cfg: Optional[ScoringConfig] = None, device: int = 0, decay_lut: Optional[np.ndarray] = None):
+        self.L = load_library()
+        cfg = cfg or ScoringConfig()
+        self.cfg = cfg
+        lut_p = None
+        if decay_lut is not None:
+            self._lut = np.ascontiguousarray(decay_lut, dtype=np.float64)
+            assert self._lut.shape[0] >= cfg.max_window + 1
+            lut_p = self._lut.ctypes.data_as(C.POINTER(C.c_double))
+        sc = ScoringCfg(cfg.decay_constant, cfg.max_window, cfg.time_window_hours, cfg.early_bonus_threshold,
+                        cfg.max_early_bonus, cfg.penalty_threshold, cfg.max_context_factor, cfg.frequency_threshold,
+                        cfg.max_penalty, lut_p)
+        self.h = self.L.lp_create(C.byref(sc), device)
+        if not self.h:
+            raise LpError(LP_ERR_CUDA, _last_error())
+        self.n_patterns = 0
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.L.lp_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def load_patterns(self, patterns: Sequence[PatternSpec]):
+        t = PatternTable(patterns)
+        bad = C.c_int64(-1)
+        rc = self.L.lp_load_patterns(self.h, t.arr, t.n, C.byref(bad))
+        if rc != LP_OK:
+            _raise(rc, bad.value)
+        self.n_patterns = t.n
+
+    # ---- helpers
+    def _prior(self, prior_count):
+        if prior_count is None:
+            return None, None
+        a = np.ascontiguousarray(prior_count, dtype=np.uint64)
+        assert a.shape[0] == self.n_patterns
+        return a, a.ctypes.data_as(C.POINTER(C.c_uint64))
+
+    def _take(self, out) -> Result:
+        v = ResultView()
+        rc = self.L.lp_result_get(out, C.byref(v))
+        if rc != LP_OK:
+            _raise(rc)
+        m, nl = v.n_events, v.n_logs
+        res = Result(
+            n_logs=nl, log_n_lines=_arr(v.log_n_lines, nl, np.uint64), log_event_begin=_arr(v.log_event_begin, nl + 1, np.uint64),
+            line=_arr(v.line, m, np.uint32), pattern=_arr(v.pattern, m, np.uint32), score=_arr(v.score, m, np.float64),
+            rank=_arr(v.rank, m, np.uint32), freq_delta=_arr(v.freq_delta, v.n_patterns, np.uint64))
+        if v.factors:
+            res.factors = _arr(v.factors, m * 7, np.float64).reshape(m, 7)
+        if v.line_start:
+            res.line_start = _arr(v.line_start, v.total_lines + 1, np.uint32)
+            res.line_end = _arr(v.line_end, v.total_lines, np.uint32)
+        self.L.lp_result_free(out)
+        return res
+
+    # ---- the hot path
+    def analyze(self, log, prior_count=None, options: int = 0) -> Result:
+        """lp_analyze: host buffer in, events out (replaces AnalysisService.java:53-113)."""
+        buf = np.frombuffer(log, dtype=np.uint8) if not isinstance(log, np.ndarray) else log
+        keep, pp = self._prior(prior_count)
+        out = C.c_void_p()
+        rc = self.L.lp_analyze(self.h, buf.ctypes.data if buf.size else None, buf.size, pp, options, C.byref(out))
+        if rc != LP_OK:
+            _raise(rc)
+        return self._take(out)
+
+    def analyze_host_ptr(self, ptr: int, nbytes: int, prior_count=None, options: int = 0) -> Result:
+        keep, pp = self._prior(prior_count)
+        out = C.c_void_p()
+        rc = self.L.lp_analyze(self.h, ptr, nbytes, pp, options, C.byref(out))
+        if rc != LP_OK:
+            _raise(rc)
+        return self._take(out)
+
+    def analyze_device(self, dev_ptr: int, nbytes: int, prior_count=None, options: int = 0) -> Result:
+        keep, pp = self._prior(prior_count)
+        out = C.c_void_p()
+        rc = self.L.lp_analyze_device(self.h, dev_ptr, nbytes, pp, options, C.byref(out))
+        if rc != LP_OK:
+            _raise(rc)
+        return self._take(out)
+
+    @staticmethod
+    def _offsets(offsets):
+        a = np.ascontiguousarray(offsets, dtype=np.uint64)
+        return a, a.ctypes.data_as(C.POINTER(C.c_uint64))
+
+    def analyze_batch(self, logs: Sequence[bytes], prior_count=None, options: int = 0) -> Result:
+        blob = b"".join(logs)
+        off = np.zeros(len(logs) + 1, np.uint64)
+        np.cumsum([len(x) for x in logs], out=off[1:])
+        buf = np.frombuffer(blob, dtype=np.uint8)
+        oa, op = self._offsets(off)
+        keep, pp = self._prior(prior_count)
+        out = C.c_void_p()
+        rc = self.L.lp_analyze_batch(self.h, buf.ctypes.data if buf.size else None, op, len(logs), pp, options, C.byref(out))
+        if rc != LP_OK:
+            _raise(rc)
+        return self._take(out)
+
+    def analyze_batch_device(self, dev_ptr: int, offsets, prior_count=None, options: int = 0) -> Result:
+        oa, op = self._offsets(offsets)
+        keep, pp = self._prior(prior_count)
+        out = C.c_void_p()
+        rc = self.L.lp_analyze_batch_device(self.h, dev_ptr, op, len(oa) - 1, pp, options, C.byref(out))
+        if rc != LP_OK:
+            _raise(rc)
+        return self._take(out)
+
+    def batch_scan_device(self, dev_ptr: int, offsets, options: int = 0) -> np.ndarray:
+        oa, op = self._offsets(offsets)
+        counts = np.zeros(max(1, self.n_patterns), np.uint64)
+        rc = self.L.lp_batch_scan_device(self.h, dev_ptr, op, len(oa) - 1, options, counts.ctypes.data_as(C.POINTER(C.c_uint64)))
+        if rc != LP_OK:
+            _raise(rc)
+        return counts[: self.n_patterns]
+
+    def batch_score(self, prior_count=None) -> Result:
+        keep, pp = self._prior(prior_count)
+        out = C.c_void_p()
+        rc = self.L.lp_batch_score(self.h, pp, C.byref(out))
+        if rc != LP_OK:
+            _raise(rc)
+        return self._take(out)
+
+    def stream_ptr(self) -> int:
+        return int(self.L.lp_stream(self.h) or 0)
+
+    def timings(self) -> dict:
+        t = Timings()
+        self.L.lp_get_timings(self.h, C.byref(t))
+        return {f[0]: getattr(t, f[0]) for f in Timings._fields_}
+
+
+class DebugRegex:
+    """Host-compiler introspection for the CPU-only test tier (never part of analyze)."""
+
+    def __init__(self, pattern: str, flags: int = 0, force_vm: bool = False):
+        self.L = load_library()
+        err = C.create_string_buffer(512)
+        kind = C.c_int(0)
+        self.h = self.L.lp_debug_rx_compile(pattern.encode("utf-8"), flags, 1 if force_vm else 0, err, 512, C.byref(kind))
+        if not self.h:
+            msg = err.value.decode("utf-8", "replace")
+            if kind.value == 1:
+                raise PatternSyntaxError(LP_ERR_SYNTAX, msg)
+            if kind.value == 2:
+                raise UnsupportedRegexError(LP_ERR_UNSUPPORTED, msg)
+            raise LpError(LP_ERR_INVALID, msg)
+
+    @property
+    def is_dfa(self) -> bool:
+        return bool(self.L.lp_debug_rx_is_dfa(self.h))
+
+    @property
+    def size(self) -> int:
+        return self.L.lp_debug_rx_states(self.h)
+
+    def match(self, text) -> int:
+        b = text.encode("utf-8") if isinstance(text, str) else bytes(text)
+        return self.L.lp_debug_rx_match(self.h, b, len(b))
+
+    def literals(self):
+        n = self.L.lp_debug_rx_literals(self.h, None, 0)
+        buf = C.create_string_buffer(n + 1)
+        self.L.lp_debug_rx_literals(self.h, buf, n + 1)
+        out = []
+        for ln in buf.raw[:n].split(b"\n"):
+            if ln:
+                out.append((ln[:1] == b"i", ln[2:]))
+        return out
+
+    def __del__(self):
+        try:
+            if self.h:
+                self.L.lp_debug_rx_free(self.h)
+        except Exception:
+            pass

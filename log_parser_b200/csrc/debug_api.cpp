@@ -1,0 +1,84 @@
+// Host-compiler introspection exported from liblogparser_b200.so for the CPU-only test tier
+// (`pytest -m "not gpu"`): lets the tests diff the exact tables the device walks against the
+// oracle without a GPU. Never called by lp_analyze*; it is not a CPU fallback of the product path.
+#include <cstring>
+#include <string>
+
+#include "rx.h"
+#include "vm.h"
+
+using namespace lpx;
+
+namespace {
+struct DebugRx {
+    ParsedRegex parsed;
+    bool has_dfa = false;
+    Dfa dfa;
+    bool has_vm = false;
+    VmProgram vm;
+    std::vector<Literal> lits;
+};
+void put_err(char* err, size_t n, const std::string& m) {
+    if (!err || !n) return;
+    size_t k = std::min(n - 1, m.size());
+    memcpy(err, m.data(), k);
+    err[k] = 0;
+}
+}  // namespace
+
+extern "C" {
+
+// kind: 0 ok, 1 PatternSyntaxException, 2 unsupported construct, 3 internal
+void* lp_debug_rx_compile(const char* regex, int flags, int force_vm, char* err, size_t errlen, int* kind) {
+    if (kind) *kind = 0;
+    try {
+        DebugRx* d = new DebugRx();
+        try {
+            d->parsed = parse_java_regex(regex, flags);
+            if (d->parsed.regular && !force_vm) d->has_dfa = build_dfa(*d->parsed.root, d->dfa);
+            if (!d->has_dfa) { build_vm(d->parsed, d->vm); d->has_vm = true; }
+            d->lits = required_literals(*d->parsed.root, 4);
+        } catch (...) { delete d; throw; }
+        return d;
+    } catch (const RegexSyntaxError& e) {
+        if (kind) *kind = 1;
+        put_err(err, errlen, std::string(e.what()) + " near index " + std::to_string(e.index));
+    } catch (const RegexUnsupported& e) {
+        if (kind) *kind = 2;
+        put_err(err, errlen, std::string("unsupported: ") + e.what());
+    } catch (const std::exception& e) {
+        if (kind) *kind = 3;
+        put_err(err, errlen, e.what());
+    }
+    return nullptr;
+}
+void lp_debug_rx_free(void* h) { delete static_cast<DebugRx*>(h); }
+int lp_debug_rx_is_dfa(void* h) { return static_cast<DebugRx*>(h)->has_dfa ? 1 : 0; }
+uint32_t lp_debug_rx_states(void* h) {
+    DebugRx* d = static_cast<DebugRx*>(h);
+    return d->has_dfa ? d->dfa.n_states() : (uint32_t)d->vm.code.size();
+}
+// Walks the same tables with the same loop as the device verifier. Returns 1/0, or <0 for a
+// backtracking-budget overflow (the device reports the same condition as an error).
+int lp_debug_rx_match(void* h, const uint8_t* s, size_t n) {
+    DebugRx* d = static_cast<DebugRx*>(h);
+    if (d->has_dfa) return d->dfa.match(s, n) ? 1 : 0;
+    return vm_match_host(d->vm, s, n);
+}
+size_t lp_debug_rx_literals(void* h, char* buf, size_t cap) {
+    DebugRx* d = static_cast<DebugRx*>(h);
+    std::string out;
+    for (const auto& l : d->lits) {
+        out += l.icase ? "i:" : "s:";
+        out += l.bytes;
+        out.push_back('\n');
+    }
+    if (buf && cap) {
+        size_t k = std::min(cap - 1, out.size());
+        memcpy(buf, out.data(), k);
+        buf[k] = 0;
+    }
+    return out.size();
+}
+
+}  // extern "C"

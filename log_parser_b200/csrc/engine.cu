@@ -1,0 +1,1327 @@
+// liblogparser_b200.so: kernels + host orchestration + the C ABI of include/logparser_b200.h.
+// See kernels.cuh for the kernel -> reference map. No CPU fallback exists in this file.
+#include <cub/cub.cuh>
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <memory>
+#include <mutex>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "../../include/logparser_b200.h"
+#include "kernels.cuh"
+#include "plan.h"
+
+using namespace lpk;
+
+// ============================================================================================
+//                                         device code
+// ============================================================================================
+namespace {
+
+__device__ __forceinline__ uint32_t zero_byte_flags(uint32_t x) {
+    // exact per-byte "== 0" detector: bit 7 of each byte set iff that byte of x is zero
+    uint32_t t = ((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x;
+    return ~(t | 0x7F7F7F7Fu);
+}
+__device__ __forceinline__ uint32_t nl_mask4(uint32_t w) {
+    uint32_t m = (zero_byte_flags(w ^ 0x0A0A0A0Au) >> 7);
+    return ((m * 0x00204081u) >> 21) & 0xFu;
+}
+__device__ __forceinline__ uint32_t nl_mask16(const uint4& v) {
+    return nl_mask4(v.x) | (nl_mask4(v.y) << 4) | (nl_mask4(v.z) << 8) | (nl_mask4(v.w) << 12);
+}
+
+// 16 bytes at `pos`; bytes at or beyond `len` read as zero. `text` is 16-byte aligned.
+__device__ __forceinline__ uint4 load16(const uint8_t* __restrict__ text, uint64_t pos, uint64_t len) {
+    if (pos + 16 <= len) return __ldg(reinterpret_cast<const uint4*>(text + pos));
+    uint32_t w[4] = {0, 0, 0, 0};
+    for (int i = 0; i < 16; ++i)
+        if (pos + i < len) w[i >> 2] |= (uint32_t)text[pos + i] << ((i & 3) * 8);
+    return make_uint4(w[0], w[1], w[2], w[3]);
+}
+__device__ __forceinline__ uint32_t load4_safe(const uint8_t* __restrict__ text, uint64_t pos, uint64_t len) {
+    if (pos + 4 <= len) return __ldg(reinterpret_cast<const uint32_t*>(text + pos));  // pos is 4-aligned here
+    uint32_t w = 0;
+    for (int i = 0; i < 4; ++i)
+        if (pos + i < len) w |= (uint32_t)text[pos + i] << (i * 8);
+    return w;
+}
+
+// number of elements of a[0..n) that are <= v   (upper bound)
+template <class T>
+__device__ __forceinline__ uint32_t upper_bound_dev(const T* __restrict__ a, uint32_t n, T v) {
+    uint32_t lo = 0, hi = n;
+    while (lo < hi) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (a[mid] <= v) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+// number of elements of a[0..n) that are < v   (lower bound)
+template <class T>
+__device__ __forceinline__ uint32_t lower_bound_dev(const T* __restrict__ a, uint32_t n, T v) {
+    uint32_t lo = 0, hi = n;
+    while (lo < hi) {
+        uint32_t mid = (lo + hi) >> 1;
+        if (a[mid] < v) lo = mid + 1; else hi = mid;
+    }
+    return lo;
+}
+
+// ------------------------------------------------------------------ K1: newline count per tile
+__global__ void __launch_bounds__(SCAN_THREADS) k_count_nl(const uint8_t* __restrict__ text, uint64_t len,
+                                                             uint32_t n_tiles, uint32_t* __restrict__ tile_counts) {
+    __shared__ uint32_t warp_sum[SCAN_THREADS / 32];
+    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const uint64_t base = (uint64_t)tile * TILE_BYTES + (uint64_t)threadIdx.x * 16;
+        uint32_t cnt = 0;
+        uint4 v[SCAN_ITERS];
+#pragma unroll
+        for (int it = 0; it < SCAN_ITERS; ++it) {
+            uint64_t pos = base + (uint64_t)it * SCAN_THREADS * 16;
+            v[it] = pos < len ? load16(text, pos, len) : make_uint4(0, 0, 0, 0);
+        }
+#pragma unroll
+        for (int it = 0; it < SCAN_ITERS; ++it) cnt += __popc(nl_mask16(v[it]));
+        for (int o = 16; o; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+        if ((threadIdx.x & 31) == 0) warp_sum[threadIdx.x >> 5] = cnt;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint32_t s = 0;
+            for (int w = 0; w < SCAN_THREADS / 32; ++w) s += warp_sum[w];
+            tile_counts[tile] = s;
+        }
+        __syncthreads();
+    }
+}
+
+// exclusive scan of tile counts (one block); also publishes the total
+__global__ void __launch_bounds__(1024) k_scan_tiles(uint32_t* __restrict__ tile_counts, uint32_t n_tiles, Counters* ctr) {
+    __shared__ uint32_t warp_tot[32];
+    __shared__ uint32_t carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < n_tiles; base += 1024) {
+        uint32_t i = base + threadIdx.x;
+        uint32_t v = i < n_tiles ? tile_counts[i] : 0;
+        uint32_t inc = v;
+        for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, inc, o); if ((threadIdx.x & 31) >= o) inc += t; }
+        if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = inc;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            uint32_t w = warp_tot[threadIdx.x];
+            uint32_t wi = w;
+            for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, wi, o); if (threadIdx.x >= o) wi += t; }
+            warp_tot[threadIdx.x] = wi - w;  // exclusive
+        }
+        __syncthreads();
+        uint32_t excl = carry + warp_tot[threadIdx.x >> 5] + inc - v;
+        if (i < n_tiles) tile_counts[i] = excl;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = excl + v;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) ctr->total_nl = carry;
+}
+
+// ------------------------------------------------------------------ K2: line offsets + gram prefilter
+// One pass over the log: every '\n' yields line_end[g] / line_start[g+1] (with the \r?\n rule and
+// the log boundaries of a batch), and every 4-byte window is tested against the literal-gram
+// bitmap held in shared memory; hits are appended to the candidate queue (warp-aggregated atomics).
+struct ScanArgs {
+    const uint8_t* text;
+    uint64_t len;
+    uint32_t n_tiles;
+    const uint32_t* tile_prefix;      // exclusive newline count before each tile
+    const uint64_t* log_off;          // [n_logs+1]
+    uint32_t n_logs;
+    uint32_t* line_start;             // [G]
+    uint32_t* line_end;               // [G]
+    uint32_t* first_line;             // [n_logs+1]
+    const uint32_t* bitmap;           // GRAM_WORDS words
+    uint32_t* cand;                   // candidate byte positions
+    uint32_t cand_cap;
+    Counters* ctr;
+    int use_filter;
+};
+
+__global__ void __launch_bounds__(SCAN_THREADS) k_lines_filter(ScanArgs a) {
+    extern __shared__ uint32_t s_bitmap[];
+    __shared__ uint32_t s_warp[2][SCAN_THREADS / 32];
+    __shared__ uint32_t s_k0, s_inner, s_events;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+
+    if (a.use_filter) {
+        const uint4* src = reinterpret_cast<const uint4*>(a.bitmap);
+        uint4* dst = reinterpret_cast<uint4*>(s_bitmap);
+        for (uint32_t i = threadIdx.x; i < GRAM_WORDS / 4; i += SCAN_THREADS) dst[i] = __ldg(src + i);
+    }
+    __syncthreads();
+
+    for (uint32_t tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+        const uint64_t tile_base = (uint64_t)tile * TILE_BYTES;
+        const uint64_t tile_end = tile_base + TILE_BYTES;
+        if (threadIdx.x == 0) {
+            // log containing the first byte of the tile; any boundary strictly inside; any boundary event in [base,end)
+            uint32_t j0 = upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, tile_base);
+            s_k0 = j0 - 1;
+            s_inner = (j0 <= a.n_logs && a.log_off[j0] < tile_end) ? 1u : 0u;
+            uint32_t j1 = lower_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, tile_base);
+            s_events = (j1 <= a.n_logs && a.log_off[j1] < tile_end) ? 1u : 0u;
+        }
+        __syncthreads();
+        const uint32_t k0 = s_k0;
+        const bool inner = s_inner != 0, events = s_events != 0;
+        uint32_t running = a.tile_prefix[tile];
+
+#pragma unroll 1
+        for (int it = 0; it < SCAN_ITERS; ++it) {
+            const uint64_t pos = tile_base + ((uint64_t)it * SCAN_THREADS + threadIdx.x) * 16;
+            uint4 v = make_uint4(0, 0, 0, 0);
+            if (pos < a.len) v = load16(a.text, pos, a.len);
+            const uint32_t nlm = nl_mask16(v);
+            const uint32_t cnt = __popc(nlm);
+            // block-wide exclusive prefix of newline counts
+            uint32_t inc = cnt;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+            if (lane == 31) s_warp[it & 1][warp] = inc;
+            __syncthreads();
+            uint32_t wbase = 0, btotal = 0;
+#pragma unroll
+            for (int w = 0; w < SCAN_THREADS / 32; ++w) { uint32_t t = s_warp[it & 1][w]; if (w < warp) wbase += t; btotal += t; }
+            const uint32_t excl = running + wbase + inc - cnt;   // newlines before this thread's 16 bytes
+            running += btotal;
+
+            // ---- newline events
+            uint32_t m = nlm;
+            while (m) {
+                const int i = __ffs(m) - 1;
+                m &= m - 1;
+                const uint64_t p = pos + i;
+                uint32_t k = k0;
+                if (inner) k = upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, p) - 1;
+                const uint32_t g = excl + __popc(nlm & ((1u << i) - 1u)) + k;
+                const bool cr = p > a.log_off[k] && a.text[p - 1] == '\r';
+                a.line_end[g] = (uint32_t)(p - (cr ? 1 : 0));
+                a.line_start[g + 1] = (uint32_t)(p + 1);
+            }
+            // ---- log boundary events (start of log k / end of log k-1) falling in this thread's 16 bytes
+            if (events && pos <= a.len) {
+                uint32_t j = lower_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, pos);
+                while (j <= a.n_logs && a.log_off[j] < pos + 16) {
+                    const uint64_t b = a.log_off[j];
+                    const uint32_t nlb = excl + __popc(nlm & ((1u << (uint32_t)(b - pos)) - 1u));
+                    if (j < a.n_logs) { a.line_start[nlb + j] = (uint32_t)b; }
+                    a.first_line[j] = nlb + j;
+                    if (j > 0) a.line_end[nlb + j - 1] = (uint32_t)b;
+                    ++j;
+                }
+            }
+            // ---- gram prefilter over the 16 windows that start in this thread's bytes
+            if (a.use_filter) {
+                uint32_t nxt = __shfl_down_sync(0xffffffffu, v.x, 1);
+                if (lane == 31) nxt = (pos + 16 < a.len) ? load4_safe(a.text, pos + 16, a.len) : 0u;
+                const uint32_t w[5] = {v.x, v.y, v.z, v.w, nxt};
+                uint32_t hits = 0;
+#pragma unroll
+                for (int i = 0; i < 16; ++i) {
+                    const uint32_t win = __funnelshift_r(w[i >> 2], w[(i >> 2) + 1], (i & 3) * 8) | 0x20202020u;
+                    const uint32_t h = (win * GRAM_MUL) >> (32 - GRAM_BITS);
+                    hits |= ((s_bitmap[h >> 5] >> (h & 31)) & 1u) << i;
+                }
+                if (pos >= a.len) hits = 0;
+                const uint32_t n = __popc(hits);
+                if (__ballot_sync(0xffffffffu, n != 0)) {
+                    uint32_t hinc = n;
+#pragma unroll
+                    for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, hinc, o); if (lane >= o) hinc += t; }
+                    const uint32_t total = __shfl_sync(0xffffffffu, hinc, 31);
+                    uint32_t base = 0;
+                    if (lane == 0) base = atomicAdd(&a.ctr->n_cand, total);
+                    base = __shfl_sync(0xffffffffu, base, 0) + hinc - n;
+                    uint32_t hm = hits;
+                    while (hm) {
+                        const int i = __ffs(hm) - 1;
+                        hm &= hm - 1;
+                        if (base < a.cand_cap) a.cand[base] = (uint32_t)(pos + i);
+                        else atomicOr(&a.ctr->overflow, 1u);
+                        ++base;
+                    }
+                }
+            }
+        }
+        __syncthreads();
+    }
+}
+
+// Java's Pattern.split(…, 0) drops trailing empty strings; no separator at all keeps [input].
+__global__ void k_log_meta(const uint32_t* __restrict__ first_line, const uint32_t* __restrict__ line_start,
+                           const uint32_t* __restrict__ line_end, uint32_t n_logs, uint32_t* __restrict__ n_lines) {
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n_logs) return;
+    const uint32_t f = first_line[k];
+    uint32_t n = first_line[k + 1] - f;
+    if (n > 1) {
+        while (n > 0 && line_end[f + n - 1] == line_start[f + n - 1]) --n;
+    }
+    n_lines[k] = n;
+}
+
+// ------------------------------------------------------------------ DFA walker (same loop as lpx::Dfa::match)
+__device__ __forceinline__ long tail_terminator(const uint8_t* __restrict__ s, uint32_t ls, uint32_t le) {
+    const uint32_t n = le - ls;
+    if (n >= 1 && s[le - 1] == '\r') return (long)le - 1;
+    if (n >= 2 && s[le - 2] == 0xC2 && s[le - 1] == 0x85) return (long)le - 2;
+    if (n >= 3 && s[le - 3] == 0xE2 && s[le - 2] == 0x80 && (s[le - 1] == 0xA8 || s[le - 1] == 0xA9)) return (long)le - 3;
+    return -1;
+}
+__device__ bool dfa_walk(const DevPlan& P, uint32_t r, const uint8_t* __restrict__ text, uint32_t ls, uint32_t le) {
+    const uint32_t nc = P.rx_ncls[r];
+    const uint16_t* __restrict__ T = P.dfa_trans + P.rx_dfa_off[r];
+    const uint8_t* __restrict__ cm = P.rx_cmap + (size_t)r * 256;
+    uint32_t st = P.rx_start[r];
+    const long tpos = tail_terminator(text, ls, le);
+    for (uint32_t i = ls; i < le && st > 1; ++i) {
+        if ((long)i == tpos) st = T[st * nc + nc - 2];
+        st = T[st * nc + cm[text[i]]];
+    }
+    if (st > 1) st = T[st * nc + nc - 1];
+    return st == 1;
+}
+
+__device__ __forceinline__ void emit_record(Counters* ctr, unsigned long long* recs, uint32_t cap, bool hit, uint32_t r, uint32_t g) {
+    const unsigned mask = 0xffffffffu;   // callers keep all 32 lanes in the loop
+    const unsigned votes = __ballot_sync(mask, hit);
+    if (!votes) return;
+    const int lane = threadIdx.x & 31;
+    const int leader = __ffs(votes) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(&ctr->n_recs, (unsigned)__popc(votes));
+    base = __shfl_sync(mask, base, leader);
+    if (hit) {
+        const uint32_t idx = base + __popc(votes & ((1u << lane) - 1u));
+        if (idx < cap) recs[idx] = ((unsigned long long)r << 32) | g;
+        else atomicOr(&ctr->overflow, 4u);
+    }
+}
+
+// ------------------------------------------------------------------ K3: confirm gram hits -> (line, regex) tasks
+struct ConfirmArgs {
+    const uint8_t* text;
+    uint64_t len;
+    const uint32_t* cand;
+    uint32_t cand_cap;
+    const uint32_t* line_start;
+    const uint32_t* line_end;
+    uint32_t n_lines_total;
+    unsigned long long* tasks;
+    uint32_t task_cap;
+    Counters* ctr;
+};
+__global__ void __launch_bounds__(256) k_confirm(ConfirmArgs a, DevPlan P) {
+    const uint32_t n = min(a.ctr->n_cand, a.cand_cap);
+    for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < n; c += gridDim.x * blockDim.x) {
+        const uint32_t pos = a.cand[c];
+        uint32_t w = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) if ((uint64_t)pos + i < a.len) w |= (uint32_t)a.text[pos + i] << (8 * i);
+        const uint32_t f = w | 0x20202020u;
+        const uint32_t tmask = (1u << P.table_bits) - 1u;
+        uint32_t slot = (f * GRAM_MUL2) >> (32 - P.table_bits);
+        uint32_t key;
+        while ((key = P.table_key[slot]) != 0 && key != f) slot = (slot + 1) & tmask;
+        if (key == 0) continue;
+        const uint32_t g = upper_bound_dev<uint32_t>(a.line_start, a.n_lines_total, pos) - 1;
+        const uint32_t ls = a.line_start[g], le = a.line_end[g];
+        const uint32_t lb = P.table_begin[slot], lc = P.table_count[slot];
+        for (uint32_t q = 0; q < lc; ++q) {
+            const uint32_t l = P.gram_lits[lb + q];
+            const uint32_t go = P.lit_gram_off[l], ll = P.lit_len[l];
+            if (pos < ls + go) continue;
+            const uint32_t s = pos - go;
+            if (s + ll > le) continue;
+            const uint8_t* __restrict__ lit = P.lit_bytes + P.lit_off[l];
+            bool ok = true;
+            if (P.lit_icase[l]) {
+                for (uint32_t j = 0; j < ll && ok; ++j) {
+                    uint8_t b = a.text[s + j];
+                    if (b >= 'A' && b <= 'Z') b += 32;
+                    ok = b == lit[j];
+                }
+            } else {
+                for (uint32_t j = 0; j < ll && ok; ++j) ok = a.text[s + j] == lit[j];
+            }
+            if (!ok) continue;
+            const uint32_t rb = P.lit_rx_begin[l], re = P.lit_rx_begin[l + 1];
+            const uint32_t base = atomicAdd(&a.ctr->n_tasks, re - rb);
+            for (uint32_t j = rb; j < re; ++j) {
+                const uint32_t idx = base + (j - rb);
+                if (idx < a.task_cap) a.tasks[idx] = ((unsigned long long)P.lit_rx[j] << 32) | g;
+                else atomicOr(&a.ctr->overflow, 2u);
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------ K4: verify tasks
+struct VerifyArgs {
+    const uint8_t* text;
+    const uint32_t* line_start;
+    const uint32_t* line_end;
+    const unsigned long long* tasks;
+    uint32_t task_cap;
+    unsigned long long* recs;
+    uint32_t rec_cap;
+    Counters* ctr;
+    // always-candidates pass
+    uint32_t n_lines_total;
+    const uint32_t* first_line;
+    const uint32_t* n_lines;
+    uint32_t n_logs;
+};
+__global__ void __launch_bounds__(256) k_verify(VerifyArgs a, DevPlan P) {
+    const uint32_t n = min(a.ctr->n_tasks, a.task_cap);
+    const uint32_t stride = gridDim.x * blockDim.x;
+    const uint32_t rounds = (n + stride - 1) / stride;
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    for (uint32_t it = 0; it < rounds; ++it, t += stride) {
+        bool hit = false;
+        uint32_t r = 0, g = 0;
+        if (t < n) {
+            const unsigned long long task = a.tasks[t];
+            r = (uint32_t)(task >> 32);
+            g = (uint32_t)task;
+            if (P.rx_kind[r] == 0) hit = dfa_walk(P, r, a.text, a.line_start[g], a.line_end[g]);
+        }
+        emit_record(a.ctr, a.recs, a.rec_cap, hit, r, g);
+    }
+}
+// regexes without a usable literal: every (untrimmed) line is a candidate
+__global__ void __launch_bounds__(256) k_verify_always(VerifyArgs a, DevPlan P) {
+    const uint32_t stride = gridDim.x * blockDim.x;
+    const uint32_t rounds = (a.n_lines_total + stride - 1) / stride;
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    for (uint32_t it = 0; it < rounds; ++it, g += stride) {
+        bool live = g < a.n_lines_total;
+        uint32_t ls = 0, le = 0;
+        if (live) {
+            uint32_t k = a.n_logs == 1 ? 0 : upper_bound_dev<uint32_t>(a.first_line, a.n_logs + 1, g) - 1;
+            live = k < a.n_logs && g - a.first_line[k] < a.n_lines[k];
+            if (live) { ls = a.line_start[g]; le = a.line_end[g]; }
+        }
+        for (uint32_t q = 0; q < P.n_always; ++q) {
+            const uint32_t r = P.always_list[q];
+            bool hit = false;
+            if (live && P.rx_kind[r] == 0) hit = dfa_walk(P, r, a.text, ls, le);
+            emit_record(a.ctr, a.recs, a.rec_cap, hit, r, g);
+        }
+    }
+}
+
+// ------------------------------------------------------------------ record post-processing
+__global__ void k_rx_bounds(const unsigned long long* __restrict__ keys, uint32_t n, uint32_t n_rx, uint32_t* __restrict__ rx_begin) {
+    uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
+    if (r > n_rx) return;
+    rx_begin[r] = lower_bound_dev<unsigned long long>(keys, n, (unsigned long long)r << 32);
+}
+__global__ void k_ctx_flags(const unsigned long long* __restrict__ keys, const uint32_t* __restrict__ rx_begin, uint32_t* __restrict__ flags32) {
+    const uint32_t n = rx_begin[4];
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const unsigned long long k = keys[i];
+        const uint32_t r = (uint32_t)(k >> 32), g = (uint32_t)k;
+        atomicOr(&flags32[g >> 2], (1u << r) << ((g & 3) * 8));
+    }
+}
+__global__ void k_emit_events(const unsigned long long* __restrict__ keys, uint32_t n, DevPlan P,
+                              unsigned long long* __restrict__ ev_key, uint32_t ev_cap, Counters* ctr) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const unsigned long long k = keys[i];
+        const uint32_t r = (uint32_t)(k >> 32), g = (uint32_t)k;
+        const uint32_t pb = P.rxp_begin[r], pe = P.rxp_begin[r + 1];
+        if (pb == pe) continue;
+        const uint32_t base = atomicAdd(&ctr->n_events, pe - pb);
+        for (uint32_t j = pb; j < pe; ++j) {
+            const uint32_t idx = base + (j - pb);
+            if (idx < ev_cap) ev_key[idx] = ((unsigned long long)g << 32) | P.rxp_pat[j];
+            else atomicOr(&ctr->overflow, 8u);
+        }
+    }
+}
+__global__ void k_event_prep(const unsigned long long* __restrict__ ev_key, uint32_t m, DevPlan P,
+                             const uint32_t* __restrict__ first_line, uint32_t n_logs,
+                             uint32_t* __restrict__ ev_log, uint32_t* __restrict__ slot_key, uint32_t* __restrict__ ev_idx,
+                             unsigned long long* __restrict__ freq_delta) {
+    uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= m) return;
+    const unsigned long long k = ev_key[e];
+    const uint32_t g = (uint32_t)(k >> 32), p = (uint32_t)k;
+    ev_log[e] = n_logs == 1 ? 0 : upper_bound_dev<uint32_t>(first_line, n_logs + 1, g) - 1;
+    slot_key[e] = (uint32_t)P.pat_slot[p];
+    ev_idx[e] = e;
+    atomicAdd(&freq_delta[p], 1ull);
+}
+__global__ void k_slot_rank(const uint32_t* __restrict__ sorted_slot, const uint32_t* __restrict__ sorted_idx, uint32_t m,
+                            uint32_t* __restrict__ rank_in_slot) {
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= m) return;
+    const uint32_t s = sorted_slot[j];
+    rank_in_slot[sorted_idx[j]] = j - lower_bound_dev<uint32_t>(sorted_slot, m, s);
+}
+__global__ void k_log_event_begin(const unsigned long long* __restrict__ ev_key, uint32_t m, const uint32_t* __restrict__ first_line,
+                                  uint32_t n_logs, unsigned long long* __restrict__ begin) {
+    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
+    if (k > n_logs) return;
+    begin[k] = lower_bound_dev<unsigned long long>(ev_key, m, (unsigned long long)first_line[k] << 32);
+}
+
+// ------------------------------------------------------------------ K5: scoring (fp64, no contraction)
+struct ScoreArgs {
+    const unsigned long long* ev_key;
+    uint32_t m;
+    const uint32_t* ev_log;
+    const uint32_t* rank_in_slot;
+    const unsigned long long* prior;      // [n_pat] in-window counts at call start (+ lower ranks), may be null
+    const uint32_t* first_line;
+    const uint32_t* n_lines;
+    const unsigned long long* keys;       // unique (regex, line) records
+    const uint32_t* rx_begin;
+    const uint8_t* ctx_flags;
+    uint32_t* out_line;
+    uint32_t* out_pat;
+    double* out_score;
+    double* out_factors;                  // may be null
+    unsigned long long* sort_key;         // descending-score key for ranking
+};
+
+__device__ __forceinline__ bool list_any_in(const unsigned long long* __restrict__ keys, uint32_t b, uint32_t e, uint32_t r,
+                                            uint32_t lo, uint32_t hi /* [lo,hi) global lines */) {
+    if (lo >= hi) return false;
+    const uint32_t i = b + lower_bound_dev<unsigned long long>(keys + b, e - b, ((unsigned long long)r << 32) | lo);
+    return i < e && (uint32_t)keys[i] < hi;
+}
+
+__global__ void __launch_bounds__(128) k_score(ScoreArgs a, DevPlan P, ScoreCfg C) {
+    const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= a.m) return;
+    const unsigned long long ek = a.ev_key[e];
+    const uint32_t g = (uint32_t)(ek >> 32), p = (uint32_t)ek;
+    const uint32_t k = a.ev_log[e];
+    const uint32_t first = a.first_line[k];
+    const long long N = a.n_lines[k];
+    const long long i = (long long)g - first;
+
+    const double base = P.pat_conf[p];
+    const double sev = P.pat_sev[p];
+
+    // chronological factor, SS:123-151
+    const double pos = __ddiv_rn((double)i, (double)N);
+    double chrono;
+    if (pos <= C.early) {
+        const double range = __dsub_rn(C.max_early, 1.5);
+        chrono = __dadd_rn(1.5, __dmul_rn(__dsub_rn(C.early, pos), __ddiv_rn(range, C.early)));
+    } else if (pos <= C.penalty) {
+        const double mid = __dsub_rn(C.penalty, C.early);
+        chrono = __dadd_rn(1.0, __dmul_rn(__dsub_rn(C.penalty, pos), __ddiv_rn(0.5, mid)));
+    } else {
+        chrono = __dadd_rn(0.5, __dsub_rn(1.0, pos));
+    }
+
+    // proximity factor, SS:161-190 + 315-347: closest hit of each secondary inside its window
+    double prox = 1.0;
+    {
+        const uint32_t sb = P.sec_begin[p], se = P.sec_begin[p + 1];
+        if (sb != se) {
+            double total = 0.0;
+            for (uint32_t s = sb; s < se; ++s) {
+                const long long win = min((long long)C.max_window, (long long)P.sec_window[s]);
+                const long long lo = max(0ll, i - win), hi = min(N, i + win + 1);   // local [lo,hi)
+                if (lo >= hi) continue;
+                const uint32_t r = P.sec_rx[s];
+                const uint32_t b = a.rx_begin[r], en = a.rx_begin[r + 1];
+                const unsigned long long* kk = a.keys + b;
+                const uint32_t cnt = en - b;
+                const unsigned long long self = ((unsigned long long)r << 32) | g;
+                const uint32_t at = lower_bound_dev<unsigned long long>(kk, cnt, self);
+                long long best = -1;
+                if (at > 0) {
+                    const long long l = (long long)(uint32_t)kk[at - 1] - first;
+                    if (l >= lo) best = i - l;
+                }
+                uint32_t nx = at;
+                if (nx < cnt && kk[nx] == self) ++nx;
+                if (nx < cnt) {
+                    const long long l = (long long)(uint32_t)kk[nx] - first;
+                    if (l < hi) { const long long d = l - i; if (best < 0 || d < best) best = d; }
+                }
+                if (best >= 0) total = __dadd_rn(total, __dmul_rn(P.sec_weight[s], C.decay_lut[best]));
+            }
+            prox = __dadd_rn(1.0, total);
+        }
+    }
+
+    // temporal factor, SS:199-305 (backward greedy walk == forward threshold)
+    double temporal = 1.0;
+    {
+        const uint32_t qb = P.seq_begin[p], qe = P.seq_begin[p + 1];
+        if (qb != qe) {
+            double total = 0.0;
+            for (uint32_t q = qb; q < qe; ++q) {
+                const uint32_t eb = P.seq_ev_begin[q], ee = P.seq_ev_begin[q + 1];
+                if (eb == ee) continue;                                  // SS:233-235
+                const uint32_t rl = P.ev_rx[ee - 1];
+                const long long nlo = max(0ll, i - 5), nhi = min(N, i + 6);  // SS:275-277
+                if (!list_any_in(a.keys, a.rx_begin[rl], a.rx_begin[rl + 1], rl, first + (uint32_t)nlo, first + (uint32_t)nhi)) continue;
+                bool ok = true;
+                long long T = -1;   // local line of the earliest feasible position of the previous event
+                for (uint32_t j = eb; j + 1 < ee && ok; ++j) {
+                    const uint32_t r = P.ev_rx[j];
+                    const uint32_t b = a.rx_begin[r], en = a.rx_begin[r + 1];
+                    const unsigned long long want = ((unsigned long long)r << 32) | (uint32_t)(first + T + 1);
+                    const uint32_t at = b + lower_bound_dev<unsigned long long>(a.keys + b, en - b, want);
+                    if (at >= en) { ok = false; break; }
+                    const long long l = (long long)(uint32_t)a.keys[at] - first;
+                    if (l >= i) { ok = false; break; }     // must end strictly before the primary line
+                    T = l;
+                }
+                if (ok) total = __dadd_rn(total, P.seq_bonus[q]);
+            }
+            temporal = __dadd_rn(1.0, total);
+        }
+    }
+
+    // context factor, CAS:46-117, accumulated in the reference's per-line order
+    double ctx;
+    {
+        long long b0 = i, a1 = i + 1;
+        if (P.pat_has_ctx[p]) { b0 = max(0ll, i - (long long)P.pat_before[p]); a1 = min(N, i + 1 + (long long)P.pat_after[p]); }
+        double score = 0.0;
+        int err = 0, stack = 0;
+        const uint8_t* __restrict__ fl = a.ctx_flags + first;
+        for (long long l = b0; l < a1; ++l) {
+            const uint32_t f = fl[l];
+            if (f & 1u) { ++err; score = __dadd_rn(score, 0.4); }
+            else if (f & 2u) { score = __dadd_rn(score, 0.2); }
+            if (f & 4u) { ++stack; score = __dadd_rn(score, 0.1); }
+            if (f & 8u) { score = __dadd_rn(score, 0.3); }
+        }
+        if (stack > 0) score = __dadd_rn(score, fmin(__dmul_rn((double)stack, 0.1), 0.5));
+        const int total = (int)(a1 - b0);
+        if (total > 10 && (double)(stack + err) > __dmul_rn((double)total, 0.7)) score = __dmul_rn(score, 0.8);
+        ctx = __dadd_rn(1.0, score);
+        if (ctx > C.max_ctx) ctx = C.max_ctx;
+        if (total <= 0) ctx = 1.0;
+    }
+
+    // frequency penalty, FTS:64-93 with the count read before this match is recorded (SS:84-88)
+    double pen = 0.0;
+    {
+        const int slot = P.pat_slot[p];
+        if (slot >= 0) {
+            const unsigned long long pr = a.prior ? a.prior[P.slot_first_pat[slot]] : 0ull;
+            const unsigned long long cnt = pr + a.rank_in_slot[e];
+            if (cnt > 0) {
+                const double rate = __ddiv_rn((double)cnt, (double)C.hours);
+                if (rate > C.freq_thr) pen = fmin(C.max_pen, __ddiv_rn(__dsub_rn(rate, C.freq_thr), C.freq_thr));
+            }
+        }
+    }
+
+    double s = __dmul_rn(base, sev);
+    s = __dmul_rn(s, chrono);
+    s = __dmul_rn(s, prox);
+    s = __dmul_rn(s, temporal);
+    s = __dmul_rn(s, ctx);
+    s = __dmul_rn(s, __dsub_rn(1.0, pen));
+
+    a.out_line[e] = (uint32_t)(i + 1);
+    a.out_pat[e] = p;
+    a.out_score[e] = s;
+    if (a.out_factors) {
+        double* f = a.out_factors + (size_t)e * 7;
+        f[0] = base; f[1] = sev; f[2] = chrono; f[3] = prox; f[4] = temporal; f[5] = ctx; f[6] = pen;
+    }
+    // order-preserving key: larger score first; -0.0/+0.0 and NaN keep IEEE total order
+    unsigned long long bits = (unsigned long long)__double_as_longlong(s);
+    bits = (bits & 0x8000000000000000ull) ? ~bits : (bits | 0x8000000000000000ull);
+    a.sort_key[e] = ~bits;
+}
+__global__ void k_write_rank(const uint32_t* __restrict__ order, const uint32_t* __restrict__ ev_log,
+                             const unsigned long long* __restrict__ log_begin, uint32_t m, uint32_t* __restrict__ rank) {
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= m) return;
+    const uint32_t e = order[j];
+    rank[e] = j - (uint32_t)log_begin[ev_log[e]];
+}
+__global__ void k_gather_u32(const uint32_t* __restrict__ src, const uint32_t* __restrict__ idx, uint32_t n, uint32_t* __restrict__ dst) {
+    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j < n) dst[j] = src[idx[j]];
+}
+__global__ void k_count_per_pattern(const unsigned long long* __restrict__ keys, uint32_t n, DevPlan P, unsigned long long* __restrict__ counts) {
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t r = (uint32_t)(keys[i] >> 32);
+        for (uint32_t j = P.rxp_begin[r]; j < P.rxp_begin[r + 1]; ++j) atomicAdd(&counts[P.rxp_pat[j]], 1ull);
+    }
+}
+
+}  // namespace
+
+// ============================================================================================
+//                                         host code
+// ============================================================================================
+namespace {
+
+thread_local std::string g_last_error;
+
+struct CudaFail : std::runtime_error {
+    explicit CudaFail(const std::string& m) : std::runtime_error(m) {}
+};
+struct LimitFail : std::runtime_error {
+    explicit LimitFail(const std::string& m) : std::runtime_error(m) {}
+};
+#define CK(call)                                                                                          \
+    do {                                                                                                  \
+        cudaError_t e_ = (call);                                                                          \
+        if (e_ != cudaSuccess)                                                                            \
+            throw CudaFail(std::string(#call) + ": " + cudaGetErrorString(e_) + " (" __FILE__ ":" + std::to_string(__LINE__) + ")"); \
+    } while (0)
+
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    void ensure(size_t n) {
+        if (n <= cap) return;
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+        size_t want = std::max<size_t>(n + n / 4, 256);
+        CK(cudaMalloc(&p, want));
+        cap = want;
+    }
+    void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
+    template <class T> T* as() const { return static_cast<T*>(p); }
+};
+
+template <class T>
+const T* upload(std::vector<DevBuf>& keep, const std::vector<T>& v) {
+    DevBuf b;
+    b.ensure(std::max<size_t>(v.size() * sizeof(T), 16));
+    if (!v.empty()) CK(cudaMemcpy(b.p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+    keep.push_back(b);
+    return static_cast<const T*>(b.p);
+}
+
+}  // namespace
+
+struct lp_result {
+    std::vector<uint64_t> log_n_lines, log_event_begin, freq_delta;
+    std::vector<uint32_t> line, pattern, rank, line_start, line_end;
+    std::vector<double> score, factors;
+    uint64_t n_logs = 0, n_events = 0, total_lines = 0;
+    bool has_factors = false, has_offsets = false;
+};
+
+struct lp_ctx {
+    int device = 0;
+    lp_scoring_cfg cfg{};
+    cudaStream_t stream = nullptr;
+    std::mutex mu;
+    int n_sm = 148;
+
+    lpx::Plan plan;
+    bool loaded = false;
+    std::vector<DevBuf> plan_bufs;
+    DevPlan dp{};
+    DevBuf d_lut;
+    ScoreCfg sc{};
+
+    // scratch (grow-only)
+    DevBuf text, log_off, tile_counts, counters, line_start, line_end, first_line, n_lines;
+    DevBuf cand, tasks, recs, recs_alt, cub_tmp, rx_begin, ctx_flags;
+    DevBuf ev_key, ev_key_alt, ev_log, slot_key, slot_key_alt, ev_idx, ev_idx_alt, rank_in_slot, freq_delta, prior;
+    DevBuf out_line, out_pat, out_score, out_factors, sort_key, sort_key_alt, order, order_alt, log_sorted, log_sorted_alt;
+    DevBuf rank, log_event_begin, n_unique;
+    size_t cand_cap = 0, task_cap = 0;
+
+    // scan-phase state kept for the two-phase batch API
+    struct Pending {
+        bool valid = false;
+        const uint8_t* d_text = nullptr;
+        uint64_t len = 0;
+        uint32_t n_logs = 0, G = 0, n_unique = 0, m = 0;
+        int options = 0;
+    } pend;
+
+    cudaEvent_t ev[6]{};
+    lp_timings tm{};
+    uint64_t launches = 0;
+};
+
+namespace {
+
+void upload_plan(lp_ctx* c) {
+    for (auto& b : c->plan_bufs) b.release();
+    c->plan_bufs.clear();
+    const lpx::Plan& pl = c->plan;
+    DevPlan& d = c->dp;
+    auto& K = c->plan_bufs;
+    d.n_rx = pl.n_rx;
+    d.rx_kind = upload(K, pl.rx_kind);
+    d.rx_dfa_off = upload(K, pl.rx_dfa_off);
+    d.rx_ncls = upload(K, pl.rx_ncls);
+    d.rx_start = upload(K, pl.rx_start);
+    d.dfa_trans = upload(K, pl.dfa_trans);
+    d.rx_cmap = upload(K, pl.rx_cmap);
+    d.always_list = upload(K, pl.always_list);
+    d.n_always = (uint32_t)pl.always_list.size();
+    d.bitmap = upload(K, pl.bitmap);
+    d.table_bits = pl.table_bits;
+    d.table_key = upload(K, pl.table_key);
+    d.table_begin = upload(K, pl.table_begin);
+    d.table_count = upload(K, pl.table_count);
+    d.gram_lits = upload(K, pl.gram_lits);
+    d.lit_bytes = upload(K, pl.lit_bytes);
+    d.lit_off = upload(K, pl.lit_off);
+    d.lit_len = upload(K, pl.lit_len);
+    d.lit_gram_off = upload(K, pl.lit_gram_off);
+    d.lit_icase = upload(K, pl.lit_icase);
+    d.lit_rx_begin = upload(K, pl.lit_rx_begin);
+    d.lit_rx = upload(K, pl.lit_rx);
+    d.n_pat = pl.n_pat;
+    d.pat_primary = upload(K, pl.pat_primary);
+    d.pat_conf = upload(K, pl.pat_conf);
+    d.pat_sev = upload(K, pl.pat_sev);
+    d.pat_has_ctx = upload(K, pl.pat_has_ctx);
+    d.pat_before = upload(K, pl.pat_before);
+    d.pat_after = upload(K, pl.pat_after);
+    d.pat_slot = upload(K, pl.pat_slot);
+    d.slot_first_pat = upload(K, pl.slot_first_pat);
+    d.sec_begin = upload(K, pl.sec_begin);
+    d.sec_rx = upload(K, pl.sec_rx);
+    d.sec_weight = upload(K, pl.sec_weight);
+    d.sec_window = upload(K, pl.sec_window);
+    d.seq_begin = upload(K, pl.seq_begin);
+    d.seq_ev_begin = upload(K, pl.seq_ev_begin);
+    d.ev_rx = upload(K, pl.ev_rx);
+    d.seq_bonus = upload(K, pl.seq_bonus);
+    d.rxp_begin = upload(K, pl.rxp_begin);
+    d.rxp_pat = upload(K, pl.rxp_pat);
+    d.rx_vm_off = upload(K, pl.rx_vm_off);
+    d.rx_vm_len = upload(K, pl.rx_vm_len);
+    d.rx_vm_slots = upload(K, pl.rx_vm_slots);
+    d.rx_vm_caps = upload(K, pl.rx_vm_caps);
+    d.rx_vm_set_base = upload(K, pl.rx_vm_set_base);
+    d.vm_code = upload(K, pl.vm_code);
+    d.vm_set_off = upload(K, pl.vm_set_off);
+    d.vm_set_ranges = upload(K, pl.vm_set_ranges);
+}
+
+inline uint32_t blocks_for(uint64_t n, uint32_t threads) { return (uint32_t)std::max<uint64_t>(1, (n + threads - 1) / threads); }
+
+template <class K>
+void sort_keys(lp_ctx* c, K* in, K* out, uint32_t n, int end_bit) {
+    size_t tmp = 0;
+    cub::DeviceRadixSort::SortKeys(nullptr, tmp, in, out, (int)n, 0, end_bit, c->stream);
+    c->cub_tmp.ensure(tmp);
+    CK(cub::DeviceRadixSort::SortKeys(c->cub_tmp.p, tmp, in, out, (int)n, 0, end_bit, c->stream));
+    c->launches += 3;
+}
+template <class K, class V>
+void sort_pairs(lp_ctx* c, K* kin, K* kout, V* vin, V* vout, uint32_t n, int end_bit) {
+    size_t tmp = 0;
+    cub::DeviceRadixSort::SortPairs(nullptr, tmp, kin, kout, vin, vout, (int)n, 0, end_bit, c->stream);
+    c->cub_tmp.ensure(tmp);
+    CK(cub::DeviceRadixSort::SortPairs(c->cub_tmp.p, tmp, kin, kout, vin, vout, (int)n, 0, end_bit, c->stream));
+    c->launches += 3;
+}
+int bits_for(uint64_t v) { int b = 1; while (b < 64 && (v >> b)) ++b; return b; }
+
+// ---- phase 1: split + prefilter + verify + unique records; leaves state in ctx->pend
+void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_off, uint32_t n_logs, int options) {
+    if (!c->loaded) throw std::invalid_argument("lp_load_patterns has not been called");
+    if (len >= 0xFFFFFFF0ull) throw LimitFail("log/batch larger than 4 GiB - 16 bytes; shard it (see DESIGN.md)");
+    if (n_logs == 0) throw std::invalid_argument("n_logs == 0");
+    if ((reinterpret_cast<uintptr_t>(d_text) & 15) != 0) throw std::invalid_argument("device log pointer must be 16-byte aligned");
+    for (uint32_t k = 0; k < n_logs; ++k) if (h_off[k] > h_off[k + 1]) throw std::invalid_argument("offsets must be non-decreasing");
+    if (h_off[0] != 0 || h_off[n_logs] != len) throw std::invalid_argument("offsets[0] must be 0 and offsets[n_logs] the total size");
+    cudaStream_t st = c->stream;
+    c->pend = lp_ctx::Pending();
+    c->launches = 0;
+    c->tm = lp_timings();
+
+    const uint32_t n_tiles = (uint32_t)((len + 1 + TILE_BYTES - 1) / TILE_BYTES);   // covers position `len` too
+    c->log_off.ensure((n_logs + 1) * sizeof(uint64_t));
+    CK(cudaMemcpyAsync(c->log_off.p, h_off, (n_logs + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
+    c->tile_counts.ensure((size_t)n_tiles * 4);
+    c->counters.ensure(sizeof(Counters));
+    CK(cudaMemsetAsync(c->counters.p, 0, sizeof(Counters), st));
+    Counters* ctr = c->counters.as<Counters>();
+
+    CK(cudaEventRecord(c->ev[0], st));
+    k_count_nl<<<std::min<uint32_t>(n_tiles, c->n_sm * 16), SCAN_THREADS, 0, st>>>(d_text, len, n_tiles, c->tile_counts.as<uint32_t>());
+    k_scan_tiles<<<1, 1024, 0, st>>>(c->tile_counts.as<uint32_t>(), n_tiles, ctr);
+    c->launches += 2;
+    Counters h{};
+    CK(cudaMemcpyAsync(&h, ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    const uint64_t G64 = h.total_nl + n_logs;
+    if (G64 >= 0xFFFFFFF0ull) throw LimitFail("too many lines");
+    const uint32_t G = (uint32_t)G64;
+
+    c->line_start.ensure((size_t)(G + 1) * 4);
+    c->line_end.ensure((size_t)(G + 1) * 4);
+    c->first_line.ensure((size_t)(n_logs + 1) * 4);
+    c->n_lines.ensure((size_t)n_logs * 4);
+    const bool use_filter = !c->plan.lit_off.empty();
+    const uint32_t n_always = (uint32_t)c->plan.always_list.size();
+
+    for (int attempt = 0;; ++attempt) {
+        if (c->cand_cap == 0) c->cand_cap = std::max<size_t>(1u << 16, len / 8);
+        if (c->task_cap == 0) c->task_cap = std::max<size_t>(1u << 16, len / 8);
+        c->cand.ensure(c->cand_cap * 4);
+        c->tasks.ensure(c->task_cap * 8);
+        const size_t rec_cap = c->task_cap + (size_t)G * n_always + 16;
+        if (rec_cap >= 0x7FFFFFFFull) throw LimitFail("record capacity exceeds 2^31; shard the batch");
+        c->recs.ensure(rec_cap * 8);
+        c->recs_alt.ensure(rec_cap * 8);
+
+        CK(cudaMemsetAsync(&ctr->n_cand, 0, sizeof(Counters) - offsetof(Counters, n_cand), st));
+        ScanArgs sa{};
+        sa.text = d_text; sa.len = len; sa.n_tiles = n_tiles; sa.tile_prefix = c->tile_counts.as<uint32_t>();
+        sa.log_off = c->log_off.as<uint64_t>(); sa.n_logs = n_logs;
+        sa.line_start = c->line_start.as<uint32_t>(); sa.line_end = c->line_end.as<uint32_t>();
+        sa.first_line = c->first_line.as<uint32_t>(); sa.bitmap = c->dp.bitmap;
+        sa.cand = c->cand.as<uint32_t>(); sa.cand_cap = (uint32_t)std::min<size_t>(c->cand_cap, 0xFFFFFFFFu);
+        sa.ctr = ctr; sa.use_filter = use_filter ? 1 : 0;
+        const size_t smem = use_filter ? GRAM_WORDS * 4 : 0;
+        const uint32_t grid = std::min<uint32_t>(n_tiles, (uint32_t)c->n_sm * 3);
+        CK(cudaEventRecord(c->ev[1], st));
+        k_lines_filter<<<grid, SCAN_THREADS, smem, st>>>(sa);
+        CK(cudaEventRecord(c->ev[2], st));
+        k_log_meta<<<blocks_for(n_logs, 128), 128, 0, st>>>(c->first_line.as<uint32_t>(), c->line_start.as<uint32_t>(),
+                                                             c->line_end.as<uint32_t>(), n_logs, c->n_lines.as<uint32_t>());
+        c->launches += 2;
+
+        VerifyArgs va{};
+        va.text = d_text; va.line_start = c->line_start.as<uint32_t>(); va.line_end = c->line_end.as<uint32_t>();
+        va.tasks = c->tasks.as<unsigned long long>(); va.task_cap = (uint32_t)std::min<size_t>(c->task_cap, 0xFFFFFFFFu); va.recs = c->recs.as<unsigned long long>();
+        va.rec_cap = (uint32_t)rec_cap; va.ctr = ctr; va.n_lines_total = G;
+        va.first_line = c->first_line.as<uint32_t>(); va.n_lines = c->n_lines.as<uint32_t>(); va.n_logs = n_logs;
+        if (use_filter) {
+            ConfirmArgs ca{};
+            ca.text = d_text; ca.len = len; ca.cand = c->cand.as<uint32_t>(); ca.cand_cap = sa.cand_cap;
+            ca.line_start = c->line_start.as<uint32_t>(); ca.line_end = c->line_end.as<uint32_t>(); ca.n_lines_total = G;
+            ca.tasks = c->tasks.as<unsigned long long>(); ca.task_cap = (uint32_t)std::min<size_t>(c->task_cap, 0xFFFFFFFFu); ca.ctr = ctr;
+            k_confirm<<<c->n_sm * 8, 256, 0, st>>>(ca, c->dp);
+            k_verify<<<c->n_sm * 8, 256, 0, st>>>(va, c->dp);
+            c->launches += 2;
+        }
+        if (n_always) {
+            k_verify_always<<<std::min<uint32_t>(blocks_for(G, 256), c->n_sm * 8), 256, 0, st>>>(va, c->dp);
+            c->launches += 1;
+        }
+        CK(cudaEventRecord(c->ev[3], st));
+        CK(cudaMemcpyAsync(&h, ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        CK(cudaGetLastError());
+        if (h.overflow & 16u) throw std::overflow_error("backtracking verifier exceeded its budget");
+        if (h.overflow == 0) break;
+        if (attempt >= 6) throw LimitFail("candidate queues keep overflowing");
+        if (h.overflow & 1u) c->cand_cap = std::max<size_t>(c->cand_cap * 2, (size_t)h.n_cand + 1024);
+        if (h.overflow & 2u) c->task_cap = std::max<size_t>(c->task_cap * 2, (size_t)h.n_tasks + 1024);
+        if (h.overflow & 4u) c->task_cap = std::max<size_t>(c->task_cap * 2, (size_t)h.n_recs + 1024);
+    }
+    c->tm.candidates = h.n_cand;
+    c->tm.verify_tasks = (uint64_t)h.n_tasks + (uint64_t)G * n_always;
+
+    // ---- sort + unique the (regex, line) records
+    uint32_t n_unique = 0;
+    const uint32_t n_recs = h.n_recs;
+    c->rx_begin.ensure((size_t)(c->dp.n_rx + 2) * 4);
+    c->ctx_flags.ensure(((size_t)G / 4 + 2) * 4);
+    CK(cudaMemsetAsync(c->ctx_flags.p, 0, ((size_t)G / 4 + 2) * 4, st));
+    if (n_recs) {
+        const int kb = 32 + bits_for(c->dp.n_rx);
+        sort_keys<unsigned long long>(c, c->recs.as<unsigned long long>(), c->recs_alt.as<unsigned long long>(), n_recs, kb);
+        c->n_unique.ensure(16);
+        size_t tmp = 0;
+        cub::DeviceSelect::Unique(nullptr, tmp, c->recs_alt.as<unsigned long long>(), c->recs.as<unsigned long long>(),
+                                  c->n_unique.as<uint32_t>(), (int)n_recs, st);
+        c->cub_tmp.ensure(tmp);
+        CK(cub::DeviceSelect::Unique(c->cub_tmp.p, tmp, c->recs_alt.as<unsigned long long>(), c->recs.as<unsigned long long>(),
+                                     c->n_unique.as<uint32_t>(), (int)n_recs, st));
+        c->launches += 2;
+        CK(cudaMemcpyAsync(&n_unique, c->n_unique.p, 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+    }
+    k_rx_bounds<<<blocks_for(c->dp.n_rx + 1, 128), 128, 0, st>>>(c->recs.as<unsigned long long>(), n_unique, c->dp.n_rx, c->rx_begin.as<uint32_t>());
+    k_ctx_flags<<<c->n_sm * 4, 256, 0, st>>>(c->recs.as<unsigned long long>(), c->rx_begin.as<uint32_t>(), c->ctx_flags.as<uint32_t>());
+    c->launches += 2;
+
+    // ---- events in discovery order (global line, pattern index)
+    uint32_t m = 0;
+    if (n_unique) {
+        const size_t ev_cap = (size_t)n_unique * c->plan.max_fanout;
+        c->ev_key.ensure(ev_cap * 8 + 8);
+        c->ev_key_alt.ensure(ev_cap * 8 + 8);
+        k_emit_events<<<c->n_sm * 4, 256, 0, st>>>(c->recs.as<unsigned long long>(), n_unique, c->dp,
+                                                    c->ev_key_alt.as<unsigned long long>(), (uint32_t)ev_cap, ctr);
+        c->launches += 1;
+        CK(cudaMemcpyAsync(&h, ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        m = h.n_events;
+        if (m) sort_keys<unsigned long long>(c, c->ev_key_alt.as<unsigned long long>(), c->ev_key.as<unsigned long long>(), m,
+                                             32 + bits_for(G));
+    }
+    c->pend.valid = true;
+    c->pend.d_text = d_text; c->pend.len = len; c->pend.n_logs = n_logs; c->pend.G = G;
+    c->pend.n_unique = n_unique; c->pend.m = m; c->pend.options = options;
+    c->tm.scan_bytes = len + 4ull * ((uint64_t)G + 1) + 8ull * m;
+}
+
+void per_pattern_counts(lp_ctx* c, uint64_t* counts_out) {
+    cudaStream_t st = c->stream;
+    const uint32_t np = c->dp.n_pat;
+    c->freq_delta.ensure((size_t)std::max<uint32_t>(np, 1) * 8);
+    CK(cudaMemsetAsync(c->freq_delta.p, 0, (size_t)std::max<uint32_t>(np, 1) * 8, st));
+    if (c->pend.n_unique) {
+        k_count_per_pattern<<<c->n_sm * 4, 256, 0, st>>>(c->recs.as<unsigned long long>(), c->pend.n_unique, c->dp,
+                                                          c->freq_delta.as<unsigned long long>());
+        c->launches += 1;
+    }
+    if (np) CK(cudaMemcpyAsync(counts_out, c->freq_delta.p, (size_t)np * 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+}
+
+// ---- phase 2: frequency ranks, scoring, ranking, result download
+lp_result* run_score(lp_ctx* c, const uint64_t* prior_count) {
+    if (!c->pend.valid) throw std::invalid_argument("no scan is pending on this context");
+    cudaStream_t st = c->stream;
+    const uint32_t m = c->pend.m, n_logs = c->pend.n_logs, G = c->pend.G, np = c->dp.n_pat;
+    const int options = c->pend.options;
+    std::unique_ptr<lp_result> res(new lp_result());
+    res->n_logs = n_logs;
+    res->n_events = m;
+    res->total_lines = G;
+    res->freq_delta.assign(np, 0);
+    res->log_n_lines.assign(n_logs, 0);
+    res->log_event_begin.assign(n_logs + 1, 0);
+
+    c->freq_delta.ensure((size_t)std::max<uint32_t>(np, 1) * 8);
+    CK(cudaMemsetAsync(c->freq_delta.p, 0, (size_t)std::max<uint32_t>(np, 1) * 8, st));
+    c->log_event_begin.ensure((size_t)(n_logs + 1) * 8);
+
+    if (m) {
+        c->ev_log.ensure((size_t)m * 4); c->slot_key.ensure((size_t)m * 4); c->slot_key_alt.ensure((size_t)m * 4);
+        c->ev_idx.ensure((size_t)m * 4); c->ev_idx_alt.ensure((size_t)m * 4); c->rank_in_slot.ensure((size_t)m * 4);
+        c->out_line.ensure((size_t)m * 4); c->out_pat.ensure((size_t)m * 4); c->out_score.ensure((size_t)m * 8);
+        c->sort_key.ensure((size_t)m * 8); c->sort_key_alt.ensure((size_t)m * 8);
+        c->order.ensure((size_t)m * 4); c->order_alt.ensure((size_t)m * 4); c->rank.ensure((size_t)m * 4);
+        c->log_sorted.ensure((size_t)m * 4); c->log_sorted_alt.ensure((size_t)m * 4);
+        if (options & LP_OPT_FACTORS) c->out_factors.ensure((size_t)m * 7 * 8);
+        const unsigned long long* prior_d = nullptr;
+        if (prior_count && np) {
+            c->prior.ensure((size_t)np * 8);
+            CK(cudaMemcpyAsync(c->prior.p, prior_count, (size_t)np * 8, cudaMemcpyHostToDevice, st));
+            prior_d = c->prior.as<unsigned long long>();
+        }
+        const uint32_t gb = blocks_for(m, 256);
+        k_event_prep<<<gb, 256, 0, st>>>(c->ev_key.as<unsigned long long>(), m, c->dp, c->first_line.as<uint32_t>(), n_logs,
+                                         c->ev_log.as<uint32_t>(), c->slot_key.as<uint32_t>(), c->ev_idx.as<uint32_t>(),
+                                         c->freq_delta.as<unsigned long long>());
+        sort_pairs<uint32_t, uint32_t>(c, c->slot_key.as<uint32_t>(), c->slot_key_alt.as<uint32_t>(), c->ev_idx.as<uint32_t>(),
+                                       c->ev_idx_alt.as<uint32_t>(), m, 32);
+        k_slot_rank<<<gb, 256, 0, st>>>(c->slot_key_alt.as<uint32_t>(), c->ev_idx_alt.as<uint32_t>(), m, c->rank_in_slot.as<uint32_t>());
+        ScoreArgs sa{};
+        sa.ev_key = c->ev_key.as<unsigned long long>(); sa.m = m; sa.ev_log = c->ev_log.as<uint32_t>();
+        sa.rank_in_slot = c->rank_in_slot.as<uint32_t>(); sa.prior = prior_d;
+        sa.first_line = c->first_line.as<uint32_t>(); sa.n_lines = c->n_lines.as<uint32_t>();
+        sa.keys = c->recs.as<unsigned long long>(); sa.rx_begin = c->rx_begin.as<uint32_t>();
+        sa.ctx_flags = c->ctx_flags.as<uint8_t>();
+        sa.out_line = c->out_line.as<uint32_t>(); sa.out_pat = c->out_pat.as<uint32_t>(); sa.out_score = c->out_score.as<double>();
+        sa.out_factors = (options & LP_OPT_FACTORS) ? c->out_factors.as<double>() : nullptr;
+        sa.sort_key = c->sort_key.as<unsigned long long>();
+        k_score<<<blocks_for(m, 128), 128, 0, st>>>(sa, c->dp, c->sc);
+        c->launches += 3;
+    }
+    k_log_event_begin<<<blocks_for(n_logs + 1, 128), 128, 0, st>>>(c->ev_key.as<unsigned long long>(), m, c->first_line.as<uint32_t>(),
+                                                                   n_logs, c->log_event_begin.as<unsigned long long>());
+    c->launches += 1;
+    if (m && !(options & LP_OPT_NO_RANK)) {
+        // stable sort by descending score (ties keep discovery order), then stably by log
+        sort_pairs<unsigned long long, uint32_t>(c, c->sort_key.as<unsigned long long>(), c->sort_key_alt.as<unsigned long long>(),
+                                                 c->ev_idx.as<uint32_t>(), c->order.as<uint32_t>(), m, 64);
+        uint32_t* order = c->order.as<uint32_t>();
+        if (n_logs > 1) {
+            k_gather_u32<<<blocks_for(m, 256), 256, 0, st>>>(c->ev_log.as<uint32_t>(), order, m, c->log_sorted.as<uint32_t>());
+            sort_pairs<uint32_t, uint32_t>(c, c->log_sorted.as<uint32_t>(), c->log_sorted_alt.as<uint32_t>(), order,
+                                           c->order_alt.as<uint32_t>(), m, bits_for(n_logs));
+            order = c->order_alt.as<uint32_t>();
+            c->launches += 1;
+        }
+        k_write_rank<<<blocks_for(m, 256), 256, 0, st>>>(order, c->ev_log.as<uint32_t>(), c->log_event_begin.as<unsigned long long>(), m,
+                                                         c->rank.as<uint32_t>());
+        c->launches += 1;
+    }
+    CK(cudaEventRecord(c->ev[4], st));
+
+    // ---- download
+    res->line.resize(m); res->pattern.resize(m); res->score.resize(m); res->rank.assign(m, 0);
+    if (m) {
+        CK(cudaMemcpyAsync(res->line.data(), c->out_line.p, (size_t)m * 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(res->pattern.data(), c->out_pat.p, (size_t)m * 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(res->score.data(), c->out_score.p, (size_t)m * 8, cudaMemcpyDeviceToHost, st));
+        if (!(options & LP_OPT_NO_RANK)) CK(cudaMemcpyAsync(res->rank.data(), c->rank.p, (size_t)m * 4, cudaMemcpyDeviceToHost, st));
+        if (options & LP_OPT_FACTORS) {
+            res->factors.resize((size_t)m * 7);
+            res->has_factors = true;
+            CK(cudaMemcpyAsync(res->factors.data(), c->out_factors.p, (size_t)m * 7 * 8, cudaMemcpyDeviceToHost, st));
+        }
+    }
+    if (np) CK(cudaMemcpyAsync(res->freq_delta.data(), c->freq_delta.p, (size_t)np * 8, cudaMemcpyDeviceToHost, st));
+    std::vector<uint32_t> nl(n_logs);
+    CK(cudaMemcpyAsync(nl.data(), c->n_lines.p, (size_t)n_logs * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(res->log_event_begin.data(), c->log_event_begin.p, (size_t)(n_logs + 1) * 8, cudaMemcpyDeviceToHost, st));
+    if (options & LP_OPT_LINE_OFFSETS) {
+        res->has_offsets = true;
+        res->line_start.resize((size_t)G + 1);
+        res->line_end.resize((size_t)G);
+        CK(cudaMemcpyAsync(res->line_start.data(), c->line_start.p, (size_t)G * 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(res->line_end.data(), c->line_end.p, (size_t)G * 4, cudaMemcpyDeviceToHost, st));
+    }
+    CK(cudaStreamSynchronize(st));
+    CK(cudaGetLastError());
+    for (uint32_t k = 0; k < n_logs; ++k) res->log_n_lines[k] = nl[k];
+    if (res->has_offsets) res->line_start[G] = (uint32_t)c->pend.len;
+
+    float ms = 0;
+    cudaEventElapsedTime(&ms, c->ev[0], c->ev[4]); c->tm.total_ms = ms;
+    cudaEventElapsedTime(&ms, c->ev[1], c->ev[2]); c->tm.scan_ms = ms;
+    cudaEventElapsedTime(&ms, c->ev[2], c->ev[3]); c->tm.verify_ms = ms;
+    cudaEventElapsedTime(&ms, c->ev[3], c->ev[4]); c->tm.score_ms = ms;
+    c->tm.kernel_launches = c->launches;
+    c->pend.valid = false;
+    return res.release();
+}
+
+template <class F>
+int guarded(lp_ctx* c, F&& f) {
+    try {
+        if (c) CK(cudaSetDevice(c->device));
+        f();
+        return LP_OK;
+    } catch (const lpx::RegexSyntaxError& e) {
+        g_last_error = std::string("PatternSyntaxException: ") + e.what() + " near index " + std::to_string(e.index);
+        return LP_ERR_SYNTAX;
+    } catch (const lpx::RegexUnsupported& e) {
+        g_last_error = std::string("unsupported regex construct: ") + e.what();
+        return LP_ERR_UNSUPPORTED;
+    } catch (const CudaFail& e) {
+        g_last_error = e.what();
+        return LP_ERR_CUDA;
+    } catch (const LimitFail& e) {
+        g_last_error = e.what();
+        return LP_ERR_LIMIT;
+    } catch (const std::overflow_error& e) {
+        g_last_error = e.what();
+        return LP_ERR_BACKTRACK;
+    } catch (const std::invalid_argument& e) {
+        g_last_error = e.what();
+        return LP_ERR_INVALID;
+    } catch (const std::exception& e) {
+        g_last_error = e.what();
+        return LP_ERR_INVALID;
+    }
+}
+
+const uint8_t* stage_host_log(lp_ctx* c, const uint8_t* host, uint64_t len) {
+    c->text.ensure(len + 64);
+    CK(cudaEventRecord(c->ev[5], c->stream));
+    if (len) CK(cudaMemcpyAsync(c->text.p, host, len, cudaMemcpyHostToDevice, c->stream));
+    return c->text.as<uint8_t>();
+}
+
+}  // namespace
+
+// ============================================================================================
+//                                         C ABI
+// ============================================================================================
+extern "C" {
+
+const char* lp_last_error(void) { return g_last_error.c_str(); }
+const char* lp_version(void) { return "logparser_b200 0.1 (sm_100a)"; }
+
+lp_ctx* lp_create(const lp_scoring_cfg* cfg, int device) {
+    lp_ctx* c = nullptr;
+    int rc = guarded(nullptr, [&] {
+        if (!cfg) throw std::invalid_argument("cfg is NULL");
+        if (cfg->max_window < 0) throw std::invalid_argument("scoring.proximity.max-window < 0");
+        if (cfg->time_window_hours <= 0) throw std::invalid_argument("scoring.frequency.time-window-hours <= 0");
+        int n = 0;
+        CK(cudaGetDeviceCount(&n));
+        if (n <= 0) throw CudaFail("no CUDA device visible");
+        if (device < 0 || device >= n) throw std::invalid_argument("device index out of range");
+        CK(cudaSetDevice(device));
+        std::unique_ptr<lp_ctx> ctx(new lp_ctx());
+        ctx->device = device;
+        ctx->cfg = *cfg;
+        ctx->cfg.decay_lut = nullptr;
+        CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+        for (auto& e : ctx->ev) CK(cudaEventCreate(&e));
+        cudaDeviceProp prop;
+        CK(cudaGetDeviceProperties(&prop, device));
+        ctx->n_sm = prop.multiProcessorCount;
+        CK(cudaFuncSetAttribute(k_lines_filter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(GRAM_WORDS * 4)));
+        std::vector<double> lut((size_t)cfg->max_window + 1);
+        for (int d = 0; d <= cfg->max_window; ++d)
+            lut[d] = cfg->decay_lut ? cfg->decay_lut[d] : std::exp(-(double)d / cfg->decay_constant);   // SS:177
+        ctx->d_lut.ensure(lut.size() * 8);
+        CK(cudaMemcpy(ctx->d_lut.p, lut.data(), lut.size() * 8, cudaMemcpyHostToDevice));
+        ScoreCfg& s = ctx->sc;
+        s.early = cfg->early_bonus_threshold; s.max_early = cfg->max_early_bonus; s.penalty = cfg->penalty_threshold;
+        s.max_ctx = cfg->max_context_factor; s.freq_thr = cfg->frequency_threshold; s.max_pen = cfg->max_penalty;
+        s.max_window = cfg->max_window; s.hours = cfg->time_window_hours; s.decay_lut = ctx->d_lut.as<double>();
+        c = ctx.release();
+    });
+    return rc == LP_OK ? c : nullptr;
+}
+
+void lp_destroy(lp_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    for (auto& b : c->plan_bufs) b.release();
+    DevBuf* all[] = {&c->text, &c->log_off, &c->tile_counts, &c->counters, &c->line_start, &c->line_end, &c->first_line, &c->n_lines,
+                     &c->cand, &c->tasks, &c->recs, &c->recs_alt, &c->cub_tmp, &c->rx_begin, &c->ctx_flags, &c->ev_key, &c->ev_key_alt,
+                     &c->ev_log, &c->slot_key, &c->slot_key_alt, &c->ev_idx, &c->ev_idx_alt, &c->rank_in_slot, &c->freq_delta, &c->prior,
+                     &c->out_line, &c->out_pat, &c->out_score, &c->out_factors, &c->sort_key, &c->sort_key_alt, &c->order, &c->order_alt,
+                     &c->log_sorted, &c->log_sorted_alt, &c->rank, &c->log_event_begin, &c->n_unique, &c->d_lut};
+    for (DevBuf* b : all) b->release();
+    for (auto& e : c->ev) if (e) cudaEventDestroy(e);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int lp_load_patterns(lp_ctx* c, const lp_pattern_desc* pats, size_t n, int64_t* bad_pattern) {
+    if (bad_pattern) *bad_pattern = -1;
+    if (!c) { g_last_error = "ctx is NULL"; return LP_ERR_INVALID; }
+    return guarded(c, [&] {
+        if (n && !pats) throw std::invalid_argument("patterns is NULL");
+        std::lock_guard<std::mutex> lk(c->mu);
+        std::vector<lpx::PlanPatternIn> in(n);
+        for (size_t i = 0; i < n; ++i) {
+            const lp_pattern_desc& d = pats[i];
+            if (!d.primary_regex) { if (bad_pattern) *bad_pattern = (int64_t)i; throw std::invalid_argument("primary_regex is NULL"); }
+            in[i].has_id = d.id != nullptr;
+            if (d.id) in[i].id = d.id;
+            in[i].primary = d.primary_regex;
+            in[i].confidence = d.confidence; in[i].severity = d.severity_multiplier;
+            in[i].has_context = d.has_context; in[i].before = d.lines_before; in[i].after = d.lines_after;
+            for (uint32_t s = 0; s < d.n_secondaries; ++s) {
+                if (!d.secondaries[s].regex) { if (bad_pattern) *bad_pattern = (int64_t)i; throw std::invalid_argument("secondary regex is NULL"); }
+                in[i].secs.push_back({d.secondaries[s].regex, d.secondaries[s].weight, d.secondaries[s].proximity_window});
+            }
+            for (uint32_t s = 0; s < d.n_sequences; ++s) {
+                lpx::PlanPatternIn::Seq q;
+                q.bonus = d.sequences[s].bonus_multiplier;
+                for (uint32_t e = 0; e < d.sequences[s].n_events; ++e) {
+                    if (!d.sequences[s].event_regex[e]) { if (bad_pattern) *bad_pattern = (int64_t)i; throw std::invalid_argument("sequence event regex is NULL"); }
+                    q.events.push_back(d.sequences[s].event_regex[e]);
+                }
+                in[i].seqs.push_back(std::move(q));
+            }
+        }
+        c->loaded = false;
+        lpx::build_plan(in, c->plan, bad_pattern);
+        upload_plan(c);
+        c->loaded = true;
+    });
+}
+
+int lp_batch_scan_device(lp_ctx* c, const uint8_t* d_logs, const uint64_t* offsets, size_t n_logs, int options, uint64_t* counts_out) {
+    if (!c) { g_last_error = "ctx is NULL"; return LP_ERR_INVALID; }
+    return guarded(c, [&] {
+        if (!offsets) throw std::invalid_argument("offsets is NULL");
+        std::lock_guard<std::mutex> lk(c->mu);
+        run_scan(c, d_logs, offsets[n_logs], offsets, (uint32_t)n_logs, options);
+        if (counts_out) per_pattern_counts(c, counts_out);
+    });
+}
+int lp_batch_score(lp_ctx* c, const uint64_t* prior_count, lp_result** out) {
+    if (!c || !out) { g_last_error = "NULL argument"; return LP_ERR_INVALID; }
+    return guarded(c, [&] {
+        std::lock_guard<std::mutex> lk(c->mu);
+        *out = run_score(c, prior_count);
+    });
+}
+
+int lp_analyze_batch_device(lp_ctx* c, const uint8_t* d_logs, const uint64_t* offsets, size_t n_logs, const uint64_t* prior_count,
+                            int options, lp_result** out) {
+    if (!c || !out) { g_last_error = "NULL argument"; return LP_ERR_INVALID; }
+    return guarded(c, [&] {
+        if (!offsets) throw std::invalid_argument("offsets is NULL");
+        std::lock_guard<std::mutex> lk(c->mu);
+        run_scan(c, d_logs, offsets[n_logs], offsets, (uint32_t)n_logs, options);
+        *out = run_score(c, prior_count);
+    });
+}
+int lp_analyze_batch(lp_ctx* c, const uint8_t* logs, const uint64_t* offsets, size_t n_logs, const uint64_t* prior_count, int options,
+                     lp_result** out) {
+    if (!c || !out) { g_last_error = "NULL argument"; return LP_ERR_INVALID; }
+    return guarded(c, [&] {
+        if (!offsets) throw std::invalid_argument("offsets is NULL");
+        std::lock_guard<std::mutex> lk(c->mu);
+        const uint64_t len = offsets[n_logs];
+        if (len && !logs) throw std::invalid_argument("logs is NULL");
+        const uint8_t* d = stage_host_log(c, logs, len);
+        run_scan(c, d, len, offsets, (uint32_t)n_logs, options);
+        *out = run_score(c, prior_count);
+        float ms = 0;
+        cudaEventElapsedTime(&ms, c->ev[5], c->ev[0]);
+        c->tm.h2d_ms = ms;
+    });
+}
+int lp_analyze_device(lp_ctx* c, const uint8_t* d_log, size_t len, const uint64_t* prior_count, int options, lp_result** out) {
+    const uint64_t off[2] = {0, (uint64_t)len};
+    return lp_analyze_batch_device(c, d_log, off, 1, prior_count, options, out);
+}
+int lp_analyze(lp_ctx* c, const uint8_t* log, size_t len, const uint64_t* prior_count, int options, lp_result** out) {
+    const uint64_t off[2] = {0, (uint64_t)len};
+    return lp_analyze_batch(c, log, off, 1, prior_count, options, out);
+}
+
+int lp_result_get(const lp_result* r, lp_result_view* v) {
+    if (!r || !v) { g_last_error = "NULL argument"; return LP_ERR_INVALID; }
+    memset(v, 0, sizeof *v);
+    v->n_logs = r->n_logs;
+    v->n_events = r->n_events;
+    v->log_n_lines = r->log_n_lines.data();
+    v->log_event_begin = r->log_event_begin.data();
+    v->line = r->line.data();
+    v->pattern = r->pattern.data();
+    v->score = r->score.data();
+    v->rank = r->rank.data();
+    v->factors = r->has_factors ? r->factors.data() : nullptr;
+    v->freq_delta = r->freq_delta.data();
+    v->n_patterns = r->freq_delta.size();
+    v->line_start = r->has_offsets ? r->line_start.data() : nullptr;
+    v->line_end = r->has_offsets ? r->line_end.data() : nullptr;
+    v->total_lines = r->total_lines;
+    return LP_OK;
+}
+void lp_result_free(lp_result* r) { delete r; }
+
+int lp_get_timings(const lp_ctx* c, lp_timings* out) {
+    if (!c || !out) { g_last_error = "NULL argument"; return LP_ERR_INVALID; }
+    *out = c->tm;
+    return LP_OK;
+}
+
+void* lp_stream(const lp_ctx* c) { return c ? (void*)c->stream : nullptr; }
+
+}  // extern "C"

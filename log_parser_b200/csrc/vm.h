@@ -1,0 +1,36 @@
+// Backtracking bytecode for patterns a DFA cannot decide (look-around, back-references,
+// possessive quantifiers, atomic groups, MULTILINE anchors). Compiled on the host, executed by
+// the device verifier on prefiltered candidate lines only; vm_match_host() runs the identical
+// interpreter on the host for the CPU-only test tier.
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <vector>
+
+#include "rx.h"
+
+namespace lpx {
+
+struct VmInsn {
+    uint8_t op;
+    uint8_t flag;
+    uint16_t aux;
+    int32_t a;
+    int32_t b;
+};
+
+struct VmProgram {
+    std::vector<VmInsn> code;
+    std::vector<uint32_t> set_off;   // per set: offset into set_ranges (pairs lo,hi), size n+1
+    std::vector<uint32_t> set_ranges;
+    uint32_t n_slots = 0;            // capture slots + loop marks
+    uint32_t n_caps = 0;             // 2 * groups
+};
+
+// Throws RegexUnsupported for constructs the bytecode cannot express.
+void build_vm(const ParsedRegex& rx, VmProgram& out);
+
+// 1 match, 0 no match, -1 backtracking budget exhausted.
+int vm_match_host(const VmProgram& p, const uint8_t* s, size_t n);
+
+}  // namespace lpx

@@ -1,0 +1,228 @@
+"""GPU parity tests proper: the CUDA path, called through the C ABI, against the oracle on the same
+seeded inputs. Bar (BASELINE.json north_star): pattern ids and line numbers bit-exact, discovery
+order identical, scores <= 1e-9 relative (they are in fact compared for bit equality first), final
+ranking identical."""
+import random
+
+import numpy as np
+import pytest
+
+from log_parser_b200 import binding, synth
+from log_parser_b200.model import PatternSpec, ScoringConfig, SecondaryPattern, SequencePattern
+
+pytestmark = pytest.mark.gpu
+
+REL_TOL = 1e-9   # north_star: scores accumulated in fp64 must agree to <= 1e-9 relative
+
+
+def _check(res, ora, log_index=0, check_factors=True):
+    b, e = int(res.log_event_begin[log_index]), int(res.log_event_begin[log_index + 1])
+    assert int(res.log_n_lines[log_index]) == ora.n_lines
+    assert e - b == len(ora.line), f"event count {e - b} != oracle {len(ora.line)}"
+    np.testing.assert_array_equal(res.line[b:e], ora.line)
+    np.testing.assert_array_equal(res.pattern[b:e], ora.pattern)
+    if check_factors and res.factors is not None and len(ora.line):
+        names = ["base", "sev", "chrono", "prox", "temporal", "ctx", "penalty"]
+        for k, nm in enumerate(names):
+            bad = np.nonzero(res.factors[b:e, k] != ora.factors[:, k])[0]
+            assert bad.size == 0, f"factor {nm} differs at event {bad[0]} (line {ora.line[bad[0]]}, pattern {ora.pattern[bad[0]]}): " \
+                                  f"{res.factors[b + bad[0], k]!r} vs {ora.factors[bad[0], k]!r}"
+    if len(ora.line):
+        rel = np.abs(res.score[b:e] - ora.score) / np.maximum(np.abs(ora.score), 1e-300)
+        assert rel.max() <= REL_TOL
+        # ranking: score descending, ties by discovery order (stable)
+        exp_order = np.argsort(-ora.score, kind="stable")
+        exp_rank = np.empty_like(exp_order)
+        exp_rank[exp_order] = np.arange(len(exp_order))
+        np.testing.assert_array_equal(res.rank[b:e], exp_rank.astype(np.uint32))
+
+
+@pytest.fixture(scope="module")
+def parser():
+    p = binding.LogParser(ScoringConfig())
+    yield p
+    p.close()
+
+
+def test_c1_full_parity(parser, oracle):
+    """configs[0]: one 10k-line Java stack-trace pod log vs ~50 patterns."""
+    wl, log = synth.config_c1()
+    parser.load_patterns(wl.patterns)
+    res = parser.analyze(log, options=binding.OPT_FACTORS)
+    ora = oracle.analyze(ScoringConfig(), wl.patterns, log)
+    assert len(ora.line) > 20
+    _check(res, ora)
+    np.testing.assert_array_equal(res.freq_delta, ora.freq_delta)
+    # bit-exact scores, not just within tolerance
+    np.testing.assert_array_equal(res.score, ora.score)
+
+
+@pytest.mark.parametrize("log,n", [
+    (b"", 1), (b"\n\n", 0), (b"\na", 2), (b"a\r\nb\n\n", 2), (b"a\rb", 1), (b"a\n\r", 2), (b"a\n\r\n\n", 1),
+    (b"a\n \n", 2), (b"\r\r\n", 1), (b"x", 1), (b"x\n", 1), (b"\n", 0), (b"\r\n", 0), (b"a\n\nb", 3),
+    (b"hit\n" * 40, 40), (b"\n" * 100 + b"hit", 101), (b"hit" + b"\n" * 100, 1),
+])
+def test_split_edge_cases(parser, oracle, log, n):
+    pats = [PatternSpec(id="p", primary_regex="hit|^$|a", confidence=0.7, severity="HIGH", lines_before=2, lines_after=2)]
+    parser.load_patterns(pats)
+    res = parser.analyze(log, options=binding.OPT_FACTORS | binding.OPT_LINE_OFFSETS)
+    ora = oracle.analyze(ScoringConfig(), pats, log)
+    assert ora.n_lines == n
+    _check(res, ora)
+    spans = oracle.split(log)
+    for i, (s, e) in enumerate(spans):
+        assert (int(res.line_start[i]), int(res.line_end[i])) == (s, e)
+
+
+def test_all_factors_small(parser, oracle):
+    log = b"\n".join([b"start", b"connect begin", b"WARN slow", b"boom OutOfMemoryError", b"retry", b"x", b"y", b"z", b"w", b"v"])
+    pats = [PatternSpec(id="p1", primary_regex="OutOfMemoryError", confidence=0.8, severity="high", lines_before=2, lines_after=1,
+                        secondaries=[SecondaryPattern("retry", 0.8, 10), SecondaryPattern("nomatch", 0.5, 10)],
+                        sequences=[SequencePattern(["start", "connect", "boom"], 0.5), SequencePattern(["zzz", "boom"], 0.9)]),
+            PatternSpec(id=None, primary_regex="^x$|retry", confidence=0.5, severity="weird"),
+            PatternSpec(id="p1", primary_regex="boom", confidence=0.9, severity="LOW", lines_before=0, lines_after=0)]
+    parser.load_patterns(pats)
+    res = parser.analyze(log, options=binding.OPT_FACTORS)
+    ora = oracle.analyze(ScoringConfig(), pats, log)
+    assert len(ora.line) == 4
+    _check(res, ora)
+    np.testing.assert_array_equal(res.score, ora.score)
+
+
+def test_random_small_logs_many_configs(parser, oracle):
+    """Random pattern sets over a small vocabulary: dense matches, windows clipped at both ends,
+    sequences of 1-4 events, shared regexes between roles, shared frequency ids."""
+    rng = random.Random(1234)
+    toks = ["ERROR", "warn", "Exception", "FooError", "alpha", "beta", "gamma", "delta", "at x.y(Z.java:1)", "retry", "timeout", "\tat a.b(C.java:2)"]
+    for it in range(40):
+        n = rng.randint(1, 120)
+        lines = []
+        for _ in range(n):
+            k = rng.randint(0, 4)
+            lines.append(" ".join(rng.choice(toks) for _ in range(k)))
+        sep = rng.choice(["\n", "\r\n"])
+        log = sep.join(lines).encode() + (b"\n" if rng.random() < 0.5 else b"")
+        pats = []
+        for p in range(rng.randint(1, 6)):
+            voc = ["alpha", "beta", "gamma", "delta", "retry", "timeout", "Foo\\w+", "^$", "\\bat\\b", "a.*a", "[bg]\\w+a\\b"]
+            secs = [SecondaryPattern(rng.choice(voc), round(rng.uniform(0.1, 0.9), 2), rng.randint(0, 30)) for _ in range(rng.randint(0, 3))]
+            seqs = [SequencePattern([rng.choice(voc) for _ in range(rng.randint(0, 4))], round(rng.uniform(0.1, 0.9), 2)) for _ in range(rng.randint(0, 2))]
+            ctx = rng.random() < 0.8
+            pats.append(PatternSpec(id=rng.choice(["a", "b", "", None, "c"]), primary_regex=rng.choice(voc), confidence=round(rng.uniform(0.1, 1), 3),
+                                    severity=rng.choice(["CRITICAL", "high", "Medium", "LOW", "INFO", "x"]),
+                                    lines_before=rng.randint(0, 15) if ctx else None, lines_after=rng.randint(0, 15) if ctx else None,
+                                    secondaries=secs, sequences=seqs))
+        cfg = ScoringConfig(max_window=rng.choice([0, 3, 100]), frequency_threshold=rng.choice([2.0, 10.0]),
+                            max_context_factor=rng.choice([2.5, 50.0]))
+        lp = binding.LogParser(cfg)
+        lp.load_patterns(pats)
+        prior = [rng.randint(0, 15) for _ in pats] if rng.random() < 0.5 else None
+        # patterns sharing an id share one frequency slot: the prior of the first one counts
+        res = lp.analyze(log, prior_count=prior, options=binding.OPT_FACTORS)
+        ora = oracle.analyze(cfg, pats, log, prior_count=prior)
+        _check(res, ora)
+        np.testing.assert_array_equal(res.score, ora.score)
+        np.testing.assert_array_equal(res.freq_delta, ora.freq_delta)
+        lp.close()
+
+
+def test_non_ascii_lines(parser, oracle):
+    log = "café ERROR\néERROR x\nnaïve FooException  \nplain\n\U0001F600 boom\n".encode("utf-8")
+    pats = [PatternSpec(id="a", primary_regex=r"\bERROR\b", confidence=1.0, lines_before=1, lines_after=1),
+            PatternSpec(id="b", primary_regex=r"[^\x00-\x7F]+ boom$", confidence=1.0),
+            PatternSpec(id="c", primary_regex=r"plain$", confidence=1.0),
+            PatternSpec(id="d", primary_regex=r"^.{5} ", confidence=1.0)]
+    parser.load_patterns(pats)
+    res = parser.analyze(log, options=binding.OPT_FACTORS)
+    ora = oracle.analyze(ScoringConfig(), pats, log)
+    _check(res, ora)
+
+
+def test_batch_matches_sequential_requests(parser, oracle):
+    """lp_analyze_batch == the reference handling the logs one request after the other
+    (frequency state carried from log k to log k+1)."""
+    wl = synth.make_patterns(40, 99, noliteral=1)
+    logs = [synth.make_log(wl, n, 1000 + i, pool_blocks=500, hit_rate=0.05) for i, n in enumerate([300, 1, 77, 1200])]
+    logs.insert(2, b"")
+    logs.append(b"no newline at end")
+    parser.load_patterns(wl.patterns)
+    res = parser.analyze_batch(logs, options=binding.OPT_FACTORS)
+    prior = np.zeros(len(wl.patterns), np.uint64)
+    for k, lg in enumerate(logs):
+        ora = oracle.analyze(ScoringConfig(), wl.patterns, lg, prior_count=prior)
+        _check(res, ora, log_index=k)
+        prior = prior + ora.freq_delta
+    np.testing.assert_array_equal(res.freq_delta, prior)
+
+
+def test_two_phase_equals_one_call(parser):
+    import torch
+
+    wl = synth.make_patterns(30, 5, noliteral=0)
+    logs = [synth.make_log(wl, 400, 50 + i, pool_blocks=400, hit_rate=0.05) for i in range(3)]
+    parser.load_patterns(wl.patterns)
+    one = parser.analyze_batch(logs)
+    blob = np.frombuffer(b"".join(logs), np.uint8)
+    d = torch.from_numpy(blob.copy()).cuda()
+    off = np.concatenate([[0], np.cumsum([len(x) for x in logs])]).astype(np.uint64)
+    counts = parser.batch_scan_device(d.data_ptr(), off)
+    two = parser.batch_score(None)
+    np.testing.assert_array_equal(counts, one.freq_delta)
+    np.testing.assert_array_equal(one.score, two.score)
+    np.testing.assert_array_equal(one.line, two.line)
+    np.testing.assert_array_equal(one.rank, two.rank)
+
+
+def test_device_resident_equals_host_path(parser):
+    import torch
+
+    wl, log = synth.config_c1()
+    parser.load_patterns(wl.patterns)
+    a = parser.analyze(log)
+    d = torch.from_numpy(np.frombuffer(log, np.uint8).copy()).cuda()
+    b = parser.analyze_device(d.data_ptr(), d.numel())
+    np.testing.assert_array_equal(a.score, b.score)
+    np.testing.assert_array_equal(a.line, b.line)
+    t = parser.timings()
+    assert t["kernel_launches"] > 5 and t["scan_ms"] > 0
+
+
+def test_bad_pattern_reports_index(parser):
+    pats = [PatternSpec(id="ok", primary_regex="fine", confidence=1.0), PatternSpec(id="bad", primary_regex="a{,2}", confidence=1.0)]
+    with pytest.raises(binding.PatternSyntaxError) as ei:
+        parser.load_patterns(pats)
+    assert ei.value.bad_pattern == 1
+
+
+def test_c2_sample_parity_and_properties(parser, oracle):
+    """configs[1] shape at a size the oracle finishes in seconds, plus size-independent properties
+    on a larger log: events sorted in discovery order, rank is a permutation ordered by score,
+    idempotence, and line count equal to the newline count."""
+    wl, log = synth.config_c2(n_lines=20_000, n_patterns=500)
+    parser.load_patterns(wl.patterns)
+    res = parser.analyze(log, options=binding.OPT_FACTORS)
+    ora = oracle.analyze(ScoringConfig(), wl.patterns, log)
+    assert len(ora.line) > 50
+    _check(res, ora)
+    np.testing.assert_array_equal(res.score, ora.score)
+
+    wl, big = synth.config_c2(n_lines=300_000, n_patterns=500)
+    parser.load_patterns(wl.patterns)
+    r1 = parser.analyze(big)
+    r2 = parser.analyze(big)
+    assert r1.n_lines == 300_000 == big.count(b"\n")
+    key = r1.line.astype(np.uint64) * 1000 + r1.pattern
+    assert (np.diff(key.astype(np.int64)) > 0).all()
+    order = np.argsort(r1.rank)
+    assert (np.sort(r1.rank) == np.arange(r1.n_events)).all()
+    assert (np.diff(r1.score[order]) <= 0).all()
+    np.testing.assert_array_equal(r1.score, r2.score)
+    np.testing.assert_array_equal(r1.rank, r2.rank)
+    # linearity of the event set: the first half of the log yields exactly the events of those lines
+    # whose scoring windows do not reach the cut (checked on ids only)
+    half = big[: big.index(b"\n", len(big) // 2) + 1]
+    rh = parser.analyze(half)
+    nh = rh.n_lines
+    sel = r1.line <= nh
+    np.testing.assert_array_equal(r1.line[sel], rh.line)
+    np.testing.assert_array_equal(r1.pattern[sel], rh.pattern)

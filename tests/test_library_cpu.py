@@ -1,0 +1,133 @@
+"""CPU-only tier: the C-ABI library loads and exports every symbol of include/logparser_b200.h,
+fails loudly without a GPU, and its host-side regex compiler (the tables the device walks) agrees
+with the oracle. No compute entry point is exercised here."""
+import os
+import random
+import re
+
+import pytest
+
+from log_parser_b200 import binding
+from log_parser_b200.model import PatternSpec, ScoringConfig
+from rxgen import Gen, gen_text
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    from log_parser_b200 import build
+
+    build.build()
+    return binding.load_library()
+
+
+def test_header_symbols_exported(lib):
+    hdr = open(os.path.join(ROOT, "include", "logparser_b200.h")).read()
+    declared = set(re.findall(r"\b(lp_[a-z_0-9]+)\s*\(", hdr))
+    assert declared, "no declarations parsed"
+    assert declared == set(binding.EXPORTS)
+    for name in declared:
+        assert hasattr(lib, name), f"{name} is declared in the header but not exported"
+
+
+def test_version_and_error_string(lib):
+    assert b"sm_100a" in lib.lp_version()
+    assert isinstance(lib.lp_last_error(), bytes)
+
+
+def test_no_cpu_fallback_without_gpu(lib):
+    import torch
+
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    with pytest.raises(binding.LpError) as ei:
+        binding.LogParser(ScoringConfig())
+    assert ei.value.code == binding.LP_ERR_CUDA
+
+
+def test_product_does_not_import_oracle():
+    pkg = os.path.join(ROOT, "log_parser_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cpp", ".h", ".cuh")):
+                src = open(os.path.join(dirpath, f), errors="replace").read()
+                assert "import oracle" not in src and "from oracle" not in src and "oracle/" not in src, f
+
+
+def test_dfa_tables_vs_oracle_random(lib, oracle):
+    rng = random.Random(4242)
+    checked = 0
+    for _ in range(1500):
+        j, _p = Gen(rng, regular_only=True).regex()
+        try:
+            o = oracle.Regex(j)
+        except (oracle.OracleSyntaxError, oracle.OracleUnsupported):
+            continue
+        d = binding.DebugRegex(j)
+        assert d.is_dfa, j
+        for _k in range(10):
+            t = gen_text(rng)
+            assert bool(d.match(t)) == o.find(t), (j, t)
+            checked += 1
+    assert checked > 10000
+
+
+@pytest.mark.parametrize("pat,flags", [
+    (r"\b(ERROR|FATAL|CRITICAL|SEVERE)\b", 2), (r"\b(WARN|WARNING)\b", 2),
+    (r"^\s*at\s+[\w\.\$]+\(.*\)\s*$", 0), (r"\b\w*Exception\b|\b\w*Error\b", 0),
+])
+def test_context_regex_tables(lib, oracle, pat, flags):
+    rng = random.Random(3)
+    words = ["ERROR", "error", "Fatal", "CRITICAL", "severe", "WARN", "warning", "Warnings", "xERROR", "ERRORS", "at", "\tat",
+             "  at", "com.foo.Bar$1.run(Bar.java:12)", "NullPointerException", "OutOfMemoryError", "Errors", "exception",
+             "MyError:", "(x)", "()", " ", "INFO", "foo", "-", "\r", "é", " ", "\x85"]
+    d = binding.DebugRegex(pat, flags)
+    o = oracle.Regex(pat, flags)
+    for _ in range(3000):
+        t = " ".join(rng.choice(words) for _ in range(rng.randint(0, 5)))
+        if rng.random() < 0.3:
+            t = rng.choice(["\tat ", "   at ", "at "]) + t
+        if rng.random() < 0.1:
+            t += rng.choice(["\r", " ", "\x85", "\r\r"])
+        assert bool(d.match(t)) == o.find(t), (pat, t)
+
+
+@pytest.mark.parametrize("pat,text", [
+    ("a$", "a\r"), ("a$", "a "), ("a$", "a\x85"), ("a$", "a\r\r"), ("a\\z", "a\r"), ("a$\\r", "a\r"), ("^.$", "é"),
+    ("^..$", "\U0001F600"), ("[^a]", "é"), ("é+$", "ééé"), ("[à-ÿ]x", "éx"), ("\\bé", "é"), ("x\\B", "xé"), (".", "\r"),
+    ("(?s).", "\r"), ("(?d).", "\r"), ("(?d)a$", "a\r"), ("\\R", "\r"), ("^$", ""), ("\\B", ""), ("\\b", ""), ("a{3,}", "aa"),
+    ("(a|b)*?c$", "abcab"), ("x*", ""), ("\\p{Alpha}+\\d", "ab1"), ("\\Qa.b\\E", "axb"), ("[\\w&&[^\\d]]+$", "ab1"),
+])
+def test_dfa_java_specifics(lib, oracle, pat, text):
+    assert bool(binding.DebugRegex(pat).match(text)) == oracle.Regex(pat).find(text)
+
+
+def test_syntax_errors_surface_like_java(lib):
+    for bad in ["a{,2}", "(a", "[a", "*a", "a{3,2}", "\\k<x>", "(?<=a*)b"]:
+        with pytest.raises(binding.PatternSyntaxError):
+            binding.DebugRegex(bad)
+    for unsup in ["\\X", "\\G", "\\p{L}", "(?u)a"]:
+        with pytest.raises(binding.UnsupportedRegexError):
+            binding.DebugRegex(unsup)
+
+
+def test_required_literals_are_sound(lib, oracle):
+    """Every matching text contains one of the extracted literals."""
+    from log_parser_b200 import synth
+
+    rng = random.Random(9)
+    wl = synth.make_patterns(200, 77)
+    for p, render in zip(wl.patterns, wl.renderers):
+        try:
+            d = binding.DebugRegex(p.primary_regex)
+        except binding.UnsupportedRegexError:
+            continue
+        lits = d.literals()
+        o = oracle.Regex(p.primary_regex)
+        for _ in range(5):
+            t = render(rng)
+            assert o.find(t), (p.primary_regex, t)
+            if lits:
+                tb = t.encode()
+                assert any((l.lower() in tb.lower()) if ic else (l in tb) for ic, l in lits), (p.primary_regex, t, lits)
