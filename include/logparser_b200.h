@@ -141,6 +141,29 @@ int lp_batch_scan_device(lp_ctx* ctx, const uint8_t* d_logs, const uint64_t* off
                          int options, uint64_t* counts_out /* [n_patterns] */);
 int lp_batch_score(lp_ctx* ctx, const uint64_t* prior_count, lp_result** out);
 
+/* No counterpart in the reference. Line splitting (the String.split step only) for hosts that may
+ * not allocate GPU memory themselves or let a library do it on their behalf: processes with a
+ * fixed device-memory plan, plugins living inside somebody else's allocator, callers for whom an
+ * allocation-induced device synchronisation is unacceptable. Every other lp_* call grows a
+ * scratch pool with cudaMalloc; this one allocates nothing, on the device or through any library:
+ * its scratch is a fixed array inside the loaded module (about 128 KiB per GPU, held until the
+ * process exits), which is why the input is limited to LP_NOALLOC_MAX_BYTES per call
+ * (LP_ERR_LIMIT beyond that, with the reason in `err`).
+ *   d_log         device pointer, 16-byte aligned, `len` bytes of UTF-8
+ *   d_line_start  device, `capacity` entries: start offset of every line segment
+ *   d_line_end    device, `capacity` entries: end offset (exclusive; a '\r' before '\n' is dropped)
+ *   d_counts      device, 3 entries: [0] lines after Java's trailing-empty trimming (logLines.length),
+ *                 [1] line segments written (newlines + 1), [2] non-zero if `capacity` was too small
+ *   stream        cudaStream_t to run on (NULL = default stream); the call returns after it drained
+ *   err/errlen    optional buffer for a message when the return value is not LP_OK
+ * The first call on each device looks up the scratch array's address; issue it before starting
+ * any stream capture. All calls on one device share that array and it keeps the previous call's
+ * contents (the call clears what it needs): calls that can overlap on the GPU corrupt each other,
+ * so keep them on one stream or otherwise serialised. */
+#define LP_NOALLOC_MAX_BYTES (1ull << 30)
+int lp_split_lines_noalloc(int device, const uint8_t* d_log, size_t len, uint32_t* d_line_start, uint32_t* d_line_end,
+                           size_t capacity, uint64_t* d_counts, void* stream, char* err, size_t errlen);
+
 int lp_result_get(const lp_result* r, lp_result_view* view);
 void lp_result_free(lp_result* r);
 

@@ -83,7 +83,7 @@ class Timings(C.Structure):
 EXPORTS = [
     "lp_create", "lp_destroy", "lp_last_error", "lp_version", "lp_load_patterns", "lp_analyze", "lp_analyze_device",
     "lp_analyze_batch", "lp_analyze_batch_device", "lp_batch_scan_device", "lp_batch_score", "lp_result_get",
-    "lp_result_free", "lp_get_timings", "lp_stream",
+    "lp_result_free", "lp_get_timings", "lp_stream", "lp_split_lines_noalloc",
 ]
 
 _lib = None
@@ -116,6 +116,7 @@ def load_library() -> C.CDLL:
     L.lp_get_timings.argtypes = [vp, C.POINTER(Timings)]
     L.lp_stream.restype = vp
     L.lp_stream.argtypes = [vp]
+    L.lp_split_lines_noalloc.argtypes = [C.c_int, vp, C.c_size_t, vp, vp, C.c_size_t, vp, vp, C.c_char_p, C.c_size_t]
     # host-compiler introspection (CPU-only test tier)
     L.lp_debug_rx_compile.restype = vp
     L.lp_debug_rx_compile.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_char_p, C.c_size_t, C.POINTER(C.c_int)]
@@ -339,6 +340,22 @@ class LogParser:
         t = Timings()
         self.L.lp_get_timings(self.h, C.byref(t))
         return {f[0]: getattr(t, f[0]) for f in Timings._fields_}
+
+
+NOALLOC_MAX_BYTES = 1 << 30
+
+
+def split_lines_noalloc(device: int, d_log: int, nbytes: int, d_line_start: int, d_line_end: int, capacity: int,
+                        d_counts: int, stream: int = 0) -> None:
+    """lp_split_lines_noalloc on caller-owned device buffers (raw pointers). For callers that must
+    not trigger any GPU allocation: the library's scratch for this call is a fixed in-module array,
+    so inputs above NOALLOC_MAX_BYTES are refused, and concurrent calls on one device must be
+    serialised by the caller."""
+    L = load_library()
+    err = C.create_string_buffer(512)
+    rc = L.lp_split_lines_noalloc(device, d_log, nbytes, d_line_start, d_line_end, capacity, d_counts, stream or None, err, 512)
+    if rc != LP_OK:
+        raise LpError(rc, err.value.decode("utf-8", "replace"))
 
 
 class DebugRegex:
