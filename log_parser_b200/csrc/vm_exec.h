@@ -50,6 +50,8 @@ struct VmView {
 };
 
 constexpr uint32_t VM_MAX_SLOTS = 64;
+constexpr uint32_t VM_STACK_WORDS = 4096;     // backtracking stack per (line, regex) evaluation: 2048 entries
+constexpr int VM_MAX_STEPS = 1 << 22;          // interpreter steps per (line, regex) evaluation
 constexpr uint32_t VM_NONE = 0xFFFFFFFFu;
 
 // stack entry kinds (top 4 bits of word 0)
@@ -58,10 +60,8 @@ enum : uint32_t { VK_CHOICE = 1, VK_UNDO, VK_BARRIER, VK_LOOKPOS, VK_LOOKNEG, VK
 LPX_HD uint32_t vm_decode(const uint8_t* s, uint32_t pos, uint32_t le, uint32_t& len) {
     const uint32_t c = s[pos];
     if (c < 0x80) { len = 1; return c; }
-    uint32_t need = c >= 0xF0 ? 3 : c >= 0xE0 ? 2 : c >= 0xC0 ? 1 : 0;
-    if (need == 0 || pos + need >= le + 0u + (need ? 0 : 1) ) {
-        if (need == 0 || pos + need > le - 1 + 0u) { len = 1; return 0xFFFD; }
-    }
+    const uint32_t need = c >= 0xF0 ? 3 : c >= 0xE0 ? 2 : c >= 0xC0 ? 1 : 0;
+    if (need == 0 || pos + need >= le) { len = 1; return 0xFFFD; }   // stray continuation byte / truncated sequence
     uint32_t cp = need == 1 ? (c & 0x1F) : need == 2 ? (c & 0x0F) : (c & 0x07);
     for (uint32_t k = 1; k <= need; ++k) cp = (cp << 6) | (s[pos + k] & 0x3F);
     len = need + 1;
@@ -200,13 +200,12 @@ LPX_HD int vm_run(const VmView& v, const uint8_t* s, uint32_t ls, uint32_t le, u
             }
             case VM_ATOMIC_BEGIN: VM_PUSH((VK_BARRIER << 28), 0); ++pc; break;
             case VM_ATOMIC_END: {
-                // commit: drop every alternative created since the barrier, keep the undo log
+                // commit: forget every alternative created since the barrier. Java runs the atom as a
+                // stand-alone match, so what it captured is never rolled back either: the undo log
+                // of the group is dropped with the choices.
                 uint32_t r = sp;
                 while (r > 0 && (stack[r - 2] >> 28) != VK_BARRIER) r -= 2;
-                uint32_t w = r - 2;
-                for (uint32_t q = r; q < sp; q += 2)
-                    if ((stack[q] >> 28) == VK_UNDO) { stack[w] = stack[q]; stack[w + 1] = stack[q + 1]; w += 2; }
-                sp = w; ++pc;
+                sp = r - 2; ++pc;
                 break;
             }
             case VM_LOOK_BEGIN:
@@ -215,21 +214,14 @@ LPX_HD int vm_run(const VmView& v, const uint8_t* s, uint32_t ls, uint32_t le, u
                 ++pc;
                 break;
             case VM_LOOK_END: {
+                // the condition matched; like the atomic group, its captures stay whatever follows
                 uint32_t r = sp;
                 while (r > 0 && (stack[r - 2] >> 28) != VK_LOOKPOS && (stack[r - 2] >> 28) != VK_LOOKNEG) r -= 2;
                 const uint32_t frame = r - 2;
-                if ((stack[frame] >> 28) == VK_LOOKPOS) {       // body matched: keep captures, restore position
-                    pos = stack[frame + 1];
-                    uint32_t w = frame;
-                    for (uint32_t q = r; q < sp; q += 2)
-                        if ((stack[q] >> 28) == VK_UNDO) { stack[w] = stack[q]; stack[w + 1] = stack[q + 1]; w += 2; }
-                    sp = w; ++pc;
-                } else {                                        // negative look-around whose body matched: fail
-                    for (uint32_t q = sp; q > r; q -= 2)
-                        if ((stack[q - 2] >> 28) == VK_UNDO) slots[stack[q - 2] & 0x0FFFFFFFu] = stack[q - 1];
-                    sp = frame;
-                    fail = true;
-                }
+                const bool negative = (stack[frame] >> 28) == VK_LOOKNEG;
+                pos = stack[frame + 1];
+                sp = frame;
+                if (negative) fail = true; else ++pc;
                 break;
             }
             case VM_BACK: {
@@ -297,8 +289,8 @@ LPX_HD int vm_find(const VmView& v, const uint8_t* s, uint32_t ls, uint32_t le, 
     uint32_t slots[VM_MAX_SLOTS];
     int steps = max_steps;
     uint32_t start = ls;
+    for (uint32_t i = 0; i < v.n_slots; ++i) slots[i] = VM_NONE;   // once per find(), as Matcher.search() does
     for (;;) {
-        for (uint32_t i = 0; i < v.n_slots; ++i) slots[i] = VM_NONE;
         const int r = vm_run(v, s, ls, le, start, tpos, slots, stack, cap, steps);
         if (r != 0) return r;
         if (start >= le) return 0;

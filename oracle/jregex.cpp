@@ -846,22 +846,19 @@ bool m(const Node* nd, int i, Ctx& cx, FR k) {
         }
         case N_LOOK: {
             const Node* body = nd->kids[0].get();
+            // Pos/Neg/Behind/NotBehind run the condition as a stand-alone match and never roll its
+            // captures back, whatever happens afterwards (groups set inside a look-around that
+            // matched stay set even when the enclosing path later fails).
             bool ok = false;
             if (!nd->behind) {
                 auto yes = [&](int) { return true; };
-                std::vector<int> saved;
-                if (nd->neg) saved = cx.cap;
                 ok = m(body, i, cx, mkfr(yes));
-                if (nd->neg) cx.cap = saved;
             } else {
-                std::vector<int> saved;
-                if (nd->neg) saved = cx.cap;
                 int lo = body->maxLen < 0 ? 0 : std::max(0, i - body->maxLen);
                 for (int j = i - body->minLen; j >= lo && !ok; --j) {
                     auto at = [&](int e) { return e == i; };
                     ok = m(body, j, cx, mkfr(at));
                 }
-                if (nd->neg) cx.cap = saved;
             }
             return (ok != nd->neg) && k(i);
         }
@@ -927,7 +924,7 @@ bool Regex::find_cp(const int* t, int n, int* start, int* end) const {
             if (s >= n) break;
             if (!first_.has(t[s])) continue;
         }
-        std::fill(cx.cap.begin(), cx.cap.end(), -1);
+        // Matcher.search() clears the groups once per find(), not per start position
         if (m(root_.get(), s, cx, mkfr(fin))) {
             if (start) *start = s;
             if (end) *end = e;
