@@ -16,6 +16,7 @@
 #include "../../include/logparser_b200.h"
 #include "kernels.cuh"
 #include "plan.h"
+#include "vm_exec.h"
 
 using namespace lpk;
 
@@ -323,6 +324,8 @@ struct ConfirmArgs {
     uint32_t n_lines_total;
     unsigned long long* tasks;
     uint32_t task_cap;
+    unsigned long long* vm_tasks;
+    uint32_t vm_task_cap;
     Counters* ctr;
 };
 __global__ void __launch_bounds__(256) k_confirm(ConfirmArgs a, DevPlan P) {
@@ -360,11 +363,17 @@ __global__ void __launch_bounds__(256) k_confirm(ConfirmArgs a, DevPlan P) {
             }
             if (!ok) continue;
             const uint32_t rb = P.lit_rx_begin[l], re = P.lit_rx_begin[l + 1];
-            const uint32_t base = atomicAdd(&a.ctr->n_tasks, re - rb);
             for (uint32_t j = rb; j < re; ++j) {
-                const uint32_t idx = base + (j - rb);
-                if (idx < a.task_cap) a.tasks[idx] = ((unsigned long long)P.lit_rx[j] << 32) | g;
-                else atomicOr(&a.ctr->overflow, 2u);
+                const uint32_t r = P.lit_rx[j];
+                if (P.rx_kind[r] == 0) {
+                    const uint32_t idx = atomicAdd(&a.ctr->n_tasks, 1u);
+                    if (idx < a.task_cap) a.tasks[idx] = ((unsigned long long)r << 32) | g;
+                    else atomicOr(&a.ctr->overflow, 2u);
+                } else {
+                    const uint32_t idx = atomicAdd(&a.ctr->n_vm_tasks, 1u);
+                    if (idx < a.vm_task_cap) a.vm_tasks[idx] = ((unsigned long long)r << 32) | g;
+                    else atomicOr(&a.ctr->overflow, 32u);
+                }
             }
         }
     }
@@ -385,6 +394,10 @@ struct VerifyArgs {
     const uint32_t* first_line;
     const uint32_t* n_lines;
     uint32_t n_logs;
+    // backtracking verifier
+    const unsigned long long* vm_tasks;
+    uint32_t vm_task_cap;
+    uint32_t* vm_stack;               // VM_STACK_WORDS words per thread of the VM grid
 };
 __global__ void __launch_bounds__(256) k_verify(VerifyArgs a, DevPlan P) {
     const uint32_t n = min(a.ctr->n_tasks, a.task_cap);
@@ -420,6 +433,57 @@ __global__ void __launch_bounds__(256) k_verify_always(VerifyArgs a, DevPlan P) 
             const uint32_t r = P.always_list[q];
             bool hit = false;
             if (live && P.rx_kind[r] == 0) hit = dfa_walk(P, r, a.text, ls, le);
+            emit_record(a.ctr, a.recs, a.rec_cap, hit, r, g);
+        }
+    }
+}
+
+// backtracking verifier: look-around, back-references, possessive/atomic, MULTILINE anchors, DFA blow-ups
+__device__ __forceinline__ bool vm_eval(const DevPlan& P, uint32_t r, const uint8_t* __restrict__ text, uint32_t ls, uint32_t le,
+                                        uint32_t* stack, Counters* ctr) {
+    lpx::VmView v;
+    v.code = reinterpret_cast<const lpx::VmCode*>(P.vm_code) + P.rx_vm_off[r];
+    v.set_off = P.vm_set_off + P.rx_vm_set_base[r];
+    v.set_data = P.vm_set_ranges;
+    v.n_slots = P.rx_vm_slots[r];
+    const int res = lpx::vm_find(v, text, ls, le, stack, lpx::VM_STACK_WORDS, lpx::VM_MAX_STEPS);
+    if (res < 0) atomicOr(&ctr->overflow, 16u);
+    return res > 0;
+}
+__global__ void __launch_bounds__(128) k_verify_vm(VerifyArgs a, DevPlan P) {
+    const uint32_t n = min(a.ctr->n_vm_tasks, a.vm_task_cap);
+    const uint32_t stride = gridDim.x * blockDim.x;
+    const uint32_t rounds = (n + stride - 1) / stride;
+    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t* stack = a.vm_stack + (size_t)t * lpx::VM_STACK_WORDS;
+    for (uint32_t it = 0; it < rounds; ++it, t += stride) {
+        bool hit = false;
+        uint32_t r = 0, g = 0;
+        if (t < n) {
+            const unsigned long long task = a.vm_tasks[t];
+            r = (uint32_t)(task >> 32);
+            g = (uint32_t)task;
+            hit = vm_eval(P, r, a.text, a.line_start[g], a.line_end[g], stack, a.ctr);
+        }
+        emit_record(a.ctr, a.recs, a.rec_cap, hit, r, g);
+    }
+}
+__global__ void __launch_bounds__(128) k_verify_vm_always(VerifyArgs a, DevPlan P) {
+    const uint32_t stride = gridDim.x * blockDim.x;
+    const uint32_t rounds = (a.n_lines_total + stride - 1) / stride;
+    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
+    uint32_t* stack = a.vm_stack + (size_t)g * lpx::VM_STACK_WORDS;
+    for (uint32_t it = 0; it < rounds; ++it, g += stride) {
+        bool live = g < a.n_lines_total;
+        uint32_t ls = 0, le = 0;
+        if (live) {
+            uint32_t k = a.n_logs == 1 ? 0 : upper_bound_dev<uint32_t>(a.first_line, a.n_logs + 1, g) - 1;
+            live = k < a.n_logs && g - a.first_line[k] < a.n_lines[k];
+            if (live) { ls = a.line_start[g]; le = a.line_end[g]; }
+        }
+        for (uint32_t q = 0; q < P.n_always_vm; ++q) {
+            const uint32_t r = P.always_vm_list[q];
+            const bool hit = live && vm_eval(P, r, a.text, ls, le, stack, a.ctr);
             emit_record(a.ctr, a.recs, a.rec_cap, hit, r, g);
         }
     }
@@ -742,11 +806,11 @@ struct lp_ctx {
 
     // scratch (grow-only)
     DevBuf text, log_off, tile_counts, counters, line_start, line_end, first_line, n_lines;
-    DevBuf cand, tasks, recs, recs_alt, cub_tmp, rx_begin, ctx_flags;
+    DevBuf cand, tasks, vm_tasks, vm_stack, recs, recs_alt, cub_tmp, rx_begin, ctx_flags;
     DevBuf ev_key, ev_key_alt, ev_log, slot_key, slot_key_alt, ev_idx, ev_idx_alt, rank_in_slot, freq_delta, prior;
     DevBuf out_line, out_pat, out_score, out_factors, sort_key, sort_key_alt, order, order_alt, log_sorted, log_sorted_alt;
     DevBuf rank, log_event_begin, n_unique;
-    size_t cand_cap = 0, task_cap = 0;
+    size_t cand_cap = 0, task_cap = 0, vm_task_cap = 0;
 
     // scan-phase state kept for the two-phase batch API
     struct Pending {
@@ -779,6 +843,8 @@ void upload_plan(lp_ctx* c) {
     d.rx_cmap = upload(K, pl.rx_cmap);
     d.always_list = upload(K, pl.always_list);
     d.n_always = (uint32_t)pl.always_list.size();
+    d.always_vm_list = upload(K, pl.always_vm_list);
+    d.n_always_vm = (uint32_t)pl.always_vm_list.size();
     d.bitmap = upload(K, pl.bitmap);
     d.table_bits = pl.table_bits;
     d.table_key = upload(K, pl.table_key);
@@ -879,13 +945,21 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     c->n_lines.ensure((size_t)n_logs * 4);
     const bool use_filter = !c->plan.lit_off.empty();
     const uint32_t n_always = (uint32_t)c->plan.always_list.size();
+    const uint32_t n_always_vm = (uint32_t)c->plan.always_vm_list.size();
+    const bool has_vm = c->plan.n_vm > 0;
+    const uint32_t vm_grid = (uint32_t)c->n_sm * 2, vm_block = 128;
+    if (has_vm) c->vm_stack.ensure((size_t)vm_grid * vm_block * lpx::VM_STACK_WORDS * 4);
 
     for (int attempt = 0;; ++attempt) {
         if (c->cand_cap == 0) c->cand_cap = std::max<size_t>(1u << 16, len / 8);
         if (c->task_cap == 0) c->task_cap = std::max<size_t>(1u << 16, len / 8);
         c->cand.ensure(c->cand_cap * 4);
         c->tasks.ensure(c->task_cap * 8);
-        const size_t rec_cap = c->task_cap + (size_t)G * n_always + 16;
+        if (has_vm) {
+            if (c->vm_task_cap == 0) c->vm_task_cap = std::max<size_t>(1u << 14, len / 64);
+            c->vm_tasks.ensure(c->vm_task_cap * 8);
+        }
+        const size_t rec_cap = c->task_cap + (has_vm ? c->vm_task_cap : 0) + (size_t)G * (n_always + n_always_vm) + 16;
         if (rec_cap >= 0x7FFFFFFFull) throw LimitFail("record capacity exceeds 2^31; shard the batch");
         c->recs.ensure(rec_cap * 8);
         c->recs_alt.ensure(rec_cap * 8);
@@ -912,17 +986,25 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         va.tasks = c->tasks.as<unsigned long long>(); va.task_cap = (uint32_t)std::min<size_t>(c->task_cap, 0xFFFFFFFFu); va.recs = c->recs.as<unsigned long long>();
         va.rec_cap = (uint32_t)rec_cap; va.ctr = ctr; va.n_lines_total = G;
         va.first_line = c->first_line.as<uint32_t>(); va.n_lines = c->n_lines.as<uint32_t>(); va.n_logs = n_logs;
+        va.vm_tasks = c->vm_tasks.as<unsigned long long>(); va.vm_task_cap = (uint32_t)std::min<size_t>(c->vm_task_cap, 0xFFFFFFFFu);
+        va.vm_stack = c->vm_stack.as<uint32_t>();
         if (use_filter) {
             ConfirmArgs ca{};
             ca.text = d_text; ca.len = len; ca.cand = c->cand.as<uint32_t>(); ca.cand_cap = sa.cand_cap;
             ca.line_start = c->line_start.as<uint32_t>(); ca.line_end = c->line_end.as<uint32_t>(); ca.n_lines_total = G;
             ca.tasks = c->tasks.as<unsigned long long>(); ca.task_cap = (uint32_t)std::min<size_t>(c->task_cap, 0xFFFFFFFFu); ca.ctr = ctr;
+            ca.vm_tasks = c->vm_tasks.as<unsigned long long>(); ca.vm_task_cap = va.vm_task_cap;
             k_confirm<<<c->n_sm * 8, 256, 0, st>>>(ca, c->dp);
             k_verify<<<c->n_sm * 8, 256, 0, st>>>(va, c->dp);
             c->launches += 2;
+            if (has_vm) { k_verify_vm<<<vm_grid, vm_block, 0, st>>>(va, c->dp); c->launches += 1; }
         }
         if (n_always) {
             k_verify_always<<<std::min<uint32_t>(blocks_for(G, 256), c->n_sm * 8), 256, 0, st>>>(va, c->dp);
+            c->launches += 1;
+        }
+        if (n_always_vm) {
+            k_verify_vm_always<<<vm_grid, vm_block, 0, st>>>(va, c->dp);
             c->launches += 1;
         }
         CK(cudaEventRecord(c->ev[3], st));
@@ -935,9 +1017,10 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         if (h.overflow & 1u) c->cand_cap = std::max<size_t>(c->cand_cap * 2, (size_t)h.n_cand + 1024);
         if (h.overflow & 2u) c->task_cap = std::max<size_t>(c->task_cap * 2, (size_t)h.n_tasks + 1024);
         if (h.overflow & 4u) c->task_cap = std::max<size_t>(c->task_cap * 2, (size_t)h.n_recs + 1024);
+        if (h.overflow & 32u) c->vm_task_cap = std::max<size_t>(c->vm_task_cap * 2, (size_t)h.n_vm_tasks + 1024);
     }
     c->tm.candidates = h.n_cand;
-    c->tm.verify_tasks = (uint64_t)h.n_tasks + (uint64_t)G * n_always;
+    c->tm.verify_tasks = (uint64_t)h.n_tasks + h.n_vm_tasks + (uint64_t)G * (n_always + n_always_vm);
 
     // ---- sort + unique the (regex, line) records
     uint32_t n_unique = 0;
@@ -1197,7 +1280,7 @@ void lp_destroy(lp_ctx* c) {
     cudaStreamSynchronize(c->stream);
     for (auto& b : c->plan_bufs) b.release();
     DevBuf* all[] = {&c->text, &c->log_off, &c->tile_counts, &c->counters, &c->line_start, &c->line_end, &c->first_line, &c->n_lines,
-                     &c->cand, &c->tasks, &c->recs, &c->recs_alt, &c->cub_tmp, &c->rx_begin, &c->ctx_flags, &c->ev_key, &c->ev_key_alt,
+                     &c->cand, &c->tasks, &c->vm_tasks, &c->vm_stack, &c->recs, &c->recs_alt, &c->cub_tmp, &c->rx_begin, &c->ctx_flags, &c->ev_key, &c->ev_key_alt,
                      &c->ev_log, &c->slot_key, &c->slot_key_alt, &c->ev_idx, &c->ev_idx_alt, &c->rank_in_slot, &c->freq_delta, &c->prior,
                      &c->out_line, &c->out_pat, &c->out_score, &c->out_factors, &c->sort_key, &c->sort_key_alt, &c->order, &c->order_alt,
                      &c->log_sorted, &c->log_sorted_alt, &c->rank, &c->log_event_begin, &c->n_unique, &c->d_lut};

@@ -28,8 +28,10 @@ struct DevPlan {
     const uint16_t* rx_start;
     const uint16_t* dfa_trans;
     const uint8_t* rx_cmap;
-    const uint32_t* always_list;
+    const uint32_t* always_list;      // DFA regexes without a usable literal
     uint32_t n_always;
+    const uint32_t* always_vm_list;   // bytecode regexes without a usable literal
+    uint32_t n_always_vm;
     // literals / gram filter
     const uint32_t* bitmap;
     uint32_t table_bits;
@@ -90,7 +92,8 @@ struct Counters {
     unsigned int n_events;
     unsigned int overflow;     // bit0 cand, bit1 tasks, bit2 recs, bit3 events, bit4 backtrack budget
     unsigned int n_unique;
-    unsigned int pad[6];
+    unsigned int n_vm_tasks;
+    unsigned int pad[5];
 };
 
 }  // namespace lpk

@@ -130,7 +130,8 @@ void build_plan(const std::vector<PlanPatternIn>& pats, Plan& pl, int64_t* bad) 
         pl.max_fanout = std::max<uint32_t>(pl.max_fanout, (uint32_t)by_primary[r].size());
         for (uint32_t p : by_primary[r]) pl.rxp_pat.push_back(p);
     }
-    for (uint32_t r = 0; r < pl.n_rx; ++r) if (pl.rx_always[r]) pl.always_list.push_back(r);
+    for (uint32_t r = 0; r < pl.n_rx; ++r)
+        if (pl.rx_always[r]) (pl.rx_kind[r] == RXK_DFA ? pl.always_list : pl.always_vm_list).push_back(r);
 
     // ---- literal table: de-duplicate (bytes, icase) across regexes
     std::map<std::pair<std::string, bool>, uint32_t> lit_ids;

@@ -42,7 +42,7 @@ struct Plan {
     std::vector<uint16_t> rx_start;
     std::vector<uint16_t> dfa_trans;
     std::vector<uint8_t> rx_cmap;         // 256 per regex
-    std::vector<uint32_t> always_list;
+    std::vector<uint32_t> always_list, always_vm_list;
     // bytecode programs (RXK_VM)
     std::vector<uint32_t> rx_vm_off, rx_vm_len, rx_vm_slots, rx_vm_caps, rx_vm_set_base;
     std::vector<VmInsn> vm_code;

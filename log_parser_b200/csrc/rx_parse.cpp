@@ -589,6 +589,23 @@ void lookbehind_bounded(const Ast* a) {
     for (auto& k : a->kids) lookbehind_bounded(k.get());
 }
 
+bool has_assert(const Ast* a) {
+    if (a->kind == AstKind::Assert) return true;
+    for (auto& k : a->kids) if (has_assert(k.get())) return true;
+    return false;
+}
+// Loop.match sends an iteration that consumed nothing straight on to what follows the loop, even
+// when iterations are still owed. When the body can only match empty where an assertion holds
+// (e.g. (?:^x*){2}a), that prunes matches a pure regular-language reading would find, so such
+// loops are decided by the backtracking verifier, which follows the same rule.
+bool has_assertion_guarded_empty_loop(const Ast* a) {
+    if (a->kind == AstKind::Repeat && a->kids[0]->kind != AstKind::Set && (a->max < 0 || a->max > 1) &&
+        a->kids[0]->min_len == 0 && has_assert(a->kids[0].get()))
+        return true;
+    for (auto& k : a->kids) if (has_assertion_guarded_empty_loop(k.get())) return true;
+    return false;
+}
+
 }  // namespace
 
 ParsedRegex parse_java_regex(const std::string& utf8, int flags) {
@@ -607,7 +624,7 @@ ParsedRegex parse_java_regex(const std::string& utf8, int flags) {
     ParsedRegex out;
     out.root = std::move(root);
     out.n_groups = p.groups;
-    out.regular = p.regular;
+    out.regular = p.regular && !has_assertion_guarded_empty_loop(out.root.get());
     return out;
 }
 

@@ -187,6 +187,25 @@ def test_device_resident_equals_host_path(parser):
     assert t["kernel_launches"] > 5 and t["scan_ms"] > 0
 
 
+def test_c3_nonregular_patterns(parser, oracle):
+    """configs[2] shape: look-around / back-reference / possessive+atomic primaries take the
+    backtracking verifier on prefiltered candidate lines; results must still equal the oracle's."""
+    wl = synth.make_patterns(80, 31337, nonregular_frac=0.5, noliteral=2)
+    extra = [PatternSpec(id="nl1", primary_regex=r"(?<=\[)\w+-(\d+)\] \w+\.\w+", confidence=0.5, lines_before=3, lines_after=3),
+             PatternSpec(id="nl2", primary_regex=r"x.{0,60}yz", confidence=0.5),
+             PatternSpec(id="nl3", primary_regex=r"(?m)^\tat .*\)$", confidence=0.4, secondaries=[SecondaryPattern(r"(?i)caused by(?=:)", 0.5, 20)])]
+    pats = wl.patterns + extra
+    log = synth.make_log(wl, 4000, 4242, pool_blocks=1500, hit_rate=0.05)
+    parser.load_patterns(pats)
+    res = parser.analyze(log, options=binding.OPT_FACTORS)
+    ora = oracle.analyze(ScoringConfig(), pats, log)
+    assert len(ora.line) > 100
+    nonreg = sum(1 for i in set(ora.pattern.tolist()) if any(t in pats[i].primary_regex for t in ("(?<", "(?=", "\\1", "(?>", "(?m)")))
+    assert nonreg >= 5, "the log must exercise the backtracking path"
+    _check(res, ora)
+    np.testing.assert_array_equal(res.score, ora.score)
+
+
 def test_bad_pattern_reports_index(parser):
     pats = [PatternSpec(id="ok", primary_regex="fine", confidence=1.0), PatternSpec(id="bad", primary_regex="a{,2}", confidence=1.0)]
     with pytest.raises(binding.PatternSyntaxError) as ei:

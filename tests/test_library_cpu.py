@@ -57,7 +57,7 @@ def test_product_does_not_import_oracle():
 
 def test_dfa_tables_vs_oracle_random(lib, oracle):
     rng = random.Random(4242)
-    checked = 0
+    checked = n_dfa = 0
     for _ in range(1500):
         j, _p = Gen(rng, regular_only=True).regex()
         try:
@@ -65,12 +65,53 @@ def test_dfa_tables_vs_oracle_random(lib, oracle):
         except (oracle.OracleSyntaxError, oracle.OracleUnsupported):
             continue
         d = binding.DebugRegex(j)
-        assert d.is_dfa, j
+        n_dfa += d.is_dfa      # a few land on the bytecode path (assertion-guarded empty loops)
         for _k in range(10):
             t = gen_text(rng)
             assert bool(d.match(t)) == o.find(t), (j, t)
             checked += 1
-    assert checked > 10000
+    assert checked > 10000 and n_dfa > 1200
+
+
+def test_backtracking_bytecode_vs_oracle_random(lib, oracle):
+    """The interpreter of csrc/vm_exec.h (same code on host and device) against the oracle, on
+    patterns with look-around, back-references, possessive/atomic constructs — and on regular ones
+    forced through the bytecode path."""
+    rng = random.Random(77)
+    checked = budget = 0
+    for _ in range(900):
+        j, _p = Gen(rng, max_depth=2).regex()
+        try:
+            o = oracle.Regex(j)
+        except (oracle.OracleSyntaxError, oracle.OracleUnsupported):
+            continue
+        try:
+            d = binding.DebugRegex(j, force_vm=True)
+        except binding.UnsupportedRegexError:
+            continue
+        assert not d.is_dfa
+        for _k in range(8):
+            t = gen_text(rng, maxlen=16)
+            got = d.match(t)
+            if got < 0:
+                budget += 1      # bounded backtracking: reported as LP_ERR_BACKTRACK by the device path
+                continue
+            assert bool(got) == o.find(t), (j, t)
+            checked += 1
+    assert checked > 5000 and budget < checked // 100
+
+
+@pytest.mark.parametrize("pat,text", [
+    (r"(?<![\w.])FooError(?!\w)", "x FooError: y"), (r"(?<![\w.])FooError(?!\w)", "x.FooError"),
+    (r"Foo: (\w+) .*\b\1\b", "Foo: abc failed for abc again"), (r"Foo: (\w+) .*\b\1\b", "Foo: abc failed for abd again"),
+    (r"\bFoo(?>: \w++)", "a Foo: bar"), (r"(?m)^a", "b\ra"), (r"(?m)a$", "a\rb"), (r"(?m)^$", ""),
+    (r"x.{0,40}y", "x" + "a" * 30 + "y"), (r"x.{0,40}y", "x" + "a" * 41 + "y"), (r"(?=.*\[edge1\])lost \d+", "lost 12 [edge1]"),
+    (r"(?i)(a)\1", "aA"), (r"(?<=é)x", "éx"), (r"(?<=\bab|c)x", "abx"), (r"^(?:a|ab)*+c", "abac"), (r"(a*)*b", "aaaa"),
+    (r"(?:^_??[^x]*){2}a", "  a:.Ec_11E"), (r"(\w+)\s\1$", "hello hello\r"), (r"(?<=\d{2,4})ms", "x1234ms"),
+])
+def test_backtracking_cases(lib, oracle, pat, text):
+    d = binding.DebugRegex(pat)
+    assert bool(d.match(text)) == oracle.Regex(pat).find(text)
 
 
 @pytest.mark.parametrize("pat,flags", [
