@@ -178,6 +178,9 @@ typedef struct lp_timings {
     uint64_t scan_bytes;        /* algorithmic bytes of the scan kernel: B + 4(N+1) + 8M          */
     uint64_t candidates;        /* gram-filter hits handed to confirmation                        */
     uint64_t verify_tasks;      /* (line, regex) pairs verified                                   */
+    float dfa_scan_ms;          /* the always-on shared-memory product-DFA scan (part of verify_ms) */
+    float reserved;
+    uint64_t dfa_scan_bytes;    /* its algorithmic bytes: B + 8(G+1) + G                          */
 } lp_timings;
 int lp_get_timings(const lp_ctx* ctx, lp_timings* out);
 /* The cudaStream_t all kernels and copies of this context are issued on (for callers that order

@@ -75,7 +75,8 @@ class Timings(C.Structure):
     _fields_ = [
         ("total_ms", C.c_float), ("scan_ms", C.c_float), ("verify_ms", C.c_float), ("score_ms", C.c_float),
         ("h2d_ms", C.c_float), ("kernel_launches", C.c_uint64), ("scan_bytes", C.c_uint64),
-        ("candidates", C.c_uint64), ("verify_tasks", C.c_uint64),
+        ("candidates", C.c_uint64), ("verify_tasks", C.c_uint64), ("dfa_scan_ms", C.c_float), ("reserved", C.c_float),
+        ("dfa_scan_bytes", C.c_uint64),
     ]
 
 

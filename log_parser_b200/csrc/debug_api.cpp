@@ -5,6 +5,7 @@
 #include <string>
 
 #include "rx.h"
+#include "plan.h"
 #include "vm.h"
 
 using namespace lpx;
@@ -79,6 +80,27 @@ size_t lp_debug_rx_literals(void* h, char* buf, size_t cap) {
         buf[k] = 0;
     }
     return out.size();
+}
+
+// Builds one scan group (product DFA) from `n` regexes and walks `text` through its serialised
+// tables exactly as k_dfa_scan does. Returns the hit mask (bit k = regex k), or 0xFFFFFFFF when the
+// group cannot be built.
+uint32_t lp_debug_group_match(const char* const* regexes, const int* flags, size_t n, const uint8_t* text, size_t len) {
+    try {
+        std::vector<ParsedRegex> pr;
+        std::vector<const Ast*> roots;
+        for (size_t i = 0; i < n; ++i) pr.push_back(parse_java_regex(regexes[i], flags ? flags[i] : 0));
+        for (auto& p : pr) { if (!p.regular) return 0xFFFFFFFFu; roots.push_back(p.root.get()); }
+        MultiDfa d;
+        if (!build_multi_dfa(roots, d, 8192)) return 0xFFFFFFFFu;
+        std::vector<uint32_t> rx(n), blob;
+        for (size_t i = 0; i < n; ++i) rx[i] = (uint32_t)i + 4;
+        serialise_group(rx, d, blob);
+        const uint32_t a = run_group_blob(blob, text, len), b = d.run(text, len);
+        return a == b ? a : 0xFFFFFFFEu;
+    } catch (const std::exception&) {
+        return 0xFFFFFFFFu;
+    }
 }
 
 }  // extern "C"

@@ -146,7 +146,7 @@ struct ScanArgs {
     uint32_t* line_end;               // [G]
     uint32_t* first_line;             // [n_logs+1]
     const uint32_t* bitmap;           // GRAM_WORDS words
-    uint32_t* cand;                   // candidate byte positions
+    unsigned long long* cand;         // candidates: (global line << 32) | byte position
     uint32_t cand_cap;
     Counters* ctr;
     int use_filter;
@@ -225,19 +225,33 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_lines_filter(ScanArgs a) {
                     ++j;
                 }
             }
-            // ---- gram prefilter over the 16 windows that start in this thread's bytes
+            // ---- gram prefilter over the 16 windows that start in this thread's bytes:
+            // two-probe Bloom test; the first probe is evaluated for every window, the second only
+            // on the (rare) first-probe hits
             if (a.use_filter) {
                 uint32_t nxt = __shfl_down_sync(0xffffffffu, v.x, 1);
                 if (lane == 31) nxt = (pos + 16 < a.len) ? load4_safe(a.text, pos + 16, a.len) : 0u;
-                const uint32_t w[5] = {v.x, v.y, v.z, v.w, nxt};
+                const uint32_t w[5] = {v.x | 0x20202020u, v.y | 0x20202020u, v.z | 0x20202020u, v.w | 0x20202020u, nxt | 0x20202020u};
                 uint32_t hits = 0;
 #pragma unroll
-                for (int i = 0; i < 16; ++i) {
-                    const uint32_t win = __funnelshift_r(w[i >> 2], w[(i >> 2) + 1], (i & 3) * 8) | 0x20202020u;
-                    const uint32_t h = (win * GRAM_MUL) >> (32 - GRAM_BITS);
-                    hits |= ((s_bitmap[h >> 5] >> (h & 31)) & 1u) << i;
+                for (int i = 15; i >= 0; --i) {
+                    const uint32_t win = (i & 3) ? __funnelshift_r(w[i >> 2], w[(i >> 2) + 1], (i & 3) * 8) : w[i >> 2];
+                    const uint32_t h = win * GRAM_MUL;
+                    const uint32_t word = s_bitmap[h >> (32 - GRAM_BITS + 5)];
+                    hits = (hits << 1) | (__funnelshift_r(word, 0u, h >> (32 - GRAM_BITS)) & 1u);
                 }
                 if (pos >= a.len) hits = 0;
+                if (hits) {   // second probe (independent hash) removes almost all false positives
+                    uint32_t hm = hits;
+                    while (hm) {
+                        const int i = __ffs(hm) - 1;
+                        hm &= hm - 1;
+                        const uint32_t win = (i & 3) ? __funnelshift_r(w[i >> 2], w[(i >> 2) + 1], (i & 3) * 8) : w[i >> 2];
+                        const uint32_t h2 = win * GRAM_MUL2;
+                        const uint32_t word = s_bitmap[h2 >> (32 - GRAM_BITS + 5)];
+                        if (!((word >> ((h2 >> (32 - GRAM_BITS)) & 31u)) & 1u)) hits &= ~(1u << i);
+                    }
+                }
                 const uint32_t n = __popc(hits);
                 if (__ballot_sync(0xffffffffu, n != 0)) {
                     uint32_t hinc = n;
@@ -251,7 +265,11 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_lines_filter(ScanArgs a) {
                     while (hm) {
                         const int i = __ffs(hm) - 1;
                         hm &= hm - 1;
-                        if (base < a.cand_cap) a.cand[base] = (uint32_t)(pos + i);
+                        const uint64_t p = pos + i;
+                        uint32_t k = k0;
+                        if (inner) k = upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, p) - 1;
+                        const uint32_t g = excl + __popc(nlm & ((1u << i) - 1u)) + k;
+                        if (base < a.cand_cap) a.cand[base] = ((unsigned long long)g << 32) | (uint32_t)p;
                         else atomicOr(&a.ctr->overflow, 1u);
                         ++base;
                     }
@@ -317,7 +335,7 @@ __device__ __forceinline__ void emit_record(Counters* ctr, unsigned long long* r
 struct ConfirmArgs {
     const uint8_t* text;
     uint64_t len;
-    const uint32_t* cand;
+    const unsigned long long* cand;
     uint32_t cand_cap;
     const uint32_t* line_start;
     const uint32_t* line_end;
@@ -331,7 +349,8 @@ struct ConfirmArgs {
 __global__ void __launch_bounds__(256) k_confirm(ConfirmArgs a, DevPlan P) {
     const uint32_t n = min(a.ctr->n_cand, a.cand_cap);
     for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < n; c += gridDim.x * blockDim.x) {
-        const uint32_t pos = a.cand[c];
+        const unsigned long long cd = a.cand[c];
+        const uint32_t pos = (uint32_t)cd, g = (uint32_t)(cd >> 32);
         uint32_t w = 0;
 #pragma unroll
         for (int i = 0; i < 4; ++i) if ((uint64_t)pos + i < a.len) w |= (uint32_t)a.text[pos + i] << (8 * i);
@@ -341,7 +360,6 @@ __global__ void __launch_bounds__(256) k_confirm(ConfirmArgs a, DevPlan P) {
         uint32_t key;
         while ((key = P.table_key[slot]) != 0 && key != f) slot = (slot + 1) & tmask;
         if (key == 0) continue;
-        const uint32_t g = upper_bound_dev<uint32_t>(a.line_start, a.n_lines_total, pos) - 1;
         const uint32_t ls = a.line_start[g], le = a.line_end[g];
         const uint32_t lb = P.table_begin[slot], lc = P.table_count[slot];
         for (uint32_t q = 0; q < lc; ++q) {
@@ -486,6 +504,154 @@ __global__ void __launch_bounds__(128) k_verify_vm_always(VerifyArgs a, DevPlan 
             const bool hit = live && vm_eval(P, r, a.text, ls, le, stack, a.ctr);
             emit_record(a.ctr, a.recs, a.rec_cap, hit, r, g);
         }
+    }
+}
+
+
+// ------------------------------------------------------------------ always-on DFA scan
+// The multi-pattern DFA scan proper: every line is walked once through up to DS_MAXG product
+// automata (context regexes of CAS:27-34 + every DFA pattern without a usable literal, AS:93-95).
+// Transition tables, class maps and result masks are resident in shared memory for the life of the
+// CTA. One thread walks one line; it streams the line through registers with 16-byte loads, one
+// chunk prefetched ahead. (A TMA-staged shared-memory tile variant was measured first: with ~240
+// lines per 32 KiB tile the per-tile barrier left most threads idle — profiles/r01_v2_*.)
+constexpr uint32_t DS_THREADS = 256, DS_MAXG = 4;
+
+struct DfaScanArgs {
+    const uint8_t* text;
+    uint64_t len;
+    const uint32_t* line_start;
+    const uint32_t* line_end;
+    uint32_t n_lines_total;
+    const uint32_t* first_line;
+    const uint32_t* n_lines;
+    uint32_t n_logs;
+    const uint32_t* blob[DS_MAXG];
+    uint32_t blob_words[DS_MAXG];
+    uint32_t n_groups;
+    const uint8_t* rx_record;
+    uint8_t* ctx_flags;          // written for every line when write_flags
+    int write_flags;
+    unsigned long long* recs;
+    uint32_t rec_cap;
+    Counters* ctr;
+};
+
+__device__ __forceinline__ uint4 load16_any(const uint8_t* __restrict__ text, uint64_t pos, uint64_t len) {
+    if (pos + 16 <= len) return __ldg(reinterpret_cast<const uint4*>(text + pos));
+    if (pos >= len) return make_uint4(0, 0, 0, 0);
+    return load16(text, pos, len);
+}
+
+template <int NG>
+__global__ void __launch_bounds__(DS_THREADS) k_dfa_scan(DfaScanArgs a) {
+    extern __shared__ __align__(16) uint32_t ds_tabs[];
+    __shared__ uint32_t s_goff[DS_MAXG], s_recmask[DS_MAXG];
+    __shared__ int s_ctxbit[DS_MAXG][4];
+    {
+        uint32_t off = 0;
+        for (int g = 0; g < NG; ++g) {
+            for (uint32_t i = threadIdx.x; i < a.blob_words[g]; i += DS_THREADS) ds_tabs[off + i] = __ldg(a.blob[g] + i);
+            if (threadIdx.x == 0) s_goff[g] = off;
+            off += (a.blob_words[g] + 3u) & ~3u;
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < NG) {
+        const uint32_t* h = ds_tabs + s_goff[threadIdx.x];
+        uint32_t rm = 0;
+        int cb[4] = {-1, -1, -1, -1};
+        for (uint32_t k = 0; k < h[4]; ++k) {
+            const uint32_t r = h[5 + k];
+            if (a.rx_record[r]) rm |= 1u << k;
+            if (r < 4) cb[r] = (int)k;
+        }
+        s_recmask[threadIdx.x] = rm;
+        for (int c = 0; c < 4; ++c) s_ctxbit[threadIdx.x][c] = cb[c];
+    }
+    __syncthreads();
+
+    const uint8_t* cm[NG];
+    const uint16_t* T[NG];
+    const uint32_t* smask[NG];
+    uint32_t nc[NG], ff[NG], st0[NG], qa[NG], qb[NG], nb0[NG], nb1[NG];
+#pragma unroll
+    for (int g = 0; g < NG; ++g) {
+        const uint32_t* h = ds_tabs + s_goff[g];
+        nc[g] = h[1]; st0[g] = h[2]; ff[g] = h[3];
+        qa[g] = h[33]; qb[g] = h[34]; nb0[g] = h[35]; nb1[g] = h[36];
+        cm[g] = reinterpret_cast<const uint8_t*>(h + 37);
+        smask[g] = h + 101;
+        T[g] = reinterpret_cast<const uint16_t*>(h + 101 + h[0]);
+    }
+
+    const uint32_t stride = gridDim.x * DS_THREADS;
+    for (uint32_t g = blockIdx.x * DS_THREADS + threadIdx.x; g < a.n_lines_total; g += stride) {
+        const uint32_t k = a.n_logs == 1 ? 0 : upper_bound_dev<uint32_t>(a.first_line, a.n_logs + 1, g) - 1;
+        const bool live = k < a.n_logs && g - a.first_line[k] < a.n_lines[k];
+        uint32_t flags = 0;
+        if (live) {
+            const uint32_t ls = a.line_start[g], le = a.line_end[g];
+            uint32_t st[NG];
+#pragma unroll
+            for (int q = 0; q < NG; ++q) st[q] = st0[q];
+            if (le > ls) {
+                const long tpos = tail_terminator(a.text, ls, le);
+                const uint32_t tp = tpos < 0 ? 0xFFFFFFFFu : (uint32_t)tpos;
+                uint32_t i = ls;
+                uint64_t chunk = (uint64_t)(ls & ~15u);
+                uint4 cur = load16_any(a.text, chunk, a.len);
+                uint4 nxt = (chunk + 16 < le) ? load16_any(a.text, chunk + 16, a.len) : make_uint4(0, 0, 0, 0);
+                uint32_t wsel = (i >> 2) & 3u;
+                uint32_t w = (wsel == 0 ? cur.x : wsel == 1 ? cur.y : wsel == 2 ? cur.z : cur.w) >> ((i & 3u) * 8u);
+                for (;;) {
+                    const uint32_t b = w & 0xFFu;
+                    w >>= 8;
+                    if (i == tp) {
+#pragma unroll
+                        for (int q = 0; q < NG; ++q) if (st[q] < ff[q]) st[q] = T[q][st[q] * nc[q] + nc[q] - 2];
+                    }
+                    bool active = false;
+#pragma unroll
+                    for (int q = 0; q < NG; ++q) {
+                        if (st[q] < ff[q]) {
+                            const uint32_t cls = cm[q][b];
+                            // idle state + boring byte: the next idle state follows from word-ness alone
+                            if ((st[q] == qa[q] || st[q] == qb[q]) && cls < nb1[q]) st[q] = cls < nb0[q] ? qa[q] : qb[q];
+                            else st[q] = T[q][st[q] * nc[q] + cls];
+                            active = true;
+                        }
+                    }
+                    ++i;
+                    if (i >= le || !active) break;
+                    if ((i & 3u) == 0) {
+                        wsel = (i >> 2) & 3u;
+                        if (wsel == 0) {
+                            cur = nxt;
+                            chunk += 16;
+                            if (chunk + 16 < le) nxt = load16_any(a.text, chunk + 16, a.len);
+                        }
+                        w = wsel == 0 ? cur.x : wsel == 1 ? cur.y : wsel == 2 ? cur.z : cur.w;
+                    }
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < NG; ++q) {
+                const uint32_t mask = smask[q][T[q][st[q] * nc[q] + nc[q] - 1]];
+#pragma unroll
+                for (int c = 0; c < 4; ++c) { const int bit = s_ctxbit[q][c]; if (bit >= 0) flags |= ((mask >> bit) & 1u) << c; }
+                uint32_t pend = mask & s_recmask[q];
+                const uint32_t* rxs = ds_tabs + s_goff[q] + 5;
+                while (pend) {        // records of literal-free user patterns are sparse: one atomic each
+                    const uint32_t r = rxs[__ffs(pend) - 1];
+                    pend &= pend - 1;
+                    const uint32_t idx = atomicAdd(&a.ctr->n_recs, 1u);
+                    if (idx < a.rec_cap) a.recs[idx] = ((unsigned long long)r << 32) | g;
+                    else atomicOr(&a.ctr->overflow, 4u);
+                }
+            }
+        }
+        if (a.write_flags) a.ctx_flags[g] = (uint8_t)flags;
     }
 }
 
@@ -800,6 +966,13 @@ struct lp_ctx {
     lpx::Plan plan;
     bool loaded = false;
     std::vector<DevBuf> plan_bufs;
+    std::vector<const uint32_t*> d_group_blob;
+    std::vector<uint32_t> group_words;
+    const uint8_t* d_rx_record = nullptr;
+    uint32_t n_group_record_rx = 0;
+    DevBuf f_bitmap, f_key, f_begin, f_count, f_lits, f_goff;   // prefilter tables (re-uploaded by calibration)
+    bool calibrated = false;
+    int recalibrations = 0;
     DevPlan dp{};
     DevBuf d_lut;
     ScoreCfg sc{};
@@ -821,13 +994,50 @@ struct lp_ctx {
         int options = 0;
     } pend;
 
-    cudaEvent_t ev[6]{};
+    cudaEvent_t ev[8]{};
     lp_timings tm{};
     uint64_t launches = 0;
 };
 
 namespace {
 
+template <class T>
+const T* upload_into(DevBuf& b, const std::vector<T>& v) {
+    b.ensure(std::max<size_t>(v.size() * sizeof(T), 16));
+    if (!v.empty()) CK(cudaMemcpy(b.p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+    return static_cast<const T*>(b.p);
+}
+void upload_filter(lp_ctx* c) {
+    const lpx::Plan& pl = c->plan;
+    DevPlan& d = c->dp;
+    d.bitmap = upload_into(c->f_bitmap, pl.bitmap);
+    d.table_bits = pl.table_bits;
+    d.table_key = upload_into(c->f_key, pl.table_key);
+    d.table_begin = upload_into(c->f_begin, pl.table_begin);
+    d.table_count = upload_into(c->f_count, pl.table_count);
+    d.gram_lits = upload_into(c->f_lits, pl.gram_lits);
+    d.lit_gram_off = upload_into(c->f_goff, pl.lit_gram_off);
+}
+// One-time tuning of the literal prefilter against the first log this context sees: 4 x 1 MiB of
+// its text decide which 4-byte window of each literal is the rarest. Results never depend on it.
+void calibrate_filter(lp_ctx* c, const uint8_t* d_text, uint64_t len) {
+    const uint64_t piece = 1u << 20;
+    std::vector<uint8_t> sample;
+    for (int k = 0; k < 4; ++k) {
+        const uint64_t off = (len / 4) * k & ~15ull;
+        if (off >= len) break;
+        const uint64_t n = std::min<uint64_t>(piece, len - off);
+        const size_t at = sample.size();
+        sample.resize(at + n + 1);
+        CK(cudaMemcpyAsync(sample.data() + at, d_text + off, n, cudaMemcpyDeviceToHost, c->stream));
+        sample[at + n] = '\n';
+        if (len <= piece) break;
+    }
+    CK(cudaStreamSynchronize(c->stream));
+    lpx::select_grams(c->plan, sample.data(), sample.size());
+    upload_filter(c);
+    c->calibrated = true;
+}
 void upload_plan(lp_ctx* c) {
     for (auto& b : c->plan_bufs) b.release();
     c->plan_bufs.clear();
@@ -845,16 +1055,10 @@ void upload_plan(lp_ctx* c) {
     d.n_always = (uint32_t)pl.always_list.size();
     d.always_vm_list = upload(K, pl.always_vm_list);
     d.n_always_vm = (uint32_t)pl.always_vm_list.size();
-    d.bitmap = upload(K, pl.bitmap);
-    d.table_bits = pl.table_bits;
-    d.table_key = upload(K, pl.table_key);
-    d.table_begin = upload(K, pl.table_begin);
-    d.table_count = upload(K, pl.table_count);
-    d.gram_lits = upload(K, pl.gram_lits);
+    upload_filter(c);
     d.lit_bytes = upload(K, pl.lit_bytes);
     d.lit_off = upload(K, pl.lit_off);
     d.lit_len = upload(K, pl.lit_len);
-    d.lit_gram_off = upload(K, pl.lit_gram_off);
     d.lit_icase = upload(K, pl.lit_icase);
     d.lit_rx_begin = upload(K, pl.lit_rx_begin);
     d.lit_rx = upload(K, pl.lit_rx);
@@ -885,6 +1089,15 @@ void upload_plan(lp_ctx* c) {
     d.vm_code = upload(K, pl.vm_code);
     d.vm_set_off = upload(K, pl.vm_set_off);
     d.vm_set_ranges = upload(K, pl.vm_set_ranges);
+    c->d_group_blob.clear();
+    c->group_words.clear();
+    c->n_group_record_rx = 0;
+    for (const auto& g : pl.groups) {
+        c->d_group_blob.push_back(upload(K, g.blob));
+        c->group_words.push_back((uint32_t)g.blob.size());
+        for (uint32_t r : g.rx) c->n_group_record_rx += pl.rx_record[r];
+    }
+    c->d_rx_record = upload(K, pl.rx_record);
 }
 
 inline uint32_t blocks_for(uint64_t n, uint32_t threads) { return (uint32_t)std::max<uint64_t>(1, (n + threads - 1) / threads); }
@@ -943,7 +1156,9 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     c->line_end.ensure((size_t)(G + 1) * 4);
     c->first_line.ensure((size_t)(n_logs + 1) * 4);
     c->n_lines.ensure((size_t)n_logs * 4);
+    c->ctx_flags.ensure(((size_t)G / 4 + 2) * 4);
     const bool use_filter = !c->plan.lit_off.empty();
+    if (use_filter && !c->calibrated && len >= 4096) calibrate_filter(c, d_text, len);
     const uint32_t n_always = (uint32_t)c->plan.always_list.size();
     const uint32_t n_always_vm = (uint32_t)c->plan.always_vm_list.size();
     const bool has_vm = c->plan.n_vm > 0;
@@ -953,13 +1168,14 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     for (int attempt = 0;; ++attempt) {
         if (c->cand_cap == 0) c->cand_cap = std::max<size_t>(1u << 16, len / 8);
         if (c->task_cap == 0) c->task_cap = std::max<size_t>(1u << 16, len / 8);
-        c->cand.ensure(c->cand_cap * 4);
+        c->cand.ensure(c->cand_cap * 8);
         c->tasks.ensure(c->task_cap * 8);
         if (has_vm) {
             if (c->vm_task_cap == 0) c->vm_task_cap = std::max<size_t>(1u << 14, len / 64);
             c->vm_tasks.ensure(c->vm_task_cap * 8);
         }
-        const size_t rec_cap = c->task_cap + (has_vm ? c->vm_task_cap : 0) + (size_t)G * (n_always + n_always_vm) + 16;
+        const size_t rec_cap = c->task_cap + (has_vm ? c->vm_task_cap : 0) + (size_t)G * (n_always + n_always_vm) +
+                               (c->n_group_record_rx ? std::max<size_t>(1u << 16, (size_t)G / 4 * c->n_group_record_rx) : 0) + 16;
         if (rec_cap >= 0x7FFFFFFFull) throw LimitFail("record capacity exceeds 2^31; shard the batch");
         c->recs.ensure(rec_cap * 8);
         c->recs_alt.ensure(rec_cap * 8);
@@ -970,7 +1186,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         sa.log_off = c->log_off.as<uint64_t>(); sa.n_logs = n_logs;
         sa.line_start = c->line_start.as<uint32_t>(); sa.line_end = c->line_end.as<uint32_t>();
         sa.first_line = c->first_line.as<uint32_t>(); sa.bitmap = c->dp.bitmap;
-        sa.cand = c->cand.as<uint32_t>(); sa.cand_cap = (uint32_t)std::min<size_t>(c->cand_cap, 0xFFFFFFFFu);
+        sa.cand = c->cand.as<unsigned long long>(); sa.cand_cap = (uint32_t)std::min<size_t>(c->cand_cap, 0xFFFFFFFFu);
         sa.ctr = ctr; sa.use_filter = use_filter ? 1 : 0;
         const size_t smem = use_filter ? GRAM_WORDS * 4 : 0;
         const uint32_t grid = std::min<uint32_t>(n_tiles, (uint32_t)c->n_sm * 3);
@@ -990,7 +1206,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         va.vm_stack = c->vm_stack.as<uint32_t>();
         if (use_filter) {
             ConfirmArgs ca{};
-            ca.text = d_text; ca.len = len; ca.cand = c->cand.as<uint32_t>(); ca.cand_cap = sa.cand_cap;
+            ca.text = d_text; ca.len = len; ca.cand = c->cand.as<unsigned long long>(); ca.cand_cap = sa.cand_cap;
             ca.line_start = c->line_start.as<uint32_t>(); ca.line_end = c->line_end.as<uint32_t>(); ca.n_lines_total = G;
             ca.tasks = c->tasks.as<unsigned long long>(); ca.task_cap = (uint32_t)std::min<size_t>(c->task_cap, 0xFFFFFFFFu); ca.ctr = ctr;
             ca.vm_tasks = c->vm_tasks.as<unsigned long long>(); ca.vm_task_cap = va.vm_task_cap;
@@ -1007,6 +1223,33 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
             k_verify_vm_always<<<vm_grid, vm_block, 0, st>>>(va, c->dp);
             c->launches += 1;
         }
+        // always-on product-DFA scan (context regexes + literal-free DFA patterns)
+        CK(cudaEventRecord(c->ev[6], st));
+        for (size_t g0 = 0; g0 < c->d_group_blob.size(); g0 += DS_MAXG) {
+            DfaScanArgs da{};
+            da.text = d_text; da.len = len;
+            da.line_start = c->line_start.as<uint32_t>(); da.line_end = c->line_end.as<uint32_t>(); da.n_lines_total = G;
+            da.first_line = c->first_line.as<uint32_t>(); da.n_lines = c->n_lines.as<uint32_t>(); da.n_logs = n_logs;
+            size_t tab_bytes = 0;
+            da.n_groups = (uint32_t)std::min<size_t>(DS_MAXG, c->d_group_blob.size() - g0);
+            for (uint32_t q = 0; q < da.n_groups; ++q) {
+                da.blob[q] = c->d_group_blob[g0 + q]; da.blob_words[q] = c->group_words[g0 + q];
+                tab_bytes += ((size_t)c->group_words[g0 + q] + 3) / 4 * 16;
+            }
+            da.rx_record = c->d_rx_record; da.ctx_flags = c->ctx_flags.as<uint8_t>();
+            da.write_flags = (g0 == 0 && c->plan.ctx_in_groups) ? 1 : 0;
+            da.recs = c->recs.as<unsigned long long>(); da.rec_cap = (uint32_t)rec_cap; da.ctr = ctr;
+            const uint32_t per_sm = (uint32_t)std::max<size_t>(1, std::min<size_t>(8, (200 * 1024) / std::max<size_t>(tab_bytes, 1)));
+            const uint32_t grid = std::min<uint32_t>(blocks_for(G, DS_THREADS), (uint32_t)c->n_sm * per_sm);
+            switch (da.n_groups) {
+                case 1: k_dfa_scan<1><<<grid, DS_THREADS, tab_bytes, st>>>(da); break;
+                case 2: k_dfa_scan<2><<<grid, DS_THREADS, tab_bytes, st>>>(da); break;
+                case 3: k_dfa_scan<3><<<grid, DS_THREADS, tab_bytes, st>>>(da); break;
+                default: k_dfa_scan<4><<<grid, DS_THREADS, tab_bytes, st>>>(da); break;
+            }
+            c->launches += 1;
+        }
+        CK(cudaEventRecord(c->ev[7], st));
         CK(cudaEventRecord(c->ev[3], st));
         CK(cudaMemcpyAsync(&h, ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
         CK(cudaStreamSynchronize(st));
@@ -1020,14 +1263,14 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         if (h.overflow & 32u) c->vm_task_cap = std::max<size_t>(c->vm_task_cap * 2, (size_t)h.n_vm_tasks + 1024);
     }
     c->tm.candidates = h.n_cand;
+    if (use_filter && (uint64_t)h.n_cand * 2 > (uint64_t)G + 1024 && c->recalibrations < 2) { c->calibrated = false; ++c->recalibrations; }
     c->tm.verify_tasks = (uint64_t)h.n_tasks + h.n_vm_tasks + (uint64_t)G * (n_always + n_always_vm);
 
     // ---- sort + unique the (regex, line) records
     uint32_t n_unique = 0;
     const uint32_t n_recs = h.n_recs;
     c->rx_begin.ensure((size_t)(c->dp.n_rx + 2) * 4);
-    c->ctx_flags.ensure(((size_t)G / 4 + 2) * 4);
-    CK(cudaMemsetAsync(c->ctx_flags.p, 0, ((size_t)G / 4 + 2) * 4, st));
+    if (!c->plan.ctx_in_groups) CK(cudaMemsetAsync(c->ctx_flags.p, 0, ((size_t)G / 4 + 2) * 4, st));
     if (n_recs) {
         const int kb = 32 + bits_for(c->dp.n_rx);
         sort_keys<unsigned long long>(c, c->recs.as<unsigned long long>(), c->recs_alt.as<unsigned long long>(), n_recs, kb);
@@ -1043,8 +1286,11 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         CK(cudaStreamSynchronize(st));
     }
     k_rx_bounds<<<blocks_for(c->dp.n_rx + 1, 128), 128, 0, st>>>(c->recs.as<unsigned long long>(), n_unique, c->dp.n_rx, c->rx_begin.as<uint32_t>());
-    k_ctx_flags<<<c->n_sm * 4, 256, 0, st>>>(c->recs.as<unsigned long long>(), c->rx_begin.as<uint32_t>(), c->ctx_flags.as<uint32_t>());
-    c->launches += 2;
+    c->launches += 1;
+    if (!c->plan.ctx_in_groups) {
+        k_ctx_flags<<<c->n_sm * 4, 256, 0, st>>>(c->recs.as<unsigned long long>(), c->rx_begin.as<uint32_t>(), c->ctx_flags.as<uint32_t>());
+        c->launches += 1;
+    }
 
     // ---- events in discovery order (global line, pattern index)
     uint32_t m = 0;
@@ -1065,6 +1311,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     c->pend.d_text = d_text; c->pend.len = len; c->pend.n_logs = n_logs; c->pend.G = G;
     c->pend.n_unique = n_unique; c->pend.m = m; c->pend.options = options;
     c->tm.scan_bytes = len + 4ull * ((uint64_t)G + 1) + 8ull * m;
+    c->tm.dfa_scan_bytes = c->d_group_blob.empty() ? 0 : len + 8ull * ((uint64_t)G + 1) + (uint64_t)G;   // text + line offsets in, flag byte out
 }
 
 void per_pattern_counts(lp_ctx* c, uint64_t* counts_out) {
@@ -1187,6 +1434,7 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count) {
     cudaEventElapsedTime(&ms, c->ev[1], c->ev[2]); c->tm.scan_ms = ms;
     cudaEventElapsedTime(&ms, c->ev[2], c->ev[3]); c->tm.verify_ms = ms;
     cudaEventElapsedTime(&ms, c->ev[3], c->ev[4]); c->tm.score_ms = ms;
+    cudaEventElapsedTime(&ms, c->ev[6], c->ev[7]); c->tm.dfa_scan_ms = ms;
     c->tm.kernel_launches = c->launches;
     c->pend.valid = false;
     return res.release();
@@ -1260,6 +1508,10 @@ lp_ctx* lp_create(const lp_scoring_cfg* cfg, int device) {
         CK(cudaGetDeviceProperties(&prop, device));
         ctx->n_sm = prop.multiProcessorCount;
         CK(cudaFuncSetAttribute(k_lines_filter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(GRAM_WORDS * 4)));
+        CK(cudaFuncSetAttribute(k_dfa_scan<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+        CK(cudaFuncSetAttribute(k_dfa_scan<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+        CK(cudaFuncSetAttribute(k_dfa_scan<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
+        CK(cudaFuncSetAttribute(k_dfa_scan<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
         std::vector<double> lut((size_t)cfg->max_window + 1);
         for (int d = 0; d <= cfg->max_window; ++d)
             lut[d] = cfg->decay_lut ? cfg->decay_lut[d] : std::exp(-(double)d / cfg->decay_constant);   // SS:177
@@ -1283,11 +1535,39 @@ void lp_destroy(lp_ctx* c) {
                      &c->cand, &c->tasks, &c->vm_tasks, &c->vm_stack, &c->recs, &c->recs_alt, &c->cub_tmp, &c->rx_begin, &c->ctx_flags, &c->ev_key, &c->ev_key_alt,
                      &c->ev_log, &c->slot_key, &c->slot_key_alt, &c->ev_idx, &c->ev_idx_alt, &c->rank_in_slot, &c->freq_delta, &c->prior,
                      &c->out_line, &c->out_pat, &c->out_score, &c->out_factors, &c->sort_key, &c->sort_key_alt, &c->order, &c->order_alt,
-                     &c->log_sorted, &c->log_sorted_alt, &c->rank, &c->log_event_begin, &c->n_unique, &c->d_lut};
+                     &c->log_sorted, &c->log_sorted_alt, &c->rank, &c->log_event_begin, &c->n_unique, &c->d_lut,
+                     &c->f_bitmap, &c->f_key, &c->f_begin, &c->f_count, &c->f_lits, &c->f_goff};
     for (DevBuf* b : all) b->release();
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
+}
+
+static std::vector<lpx::PlanPatternIn> to_plan_input(const lp_pattern_desc* pats, size_t n, int64_t* bad_pattern) {
+    std::vector<lpx::PlanPatternIn> in(n);
+    for (size_t i = 0; i < n; ++i) {
+        const lp_pattern_desc& d = pats[i];
+        if (!d.primary_regex) { if (bad_pattern) *bad_pattern = (int64_t)i; throw std::invalid_argument("primary_regex is NULL"); }
+        in[i].has_id = d.id != nullptr;
+        if (d.id) in[i].id = d.id;
+        in[i].primary = d.primary_regex;
+        in[i].confidence = d.confidence; in[i].severity = d.severity_multiplier;
+        in[i].has_context = d.has_context; in[i].before = d.lines_before; in[i].after = d.lines_after;
+        for (uint32_t s = 0; s < d.n_secondaries; ++s) {
+            if (!d.secondaries[s].regex) { if (bad_pattern) *bad_pattern = (int64_t)i; throw std::invalid_argument("secondary regex is NULL"); }
+            in[i].secs.push_back({d.secondaries[s].regex, d.secondaries[s].weight, d.secondaries[s].proximity_window});
+        }
+        for (uint32_t s = 0; s < d.n_sequences; ++s) {
+            lpx::PlanPatternIn::Seq q;
+            q.bonus = d.sequences[s].bonus_multiplier;
+            for (uint32_t e = 0; e < d.sequences[s].n_events; ++e) {
+                if (!d.sequences[s].event_regex[e]) { if (bad_pattern) *bad_pattern = (int64_t)i; throw std::invalid_argument("sequence event regex is NULL"); }
+                q.events.push_back(d.sequences[s].event_regex[e]);
+            }
+            in[i].seqs.push_back(std::move(q));
+        }
+    }
+    return in;
 }
 
 int lp_load_patterns(lp_ctx* c, const lp_pattern_desc* pats, size_t n, int64_t* bad_pattern) {
@@ -1296,34 +1576,48 @@ int lp_load_patterns(lp_ctx* c, const lp_pattern_desc* pats, size_t n, int64_t* 
     return guarded(c, [&] {
         if (n && !pats) throw std::invalid_argument("patterns is NULL");
         std::lock_guard<std::mutex> lk(c->mu);
-        std::vector<lpx::PlanPatternIn> in(n);
-        for (size_t i = 0; i < n; ++i) {
-            const lp_pattern_desc& d = pats[i];
-            if (!d.primary_regex) { if (bad_pattern) *bad_pattern = (int64_t)i; throw std::invalid_argument("primary_regex is NULL"); }
-            in[i].has_id = d.id != nullptr;
-            if (d.id) in[i].id = d.id;
-            in[i].primary = d.primary_regex;
-            in[i].confidence = d.confidence; in[i].severity = d.severity_multiplier;
-            in[i].has_context = d.has_context; in[i].before = d.lines_before; in[i].after = d.lines_after;
-            for (uint32_t s = 0; s < d.n_secondaries; ++s) {
-                if (!d.secondaries[s].regex) { if (bad_pattern) *bad_pattern = (int64_t)i; throw std::invalid_argument("secondary regex is NULL"); }
-                in[i].secs.push_back({d.secondaries[s].regex, d.secondaries[s].weight, d.secondaries[s].proximity_window});
-            }
-            for (uint32_t s = 0; s < d.n_sequences; ++s) {
-                lpx::PlanPatternIn::Seq q;
-                q.bonus = d.sequences[s].bonus_multiplier;
-                for (uint32_t e = 0; e < d.sequences[s].n_events; ++e) {
-                    if (!d.sequences[s].event_regex[e]) { if (bad_pattern) *bad_pattern = (int64_t)i; throw std::invalid_argument("sequence event regex is NULL"); }
-                    q.events.push_back(d.sequences[s].event_regex[e]);
-                }
-                in[i].seqs.push_back(std::move(q));
-            }
-        }
+        std::vector<lpx::PlanPatternIn> in = to_plan_input(pats, n, bad_pattern);
         c->loaded = false;
+        c->calibrated = false;
+        c->recalibrations = 0;
         lpx::build_plan(in, c->plan, bad_pattern);
         upload_plan(c);
         c->loaded = true;
     });
+}
+
+// CPU-only introspection of the plan lp_load_patterns would build (tests / tuning; no GPU needed):
+// one text line per literal: "<gram hex>\t<icase>\t<literal>", then "#..." summary lines.
+size_t lp_debug_plan_dump(const lp_pattern_desc* pats, size_t n, const uint8_t* sample, size_t sample_len, char* buf, size_t cap) {
+    std::string out;
+    try {
+        lpx::Plan pl;
+        std::vector<lpx::PlanPatternIn> in = to_plan_input(pats, n, nullptr);
+        lpx::build_plan(in, pl, nullptr);
+        if (sample && sample_len) lpx::select_grams(pl, sample, sample_len);
+        for (size_t l = 0; l < pl.lit_off.size(); ++l) {
+            char g[16];
+            const uint8_t* b = &pl.lit_bytes[pl.lit_off[l] + pl.lit_gram_off[l]];
+            snprintf(g, sizeof g, "%02x%02x%02x%02x", b[0], b[1], b[2], b[3]);
+            out += g; out += "\t"; out += pl.lit_icase[l] ? "1" : "0"; out += "\t";
+            out.append(reinterpret_cast<const char*>(&pl.lit_bytes[pl.lit_off[l]]), pl.lit_len[l]);
+            out += "\n";
+        }
+        out += "#regexes " + std::to_string(pl.n_rx) + " vm " + std::to_string(pl.n_vm) + " literals " + std::to_string(pl.lit_off.size()) +
+               " groups " + std::to_string(pl.groups.size()) + " always_dfa " + std::to_string(pl.always_list.size()) +
+               " always_vm " + std::to_string(pl.always_vm_list.size()) + "\n";
+        for (const auto& g : pl.groups) {
+            out += "#group states " + std::to_string(g.blob[0]) + " classes " + std::to_string(g.blob[1]) + " bytes " + std::to_string(g.blob.size() * 4) + " rx";
+            for (uint32_t r : g.rx) out += " [" + pl.rx_src[r] + "]";
+            out += "\n";
+        }
+        for (uint32_t r : pl.always_list) out += "#always_dfa [" + pl.rx_src[r] + "]\n";
+        for (uint32_t r : pl.always_vm_list) out += "#always_vm [" + pl.rx_src[r] + "]\n";
+    } catch (const std::exception& e) {
+        out = std::string("!error ") + e.what() + "\n";
+    }
+    if (buf && cap) { size_t k = std::min(cap - 1, out.size()); memcpy(buf, out.data(), k); buf[k] = 0; }
+    return out.size();
 }
 
 int lp_batch_scan_device(lp_ctx* c, const uint8_t* d_logs, const uint64_t* offsets, size_t n_logs, int options, uint64_t* counts_out) {

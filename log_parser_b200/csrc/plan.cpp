@@ -21,6 +21,17 @@ int rarity(uint8_t b) {
     return 4;
 }
 
+// every alternative starts with \A / non-MULTILINE ^: its automaton dies within a few bytes on most lines
+bool begins_anchored(const Ast& a) {
+    switch (a.kind) {
+        case AstKind::Assert: return a.assert_kind == AssertKind::Begin;
+        case AstKind::Group: return begins_anchored(*a.kids[0]);
+        case AstKind::Cat: return !a.kids.empty() && begins_anchored(*a.kids[0]);
+        case AstKind::Alt: { for (const auto& k : a.kids) if (!begins_anchored(*k)) return false; return !a.kids.empty(); }
+        default: return false;
+    }
+}
+
 bool blank(const std::string& s) {
     for (unsigned char c : s) if (c > ' ') return false;
     return true;
@@ -28,12 +39,89 @@ bool blank(const std::string& s) {
 
 }  // namespace
 
+void select_grams(Plan& pl, const uint8_t* sample, size_t sample_len);
+
+void serialise_group(const std::vector<uint32_t>& rx, const MultiDfa& d, std::vector<uint32_t>& blob) {
+    const uint32_t ns = d.n_states(), nc = d.n_classes, nbyte = nc - 2;
+    std::vector<uint32_t> perm(ns), inv(ns);      // non-final states first
+    uint32_t w = 0;
+    for (uint32_t s2 = 0; s2 < ns; ++s2) if (!d.state_final[s2]) { perm[s2] = w; inv[w++] = s2; }
+    const uint32_t first_final = w;
+    for (uint32_t s2 = 0; s2 < ns; ++s2) if (d.state_final[s2]) { perm[s2] = w; inv[w++] = s2; }
+    auto step = [&](uint32_t st, uint8_t byte) { return (uint32_t)d.trans[st * nc + d.classmap[byte]]; };
+    // Quiescent pair: the state the automaton idles in after a boring non-word byte (qa) and
+    // after a boring word byte (qb). On "boring" byte classes both idle states move to qa/qb
+    // by word-ness alone, so the walker needs no table lookup for them.
+    uint32_t qa = 0xFFFFFFFFu, qb = 0xFFFFFFFFu;
+    std::vector<int> boring(nbyte, 0);      // 0 interesting, 1 boring non-word, 2 boring word
+    {
+        uint32_t a0 = d.start;
+        for (int it = 0; it < 4; ++it) a0 = step(a0, 0x01);
+        if (step(a0, 0x01) == a0 && !d.state_final[a0]) {
+            for (const char* wb = "zqjxkvy_0"; *wb; ++wb) {
+                uint32_t b0 = step(a0, (uint8_t)*wb);
+                if (step(b0, (uint8_t)*wb) == b0 && step(b0, 0x01) == a0 && !d.state_final[b0]) { qa = a0; qb = b0; break; }
+            }
+        }
+        if (qa != 0xFFFFFFFFu) {
+            for (uint32_t c = 0; c < nbyte; ++c) {
+                const uint32_t ta = d.trans[qa * nc + c], tb = d.trans[qb * nc + c];
+                if (ta == tb && ta == qa) boring[c] = 1;
+                else if (ta == tb && ta == qb) boring[c] = 2;
+            }
+        }
+    }
+    // classes renumbered: boring non-word, boring word, the rest
+    std::vector<uint32_t> cperm(nc);
+    uint32_t cw = 0;
+    for (uint32_t c = 0; c < nbyte; ++c) if (boring[c] == 1) cperm[c] = cw++;
+    const uint32_t nb0 = cw;
+    for (uint32_t c = 0; c < nbyte; ++c) if (boring[c] == 2) cperm[c] = cw++;
+    const uint32_t nb1 = cw;
+    for (uint32_t c = 0; c < nbyte; ++c) if (boring[c] == 0) cperm[c] = cw++;
+    cperm[nbyte] = nbyte; cperm[nbyte + 1] = nbyte + 1;
+    blob.assign(5 + 32 + 64 + ns + (ns * nc + 1) / 2, 0);
+    blob[0] = ns; blob[1] = nc; blob[2] = perm[d.start]; blob[3] = first_final; blob[4] = (uint32_t)rx.size();
+    for (size_t k = 0; k < rx.size(); ++k) blob[5 + k] = rx[k];
+    blob[33] = qa == 0xFFFFFFFFu ? 0xFFFFFFFFu : perm[qa];
+    blob[34] = qb == 0xFFFFFFFFu ? 0xFFFFFFFFu : perm[qb];
+    blob[35] = nb0; blob[36] = nb1;
+    uint8_t* cmo = reinterpret_cast<uint8_t*>(&blob[37]);
+    for (int b2 = 0; b2 < 256; ++b2) cmo[b2] = (uint8_t)cperm[d.classmap[b2]];
+    for (uint32_t s2 = 0; s2 < ns; ++s2) blob[101 + s2] = d.state_mask[inv[s2]];
+    uint16_t* t = reinterpret_cast<uint16_t*>(&blob[101 + ns]);
+    for (uint32_t s2 = 0; s2 < ns; ++s2)
+        for (uint32_t x = 0; x < nc; ++x) t[s2 * nc + cperm[x]] = (uint16_t)perm[d.trans[inv[s2] * nc + x]];
+}
+
+// Host mirror of the device walker in k_dfa_scan (same blob, same fast path); CPU-only tests use it.
+uint32_t run_group_blob(const std::vector<uint32_t>& blob, const uint8_t* s, size_t n) {
+    const uint32_t ns = blob[0], nc = blob[1], ff = blob[3], qa = blob[33], qb = blob[34], nb0 = blob[35], nb1 = blob[36];
+    const uint8_t* cm = reinterpret_cast<const uint8_t*>(&blob[37]);
+    const uint32_t* smask = &blob[101];
+    const uint16_t* T = reinterpret_cast<const uint16_t*>(&blob[101 + ns]);
+    long tpos = -1;
+    if (n >= 1 && s[n - 1] == '\r') tpos = (long)n - 1;
+    else if (n >= 2 && s[n - 2] == 0xC2 && s[n - 1] == 0x85) tpos = (long)n - 2;
+    else if (n >= 3 && s[n - 3] == 0xE2 && s[n - 2] == 0x80 && (s[n - 1] == 0xA8 || s[n - 1] == 0xA9)) tpos = (long)n - 3;
+    uint32_t st = blob[2];
+    for (size_t i = 0; i < n && st < ff; ++i) {
+        if ((long)i == tpos) st = T[st * nc + nc - 2];
+        if (st >= ff) break;
+        const uint32_t cls = cm[s[i]];
+        if ((st == qa || st == qb) && cls < nb1) st = cls < nb0 ? qa : qb;
+        else st = T[st * nc + cls];
+    }
+    return smask[T[st * nc + nc - 1]];
+}
+
 void build_plan(const std::vector<PlanPatternIn>& pats, Plan& pl, int64_t* bad) {
     pl = Plan();
     if (bad) *bad = -1;
     std::map<std::pair<std::string, int>, uint32_t> ids;
     std::vector<int> rx_flags;
     std::vector<std::vector<Literal>> rx_lits;
+    std::vector<ParsedRegex> parsed;
 
     auto add_regex = [&](const std::string& src, int flags) -> uint32_t {
         auto key = std::make_pair(src, flags);
@@ -72,8 +160,12 @@ void build_plan(const std::vector<PlanPatternIn>& pats, Plan& pl, int64_t* bad) 
             ++pl.n_vm;
         }
         std::vector<Literal> lits = required_literals(*pr.root, 4);
+        // the four context regexes hit a large share of all lines: cheaper in the always-on scan
+        // than as ~1 candidate per line in the literal prefilter
+        if (id < RX_FIRST_USER && is_dfa) lits.clear();
         pl.rx_always.push_back(lits.empty() ? 1 : 0);
         rx_lits.push_back(std::move(lits));
+        parsed.push_back(std::move(pr));
         return id;
     };
 
@@ -130,8 +222,61 @@ void build_plan(const std::vector<PlanPatternIn>& pats, Plan& pl, int64_t* bad) 
         pl.max_fanout = std::max<uint32_t>(pl.max_fanout, (uint32_t)by_primary[r].size());
         for (uint32_t p : by_primary[r]) pl.rxp_pat.push_back(p);
     }
+    // ---- scan groups: greedily pack always-on DFA regexes into product automata that fit shared memory
+    pl.rx_in_group.assign(pl.n_rx, 0);
+    pl.rx_record.assign(pl.n_rx, 0);
+    for (uint32_t r = RX_FIRST_USER; r < pl.n_rx; ++r) pl.rx_record[r] = 1;
+    for (uint32_t r : pl.pat_primary) pl.rx_record[r] = 1;
+    for (uint32_t r : pl.sec_rx) pl.rx_record[r] = 1;
+    for (uint32_t r : pl.ev_rx) pl.rx_record[r] = 1;
+    {
+        constexpr size_t GROUP_BYTES = 40 * 1024, TOTAL_BYTES = 100 * 1024;
+        std::vector<uint32_t> cand;
+        for (uint32_t r = 0; r < pl.n_rx; ++r)
+            if (pl.rx_always[r] && pl.rx_kind[r] == RXK_DFA) cand.push_back(r);
+        // unanchored automata first, begin-anchored ones last: groups made only of anchored patterns
+        // reach a final state early and stop costing table lookups
+        std::stable_sort(cand.begin(), cand.end(), [&](uint32_t x, uint32_t y) {
+            return (int)begins_anchored(*parsed[x].root) < (int)begins_anchored(*parsed[y].root);
+        });
+        auto serialise = [&](const std::vector<uint32_t>& rx, const MultiDfa& d, std::vector<uint32_t>& blob) { serialise_group(rx, d, blob); };
+        size_t total = 0;
+        std::vector<uint32_t> cur;
+        MultiDfa cur_dfa;
+        auto flush = [&]() {
+            if (cur.empty()) return;
+            Plan::ScanGroup g;
+            g.rx = cur;
+            serialise(cur, cur_dfa, g.blob);
+            total += g.blob.size() * 4;
+            for (uint32_t r : cur) pl.rx_in_group[r] = 1;
+            pl.groups.push_back(std::move(g));
+            cur.clear();
+        };
+        auto bytes_of = [](const MultiDfa& d) { return (size_t)(101 + d.n_states()) * 4 + (size_t)d.n_states() * d.n_classes * 2; };
+        for (uint32_t r : cand) {
+            std::vector<uint32_t> trial = cur;
+            trial.push_back(r);
+            std::vector<const Ast*> roots;
+            for (uint32_t q : trial) roots.push_back(parsed[q].root.get());
+            MultiDfa d;
+            if (trial.size() <= 28 && build_multi_dfa(roots, d, 4096) && bytes_of(d) <= GROUP_BYTES && total + bytes_of(d) <= TOTAL_BYTES) {
+                cur = trial; cur_dfa = d;
+                continue;
+            }
+            flush();
+            roots.assign(1, parsed[r].root.get());
+            MultiDfa single;
+            if (build_multi_dfa(roots, single, 4096) && bytes_of(single) <= GROUP_BYTES && total + bytes_of(single) <= TOTAL_BYTES) {
+                cur.assign(1, r); cur_dfa = single;
+            }   // else: stays on the global-table path (k_verify_always)
+        }
+        flush();
+        pl.ctx_in_groups = pl.rx_in_group[RX_ERR] && pl.rx_in_group[RX_WARN] && pl.rx_in_group[RX_STACK] && pl.rx_in_group[RX_EXC];
+        if (!pl.ctx_in_groups) for (uint32_t r = 0; r < RX_FIRST_USER; ++r) pl.rx_record[r] = 1;   // flags come from records
+    }
     for (uint32_t r = 0; r < pl.n_rx; ++r)
-        if (pl.rx_always[r]) (pl.rx_kind[r] == RXK_DFA ? pl.always_list : pl.always_vm_list).push_back(r);
+        if (pl.rx_always[r] && !pl.rx_in_group[r]) (pl.rx_kind[r] == RXK_DFA ? pl.always_list : pl.always_vm_list).push_back(r);
 
     // ---- literal table: de-duplicate (bytes, icase) across regexes
     std::map<std::pair<std::string, bool>, uint32_t> lit_ids;
@@ -148,16 +293,7 @@ void build_plan(const std::vector<PlanPatternIn>& pats, Plan& pl, int64_t* bad) 
                 pl.lit_icase.push_back(l.icase ? 1 : 0);
                 pl.lit_bytes.insert(pl.lit_bytes.end(), l.bytes.begin(), l.bytes.end());
                 lit_rx.emplace_back();
-                // choose the rarest 4-byte window of the literal as its filter gram
-                int best = -1; uint32_t best_off = 0;
-                for (uint32_t o = 0; o + 4 <= l.bytes.size(); ++o) {
-                    int sc = 0;
-                    for (int k = 0; k < 4; ++k) sc += rarity((uint8_t)l.bytes[o + k]);
-                    bool distinct = l.bytes[o] != l.bytes[o + 1] && l.bytes[o + 1] != l.bytes[o + 2] && l.bytes[o + 2] != l.bytes[o + 3];
-                    sc = sc * 2 + (distinct ? 1 : 0);
-                    if (sc > best) { best = sc; best_off = o; }
-                }
-                pl.lit_gram_off.push_back(best_off);
+                pl.lit_gram_off.push_back(0);
             }
             auto& v = lit_rx[it->second];
             if (std::find(v.begin(), v.end(), r) == v.end()) v.push_back(r);
@@ -168,17 +304,64 @@ void build_plan(const std::vector<PlanPatternIn>& pats, Plan& pl, int64_t* bad) 
         pl.lit_rx.insert(pl.lit_rx.end(), v.begin(), v.end());
         pl.lit_rx_begin.push_back((uint32_t)pl.lit_rx.size());
     }
+    select_grams(pl, nullptr, 0);
+}
 
-    // ---- gram bitmap + exact gram table
+// (Re)chooses one filter gram per literal and rebuilds the Bloom bitmap and the exact gram table.
+// Without a sample, the window that the fewest literals of the set share wins (a window common to
+// many patterns, like the tail of "...Exception", is also frequent in the logs they are written
+// for). With a sample of real log text, the window seen least often in the sample wins. The choice
+// only changes how many candidates the prefilter emits, never the results.
+void select_grams(Plan& pl, const uint8_t* sample, size_t sample_len) {
+    auto folded_at = [&](uint32_t l, uint32_t o) {
+        const uint8_t* b = &pl.lit_bytes[pl.lit_off[l] + o];
+        return gram_fold((uint32_t)b[0] | ((uint32_t)b[1] << 8) | ((uint32_t)b[2] << 16) | ((uint32_t)b[3] << 24));
+    };
+    const size_t n_lit = pl.lit_off.size();
+    constexpr uint32_t CB = 22;
+    std::vector<uint32_t> seen_cnt;
+    if (sample && sample_len >= 4) {
+        seen_cnt.assign(1u << CB, 0);
+        uint32_t w = (uint32_t)sample[0] | ((uint32_t)sample[1] << 8) | ((uint32_t)sample[2] << 16);
+        for (size_t i = 3; i < sample_len; ++i) {
+            w = (w & 0x00FFFFFFu) | ((uint32_t)sample[i] << 24);
+            ++seen_cnt[(gram_fold(w) * GRAM_MUL) >> (32 - CB)];
+            w >>= 8;
+        }
+    }
+    std::map<uint32_t, uint32_t> df;
+    for (uint32_t l = 0; l < n_lit; ++l) {
+        std::vector<uint32_t> seen;
+        for (uint32_t o = 0; o + 4 <= pl.lit_len[l]; ++o) {
+            uint32_t f = folded_at(l, o);
+            if (std::find(seen.begin(), seen.end(), f) == seen.end()) { seen.push_back(f); ++df[f]; }
+        }
+    }
+    for (uint32_t l = 0; l < n_lit; ++l) {
+        double best = -1e300; uint32_t best_off = 0;
+        for (uint32_t o = 0; o + 4 <= pl.lit_len[l]; ++o) {
+            const uint8_t* b = &pl.lit_bytes[pl.lit_off[l] + o];
+            int rare = 0;
+            for (int k = 0; k < 4; ++k) rare += rarity(b[k]);
+            const bool distinct = b[0] != b[1] && b[1] != b[2] && b[2] != b[3];
+            const uint32_t f = folded_at(l, o);
+            double sc = rare * 2 + (distinct ? 1 : 0);
+            if (!seen_cnt.empty()) sc -= 1000.0 * seen_cnt[(f * GRAM_MUL) >> (32 - CB)];
+            else sc -= 6.0 * (df[f] - 1);
+            if (sc > best) { best = sc; best_off = o; }
+        }
+        pl.lit_gram_off[l] = best_off;
+    }
     pl.bitmap.assign((1u << GRAM_BITS) / 32, 0);
+    pl.gram_lits.clear();
     std::map<uint32_t, std::vector<uint32_t>> gram2lits;
-    for (uint32_t l = 0; l < pl.lit_off.size(); ++l) {
-        const uint8_t* b = &pl.lit_bytes[pl.lit_off[l] + pl.lit_gram_off[l]];
-        uint32_t w = (uint32_t)b[0] | ((uint32_t)b[1] << 8) | ((uint32_t)b[2] << 16) | ((uint32_t)b[3] << 24);
-        uint32_t f = gram_fold(w);
+    for (uint32_t l = 0; l < n_lit; ++l) {
+        const uint32_t f = folded_at(l, pl.lit_gram_off[l]);
         gram2lits[f].push_back(l);
-        uint32_t h = gram_hash1(f);
+        const uint32_t h = gram_hash1(f);
         pl.bitmap[h >> 5] |= 1u << (h & 31);
+        const uint32_t h2 = (f * GRAM_MUL2) >> (32 - GRAM_BITS);       // second Bloom probe
+        pl.bitmap[h2 >> 5] |= 1u << (h2 & 31);
     }
     uint32_t bits = 4;
     while ((1u << bits) < gram2lits.size() * 2 + 1) ++bits;

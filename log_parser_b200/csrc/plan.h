@@ -48,6 +48,17 @@ struct Plan {
     std::vector<VmInsn> vm_code;
     std::vector<uint32_t> vm_set_off, vm_set_ranges;
 
+    // ---- always-on scan groups: product DFAs walked over every line from shared memory
+    // (context regexes ERR/WARN/EXC/STACK + every DFA regex without a usable literal)
+    struct ScanGroup {
+        std::vector<uint32_t> rx;        // regex ids, bit k of the group's mask <-> rx[k]
+        std::vector<uint32_t> blob;      // serialised tables (see k_dfa_scan)
+    };
+    std::vector<ScanGroup> groups;
+    std::vector<uint8_t> rx_in_group;    // 1: decided by a scan group
+    std::vector<uint8_t> rx_record;      // 1: matches must be recorded as (regex,line) (0: context flag only)
+    bool ctx_in_groups = false;          // all four context regexes are decided by scan groups
+
     // ---- literals and the gram filter
     std::vector<uint8_t> lit_bytes;
     std::vector<uint32_t> lit_off, lit_len, lit_gram_off;
@@ -76,6 +87,10 @@ struct Plan {
 
 // Throws RegexSyntaxError / RegexUnsupported; *bad receives the flat pattern index.
 void build_plan(const std::vector<PlanPatternIn>& pats, Plan& out, int64_t* bad);
+void serialise_group(const std::vector<uint32_t>& rx, const MultiDfa& d, std::vector<uint32_t>& blob);
+uint32_t run_group_blob(const std::vector<uint32_t>& blob, const uint8_t* s, size_t n);
+// Re-picks the filter grams (optionally against a sample of real log text) and rebuilds the filter tables.
+void select_grams(Plan& pl, const uint8_t* sample, size_t sample_len);
 
 inline uint32_t gram_fold(uint32_t w) { return w | 0x20202020u; }
 inline uint32_t gram_hash1(uint32_t folded) { return (folded * GRAM_MUL) >> (32 - GRAM_BITS); }

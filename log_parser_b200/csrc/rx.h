@@ -92,6 +92,21 @@ struct DfaLimits { uint32_t max_raw_states = 30000; uint32_t max_states = 8192; 
 // Returns false (and leaves `out` empty) if the pattern exceeds the limits.
 bool build_dfa(const Ast& root, Dfa& out, const DfaLimits& lim = DfaLimits());
 
+// Product automaton of several regexes for the always-on scan (patterns without a usable literal):
+// one walk of a line decides all of them. A state carries the set of regexes already matched
+// (sticky); state_mask[trans[s][SYM_EOT]] is the line's result. Symbols as in Dfa.
+struct MultiDfa {
+    uint16_t n_classes = 0;
+    uint16_t start = 0;
+    uint8_t classmap[256];
+    std::vector<uint16_t> trans;        // n_states * n_classes
+    std::vector<uint32_t> state_mask;   // bit k: regex k of the group has matched
+    std::vector<uint8_t> state_final;   // 1: no transition can change the state any more
+    uint32_t n_states() const { return n_classes ? (uint32_t)(trans.size() / n_classes) : 0; }
+    uint32_t run(const uint8_t* s, size_t n) const;   // host-side walk identical to the device's
+};
+bool build_multi_dfa(const std::vector<const Ast*>& roots, MultiDfa& out, uint32_t max_states, uint32_t max_nfa = 60000);
+
 // ---------------------------------------------------------------- required literals
 struct Literal {
     std::string bytes;  // UTF-8; if icase: ASCII letters are stored lower-case

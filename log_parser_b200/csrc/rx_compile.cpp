@@ -370,6 +370,186 @@ bool build_dfa(const Ast& root, Dfa& out, const DfaLimits& lim) {
     return true;
 }
 
+bool build_multi_dfa(const std::vector<const Ast*>& roots, MultiDfa& out, uint32_t max_states, uint32_t max_nfa) {
+    out = MultiDfa();
+    const int K = (int)roots.size();
+    if (K == 0 || K > 32) return false;
+    Nfa nfa(max_nfa);
+    std::vector<int> starts(K), accepts(K), owner;
+    try {
+        Builder b(nfa);
+        for (int k = 0; k < K; ++k) {
+            const size_t first = nfa.st.size();
+            starts[k] = nfa.add();
+            nfa.st[starts[k]].edges.push_back({0x00, 0xFF, starts[k]});
+            Frag f = b.build(*roots[k]);
+            nfa.st[starts[k]].eps.push_back(f.in);
+            accepts[k] = f.out;
+            owner.resize(nfa.st.size(), k);
+            (void)first;
+        }
+    } catch (const std::length_error&) {
+        return false;
+    }
+    std::vector<int> accept_of(nfa.st.size(), -1);
+    for (int k = 0; k < K; ++k) accept_of[accepts[k]] = k;
+
+    bool cut[257];
+    memset(cut, 0, sizeof cut);
+    cut[0] = cut[256] = true;
+    for (const auto& s : nfa.st)
+        for (const auto& e : s.edges) { cut[e.lo] = true; cut[(int)e.hi + 1] = true; }
+    for (int b = 1; b < 256; ++b)
+        if (word_byte(b) != word_byte(b - 1)) cut[b] = true;
+    std::vector<int> rep;
+    uint8_t cls_of[256];
+    for (int b = 0; b < 256; ++b) {
+        if (cut[b]) rep.push_back(b);
+        cls_of[b] = (uint8_t)(rep.size() - 1);
+    }
+    const int nb = (int)rep.size();
+    const int SYM_TPOS = nb, SYM_EOT = nb + 1, nsym = nb + 2;
+
+    Subset sub(nfa);
+    struct Key {
+        std::vector<int> k; int ctx; uint32_t mask;
+        bool operator<(const Key& o) const { return mask != o.mask ? mask < o.mask : ctx != o.ctx ? ctx < o.ctx : k < o.k; }
+    };
+    std::map<Key, int> ids;
+    struct St { std::vector<int> k; Ctx c; uint32_t mask; };
+    std::vector<St> states;
+    std::vector<std::vector<int>> trans;
+    auto intern = [&](std::vector<int> k, Ctx c, uint32_t mask) -> int {
+        std::sort(k.begin(), k.end());
+        k.erase(std::unique(k.begin(), k.end()), k.end());
+        if (!nfa.uses_eol) c.at_tpos = false;
+        if (k.empty()) c = Ctx();
+        Key key{k, c.bits(), mask};
+        auto it = ids.find(key);
+        if (it != ids.end()) return it->second;
+        int id = (int)states.size();
+        ids.emplace(std::move(key), id);
+        states.push_back(St{std::move(k), c, mask});
+        trans.emplace_back(nsym, 0);
+        return id;
+    };
+    Ctx c0;
+    c0.at_begin = true;
+    intern(std::vector<int>(starts.begin(), starts.end()), c0, 0);
+    std::vector<int> clo, nxt;
+    auto settle = [&](uint32_t mask, const std::vector<int>& closure_set, uint32_t& newmask) {
+        newmask = mask;
+        for (int s : closure_set) if (accept_of[s] >= 0) newmask |= 1u << accept_of[s];
+    };
+    for (size_t si = 0; si < states.size(); ++si) {
+        if (states.size() > max_states * 8u + 64u) return false;
+        const std::vector<int> kernel = states[si].k;
+        const Ctx c = states[si].c;
+        const uint32_t mask = states[si].mask;
+        for (int cl = 0; cl < nb; ++cl) {
+            const int b = rep[cl];
+            sub.closure(kernel, c, false, word_byte(b), clo);
+            uint32_t nm;
+            settle(mask, clo, nm);
+            nxt.clear();
+            for (int s : clo) {
+                if ((nm >> owner[s]) & 1u) continue;      // that regex is decided: drop its threads
+                for (const auto& e : nfa.st[s].edges)
+                    if (b >= e.lo && b <= e.hi) nxt.push_back(e.to);
+            }
+            Ctx c2;
+            c2.prev_word = word_byte(b);
+            trans[si][cl] = intern(nxt, c2, nm);
+        }
+        {
+            sub.closure(kernel, c, true, false, clo);
+            uint32_t nm;
+            settle(mask, clo, nm);
+            trans[si][SYM_EOT] = intern({}, Ctx(), nm);
+        }
+        if (nfa.uses_eol && !c.at_tpos && !kernel.empty()) { Ctx c2 = c; c2.at_tpos = true; trans[si][SYM_TPOS] = intern(kernel, c2, mask); }
+        else trans[si][SYM_TPOS] = (int)si;
+    }
+    const int ns = (int)states.size();
+    // Moore minimisation; the observable of a state is its mask
+    std::vector<int> part(ns);
+    {
+        std::map<uint32_t, int> m2b;
+        for (int s = 0; s < ns; ++s) {
+            auto it = m2b.find(states[s].mask);
+            if (it == m2b.end()) it = m2b.emplace(states[s].mask, (int)m2b.size()).first;
+            part[s] = it->second;
+        }
+    }
+    int nblocks = 0;
+    for (int s = 0; s < ns; ++s) nblocks = std::max(nblocks, part[s] + 1);
+    for (;;) {
+        std::map<std::vector<int>, int> sig2b;
+        std::vector<int> np(ns);
+        for (int s = 0; s < ns; ++s) {
+            std::vector<int> sig;
+            sig.reserve(nsym + 1);
+            sig.push_back(part[s]);
+            for (int x = 0; x < nsym; ++x) sig.push_back(part[trans[s][x]]);
+            auto it = sig2b.find(sig);
+            if (it == sig2b.end()) it = sig2b.emplace(std::move(sig), (int)sig2b.size()).first;
+            np[s] = it->second;
+        }
+        const int nb2 = (int)sig2b.size();
+        part.swap(np);
+        if (nb2 == nblocks) break;
+        nblocks = nb2;
+    }
+    if ((uint32_t)nblocks > max_states || nblocks > 65535) return false;
+    std::vector<std::vector<int>> bt(nblocks, std::vector<int>(nsym, 0));
+    out.state_mask.assign(nblocks, 0);
+    for (int s = 0; s < ns; ++s) {
+        out.state_mask[part[s]] = states[s].mask;
+        for (int x = 0; x < nsym; ++x) bt[part[s]][x] = part[trans[s][x]];
+    }
+    std::map<std::vector<int>, int> col2c;
+    std::vector<int> cmap(nb);
+    for (int cl = 0; cl < nb; ++cl) {
+        std::vector<int> col(nblocks);
+        for (int b = 0; b < nblocks; ++b) col[b] = bt[b][cl];
+        auto it = col2c.find(col);
+        if (it == col2c.end()) it = col2c.emplace(std::move(col), (int)col2c.size()).first;
+        cmap[cl] = it->second;
+    }
+    const int nb2 = (int)col2c.size(), nsym2 = nb2 + 2;
+    out.n_classes = (uint16_t)nsym2;
+    for (int b = 0; b < 256; ++b) out.classmap[b] = (uint8_t)cmap[cls_of[b]];
+    out.trans.assign((size_t)nblocks * nsym2, 0);
+    out.state_final.assign(nblocks, 0);
+    for (int b = 0; b < nblocks; ++b) {
+        uint16_t* row = &out.trans[(size_t)b * nsym2];
+        for (int cl = 0; cl < nb; ++cl) row[cmap[cl]] = (uint16_t)bt[b][cl];
+        row[nb2] = (uint16_t)bt[b][SYM_TPOS];
+        row[nb2 + 1] = (uint16_t)bt[b][SYM_EOT];
+        bool fin = true;
+        for (int x = 0; x < nsym2 && fin; ++x) fin = row[x] == b;
+        out.state_final[b] = fin ? 1 : 0;
+    }
+    out.start = (uint16_t)part[0];
+    return true;
+}
+
+uint32_t MultiDfa::run(const uint8_t* s, size_t n) const {
+    if (!n_classes) return 0;
+    long tpos = -1;
+    if (n >= 1 && s[n - 1] == '\r') tpos = (long)n - 1;
+    else if (n >= 2 && s[n - 2] == 0xC2 && s[n - 1] == 0x85) tpos = (long)n - 2;
+    else if (n >= 3 && s[n - 3] == 0xE2 && s[n - 2] == 0x80 && (s[n - 1] == 0xA8 || s[n - 1] == 0xA9)) tpos = (long)n - 3;
+    const unsigned nc = n_classes;
+    unsigned st = start;
+    for (size_t i = 0; i < n && !state_final[st]; ++i) {
+        if ((long)i == tpos) st = trans[st * nc + nc - 2];
+        st = trans[st * nc + classmap[s[i]]];
+    }
+    st = trans[st * nc + nc - 1];
+    return state_mask[st];
+}
+
 // Same walk as the device verifier (kernels.cu: dfa_walk).
 bool Dfa::match(const uint8_t* s, size_t n) const {
     if (!n_classes) return false;

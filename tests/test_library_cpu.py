@@ -172,3 +172,37 @@ def test_required_literals_are_sound(lib, oracle):
             if lits:
                 tb = t.encode()
                 assert any((l.lower() in tb.lower()) if ic else (l in tb) for ic, l in lits), (p.primary_regex, t, lits)
+
+
+def test_scan_group_product_dfa_vs_oracle(lib, oracle):
+    """The always-on scan walks product automata of several regexes (k_dfa_scan). The serialised
+    tables, including the idle-state fast path, are checked here on the host against the oracle."""
+    import ctypes as C
+
+    lib.lp_debug_group_match.restype = C.c_uint32
+    lib.lp_debug_group_match.argtypes = [C.POINTER(C.c_char_p), C.POINTER(C.c_int), C.c_size_t, C.c_char_p, C.c_size_t]
+    groups = [
+        ([r"\b(ERROR|FATAL|CRITICAL|SEVERE)\b", r"\b(WARN|WARNING)\b", r"\b\w*Exception\b|\b\w*Error\b", r"\b\d{8,}ms\b"], [2, 2, 0, 0]),
+        ([r"\b[45]\d\d \d+ \d+\.\d{3}$", r"^\s*at\s+[\w\.\$]+\(.*\)\s*$"], [0, 0]),
+        ([r"^\s*at\s+[\w\.\$]+\(.*\)\s*$", r"^\s+\.\.\. \d+ more$", r"^$", r"x$"], [0, 0, 0, 0]),
+        ([r"a.*b", r"\Bc\B", r"[^a-z]+$"], [0, 0, 0]),
+    ]
+    rng = random.Random(21)
+    words = ["ERROR", "error", "Fatal", "WARN", "warning", "xERROR", "at", "\tat", "com.foo.Bar$1.run(Bar.java:12)",
+             "NullPointerException", "OutOfMemoryError", "Errors", "12345678ms", "123456789ms", "x1234567ms", "503 12 0.123",
+             "404 1 22.5", "... 12 more", "\t... 3 more", " ", "é", "\r", "abc", "a", "b", "c", "x", "ms", "_", "-"]
+    for regs, flags in groups:
+        arr = (C.c_char_p * len(regs))(*[r.encode() for r in regs])
+        fl = (C.c_int * len(regs))(*flags)
+        oracles = [oracle.Regex(r, f) for r, f in zip(regs, flags)]
+        for _ in range(250):     # the hook rebuilds the group for every call
+            t = " ".join(rng.choice(words) for _ in range(rng.randint(0, 6)))
+            if rng.random() < 0.2:
+                t = rng.choice(["\tat ", "   at ", "\t"]) + t
+            if rng.random() < 0.1:
+                t += rng.choice(["\r", " ", "\x85"])
+            tb = t.encode()
+            got = lib.lp_debug_group_match(arr, fl, len(regs), tb, len(tb))
+            assert got < 0xFFFFFFF0, (regs, t, hex(got))
+            exp = sum((1 << k) for k, o in enumerate(oracles) if o.find(t))
+            assert got == exp, (regs, t, bin(got), bin(exp))
