@@ -46,6 +46,11 @@ __device__ __forceinline__ uint4 load16(const uint8_t* __restrict__ text, uint64
         if (pos + i < len) w[i >> 2] |= (uint32_t)text[pos + i] << ((i & 3) * 8);
     return make_uint4(w[0], w[1], w[2], w[3]);
 }
+__device__ __forceinline__ uint4 load16_any(const uint8_t* __restrict__ text, uint64_t pos, uint64_t len) {
+    if (pos + 16 <= len) return __ldg(reinterpret_cast<const uint4*>(text + pos));
+    if (pos >= len) return make_uint4(0, 0, 0, 0);
+    return load16(text, pos, len);
+}
 __device__ __forceinline__ uint32_t load4_safe(const uint8_t* __restrict__ text, uint64_t pos, uint64_t len) {
     if (pos + 4 <= len) return __ldg(reinterpret_cast<const uint32_t*>(text + pos));  // pos is 4-aligned here
     uint32_t w = 0;
@@ -301,15 +306,38 @@ __device__ __forceinline__ long tail_terminator(const uint8_t* __restrict__ s, u
     if (n >= 3 && s[le - 3] == 0xE2 && s[le - 2] == 0x80 && (s[le - 1] == 0xA8 || s[le - 1] == 0xA9)) return (long)le - 3;
     return -1;
 }
-__device__ bool dfa_walk(const DevPlan& P, uint32_t r, const uint8_t* __restrict__ text, uint32_t ls, uint32_t le) {
+// One regex over one line; the line streams through registers in 16-byte chunks (one chunk ahead).
+__device__ bool dfa_walk(const DevPlan& P, uint32_t r, const uint8_t* __restrict__ text, uint64_t len, uint32_t ls, uint32_t le) {
     const uint32_t nc = P.rx_ncls[r];
     const uint16_t* __restrict__ T = P.dfa_trans + P.rx_dfa_off[r];
     const uint8_t* __restrict__ cm = P.rx_cmap + (size_t)r * 256;
     uint32_t st = P.rx_start[r];
-    const long tpos = tail_terminator(text, ls, le);
-    for (uint32_t i = ls; i < le && st > 1; ++i) {
-        if ((long)i == tpos) st = T[st * nc + nc - 2];
-        st = T[st * nc + cm[text[i]]];
+    if (le > ls && st > 1) {
+        const long tpos = tail_terminator(text, ls, le);
+        const uint32_t tp = tpos < 0 ? 0xFFFFFFFFu : (uint32_t)tpos;
+        uint32_t i = ls;
+        uint64_t chunk = (uint64_t)(ls & ~15u);
+        uint4 cur = load16_any(text, chunk, len);
+        uint4 nxt = (chunk + 16 < le) ? load16_any(text, chunk + 16, len) : make_uint4(0, 0, 0, 0);
+        uint32_t wsel = (i >> 2) & 3u;
+        uint32_t w = (wsel == 0 ? cur.x : wsel == 1 ? cur.y : wsel == 2 ? cur.z : cur.w) >> ((i & 3u) * 8u);
+        for (;;) {
+            const uint32_t b = w & 0xFFu;
+            w >>= 8;
+            if (i == tp) st = T[st * nc + nc - 2];
+            st = T[st * nc + cm[b]];
+            ++i;
+            if (i >= le || st <= 1) break;
+            if ((i & 3u) == 0) {
+                wsel = (i >> 2) & 3u;
+                if (wsel == 0) {
+                    cur = nxt;
+                    chunk += 16;
+                    if (chunk + 16 < le) nxt = load16_any(text, chunk + 16, len);
+                }
+                w = wsel == 0 ? cur.x : wsel == 1 ? cur.y : wsel == 2 ? cur.z : cur.w;
+            }
+        }
     }
     if (st > 1) st = T[st * nc + nc - 1];
     return st == 1;
@@ -400,6 +428,7 @@ __global__ void __launch_bounds__(256) k_confirm(ConfirmArgs a, DevPlan P) {
 // ------------------------------------------------------------------ K4: verify tasks
 struct VerifyArgs {
     const uint8_t* text;
+    uint64_t len;
     const uint32_t* line_start;
     const uint32_t* line_end;
     const unsigned long long* tasks;
@@ -429,7 +458,7 @@ __global__ void __launch_bounds__(256) k_verify(VerifyArgs a, DevPlan P) {
             const unsigned long long task = a.tasks[t];
             r = (uint32_t)(task >> 32);
             g = (uint32_t)task;
-            if (P.rx_kind[r] == 0) hit = dfa_walk(P, r, a.text, a.line_start[g], a.line_end[g]);
+            if (P.rx_kind[r] == 0) hit = dfa_walk(P, r, a.text, a.len, a.line_start[g], a.line_end[g]);
         }
         emit_record(a.ctr, a.recs, a.rec_cap, hit, r, g);
     }
@@ -450,7 +479,7 @@ __global__ void __launch_bounds__(256) k_verify_always(VerifyArgs a, DevPlan P) 
         for (uint32_t q = 0; q < P.n_always; ++q) {
             const uint32_t r = P.always_list[q];
             bool hit = false;
-            if (live && P.rx_kind[r] == 0) hit = dfa_walk(P, r, a.text, ls, le);
+            if (live && P.rx_kind[r] == 0) hit = dfa_walk(P, r, a.text, a.len, ls, le);
             emit_record(a.ctr, a.recs, a.rec_cap, hit, r, g);
         }
     }
@@ -537,12 +566,6 @@ struct DfaScanArgs {
     Counters* ctr;
 };
 
-__device__ __forceinline__ uint4 load16_any(const uint8_t* __restrict__ text, uint64_t pos, uint64_t len) {
-    if (pos + 16 <= len) return __ldg(reinterpret_cast<const uint4*>(text + pos));
-    if (pos >= len) return make_uint4(0, 0, 0, 0);
-    return load16(text, pos, len);
-}
-
 template <int NG>
 __global__ void __launch_bounds__(DS_THREADS) k_dfa_scan(DfaScanArgs a) {
     extern __shared__ __align__(16) uint32_t ds_tabs[];
@@ -574,12 +597,11 @@ __global__ void __launch_bounds__(DS_THREADS) k_dfa_scan(DfaScanArgs a) {
     const uint8_t* cm[NG];
     const uint16_t* T[NG];
     const uint32_t* smask[NG];
-    uint32_t nc[NG], ff[NG], st0[NG], qa[NG], qb[NG], nb0[NG], nb1[NG];
+    uint32_t nc[NG], ff[NG], st0[NG];
 #pragma unroll
     for (int g = 0; g < NG; ++g) {
         const uint32_t* h = ds_tabs + s_goff[g];
         nc[g] = h[1]; st0[g] = h[2]; ff[g] = h[3];
-        qa[g] = h[33]; qb[g] = h[34]; nb0[g] = h[35]; nb1[g] = h[36];
         cm[g] = reinterpret_cast<const uint8_t*>(h + 37);
         smask[g] = h + 101;
         T[g] = reinterpret_cast<const uint16_t*>(h + 101 + h[0]);
@@ -613,15 +635,8 @@ __global__ void __launch_bounds__(DS_THREADS) k_dfa_scan(DfaScanArgs a) {
                     }
                     bool active = false;
 #pragma unroll
-                    for (int q = 0; q < NG; ++q) {
-                        if (st[q] < ff[q]) {
-                            const uint32_t cls = cm[q][b];
-                            // idle state + boring byte: the next idle state follows from word-ness alone
-                            if ((st[q] == qa[q] || st[q] == qb[q]) && cls < nb1[q]) st[q] = cls < nb0[q] ? qa[q] : qb[q];
-                            else st[q] = T[q][st[q] * nc[q] + cls];
-                            active = true;
-                        }
-                    }
+                    for (int q = 0; q < NG; ++q)
+                        if (st[q] < ff[q]) { st[q] = T[q][st[q] * nc[q] + cm[q][b]]; active = true; }
                     ++i;
                     if (i >= le || !active) break;
                     if ((i & 3u) == 0) {
@@ -1157,6 +1172,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     c->first_line.ensure((size_t)(n_logs + 1) * 4);
     c->n_lines.ensure((size_t)n_logs * 4);
     c->ctx_flags.ensure(((size_t)G / 4 + 2) * 4);
+    if (!c->plan.ctx_any_in_groups) CK(cudaMemsetAsync(c->ctx_flags.p, 0, ((size_t)G / 4 + 2) * 4, st));   // else k_dfa_scan writes every byte
     const bool use_filter = !c->plan.lit_off.empty();
     if (use_filter && !c->calibrated && len >= 4096) calibrate_filter(c, d_text, len);
     const uint32_t n_always = (uint32_t)c->plan.always_list.size();
@@ -1198,7 +1214,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         c->launches += 2;
 
         VerifyArgs va{};
-        va.text = d_text; va.line_start = c->line_start.as<uint32_t>(); va.line_end = c->line_end.as<uint32_t>();
+        va.text = d_text; va.len = len; va.line_start = c->line_start.as<uint32_t>(); va.line_end = c->line_end.as<uint32_t>();
         va.tasks = c->tasks.as<unsigned long long>(); va.task_cap = (uint32_t)std::min<size_t>(c->task_cap, 0xFFFFFFFFu); va.recs = c->recs.as<unsigned long long>();
         va.rec_cap = (uint32_t)rec_cap; va.ctr = ctr; va.n_lines_total = G;
         va.first_line = c->first_line.as<uint32_t>(); va.n_lines = c->n_lines.as<uint32_t>(); va.n_logs = n_logs;
@@ -1237,7 +1253,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
                 tab_bytes += ((size_t)c->group_words[g0 + q] + 3) / 4 * 16;
             }
             da.rx_record = c->d_rx_record; da.ctx_flags = c->ctx_flags.as<uint8_t>();
-            da.write_flags = (g0 == 0 && c->plan.ctx_in_groups) ? 1 : 0;
+            da.write_flags = (g0 == 0 && c->plan.ctx_any_in_groups) ? 1 : 0;
             da.recs = c->recs.as<unsigned long long>(); da.rec_cap = (uint32_t)rec_cap; da.ctr = ctr;
             const uint32_t per_sm = (uint32_t)std::max<size_t>(1, std::min<size_t>(8, (200 * 1024) / std::max<size_t>(tab_bytes, 1)));
             const uint32_t grid = std::min<uint32_t>(blocks_for(G, DS_THREADS), (uint32_t)c->n_sm * per_sm);
@@ -1270,7 +1286,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     uint32_t n_unique = 0;
     const uint32_t n_recs = h.n_recs;
     c->rx_begin.ensure((size_t)(c->dp.n_rx + 2) * 4);
-    if (!c->plan.ctx_in_groups) CK(cudaMemsetAsync(c->ctx_flags.p, 0, ((size_t)G / 4 + 2) * 4, st));
+
     if (n_recs) {
         const int kb = 32 + bits_for(c->dp.n_rx);
         sort_keys<unsigned long long>(c, c->recs.as<unsigned long long>(), c->recs_alt.as<unsigned long long>(), n_recs, kb);

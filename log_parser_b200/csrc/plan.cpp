@@ -96,7 +96,7 @@ void serialise_group(const std::vector<uint32_t>& rx, const MultiDfa& d, std::ve
 
 // Host mirror of the device walker in k_dfa_scan (same blob, same fast path); CPU-only tests use it.
 uint32_t run_group_blob(const std::vector<uint32_t>& blob, const uint8_t* s, size_t n) {
-    const uint32_t ns = blob[0], nc = blob[1], ff = blob[3], qa = blob[33], qb = blob[34], nb0 = blob[35], nb1 = blob[36];
+    const uint32_t ns = blob[0], nc = blob[1], ff = blob[3];
     const uint8_t* cm = reinterpret_cast<const uint8_t*>(&blob[37]);
     const uint32_t* smask = &blob[101];
     const uint16_t* T = reinterpret_cast<const uint16_t*>(&blob[101 + ns]);
@@ -108,9 +108,7 @@ uint32_t run_group_blob(const std::vector<uint32_t>& blob, const uint8_t* s, siz
     for (size_t i = 0; i < n && st < ff; ++i) {
         if ((long)i == tpos) st = T[st * nc + nc - 2];
         if (st >= ff) break;
-        const uint32_t cls = cm[s[i]];
-        if ((st == qa || st == qb) && cls < nb1) st = cls < nb0 ? qa : qb;
-        else st = T[st * nc + cls];
+        st = T[st * nc + cm[s[i]]];
     }
     return smask[T[st * nc + nc - 1]];
 }
@@ -160,9 +158,6 @@ void build_plan(const std::vector<PlanPatternIn>& pats, Plan& pl, int64_t* bad) 
             ++pl.n_vm;
         }
         std::vector<Literal> lits = required_literals(*pr.root, 4);
-        // the four context regexes hit a large share of all lines: cheaper in the always-on scan
-        // than as ~1 candidate per line in the literal prefilter
-        if (id < RX_FIRST_USER && is_dfa) lits.clear();
         pl.rx_always.push_back(lits.empty() ? 1 : 0);
         rx_lits.push_back(std::move(lits));
         parsed.push_back(std::move(pr));
@@ -273,7 +268,9 @@ void build_plan(const std::vector<PlanPatternIn>& pats, Plan& pl, int64_t* bad) 
         }
         flush();
         pl.ctx_in_groups = pl.rx_in_group[RX_ERR] && pl.rx_in_group[RX_WARN] && pl.rx_in_group[RX_STACK] && pl.rx_in_group[RX_EXC];
-        if (!pl.ctx_in_groups) for (uint32_t r = 0; r < RX_FIRST_USER; ++r) pl.rx_record[r] = 1;   // flags come from records
+        pl.ctx_any_in_groups = pl.rx_in_group[RX_ERR] || pl.rx_in_group[RX_WARN] || pl.rx_in_group[RX_STACK] || pl.rx_in_group[RX_EXC];
+        for (uint32_t r = 0; r < RX_FIRST_USER; ++r)
+            if (!pl.rx_in_group[r]) pl.rx_record[r] = 1;   // its context flag is derived from its records
     }
     for (uint32_t r = 0; r < pl.n_rx; ++r)
         if (pl.rx_always[r] && !pl.rx_in_group[r]) (pl.rx_kind[r] == RXK_DFA ? pl.always_list : pl.always_vm_list).push_back(r);

@@ -58,6 +58,7 @@ struct Plan {
     std::vector<uint8_t> rx_in_group;    // 1: decided by a scan group
     std::vector<uint8_t> rx_record;      // 1: matches must be recorded as (regex,line) (0: context flag only)
     bool ctx_in_groups = false;          // all four context regexes are decided by scan groups
+    bool ctx_any_in_groups = false;      // at least one is: k_dfa_scan writes the flag byte of every line
 
     // ---- literals and the gram filter
     std::vector<uint8_t> lit_bytes;

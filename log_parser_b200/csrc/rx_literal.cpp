@@ -2,20 +2,30 @@
 // match of the regex contains some member of L. Lines holding no member of L cannot satisfy
 // Matcher.find() (AnalysisService.java:95), so only lines where the gram filter fires are handed
 // to the DFA / backtracking verifiers. Lookaround bodies are ignored (sound: they consume nothing).
+//
+// Per node the analysis keeps: the exact language when it is a small finite set; a set every match
+// must START with and one it must END with (so that `\d{8,}ms` yields "00ms".."99ms"); and the best
+// factor set seen anywhere inside. Small character classes (digits, [45], [Ff]) are expanded.
 #include <algorithm>
+#include <cmath>
 
 #include "rx.h"
 
 namespace lpx {
 namespace {
 
-constexpr size_t MAX_SET = 24;     // alternatives kept in one literal set
+constexpr size_t MAX_SET = 256;    // alternatives kept in one literal set
 constexpr size_t MAX_LEN = 48;     // bytes kept per literal
+constexpr size_t MAX_CLASS = 16;   // a class with at most this many code points is expanded
+
+using LitSet = std::vector<Literal>;
 
 struct Info {
-    bool exact = false;            // `lits` is the complete (finite) language of the node
-    std::vector<Literal> lits;     // exact language, or empty
-    std::vector<Literal> best;     // best required-factor set seen inside (may be empty)
+    bool exact = false;     // `lits` is the complete (finite) language of the node
+    LitSet lits;
+    bool has_pre = false, has_suf = false;
+    LitSet pre, suf;        // every match starts with a member of pre / ends with a member of suf
+    LitSet best;            // best required-factor set seen inside (may be empty)
 };
 
 std::string utf8(uint32_t c) {
@@ -28,27 +38,26 @@ std::string utf8(uint32_t c) {
 }
 inline bool alpha(uint32_t c) { return (c >= 'a' && c <= 'z') || (c >= 'A' && c <= 'Z'); }
 
-// quality of a candidate set: (min length, -count); unusable if any member is shorter than min_len
-struct Score { long min_len; long neg_count; };
-Score score(const std::vector<Literal>& v) {
-    if (v.empty()) return {0, 0};
+// usefulness of a factor set: long members are selective, many members cost filter entries
+double utility(const LitSet& v) {
+    if (v.empty()) return -1e9;
     size_t m = SIZE_MAX;
     for (const auto& l : v) m = std::min(m, l.bytes.size());
-    return {(long)m, -(long)v.size()};
+    if (m == 0) return -1e9;
+    return (double)std::min<size_t>(m, 12) - 2.0 * std::log2((double)v.size());
 }
-bool better(const std::vector<Literal>& a, const std::vector<Literal>& b) {
-    Score x = score(a), y = score(b);
-    // prefer longer minimum length, but a much smaller set wins ties
-    if (x.min_len != y.min_len) return x.min_len > y.min_len;
-    return x.neg_count > y.neg_count;
+size_t min_len_of(const LitSet& v) {
+    size_t m = SIZE_MAX;
+    for (const auto& l : v) m = std::min(m, l.bytes.size());
+    return v.empty() ? 0 : m;
 }
 
-void dedupe(std::vector<Literal>& v) {
+void dedupe(LitSet& v) {
     std::sort(v.begin(), v.end(), [](const Literal& a, const Literal& b) { return a.bytes != b.bytes ? a.bytes < b.bytes : a.icase < b.icase; });
     v.erase(std::unique(v.begin(), v.end(), [](const Literal& a, const Literal& b) { return a.bytes == b.bytes && a.icase == b.icase; }), v.end());
 }
 
-bool cross(const std::vector<Literal>& a, const std::vector<Literal>& b, std::vector<Literal>& out) {
+bool cross(const LitSet& a, const LitSet& b, LitSet& out) {
     if (a.size() * b.size() > MAX_SET) return false;
     out.clear();
     for (const auto& x : a)
@@ -64,93 +73,140 @@ bool cross(const std::vector<Literal>& a, const std::vector<Literal>& b, std::ve
     return true;
 }
 
-void consider(std::vector<Literal>& best, const std::vector<Literal>& cand) {
-    if (cand.empty()) return;
-    for (const auto& l : cand) if (l.bytes.empty()) return;  // contains "", requires nothing
-    if (best.empty() || better(cand, best)) best = cand;
-}
+struct Picker {
+    size_t min_len;
+    LitSet best;
+    void consider(const LitSet& cand) {
+        if (cand.empty() || min_len_of(cand) < 1) return;
+        const bool ok_c = min_len_of(cand) >= min_len, ok_b = !best.empty() && min_len_of(best) >= min_len;
+        if (best.empty() || (ok_c && !ok_b) || (ok_c == ok_b && utility(cand) > utility(best))) best = cand;
+    }
+};
 
-Info walk(const Ast& a) {
+const LitSet EMPTY_WORD{Literal{"", false}};
+
+Info walk(const Ast& a, size_t min_len) {
     Info r;
+    Picker pk{min_len, {}};
+    auto finish = [&]() {
+        if (r.exact) { r.has_pre = r.has_suf = true; r.pre = r.suf = r.lits; pk.consider(r.lits); }
+        if (r.has_pre) pk.consider(r.pre);
+        if (r.has_suf) pk.consider(r.suf);
+        r.best = pk.best;
+        return r;
+    };
     switch (a.kind) {
         case AstKind::Empty: case AstKind::Assert: case AstKind::Look:
-            r.exact = true; r.lits = {Literal{"", false}}; return r;
+            r.exact = true; r.lits = EMPTY_WORD; r.has_pre = r.has_suf = true; r.pre = r.suf = EMPTY_WORD; return r;
         case AstKind::Backref: return r;
         case AstKind::Set: {
-            // single code point, an ASCII case pair, or a handful of code points
             size_t count = 0;
-            for (const auto& x : a.set) { count += (size_t)(x.hi - x.lo) + 1; if (count > 4) break; }
-            if (count == 0 || count > 4) return r;
+            for (const auto& x : a.set) { count += (size_t)(x.hi - x.lo) + 1; if (count > MAX_CLASS + 1) break; }
+            if (count == 0 || count > MAX_CLASS + 1) return r;
             std::vector<uint32_t> cps;
             for (const auto& x : a.set) for (uint32_t c = x.lo; c <= x.hi; ++c) cps.push_back(c);
-            if (cps.size() == 2 && alpha(cps[0]) && (cps[0] ^ 0x20) == cps[1]) {
-                r.exact = true; r.lits = {Literal{std::string(1, (char)(cps[0] | 0x20)), true}}; r.best = r.lits; return r;
-            }
             r.exact = true;
-            for (uint32_t c : cps) r.lits.push_back(Literal{utf8(c), false});
-            r.best = r.lits;
-            return r;
-        }
-        case AstKind::Group: case AstKind::Atomic: return walk(*a.kids[0]);
-        case AstKind::Alt: {
-            bool all_exact = true, all_best = true;
-            std::vector<Literal> uni, bestu;
-            for (const auto& k : a.kids) {
-                Info ki = walk(*k);
-                if (ki.exact) uni.insert(uni.end(), ki.lits.begin(), ki.lits.end()); else all_exact = false;
-                if (ki.best.empty()) all_best = false; else bestu.insert(bestu.end(), ki.best.begin(), ki.best.end());
+            // ASCII case pairs collapse to one case-insensitive member
+            std::vector<char> used(cps.size(), 0);
+            for (size_t i = 0; i < cps.size(); ++i) {
+                if (used[i]) continue;
+                bool paired = false;
+                if (alpha(cps[i]))
+                    for (size_t j = i + 1; j < cps.size(); ++j)
+                        if (!used[j] && (cps[i] ^ 0x20) == cps[j]) { used[j] = 1; paired = true; break; }
+                if (paired) r.lits.push_back(Literal{std::string(1, (char)(cps[i] | 0x20)), true});
+                else r.lits.push_back(Literal{utf8(cps[i]), false});
             }
-            dedupe(uni);
-            dedupe(bestu);
+            if (r.lits.size() > MAX_CLASS) { r.exact = false; r.lits.clear(); return r; }
+            return finish();
+        }
+        case AstKind::Group: case AstKind::Atomic: return walk(*a.kids[0], min_len);
+        case AstKind::Alt: {
+            bool all_exact = true, all_best = true, all_pre = true, all_suf = true;
+            LitSet uni, bestu, preu, sufu;
+            for (const auto& k : a.kids) {
+                Info ki = walk(*k, min_len);
+                if (ki.exact) uni.insert(uni.end(), ki.lits.begin(), ki.lits.end()); else all_exact = false;
+                if (ki.best.empty() || min_len_of(ki.best) < min_len) all_best = false; else bestu.insert(bestu.end(), ki.best.begin(), ki.best.end());
+                if (ki.has_pre) preu.insert(preu.end(), ki.pre.begin(), ki.pre.end()); else all_pre = false;
+                if (ki.has_suf) sufu.insert(sufu.end(), ki.suf.begin(), ki.suf.end()); else all_suf = false;
+            }
+            dedupe(uni); dedupe(bestu); dedupe(preu); dedupe(sufu);
             if (all_exact && uni.size() <= MAX_SET) { r.exact = true; r.lits = uni; }
-            if (all_best && bestu.size() <= MAX_SET) r.best = bestu;
-            if (r.exact) consider(r.best, r.lits);
+            if (all_pre && preu.size() <= MAX_SET) { r.has_pre = true; r.pre = preu; }
+            if (all_suf && sufu.size() <= MAX_SET) { r.has_suf = true; r.suf = sufu; }
+            if (all_best && bestu.size() <= MAX_SET) pk.consider(bestu);
+            if (r.exact) pk.consider(r.lits);
+            r.best = pk.best;
             return r;
         }
         case AstKind::Cat: {
-            std::vector<Literal> acc{Literal{"", false}};
-            bool whole = true;
+            // `acc`: every match of the kids seen so far ends with a member of acc (it may carry the
+            // required suffix of an inexact kid in); `fresh`: the exact run since the last inexact kid
+            LitSet acc = EMPTY_WORD, fresh = EMPTY_WORD;
+            bool whole = true;      // acc is still the exact language of the prefix
             for (const auto& k : a.kids) {
-                Info ki = walk(*k);
-                consider(r.best, ki.best);
+                Info ki = walk(*k, min_len);
+                pk.consider(ki.best);
                 if (ki.exact) {
-                    std::vector<Literal> nx;
-                    if (cross(acc, ki.lits, nx)) { acc.swap(nx); continue; }
-                    // too large: bank what we have, restart from this kid
-                    consider(r.best, acc);
+                    LitSet nx;
+                    if (cross(acc, ki.lits, nx)) { acc.swap(nx); }
+                    else {
+                        pk.consider(acc);
+                        if (whole) { r.has_pre = true; r.pre = acc; }
+                        whole = false;
+                        acc = ki.lits;
+                    }
+                    if (cross(fresh, ki.lits, nx)) fresh.swap(nx);
+                    else { pk.consider(fresh); fresh = ki.lits; }
+                } else {
+                    if (ki.has_pre) { LitSet nx; if (cross(acc, ki.pre, nx)) pk.consider(nx); if (cross(fresh, ki.pre, nx)) pk.consider(nx); }
+                    pk.consider(acc);
+                    pk.consider(fresh);
+                    if (whole) {   // everything before this kid was exact: it is a required prefix
+                        LitSet nx;
+                        r.has_pre = true;
+                        if (ki.has_pre && cross(acc, ki.pre, nx)) r.pre = nx; else r.pre = acc;
+                    }
                     whole = false;
-                    acc = ki.lits;
-                    if (acc.size() > MAX_SET) acc = {Literal{"", false}};
-                    continue;
+                    acc = ki.has_suf ? ki.suf : EMPTY_WORD;
+                    fresh = EMPTY_WORD;
                 }
-                consider(r.best, acc);
-                whole = false;
-                acc = {Literal{"", false}};
             }
-            consider(r.best, acc);
+            pk.consider(acc);
+            pk.consider(fresh);
             if (whole) { r.exact = true; r.lits = acc; }
+            r.has_suf = true; r.suf = acc;
+            if (r.exact) { r.has_pre = true; r.pre = acc; }
+            r.best = pk.best;
             return r;
         }
         case AstKind::Repeat: {
-            Info ki = walk(*a.kids[0]);
+            Info ki = walk(*a.kids[0], min_len);
             if (a.min == 0) {
                 if (a.max == 1 && ki.exact && ki.lits.size() < MAX_SET) {
                     r.exact = true; r.lits = ki.lits; r.lits.push_back(Literal{"", false}); dedupe(r.lits);
                 }
-                return r;
+                return r;     // may match nothing: requires nothing
             }
-            // at least one iteration happens
-            r.best = ki.best;
+            pk.consider(ki.best);
             if (ki.exact) {
-                consider(r.best, ki.lits);
-                if (a.min == a.max && a.min <= 4) {
-                    std::vector<Literal> acc{Literal{"", false}};
-                    bool ok = true;
-                    for (int i = 0; i < a.min && ok; ++i) { std::vector<Literal> nx; ok = cross(acc, ki.lits, nx); if (ok) acc.swap(nx); }
-                    if (ok) { r.exact = true; r.lits = acc; consider(r.best, acc); }
+                pk.consider(ki.lits);
+                // fixed small counts are exact; otherwise the match starts and ends with min(min,2) copies
+                const int copies = std::min(a.min, a.min == a.max ? 4 : 2);
+                LitSet acc = EMPTY_WORD;
+                bool ok = true;
+                for (int i = 0; i < copies && ok; ++i) { LitSet nx; ok = cross(acc, ki.lits, nx); if (ok) acc.swap(nx); }
+                if (ok && a.min == a.max && copies == a.min) { r.exact = true; r.lits = acc; }
+                else {
+                    r.has_pre = r.has_suf = true;
+                    r.pre = r.suf = ok ? acc : ki.lits;
                 }
+            } else {
+                if (ki.has_pre) { r.has_pre = true; r.pre = ki.pre; }
+                if (ki.has_suf) { r.has_suf = true; r.suf = ki.suf; }
             }
-            return r;
+            return finish();
         }
     }
     return r;
@@ -159,12 +215,14 @@ Info walk(const Ast& a) {
 }  // namespace
 
 std::vector<Literal> required_literals(const Ast& root, size_t min_len) {
-    Info i = walk(root);
-    std::vector<Literal> best = i.best;
-    if (i.exact) consider(best, i.lits);
-    if (best.empty()) return {};
-    for (const auto& l : best) if (l.bytes.size() < min_len) return {};
-    return best;
+    Info i = walk(root, min_len);
+    Picker pk{min_len, i.best};
+    if (i.exact) pk.consider(i.lits);
+    if (i.has_pre) pk.consider(i.pre);
+    if (i.has_suf) pk.consider(i.suf);
+    if (pk.best.empty() || min_len_of(pk.best) < min_len) return {};
+    for (const auto& l : pk.best) if (l.bytes.empty()) return {};
+    return pk.best;
 }
 
 }  // namespace lpx
