@@ -372,8 +372,11 @@ struct ConfirmArgs {
     uint32_t task_cap;
     unsigned long long* vm_tasks;
     uint32_t vm_task_cap;
+    unsigned long long* recs;
+    uint32_t rec_cap;
     Counters* ctr;
 };
+__device__ __forceinline__ bool dev_word(uint8_t b) { return (b >= '0' && b <= '9') || (b >= 'A' && b <= 'Z') || b == '_' || (b >= 'a' && b <= 'z'); }
 __global__ void __launch_bounds__(256) k_confirm(ConfirmArgs a, DevPlan P) {
     const uint32_t n = min(a.ctr->n_cand, a.cand_cap);
     for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < n; c += gridDim.x * blockDim.x) {
@@ -411,6 +414,20 @@ __global__ void __launch_bounds__(256) k_confirm(ConfirmArgs a, DevPlan P) {
             const uint32_t rb = P.lit_rx_begin[l], re = P.lit_rx_begin[l + 1];
             for (uint32_t j = rb; j < re; ++j) {
                 const uint32_t r = P.lit_rx[j];
+                const uint32_t mode = P.lit_rx_mode[j];
+                if (mode & 1u) {
+                    // literal-with-boundaries pattern: decided right here at the occurrence
+                    const uint32_t e2 = s + ll;
+                    bool hit = true;
+                    if (mode & 2u) hit = (s > ls && dev_word(a.text[s - 1])) != dev_word(a.text[s]);
+                    if (hit && (mode & 4u)) hit = dev_word(a.text[e2 - 1]) != (e2 < le && dev_word(a.text[e2]));
+                    if (hit) {
+                        const uint32_t idx = atomicAdd(&a.ctr->n_recs, 1u);
+                        if (idx < a.rec_cap) a.recs[idx] = ((unsigned long long)r << 32) | g;
+                        else atomicOr(&a.ctr->overflow, 4u);
+                    }
+                    continue;
+                }
                 if (P.rx_kind[r] == 0) {
                     const uint32_t idx = atomicAdd(&a.ctr->n_tasks, 1u);
                     if (idx < a.task_cap) a.tasks[idx] = ((unsigned long long)r << 32) | g;
@@ -1077,6 +1094,7 @@ void upload_plan(lp_ctx* c) {
     d.lit_icase = upload(K, pl.lit_icase);
     d.lit_rx_begin = upload(K, pl.lit_rx_begin);
     d.lit_rx = upload(K, pl.lit_rx);
+    d.lit_rx_mode = upload(K, pl.lit_rx_mode);
     d.n_pat = pl.n_pat;
     d.pat_primary = upload(K, pl.pat_primary);
     d.pat_conf = upload(K, pl.pat_conf);
@@ -1190,7 +1208,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
             if (c->vm_task_cap == 0) c->vm_task_cap = std::max<size_t>(1u << 14, len / 64);
             c->vm_tasks.ensure(c->vm_task_cap * 8);
         }
-        const size_t rec_cap = c->task_cap + (has_vm ? c->vm_task_cap : 0) + (size_t)G * (n_always + n_always_vm) +
+        const size_t rec_cap = c->task_cap + c->cand_cap + (has_vm ? c->vm_task_cap : 0) + (size_t)G * (n_always + n_always_vm) +
                                (c->n_group_record_rx ? std::max<size_t>(1u << 16, (size_t)G / 4 * c->n_group_record_rx) : 0) + 16;
         if (rec_cap >= 0x7FFFFFFFull) throw LimitFail("record capacity exceeds 2^31; shard the batch");
         c->recs.ensure(rec_cap * 8);
@@ -1226,6 +1244,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
             ca.line_start = c->line_start.as<uint32_t>(); ca.line_end = c->line_end.as<uint32_t>(); ca.n_lines_total = G;
             ca.tasks = c->tasks.as<unsigned long long>(); ca.task_cap = (uint32_t)std::min<size_t>(c->task_cap, 0xFFFFFFFFu); ca.ctr = ctr;
             ca.vm_tasks = c->vm_tasks.as<unsigned long long>(); ca.vm_task_cap = va.vm_task_cap;
+            ca.recs = c->recs.as<unsigned long long>(); ca.rec_cap = (uint32_t)rec_cap;
             k_confirm<<<c->n_sm * 8, 256, 0, st>>>(ca, c->dp);
             k_verify<<<c->n_sm * 8, 256, 0, st>>>(va, c->dp);
             c->launches += 2;

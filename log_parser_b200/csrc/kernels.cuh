@@ -46,6 +46,7 @@ struct DevPlan {
     const uint8_t* lit_icase;
     const uint32_t* lit_rx_begin;
     const uint32_t* lit_rx;
+    const uint8_t* lit_rx_mode;
     // patterns
     uint32_t n_pat;
     const uint32_t* pat_primary;

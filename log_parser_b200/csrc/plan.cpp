@@ -120,6 +120,7 @@ void build_plan(const std::vector<PlanPatternIn>& pats, Plan& pl, int64_t* bad) 
     std::vector<int> rx_flags;
     std::vector<std::vector<Literal>> rx_lits;
     std::vector<ParsedRegex> parsed;
+    std::vector<std::vector<uint8_t>> rx_lit_mode;     // parallel to rx_lits
 
     auto add_regex = [&](const std::string& src, int flags) -> uint32_t {
         auto key = std::make_pair(src, flags);
@@ -157,9 +158,21 @@ void build_plan(const std::vector<PlanPatternIn>& pats, Plan& pl, int64_t* bad) 
             pl.vm_code.insert(pl.vm_code.end(), vp.code.begin(), vp.code.end());
             ++pl.n_vm;
         }
-        std::vector<Literal> lits = required_literals(*pr.root, 4);
+        std::vector<Literal> lits;
+        std::vector<uint8_t> modes;
+        std::vector<LocalLiteral> local;
+        if (is_dfa && local_verify_form(*pr.root, local, 4)) {
+            for (const auto& l : local) {
+                lits.push_back(l.lit);
+                modes.push_back((uint8_t)(1 | (l.left_boundary ? 2 : 0) | (l.right_boundary ? 4 : 0)));
+            }
+        } else {
+            lits = required_literals(*pr.root, 4);
+            modes.assign(lits.size(), 0);
+        }
         pl.rx_always.push_back(lits.empty() ? 1 : 0);
         rx_lits.push_back(std::move(lits));
+        rx_lit_mode.push_back(std::move(modes));
         parsed.push_back(std::move(pr));
         return id;
     };
@@ -278,8 +291,10 @@ void build_plan(const std::vector<PlanPatternIn>& pats, Plan& pl, int64_t* bad) 
     // ---- literal table: de-duplicate (bytes, icase) across regexes
     std::map<std::pair<std::string, bool>, uint32_t> lit_ids;
     std::vector<std::vector<uint32_t>> lit_rx;
+    std::vector<std::vector<uint8_t>> lit_mode;
     for (uint32_t r = 0; r < pl.n_rx; ++r) {
-        for (const Literal& l : rx_lits[r]) {
+        for (size_t li = 0; li < rx_lits[r].size(); ++li) {
+            const Literal& l = rx_lits[r][li];
             auto key = std::make_pair(l.bytes, l.icase);
             auto it = lit_ids.find(key);
             if (it == lit_ids.end()) {
@@ -290,15 +305,17 @@ void build_plan(const std::vector<PlanPatternIn>& pats, Plan& pl, int64_t* bad) 
                 pl.lit_icase.push_back(l.icase ? 1 : 0);
                 pl.lit_bytes.insert(pl.lit_bytes.end(), l.bytes.begin(), l.bytes.end());
                 lit_rx.emplace_back();
+                lit_mode.emplace_back();
                 pl.lit_gram_off.push_back(0);
             }
             auto& v = lit_rx[it->second];
-            if (std::find(v.begin(), v.end(), r) == v.end()) v.push_back(r);
+            if (std::find(v.begin(), v.end(), r) == v.end()) { v.push_back(r); lit_mode[it->second].push_back(rx_lit_mode[r][li]); }
         }
     }
     pl.lit_rx_begin.push_back(0);
-    for (auto& v : lit_rx) {
-        pl.lit_rx.insert(pl.lit_rx.end(), v.begin(), v.end());
+    for (size_t l = 0; l < lit_rx.size(); ++l) {
+        pl.lit_rx.insert(pl.lit_rx.end(), lit_rx[l].begin(), lit_rx[l].end());
+        pl.lit_rx_mode.insert(pl.lit_rx_mode.end(), lit_mode[l].begin(), lit_mode[l].end());
         pl.lit_rx_begin.push_back((uint32_t)pl.lit_rx.size());
     }
     select_grams(pl, nullptr, 0);

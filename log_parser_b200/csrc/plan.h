@@ -65,6 +65,7 @@ struct Plan {
     std::vector<uint32_t> lit_off, lit_len, lit_gram_off;
     std::vector<uint8_t> lit_icase;
     std::vector<uint32_t> lit_rx_begin, lit_rx;       // CSR literal -> regex ids
+    std::vector<uint8_t> lit_rx_mode;                 // per CSR entry: 0 verify by automaton; 1 | left\b<<1 | right\b<<2: decided at the occurrence
     std::vector<uint32_t> bitmap;                     // 2^GRAM_BITS bits
     uint32_t table_bits = 0;
     std::vector<uint32_t> table_key;                  // folded gram, 0 = empty (0x20202020-folded grams are never 0)

@@ -111,9 +111,22 @@ bool build_multi_dfa(const std::vector<const Ast*>& roots, MultiDfa& out, uint32
 struct Literal {
     std::string bytes;  // UTF-8; if icase: ASCII letters are stored lower-case
     bool icase = false;
+    bool lossy = false; // case-sensitive letters were folded into a case-insensitive literal: superset only
 };
 // A set L such that every match of the regex contains at least one member of L as a substring.
 // Empty result = no usable literal (every line is a candidate).
 std::vector<Literal> required_literals(const Ast& root, size_t min_len);
+
+// "Literal with word-boundary conditions" form: the regex is an alternation of branches
+//   [\b] [\w*] LITERAL-SET [\b]
+// so that a line matches iff some occurrence of one of the literals satisfies its boundary
+// conditions. Such patterns (the context regexes of CAS:27-34, plain-string secondaries, ...) are
+// decided at the literal occurrence itself, without walking the line through an automaton.
+struct LocalLiteral {
+    Literal lit;
+    bool left_boundary = false;    // \b required immediately before the literal
+    bool right_boundary = false;   // \b required immediately after it
+};
+bool local_verify_form(const Ast& root, std::vector<LocalLiteral>& out, size_t min_len);
 
 }  // namespace lpx

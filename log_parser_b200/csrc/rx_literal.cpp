@@ -66,6 +66,8 @@ bool cross(const LitSet& a, const LitSet& b, LitSet& out) {
             Literal l;
             l.icase = x.icase || y.icase;
             l.bytes = x.bytes + y.bytes;
+            auto letters = [](const std::string& b) { for (unsigned char ch : b) if ((ch | 0x20) >= 'a' && (ch | 0x20) <= 'z') return true; return false; };
+            l.lossy = x.lossy || y.lossy || (l.icase && ((!x.icase && letters(x.bytes)) || (!y.icase && letters(y.bytes))));
             if (l.icase) for (auto& ch : l.bytes) if (ch >= 'A' && ch <= 'Z') ch = (char)(ch + 32);
             out.push_back(std::move(l));
         }
@@ -213,6 +215,70 @@ Info walk(const Ast& a, size_t min_len) {
 }
 
 }  // namespace
+
+namespace {
+
+const Ast* strip_groups(const Ast* a) {
+    while (a->kind == AstKind::Group) a = a->kids[0].get();
+    return a;
+}
+bool is_word_set(const CpSet& s) {
+    return s.size() == 4 && s[0].lo == '0' && s[0].hi == '9' && s[1].lo == 'A' && s[1].hi == 'Z' && s[2].lo == '_' && s[2].hi == '_' &&
+           s[3].lo == 'a' && s[3].hi == 'z';
+}
+inline bool word_byte_l(unsigned char b) { return (b >= '0' && b <= '9') || (b >= 'A' && b <= 'Z') || b == '_' || (b >= 'a' && b <= 'z'); }
+
+bool local_branch(const Ast* br, std::vector<LocalLiteral>& out, size_t min_len) {
+    br = strip_groups(br);
+    std::vector<const Ast*> kids;
+    if (br->kind == AstKind::Cat) for (const auto& k : br->kids) kids.push_back(k.get());
+    else kids.push_back(br);
+    size_t lo = 0, hi = kids.size();
+    bool left_b = false, right_b = false, skipped_w = false;
+    if (lo < hi && kids[lo]->kind == AstKind::Assert && kids[lo]->assert_kind == AssertKind::WordB) { left_b = true; ++lo; }
+    if (lo < hi && kids[lo]->kind == AstKind::Repeat && kids[lo]->min == 0 && kids[lo]->max < 0 && kids[lo]->mode != 2 &&
+        kids[lo]->kids[0]->kind == AstKind::Set && is_word_set(kids[lo]->kids[0]->set)) { skipped_w = true; ++lo; }
+    if (lo < hi && kids[hi - 1]->kind == AstKind::Assert && kids[hi - 1]->assert_kind == AssertKind::WordB) { right_b = true; --hi; }
+    if (lo >= hi) return false;
+    LitSet acc = EMPTY_WORD;
+    for (size_t i = lo; i < hi; ++i) {
+        if (kids[i]->kind == AstKind::Assert || kids[i]->kind == AstKind::Look || kids[i]->kind == AstKind::Backref) return false;
+        Info ki = walk(*kids[i], min_len);
+        if (!ki.exact) return false;
+        LitSet nx;
+        if (!cross(acc, ki.lits, nx)) return false;
+        acc.swap(nx);
+    }
+    if (acc.empty() || acc.size() > 64) return false;
+    for (const auto& l : acc) {
+        if (l.bytes.size() < min_len || l.lossy) return false;
+        const bool first_word = word_byte_l((unsigned char)l.bytes[0]);
+        LocalLiteral ll;
+        ll.lit = l;
+        ll.right_boundary = right_b;
+        if (skipped_w) {
+            // "\w*LIT" and "\b\w*LIT" hold at every occurrence whose first byte is a word byte
+            // (the word run that contains it starts at a boundary); otherwise keep the automaton
+            if (!first_word) return false;
+            ll.left_boundary = false;
+        } else ll.left_boundary = left_b;
+        out.push_back(std::move(ll));
+    }
+    return true;
+}
+
+}  // namespace
+
+bool local_verify_form(const Ast& root, std::vector<LocalLiteral>& out, size_t min_len) {
+    out.clear();
+    const Ast* r = strip_groups(&root);
+    if (r->kind == AstKind::Alt) {
+        for (const auto& k : r->kids) if (!local_branch(k.get(), out, min_len)) { out.clear(); return false; }
+        return !out.empty();
+    }
+    if (!local_branch(r, out, min_len)) { out.clear(); return false; }
+    return true;
+}
 
 std::vector<Literal> required_literals(const Ast& root, size_t min_len) {
     Info i = walk(root, min_len);

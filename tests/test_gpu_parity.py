@@ -245,3 +245,22 @@ def test_c2_sample_parity_and_properties(parser, oracle):
     sel = r1.line <= nh
     np.testing.assert_array_equal(r1.line[sel], rh.line)
     np.testing.assert_array_equal(r1.pattern[sel], rh.pattern)
+
+
+def test_literal_with_boundaries_patterns(parser, oracle):
+    """Patterns of the form [\\b][\\w*]LITERAL[\\b] are decided at the literal occurrence (no automaton
+    walk); mixed-case and case-insensitive variants must keep java.util.regex semantics."""
+    lines = ["ERROR x", "xERROR y", "ERRORS", "an error here", "Failed to bind", "FAILED TO BIND", "failed to bind", "warn", "WARNING!",
+             "prewarn", "FooException: x", "FooExceptions", "my_Error", "Error", "a SocketTimeoutException b", "aSocketTimeoutException",
+             "shutdown hook invoked", "Shutdown hook invoked twice", "é ERROR é", "ERROR", "x", ""]
+    log = ("\n".join(lines) + "\n").encode()
+    regs = [r"\b(ERROR|FATAL)\b", r"(?i)\b(warn|warning)\b", r"[Ff]ailed to bind", r"(?i)failed TO bind", r"\b\w*Exception\b|\b\w*Error\b",
+            r"\bSocketTimeoutException\b", r"Shutdown hook invoked", r"\w*Exception", r"ERROR\b", r"\bERROR", r"(?i:shut)down hook"]
+    pats = [PatternSpec(id="p%d" % i, primary_regex=r, confidence=0.5, lines_before=2, lines_after=2,
+                        secondaries=[SecondaryPattern(regs[(i + 1) % len(regs)], 0.5, 5)]) for i, r in enumerate(regs)]
+    parser.load_patterns(pats)
+    res = parser.analyze(log, options=binding.OPT_FACTORS)
+    ora = oracle.analyze(ScoringConfig(), pats, log)
+    assert len(ora.line) > 25
+    _check(res, ora)
+    np.testing.assert_array_equal(res.score, ora.score)
