@@ -38,25 +38,32 @@ __device__ __forceinline__ uint32_t nl_mask16(const uint4& v) {
     return nl_mask4(v.x) | (nl_mask4(v.y) << 4) | (nl_mask4(v.z) << 8) | (nl_mask4(v.w) << 12);
 }
 
-// 16 bytes at `pos`; bytes at or beyond `len` read as zero. `text` is 16-byte aligned.
-__device__ __forceinline__ uint4 load16(const uint8_t* __restrict__ text, uint64_t pos, uint64_t len) {
-    if (pos + 16 <= len) return __ldg(reinterpret_cast<const uint4*>(text + pos));
+// 16 bytes at `pos`; bytes at or beyond `len` read as zero. `text` is 16-byte aligned. The
+// byte-wise tail is kept out of line so that it is not if-converted into every caller's hot loop.
+__device__ __noinline__ uint4 load16_tail(const uint8_t* __restrict__ text, uint64_t pos, uint64_t len) {
     uint32_t w[4] = {0, 0, 0, 0};
     for (int i = 0; i < 16; ++i)
         if (pos + i < len) w[i >> 2] |= (uint32_t)text[pos + i] << ((i & 3) * 8);
     return make_uint4(w[0], w[1], w[2], w[3]);
+}
+__device__ __forceinline__ uint4 load16(const uint8_t* __restrict__ text, uint64_t pos, uint64_t len) {
+    if (pos + 16 <= len) return __ldg(reinterpret_cast<const uint4*>(text + pos));
+    return load16_tail(text, pos, len);
 }
 __device__ __forceinline__ uint4 load16_any(const uint8_t* __restrict__ text, uint64_t pos, uint64_t len) {
     if (pos + 16 <= len) return __ldg(reinterpret_cast<const uint4*>(text + pos));
     if (pos >= len) return make_uint4(0, 0, 0, 0);
     return load16(text, pos, len);
 }
-__device__ __forceinline__ uint32_t load4_safe(const uint8_t* __restrict__ text, uint64_t pos, uint64_t len) {
-    if (pos + 4 <= len) return __ldg(reinterpret_cast<const uint32_t*>(text + pos));  // pos is 4-aligned here
+__device__ __noinline__ uint32_t load4_tail(const uint8_t* __restrict__ text, uint64_t pos, uint64_t len) {
     uint32_t w = 0;
     for (int i = 0; i < 4; ++i)
         if (pos + i < len) w |= (uint32_t)text[pos + i] << (i * 8);
     return w;
+}
+__device__ __forceinline__ uint32_t load4_safe(const uint8_t* __restrict__ text, uint64_t pos, uint64_t len) {
+    if (pos + 4 <= len) return __ldg(reinterpret_cast<const uint32_t*>(text + pos));  // pos is 4-aligned here
+    return load4_tail(text, pos, len);
 }
 
 // number of elements of a[0..n) that are <= v   (upper bound)
@@ -1634,7 +1641,10 @@ size_t lp_debug_plan_dump(const lp_pattern_desc* pats, size_t n, const uint8_t* 
             char g[16];
             const uint8_t* b = &pl.lit_bytes[pl.lit_off[l] + pl.lit_gram_off[l]];
             snprintf(g, sizeof g, "%02x%02x%02x%02x", b[0], b[1], b[2], b[3]);
-            out += g; out += "\t"; out += pl.lit_icase[l] ? "1" : "0"; out += "\t";
+            out += g; out += "\t"; out += pl.lit_icase[l] ? "1" : "0";
+            out += ":";
+            for (uint32_t j = pl.lit_rx_begin[l]; j < pl.lit_rx_begin[l + 1]; ++j) { out += std::to_string(pl.lit_rx[j]) + "/" + std::to_string((int)pl.lit_rx_mode[j]) + ","; }
+            out += "\t";
             out.append(reinterpret_cast<const char*>(&pl.lit_bytes[pl.lit_off[l]]), pl.lit_len[l]);
             out += "\n";
         }

@@ -11,8 +11,8 @@
 
 namespace lpk {
 
-constexpr int SCAN_THREADS = 256;
-constexpr int SCAN_ITERS = 8;
+constexpr int SCAN_THREADS = 512;
+constexpr int SCAN_ITERS = 4;
 constexpr uint32_t TILE_BYTES = SCAN_THREADS * 16 * SCAN_ITERS;   // 32 KiB of log per tile
 constexpr uint32_t GRAM_BITS = 19;
 constexpr uint32_t GRAM_WORDS = (1u << GRAM_BITS) / 32;
