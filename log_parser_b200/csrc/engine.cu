@@ -115,7 +115,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_count_nl(const uint8_t* __rest
 }
 
 // exclusive scan of tile counts (one block); also publishes the total
-__global__ void __launch_bounds__(1024) k_scan_tiles(uint32_t* __restrict__ tile_counts, uint32_t n_tiles, Counters* ctr) {
+__global__ void __launch_bounds__(1024) k_scan_tiles(uint32_t* __restrict__ tile_counts, uint32_t n_tiles, uint32_t n_logs, Counters* ctr) {
     __shared__ uint32_t warp_tot[32];
     __shared__ uint32_t carry;
     if (threadIdx.x == 0) carry = 0;
@@ -140,7 +140,7 @@ __global__ void __launch_bounds__(1024) k_scan_tiles(uint32_t* __restrict__ tile
         if (threadIdx.x == 1023) carry = excl + v;
         __syncthreads();
     }
-    if (threadIdx.x == 0) ctr->total_nl = carry;
+    if (threadIdx.x == 0) { ctr->total_nl = carry; ctr->n_lines_total = carry + n_logs; }
 }
 
 // ------------------------------------------------------------------ K2: line offsets + gram prefilter
@@ -157,6 +157,7 @@ struct ScanArgs {
     uint32_t* line_start;             // [G]
     uint32_t* line_end;               // [G]
     uint32_t* first_line;             // [n_logs+1]
+    uint32_t line_cap;                // capacity of line_start / line_end (optimistic; overflow -> retry)
     const uint32_t* bitmap;           // GRAM_WORDS words
     unsigned long long* cand;         // candidates: (global line << 32) | byte position
     uint32_t cand_cap;
@@ -222,8 +223,10 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_lines_filter(ScanArgs a) {
                 if (inner) k = upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, p) - 1;
                 const uint32_t g = excl + __popc(nlm & ((1u << i) - 1u)) + k;
                 const bool cr = p > a.log_off[k] && a.text[p - 1] == '\r';
-                a.line_end[g] = (uint32_t)(p - (cr ? 1 : 0));
-                a.line_start[g + 1] = (uint32_t)(p + 1);
+                if (g + 1 < a.line_cap) {
+                    a.line_end[g] = (uint32_t)(p - (cr ? 1 : 0));
+                    a.line_start[g + 1] = (uint32_t)(p + 1);
+                } else atomicOr(&a.ctr->overflow, 64u);
             }
             // ---- log boundary events (start of log k / end of log k-1) falling in this thread's 16 bytes
             if (events && pos <= a.len) {
@@ -231,9 +234,11 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_lines_filter(ScanArgs a) {
                 while (j <= a.n_logs && a.log_off[j] < pos + 16) {
                     const uint64_t b = a.log_off[j];
                     const uint32_t nlb = excl + __popc(nlm & ((1u << (uint32_t)(b - pos)) - 1u));
-                    if (j < a.n_logs) { a.line_start[nlb + j] = (uint32_t)b; }
                     a.first_line[j] = nlb + j;
-                    if (j > 0) a.line_end[nlb + j - 1] = (uint32_t)b;
+                    if (nlb + j < a.line_cap) {
+                        if (j < a.n_logs) { a.line_start[nlb + j] = (uint32_t)b; }
+                        if (j > 0) a.line_end[nlb + j - 1] = (uint32_t)b;
+                    } else atomicOr(&a.ctr->overflow, 64u);
                     ++j;
                 }
             }
@@ -294,11 +299,12 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_lines_filter(ScanArgs a) {
 
 // Java's Pattern.split(…, 0) drops trailing empty strings; no separator at all keeps [input].
 __global__ void k_log_meta(const uint32_t* __restrict__ first_line, const uint32_t* __restrict__ line_start,
-                           const uint32_t* __restrict__ line_end, uint32_t n_logs, uint32_t* __restrict__ n_lines) {
+                           const uint32_t* __restrict__ line_end, uint32_t n_logs, uint32_t line_cap, uint32_t* __restrict__ n_lines) {
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n_logs) return;
     const uint32_t f = first_line[k];
     uint32_t n = first_line[k + 1] - f;
+    if (first_line[k + 1] > line_cap) { n_lines[k] = 0; return; }     // line arrays overflowed: the call is retried
     if (n > 1) {
         while (n > 0 && line_end[f + n - 1] == line_start[f + n - 1]) --n;
     }
@@ -350,7 +356,7 @@ __device__ bool dfa_walk(const DevPlan& P, uint32_t r, const uint8_t* __restrict
     return st == 1;
 }
 
-__device__ __forceinline__ void emit_record(Counters* ctr, unsigned long long* recs, uint32_t cap, bool hit, uint32_t r, uint32_t g) {
+__device__ __forceinline__ void emit_record(Counters* ctr, unsigned long long* recs, uint32_t cap, uint32_t gb, bool hit, uint32_t r, uint32_t g) {
     const unsigned mask = 0xffffffffu;   // callers keep all 32 lanes in the loop
     const unsigned votes = __ballot_sync(mask, hit);
     if (!votes) return;
@@ -361,7 +367,7 @@ __device__ __forceinline__ void emit_record(Counters* ctr, unsigned long long* r
     base = __shfl_sync(mask, base, leader);
     if (hit) {
         const uint32_t idx = base + __popc(votes & ((1u << lane) - 1u));
-        if (idx < cap) recs[idx] = ((unsigned long long)r << 32) | g;
+        if (idx < cap) recs[idx] = ((unsigned long long)r << gb) | g;
         else atomicOr(&ctr->overflow, 4u);
     }
 }
@@ -389,6 +395,7 @@ __global__ void __launch_bounds__(256) k_confirm(ConfirmArgs a, DevPlan P) {
     for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < n; c += gridDim.x * blockDim.x) {
         const unsigned long long cd = a.cand[c];
         const uint32_t pos = (uint32_t)cd, g = (uint32_t)(cd >> 32);
+        if (g >= a.n_lines_total) continue;      // beyond the (under-estimated) line arrays: the call is re-run
         uint32_t w = 0;
 #pragma unroll
         for (int i = 0; i < 4; ++i) if ((uint64_t)pos + i < a.len) w |= (uint32_t)a.text[pos + i] << (8 * i);
@@ -430,7 +437,7 @@ __global__ void __launch_bounds__(256) k_confirm(ConfirmArgs a, DevPlan P) {
                     if (hit && (mode & 4u)) hit = dev_word(a.text[e2 - 1]) != (e2 < le && dev_word(a.text[e2]));
                     if (hit) {
                         const uint32_t idx = atomicAdd(&a.ctr->n_recs, 1u);
-                        if (idx < a.rec_cap) a.recs[idx] = ((unsigned long long)r << 32) | g;
+                        if (idx < a.rec_cap) a.recs[idx] = ((unsigned long long)r << P.gb) | g;
                         else atomicOr(&a.ctr->overflow, 4u);
                     }
                     continue;
@@ -484,11 +491,12 @@ __global__ void __launch_bounds__(256) k_verify(VerifyArgs a, DevPlan P) {
             g = (uint32_t)task;
             if (P.rx_kind[r] == 0) hit = dfa_walk(P, r, a.text, a.len, a.line_start[g], a.line_end[g]);
         }
-        emit_record(a.ctr, a.recs, a.rec_cap, hit, r, g);
+        emit_record(a.ctr, a.recs, a.rec_cap, P.gb, hit, r, g);
     }
 }
 // regexes without a usable literal: every (untrimmed) line is a candidate
 __global__ void __launch_bounds__(256) k_verify_always(VerifyArgs a, DevPlan P) {
+    a.n_lines_total = min(a.ctr->n_lines_total, a.n_lines_total);     // host passes the capacity
     const uint32_t stride = gridDim.x * blockDim.x;
     const uint32_t rounds = (a.n_lines_total + stride - 1) / stride;
     uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
@@ -504,7 +512,7 @@ __global__ void __launch_bounds__(256) k_verify_always(VerifyArgs a, DevPlan P) 
             const uint32_t r = P.always_list[q];
             bool hit = false;
             if (live && P.rx_kind[r] == 0) hit = dfa_walk(P, r, a.text, a.len, ls, le);
-            emit_record(a.ctr, a.recs, a.rec_cap, hit, r, g);
+            emit_record(a.ctr, a.recs, a.rec_cap, P.gb, hit, r, g);
         }
     }
 }
@@ -536,10 +544,11 @@ __global__ void __launch_bounds__(128) k_verify_vm(VerifyArgs a, DevPlan P) {
             g = (uint32_t)task;
             hit = vm_eval(P, r, a.text, a.line_start[g], a.line_end[g], stack, a.ctr);
         }
-        emit_record(a.ctr, a.recs, a.rec_cap, hit, r, g);
+        emit_record(a.ctr, a.recs, a.rec_cap, P.gb, hit, r, g);
     }
 }
 __global__ void __launch_bounds__(128) k_verify_vm_always(VerifyArgs a, DevPlan P) {
+    a.n_lines_total = min(a.ctr->n_lines_total, a.n_lines_total);
     const uint32_t stride = gridDim.x * blockDim.x;
     const uint32_t rounds = (a.n_lines_total + stride - 1) / stride;
     uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
@@ -555,7 +564,7 @@ __global__ void __launch_bounds__(128) k_verify_vm_always(VerifyArgs a, DevPlan 
         for (uint32_t q = 0; q < P.n_always_vm; ++q) {
             const uint32_t r = P.always_vm_list[q];
             const bool hit = live && vm_eval(P, r, a.text, ls, le, stack, a.ctr);
-            emit_record(a.ctr, a.recs, a.rec_cap, hit, r, g);
+            emit_record(a.ctr, a.recs, a.rec_cap, P.gb, hit, r, g);
         }
     }
 }
@@ -587,6 +596,7 @@ struct DfaScanArgs {
     int write_flags;
     unsigned long long* recs;
     uint32_t rec_cap;
+    uint32_t gb;
     Counters* ctr;
 };
 
@@ -632,7 +642,8 @@ __global__ void __launch_bounds__(DS_THREADS) k_dfa_scan(DfaScanArgs a) {
     }
 
     const uint32_t stride = gridDim.x * DS_THREADS;
-    for (uint32_t g = blockIdx.x * DS_THREADS + threadIdx.x; g < a.n_lines_total; g += stride) {
+    const uint32_t n_total = min(a.ctr->n_lines_total, a.n_lines_total);     // host passes the capacity
+    for (uint32_t g = blockIdx.x * DS_THREADS + threadIdx.x; g < n_total; g += stride) {
         const uint32_t k = a.n_logs == 1 ? 0 : upper_bound_dev<uint32_t>(a.first_line, a.n_logs + 1, g) - 1;
         const bool live = k < a.n_logs && g - a.first_line[k] < a.n_lines[k];
         uint32_t flags = 0;
@@ -685,7 +696,7 @@ __global__ void __launch_bounds__(DS_THREADS) k_dfa_scan(DfaScanArgs a) {
                     const uint32_t r = rxs[__ffs(pend) - 1];
                     pend &= pend - 1;
                     const uint32_t idx = atomicAdd(&a.ctr->n_recs, 1u);
-                    if (idx < a.rec_cap) a.recs[idx] = ((unsigned long long)r << 32) | g;
+                    if (idx < a.rec_cap) a.recs[idx] = ((unsigned long long)r << a.gb) | g;
                     else atomicOr(&a.ctr->overflow, 4u);
                 }
             }
@@ -695,65 +706,72 @@ __global__ void __launch_bounds__(DS_THREADS) k_dfa_scan(DfaScanArgs a) {
 }
 
 // ------------------------------------------------------------------ record post-processing
-__global__ void k_rx_bounds(const unsigned long long* __restrict__ keys, uint32_t n, uint32_t n_rx, uint32_t* __restrict__ rx_begin) {
+__global__ void k_rx_bounds(const unsigned long long* __restrict__ keys, const Counters* ctr, uint32_t n_rx, uint32_t gb, uint32_t* __restrict__ rx_begin) {
     uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
     if (r > n_rx) return;
-    rx_begin[r] = lower_bound_dev<unsigned long long>(keys, n, (unsigned long long)r << 32);
+    const uint32_t n = ctr->n_unique;
+    rx_begin[r] = lower_bound_dev<unsigned long long>(keys, n, (unsigned long long)r << gb);
 }
-__global__ void k_ctx_flags(const unsigned long long* __restrict__ keys, const uint32_t* __restrict__ rx_begin, uint32_t* __restrict__ flags32) {
+__global__ void k_ctx_flags(const unsigned long long* __restrict__ keys, const uint32_t* __restrict__ rx_begin, uint32_t gb, uint32_t* __restrict__ flags32) {
     const uint32_t n = rx_begin[4];
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const unsigned long long k = keys[i];
-        const uint32_t r = (uint32_t)(k >> 32), g = (uint32_t)k;
+        const uint32_t r = (uint32_t)(k >> gb), g = (uint32_t)(k & ((1ull << gb) - 1ull));
         atomicOr(&flags32[g >> 2], (1u << r) << ((g & 3) * 8));
     }
 }
-__global__ void k_emit_events(const unsigned long long* __restrict__ keys, uint32_t n, DevPlan P,
+__global__ void k_emit_events(const unsigned long long* __restrict__ keys, DevPlan P,
                               unsigned long long* __restrict__ ev_key, uint32_t ev_cap, Counters* ctr) {
+    const uint32_t n = ctr->n_unique;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const unsigned long long k = keys[i];
-        const uint32_t r = (uint32_t)(k >> 32), g = (uint32_t)k;
+        const uint32_t r = (uint32_t)min(k >> P.gb, 0xFFFFFFFFull), g = (uint32_t)(k & ((1ull << P.gb) - 1ull));
+        if (r >= P.n_rx) continue;     // padding sentinel
         const uint32_t pb = P.rxp_begin[r], pe = P.rxp_begin[r + 1];
         if (pb == pe) continue;
         const uint32_t base = atomicAdd(&ctr->n_events, pe - pb);
         for (uint32_t j = pb; j < pe; ++j) {
             const uint32_t idx = base + (j - pb);
-            if (idx < ev_cap) ev_key[idx] = ((unsigned long long)g << 32) | P.rxp_pat[j];
+            if (idx < ev_cap) ev_key[idx] = ((unsigned long long)g << P.pb) | P.rxp_pat[j];
             else atomicOr(&ctr->overflow, 8u);
         }
     }
 }
-__global__ void k_event_prep(const unsigned long long* __restrict__ ev_key, uint32_t m, DevPlan P,
-                             const uint32_t* __restrict__ first_line, uint32_t n_logs,
+__global__ void k_event_prep(const unsigned long long* __restrict__ ev_key, const Counters* ctr, uint32_t m_cap, DevPlan P,
+                             const uint32_t* __restrict__ first_line, uint32_t n_logs, uint32_t n_slots,
                              uint32_t* __restrict__ ev_log, uint32_t* __restrict__ slot_key, uint32_t* __restrict__ ev_idx,
                              unsigned long long* __restrict__ freq_delta) {
     uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= m) return;
+    if (e >= m_cap) return;
+    if (e >= ctr->n_events) { ev_log[e] = n_logs; slot_key[e] = n_slots; ev_idx[e] = e; return; }   // padding
     const unsigned long long k = ev_key[e];
-    const uint32_t g = (uint32_t)(k >> 32), p = (uint32_t)k;
+    const uint32_t g = (uint32_t)(k >> P.pb), p = (uint32_t)(k & ((1ull << P.pb) - 1ull));
     ev_log[e] = n_logs == 1 ? 0 : upper_bound_dev<uint32_t>(first_line, n_logs + 1, g) - 1;
-    slot_key[e] = (uint32_t)P.pat_slot[p];
+    slot_key[e] = P.pat_slot[p] < 0 ? n_slots : (uint32_t)P.pat_slot[p];     // untracked patterns sort after every slot
     ev_idx[e] = e;
     atomicAdd(&freq_delta[p], 1ull);
 }
-__global__ void k_slot_rank(const uint32_t* __restrict__ sorted_slot, const uint32_t* __restrict__ sorted_idx, uint32_t m,
+__global__ void k_slot_rank(const uint32_t* __restrict__ sorted_slot, const uint32_t* __restrict__ sorted_idx, uint32_t m, uint32_t n_slots,
                             uint32_t* __restrict__ rank_in_slot) {
     uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= m) return;
     const uint32_t s = sorted_slot[j];
+    if (s >= n_slots) { rank_in_slot[sorted_idx[j]] = 0; return; }   // untracked pattern or padding
     rank_in_slot[sorted_idx[j]] = j - lower_bound_dev<uint32_t>(sorted_slot, m, s);
 }
-__global__ void k_log_event_begin(const unsigned long long* __restrict__ ev_key, uint32_t m, const uint32_t* __restrict__ first_line,
-                                  uint32_t n_logs, unsigned long long* __restrict__ begin) {
+__global__ void k_log_event_begin(const unsigned long long* __restrict__ ev_key, const Counters* ctr, const uint32_t* __restrict__ first_line,
+                                  uint32_t n_logs, uint32_t pb, unsigned long long* __restrict__ begin) {
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k > n_logs) return;
-    begin[k] = lower_bound_dev<unsigned long long>(ev_key, m, (unsigned long long)first_line[k] << 32);
+    const uint32_t m = ctr->n_events;
+    begin[k] = lower_bound_dev<unsigned long long>(ev_key, m, (unsigned long long)first_line[k] << pb);
 }
 
 // ------------------------------------------------------------------ K5: scoring (fp64, no contraction)
 struct ScoreArgs {
     const unsigned long long* ev_key;
-    uint32_t m;
+    uint32_t m_cap;                        // threads launched; the live count comes from ctr->n_events
+    const Counters* ctr;
     const uint32_t* ev_log;
     const uint32_t* rank_in_slot;
     const unsigned long long* prior;      // [n_pat] in-window counts at call start (+ lower ranks), may be null
@@ -769,18 +787,20 @@ struct ScoreArgs {
     unsigned long long* sort_key;         // descending-score key for ranking
 };
 
-__device__ __forceinline__ bool list_any_in(const unsigned long long* __restrict__ keys, uint32_t b, uint32_t e, uint32_t r,
+__device__ __forceinline__ bool list_any_in(const unsigned long long* __restrict__ keys, uint32_t b, uint32_t e, uint32_t r, uint32_t gb,
                                             uint32_t lo, uint32_t hi /* [lo,hi) global lines */) {
     if (lo >= hi) return false;
-    const uint32_t i = b + lower_bound_dev<unsigned long long>(keys + b, e - b, ((unsigned long long)r << 32) | lo);
-    return i < e && (uint32_t)keys[i] < hi;
+    const uint32_t i = b + lower_bound_dev<unsigned long long>(keys + b, e - b, ((unsigned long long)r << gb) | lo);
+    return i < e && (uint32_t)(keys[i] & ((1ull << gb) - 1ull)) < hi;
 }
 
 __global__ void __launch_bounds__(128) k_score(ScoreArgs a, DevPlan P, ScoreCfg C) {
     const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= a.m) return;
+    if (e >= a.m_cap) return;
+    if (e >= a.ctr->n_events) { a.sort_key[e] = ~0ull; return; }      // padding sorts last
     const unsigned long long ek = a.ev_key[e];
-    const uint32_t g = (uint32_t)(ek >> 32), p = (uint32_t)ek;
+    const uint32_t g = (uint32_t)(ek >> P.pb), p = (uint32_t)(ek & ((1ull << P.pb) - 1ull));
+    const unsigned long long gmask = (1ull << P.gb) - 1ull;
     const uint32_t k = a.ev_log[e];
     const uint32_t first = a.first_line[k];
     const long long N = a.n_lines[k];
@@ -816,17 +836,17 @@ __global__ void __launch_bounds__(128) k_score(ScoreArgs a, DevPlan P, ScoreCfg 
                 const uint32_t b = a.rx_begin[r], en = a.rx_begin[r + 1];
                 const unsigned long long* kk = a.keys + b;
                 const uint32_t cnt = en - b;
-                const unsigned long long self = ((unsigned long long)r << 32) | g;
+                const unsigned long long self = ((unsigned long long)r << P.gb) | g;
                 const uint32_t at = lower_bound_dev<unsigned long long>(kk, cnt, self);
                 long long best = -1;
                 if (at > 0) {
-                    const long long l = (long long)(uint32_t)kk[at - 1] - first;
+                    const long long l = (long long)(uint32_t)(kk[at - 1] & gmask) - first;
                     if (l >= lo) best = i - l;
                 }
                 uint32_t nx = at;
                 if (nx < cnt && kk[nx] == self) ++nx;
                 if (nx < cnt) {
-                    const long long l = (long long)(uint32_t)kk[nx] - first;
+                    const long long l = (long long)(uint32_t)(kk[nx] & gmask) - first;
                     if (l < hi) { const long long d = l - i; if (best < 0 || d < best) best = d; }
                 }
                 if (best >= 0) total = __dadd_rn(total, __dmul_rn(P.sec_weight[s], C.decay_lut[best]));
@@ -846,16 +866,16 @@ __global__ void __launch_bounds__(128) k_score(ScoreArgs a, DevPlan P, ScoreCfg 
                 if (eb == ee) continue;                                  // SS:233-235
                 const uint32_t rl = P.ev_rx[ee - 1];
                 const long long nlo = max(0ll, i - 5), nhi = min(N, i + 6);  // SS:275-277
-                if (!list_any_in(a.keys, a.rx_begin[rl], a.rx_begin[rl + 1], rl, first + (uint32_t)nlo, first + (uint32_t)nhi)) continue;
+                if (!list_any_in(a.keys, a.rx_begin[rl], a.rx_begin[rl + 1], rl, P.gb, first + (uint32_t)nlo, first + (uint32_t)nhi)) continue;
                 bool ok = true;
                 long long T = -1;   // local line of the earliest feasible position of the previous event
                 for (uint32_t j = eb; j + 1 < ee && ok; ++j) {
                     const uint32_t r = P.ev_rx[j];
                     const uint32_t b = a.rx_begin[r], en = a.rx_begin[r + 1];
-                    const unsigned long long want = ((unsigned long long)r << 32) | (uint32_t)(first + T + 1);
+                    const unsigned long long want = ((unsigned long long)r << P.gb) | (uint32_t)(first + T + 1);
                     const uint32_t at = b + lower_bound_dev<unsigned long long>(a.keys + b, en - b, want);
                     if (at >= en) { ok = false; break; }
-                    const long long l = (long long)(uint32_t)a.keys[at] - first;
+                    const long long l = (long long)(uint32_t)(a.keys[at] & gmask) - first;
                     if (l >= i) { ok = false; break; }     // must end strictly before the primary line
                     T = l;
                 }
@@ -922,9 +942,9 @@ __global__ void __launch_bounds__(128) k_score(ScoreArgs a, DevPlan P, ScoreCfg 
     a.sort_key[e] = ~bits;
 }
 __global__ void k_write_rank(const uint32_t* __restrict__ order, const uint32_t* __restrict__ ev_log,
-                             const unsigned long long* __restrict__ log_begin, uint32_t m, uint32_t* __restrict__ rank) {
+                             const unsigned long long* __restrict__ log_begin, const Counters* ctr, uint32_t* __restrict__ rank) {
     uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= m) return;
+    if (j >= ctr->n_events) return;
     const uint32_t e = order[j];
     rank[e] = j - (uint32_t)log_begin[ev_log[e]];
 }
@@ -932,9 +952,11 @@ __global__ void k_gather_u32(const uint32_t* __restrict__ src, const uint32_t* _
     uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j < n) dst[j] = src[idx[j]];
 }
-__global__ void k_count_per_pattern(const unsigned long long* __restrict__ keys, uint32_t n, DevPlan P, unsigned long long* __restrict__ counts) {
+__global__ void k_count_per_pattern(const unsigned long long* __restrict__ keys, const Counters* ctr, DevPlan P, unsigned long long* __restrict__ counts) {
+    const uint32_t n = ctr->n_unique;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const uint32_t r = (uint32_t)(keys[i] >> 32);
+        const uint32_t r = (uint32_t)min(keys[i] >> P.gb, 0xFFFFFFFFull);
+        if (r >= P.n_rx) continue;
         for (uint32_t j = P.rxp_begin[r]; j < P.rxp_begin[r + 1]; ++j) atomicAdd(&counts[P.rxp_pat[j]], 1ull);
     }
 }
@@ -974,6 +996,20 @@ struct DevBuf {
     }
     void release() { if (p) cudaFree(p); p = nullptr; cap = 0; }
     template <class T> T* as() const { return static_cast<T*>(p); }
+};
+
+struct PinnedBuf {      // grow-only page-locked host staging: device->host copies into it are truly asynchronous
+    uint8_t* p = nullptr;
+    size_t cap = 0;
+    void ensure(size_t n) {
+        if (n <= cap) return;
+        if (p) cudaFreeHost(p);
+        p = nullptr; cap = 0;
+        size_t want = std::max<size_t>(n + n / 2, 1 << 16);
+        CK(cudaMallocHost(reinterpret_cast<void**>(&p), want));
+        cap = want;
+    }
+    void release() { if (p) cudaFreeHost(p); p = nullptr; cap = 0; }
 };
 
 template <class T>
@@ -1022,7 +1058,9 @@ struct lp_ctx {
     DevBuf ev_key, ev_key_alt, ev_log, slot_key, slot_key_alt, ev_idx, ev_idx_alt, rank_in_slot, freq_delta, prior;
     DevBuf out_line, out_pat, out_score, out_factors, sort_key, sort_key_alt, order, order_alt, log_sorted, log_sorted_alt;
     DevBuf rank, log_event_begin, n_unique;
-    size_t cand_cap = 0, task_cap = 0, vm_task_cap = 0;
+    PinnedBuf stage;
+    size_t est_lines = 0, est_cand = 0, est_tasks = 0, est_vm_tasks = 0, est_recs = 0, est_events = 0;
+    int retries = 0;
 
     // scan-phase state kept for the two-phase batch API
     struct Pending {
@@ -1033,7 +1071,7 @@ struct lp_ctx {
         int options = 0;
     } pend;
 
-    cudaEvent_t ev[8]{};
+    cudaEvent_t ev[9]{};
     lp_timings tm{};
     uint64_t launches = 0;
 };
@@ -1160,7 +1198,44 @@ void sort_pairs(lp_ctx* c, K* kin, K* kout, V* vin, V* vout, uint32_t n, int end
 }
 int bits_for(uint64_t v) { int b = 1; while (b < 64 && (v >> b)) ++b; return b; }
 
-// ---- phase 1: split + prefilter + verify + unique records; leaves state in ctx->pend
+// ---- optimistic capacities -------------------------------------------------------------------
+// Every queue and output of the pipeline is sized from what earlier calls on this context needed
+// (first call: from the log size), kernels take their live counts from device-side counters, and
+// padding slots hold all-ones sentinels that sort last. The host therefore synchronises once per
+// call; a call whose real counts exceed an estimate is detected at that point and simply re-run
+// with larger buffers (first calls on a context, or a log unlike its predecessors).
+struct Retry {};
+
+void bump(size_t& est, uint64_t observed) { est = std::max<size_t>(est, (size_t)(observed + observed / 4 + 1024)); }
+
+void check_estimates(lp_ctx* c, const Counters& h, uint32_t n_logs, bool events_too) {
+    bool retry = false;
+    const uint64_t G = (uint64_t)h.total_nl + n_logs;
+    if (G >= 0xFFFFFFF0ull) throw LimitFail("too many lines");
+    if (h.overflow & 16u) throw std::overflow_error("backtracking verifier exceeded its step/stack budget");
+    if (G + 1 > c->est_lines) { bump(c->est_lines, G + 1); retry = true; }
+    if (h.n_cand > c->est_cand) { bump(c->est_cand, h.n_cand); retry = true; }
+    if (h.n_tasks > c->est_tasks) { bump(c->est_tasks, h.n_tasks); retry = true; }
+    if (h.n_vm_tasks > c->est_vm_tasks) { bump(c->est_vm_tasks, h.n_vm_tasks); retry = true; }
+    if (h.n_recs > c->est_recs) { bump(c->est_recs, h.n_recs); retry = true; }
+    if (events_too && h.n_events > c->est_events) { bump(c->est_events, h.n_events); retry = true; }
+    if (!retry && (h.overflow & ~16u)) {   // a flag without a matching count: grow everything once
+        c->est_cand *= 2; c->est_tasks *= 2; c->est_recs *= 2; c->est_events *= 2; c->est_vm_tasks *= 2;
+        retry = true;
+    }
+    if (retry) {
+        if (++c->retries > 12) throw LimitFail("queues keep overflowing");
+        throw Retry();
+    }
+    c->retries = 0;
+    // remember what this log needed (with headroom) for the next call
+    bump(c->est_lines, G + 1); bump(c->est_cand, h.n_cand); bump(c->est_tasks, h.n_tasks);
+    bump(c->est_vm_tasks, h.n_vm_tasks); bump(c->est_recs, h.n_recs);
+    if (events_too) bump(c->est_events, h.n_events);
+}
+
+// ---- phase 1: split + prefilter + verify + sorted unique records + events in discovery order.
+// Launches only; the caller synchronises.
 void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_off, uint32_t n_logs, int options) {
     if (!c->loaded) throw std::invalid_argument("lp_load_patterns has not been called");
     if (len >= 0xFFFFFFF0ull) throw LimitFail("log/batch larger than 4 GiB - 16 bytes; shard it (see DESIGN.md)");
@@ -1173,304 +1248,287 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     c->launches = 0;
     c->tm = lp_timings();
 
-    const uint32_t n_tiles = (uint32_t)((len + 1 + TILE_BYTES - 1) / TILE_BYTES);   // covers position `len` too
-    c->log_off.ensure((n_logs + 1) * sizeof(uint64_t));
-    CK(cudaMemcpyAsync(c->log_off.p, h_off, (n_logs + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
-    c->tile_counts.ensure((size_t)n_tiles * 4);
-    c->counters.ensure(sizeof(Counters));
-    CK(cudaMemsetAsync(c->counters.p, 0, sizeof(Counters), st));
-    Counters* ctr = c->counters.as<Counters>();
-
-    CK(cudaEventRecord(c->ev[0], st));
-    k_count_nl<<<std::min<uint32_t>(n_tiles, c->n_sm * 16), SCAN_THREADS, 0, st>>>(d_text, len, n_tiles, c->tile_counts.as<uint32_t>());
-    k_scan_tiles<<<1, 1024, 0, st>>>(c->tile_counts.as<uint32_t>(), n_tiles, ctr);
-    c->launches += 2;
-    Counters h{};
-    CK(cudaMemcpyAsync(&h, ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
-    const uint64_t G64 = h.total_nl + n_logs;
-    if (G64 >= 0xFFFFFFF0ull) throw LimitFail("too many lines");
-    const uint32_t G = (uint32_t)G64;
-
-    c->line_start.ensure((size_t)(G + 1) * 4);
-    c->line_end.ensure((size_t)(G + 1) * 4);
-    c->first_line.ensure((size_t)(n_logs + 1) * 4);
-    c->n_lines.ensure((size_t)n_logs * 4);
-    c->ctx_flags.ensure(((size_t)G / 4 + 2) * 4);
-    if (!c->plan.ctx_any_in_groups) CK(cudaMemsetAsync(c->ctx_flags.p, 0, ((size_t)G / 4 + 2) * 4, st));   // else k_dfa_scan writes every byte
     const bool use_filter = !c->plan.lit_off.empty();
     if (use_filter && !c->calibrated && len >= 4096) calibrate_filter(c, d_text, len);
     const uint32_t n_always = (uint32_t)c->plan.always_list.size();
     const uint32_t n_always_vm = (uint32_t)c->plan.always_vm_list.size();
     const bool has_vm = c->plan.n_vm > 0;
     const uint32_t vm_grid = (uint32_t)c->n_sm * 2, vm_block = 128;
-    if (has_vm) c->vm_stack.ensure((size_t)vm_grid * vm_block * lpx::VM_STACK_WORDS * 4);
 
-    for (int attempt = 0;; ++attempt) {
-        if (c->cand_cap == 0) c->cand_cap = std::max<size_t>(1u << 16, len / 8);
-        if (c->task_cap == 0) c->task_cap = std::max<size_t>(1u << 16, len / 8);
-        c->cand.ensure(c->cand_cap * 8);
-        c->tasks.ensure(c->task_cap * 8);
-        if (has_vm) {
-            if (c->vm_task_cap == 0) c->vm_task_cap = std::max<size_t>(1u << 14, len / 64);
-            c->vm_tasks.ensure(c->vm_task_cap * 8);
-        }
-        const size_t rec_cap = c->task_cap + c->cand_cap + (has_vm ? c->vm_task_cap : 0) + (size_t)G * (n_always + n_always_vm) +
-                               (c->n_group_record_rx ? std::max<size_t>(1u << 16, (size_t)G / 4 * c->n_group_record_rx) : 0) + 16;
-        if (rec_cap >= 0x7FFFFFFFull) throw LimitFail("record capacity exceeds 2^31; shard the batch");
-        c->recs.ensure(rec_cap * 8);
-        c->recs_alt.ensure(rec_cap * 8);
-
-        CK(cudaMemsetAsync(&ctr->n_cand, 0, sizeof(Counters) - offsetof(Counters, n_cand), st));
-        ScanArgs sa{};
-        sa.text = d_text; sa.len = len; sa.n_tiles = n_tiles; sa.tile_prefix = c->tile_counts.as<uint32_t>();
-        sa.log_off = c->log_off.as<uint64_t>(); sa.n_logs = n_logs;
-        sa.line_start = c->line_start.as<uint32_t>(); sa.line_end = c->line_end.as<uint32_t>();
-        sa.first_line = c->first_line.as<uint32_t>(); sa.bitmap = c->dp.bitmap;
-        sa.cand = c->cand.as<unsigned long long>(); sa.cand_cap = (uint32_t)std::min<size_t>(c->cand_cap, 0xFFFFFFFFu);
-        sa.ctr = ctr; sa.use_filter = use_filter ? 1 : 0;
-        const size_t smem = use_filter ? GRAM_WORDS * 4 : 0;
-        const uint32_t grid = std::min<uint32_t>(n_tiles, (uint32_t)c->n_sm * 3);
-        CK(cudaEventRecord(c->ev[1], st));
-        k_lines_filter<<<grid, SCAN_THREADS, smem, st>>>(sa);
-        CK(cudaEventRecord(c->ev[2], st));
-        k_log_meta<<<blocks_for(n_logs, 128), 128, 0, st>>>(c->first_line.as<uint32_t>(), c->line_start.as<uint32_t>(),
-                                                             c->line_end.as<uint32_t>(), n_logs, c->n_lines.as<uint32_t>());
-        c->launches += 2;
-
-        VerifyArgs va{};
-        va.text = d_text; va.len = len; va.line_start = c->line_start.as<uint32_t>(); va.line_end = c->line_end.as<uint32_t>();
-        va.tasks = c->tasks.as<unsigned long long>(); va.task_cap = (uint32_t)std::min<size_t>(c->task_cap, 0xFFFFFFFFu); va.recs = c->recs.as<unsigned long long>();
-        va.rec_cap = (uint32_t)rec_cap; va.ctr = ctr; va.n_lines_total = G;
-        va.first_line = c->first_line.as<uint32_t>(); va.n_lines = c->n_lines.as<uint32_t>(); va.n_logs = n_logs;
-        va.vm_tasks = c->vm_tasks.as<unsigned long long>(); va.vm_task_cap = (uint32_t)std::min<size_t>(c->vm_task_cap, 0xFFFFFFFFu);
-        va.vm_stack = c->vm_stack.as<uint32_t>();
-        if (use_filter) {
-            ConfirmArgs ca{};
-            ca.text = d_text; ca.len = len; ca.cand = c->cand.as<unsigned long long>(); ca.cand_cap = sa.cand_cap;
-            ca.line_start = c->line_start.as<uint32_t>(); ca.line_end = c->line_end.as<uint32_t>(); ca.n_lines_total = G;
-            ca.tasks = c->tasks.as<unsigned long long>(); ca.task_cap = (uint32_t)std::min<size_t>(c->task_cap, 0xFFFFFFFFu); ca.ctr = ctr;
-            ca.vm_tasks = c->vm_tasks.as<unsigned long long>(); ca.vm_task_cap = va.vm_task_cap;
-            ca.recs = c->recs.as<unsigned long long>(); ca.rec_cap = (uint32_t)rec_cap;
-            k_confirm<<<c->n_sm * 8, 256, 0, st>>>(ca, c->dp);
-            k_verify<<<c->n_sm * 8, 256, 0, st>>>(va, c->dp);
-            c->launches += 2;
-            if (has_vm) { k_verify_vm<<<vm_grid, vm_block, 0, st>>>(va, c->dp); c->launches += 1; }
-        }
-        if (n_always) {
-            k_verify_always<<<std::min<uint32_t>(blocks_for(G, 256), c->n_sm * 8), 256, 0, st>>>(va, c->dp);
-            c->launches += 1;
-        }
-        if (n_always_vm) {
-            k_verify_vm_always<<<vm_grid, vm_block, 0, st>>>(va, c->dp);
-            c->launches += 1;
-        }
-        // always-on product-DFA scan (context regexes + literal-free DFA patterns)
-        CK(cudaEventRecord(c->ev[6], st));
-        for (size_t g0 = 0; g0 < c->d_group_blob.size(); g0 += DS_MAXG) {
-            DfaScanArgs da{};
-            da.text = d_text; da.len = len;
-            da.line_start = c->line_start.as<uint32_t>(); da.line_end = c->line_end.as<uint32_t>(); da.n_lines_total = G;
-            da.first_line = c->first_line.as<uint32_t>(); da.n_lines = c->n_lines.as<uint32_t>(); da.n_logs = n_logs;
-            size_t tab_bytes = 0;
-            da.n_groups = (uint32_t)std::min<size_t>(DS_MAXG, c->d_group_blob.size() - g0);
-            for (uint32_t q = 0; q < da.n_groups; ++q) {
-                da.blob[q] = c->d_group_blob[g0 + q]; da.blob_words[q] = c->group_words[g0 + q];
-                tab_bytes += ((size_t)c->group_words[g0 + q] + 3) / 4 * 16;
-            }
-            da.rx_record = c->d_rx_record; da.ctx_flags = c->ctx_flags.as<uint8_t>();
-            da.write_flags = (g0 == 0 && c->plan.ctx_any_in_groups) ? 1 : 0;
-            da.recs = c->recs.as<unsigned long long>(); da.rec_cap = (uint32_t)rec_cap; da.ctr = ctr;
-            const uint32_t per_sm = (uint32_t)std::max<size_t>(1, std::min<size_t>(8, (200 * 1024) / std::max<size_t>(tab_bytes, 1)));
-            const uint32_t grid = std::min<uint32_t>(blocks_for(G, DS_THREADS), (uint32_t)c->n_sm * per_sm);
-            switch (da.n_groups) {
-                case 1: k_dfa_scan<1><<<grid, DS_THREADS, tab_bytes, st>>>(da); break;
-                case 2: k_dfa_scan<2><<<grid, DS_THREADS, tab_bytes, st>>>(da); break;
-                case 3: k_dfa_scan<3><<<grid, DS_THREADS, tab_bytes, st>>>(da); break;
-                default: k_dfa_scan<4><<<grid, DS_THREADS, tab_bytes, st>>>(da); break;
-            }
-            c->launches += 1;
-        }
-        CK(cudaEventRecord(c->ev[7], st));
-        CK(cudaEventRecord(c->ev[3], st));
-        CK(cudaMemcpyAsync(&h, ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
-        CK(cudaStreamSynchronize(st));
-        CK(cudaGetLastError());
-        if (h.overflow & 16u) throw std::overflow_error("backtracking verifier exceeded its budget");
-        if (h.overflow == 0) break;
-        if (attempt >= 6) throw LimitFail("candidate queues keep overflowing");
-        if (h.overflow & 1u) c->cand_cap = std::max<size_t>(c->cand_cap * 2, (size_t)h.n_cand + 1024);
-        if (h.overflow & 2u) c->task_cap = std::max<size_t>(c->task_cap * 2, (size_t)h.n_tasks + 1024);
-        if (h.overflow & 4u) c->task_cap = std::max<size_t>(c->task_cap * 2, (size_t)h.n_recs + 1024);
-        if (h.overflow & 32u) c->vm_task_cap = std::max<size_t>(c->vm_task_cap * 2, (size_t)h.n_vm_tasks + 1024);
+    // first-call estimates (later calls reuse what earlier logs needed; an under-estimate costs one re-run)
+    if (c->est_lines == 0) {
+        c->est_lines = (size_t)(len / 64 + n_logs + 4096);
+        c->est_cand = (size_t)(len / 256 + (1u << 16));
+        c->est_tasks = (size_t)(len / 256 + (1u << 16));
+        c->est_vm_tasks = (size_t)(len / 1024 + (1u << 14));
+        c->est_recs = (size_t)(len / 256 + (1u << 16));
+        c->est_events = (size_t)(len / 2048 + (1u << 14));
     }
-    c->tm.candidates = h.n_cand;
-    if (use_filter && (uint64_t)h.n_cand * 2 > (uint64_t)G + 1024 && c->recalibrations < 2) { c->calibrated = false; ++c->recalibrations; }
-    c->tm.verify_tasks = (uint64_t)h.n_tasks + h.n_vm_tasks + (uint64_t)G * (n_always + n_always_vm);
+    c->est_lines = std::max<size_t>(c->est_lines, (size_t)n_logs + 16);
+    const size_t line_cap = c->est_lines;
+    const size_t rec_cap = c->est_recs;
+    if (rec_cap >= 0x7FFFFFFFull || line_cap >= 0xFFFFFFF0ull) throw LimitFail("record capacity exceeds 2^31; shard the batch");
+    const size_t ev_cap = c->est_events;
+    c->dp.gb = (uint32_t)bits_for(line_cap);          // record key = regex << gb | line
+    c->dp.pb = (uint32_t)bits_for(std::max<uint32_t>(c->dp.n_pat, 1));   // event key = line << pb | pattern
 
-    // ---- sort + unique the (regex, line) records
-    uint32_t n_unique = 0;
-    const uint32_t n_recs = h.n_recs;
+    const uint32_t n_tiles = (uint32_t)((len + 1 + TILE_BYTES - 1) / TILE_BYTES);   // covers position `len` too
+    c->log_off.ensure((n_logs + 1) * sizeof(uint64_t));
+    c->tile_counts.ensure((size_t)n_tiles * 4);
+    c->counters.ensure(sizeof(Counters));
+    c->line_start.ensure((line_cap + 1) * 4);
+    c->line_end.ensure((line_cap + 1) * 4);
+    c->first_line.ensure((size_t)(n_logs + 1) * 4);
+    c->n_lines.ensure((size_t)n_logs * 4);
+    c->ctx_flags.ensure((line_cap / 4 + 2) * 4);
+    c->cand.ensure(c->est_cand * 8);
+    c->tasks.ensure(c->est_tasks * 8);
+    if (has_vm) { c->vm_tasks.ensure(c->est_vm_tasks * 8); c->vm_stack.ensure((size_t)vm_grid * vm_block * lpx::VM_STACK_WORDS * 4); }
+    c->recs.ensure(rec_cap * 8);
+    c->recs_alt.ensure(rec_cap * 8);
     c->rx_begin.ensure((size_t)(c->dp.n_rx + 2) * 4);
+    c->ev_key.ensure(ev_cap * 8 + 8);
+    c->ev_key_alt.ensure(ev_cap * 8 + 8);
+    Counters* ctr = c->counters.as<Counters>();
 
-    if (n_recs) {
-        const int kb = 32 + bits_for(c->dp.n_rx);
-        sort_keys<unsigned long long>(c, c->recs.as<unsigned long long>(), c->recs_alt.as<unsigned long long>(), n_recs, kb);
-        c->n_unique.ensure(16);
+    CK(cudaMemcpyAsync(c->log_off.p, h_off, (n_logs + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
+    CK(cudaMemsetAsync(ctr, 0, sizeof(Counters), st));
+    CK(cudaMemsetAsync(c->recs.p, 0xFF, rec_cap * 8, st));            // padding sentinels sort last
+    CK(cudaMemsetAsync(c->ev_key_alt.p, 0xFF, ev_cap * 8, st));
+    if (!c->plan.ctx_any_in_groups) CK(cudaMemsetAsync(c->ctx_flags.p, 0, (line_cap / 4 + 2) * 4, st));   // else k_dfa_scan writes every byte
+
+    CK(cudaEventRecord(c->ev[0], st));
+    k_count_nl<<<std::min<uint32_t>(n_tiles, c->n_sm * 16), SCAN_THREADS, 0, st>>>(d_text, len, n_tiles, c->tile_counts.as<uint32_t>());
+    k_scan_tiles<<<1, 1024, 0, st>>>(c->tile_counts.as<uint32_t>(), n_tiles, n_logs, ctr);
+    ScanArgs sa{};
+    sa.text = d_text; sa.len = len; sa.n_tiles = n_tiles; sa.tile_prefix = c->tile_counts.as<uint32_t>();
+    sa.log_off = c->log_off.as<uint64_t>(); sa.n_logs = n_logs;
+    sa.line_start = c->line_start.as<uint32_t>(); sa.line_end = c->line_end.as<uint32_t>();
+    sa.first_line = c->first_line.as<uint32_t>(); sa.line_cap = (uint32_t)line_cap; sa.bitmap = c->dp.bitmap;
+    sa.cand = c->cand.as<unsigned long long>(); sa.cand_cap = (uint32_t)std::min<size_t>(c->est_cand, 0xFFFFFFFFu);
+    sa.ctr = ctr; sa.use_filter = use_filter ? 1 : 0;
+    const size_t smem = use_filter ? GRAM_WORDS * 4 : 0;
+    CK(cudaEventRecord(c->ev[1], st));
+    k_lines_filter<<<std::min<uint32_t>(n_tiles, (uint32_t)c->n_sm * 3), SCAN_THREADS, smem, st>>>(sa);
+    CK(cudaEventRecord(c->ev[2], st));
+    k_log_meta<<<blocks_for(n_logs, 128), 128, 0, st>>>(c->first_line.as<uint32_t>(), c->line_start.as<uint32_t>(),
+                                                         c->line_end.as<uint32_t>(), n_logs, (uint32_t)line_cap, c->n_lines.as<uint32_t>());
+    c->launches += 4;
+
+    VerifyArgs va{};
+    va.text = d_text; va.len = len; va.line_start = c->line_start.as<uint32_t>(); va.line_end = c->line_end.as<uint32_t>();
+    va.tasks = c->tasks.as<unsigned long long>(); va.task_cap = (uint32_t)std::min<size_t>(c->est_tasks, 0xFFFFFFFFu);
+    va.recs = c->recs.as<unsigned long long>(); va.rec_cap = (uint32_t)rec_cap; va.ctr = ctr; va.n_lines_total = (uint32_t)line_cap;
+    va.first_line = c->first_line.as<uint32_t>(); va.n_lines = c->n_lines.as<uint32_t>(); va.n_logs = n_logs;
+    va.vm_tasks = c->vm_tasks.as<unsigned long long>(); va.vm_task_cap = (uint32_t)std::min<size_t>(c->est_vm_tasks, 0xFFFFFFFFu);
+    va.vm_stack = c->vm_stack.as<uint32_t>();
+    if (use_filter) {
+        ConfirmArgs ca{};
+        ca.text = d_text; ca.len = len; ca.cand = c->cand.as<unsigned long long>(); ca.cand_cap = sa.cand_cap;
+        ca.line_start = c->line_start.as<uint32_t>(); ca.line_end = c->line_end.as<uint32_t>(); ca.n_lines_total = (uint32_t)line_cap;
+        ca.tasks = c->tasks.as<unsigned long long>(); ca.task_cap = va.task_cap; ca.ctr = ctr;
+        ca.vm_tasks = c->vm_tasks.as<unsigned long long>(); ca.vm_task_cap = va.vm_task_cap;
+        ca.recs = c->recs.as<unsigned long long>(); ca.rec_cap = (uint32_t)rec_cap;
+        k_confirm<<<c->n_sm * 8, 256, 0, st>>>(ca, c->dp);
+        k_verify<<<c->n_sm * 8, 256, 0, st>>>(va, c->dp);
+        c->launches += 2;
+        if (has_vm) { k_verify_vm<<<vm_grid, vm_block, 0, st>>>(va, c->dp); c->launches += 1; }
+    }
+    if (n_always) { k_verify_always<<<std::min<uint32_t>(blocks_for(line_cap, 256), c->n_sm * 8), 256, 0, st>>>(va, c->dp); c->launches += 1; }
+    if (n_always_vm) { k_verify_vm_always<<<vm_grid, vm_block, 0, st>>>(va, c->dp); c->launches += 1; }
+    // always-on product-DFA scan (context regexes + literal-free DFA patterns)
+    CK(cudaEventRecord(c->ev[6], st));
+    for (size_t g0 = 0; g0 < c->d_group_blob.size(); g0 += DS_MAXG) {
+        DfaScanArgs da{};
+        da.text = d_text; da.len = len;
+        da.line_start = c->line_start.as<uint32_t>(); da.line_end = c->line_end.as<uint32_t>(); da.n_lines_total = (uint32_t)line_cap;
+        da.first_line = c->first_line.as<uint32_t>(); da.n_lines = c->n_lines.as<uint32_t>(); da.n_logs = n_logs;
+        size_t tab_bytes = 0;
+        da.n_groups = (uint32_t)std::min<size_t>(DS_MAXG, c->d_group_blob.size() - g0);
+        for (uint32_t q = 0; q < da.n_groups; ++q) {
+            da.blob[q] = c->d_group_blob[g0 + q]; da.blob_words[q] = c->group_words[g0 + q];
+            tab_bytes += ((size_t)c->group_words[g0 + q] + 3) / 4 * 16;
+        }
+        da.rx_record = c->d_rx_record; da.ctx_flags = c->ctx_flags.as<uint8_t>();
+        da.write_flags = (g0 == 0 && c->plan.ctx_any_in_groups) ? 1 : 0;
+        da.recs = c->recs.as<unsigned long long>(); da.rec_cap = (uint32_t)rec_cap; da.gb = c->dp.gb; da.ctr = ctr;
+        const uint32_t per_sm = (uint32_t)std::max<size_t>(1, std::min<size_t>(8, (200 * 1024) / std::max<size_t>(tab_bytes, 1)));
+        const uint32_t grid = std::min<uint32_t>(blocks_for(line_cap, DS_THREADS), (uint32_t)c->n_sm * per_sm);
+        switch (da.n_groups) {
+            case 1: k_dfa_scan<1><<<grid, DS_THREADS, tab_bytes, st>>>(da); break;
+            case 2: k_dfa_scan<2><<<grid, DS_THREADS, tab_bytes, st>>>(da); break;
+            case 3: k_dfa_scan<3><<<grid, DS_THREADS, tab_bytes, st>>>(da); break;
+            default: k_dfa_scan<4><<<grid, DS_THREADS, tab_bytes, st>>>(da); break;
+        }
+        c->launches += 1;
+    }
+    CK(cudaEventRecord(c->ev[7], st));
+    CK(cudaEventRecord(c->ev[3], st));
+
+    // ---- sort + unique the (regex, line) records; rec_cap slots are sorted, unused ones are sentinels
+    {
+        const int kb = 64;   // sentinels are all-ones: sort the full key
+        (void)kb;
+        sort_keys<unsigned long long>(c, c->recs.as<unsigned long long>(), c->recs_alt.as<unsigned long long>(), (uint32_t)rec_cap,
+                                      std::min<int>(64, (int)c->dp.gb + bits_for(c->dp.n_rx) + 1));
         size_t tmp = 0;
         cub::DeviceSelect::Unique(nullptr, tmp, c->recs_alt.as<unsigned long long>(), c->recs.as<unsigned long long>(),
-                                  c->n_unique.as<uint32_t>(), (int)n_recs, st);
+                                  &ctr->n_unique, (int)rec_cap, st);
         c->cub_tmp.ensure(tmp);
         CK(cub::DeviceSelect::Unique(c->cub_tmp.p, tmp, c->recs_alt.as<unsigned long long>(), c->recs.as<unsigned long long>(),
-                                     c->n_unique.as<uint32_t>(), (int)n_recs, st));
+                                     &ctr->n_unique, (int)rec_cap, st));
         c->launches += 2;
-        CK(cudaMemcpyAsync(&n_unique, c->n_unique.p, 4, cudaMemcpyDeviceToHost, st));
-        CK(cudaStreamSynchronize(st));
     }
-    k_rx_bounds<<<blocks_for(c->dp.n_rx + 1, 128), 128, 0, st>>>(c->recs.as<unsigned long long>(), n_unique, c->dp.n_rx, c->rx_begin.as<uint32_t>());
+    k_rx_bounds<<<blocks_for(c->dp.n_rx + 1, 128), 128, 0, st>>>(c->recs.as<unsigned long long>(), ctr, c->dp.n_rx, c->dp.gb, c->rx_begin.as<uint32_t>());
     c->launches += 1;
     if (!c->plan.ctx_in_groups) {
-        k_ctx_flags<<<c->n_sm * 4, 256, 0, st>>>(c->recs.as<unsigned long long>(), c->rx_begin.as<uint32_t>(), c->ctx_flags.as<uint32_t>());
+        k_ctx_flags<<<c->n_sm * 4, 256, 0, st>>>(c->recs.as<unsigned long long>(), c->rx_begin.as<uint32_t>(), c->dp.gb, c->ctx_flags.as<uint32_t>());
         c->launches += 1;
     }
-
     // ---- events in discovery order (global line, pattern index)
-    uint32_t m = 0;
-    if (n_unique) {
-        const size_t ev_cap = (size_t)n_unique * c->plan.max_fanout;
-        c->ev_key.ensure(ev_cap * 8 + 8);
-        c->ev_key_alt.ensure(ev_cap * 8 + 8);
-        k_emit_events<<<c->n_sm * 4, 256, 0, st>>>(c->recs.as<unsigned long long>(), n_unique, c->dp,
-                                                    c->ev_key_alt.as<unsigned long long>(), (uint32_t)ev_cap, ctr);
-        c->launches += 1;
-        CK(cudaMemcpyAsync(&h, ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
-        CK(cudaStreamSynchronize(st));
-        m = h.n_events;
-        if (m) sort_keys<unsigned long long>(c, c->ev_key_alt.as<unsigned long long>(), c->ev_key.as<unsigned long long>(), m,
-                                             32 + bits_for(G));
-    }
+    k_emit_events<<<c->n_sm * 4, 256, 0, st>>>(c->recs.as<unsigned long long>(), c->dp, c->ev_key_alt.as<unsigned long long>(), (uint32_t)ev_cap, ctr);
+    sort_keys<unsigned long long>(c, c->ev_key_alt.as<unsigned long long>(), c->ev_key.as<unsigned long long>(), (uint32_t)ev_cap,
+                                  std::min<int>(64, (int)c->dp.gb + (int)c->dp.pb + 1));
+    c->launches += 1;
+
     c->pend.valid = true;
-    c->pend.d_text = d_text; c->pend.len = len; c->pend.n_logs = n_logs; c->pend.G = G;
-    c->pend.n_unique = n_unique; c->pend.m = m; c->pend.options = options;
-    c->tm.scan_bytes = len + 4ull * ((uint64_t)G + 1) + 8ull * m;
-    c->tm.dfa_scan_bytes = c->d_group_blob.empty() ? 0 : len + 8ull * ((uint64_t)G + 1) + (uint64_t)G;   // text + line offsets in, flag byte out
+    c->pend.d_text = d_text; c->pend.len = len; c->pend.n_logs = n_logs; c->pend.G = (uint32_t)line_cap;
+    c->pend.m = (uint32_t)ev_cap; c->pend.options = options;
 }
 
+// Counts per pattern for the two-phase (multi-GPU) API; synchronises and validates the estimates.
 void per_pattern_counts(lp_ctx* c, uint64_t* counts_out) {
     cudaStream_t st = c->stream;
     const uint32_t np = c->dp.n_pat;
+    Counters* ctr = c->counters.as<Counters>();
     c->freq_delta.ensure((size_t)std::max<uint32_t>(np, 1) * 8);
     CK(cudaMemsetAsync(c->freq_delta.p, 0, (size_t)std::max<uint32_t>(np, 1) * 8, st));
-    if (c->pend.n_unique) {
-        k_count_per_pattern<<<c->n_sm * 4, 256, 0, st>>>(c->recs.as<unsigned long long>(), c->pend.n_unique, c->dp,
-                                                          c->freq_delta.as<unsigned long long>());
-        c->launches += 1;
-    }
+    k_count_per_pattern<<<c->n_sm * 4, 256, 0, st>>>(c->recs.as<unsigned long long>(), ctr, c->dp, c->freq_delta.as<unsigned long long>());
+    c->launches += 1;
+    Counters h{};
+    CK(cudaMemcpyAsync(&h, ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
     if (np) CK(cudaMemcpyAsync(counts_out, c->freq_delta.p, (size_t)np * 8, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
+    CK(cudaGetLastError());
+    check_estimates(c, h, c->pend.n_logs, true);
 }
 
-// ---- phase 2: frequency ranks, scoring, ranking, result download
+// ---- phase 2: frequency ranks, scoring, ranking, result download (one synchronisation)
 lp_result* run_score(lp_ctx* c, const uint64_t* prior_count) {
     if (!c->pend.valid) throw std::invalid_argument("no scan is pending on this context");
     cudaStream_t st = c->stream;
-    const uint32_t m = c->pend.m, n_logs = c->pend.n_logs, G = c->pend.G, np = c->dp.n_pat;
+    const uint32_t mc = c->pend.m, n_logs = c->pend.n_logs, line_cap = c->pend.G, np = c->dp.n_pat;
     const int options = c->pend.options;
-    std::unique_ptr<lp_result> res(new lp_result());
-    res->n_logs = n_logs;
-    res->n_events = m;
-    res->total_lines = G;
-    res->freq_delta.assign(np, 0);
-    res->log_n_lines.assign(n_logs, 0);
-    res->log_event_begin.assign(n_logs + 1, 0);
+    Counters* ctr = c->counters.as<Counters>();
 
     c->freq_delta.ensure((size_t)std::max<uint32_t>(np, 1) * 8);
     CK(cudaMemsetAsync(c->freq_delta.p, 0, (size_t)std::max<uint32_t>(np, 1) * 8, st));
     c->log_event_begin.ensure((size_t)(n_logs + 1) * 8);
-
-    if (m) {
-        c->ev_log.ensure((size_t)m * 4); c->slot_key.ensure((size_t)m * 4); c->slot_key_alt.ensure((size_t)m * 4);
-        c->ev_idx.ensure((size_t)m * 4); c->ev_idx_alt.ensure((size_t)m * 4); c->rank_in_slot.ensure((size_t)m * 4);
-        c->out_line.ensure((size_t)m * 4); c->out_pat.ensure((size_t)m * 4); c->out_score.ensure((size_t)m * 8);
-        c->sort_key.ensure((size_t)m * 8); c->sort_key_alt.ensure((size_t)m * 8);
-        c->order.ensure((size_t)m * 4); c->order_alt.ensure((size_t)m * 4); c->rank.ensure((size_t)m * 4);
-        c->log_sorted.ensure((size_t)m * 4); c->log_sorted_alt.ensure((size_t)m * 4);
-        if (options & LP_OPT_FACTORS) c->out_factors.ensure((size_t)m * 7 * 8);
-        const unsigned long long* prior_d = nullptr;
-        if (prior_count && np) {
-            c->prior.ensure((size_t)np * 8);
-            CK(cudaMemcpyAsync(c->prior.p, prior_count, (size_t)np * 8, cudaMemcpyHostToDevice, st));
-            prior_d = c->prior.as<unsigned long long>();
-        }
-        const uint32_t gb = blocks_for(m, 256);
-        k_event_prep<<<gb, 256, 0, st>>>(c->ev_key.as<unsigned long long>(), m, c->dp, c->first_line.as<uint32_t>(), n_logs,
-                                         c->ev_log.as<uint32_t>(), c->slot_key.as<uint32_t>(), c->ev_idx.as<uint32_t>(),
-                                         c->freq_delta.as<unsigned long long>());
-        sort_pairs<uint32_t, uint32_t>(c, c->slot_key.as<uint32_t>(), c->slot_key_alt.as<uint32_t>(), c->ev_idx.as<uint32_t>(),
-                                       c->ev_idx_alt.as<uint32_t>(), m, 32);
-        k_slot_rank<<<gb, 256, 0, st>>>(c->slot_key_alt.as<uint32_t>(), c->ev_idx_alt.as<uint32_t>(), m, c->rank_in_slot.as<uint32_t>());
-        ScoreArgs sa{};
-        sa.ev_key = c->ev_key.as<unsigned long long>(); sa.m = m; sa.ev_log = c->ev_log.as<uint32_t>();
-        sa.rank_in_slot = c->rank_in_slot.as<uint32_t>(); sa.prior = prior_d;
-        sa.first_line = c->first_line.as<uint32_t>(); sa.n_lines = c->n_lines.as<uint32_t>();
-        sa.keys = c->recs.as<unsigned long long>(); sa.rx_begin = c->rx_begin.as<uint32_t>();
-        sa.ctx_flags = c->ctx_flags.as<uint8_t>();
-        sa.out_line = c->out_line.as<uint32_t>(); sa.out_pat = c->out_pat.as<uint32_t>(); sa.out_score = c->out_score.as<double>();
-        sa.out_factors = (options & LP_OPT_FACTORS) ? c->out_factors.as<double>() : nullptr;
-        sa.sort_key = c->sort_key.as<unsigned long long>();
-        k_score<<<blocks_for(m, 128), 128, 0, st>>>(sa, c->dp, c->sc);
-        c->launches += 3;
+    c->ev_log.ensure((size_t)mc * 4); c->slot_key.ensure((size_t)mc * 4); c->slot_key_alt.ensure((size_t)mc * 4);
+    c->ev_idx.ensure((size_t)mc * 4); c->ev_idx_alt.ensure((size_t)mc * 4); c->rank_in_slot.ensure((size_t)mc * 4);
+    c->out_line.ensure((size_t)mc * 4); c->out_pat.ensure((size_t)mc * 4); c->out_score.ensure((size_t)mc * 8);
+    c->sort_key.ensure((size_t)mc * 8); c->sort_key_alt.ensure((size_t)mc * 8);
+    c->order.ensure((size_t)mc * 4); c->order_alt.ensure((size_t)mc * 4); c->rank.ensure((size_t)mc * 4);
+    c->log_sorted.ensure((size_t)mc * 4); c->log_sorted_alt.ensure((size_t)mc * 4);
+    if (options & LP_OPT_FACTORS) c->out_factors.ensure((size_t)mc * 7 * 8);
+    const unsigned long long* prior_d = nullptr;
+    if (prior_count && np) {
+        c->prior.ensure((size_t)np * 8);
+        CK(cudaMemcpyAsync(c->prior.p, prior_count, (size_t)np * 8, cudaMemcpyHostToDevice, st));
+        prior_d = c->prior.as<unsigned long long>();
     }
-    k_log_event_begin<<<blocks_for(n_logs + 1, 128), 128, 0, st>>>(c->ev_key.as<unsigned long long>(), m, c->first_line.as<uint32_t>(),
-                                                                   n_logs, c->log_event_begin.as<unsigned long long>());
-    c->launches += 1;
-    if (m && !(options & LP_OPT_NO_RANK)) {
+    const uint32_t gb = blocks_for(mc, 256);
+    const uint32_t n_slots = (uint32_t)c->plan.slot_first_pat.size();
+    k_event_prep<<<gb, 256, 0, st>>>(c->ev_key.as<unsigned long long>(), ctr, mc, c->dp, c->first_line.as<uint32_t>(), n_logs, n_slots,
+                                     c->ev_log.as<uint32_t>(), c->slot_key.as<uint32_t>(), c->ev_idx.as<uint32_t>(),
+                                     c->freq_delta.as<unsigned long long>());
+    sort_pairs<uint32_t, uint32_t>(c, c->slot_key.as<uint32_t>(), c->slot_key_alt.as<uint32_t>(), c->ev_idx.as<uint32_t>(),
+                                   c->ev_idx_alt.as<uint32_t>(), mc, bits_for(n_slots + 1));
+    k_slot_rank<<<gb, 256, 0, st>>>(c->slot_key_alt.as<uint32_t>(), c->ev_idx_alt.as<uint32_t>(), mc, n_slots, c->rank_in_slot.as<uint32_t>());
+    ScoreArgs sa{};
+    sa.ev_key = c->ev_key.as<unsigned long long>(); sa.m_cap = mc; sa.ctr = ctr; sa.ev_log = c->ev_log.as<uint32_t>();
+    sa.rank_in_slot = c->rank_in_slot.as<uint32_t>(); sa.prior = prior_d;
+    sa.first_line = c->first_line.as<uint32_t>(); sa.n_lines = c->n_lines.as<uint32_t>();
+    sa.keys = c->recs.as<unsigned long long>(); sa.rx_begin = c->rx_begin.as<uint32_t>();
+    sa.ctx_flags = c->ctx_flags.as<uint8_t>();
+    sa.out_line = c->out_line.as<uint32_t>(); sa.out_pat = c->out_pat.as<uint32_t>(); sa.out_score = c->out_score.as<double>();
+    sa.out_factors = (options & LP_OPT_FACTORS) ? c->out_factors.as<double>() : nullptr;
+    sa.sort_key = c->sort_key.as<unsigned long long>();
+    k_score<<<blocks_for(mc, 128), 128, 0, st>>>(sa, c->dp, c->sc);
+    k_log_event_begin<<<blocks_for(n_logs + 1, 128), 128, 0, st>>>(c->ev_key.as<unsigned long long>(), ctr, c->first_line.as<uint32_t>(),
+                                                                   n_logs, c->dp.pb, c->log_event_begin.as<unsigned long long>());
+    c->launches += 4;
+    if (!(options & LP_OPT_NO_RANK)) {
         // stable sort by descending score (ties keep discovery order), then stably by log
         sort_pairs<unsigned long long, uint32_t>(c, c->sort_key.as<unsigned long long>(), c->sort_key_alt.as<unsigned long long>(),
-                                                 c->ev_idx.as<uint32_t>(), c->order.as<uint32_t>(), m, 64);
+                                                 c->ev_idx.as<uint32_t>(), c->order.as<uint32_t>(), mc, 64);
         uint32_t* order = c->order.as<uint32_t>();
         if (n_logs > 1) {
-            k_gather_u32<<<blocks_for(m, 256), 256, 0, st>>>(c->ev_log.as<uint32_t>(), order, m, c->log_sorted.as<uint32_t>());
+            k_gather_u32<<<blocks_for(mc, 256), 256, 0, st>>>(c->ev_log.as<uint32_t>(), order, mc, c->log_sorted.as<uint32_t>());
             sort_pairs<uint32_t, uint32_t>(c, c->log_sorted.as<uint32_t>(), c->log_sorted_alt.as<uint32_t>(), order,
-                                           c->order_alt.as<uint32_t>(), m, bits_for(n_logs));
+                                           c->order_alt.as<uint32_t>(), mc, bits_for(n_logs));
             order = c->order_alt.as<uint32_t>();
             c->launches += 1;
         }
-        k_write_rank<<<blocks_for(m, 256), 256, 0, st>>>(order, c->ev_log.as<uint32_t>(), c->log_event_begin.as<unsigned long long>(), m,
-                                                         c->rank.as<uint32_t>());
+        k_write_rank<<<blocks_for(mc, 256), 256, 0, st>>>(order, c->ev_log.as<uint32_t>(), c->log_event_begin.as<unsigned long long>(), ctr,
+                                                          c->rank.as<uint32_t>());
         c->launches += 1;
     }
     CK(cudaEventRecord(c->ev[4], st));
 
-    // ---- download
-    res->line.resize(m); res->pattern.resize(m); res->score.resize(m); res->rank.assign(m, 0);
-    if (m) {
-        CK(cudaMemcpyAsync(res->line.data(), c->out_line.p, (size_t)m * 4, cudaMemcpyDeviceToHost, st));
-        CK(cudaMemcpyAsync(res->pattern.data(), c->out_pat.p, (size_t)m * 4, cudaMemcpyDeviceToHost, st));
-        CK(cudaMemcpyAsync(res->score.data(), c->out_score.p, (size_t)m * 8, cudaMemcpyDeviceToHost, st));
-        if (!(options & LP_OPT_NO_RANK)) CK(cudaMemcpyAsync(res->rank.data(), c->rank.p, (size_t)m * 4, cudaMemcpyDeviceToHost, st));
-        if (options & LP_OPT_FACTORS) {
-            res->factors.resize((size_t)m * 7);
-            res->has_factors = true;
-            CK(cudaMemcpyAsync(res->factors.data(), c->out_factors.p, (size_t)m * 7 * 8, cudaMemcpyDeviceToHost, st));
-        }
+    // ---- download into page-locked staging (asynchronous copies, one synchronisation), sizes from
+    // the estimates; trimmed after the counters arrive
+    std::unique_ptr<lp_result> res(new lp_result());
+    res->n_logs = n_logs;
+    const bool want_rank = !(options & LP_OPT_NO_RANK), want_factors = (options & LP_OPT_FACTORS) != 0;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 63) & ~size_t(63); return o; };
+    const size_t o_ctr = take(sizeof(Counters)), o_line = take((size_t)mc * 4), o_pat = take((size_t)mc * 4), o_score = take((size_t)mc * 8),
+                 o_rank = take(want_rank ? (size_t)mc * 4 : 0), o_fac = take(want_factors ? (size_t)mc * 56 : 0),
+                 o_delta = take((size_t)np * 8), o_nl = take((size_t)n_logs * 4), o_leb = take((size_t)(n_logs + 1) * 8);
+    c->stage.ensure(off);
+    uint8_t* hs = c->stage.p;
+    CK(cudaMemcpyAsync(hs + o_ctr, ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
+    if (mc) {
+        CK(cudaMemcpyAsync(hs + o_line, c->out_line.p, (size_t)mc * 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(hs + o_pat, c->out_pat.p, (size_t)mc * 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaMemcpyAsync(hs + o_score, c->out_score.p, (size_t)mc * 8, cudaMemcpyDeviceToHost, st));
+        if (want_rank) CK(cudaMemcpyAsync(hs + o_rank, c->rank.p, (size_t)mc * 4, cudaMemcpyDeviceToHost, st));
+        if (want_factors) CK(cudaMemcpyAsync(hs + o_fac, c->out_factors.p, (size_t)mc * 56, cudaMemcpyDeviceToHost, st));
     }
-    if (np) CK(cudaMemcpyAsync(res->freq_delta.data(), c->freq_delta.p, (size_t)np * 8, cudaMemcpyDeviceToHost, st));
-    std::vector<uint32_t> nl(n_logs);
-    CK(cudaMemcpyAsync(nl.data(), c->n_lines.p, (size_t)n_logs * 4, cudaMemcpyDeviceToHost, st));
-    CK(cudaMemcpyAsync(res->log_event_begin.data(), c->log_event_begin.p, (size_t)(n_logs + 1) * 8, cudaMemcpyDeviceToHost, st));
+    if (np) CK(cudaMemcpyAsync(hs + o_delta, c->freq_delta.p, (size_t)np * 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(hs + o_nl, c->n_lines.p, (size_t)n_logs * 4, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(hs + o_leb, c->log_event_begin.p, (size_t)(n_logs + 1) * 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaStreamSynchronize(st));
+    CK(cudaGetLastError());
+    Counters h;
+    memcpy(&h, hs + o_ctr, sizeof h);
+    check_estimates(c, h, n_logs, true);       // throws Retry when a buffer was too small
+
+    const uint32_t m = h.n_events;
+    const uint32_t G = (uint32_t)(h.total_nl + n_logs);
+    res->n_events = m;
+    res->total_lines = G;
+    res->line.assign(reinterpret_cast<uint32_t*>(hs + o_line), reinterpret_cast<uint32_t*>(hs + o_line) + m);
+    res->pattern.assign(reinterpret_cast<uint32_t*>(hs + o_pat), reinterpret_cast<uint32_t*>(hs + o_pat) + m);
+    res->score.assign(reinterpret_cast<double*>(hs + o_score), reinterpret_cast<double*>(hs + o_score) + m);
+    if (want_rank) res->rank.assign(reinterpret_cast<uint32_t*>(hs + o_rank), reinterpret_cast<uint32_t*>(hs + o_rank) + m);
+    else res->rank.assign(m, 0);
+    if (want_factors) { res->has_factors = true; res->factors.assign(reinterpret_cast<double*>(hs + o_fac), reinterpret_cast<double*>(hs + o_fac) + (size_t)m * 7); }
+    res->freq_delta.assign(reinterpret_cast<uint64_t*>(hs + o_delta), reinterpret_cast<uint64_t*>(hs + o_delta) + np);
+    res->log_n_lines.resize(n_logs);
+    for (uint32_t k = 0; k < n_logs; ++k) res->log_n_lines[k] = reinterpret_cast<uint32_t*>(hs + o_nl)[k];
+    res->log_event_begin.assign(reinterpret_cast<uint64_t*>(hs + o_leb), reinterpret_cast<uint64_t*>(hs + o_leb) + n_logs + 1);
     if (options & LP_OPT_LINE_OFFSETS) {
         res->has_offsets = true;
         res->line_start.resize((size_t)G + 1);
         res->line_end.resize((size_t)G);
         CK(cudaMemcpyAsync(res->line_start.data(), c->line_start.p, (size_t)G * 4, cudaMemcpyDeviceToHost, st));
         CK(cudaMemcpyAsync(res->line_end.data(), c->line_end.p, (size_t)G * 4, cudaMemcpyDeviceToHost, st));
+        CK(cudaStreamSynchronize(st));
+        res->line_start[G] = (uint32_t)c->pend.len;
     }
-    CK(cudaStreamSynchronize(st));
-    CK(cudaGetLastError());
-    for (uint32_t k = 0; k < n_logs; ++k) res->log_n_lines[k] = nl[k];
-    if (res->has_offsets) res->line_start[G] = (uint32_t)c->pend.len;
-
+    (void)line_cap;
     float ms = 0;
     cudaEventElapsedTime(&ms, c->ev[0], c->ev[4]); c->tm.total_ms = ms;
     cudaEventElapsedTime(&ms, c->ev[1], c->ev[2]); c->tm.scan_ms = ms;
@@ -1478,8 +1536,27 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count) {
     cudaEventElapsedTime(&ms, c->ev[3], c->ev[4]); c->tm.score_ms = ms;
     cudaEventElapsedTime(&ms, c->ev[6], c->ev[7]); c->tm.dfa_scan_ms = ms;
     c->tm.kernel_launches = c->launches;
+    c->tm.candidates = h.n_cand;
+    c->tm.verify_tasks = (uint64_t)h.n_tasks + h.n_vm_tasks + (uint64_t)G * (c->plan.always_list.size() + c->plan.always_vm_list.size());
+    c->tm.scan_bytes = c->pend.len + 4ull * ((uint64_t)G + 1) + 8ull * m;
+    c->tm.dfa_scan_bytes = c->d_group_blob.empty() ? 0 : c->pend.len + 8ull * ((uint64_t)G + 1) + (uint64_t)G;
+    if (!c->plan.lit_off.empty() && (uint64_t)h.n_cand * 2 > (uint64_t)G + 1024 && c->recalibrations < 2) { c->calibrated = false; ++c->recalibrations; }
     c->pend.valid = false;
     return res.release();
+}
+
+// scan + score with the re-run loop for under-estimated buffers
+template <class Stage>
+lp_result* run_all(lp_ctx* c, Stage&& stage_text, uint64_t len, const uint64_t* offsets, uint32_t n_logs, const uint64_t* prior, int options) {
+    for (;;) {
+        try {
+            const uint8_t* d = stage_text();
+            run_scan(c, d, len, offsets, n_logs, options);
+            return run_score(c, prior);
+        } catch (const Retry&) {
+            continue;
+        }
+    }
 }
 
 template <class F>
@@ -1516,6 +1593,7 @@ const uint8_t* stage_host_log(lp_ctx* c, const uint8_t* host, uint64_t len) {
     c->text.ensure(len + 64);
     CK(cudaEventRecord(c->ev[5], c->stream));
     if (len) CK(cudaMemcpyAsync(c->text.p, host, len, cudaMemcpyHostToDevice, c->stream));
+    CK(cudaEventRecord(c->ev[8], c->stream));
     return c->text.as<uint8_t>();
 }
 
@@ -1580,6 +1658,7 @@ void lp_destroy(lp_ctx* c) {
                      &c->log_sorted, &c->log_sorted_alt, &c->rank, &c->log_event_begin, &c->n_unique, &c->d_lut,
                      &c->f_bitmap, &c->f_key, &c->f_begin, &c->f_count, &c->f_lits, &c->f_goff};
     for (DevBuf* b : all) b->release();
+    c->stage.release();
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -1670,15 +1749,26 @@ int lp_batch_scan_device(lp_ctx* c, const uint8_t* d_logs, const uint64_t* offse
     return guarded(c, [&] {
         if (!offsets) throw std::invalid_argument("offsets is NULL");
         std::lock_guard<std::mutex> lk(c->mu);
-        run_scan(c, d_logs, offsets[n_logs], offsets, (uint32_t)n_logs, options);
-        if (counts_out) per_pattern_counts(c, counts_out);
+        std::vector<uint64_t> tmp(std::max<uint32_t>(c->dp.n_pat, 1));
+        for (;;) {
+            try {
+                run_scan(c, d_logs, offsets[n_logs], offsets, (uint32_t)n_logs, options);
+                per_pattern_counts(c, tmp.data());
+                break;
+            } catch (const Retry&) { continue; }
+        }
+        if (counts_out) memcpy(counts_out, tmp.data(), (size_t)c->dp.n_pat * 8);
     });
 }
 int lp_batch_score(lp_ctx* c, const uint64_t* prior_count, lp_result** out) {
     if (!c || !out) { g_last_error = "NULL argument"; return LP_ERR_INVALID; }
     return guarded(c, [&] {
         std::lock_guard<std::mutex> lk(c->mu);
-        *out = run_score(c, prior_count);
+        try {
+            *out = run_score(c, prior_count);
+        } catch (const Retry&) {
+            throw LimitFail("internal: estimates validated by lp_batch_scan_device were exceeded in lp_batch_score");
+        }
     });
 }
 
@@ -1688,8 +1778,7 @@ int lp_analyze_batch_device(lp_ctx* c, const uint8_t* d_logs, const uint64_t* of
     return guarded(c, [&] {
         if (!offsets) throw std::invalid_argument("offsets is NULL");
         std::lock_guard<std::mutex> lk(c->mu);
-        run_scan(c, d_logs, offsets[n_logs], offsets, (uint32_t)n_logs, options);
-        *out = run_score(c, prior_count);
+        *out = run_all(c, [&] { return d_logs; }, offsets[n_logs], offsets, (uint32_t)n_logs, prior_count, options);
     });
 }
 int lp_analyze_batch(lp_ctx* c, const uint8_t* logs, const uint64_t* offsets, size_t n_logs, const uint64_t* prior_count, int options,
@@ -1700,11 +1789,12 @@ int lp_analyze_batch(lp_ctx* c, const uint8_t* logs, const uint64_t* offsets, si
         std::lock_guard<std::mutex> lk(c->mu);
         const uint64_t len = offsets[n_logs];
         if (len && !logs) throw std::invalid_argument("logs is NULL");
-        const uint8_t* d = stage_host_log(c, logs, len);
-        run_scan(c, d, len, offsets, (uint32_t)n_logs, options);
-        *out = run_score(c, prior_count);
+        bool staged = false;
+        const uint8_t* d = nullptr;
+        *out = run_all(c, [&] { if (!staged) { d = stage_host_log(c, logs, len); staged = true; } return d; }, len, offsets, (uint32_t)n_logs,
+                       prior_count, options);
         float ms = 0;
-        cudaEventElapsedTime(&ms, c->ev[5], c->ev[0]);
+        cudaEventElapsedTime(&ms, c->ev[5], c->ev[8]);
         c->tm.h2d_ms = ms;
     });
 }

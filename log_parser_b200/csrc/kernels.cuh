@@ -20,6 +20,8 @@ constexpr uint32_t GRAM_MUL = 0x9E3779B1u;
 constexpr uint32_t GRAM_MUL2 = 0x85EBCA6Bu;
 
 struct DevPlan {
+    // key layouts of this call: record = regex << gb | line, event = line << pb | pattern
+    uint32_t gb, pb;
     // regex universe
     uint32_t n_rx;
     const uint8_t* rx_kind;
@@ -91,10 +93,11 @@ struct Counters {
     unsigned int n_tasks;
     unsigned int n_recs;
     unsigned int n_events;
-    unsigned int overflow;     // bit0 cand, bit1 tasks, bit2 recs, bit3 events, bit4 backtrack budget
-    unsigned int n_unique;
+    unsigned int overflow;     // bit0 cand, bit1 tasks, bit2 recs, bit3 events, bit4 backtrack budget, bit5 vm tasks, bit6 line arrays
+    unsigned int n_unique;     // written by the unique pass (includes one sentinel group when padding was sorted)
     unsigned int n_vm_tasks;
-    unsigned int pad[5];
+    unsigned int n_lines_total;    // newlines + logs (G), published by k_scan_tiles
+    unsigned int pad[4];
 };
 
 }  // namespace lpk
