@@ -177,7 +177,7 @@ def main():
     import torch
     import torch.distributed as dist
 
-    from log_parser_b200 import binding, build
+    from log_parser_b200 import binding, build, parallel
     from log_parser_b200.model import ScoringConfig
 
     if not torch.cuda.is_available():
@@ -198,16 +198,13 @@ def main():
     copies = [host.to(f"cuda:{local_rank}", non_blocking=False).clone() for _ in range(3)]
     off = np.array([0, nbytes], dtype=np.uint64)
     lib_stream = torch.cuda.ExternalStream(lp.stream_ptr(), device=torch.device("cuda", local_rank))
-    counts_all = torch.zeros(world, P, dtype=torch.int64, device=f"cuda:{local_rank}") if world > 1 else None
 
     def step_device(i):
         d = copies[i % len(copies)]
         if world == 1:
             return lp.analyze_device(d.data_ptr(), nbytes)
         counts = lp.batch_scan_device(d.data_ptr(), off)
-        mine = torch.from_numpy(counts.astype(np.int64)).to(f"cuda:{local_rank}")
-        dist.all_gather_into_tensor(counts_all.view(-1), mine)
-        prior = counts_all[:rank].sum(dim=0).cpu().numpy().astype(np.uint64)   # exclusive prefix over lower ranks
+        prior, _total = parallel.exclusive_prefix(counts, rank, world)     # one NCCL all-gather of P x int64
         return lp.batch_score(prior)
 
     def barrier():

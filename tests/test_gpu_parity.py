@@ -264,3 +264,29 @@ def test_literal_with_boundaries_patterns(parser, oracle):
     assert len(ora.line) > 25
     _check(res, ora)
     np.testing.assert_array_equal(res.score, ora.score)
+
+
+def test_sharded_blocks_equal_one_batch(parser):
+    """The multi-GPU decomposition on one GPU: two contiguous blocks of logs, scanned and scored
+    with the exclusive prefix of the per-pattern counts, concatenate to the single-batch result."""
+    from log_parser_b200 import parallel
+
+    wl = synth.make_patterns(40, 777, noliteral=1)
+    logs = [synth.make_log(wl, n, 300 + i, pool_blocks=400, hit_rate=0.06) for i, n in enumerate([500, 200, 900, 50, 400, 300])]
+    parser.load_patterns(wl.patterns)
+    whole = parser.analyze_batch(logs)
+    eng = parallel.GpuBatchEngine(parser)
+    bounds = parallel.shard_bounds([len(x) for x in logs], 2)
+    assert bounds[0][1] == bounds[1][0] and 0 < bounds[0][1] < len(logs)
+    prior = np.zeros(len(wl.patterns), np.uint64)
+    lines, pats, scores = [], [], []
+    for lo, hi in bounds:
+        counts = eng.scan(logs[lo:hi])
+        r = eng.score(prior)
+        np.testing.assert_array_equal(counts, r.freq_delta)
+        lines.append(r.line); pats.append(r.pattern); scores.append(r.score)
+        prior = prior + counts
+    np.testing.assert_array_equal(np.concatenate(lines), whole.line)
+    np.testing.assert_array_equal(np.concatenate(pats), whole.pattern)
+    np.testing.assert_array_equal(np.concatenate(scores), whole.score)
+    np.testing.assert_array_equal(prior, whole.freq_delta)
