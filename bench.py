@@ -100,12 +100,57 @@ def build_workload(args, rank: int):
     return wl, log
 
 
+def jvm_harness_run(wl, log, per_lines: int, steps: int, warmup: int):
+    """oracle/RefHarness.java on the real java.util.regex, if a JDK exists on this box (none in the
+    authoring image). One request on one thread, as the reference serves it. Returns None if unusable."""
+    import base64
+    import shutil
+    import tempfile
+
+    from log_parser_b200.model import severity_multiplier
+
+    java = shutil.which("java")
+    if not java:
+        return None
+    try:
+        b = lambda x: base64.b64encode(x.encode("utf-8")).decode("ascii")
+        rows = []
+        for p in wl.patterns:
+            f = [p.id or "", repr(p.confidence), repr(severity_multiplier(p.severity)), "1" if p.has_context else "0",
+                 str(p.lines_before or 0), str(p.lines_after or 0), b(p.primary_regex), str(len(p.secondaries))]
+            for s in p.secondaries:
+                f += [b(s.regex), repr(s.weight), str(s.proximity_window)]
+            f.append(str(len(p.sequences)))
+            for q in p.sequences:
+                f += [repr(q.bonus_multiplier), str(len(q.events))] + [b(e) for e in q.events]
+            rows.append("\t".join(f))
+        lines = log.split(b"\n")
+        sample = b"\n".join(lines[:per_lines]) + b"\n"
+        with tempfile.TemporaryDirectory() as d:
+            open(os.path.join(d, "p.tsv"), "w").write("\n".join(rows) + "\n")
+            open(os.path.join(d, "l.log"), "wb").write(sample)
+            r = subprocess.run([java, os.path.join(ROOT, "oracle", "RefHarness.java"), os.path.join(d, "p.tsv"), os.path.join(d, "l.log"),
+                                str(max(warmup, 3)), str(max(steps, 1))], capture_output=True, text=True, timeout=600)
+        if r.returncode != 0:
+            return None
+        kv = dict(x.split("=") for x in r.stdout.strip().split())
+        ms = float(kv["ms_per_step"])
+        return {"value": float(kv["lines"]) / (ms / 1e3), "ms_per_step": ms, "cores": 1, "kind": "port",
+                "sample": f"RefHarness.java on java.util.regex: 1 request x {per_lines} lines x {len(wl.patterns)} patterns, 1 thread",
+                "sample_lines": per_lines, "bytes_per_line": len(sample) / max(1, per_lines)}
+    except Exception:   # noqa: BLE001
+        return None
+
+
 def cpu_reference_run(args, wl, log, steps: int, warmup: int):
     """The reference's CPU path (oracle restatement; no JVM in this image) on a bounded sample.
     One request per host thread: the reference's only parallelism (AnalysisService.java:89-113)."""
     from oracle import oracle as O
     from log_parser_b200.model import ScoringConfig
 
+    jvm = jvm_harness_run(wl, log, args.ref_lines * 4, steps, warmup)
+    if jvm is not None:
+        return jvm
     cores = os.cpu_count() or 1
     threads = max(1, min(cores, args.ref_threads or cores))
     per = args.ref_lines
