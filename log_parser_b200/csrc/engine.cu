@@ -55,6 +55,17 @@ __device__ __forceinline__ uint4 load16_any(const uint8_t* __restrict__ text, ui
     if (pos >= len) return make_uint4(0, 0, 0, 0);
     return load16(text, pos, len);
 }
+__device__ __noinline__ unsigned long long load8_tail(const uint8_t* __restrict__ text, uint64_t pos, uint64_t len) {
+    unsigned long long w = 0;
+    for (int i = 0; i < 8; ++i)
+        if (pos + i < len) w |= (unsigned long long)text[pos + i] << (i * 8);
+    return w;
+}
+// 8 bytes at the 8-aligned `pos`; bytes at or beyond `len` read as zero
+__device__ __forceinline__ unsigned long long load8_any(const uint8_t* __restrict__ text, uint64_t pos, uint64_t len) {
+    if (pos + 8 <= len) { const uint2 v = __ldg(reinterpret_cast<const uint2*>(text + pos)); return ((unsigned long long)v.y << 32) | v.x; }
+    return load8_tail(text, pos, len);
+}
 __device__ __noinline__ uint32_t load4_tail(const uint8_t* __restrict__ text, uint64_t pos, uint64_t len) {
     uint32_t w = 0;
     for (int i = 0; i < 4; ++i)
@@ -319,41 +330,76 @@ __device__ __forceinline__ long tail_terminator(const uint8_t* __restrict__ s, u
     if (n >= 3 && s[le - 3] == 0xE2 && s[le - 2] == 0x80 && (s[le - 1] == 0xA8 || s[le - 1] == 0xA9)) return (long)le - 3;
     return -1;
 }
-// One regex over one line; the line streams through registers in 16-byte chunks (one chunk ahead).
-__device__ bool dfa_walk(const DevPlan& P, uint32_t r, const uint8_t* __restrict__ text, uint64_t len, uint32_t ls, uint32_t le) {
-    const uint32_t nc = P.rx_ncls[r];
-    const uint16_t* __restrict__ T = P.dfa_trans + P.rx_dfa_off[r];
-    const uint8_t* __restrict__ cm = P.rx_cmap + (size_t)r * 256;
-    uint32_t st = P.rx_start[r];
-    if (le > ls && st > 1) {
-        const long tpos = tail_terminator(text, ls, le);
-        const uint32_t tp = tpos < 0 ? 0xFFFFFFFFu : (uint32_t)tpos;
-        uint32_t i = ls;
-        uint64_t chunk = (uint64_t)(ls & ~15u);
-        uint4 cur = load16_any(text, chunk, len);
-        uint4 nxt = (chunk + 16 < le) ? load16_any(text, chunk + 16, len) : make_uint4(0, 0, 0, 0);
-        uint32_t wsel = (i >> 2) & 3u;
-        uint32_t w = (wsel == 0 ? cur.x : wsel == 1 ? cur.y : wsel == 2 ? cur.z : cur.w) >> ((i & 3u) * 8u);
+// NG automata over one line. The line is consumed 8 bytes per (aligned) load with the eight
+// transitions unrolled; unaligned head/tail bytes are stepped one by one. `LOWFINAL` selects the
+// single-DFA convention (states 0/1 = DEAD/MATCH are final) or the product-DFA one (states >= ff).
+template <int NG, bool LOWFINAL>
+struct LineWalker {
+    const uint8_t* __restrict__ cm[NG];
+    const uint16_t* __restrict__ T[NG];
+    uint32_t nc[NG], ff[NG], st[NG];
+
+    __device__ __forceinline__ bool live(int q) const { return LOWFINAL ? st[q] > 1u : st[q] < ff[q]; }
+    __device__ __forceinline__ bool step(uint32_t b) {
+        bool any = false;
+#pragma unroll
+        for (int q = 0; q < NG; ++q)
+            if (live(q)) { st[q] = T[q][st[q] * nc[q] + cm[q][b]]; any = true; }
+        return any;
+    }
+    __device__ __forceinline__ void symbol(uint32_t col_from_end) {     // 2 = TPOS, 1 = EOT
+#pragma unroll
+        for (int q = 0; q < NG; ++q) if (live(q)) st[q] = T[q][st[q] * nc[q] + nc[q] - col_from_end];
+    }
+    // bytes [a, b) of text; returns false once every automaton is final. Aligned 8-byte words,
+    // one word prefetched ahead; partial first/last words are stepped byte by byte from registers.
+    __device__ __forceinline__ bool segment(const uint8_t* __restrict__ text, uint64_t len, uint32_t a, uint32_t b) {
+        if (a >= b) return true;
+        uint32_t base = a & ~7u;
+        unsigned long long cur = load8_any(text, base, len);
+        unsigned long long nxt = (base + 8 < b) ? load8_any(text, (uint64_t)base + 8, len) : 0ull;
+        uint32_t lo = a - base;
         for (;;) {
-            const uint32_t b = w & 0xFFu;
-            w >>= 8;
-            if (i == tp) st = T[st * nc + nc - 2];
-            st = T[st * nc + cm[b]];
-            ++i;
-            if (i >= le || st <= 1) break;
-            if ((i & 3u) == 0) {
-                wsel = (i >> 2) & 3u;
-                if (wsel == 0) {
-                    cur = nxt;
-                    chunk += 16;
-                    if (chunk + 16 < le) nxt = load16_any(text, chunk + 16, len);
-                }
-                w = wsel == 0 ? cur.x : wsel == 1 ? cur.y : wsel == 2 ? cur.z : cur.w;
+            const uint32_t hi = min(8u, b - base);
+            if (lo == 0 && hi == 8) {
+                const uint32_t x = (uint32_t)cur, y = (uint32_t)(cur >> 32);
+                bool any = true;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) any = step((x >> (8 * k)) & 0xFFu);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) any = step((y >> (8 * k)) & 0xFFu);
+                if (!any) return false;
+            } else {
+                for (uint32_t k = lo; k < hi; ++k)
+                    if (!step((uint32_t)(cur >> (8 * k)) & 0xFFu)) return false;
             }
+            base += 8;
+            if (base >= b) return true;
+            lo = 0;
+            cur = nxt;
+            nxt = (base + 8 < b) ? load8_any(text, (uint64_t)base + 8, len) : 0ull;
         }
     }
-    if (st > 1) st = T[st * nc + nc - 1];
-    return st == 1;
+    __device__ __forceinline__ void run(const uint8_t* __restrict__ text, uint64_t len, uint32_t ls, uint32_t le) {
+        if (le > ls) {
+            const long tpos = tail_terminator(text, ls, le);
+            if (tpos < 0) segment(text, len, ls, le);
+            else if (segment(text, len, ls, (uint32_t)tpos)) { symbol(2); segment(text, len, (uint32_t)tpos, le); }
+        }
+        symbol(1);
+    }
+};
+
+// One regex over one line (tables in global memory, L1/L2-cached).
+__device__ bool dfa_walk(const DevPlan& P, uint32_t r, const uint8_t* __restrict__ text, uint64_t len, uint32_t ls, uint32_t le) {
+    LineWalker<1, true> w;
+    w.nc[0] = P.rx_ncls[r];
+    w.T[0] = P.dfa_trans + P.rx_dfa_off[r];
+    w.cm[0] = P.rx_cmap + (size_t)r * 256;
+    w.ff[0] = 0;
+    w.st[0] = P.rx_start[r];
+    w.run(text, len, ls, le);
+    return w.st[0] == 1;
 }
 
 __device__ __forceinline__ void emit_record(Counters* ctr, unsigned long long* recs, uint32_t cap, uint32_t gb, bool hit, uint32_t r, uint32_t g) {
@@ -649,45 +695,13 @@ __global__ void __launch_bounds__(DS_THREADS) k_dfa_scan(DfaScanArgs a) {
         uint32_t flags = 0;
         if (live) {
             const uint32_t ls = a.line_start[g], le = a.line_end[g];
-            uint32_t st[NG];
+            LineWalker<NG, false> w;
 #pragma unroll
-            for (int q = 0; q < NG; ++q) st[q] = st0[q];
-            if (le > ls) {
-                const long tpos = tail_terminator(a.text, ls, le);
-                const uint32_t tp = tpos < 0 ? 0xFFFFFFFFu : (uint32_t)tpos;
-                uint32_t i = ls;
-                uint64_t chunk = (uint64_t)(ls & ~15u);
-                uint4 cur = load16_any(a.text, chunk, a.len);
-                uint4 nxt = (chunk + 16 < le) ? load16_any(a.text, chunk + 16, a.len) : make_uint4(0, 0, 0, 0);
-                uint32_t wsel = (i >> 2) & 3u;
-                uint32_t w = (wsel == 0 ? cur.x : wsel == 1 ? cur.y : wsel == 2 ? cur.z : cur.w) >> ((i & 3u) * 8u);
-                for (;;) {
-                    const uint32_t b = w & 0xFFu;
-                    w >>= 8;
-                    if (i == tp) {
-#pragma unroll
-                        for (int q = 0; q < NG; ++q) if (st[q] < ff[q]) st[q] = T[q][st[q] * nc[q] + nc[q] - 2];
-                    }
-                    bool active = false;
-#pragma unroll
-                    for (int q = 0; q < NG; ++q)
-                        if (st[q] < ff[q]) { st[q] = T[q][st[q] * nc[q] + cm[q][b]]; active = true; }
-                    ++i;
-                    if (i >= le || !active) break;
-                    if ((i & 3u) == 0) {
-                        wsel = (i >> 2) & 3u;
-                        if (wsel == 0) {
-                            cur = nxt;
-                            chunk += 16;
-                            if (chunk + 16 < le) nxt = load16_any(a.text, chunk + 16, a.len);
-                        }
-                        w = wsel == 0 ? cur.x : wsel == 1 ? cur.y : wsel == 2 ? cur.z : cur.w;
-                    }
-                }
-            }
+            for (int q = 0; q < NG; ++q) { w.cm[q] = cm[q]; w.T[q] = T[q]; w.nc[q] = nc[q]; w.ff[q] = ff[q]; w.st[q] = st0[q]; }
+            w.run(a.text, a.len, ls, le);
 #pragma unroll
             for (int q = 0; q < NG; ++q) {
-                const uint32_t mask = smask[q][T[q][st[q] * nc[q] + nc[q] - 1]];
+                const uint32_t mask = smask[q][w.st[q]];
 #pragma unroll
                 for (int c = 0; c < 4; ++c) { const int bit = s_ctxbit[q][c]; if (bit >= 0) flags |= ((mask >> bit) & 1u) << c; }
                 uint32_t pend = mask & s_recmask[q];
