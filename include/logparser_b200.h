@@ -170,12 +170,12 @@ void lp_result_free(lp_result* r);
 /* ---- measurement ------------------------------------------------------------------------- */
 typedef struct lp_timings {
     float total_ms;        /* first to last kernel of the last lp_analyze* call (CUDA events)     */
-    float scan_ms;         /* the line-split + prefilter kernel (the dominant streaming kernel)   */
+    float scan_ms;         /* k_filter_count: newline count + literal prefilter, the dominant streaming kernel */
     float verify_ms;       /* candidate confirmation + DFA / backtracking verification            */
     float score_ms;        /* sorting, event assembly, scoring, ranking                           */
     float h2d_ms;          /* host->device copy of the log (lp_analyze / lp_analyze_batch only)   */
     uint64_t kernel_launches;   /* kernels of this library launched by the last call             */
-    uint64_t scan_bytes;        /* algorithmic bytes of the scan kernel: B + 4(N+1) + 8M          */
+    uint64_t scan_bytes;        /* its algorithmic bytes: B read + 4 per tile + 4 per candidate   */
     uint64_t candidates;        /* gram-filter hits handed to confirmation                        */
     uint64_t verify_tasks;      /* (line, regex) pairs verified                                   */
     float dfa_scan_ms;          /* the always-on shared-memory product-DFA scan (part of verify_ms) */

@@ -125,6 +125,125 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_count_nl(const uint8_t* __rest
     }
 }
 
+// ------------------------------------------------------------------ K1': newline count per tile + gram prefilter
+// The streaming kernel of the scan: one pass over the log, 16 bytes per thread and iteration.
+// It needs no line structure: newlines are only counted per tile (for the offsets pass that
+// follows), and every 4-byte window is tested against the literal-gram Bloom bitmap in shared
+// memory (first probe for all windows, second probe only for first-probe hits); surviving window
+// positions go to the candidate queue with one warp-aggregated atomic per warp and iteration.
+constexpr uint32_t CAND_STAGE = 2048;      // candidates staged per block and tile in shared memory
+struct FilterArgs {
+    const uint8_t* text;
+    uint64_t len;
+    uint32_t n_tiles;
+    uint32_t* tile_counts;
+    const uint32_t* bitmap;
+    uint32_t* cand;                   // candidate byte positions
+    uint32_t cand_cap;
+    Counters* ctr;
+    int use_filter;
+};
+__global__ void __launch_bounds__(SCAN_THREADS) k_filter_count(FilterArgs a) {
+    extern __shared__ uint32_t s_bitmap[];
+    __shared__ uint32_t warp_sum[SCAN_THREADS / 32];
+    __shared__ uint32_t s_cand[CAND_STAGE];
+    __shared__ uint32_t s_ncand, s_gbase;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) s_ncand = 0;
+    if (a.use_filter) {
+        const uint4* src = reinterpret_cast<const uint4*>(a.bitmap);
+        uint4* dst = reinterpret_cast<uint4*>(s_bitmap);
+        for (uint32_t i = threadIdx.x; i < GRAM_WORDS / 4; i += SCAN_THREADS) dst[i] = __ldg(src + i);
+    }
+    __syncthreads();
+    for (uint32_t tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+        const uint64_t tile_base = (uint64_t)tile * TILE_BYTES;
+        uint32_t cnt = 0;
+        const uint64_t pos0 = tile_base + (uint64_t)threadIdx.x * 16;
+        uint4 vnext = pos0 < a.len ? load16(a.text, pos0, a.len) : make_uint4(0, 0, 0, 0);
+#pragma unroll 1
+        for (int it = 0; it < SCAN_ITERS; ++it) {
+            const uint64_t pos = tile_base + ((uint64_t)it * SCAN_THREADS + threadIdx.x) * 16;
+            const uint4 v = vnext;
+            {   // the next iteration's 16 bytes are requested before this iteration's work starts
+                const uint64_t pn = pos + (uint64_t)SCAN_THREADS * 16;
+                vnext = (it + 1 < SCAN_ITERS && pn < a.len) ? load16(a.text, pn, a.len) : make_uint4(0, 0, 0, 0);
+            }
+            cnt += __popc(zero_byte_flags(v.x ^ 0x0A0A0A0Au)) + __popc(zero_byte_flags(v.y ^ 0x0A0A0A0Au)) +
+                   __popc(zero_byte_flags(v.z ^ 0x0A0A0A0Au)) + __popc(zero_byte_flags(v.w ^ 0x0A0A0A0Au));
+            if (!a.use_filter) continue;
+            uint32_t nxt = __shfl_down_sync(0xffffffffu, v.x, 1);
+            if (lane == 31) nxt = (pos + 16 < a.len) ? load4_safe(a.text, pos + 16, a.len) : 0u;
+            const uint32_t w[5] = {v.x | 0x20202020u, v.y | 0x20202020u, v.z | 0x20202020u, v.w | 0x20202020u, nxt | 0x20202020u};
+            uint32_t hits = 0;
+#pragma unroll
+            for (int i = 15; i >= 0; --i) {
+                const uint32_t win = (i & 3) ? __funnelshift_r(w[i >> 2], w[(i >> 2) + 1], (i & 3) * 8) : w[i >> 2];
+                const uint32_t h = win * GRAM_MUL;
+                const uint32_t word = s_bitmap[h >> (32 - GRAM_BITS + 5)];
+                hits = (hits << 1) | (__funnelshift_r(word, 0u, h >> (32 - GRAM_BITS)) & 1u);
+            }
+            if (pos >= a.len) hits = 0;
+            if (hits) {
+                uint32_t hm = hits;
+                while (hm) {
+                    const int i = __ffs(hm) - 1;
+                    hm &= hm - 1;
+                    const uint32_t win = (i & 3) ? __funnelshift_r(w[i >> 2], w[(i >> 2) + 1], (i & 3) * 8) : w[i >> 2];
+                    const uint32_t h2 = win * GRAM_MUL2;
+                    const uint32_t word = s_bitmap[h2 >> (32 - GRAM_BITS + 5)];
+                    if (!((word >> ((h2 >> (32 - GRAM_BITS)) & 31u)) & 1u)) hits &= ~(1u << i);
+                }
+            }
+            // hits go to a per-block staging buffer in shared memory (one shared-memory atomic per
+            // warp and iteration); the block publishes them with ONE global atomic per tile
+            const uint32_t n = __popc(hits);
+            if (__ballot_sync(0xffffffffu, n != 0)) {
+                uint32_t hinc = n;
+#pragma unroll
+                for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, hinc, o); if (lane >= o) hinc += t; }
+                const uint32_t total = __shfl_sync(0xffffffffu, hinc, 31);
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(&s_ncand, total);
+                base = __shfl_sync(0xffffffffu, base, 0) + hinc - n;
+                uint32_t hm = hits;
+                while (hm) {
+                    const int i = __ffs(hm) - 1;
+                    hm &= hm - 1;
+                    if (base < CAND_STAGE) s_cand[base] = (uint32_t)(pos + i);
+                    else {      // staging full (a tile dense with hits): straight to the global queue
+                        const uint32_t gi = atomicAdd(&a.ctr->n_cand, 1u);
+                        if (gi < a.cand_cap) a.cand[gi] = (uint32_t)(pos + i);
+                        else atomicOr(&a.ctr->overflow, 1u);
+                    }
+                    ++base;
+                }
+            }
+        }
+        for (int o = 16; o; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+        if (lane == 0) warp_sum[warp] = cnt;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint32_t sum = 0;
+            for (int q = 0; q < SCAN_THREADS / 32; ++q) sum += warp_sum[q];
+            a.tile_counts[tile] = sum;
+            const uint32_t staged = min(s_ncand, CAND_STAGE);
+            s_gbase = staged ? atomicAdd(&a.ctr->n_cand, staged) : 0u;
+        }
+        __syncthreads();
+        {
+            const uint32_t staged = min(s_ncand, CAND_STAGE), gbase = s_gbase;
+            for (uint32_t q = threadIdx.x; q < staged; q += SCAN_THREADS) {
+                if (gbase + q < a.cand_cap) a.cand[gbase + q] = s_cand[q];
+                else atomicOr(&a.ctr->overflow, 1u);
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) s_ncand = 0;
+        __syncthreads();
+    }
+}
+
 // exclusive scan of tile counts (one block); also publishes the total
 __global__ void __launch_bounds__(1024) k_scan_tiles(uint32_t* __restrict__ tile_counts, uint32_t n_tiles, uint32_t n_logs, Counters* ctr) {
     __shared__ uint32_t warp_tot[32];
@@ -176,132 +295,74 @@ struct ScanArgs {
     int use_filter;
 };
 
-__global__ void __launch_bounds__(SCAN_THREADS) k_lines_filter(ScanArgs a) {
-    extern __shared__ uint32_t s_bitmap[];
-    __shared__ uint32_t s_warp[2][SCAN_THREADS / 32];
+// Line offsets: every '\n' at p ends line g (at p, or p-1 after a '\r') and starts line g+1 at p+1;
+// log boundaries of a batch act as line breaks. One thread owns 64 contiguous bytes, so a tile
+// needs a single block-wide prefix of the per-thread newline counts.
+constexpr uint32_t LN_SPAN = 64;                                   // bytes per thread
+constexpr uint32_t LN_TILE_THREADS = TILE_BYTES / LN_SPAN;         // 512 threads cover one 32 KiB tile
+__global__ void __launch_bounds__(LN_TILE_THREADS) k_lines(ScanArgs a) {
+    __shared__ uint32_t s_warp[LN_TILE_THREADS / 32];
     __shared__ uint32_t s_k0, s_inner, s_events;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-
-    if (a.use_filter) {
-        const uint4* src = reinterpret_cast<const uint4*>(a.bitmap);
-        uint4* dst = reinterpret_cast<uint4*>(s_bitmap);
-        for (uint32_t i = threadIdx.x; i < GRAM_WORDS / 4; i += SCAN_THREADS) dst[i] = __ldg(src + i);
-    }
-    __syncthreads();
-
     for (uint32_t tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
         const uint64_t tile_base = (uint64_t)tile * TILE_BYTES;
         const uint64_t tile_end = tile_base + TILE_BYTES;
         if (threadIdx.x == 0) {
-            // log containing the first byte of the tile; any boundary strictly inside; any boundary event in [base,end)
             uint32_t j0 = upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, tile_base);
             s_k0 = j0 - 1;
             s_inner = (j0 <= a.n_logs && a.log_off[j0] < tile_end) ? 1u : 0u;
             uint32_t j1 = lower_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, tile_base);
             s_events = (j1 <= a.n_logs && a.log_off[j1] < tile_end) ? 1u : 0u;
         }
+        const uint64_t pos = tile_base + (uint64_t)threadIdx.x * LN_SPAN;
+        unsigned long long nl = 0;        // bit i: byte pos+i is '\n'
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const uint64_t cp = pos + 16 * q;
+            if (cp < a.len) {
+                const uint4 v = load16(a.text, cp, a.len);
+                const uint32_t f = zero_byte_flags(v.x ^ 0x0A0A0A0Au) | zero_byte_flags(v.y ^ 0x0A0A0A0Au) |
+                                   zero_byte_flags(v.z ^ 0x0A0A0A0Au) | zero_byte_flags(v.w ^ 0x0A0A0A0Au);
+                if (f) nl |= (unsigned long long)nl_mask16(v) << (16 * q);
+            }
+        }
+        const uint32_t cnt = __popcll(nl);
+        uint32_t inc = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
+        if (lane == 31) s_warp[warp] = inc;
         __syncthreads();
+        uint32_t wbase = 0;
+#pragma unroll
+        for (int w = 0; w < LN_TILE_THREADS / 32; ++w) { const uint32_t t = s_warp[w]; if (w < warp) wbase += t; }
+        const uint32_t excl = a.tile_prefix[tile] + wbase + inc - cnt;     // newlines before this thread's bytes
         const uint32_t k0 = s_k0;
         const bool inner = s_inner != 0, events = s_events != 0;
-        uint32_t running = a.tile_prefix[tile];
-
-#pragma unroll 1
-        for (int it = 0; it < SCAN_ITERS; ++it) {
-            const uint64_t pos = tile_base + ((uint64_t)it * SCAN_THREADS + threadIdx.x) * 16;
-            uint4 v = make_uint4(0, 0, 0, 0);
-            if (pos < a.len) v = load16(a.text, pos, a.len);
-            const uint32_t nlm = nl_mask16(v);
-            const uint32_t cnt = __popc(nlm);
-            // block-wide exclusive prefix of newline counts
-            uint32_t inc = cnt;
-#pragma unroll
-            for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
-            if (lane == 31) s_warp[it & 1][warp] = inc;
-            __syncthreads();
-            uint32_t wbase = 0, btotal = 0;
-#pragma unroll
-            for (int w = 0; w < SCAN_THREADS / 32; ++w) { uint32_t t = s_warp[it & 1][w]; if (w < warp) wbase += t; btotal += t; }
-            const uint32_t excl = running + wbase + inc - cnt;   // newlines before this thread's 16 bytes
-            running += btotal;
-
-            // ---- newline events
-            uint32_t m = nlm;
-            while (m) {
-                const int i = __ffs(m) - 1;
-                m &= m - 1;
-                const uint64_t p = pos + i;
-                uint32_t k = k0;
-                if (inner) k = upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, p) - 1;
-                const uint32_t g = excl + __popc(nlm & ((1u << i) - 1u)) + k;
-                const bool cr = p > a.log_off[k] && a.text[p - 1] == '\r';
-                if (g + 1 < a.line_cap) {
-                    a.line_end[g] = (uint32_t)(p - (cr ? 1 : 0));
-                    a.line_start[g + 1] = (uint32_t)(p + 1);
+        unsigned long long m = nl;
+        while (m) {
+            const int i = __ffsll((long long)m) - 1;
+            m &= m - 1;
+            const uint64_t p = pos + i;
+            uint32_t k = k0;
+            if (inner) k = upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, p) - 1;
+            const uint32_t g = excl + __popcll(nl & ((1ull << i) - 1ull)) + k;
+            const bool cr = p > a.log_off[k] && a.text[p - 1] == '\r';
+            if (g + 1 < a.line_cap) {
+                a.line_end[g] = (uint32_t)(p - (cr ? 1 : 0));
+                a.line_start[g + 1] = (uint32_t)(p + 1);
+            } else atomicOr(&a.ctr->overflow, 64u);
+        }
+        if (events && pos <= a.len) {     // start of log j / end of log j-1 inside this thread's bytes
+            uint32_t j = lower_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, pos);
+            while (j <= a.n_logs && a.log_off[j] < pos + LN_SPAN) {
+                const uint64_t b = a.log_off[j];
+                const uint32_t nlb = excl + __popcll(nl & ((1ull << (uint32_t)(b - pos)) - 1ull));
+                a.first_line[j] = nlb + j;
+                if (nlb + j < a.line_cap) {
+                    if (j < a.n_logs) { a.line_start[nlb + j] = (uint32_t)b; }
+                    if (j > 0) a.line_end[nlb + j - 1] = (uint32_t)b;
                 } else atomicOr(&a.ctr->overflow, 64u);
-            }
-            // ---- log boundary events (start of log k / end of log k-1) falling in this thread's 16 bytes
-            if (events && pos <= a.len) {
-                uint32_t j = lower_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, pos);
-                while (j <= a.n_logs && a.log_off[j] < pos + 16) {
-                    const uint64_t b = a.log_off[j];
-                    const uint32_t nlb = excl + __popc(nlm & ((1u << (uint32_t)(b - pos)) - 1u));
-                    a.first_line[j] = nlb + j;
-                    if (nlb + j < a.line_cap) {
-                        if (j < a.n_logs) { a.line_start[nlb + j] = (uint32_t)b; }
-                        if (j > 0) a.line_end[nlb + j - 1] = (uint32_t)b;
-                    } else atomicOr(&a.ctr->overflow, 64u);
-                    ++j;
-                }
-            }
-            // ---- gram prefilter over the 16 windows that start in this thread's bytes:
-            // two-probe Bloom test; the first probe is evaluated for every window, the second only
-            // on the (rare) first-probe hits
-            if (a.use_filter) {
-                uint32_t nxt = __shfl_down_sync(0xffffffffu, v.x, 1);
-                if (lane == 31) nxt = (pos + 16 < a.len) ? load4_safe(a.text, pos + 16, a.len) : 0u;
-                const uint32_t w[5] = {v.x | 0x20202020u, v.y | 0x20202020u, v.z | 0x20202020u, v.w | 0x20202020u, nxt | 0x20202020u};
-                uint32_t hits = 0;
-#pragma unroll
-                for (int i = 15; i >= 0; --i) {
-                    const uint32_t win = (i & 3) ? __funnelshift_r(w[i >> 2], w[(i >> 2) + 1], (i & 3) * 8) : w[i >> 2];
-                    const uint32_t h = win * GRAM_MUL;
-                    const uint32_t word = s_bitmap[h >> (32 - GRAM_BITS + 5)];
-                    hits = (hits << 1) | (__funnelshift_r(word, 0u, h >> (32 - GRAM_BITS)) & 1u);
-                }
-                if (pos >= a.len) hits = 0;
-                if (hits) {   // second probe (independent hash) removes almost all false positives
-                    uint32_t hm = hits;
-                    while (hm) {
-                        const int i = __ffs(hm) - 1;
-                        hm &= hm - 1;
-                        const uint32_t win = (i & 3) ? __funnelshift_r(w[i >> 2], w[(i >> 2) + 1], (i & 3) * 8) : w[i >> 2];
-                        const uint32_t h2 = win * GRAM_MUL2;
-                        const uint32_t word = s_bitmap[h2 >> (32 - GRAM_BITS + 5)];
-                        if (!((word >> ((h2 >> (32 - GRAM_BITS)) & 31u)) & 1u)) hits &= ~(1u << i);
-                    }
-                }
-                const uint32_t n = __popc(hits);
-                if (__ballot_sync(0xffffffffu, n != 0)) {
-                    uint32_t hinc = n;
-#pragma unroll
-                    for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, hinc, o); if (lane >= o) hinc += t; }
-                    const uint32_t total = __shfl_sync(0xffffffffu, hinc, 31);
-                    uint32_t base = 0;
-                    if (lane == 0) base = atomicAdd(&a.ctr->n_cand, total);
-                    base = __shfl_sync(0xffffffffu, base, 0) + hinc - n;
-                    uint32_t hm = hits;
-                    while (hm) {
-                        const int i = __ffs(hm) - 1;
-                        hm &= hm - 1;
-                        const uint64_t p = pos + i;
-                        uint32_t k = k0;
-                        if (inner) k = upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, p) - 1;
-                        const uint32_t g = excl + __popc(nlm & ((1u << i) - 1u)) + k;
-                        if (base < a.cand_cap) a.cand[base] = ((unsigned long long)g << 32) | (uint32_t)p;
-                        else atomicOr(&a.ctr->overflow, 1u);
-                        ++base;
-                    }
-                }
+                ++j;
             }
         }
         __syncthreads();
@@ -422,8 +483,12 @@ __device__ __forceinline__ void emit_record(Counters* ctr, unsigned long long* r
 struct ConfirmArgs {
     const uint8_t* text;
     uint64_t len;
-    const unsigned long long* cand;
+    const uint32_t* cand;
     uint32_t cand_cap;
+    const uint32_t* tile_prefix;     // exclusive newline count before each 32 KiB tile
+    uint32_t n_tiles;
+    const uint64_t* log_off;
+    uint32_t n_logs;
     const uint32_t* line_start;
     const uint32_t* line_end;
     uint32_t n_lines_total;
@@ -439,9 +504,7 @@ __device__ __forceinline__ bool dev_word(uint8_t b) { return (b >= '0' && b <= '
 __global__ void __launch_bounds__(256) k_confirm(ConfirmArgs a, DevPlan P) {
     const uint32_t n = min(a.ctr->n_cand, a.cand_cap);
     for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < n; c += gridDim.x * blockDim.x) {
-        const unsigned long long cd = a.cand[c];
-        const uint32_t pos = (uint32_t)cd, g = (uint32_t)(cd >> 32);
-        if (g >= a.n_lines_total) continue;      // beyond the (under-estimated) line arrays: the call is re-run
+        const uint32_t pos = a.cand[c];
         uint32_t w = 0;
 #pragma unroll
         for (int i = 0; i < 4; ++i) if ((uint64_t)pos + i < a.len) w |= (uint32_t)a.text[pos + i] << (8 * i);
@@ -451,6 +514,18 @@ __global__ void __launch_bounds__(256) k_confirm(ConfirmArgs a, DevPlan P) {
         uint32_t key;
         while ((key = P.table_key[slot]) != 0 && key != f) slot = (slot + 1) & tmask;
         if (key == 0) continue;
+        // line of `pos`: the newline prefix of its tile (and its neighbour) brackets the index
+        const uint32_t t = pos / TILE_BYTES;
+        uint32_t glo = a.tile_prefix[t], ghi = (t + 1 < a.n_tiles ? a.tile_prefix[t + 1] : a.ctr->n_lines_total) + 1;
+        if (a.n_logs > 1) {
+            glo += upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, (uint64_t)t * TILE_BYTES) - 1;
+            ghi += upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, (uint64_t)(t + 1) * TILE_BYTES);
+        }
+        const uint32_t gmax = min(a.ctr->n_lines_total, a.n_lines_total);
+        ghi = min(ghi, gmax);
+        if (glo >= ghi) continue;                 // beyond the (under-estimated) line arrays: the call is re-run
+        const uint32_t g = glo + upper_bound_dev<uint32_t>(a.line_start + glo, ghi - glo, pos) - 1;
+        if (g >= gmax || g + 1 == glo) continue;
         const uint32_t ls = a.line_start[g], le = a.line_end[g];
         const uint32_t lb = P.table_begin[slot], lc = P.table_count[slot];
         for (uint32_t q = 0; q < lc; ++q) {
@@ -1295,7 +1370,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     c->first_line.ensure((size_t)(n_logs + 1) * 4);
     c->n_lines.ensure((size_t)n_logs * 4);
     c->ctx_flags.ensure((line_cap / 4 + 2) * 4);
-    c->cand.ensure(c->est_cand * 8);
+    c->cand.ensure(c->est_cand * 4);
     c->tasks.ensure(c->est_tasks * 8);
     if (has_vm) { c->vm_tasks.ensure(c->est_vm_tasks * 8); c->vm_stack.ensure((size_t)vm_grid * vm_block * lpx::VM_STACK_WORDS * 4); }
     c->recs.ensure(rec_cap * 8);
@@ -1312,19 +1387,23 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     if (!c->plan.ctx_any_in_groups) CK(cudaMemsetAsync(c->ctx_flags.p, 0, (line_cap / 4 + 2) * 4, st));   // else k_dfa_scan writes every byte
 
     CK(cudaEventRecord(c->ev[0], st));
-    k_count_nl<<<std::min<uint32_t>(n_tiles, c->n_sm * 16), SCAN_THREADS, 0, st>>>(d_text, len, n_tiles, c->tile_counts.as<uint32_t>());
+    const size_t smem = use_filter ? GRAM_WORDS * 4 : 0;
+    FilterArgs fa{};
+    fa.text = d_text; fa.len = len; fa.n_tiles = n_tiles; fa.tile_counts = c->tile_counts.as<uint32_t>(); fa.bitmap = c->dp.bitmap;
+    fa.cand = c->cand.as<uint32_t>(); fa.cand_cap = (uint32_t)std::min<size_t>(c->est_cand, 0xFFFFFFFFu); fa.ctr = ctr;
+    fa.use_filter = use_filter ? 1 : 0;
+    CK(cudaEventRecord(c->ev[1], st));
+    k_filter_count<<<std::min<uint32_t>(n_tiles, (uint32_t)c->n_sm * 3), SCAN_THREADS, smem, st>>>(fa);
+    CK(cudaEventRecord(c->ev[2], st));
     k_scan_tiles<<<1, 1024, 0, st>>>(c->tile_counts.as<uint32_t>(), n_tiles, n_logs, ctr);
     ScanArgs sa{};
     sa.text = d_text; sa.len = len; sa.n_tiles = n_tiles; sa.tile_prefix = c->tile_counts.as<uint32_t>();
     sa.log_off = c->log_off.as<uint64_t>(); sa.n_logs = n_logs;
     sa.line_start = c->line_start.as<uint32_t>(); sa.line_end = c->line_end.as<uint32_t>();
     sa.first_line = c->first_line.as<uint32_t>(); sa.line_cap = (uint32_t)line_cap; sa.bitmap = c->dp.bitmap;
-    sa.cand = c->cand.as<unsigned long long>(); sa.cand_cap = (uint32_t)std::min<size_t>(c->est_cand, 0xFFFFFFFFu);
-    sa.ctr = ctr; sa.use_filter = use_filter ? 1 : 0;
-    const size_t smem = use_filter ? GRAM_WORDS * 4 : 0;
-    CK(cudaEventRecord(c->ev[1], st));
-    k_lines_filter<<<std::min<uint32_t>(n_tiles, (uint32_t)c->n_sm * 3), SCAN_THREADS, smem, st>>>(sa);
-    CK(cudaEventRecord(c->ev[2], st));
+    sa.cand = nullptr; sa.cand_cap = 0;
+    sa.ctr = ctr; sa.use_filter = 0;      // offsets only: the prefilter ran in k_filter_count
+    k_lines<<<std::min<uint32_t>(n_tiles, (uint32_t)c->n_sm * 4), LN_TILE_THREADS, 0, st>>>(sa);
     k_log_meta<<<blocks_for(n_logs, 128), 128, 0, st>>>(c->first_line.as<uint32_t>(), c->line_start.as<uint32_t>(),
                                                          c->line_end.as<uint32_t>(), n_logs, (uint32_t)line_cap, c->n_lines.as<uint32_t>());
     c->launches += 4;
@@ -1338,7 +1417,8 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     va.vm_stack = c->vm_stack.as<uint32_t>();
     if (use_filter) {
         ConfirmArgs ca{};
-        ca.text = d_text; ca.len = len; ca.cand = c->cand.as<unsigned long long>(); ca.cand_cap = sa.cand_cap;
+        ca.text = d_text; ca.len = len; ca.cand = c->cand.as<uint32_t>(); ca.cand_cap = fa.cand_cap;
+        ca.tile_prefix = c->tile_counts.as<uint32_t>(); ca.n_tiles = n_tiles; ca.log_off = c->log_off.as<uint64_t>(); ca.n_logs = n_logs;
         ca.line_start = c->line_start.as<uint32_t>(); ca.line_end = c->line_end.as<uint32_t>(); ca.n_lines_total = (uint32_t)line_cap;
         ca.tasks = c->tasks.as<unsigned long long>(); ca.task_cap = va.task_cap; ca.ctr = ctr;
         ca.vm_tasks = c->vm_tasks.as<unsigned long long>(); ca.vm_task_cap = va.vm_task_cap;
@@ -1552,7 +1632,8 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count) {
     c->tm.kernel_launches = c->launches;
     c->tm.candidates = h.n_cand;
     c->tm.verify_tasks = (uint64_t)h.n_tasks + h.n_vm_tasks + (uint64_t)G * (c->plan.always_list.size() + c->plan.always_vm_list.size());
-    c->tm.scan_bytes = c->pend.len + 4ull * ((uint64_t)G + 1) + 8ull * m;
+    // k_filter_count: the log read once, one count per tile and one position per candidate written
+    c->tm.scan_bytes = c->pend.len + 4ull * ((c->pend.len + TILE_BYTES) / TILE_BYTES) + 4ull * h.n_cand;
     c->tm.dfa_scan_bytes = c->d_group_blob.empty() ? 0 : c->pend.len + 8ull * ((uint64_t)G + 1) + (uint64_t)G;
     if (!c->plan.lit_off.empty() && (uint64_t)h.n_cand * 2 > (uint64_t)G + 1024 && c->recalibrations < 2) { c->calibrated = false; ++c->recalibrations; }
     c->pend.valid = false;
@@ -1641,7 +1722,7 @@ lp_ctx* lp_create(const lp_scoring_cfg* cfg, int device) {
         cudaDeviceProp prop;
         CK(cudaGetDeviceProperties(&prop, device));
         ctx->n_sm = prop.multiProcessorCount;
-        CK(cudaFuncSetAttribute(k_lines_filter, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(GRAM_WORDS * 4)));
+        CK(cudaFuncSetAttribute(k_filter_count, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(GRAM_WORDS * 4)));
         CK(cudaFuncSetAttribute(k_dfa_scan<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
         CK(cudaFuncSetAttribute(k_dfa_scan<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
         CK(cudaFuncSetAttribute(k_dfa_scan<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
