@@ -479,6 +479,39 @@ __device__ __forceinline__ void emit_record(Counters* ctr, unsigned long long* r
     }
 }
 
+// Block-level staging of queue output: entries are collected in shared memory (shared-memory
+// atomics only) and published with one global atomic per flush, so no warp waits on a global atomic.
+constexpr uint32_t Q_STAGE = 2048;
+struct QStage {
+    unsigned long long buf[Q_STAGE];
+    uint32_t n, base;
+};
+__device__ __forceinline__ void stage_put(QStage& sg, Counters* ctr, unsigned int* gcount, unsigned long long* gbuf, uint32_t cap,
+                                          uint32_t overflow_bit, unsigned long long key) {
+    const uint32_t idx = atomicAdd(&sg.n, 1u);
+    if (idx < Q_STAGE) sg.buf[idx] = key;
+    else {      // staging full: straight to the global queue
+        const uint32_t gi = atomicAdd(gcount, 1u);
+        if (gi < cap) gbuf[gi] = key; else atomicOr(&ctr->overflow, overflow_bit);
+    }
+}
+// all threads of the block; `force` flushes whatever is staged, otherwise only a nearly full buffer
+__device__ __forceinline__ void stage_flush(QStage& sg, Counters* ctr, unsigned int* gcount, unsigned long long* gbuf, uint32_t cap,
+                                            uint32_t overflow_bit, bool force) {
+    __syncthreads();
+    const uint32_t staged = min(sg.n, Q_STAGE);
+    if (staged == 0 || (!force && staged < Q_STAGE - 2 * blockDim.x)) return;     // block-uniform
+    if (threadIdx.x == 0) sg.base = atomicAdd(gcount, staged);
+    __syncthreads();
+    const uint32_t base = sg.base;
+    for (uint32_t q = threadIdx.x; q < staged; q += blockDim.x) {
+        if (base + q < cap) gbuf[base + q] = sg.buf[q]; else atomicOr(&ctr->overflow, overflow_bit);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) sg.n = 0;
+    __syncthreads();
+}
+
 // ------------------------------------------------------------------ K3: confirm gram hits -> (line, regex) tasks
 struct ConfirmArgs {
     const uint8_t* text;
@@ -502,8 +535,19 @@ struct ConfirmArgs {
 };
 __device__ __forceinline__ bool dev_word(uint8_t b) { return (b >= '0' && b <= '9') || (b >= 'A' && b <= 'Z') || b == '_' || (b >= 'a' && b <= 'z'); }
 __global__ void __launch_bounds__(256) k_confirm(ConfirmArgs a, DevPlan P) {
+    __shared__ QStage s_rec, s_task;
+    if (threadIdx.x == 0) { s_rec.n = 0; s_task.n = 0; }
+    __syncthreads();
     const uint32_t n = min(a.ctr->n_cand, a.cand_cap);
-    for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < n; c += gridDim.x * blockDim.x) {
+    const uint32_t stride = gridDim.x * blockDim.x;
+    const uint32_t rounds = (n + stride - 1) / stride;
+    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
+    for (uint32_t round = 0; round < rounds; ++round, c += stride) {
+      if (round) {
+          stage_flush(s_rec, a.ctr, &a.ctr->n_recs, a.recs, a.rec_cap, 4u, false);
+          stage_flush(s_task, a.ctr, &a.ctr->n_tasks, a.tasks, a.task_cap, 2u, false);
+      }
+      if (c < n) do {
         const uint32_t pos = a.cand[c];
         uint32_t w = 0;
 #pragma unroll
@@ -513,7 +557,7 @@ __global__ void __launch_bounds__(256) k_confirm(ConfirmArgs a, DevPlan P) {
         uint32_t slot = (f * GRAM_MUL2) >> (32 - P.table_bits);
         uint32_t key;
         while ((key = P.table_key[slot]) != 0 && key != f) slot = (slot + 1) & tmask;
-        if (key == 0) continue;
+        if (key == 0) break;
         // line of `pos`: the newline prefix of its tile (and its neighbour) brackets the index
         const uint32_t t = pos / TILE_BYTES;
         uint32_t glo = a.tile_prefix[t], ghi = (t + 1 < a.n_tiles ? a.tile_prefix[t + 1] : a.ctr->n_lines_total) + 1;
@@ -523,9 +567,9 @@ __global__ void __launch_bounds__(256) k_confirm(ConfirmArgs a, DevPlan P) {
         }
         const uint32_t gmax = min(a.ctr->n_lines_total, a.n_lines_total);
         ghi = min(ghi, gmax);
-        if (glo >= ghi) continue;                 // beyond the (under-estimated) line arrays: the call is re-run
+        if (glo >= ghi) break;                    // beyond the (under-estimated) line arrays: the call is re-run
         const uint32_t g = glo + upper_bound_dev<uint32_t>(a.line_start + glo, ghi - glo, pos) - 1;
-        if (g >= gmax || g + 1 == glo) continue;
+        if (g >= gmax || g + 1 == glo) break;
         const uint32_t ls = a.line_start[g], le = a.line_end[g];
         const uint32_t lb = P.table_begin[slot], lc = P.table_count[slot];
         for (uint32_t q = 0; q < lc; ++q) {
@@ -556,17 +600,11 @@ __global__ void __launch_bounds__(256) k_confirm(ConfirmArgs a, DevPlan P) {
                     bool hit = true;
                     if (mode & 2u) hit = (s > ls && dev_word(a.text[s - 1])) != dev_word(a.text[s]);
                     if (hit && (mode & 4u)) hit = dev_word(a.text[e2 - 1]) != (e2 < le && dev_word(a.text[e2]));
-                    if (hit) {
-                        const uint32_t idx = atomicAdd(&a.ctr->n_recs, 1u);
-                        if (idx < a.rec_cap) a.recs[idx] = ((unsigned long long)r << P.gb) | g;
-                        else atomicOr(&a.ctr->overflow, 4u);
-                    }
+                    if (hit) stage_put(s_rec, a.ctr, &a.ctr->n_recs, a.recs, a.rec_cap, 4u, ((unsigned long long)r << P.gb) | g);
                     continue;
                 }
                 if (P.rx_kind[r] == 0) {
-                    const uint32_t idx = atomicAdd(&a.ctr->n_tasks, 1u);
-                    if (idx < a.task_cap) a.tasks[idx] = ((unsigned long long)r << 32) | g;
-                    else atomicOr(&a.ctr->overflow, 2u);
+                    stage_put(s_task, a.ctr, &a.ctr->n_tasks, a.tasks, a.task_cap, 2u, ((unsigned long long)r << 32) | g);
                 } else {
                     const uint32_t idx = atomicAdd(&a.ctr->n_vm_tasks, 1u);
                     if (idx < a.vm_task_cap) a.vm_tasks[idx] = ((unsigned long long)r << 32) | g;
@@ -574,7 +612,10 @@ __global__ void __launch_bounds__(256) k_confirm(ConfirmArgs a, DevPlan P) {
                 }
             }
         }
+      } while (false);
     }
+    stage_flush(s_rec, a.ctr, &a.ctr->n_recs, a.recs, a.rec_cap, 4u, true);
+    stage_flush(s_task, a.ctr, &a.ctr->n_tasks, a.tasks, a.task_cap, 2u, true);
 }
 
 // ------------------------------------------------------------------ K4: verify tasks
@@ -599,21 +640,23 @@ struct VerifyArgs {
     uint32_t* vm_stack;               // VM_STACK_WORDS words per thread of the VM grid
 };
 __global__ void __launch_bounds__(256) k_verify(VerifyArgs a, DevPlan P) {
+    __shared__ QStage sg;
+    if (threadIdx.x == 0) sg.n = 0;
+    __syncthreads();
     const uint32_t n = min(a.ctr->n_tasks, a.task_cap);
     const uint32_t stride = gridDim.x * blockDim.x;
     const uint32_t rounds = (n + stride - 1) / stride;
     uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     for (uint32_t it = 0; it < rounds; ++it, t += stride) {
-        bool hit = false;
-        uint32_t r = 0, g = 0;
         if (t < n) {
             const unsigned long long task = a.tasks[t];
-            r = (uint32_t)(task >> 32);
-            g = (uint32_t)task;
-            if (P.rx_kind[r] == 0) hit = dfa_walk(P, r, a.text, a.len, a.line_start[g], a.line_end[g]);
+            const uint32_t r = (uint32_t)(task >> 32), g = (uint32_t)task;
+            if (P.rx_kind[r] == 0 && dfa_walk(P, r, a.text, a.len, a.line_start[g], a.line_end[g]))
+                stage_put(sg, a.ctr, &a.ctr->n_recs, a.recs, a.rec_cap, 4u, ((unsigned long long)r << P.gb) | g);
         }
-        emit_record(a.ctr, a.recs, a.rec_cap, P.gb, hit, r, g);
+        stage_flush(sg, a.ctr, &a.ctr->n_recs, a.recs, a.rec_cap, 4u, false);
     }
+    stage_flush(sg, a.ctr, &a.ctr->n_recs, a.recs, a.rec_cap, 4u, true);
 }
 // regexes without a usable literal: every (untrimmed) line is a candidate
 __global__ void __launch_bounds__(256) k_verify_always(VerifyArgs a, DevPlan P) {
