@@ -1046,7 +1046,19 @@ __global__ void __launch_bounds__(128) k_score(ScoreArgs a, DevPlan P, ScoreCfg 
         const int slot = P.pat_slot[p];
         if (slot >= 0) {
             const unsigned long long pr = a.prior ? a.prior[P.slot_first_pat[slot]] : 0ull;
-            const unsigned long long cnt = pr + a.rank_in_slot[e];
+            // events of this frequency slot that come earlier in discovery order (whole batch): for
+            // every pattern q sharing the id, the records of its primary on earlier lines, plus the
+            // one on this line when q precedes p
+            unsigned long long earlier = 0;
+            for (uint32_t j = P.slot_begin[slot]; j < P.slot_begin[slot + 1]; ++j) {
+                const uint32_t q = P.slot_pats[j], rq = P.pat_primary[q];
+                const uint32_t b = a.rx_begin[rq], cnt2 = a.rx_begin[rq + 1] - b;
+                const unsigned long long want = ((unsigned long long)rq << P.gb) | g;
+                const uint32_t at = lower_bound_dev<unsigned long long>(a.keys + b, cnt2, want);
+                earlier += at;
+                if (q < p && at < cnt2 && a.keys[b + at] == want) earlier += 1;
+            }
+            const unsigned long long cnt = pr + earlier;
             if (cnt > 0) {
                 const double rate = __ddiv_rn((double)cnt, (double)C.hours);
                 if (rate > C.freq_thr) pen = fmin(C.max_pen, __ddiv_rn(__dsub_rn(rate, C.freq_thr), C.freq_thr));
@@ -1281,6 +1293,8 @@ void upload_plan(lp_ctx* c) {
     d.pat_after = upload(K, pl.pat_after);
     d.pat_slot = upload(K, pl.pat_slot);
     d.slot_first_pat = upload(K, pl.slot_first_pat);
+    d.slot_begin = upload(K, pl.slot_begin);
+    d.slot_pats = upload(K, pl.slot_pats);
     d.sec_begin = upload(K, pl.sec_begin);
     d.sec_rx = upload(K, pl.sec_rx);
     d.sec_weight = upload(K, pl.sec_weight);
@@ -1579,9 +1593,6 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count) {
     k_event_prep<<<gb, 256, 0, st>>>(c->ev_key.as<unsigned long long>(), ctr, mc, c->dp, c->first_line.as<uint32_t>(), n_logs, n_slots,
                                      c->ev_log.as<uint32_t>(), c->slot_key.as<uint32_t>(), c->ev_idx.as<uint32_t>(),
                                      c->freq_delta.as<unsigned long long>());
-    sort_pairs<uint32_t, uint32_t>(c, c->slot_key.as<uint32_t>(), c->slot_key_alt.as<uint32_t>(), c->ev_idx.as<uint32_t>(),
-                                   c->ev_idx_alt.as<uint32_t>(), mc, bits_for(n_slots + 1));
-    k_slot_rank<<<gb, 256, 0, st>>>(c->slot_key_alt.as<uint32_t>(), c->ev_idx_alt.as<uint32_t>(), mc, n_slots, c->rank_in_slot.as<uint32_t>());
     ScoreArgs sa{};
     sa.ev_key = c->ev_key.as<unsigned long long>(); sa.m_cap = mc; sa.ctr = ctr; sa.ev_log = c->ev_log.as<uint32_t>();
     sa.rank_in_slot = c->rank_in_slot.as<uint32_t>(); sa.prior = prior_d;
@@ -1594,7 +1605,7 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count) {
     k_score<<<blocks_for(mc, 128), 128, 0, st>>>(sa, c->dp, c->sc);
     k_log_event_begin<<<blocks_for(n_logs + 1, 128), 128, 0, st>>>(c->ev_key.as<unsigned long long>(), ctr, c->first_line.as<uint32_t>(),
                                                                    n_logs, c->dp.pb, c->log_event_begin.as<unsigned long long>());
-    c->launches += 4;
+    c->launches += 3;
     if (!(options & LP_OPT_NO_RANK)) {
         // stable sort by descending score (ties keep discovery order), then stably by log
         sort_pairs<unsigned long long, uint32_t>(c, c->sort_key.as<unsigned long long>(), c->sort_key_alt.as<unsigned long long>(),

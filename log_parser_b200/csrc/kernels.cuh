@@ -59,6 +59,8 @@ struct DevPlan {
     const int32_t* pat_after;
     const int32_t* pat_slot;
     const uint32_t* slot_first_pat;
+    const uint32_t* slot_begin;
+    const uint32_t* slot_pats;
     const uint32_t* sec_begin;
     const uint32_t* sec_rx;
     const double* sec_weight;

@@ -223,6 +223,12 @@ void build_plan(const std::vector<PlanPatternIn>& pats, Plan& pl, int64_t* bad) 
         pl.seq_begin.push_back((uint32_t)pl.seq_bonus.size());
     }
     if (bad) *bad = -1;
+    {
+        std::vector<std::vector<uint32_t>> members(pl.slot_first_pat.size());
+        for (uint32_t p2 = 0; p2 < pl.n_pat; ++p2) if (pl.pat_slot[p2] >= 0) members[pl.pat_slot[p2]].push_back(p2);
+        pl.slot_begin.assign(1, 0);
+        for (auto& v : members) { pl.slot_pats.insert(pl.slot_pats.end(), v.begin(), v.end()); pl.slot_begin.push_back((uint32_t)pl.slot_pats.size()); }
+    }
     by_primary.resize(pl.n_rx);
     pl.rxp_begin.assign(pl.n_rx + 1, 0);
     for (uint32_t r = 0; r < pl.n_rx; ++r) {

@@ -79,6 +79,7 @@ struct Plan {
     std::vector<int32_t> pat_has_ctx, pat_before, pat_after;
     std::vector<int32_t> pat_slot;                    // frequency slot or -1 (FTS keys by id string)
     std::vector<uint32_t> slot_first_pat;
+    std::vector<uint32_t> slot_begin, slot_pats;      // CSR frequency slot -> patterns sharing that id
     std::vector<uint32_t> sec_begin, sec_rx; std::vector<double> sec_weight; std::vector<int32_t> sec_window;
     std::vector<uint32_t> seq_begin, seq_ev_begin, ev_rx; std::vector<double> seq_bonus;
     std::vector<uint32_t> rxp_begin, rxp_pat;         // CSR primary regex -> patterns (list order)
