@@ -290,3 +290,20 @@ def test_sharded_blocks_equal_one_batch(parser):
     np.testing.assert_array_equal(np.concatenate(pats), whole.pattern)
     np.testing.assert_array_equal(np.concatenate(scores), whole.score)
     np.testing.assert_array_equal(prior, whole.freq_delta)
+
+
+def test_c4_shape_large_windows(oracle):
+    """configs[3] shape at a size the oracle finishes: dense secondary matches, proximity windows up
+    to scoring.proximity.max-window = 1000, context +-500 lines, 3 secondaries + 2 sequences per pattern."""
+    cfg = ScoringConfig(max_window=1000)
+    wl = synth.make_patterns(30, 4040, scoring_heavy=True, noliteral=0)
+    log = synth.make_log(wl, 6000, 4041, hit_rate=0.05, symptom_rate=0.4, phase_rate=0.01, pool_blocks=1500)
+    lp = binding.LogParser(cfg)
+    lp.load_patterns(wl.patterns)
+    res = lp.analyze(log, options=binding.OPT_FACTORS)
+    ora = oracle.analyze(cfg, wl.patterns, log)
+    assert len(ora.line) > 100
+    assert (ora.factors[:, 3] > 1.0).mean() > 0.5      # proximity bonus present on most events
+    _check(res, ora)
+    np.testing.assert_array_equal(res.score, ora.score)
+    lp.close()
