@@ -191,6 +191,9 @@ def main():
     ap.add_argument("--ref-threads", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs)")
+    ap.add_argument("--shard", default="logs", choices=["logs", "lines"],
+                    help="N>1 only. logs: one C2 log per GPU (weak scaling, the default); lines: ONE C2 log cut by line range "
+                         "with halos over the GPUs (strong scaling, lp_range_*)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
 
@@ -202,6 +205,11 @@ def main():
               "parallelism": f"sharded by log over {world} GPU(s); per-pattern frequency counts all-gathered over NCCL" if world > 1 else "1 GPU",
               "l2": "3 device copies of the log at distinct addresses, rotated per step (420 MB > 126 MB L2)"}
 
+    by_lines = args.shard == "lines" and world > 1
+    if by_lines:
+        config["logs_per_gpu"] = 1.0 / world
+        config["parallelism"] = (f"ONE log cut by line range over {world} GPUs with halos of lp_range_halo_lines() lines; "
+                                 "one NCCL all-gather of the shard summaries (line counts, per-pattern counts, sequence-chain states)")
     if args.impl == "reference":
         if rank != 0:
             return 0
@@ -232,13 +240,19 @@ def main():
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
-    wl, log = build_workload(args, rank)
+    wl, log = build_workload(args, 0 if by_lines else rank)
     nbytes = len(log)
     config["workload"] = config["workload"].format(nbytes / 1e6)
     lp = binding.LogParser(ScoringConfig(), device=local_rank)
     lp.load_patterns(wl.patterns)
     P = len(wl.patterns)
 
+    halo_b = halo_a = 0
+    if by_lines:      # this rank keeps only its own line range + halos
+        end = parallel.strip_trailing_separators(log)
+        tb, te, halo_b, halo_a = parallel.split_line_ranges(log, world, lp.range_halo_lines(), end)[rank]
+        log = bytes(log[tb:te])
+        nbytes_all, nbytes = nbytes, len(log)
     host = torch.from_numpy(np.frombuffer(log, dtype=np.uint8).copy()).pin_memory()
     copies = [host.to(f"cuda:{local_rank}", non_blocking=False).clone() for _ in range(3)]
     off = np.array([0, nbytes], dtype=np.uint64)
@@ -248,6 +262,9 @@ def main():
         d = copies[i % len(copies)]
         if world == 1:
             return lp.analyze_device(d.data_ptr(), nbytes)
+        if by_lines:
+            summary = lp.range_scan_device(d.data_ptr(), nbytes, halo_b, halo_a)
+            return lp.range_score(parallel.gather_summaries(summary, world), rank, world)
         counts = lp.batch_scan_device(d.data_ptr(), off)
         prior, _total = parallel.exclusive_prefix(counts, rank, world)     # one NCCL all-gather of P x int64
         return lp.batch_score(prior)
@@ -288,24 +305,35 @@ def main():
     if world > 1:
         dist.all_reduce(el, op=dist.ReduceOp.MAX)
     dev_s, wall_s = float(el[0]), float(el[1])
-    total_lines = args.lines * world * args.steps
+    total_lines = args.lines * (1 if by_lines else world) * args.steps
     value = total_lines / dev_s
 
     # ---- e2e: host buffer in, events out, through lp_analyze (the call the JVM makes)
     e2e_steps = 0 if args.no_e2e else max(3, min(args.steps, 10))
     r2 = res
+
+    def step_host():
+        if not by_lines:
+            return lp.analyze_host_ptr(host.data_ptr(), nbytes)
+        with torch.cuda.stream(lib_stream):
+            copies[0].copy_(host, non_blocking=True)          # own range + halos, pinned host -> device on the library stream
+        summary = lp.range_scan_device(copies[0].data_ptr(), nbytes, halo_b, halo_a)
+        return lp.range_score(parallel.gather_summaries(summary, world), rank, world)
+
     for i in range(0 if args.no_e2e else 2):
-        r2 = lp.analyze_host_ptr(host.data_ptr(), nbytes)
+        r2 = step_host()
     barrier()
     t0 = time.perf_counter()
     for i in range(e2e_steps):
-        r2 = lp.analyze_host_ptr(host.data_ptr(), nbytes)
+        r2 = step_host()
     barrier()
     e2e_wall = time.perf_counter() - t0
     el2 = torch.tensor([e2e_wall], dtype=torch.float64, device=f"cuda:{local_rank}")
     if world > 1:
         dist.all_reduce(el2, op=dist.ReduceOp.MAX)
-    e2e_value = args.lines * world * e2e_steps / max(float(el2[0]), 1e-9)
+    e2e_value = args.lines * (1 if by_lines else world) * e2e_steps / max(float(el2[0]), 1e-9)
+    if by_lines:
+        nbytes = nbytes_all
     d2h = int(r2.n_events * (4 + 4 + 8 + 4) + P * 8 + 8 * 3)
 
     if rank == 0:
@@ -314,7 +342,7 @@ def main():
         achieved = (sum(scan_bytes) / len(scan_bytes)) / scan_s / 1e9
         line = {
             "metric": METRIC, "value": value, "unit": "lines/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": 1e3 * dev_s / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": 1e3 * dev_s / args.steps, "higher_is_better": True, "scaling": "strong" if by_lines else "weak", "vs_baseline": None,
             "dtype": "u8/f64", "data": "synthetic", "config": config,
             "gb_per_s": value * nbytes / args.lines / 1e9,
             "wall_ms_per_step": 1e3 * wall_s / args.steps,

@@ -141,6 +141,31 @@ int lp_batch_scan_device(lp_ctx* ctx, const uint8_t* d_logs, const uint64_t* off
                          int options, uint64_t* counts_out /* [n_patterns] */);
 int lp_batch_score(lp_ctx* ctx, const uint64_t* prior_count, lp_result** out);
 
+/* ONE log sharded by line range over several GPUs (second mode; the reference walks
+ * the whole log on one thread, AS:89-113). The host first removes the log's trailing separators
+ * (the trailing empty strings String.split drops, AS:53), cuts the rest on line boundaries into
+ * `world` contiguous pieces and gives every rank its piece plus up to lp_range_halo_lines() whole
+ * lines on either side, WITHOUT the separator that ends the text (so the text ends with the content
+ * of its last line). Halo lines feed only the windows of the rank's own lines:
+ *   proximity  min(max-window, proximity_window) lines either side     SS:319-328
+ *   sequence   5 lines either side for the last event                  SS:275-277
+ *   context    lines_before / lines_after                              AS:142-150
+ * Quantities that need the whole log travel in a per-rank summary of lp_range_summary_words()
+ * uint64 words, exchanged by the host with one all-gather:
+ *   [0] own line count -> global line numbers and the N of the chronological factor (SS:125)
+ *   [1] n_patterns, [2..] per-pattern event counts -> exclusive prefix for FTS:64-93
+ *   then, per sequence and per state its backward walk (SS:250-258, in forward form) can enter the
+ *   shard in: the state on exit and the own line where the last-but-one event was reached.
+ * lp_range_score composes them (ranks in text order) and scores this rank's lines; result line
+ * numbers are global, `log_n_lines[0]` is the whole log's N, `rank[]` orders this shard's events
+ * only (merge by score across shards on the host), freq_delta covers this shard's lines. */
+uint32_t lp_range_halo_lines(const lp_ctx* ctx);
+size_t lp_range_summary_words(const lp_ctx* ctx);
+int lp_range_scan_device(lp_ctx* ctx, const uint8_t* d_text, size_t len, uint32_t halo_before_lines,
+                         uint32_t halo_after_lines, int options, uint64_t* summary_out);
+int lp_range_score(lp_ctx* ctx, const uint64_t* summaries /* [world][words] */, uint32_t rank, uint32_t world,
+                   const uint64_t* prior_count, lp_result** out);
+
 /* No counterpart in the reference. Line splitting (the String.split step only) for hosts that may
  * not allocate GPU memory themselves or let a library do it on their behalf: processes with a
  * fixed device-memory plan, plugins living inside somebody else's allocator, callers for whom an

@@ -85,6 +85,7 @@ EXPORTS = [
     "lp_create", "lp_destroy", "lp_last_error", "lp_version", "lp_load_patterns", "lp_analyze", "lp_analyze_device",
     "lp_analyze_batch", "lp_analyze_batch_device", "lp_batch_scan_device", "lp_batch_score", "lp_result_get",
     "lp_result_free", "lp_get_timings", "lp_stream", "lp_split_lines_noalloc",
+    "lp_range_halo_lines", "lp_range_summary_words", "lp_range_scan_device", "lp_range_score",
 ]
 
 _lib = None
@@ -117,6 +118,12 @@ def load_library() -> C.CDLL:
     L.lp_get_timings.argtypes = [vp, C.POINTER(Timings)]
     L.lp_stream.restype = vp
     L.lp_stream.argtypes = [vp]
+    L.lp_range_halo_lines.restype = C.c_uint32
+    L.lp_range_halo_lines.argtypes = [vp]
+    L.lp_range_summary_words.restype = C.c_size_t
+    L.lp_range_summary_words.argtypes = [vp]
+    L.lp_range_scan_device.argtypes = [vp, u8p, C.c_size_t, C.c_uint32, C.c_uint32, C.c_int, u64p]
+    L.lp_range_score.argtypes = [vp, u64p, C.c_uint32, C.c_uint32, u64p, C.POINTER(vp)]
     L.lp_split_lines_noalloc.argtypes = [C.c_int, vp, C.c_size_t, vp, vp, C.c_size_t, vp, vp, C.c_char_p, C.c_size_t]
     # host-compiler introspection (CPU-only test tier)
     L.lp_debug_rx_compile.restype = vp
@@ -330,6 +337,30 @@ class LogParser:
         keep, pp = self._prior(prior_count)
         out = C.c_void_p()
         rc = self.L.lp_batch_score(self.h, pp, C.byref(out))
+        if rc != LP_OK:
+            _raise(rc)
+        return self._take(out)
+
+    # ---- one log sharded by line range (lp_range_*)
+    def range_halo_lines(self) -> int:
+        return int(self.L.lp_range_halo_lines(self.h))
+
+    def range_summary_words(self) -> int:
+        return int(self.L.lp_range_summary_words(self.h))
+
+    def range_scan_device(self, dev_ptr: int, length: int, halo_before: int, halo_after: int, options: int = 0) -> np.ndarray:
+        summary = np.zeros(max(1, self.range_summary_words()), np.uint64)
+        rc = self.L.lp_range_scan_device(self.h, dev_ptr, length, halo_before, halo_after, options,
+                                         summary.ctypes.data_as(C.POINTER(C.c_uint64)))
+        if rc != LP_OK:
+            _raise(rc)
+        return summary
+
+    def range_score(self, summaries: np.ndarray, rank: int, world: int, prior_count=None) -> Result:
+        sa = np.ascontiguousarray(summaries, dtype=np.uint64).reshape(world, -1)
+        keep, pp = self._prior(prior_count)
+        out = C.c_void_p()
+        rc = self.L.lp_range_score(self.h, sa.ctypes.data_as(C.POINTER(C.c_uint64)), rank, world, pp, C.byref(out))
         if rc != LP_OK:
             _raise(rc)
         return self._take(out)

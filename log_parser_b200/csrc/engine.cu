@@ -7,6 +7,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <limits>
 #include <memory>
 #include <mutex>
 #include <stdexcept>
@@ -371,13 +372,14 @@ __global__ void __launch_bounds__(LN_TILE_THREADS) k_lines(ScanArgs a) {
 
 // Java's Pattern.split(…, 0) drops trailing empty strings; no separator at all keeps [input].
 __global__ void k_log_meta(const uint32_t* __restrict__ first_line, const uint32_t* __restrict__ line_start,
-                           const uint32_t* __restrict__ line_end, uint32_t n_logs, uint32_t line_cap, uint32_t* __restrict__ n_lines) {
+                           const uint32_t* __restrict__ line_end, uint32_t n_logs, uint32_t line_cap, uint32_t no_trim,
+                           uint32_t* __restrict__ n_lines) {
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= n_logs) return;
     const uint32_t f = first_line[k];
     uint32_t n = first_line[k + 1] - f;
     if (first_line[k + 1] > line_cap) { n_lines[k] = 0; return; }     // line arrays overflowed: the call is retried
-    if (n > 1) {
+    if (n > 1 && !no_trim) {      // a line-range shard is cut from a log whose trailing empty lines are already gone
         while (n > 0 && line_end[f + n - 1] == line_start[f + n - 1]) --n;
     }
     n_lines[k] = n;
@@ -852,13 +854,17 @@ __global__ void k_ctx_flags(const unsigned long long* __restrict__ keys, const u
         atomicOr(&flags32[g >> 2], (1u << r) << ((g & 3) * 8));
     }
 }
+// Events are emitted for lines [core_lo, G - halo_after): the whole text unless it is a line-range
+// shard, whose halo lines only feed the windows of its own lines.
 __global__ void k_emit_events(const unsigned long long* __restrict__ keys, DevPlan P,
-                              unsigned long long* __restrict__ ev_key, uint32_t ev_cap, Counters* ctr) {
+                              unsigned long long* __restrict__ ev_key, uint32_t ev_cap, Counters* ctr, uint32_t core_lo, uint32_t halo_after) {
     const uint32_t n = ctr->n_unique;
+    const uint32_t core_hi = ctr->n_lines_total > halo_after ? ctr->n_lines_total - halo_after : 0;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const unsigned long long k = keys[i];
         const uint32_t r = (uint32_t)min(k >> P.gb, 0xFFFFFFFFull), g = (uint32_t)(k & ((1ull << P.gb) - 1ull));
         if (r >= P.n_rx) continue;     // padding sentinel
+        if (g < core_lo || g >= core_hi) continue;
         const uint32_t pb = P.rxp_begin[r], pe = P.rxp_begin[r + 1];
         if (pb == pe) continue;
         const uint32_t base = atomicAdd(&ctr->n_events, pe - pb);
@@ -917,6 +923,12 @@ struct ScoreArgs {
     double* out_score;
     double* out_factors;                  // may be null
     unsigned long long* sort_key;         // descending-score key for ranking
+    // line-range shard (n_global != 0): position of text line 0 in the whole log, the whole log's line
+    // count, the first own line, and the per-sequence chain thresholds composed over all shards
+    long long line_base;
+    long long n_global;
+    uint32_t core_lo;
+    const long long* seq_T;
 };
 
 __device__ __forceinline__ bool list_any_in(const unsigned long long* __restrict__ keys, uint32_t b, uint32_t e, uint32_t r, uint32_t gb,
@@ -942,7 +954,7 @@ __global__ void __launch_bounds__(128) k_score(ScoreArgs a, DevPlan P, ScoreCfg 
     const double sev = P.pat_sev[p];
 
     // chronological factor, SS:123-151
-    const double pos = __ddiv_rn((double)i, (double)N);
+    const double pos = a.n_global ? __ddiv_rn((double)(i + a.line_base), (double)a.n_global) : __ddiv_rn((double)i, (double)N);
     double chrono;
     if (pos <= C.early) {
         const double range = __dsub_rn(C.max_early, 1.5);
@@ -1001,7 +1013,8 @@ __global__ void __launch_bounds__(128) k_score(ScoreArgs a, DevPlan P, ScoreCfg 
                 if (!list_any_in(a.keys, a.rx_begin[rl], a.rx_begin[rl + 1], rl, P.gb, first + (uint32_t)nlo, first + (uint32_t)nhi)) continue;
                 bool ok = true;
                 long long T = -1;   // local line of the earliest feasible position of the previous event
-                for (uint32_t j = eb; j + 1 < ee && ok; ++j) {
+                if (a.seq_T) ok = a.seq_T[q] < i + a.line_base;
+                else for (uint32_t j = eb; j + 1 < ee && ok; ++j) {
                     const uint32_t r = P.ev_rx[j];
                     const uint32_t b = a.rx_begin[r], en = a.rx_begin[r + 1];
                     const unsigned long long want = ((unsigned long long)r << P.gb) | (uint32_t)(first + T + 1);
@@ -1056,6 +1069,7 @@ __global__ void __launch_bounds__(128) k_score(ScoreArgs a, DevPlan P, ScoreCfg 
                 const unsigned long long want = ((unsigned long long)rq << P.gb) | g;
                 const uint32_t at = lower_bound_dev<unsigned long long>(a.keys + b, cnt2, want);
                 earlier += at;
+                if (a.n_global) earlier -= lower_bound_dev<unsigned long long>(a.keys + b, cnt2, ((unsigned long long)rq << P.gb) | a.core_lo);
                 if (q < p && at < cnt2 && a.keys[b + at] == want) earlier += 1;
             }
             const unsigned long long cnt = pr + earlier;
@@ -1073,7 +1087,7 @@ __global__ void __launch_bounds__(128) k_score(ScoreArgs a, DevPlan P, ScoreCfg 
     s = __dmul_rn(s, ctx);
     s = __dmul_rn(s, __dsub_rn(1.0, pen));
 
-    a.out_line[e] = (uint32_t)(i + 1);
+    a.out_line[e] = (uint32_t)(i + a.line_base + 1);
     a.out_pat[e] = p;
     a.out_score[e] = s;
     if (a.out_factors) {
@@ -1096,11 +1110,45 @@ __global__ void k_gather_u32(const uint32_t* __restrict__ src, const uint32_t* _
     uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j < n) dst[j] = src[idx[j]];
 }
-__global__ void k_count_per_pattern(const unsigned long long* __restrict__ keys, const Counters* ctr, DevPlan P, unsigned long long* __restrict__ counts) {
+// Line-range shards: the sequence chain of SS:250-258 (forward form) restricted to this
+// shard's own lines, for every state the chain can be in when it enters the shard. tab[off[q] + s] =
+// (state on exit) << 32 | (1 + own-line index where the last-but-one event was reached, 0 if not reached).
+__global__ void k_range_tables(const unsigned long long* __restrict__ keys, const uint32_t* __restrict__ rx_begin, DevPlan P, const Counters* ctr,
+                               uint32_t n_seq, const uint32_t* __restrict__ tab_off, uint32_t core_lo, uint32_t halo_after,
+                               unsigned long long* __restrict__ tab) {
+    const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+    if (q >= n_seq) return;
+    const uint32_t core_hi = ctr->n_lines_total > halo_after ? ctr->n_lines_total - halo_after : 0;
+    const uint32_t eb = P.seq_ev_begin[q], ee = P.seq_ev_begin[q + 1];
+    const uint32_t k = ee - eb;
+    if (k < 2) return;
+    const unsigned long long gmask = (1ull << P.gb) - 1ull;
+    for (uint32_t s = 0; s + 1 < k; ++s) {
+        uint32_t j = s;
+        long long T = (long long)core_lo - 1;
+        while (j + 1 < k) {
+            const uint32_t r = P.ev_rx[eb + j];
+            const uint32_t b = rx_begin[r], en = rx_begin[r + 1];
+            const unsigned long long want = ((unsigned long long)r << P.gb) | (uint32_t)(T + 1);
+            const uint32_t at = b + lower_bound_dev<unsigned long long>(keys + b, en - b, want);
+            if (at >= en) break;
+            const uint32_t l = (uint32_t)(keys[at] & gmask);
+            if (l >= core_hi) break;
+            T = l;
+            ++j;
+        }
+        tab[tab_off[q] + s] = ((unsigned long long)j << 32) | (j + 1 == k ? (unsigned long long)(T - core_lo + 1) : 0ull);
+    }
+}
+__global__ void k_count_per_pattern(const unsigned long long* __restrict__ keys, const Counters* ctr, DevPlan P, unsigned long long* __restrict__ counts,
+                                    uint32_t core_lo, uint32_t halo_after) {
     const uint32_t n = ctr->n_unique;
+    const uint32_t core_hi = ctr->n_lines_total > halo_after ? ctr->n_lines_total - halo_after : 0;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const uint32_t r = (uint32_t)min(keys[i] >> P.gb, 0xFFFFFFFFull);
         if (r >= P.n_rx) continue;
+        const uint32_t g = (uint32_t)(keys[i] & ((1ull << P.gb) - 1ull));
+        if (g < core_lo || g >= core_hi) continue;
         for (uint32_t j = P.rxp_begin[r]; j < P.rxp_begin[r + 1]; ++j) atomicAdd(&counts[P.rxp_pat[j]], 1ull);
     }
 }
@@ -1213,7 +1261,12 @@ struct lp_ctx {
         uint64_t len = 0;
         uint32_t n_logs = 0, G = 0, n_unique = 0, m = 0;
         int options = 0;
+        bool range = false;                 // line-range shard: events only for the lines between the halos
+        uint32_t halo_before = 0, halo_after = 0;
     } pend;
+    DevBuf seq_tab_off, seq_tab, seq_T;
+    std::vector<uint32_t> h_seq_tab_off;    // per sequence, offset of its chain table in a shard summary
+    uint32_t n_seq = 0;
 
     cudaEvent_t ev[9]{};
     lp_timings tm{};
@@ -1382,7 +1435,10 @@ void check_estimates(lp_ctx* c, const Counters& h, uint32_t n_logs, bool events_
 
 // ---- phase 1: split + prefilter + verify + sorted unique records + events in discovery order.
 // Launches only; the caller synchronises.
-void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_off, uint32_t n_logs, int options) {
+struct RangeShard { uint32_t halo_before, halo_after; };
+
+void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_off, uint32_t n_logs, int options,
+              const RangeShard* rg = nullptr) {
     if (!c->loaded) throw std::invalid_argument("lp_load_patterns has not been called");
     if (len >= 0xFFFFFFF0ull) throw LimitFail("log/batch larger than 4 GiB - 16 bytes; shard it (see DESIGN.md)");
     if (n_logs == 0) throw std::invalid_argument("n_logs == 0");
@@ -1462,7 +1518,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     sa.ctr = ctr; sa.use_filter = 0;      // offsets only: the prefilter ran in k_filter_count
     k_lines<<<std::min<uint32_t>(n_tiles, (uint32_t)c->n_sm * 4), LN_TILE_THREADS, 0, st>>>(sa);
     k_log_meta<<<blocks_for(n_logs, 128), 128, 0, st>>>(c->first_line.as<uint32_t>(), c->line_start.as<uint32_t>(),
-                                                         c->line_end.as<uint32_t>(), n_logs, (uint32_t)line_cap, c->n_lines.as<uint32_t>());
+                                                         c->line_end.as<uint32_t>(), n_logs, (uint32_t)line_cap, rg ? 1u : 0u, c->n_lines.as<uint32_t>());
     c->launches += 4;
 
     VerifyArgs va{};
@@ -1537,7 +1593,8 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         c->launches += 1;
     }
     // ---- events in discovery order (global line, pattern index)
-    k_emit_events<<<c->n_sm * 4, 256, 0, st>>>(c->recs.as<unsigned long long>(), c->dp, c->ev_key_alt.as<unsigned long long>(), (uint32_t)ev_cap, ctr);
+    k_emit_events<<<c->n_sm * 4, 256, 0, st>>>(c->recs.as<unsigned long long>(), c->dp, c->ev_key_alt.as<unsigned long long>(), (uint32_t)ev_cap, ctr,
+                                              rg ? rg->halo_before : 0u, rg ? rg->halo_after : 0u);
     sort_keys<unsigned long long>(c, c->ev_key_alt.as<unsigned long long>(), c->ev_key.as<unsigned long long>(), (uint32_t)ev_cap,
                                   std::min<int>(64, (int)c->dp.gb + (int)c->dp.pb + 1));
     c->launches += 1;
@@ -1545,6 +1602,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     c->pend.valid = true;
     c->pend.d_text = d_text; c->pend.len = len; c->pend.n_logs = n_logs; c->pend.G = (uint32_t)line_cap;
     c->pend.m = (uint32_t)ev_cap; c->pend.options = options;
+    if (rg) { c->pend.range = true; c->pend.halo_before = rg->halo_before; c->pend.halo_after = rg->halo_after; }
 }
 
 // Counts per pattern for the two-phase (multi-GPU) API; synchronises and validates the estimates.
@@ -1554,7 +1612,8 @@ void per_pattern_counts(lp_ctx* c, uint64_t* counts_out) {
     Counters* ctr = c->counters.as<Counters>();
     c->freq_delta.ensure((size_t)std::max<uint32_t>(np, 1) * 8);
     CK(cudaMemsetAsync(c->freq_delta.p, 0, (size_t)std::max<uint32_t>(np, 1) * 8, st));
-    k_count_per_pattern<<<c->n_sm * 4, 256, 0, st>>>(c->recs.as<unsigned long long>(), ctr, c->dp, c->freq_delta.as<unsigned long long>());
+    k_count_per_pattern<<<c->n_sm * 4, 256, 0, st>>>(c->recs.as<unsigned long long>(), ctr, c->dp, c->freq_delta.as<unsigned long long>(),
+                                                    c->pend.range ? c->pend.halo_before : 0u, c->pend.range ? c->pend.halo_after : 0u);
     c->launches += 1;
     Counters h{};
     CK(cudaMemcpyAsync(&h, ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
@@ -1565,7 +1624,9 @@ void per_pattern_counts(lp_ctx* c, uint64_t* counts_out) {
 }
 
 // ---- phase 2: frequency ranks, scoring, ranking, result download (one synchronisation)
-lp_result* run_score(lp_ctx* c, const uint64_t* prior_count) {
+struct RangeGlobal { long long line_base, n_global; const long long* seq_T; };   // seq_T: host array [n_seq]
+
+lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* rgl = nullptr) {
     if (!c->pend.valid) throw std::invalid_argument("no scan is pending on this context");
     cudaStream_t st = c->stream;
     const uint32_t mc = c->pend.m, n_logs = c->pend.n_logs, line_cap = c->pend.G, np = c->dp.n_pat;
@@ -1602,6 +1663,14 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count) {
     sa.out_line = c->out_line.as<uint32_t>(); sa.out_pat = c->out_pat.as<uint32_t>(); sa.out_score = c->out_score.as<double>();
     sa.out_factors = (options & LP_OPT_FACTORS) ? c->out_factors.as<double>() : nullptr;
     sa.sort_key = c->sort_key.as<unsigned long long>();
+    if (rgl) {
+        sa.line_base = rgl->line_base; sa.n_global = rgl->n_global; sa.core_lo = c->pend.halo_before;
+        if (c->n_seq) {
+            c->seq_T.ensure((size_t)c->n_seq * 8);
+            CK(cudaMemcpyAsync(c->seq_T.p, rgl->seq_T, (size_t)c->n_seq * 8, cudaMemcpyHostToDevice, st));
+            sa.seq_T = c->seq_T.as<long long>();
+        }
+    }
     k_score<<<blocks_for(mc, 128), 128, 0, st>>>(sa, c->dp, c->sc);
     k_log_event_begin<<<blocks_for(n_logs + 1, 128), 128, 0, st>>>(c->ev_key.as<unsigned long long>(), ctr, c->first_line.as<uint32_t>(),
                                                                    n_logs, c->dp.pb, c->log_event_begin.as<unsigned long long>());
@@ -1666,6 +1735,7 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count) {
     res->freq_delta.assign(reinterpret_cast<uint64_t*>(hs + o_delta), reinterpret_cast<uint64_t*>(hs + o_delta) + np);
     res->log_n_lines.resize(n_logs);
     for (uint32_t k = 0; k < n_logs; ++k) res->log_n_lines[k] = reinterpret_cast<uint32_t*>(hs + o_nl)[k];
+    if (rgl) res->log_n_lines[0] = (uint64_t)rgl->n_global;      // a shard reports the whole log's line count
     res->log_event_begin.assign(reinterpret_cast<uint64_t*>(hs + o_leb), reinterpret_cast<uint64_t*>(hs + o_leb) + n_logs + 1);
     if (options & LP_OPT_LINE_OFFSETS) {
         res->has_offsets = true;
@@ -1852,6 +1922,14 @@ int lp_load_patterns(lp_ctx* c, const lp_pattern_desc* pats, size_t n, int64_t* 
         c->recalibrations = 0;
         lpx::build_plan(in, c->plan, bad_pattern);
         upload_plan(c);
+        // line-range shards: where each sequence's chain table sits in a shard summary
+        c->n_seq = (uint32_t)c->plan.seq_bonus.size();
+        c->h_seq_tab_off.assign(c->n_seq + 1, 0);
+        for (uint32_t q = 0; q < c->n_seq; ++q) {
+            const uint32_t k = c->plan.seq_ev_begin[q + 1] - c->plan.seq_ev_begin[q];
+            c->h_seq_tab_off[q + 1] = c->h_seq_tab_off[q] + (k >= 2 ? k - 1 : 0);
+        }
+        upload_into(c->seq_tab_off, c->h_seq_tab_off);
         c->loaded = true;
     });
 }
@@ -1917,6 +1995,104 @@ int lp_batch_score(lp_ctx* c, const uint64_t* prior_count, lp_result** out) {
             *out = run_score(c, prior_count);
         } catch (const Retry&) {
             throw LimitFail("internal: estimates validated by lp_batch_scan_device were exceeded in lp_batch_score");
+        }
+    });
+}
+
+// ---- one log sharded by line range (second mode)
+uint32_t lp_range_halo_lines(const lp_ctx* c) {
+    if (!c || !c->loaded) return 0;
+    long long h = 5;                                                   // SS:275 looks 5 lines either side
+    for (int32_t w : c->plan.sec_window) h = std::max<long long>(h, std::min<long long>(c->sc.max_window, w));   // SS:319
+    for (uint32_t p = 0; p < c->plan.n_pat; ++p)
+        if (c->plan.pat_has_ctx[p]) h = std::max<long long>(h, std::max(c->plan.pat_before[p], c->plan.pat_after[p]));   // AS:142-150
+    return (uint32_t)std::min<long long>(h, 0x7FFFFFFF);
+}
+size_t lp_range_summary_words(const lp_ctx* c) {
+    if (!c || !c->loaded) return 0;
+    return 2 + (size_t)c->dp.n_pat + c->h_seq_tab_off[c->n_seq];
+}
+int lp_range_scan_device(lp_ctx* c, const uint8_t* d_text, size_t len, uint32_t halo_before_lines, uint32_t halo_after_lines, int options,
+                         uint64_t* summary_out) {
+    if (!c || !summary_out) { g_last_error = "NULL argument"; return LP_ERR_INVALID; }
+    return guarded(c, [&] {
+        std::lock_guard<std::mutex> lk(c->mu);
+        if (!c->loaded) throw std::invalid_argument("lp_load_patterns has not been called");
+        const uint64_t off[2] = {0, (uint64_t)len};
+        const RangeShard rg{halo_before_lines, halo_after_lines};
+        const uint32_t np = c->dp.n_pat, n_tab = c->h_seq_tab_off[c->n_seq];
+        std::vector<uint64_t> counts(std::max<uint32_t>(np, 1));
+        std::vector<uint64_t> tab(std::max<uint32_t>(n_tab, 1));
+        for (;;) {
+            try {
+                run_scan(c, d_text, len, off, 1, options, &rg);
+                if (n_tab) {
+                    c->seq_tab.ensure((size_t)n_tab * 8);
+                    CK(cudaMemsetAsync(c->seq_tab.p, 0, (size_t)n_tab * 8, c->stream));
+                    k_range_tables<<<blocks_for(c->n_seq, 128), 128, 0, c->stream>>>(
+                        c->recs.as<unsigned long long>(), c->rx_begin.as<uint32_t>(), c->dp, c->counters.as<Counters>(), c->n_seq,
+                        c->seq_tab_off.as<uint32_t>(), rg.halo_before, rg.halo_after, c->seq_tab.as<unsigned long long>());
+                    c->launches += 1;
+                    CK(cudaMemcpyAsync(tab.data(), c->seq_tab.p, (size_t)n_tab * 8, cudaMemcpyDeviceToHost, c->stream));
+                }
+                per_pattern_counts(c, counts.data());     // synchronises, validates the estimates
+                break;
+            } catch (const Retry&) { continue; }
+        }
+        Counters h{};
+        CK(cudaMemcpy(&h, c->counters.p, sizeof h, cudaMemcpyDeviceToHost));
+        const uint64_t lines = h.total_nl + 1;
+        if ((uint64_t)halo_before_lines + halo_after_lines > lines) throw std::invalid_argument("halo line counts exceed the lines of the text");
+        summary_out[0] = lines - halo_before_lines - halo_after_lines;
+        summary_out[1] = np;
+        for (uint32_t p = 0; p < np; ++p) summary_out[2 + p] = counts[p];
+        for (uint32_t t = 0; t < n_tab; ++t) summary_out[2 + np + t] = tab[t];
+    });
+}
+int lp_range_score(lp_ctx* c, const uint64_t* summaries, uint32_t rank, uint32_t world, const uint64_t* prior_count, lp_result** out) {
+    if (!c || !out || !summaries) { g_last_error = "NULL argument"; return LP_ERR_INVALID; }
+    return guarded(c, [&] {
+        std::lock_guard<std::mutex> lk(c->mu);
+        if (!c->pend.valid || !c->pend.range) throw std::invalid_argument("no line-range scan is pending on this context");
+        if (rank >= world) throw std::invalid_argument("rank >= world");
+        const uint32_t np = c->dp.n_pat;
+        const size_t words = 2 + (size_t)np + c->h_seq_tab_off[c->n_seq];
+        long long base = 0, n_global = 0;
+        std::vector<long long> core_base(world);
+        for (uint32_t r = 0; r < world; ++r) {
+            const uint64_t* s = summaries + (size_t)r * words;
+            if (s[1] != np) throw std::invalid_argument("shard summaries come from a different pattern set");
+            core_base[r] = n_global;
+            if (r < rank) base += (long long)s[0];
+            n_global += (long long)s[0];
+        }
+        if (base < (long long)c->pend.halo_before) throw std::invalid_argument("halo_before exceeds the lines of the lower shards");
+        // counts seen before this shard's lines: the window's prior plus every lower shard (FTS read-before-increment order)
+        std::vector<uint64_t> prior(std::max<uint32_t>(np, 1), 0);
+        for (uint32_t p = 0; p < np; ++p) {
+            prior[p] = prior_count ? prior_count[p] : 0;
+            for (uint32_t r = 0; r < rank; ++r) prior[p] += summaries[(size_t)r * words + 2 + p];
+        }
+        // per sequence: the line where its last-but-one event is first reachable, walking the shards in order
+        std::vector<long long> seq_T(std::max<uint32_t>(c->n_seq, 1), -1);
+        for (uint32_t q = 0; q < c->n_seq; ++q) {
+            const uint32_t k = c->plan.seq_ev_begin[q + 1] - c->plan.seq_ev_begin[q];
+            if (k < 2) { seq_T[q] = -1; continue; }             // no earlier events: condition holds for every line
+            uint32_t state = 0;
+            long long T = std::numeric_limits<long long>::max();  // never reached
+            for (uint32_t r = 0; r < world && state + 1 < k; ++r) {
+                const uint64_t e = summaries[(size_t)r * words + 2 + np + c->h_seq_tab_off[q] + state];
+                const uint32_t exit_state = (uint32_t)(e >> 32), at = (uint32_t)(e & 0xFFFFFFFFull);
+                if (exit_state + 1 >= k && at) { T = core_base[r] + (long long)at - 1; state = exit_state; break; }
+                state = exit_state;
+            }
+            seq_T[q] = T;
+        }
+        const RangeGlobal rgl{base - (long long)c->pend.halo_before, n_global, seq_T.data()};
+        try {
+            *out = run_score(c, prior.data(), &rgl);
+        } catch (const Retry&) {
+            throw LimitFail("internal: estimates validated by lp_range_scan_device were exceeded in lp_range_score");
         }
     });
 }

@@ -92,3 +92,130 @@ class GpuBatchEngine:
 
     def score(self, prior: np.ndarray):
         return self.lp.batch_score(prior)
+
+
+# ------------------------------------------------------------------------------------------------
+# One log sharded by line range (second mode; lp_range_* in include/logparser_b200.h)
+# ------------------------------------------------------------------------------------------------
+def strip_trailing_separators(log: bytes) -> int:
+    """Length of `log` without its trailing `\\r?\\n` separators — the trailing empty strings that
+    String.split drops (AnalysisService.java:53). 0 for a non-empty log means it has no lines at all."""
+    n = len(log)
+    while n > 0 and log[n - 1] == 0x0A:
+        n -= 1
+        if n > 0 and log[n - 1] == 0x0D:
+            n -= 1
+    return n
+
+
+def _line_starts_forward(log, pos: int, n_lines: int, end: int) -> Tuple[int, int]:
+    """From line start `pos`, skips up to n_lines whole lines; positions are in the log extended by
+    one virtual '\\n' at `end` (so `end + 1` is "after the last line"). Returns (position, lines skipped)."""
+    k = 0
+    while k < n_lines and pos <= end:
+        j = log.find(b"\n", pos, end)
+        pos = (j if j >= 0 else end) + 1
+        k += 1
+    return pos, k
+
+
+def _line_starts_backward(log, pos: int, n_lines: int) -> Tuple[int, int]:
+    k = 0
+    while k < n_lines and pos > 0:
+        j = log.rfind(b"\n", 0, pos - 1)
+        pos = j + 1
+        k += 1
+    return pos, k
+
+
+def split_line_ranges(log: bytes, world_size: int, halo_lines: int, length: Optional[int] = None):
+    """Cuts log[:length] (no trailing separators) on line boundaries into world_size contiguous own
+    ranges balanced by bytes, each widened by up to halo_lines whole lines on either side.
+    Returns, per rank, (text_begin, text_end, halo_before_lines, halo_after_lines) where
+    log[text_begin:text_end] is the text to hand to lp_range_scan_device: it ends with the content of
+    its last line (the separator after it is not included)."""
+    if halo_lines < 1:
+        raise ValueError("halo_lines must be >= 1 (a shard without own lines is described by its halo)")
+    end = strip_trailing_separators(log) if length is None else length
+    cuts = [0]
+    for r in range(1, world_size):
+        target = max(cuts[-1], (end * r) // world_size)
+        if target == 0:
+            cuts.append(0)
+            continue
+        j = log.find(b"\n", target - 1, end)
+        cuts.append((j if j >= 0 else end) + 1)       # end + 1: after the last line
+    cuts.append(end + 1)
+    out = []
+    for r in range(world_size):
+        own_b, own_e = cuts[r], cuts[r + 1]
+        tb, before = _line_starts_backward(log, own_b, halo_lines)
+        te, after = _line_starts_forward(log, own_e, halo_lines, end)
+        # te is one past a (real or virtual) '\n'; drop that separator, and the '\r' of a "\r\n"
+        stop = te - 1
+        if stop < end and stop - 1 >= tb and log[stop - 1] == 0x0D:
+            stop -= 1
+        out.append((tb, max(tb, stop), before, after))
+    return out
+
+
+def merge_ranks(scores_per_rank: Sequence[np.ndarray]) -> List[np.ndarray]:
+    """Whole-log ranking (score descending, discovery order on ties) from the shards' scores in rank order."""
+    sizes = [len(s) for s in scores_per_rank]
+    allv = np.concatenate([np.asarray(s, np.float64) for s in scores_per_rank]) if sizes else np.zeros(0)
+    order = np.lexsort((np.arange(allv.size), -allv))
+    rank = np.empty(allv.size, np.uint32)
+    rank[order] = np.arange(allv.size, dtype=np.uint32)
+    out, at = [], 0
+    for n in sizes:
+        out.append(rank[at:at + n])
+        at += n
+    return out
+
+
+class GpuRangeEngine:
+    """lp_range_scan_device / lp_range_score on the current CUDA device."""
+
+    def __init__(self, parser):
+        self.lp = parser
+        self._keep = None
+
+    def halo_lines(self) -> int:
+        return self.lp.range_halo_lines()
+
+    def scan(self, text: bytes, halo_before: int, halo_after: int) -> np.ndarray:
+        import torch
+
+        host = np.frombuffer(text, dtype=np.uint8) if len(text) else np.zeros(16, np.uint8)
+        self._keep = torch.from_numpy(host.copy()).cuda()
+        return self.lp.range_scan_device(self._keep.data_ptr(), len(text), halo_before, halo_after)
+
+    def score(self, summaries: np.ndarray, rank: int, world_size: int, prior):
+        return self.lp.range_score(summaries, rank, world_size, prior)
+
+
+def gather_summaries(summary: np.ndarray, world_size: int, group=None) -> np.ndarray:
+    """All-gathers the per-rank shard summaries -> [world_size, words] (NCCL on GPUs, gloo in CPU tests)."""
+    import torch
+    import torch.distributed as dist
+
+    if world_size == 1:
+        return summary.reshape(1, -1).copy()
+    backend = dist.get_backend(group)
+    dev = torch.device("cuda", torch.cuda.current_device()) if backend == "nccl" else torch.device("cpu")
+    mine = torch.from_numpy(summary.view(np.int64).copy()).to(dev)
+    gathered = torch.empty(world_size * mine.numel(), dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(gathered, mine, group=group)
+    return gathered.cpu().numpy().view(np.uint64).reshape(world_size, -1)
+
+
+def analyze_range_sharded(engine, log: bytes, rank: int, world_size: int, prior_count=None, group=None):
+    """This rank's share of ONE log cut by line range. Every rank holds (or can read) the log bytes but
+    uploads only its own range plus halos. Returns the shard's result (global line numbers), or None
+    when the log has no lines at all."""
+    end = strip_trailing_separators(log)
+    if end == 0 and len(log) > 0:
+        return None                                   # only separators: String.split gives [] (AS:53)
+    tb, te, before, after = split_line_ranges(log, world_size, engine.halo_lines(), end)[rank]
+    summary = engine.scan(bytes(log[tb:te]), before, after)
+    return engine.score(gather_summaries(summary, world_size, group), rank, world_size, prior_count)

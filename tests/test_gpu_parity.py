@@ -307,3 +307,109 @@ def test_c4_shape_large_windows(oracle):
     _check(res, ora)
     np.testing.assert_array_equal(res.score, ora.score)
     lp.close()
+
+
+def _range_sharded(cfg, patterns, log, world, prior=None):
+    """The line-range decomposition run on one GPU: `world` contexts play the ranks, the summaries
+    are stacked instead of all-gathered."""
+    from log_parser_b200 import parallel
+
+    lps = [binding.LogParser(cfg) for _ in range(world)]
+    try:
+        for lp in lps:
+            lp.load_patterns(patterns)
+        engines = [parallel.GpuRangeEngine(lp) for lp in lps]
+        end = parallel.strip_trailing_separators(log)
+        assert not (end == 0 and len(log) > 0)
+        pieces = parallel.split_line_ranges(log, world, engines[0].halo_lines(), end)
+        summaries = np.stack([engines[r].scan(bytes(log[tb:te]), hb, ha) for r, (tb, te, hb, ha) in enumerate(pieces)])
+        results = [engines[r].score(summaries, r, world, prior) for r in range(world)]
+        return results, summaries
+    finally:
+        for lp in lps:
+            lp.close()
+
+
+@pytest.mark.parametrize("world", [1, 2, 3, 5])
+def test_line_range_shards_equal_whole_log(parser, world):
+    """SURVEY §8e second mode: one log cut by line range with halos, scored per shard after one
+    exchange of shard summaries, concatenates (in shard order) to the whole-log result bit for bit:
+    global line numbers, chronological factor on the whole log's N, windows through the halos, the
+    unbounded backward sequence walk (SS:296-305) across shards, frequency counts in discovery order."""
+    from log_parser_b200 import parallel
+
+    cfg = ScoringConfig()
+    wl = synth.make_patterns(40, 5150 + world, scoring_heavy=True, noliteral=1)
+    log = synth.make_log(wl, 7000, 5151, hit_rate=0.05, symptom_rate=0.3, phase_rate=0.01, pool_blocks=1500) + b"\r\n\n\n"
+    prior = (np.arange(len(wl.patterns)) % 7).astype(np.uint64)
+    parser.load_patterns(wl.patterns)
+    whole = parser.analyze(log, prior_count=prior, options=binding.OPT_FACTORS)
+    assert whole.n_events > 200
+    assert (whole.factors[:, 4] > 1.0).any() and (whole.factors[:, 6] > 0.0).any()     # sequences and penalties in play
+    results, summaries = _range_sharded(cfg, wl.patterns, log, world, prior)
+    assert int(summaries[:, 0].sum()) == int(whole.log_n_lines[0])
+    assert all(int(r.log_n_lines[0]) == int(whole.log_n_lines[0]) for r in results)
+    np.testing.assert_array_equal(np.concatenate([r.line for r in results]), whole.line)
+    np.testing.assert_array_equal(np.concatenate([r.pattern for r in results]), whole.pattern)
+    np.testing.assert_array_equal(np.concatenate([r.score for r in results]), whole.score)
+    np.testing.assert_array_equal(sum(r.freq_delta for r in results), whole.freq_delta)
+    merged = parallel.merge_ranks([r.score for r in results])
+    np.testing.assert_array_equal(np.concatenate(merged), whole.rank)
+
+
+def test_line_range_shards_c4_windows():
+    """configs[3]: proximity windows up to 1000 lines and +-500 context lines => 1000-line halos."""
+    cfg = ScoringConfig(max_window=1000)
+    wl = synth.make_patterns(30, 4040, scoring_heavy=True, noliteral=0)
+    log = synth.make_log(wl, 9000, 4042, hit_rate=0.05, symptom_rate=0.4, phase_rate=0.01, pool_blocks=1500)
+    lp = binding.LogParser(cfg)
+    lp.load_patterns(wl.patterns)
+    assert lp.range_halo_lines() >= 500
+    whole = lp.analyze(log)
+    lp.close()
+    results, _ = _range_sharded(cfg, wl.patterns, log, 3)
+    np.testing.assert_array_equal(np.concatenate([r.line for r in results]), whole.line)
+    np.testing.assert_array_equal(np.concatenate([r.pattern for r in results]), whole.pattern)
+    np.testing.assert_array_equal(np.concatenate([r.score for r in results]), whole.score)
+
+
+@pytest.mark.parametrize("log", [b"", b"x", b"ERROR a\nb", b"a\n\n\nb\n", b"\n\nz", b"a\r\nb\r\n\r\n"])
+def test_line_range_shards_tiny_logs(parser, log):
+    """More ranks than lines: shards without own lines still take part in the exchange."""
+    cfg = ScoringConfig()
+    pats = [PatternSpec(id="p", primary_regex="ERROR|b|z|^$", confidence=0.9, severity="HIGH",
+                        secondaries=[SecondaryPattern(regex="a", weight=0.5, proximity_window=3)],
+                        sequences=[SequencePattern(events=["a", "b|z"], bonus_multiplier=0.3)])]
+    parser.load_patterns(pats)
+    whole = parser.analyze(log)
+    results, summaries = _range_sharded(cfg, pats, log, 4)
+    assert int(summaries[:, 0].sum()) == int(whole.log_n_lines[0])
+    np.testing.assert_array_equal(np.concatenate([r.line for r in results]), whole.line)
+    np.testing.assert_array_equal(np.concatenate([r.score for r in results]), whole.score)
+
+
+def test_line_range_sequence_chain_spans_shards(parser):
+    """The backward sequence walk is unbounded (SS:296-305): its events may sit in different shards,
+    far outside any halo. 4 events: alpha@53, beta@32+214, gamma@102+333, then the last event next to
+    the primary; with 5 shards of ~90 lines the chain enters shards in states 1 and 2."""
+    cfg = ScoringConfig()
+    lines = [b"INFO tick %d" % i for i in range(450)]
+    lines[53] = b"alpha"; lines[32] = b"beta"; lines[214] = b"beta"; lines[102] = b"gamma"; lines[333] = b"gamma"
+    for i in range(0, 441, 7):
+        lines[i + 1] = b"ERR boom"
+        lines[i + 2] = b"delta"
+    log = b"\n".join(lines) + b"\n"
+    pats = [PatternSpec(id="p", primary_regex="ERR", confidence=0.9, severity="HIGH",
+                        sequences=[SequencePattern(events=["alpha", "beta", "gamma", "delta"], bonus_multiplier=0.25),
+                                   SequencePattern(events=["gamma", "alpha", "delta"], bonus_multiplier=0.5),      # never completes
+                                   SequencePattern(events=["delta"], bonus_multiplier=0.125)])]
+    parser.load_patterns(pats)
+    whole = parser.analyze(log, options=binding.OPT_FACTORS)
+    t = whole.factors[:, 4]
+    assert set(np.unique(t)) == {1.125, 1.375}
+    assert int(whole.line[np.argmax(t > 1.2)]) == 338          # first primary line after gamma@333 (0-based 337)
+    for world in (2, 5):
+        results, _ = _range_sharded(cfg, pats, log, world)
+        assert len(results) == world and min(len(r.line) for r in results) > 0
+        np.testing.assert_array_equal(np.concatenate([r.line for r in results]), whole.line)
+        np.testing.assert_array_equal(np.concatenate([r.score for r in results]), whole.score)

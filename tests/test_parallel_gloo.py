@@ -93,3 +93,73 @@ def test_world_size_2_matches_sequential(tmp_path, oracle):
     for p in parts:
         np.testing.assert_array_equal(p["total"], total)
     assert (np.concatenate(exp_scores) > 0).all() and total.sum() > 20
+
+
+# ---- one log sharded by line range: host-side cutting and the summary exchange
+def _java_split(log: bytes):
+    import re
+    parts = re.split(rb"\r?\n", log)
+    while parts and parts[-1] == b"":
+        parts.pop()
+    return parts if (parts or log) else [b""]      # "" -> [""], only separators -> []
+
+
+def test_split_line_ranges_reassemble_to_java_split():
+    import random
+    rnd = random.Random(77)
+    alphabet = [b"a", b"bc", b"", b"x\r", b"\r", b"ERROR q", b"  at f(G.java:1)"]
+    for trial in range(300):
+        n = rnd.randrange(0, 40)
+        log = b"".join(rnd.choice(alphabet) + rnd.choice([b"\n", b"\r\n"]) for _ in range(n))
+        if rnd.random() < 0.5:
+            log += rnd.choice([b"tail", b"\r", b"t\r"])
+        log += rnd.choice([b"", b"\n", b"\r\n\n", b"\n\r\n"])
+        expect = _java_split(log)
+        end = parallel.strip_trailing_separators(log)
+        if end == 0 and len(log) > 0:
+            assert expect == []
+            continue
+        for world in (1, 2, 3, 5, 8):
+            halo = rnd.randrange(1, 7)
+            pieces = parallel.split_line_ranges(log, world, halo, end)
+            assert len(pieces) == world
+            own_all = []
+            for tb, te, before, after in pieces:
+                lines = log[tb:te].split(b"\n")
+                lines = [ln[:-1] if ln.endswith(b"\r") and i + 1 < len(lines) else ln for i, ln in enumerate(lines)]
+                # a '\r' ending the very last line of a text is content only when no '\n' followed it in the log
+                assert before + after <= len(lines)
+                assert before <= halo and after <= halo
+                own = lines[before:len(lines) - after]
+                own_all.extend(own)
+                # halos are as long as the log allows
+                first_own = len(own_all) - len(own)
+                assert before == min(halo, first_own)
+                assert after == min(halo, len(expect) - first_own - len(own))
+            assert own_all == expect, (log, world, halo)
+
+
+def _gather_worker(rank, world, port, path):
+    import torch.distributed as dist
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    mine = (np.arange(11, dtype=np.uint64) + 1000 * rank) | (np.uint64(rank + 1) << np.uint64(63 - rank))
+    allv = parallel.gather_summaries(mine, world)
+    np.save(os.path.join(path, f"g{rank}.npy"), allv)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_gather_summaries_world_size_2(tmp_path):
+    import torch.multiprocessing as mp
+
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    mp.spawn(_gather_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    exp = np.stack([(np.arange(11, dtype=np.uint64) + 1000 * r) | (np.uint64(r + 1) << np.uint64(63 - r)) for r in range(2)])
+    for r in range(2):
+        np.testing.assert_array_equal(np.load(os.path.join(tmp_path, f"g{r}.npy")), exp)   # rank order, all 64 bits kept
