@@ -315,8 +315,7 @@ def main():
     def step_host():
         if not by_lines:
             return lp.analyze_host_ptr(host.data_ptr(), nbytes)
-        with torch.cuda.stream(lib_stream):
-            copies[0].copy_(host, non_blocking=True)          # own range + halos, pinned host -> device on the library stream
+        copies[0].copy_(host, non_blocking=False)             # own range + halos, pinned host -> device
         summary = lp.range_scan_device(copies[0].data_ptr(), nbytes, halo_b, halo_a)
         return lp.range_score(parallel.gather_summaries(summary, world), rank, world)
 
