@@ -258,6 +258,8 @@ def main():
     off = np.array([0, nbytes], dtype=np.uint64)
     lib_stream = torch.cuda.ExternalStream(lp.stream_ptr(), device=torch.device("cuda", local_rank))
 
+    exchange = parallel.DeviceExchange(lp, rank, world) if (world > 1 and not by_lines) else None
+
     def step_device(i):
         d = copies[i % len(copies)]
         if world == 1:
@@ -265,9 +267,7 @@ def main():
         if by_lines:
             summary = lp.range_scan_device(d.data_ptr(), nbytes, halo_b, halo_a)
             return lp.range_score(parallel.gather_summaries(summary, world), rank, world)
-        counts = lp.batch_scan_device(d.data_ptr(), off)
-        prior, _total = parallel.exclusive_prefix(counts, rank, world)     # one NCCL all-gather of P x int64
-        return lp.batch_score(prior)
+        return exchange.step(d.data_ptr(), off)       # scan -> NCCL all-gather of (P + 1) x int64 on the device -> score
 
     def barrier():
         if world > 1:
@@ -359,6 +359,8 @@ def main():
             r = cpu_reference_run(args, wl, log, steps=1, warmup=0)
             line["cpu_baseline"] = {"value": r["value"], "unit": "lines/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]}
         print(json.dumps(line))
+    if exchange is not None:
+        exchange.close()
     if world > 1:
         dist.destroy_process_group()
     lp.close()

@@ -141,6 +141,19 @@ int lp_batch_scan_device(lp_ctx* ctx, const uint8_t* d_logs, const uint64_t* off
                          int options, uint64_t* counts_out /* [n_patterns] */);
 int lp_batch_score(lp_ctx* ctx, const uint64_t* prior_count, lp_result** out);
 
+/* The same two phases with the exchange kept on the device (no host round trip between them):
+ * phase 1 only enqueues work on lp_stream() and writes [n_patterns counts, 1 status word] to
+ * DEVICE memory `d_counts_out`; the host all-gathers those n_patterns + 1 words of every rank into
+ * `d_all_counts` ([world][n_patterns + 1], rank order, device memory, ordered after lp_stream() — e.g.
+ * ncclAllGather on that stream); phase 2 forms the exclusive prefix on the device, scores and
+ * synchronises once. Returns LP_RETRY (not an error) when some rank's scratch estimates were too
+ * small for its logs: every rank sees the same status words, so every rank repeats both phases. */
+#define LP_RETRY 1
+int lp_batch_scan_device_async(lp_ctx* ctx, const uint8_t* d_logs, const uint64_t* offsets, size_t n_logs,
+                               int options, uint64_t* d_counts_out /* device, [n_patterns + 1] */);
+int lp_batch_score_gathered(lp_ctx* ctx, const uint64_t* d_all_counts, uint32_t rank, uint32_t world,
+                            const uint64_t* prior_count, lp_result** out);
+
 /* ONE log sharded by line range over several GPUs (second mode; the reference walks
  * the whole log on one thread, AS:89-113). The host first removes the log's trailing separators
  * (the trailing empty strings String.split drops, AS:53), cuts the rest on line boundaries into

@@ -85,7 +85,7 @@ EXPORTS = [
     "lp_create", "lp_destroy", "lp_last_error", "lp_version", "lp_load_patterns", "lp_analyze", "lp_analyze_device",
     "lp_analyze_batch", "lp_analyze_batch_device", "lp_batch_scan_device", "lp_batch_score", "lp_result_get",
     "lp_result_free", "lp_get_timings", "lp_stream", "lp_split_lines_noalloc",
-    "lp_range_halo_lines", "lp_range_summary_words", "lp_range_scan_device", "lp_range_score",
+    "lp_batch_scan_device_async", "lp_batch_score_gathered", "lp_range_halo_lines", "lp_range_summary_words", "lp_range_scan_device", "lp_range_score",
 ]
 
 _lib = None
@@ -118,6 +118,8 @@ def load_library() -> C.CDLL:
     L.lp_get_timings.argtypes = [vp, C.POINTER(Timings)]
     L.lp_stream.restype = vp
     L.lp_stream.argtypes = [vp]
+    L.lp_batch_scan_device_async.argtypes = [vp, u8p, u64p, C.c_size_t, C.c_int, vp]
+    L.lp_batch_score_gathered.argtypes = [vp, vp, C.c_uint32, C.c_uint32, u64p, C.POINTER(vp)]
     L.lp_range_halo_lines.restype = C.c_uint32
     L.lp_range_halo_lines.argtypes = [vp]
     L.lp_range_summary_words.restype = C.c_size_t
@@ -337,6 +339,23 @@ class LogParser:
         keep, pp = self._prior(prior_count)
         out = C.c_void_p()
         rc = self.L.lp_batch_score(self.h, pp, C.byref(out))
+        if rc != LP_OK:
+            _raise(rc)
+        return self._take(out)
+
+    def batch_scan_device_async(self, dev_ptr: int, offsets, counts_dev_ptr: int, options: int = 0) -> None:
+        oa, op = self._offsets(offsets)
+        rc = self.L.lp_batch_scan_device_async(self.h, dev_ptr, op, len(oa) - 1, options, counts_dev_ptr)
+        if rc != LP_OK:
+            _raise(rc)
+
+    def batch_score_gathered(self, all_counts_dev_ptr: int, rank: int, world: int, prior_count=None) -> Optional[Result]:
+        """None = LP_RETRY: every rank repeats scan + exchange + score (some rank's buffers were regrown)."""
+        keep, pp = self._prior(prior_count)
+        out = C.c_void_p()
+        rc = self.L.lp_batch_score_gathered(self.h, all_counts_dev_ptr, rank, world, pp, C.byref(out))
+        if rc == 1:
+            return None
         if rc != LP_OK:
             _raise(rc)
         return self._take(out)

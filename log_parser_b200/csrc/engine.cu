@@ -1140,6 +1140,25 @@ __global__ void k_range_tables(const unsigned long long* __restrict__ keys, cons
         tab[tab_off[q] + s] = ((unsigned long long)j << 32) | (j + 1 == k ? (unsigned long long)(T - core_lo + 1) : 0ull);
     }
 }
+// Multi-GPU batches with the exchange kept on the device: `all` holds every rank's [n_pat counts, overflow word]
+// (all-gathered); prior_out[p] = window prior + the counts of the lower ranks; *any_flag = OR of the overflow words.
+__global__ void k_prior_prefix(const unsigned long long* __restrict__ all, uint32_t n_pat, uint32_t rank, uint32_t world,
+                               const unsigned long long* __restrict__ prior_in, unsigned long long* __restrict__ prior_out,
+                               unsigned long long* __restrict__ any_flag) {
+    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t stride = (size_t)n_pat + 1;
+    if (p < n_pat) {
+        unsigned long long v = prior_in ? prior_in[p] : 0ull;
+        for (uint32_t r = 0; r < rank; ++r) v += all[r * stride + p];
+        prior_out[p] = v;
+    }
+    if (p == 0) {
+        unsigned long long f = 0;
+        for (uint32_t r = 0; r < world; ++r) f |= all[r * stride + n_pat];
+        *any_flag = f;
+    }
+}
+__global__ void k_publish_overflow(const Counters* ctr, unsigned long long* __restrict__ dst) { *dst = ctr->overflow; }
 __global__ void k_count_per_pattern(const unsigned long long* __restrict__ keys, const Counters* ctr, DevPlan P, unsigned long long* __restrict__ counts,
                                     uint32_t core_lo, uint32_t halo_after) {
     const uint32_t n = ctr->n_unique;
@@ -1264,7 +1283,7 @@ struct lp_ctx {
         bool range = false;                 // line-range shard: events only for the lines between the halos
         uint32_t halo_before = 0, halo_after = 0;
     } pend;
-    DevBuf seq_tab_off, seq_tab, seq_T;
+    DevBuf seq_tab_off, seq_tab, seq_T, prior_eff, any_flag;
     std::vector<uint32_t> h_seq_tab_off;    // per sequence, offset of its chain table in a shard summary
     uint32_t n_seq = 0;
 
@@ -1626,7 +1645,8 @@ void per_pattern_counts(lp_ctx* c, uint64_t* counts_out) {
 // ---- phase 2: frequency ranks, scoring, ranking, result download (one synchronisation)
 struct RangeGlobal { long long line_base, n_global; const long long* seq_T; };   // seq_T: host array [n_seq]
 
-lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* rgl = nullptr) {
+lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* rgl = nullptr,
+                     const unsigned long long* prior_dev = nullptr) {
     if (!c->pend.valid) throw std::invalid_argument("no scan is pending on this context");
     cudaStream_t st = c->stream;
     const uint32_t mc = c->pend.m, n_logs = c->pend.n_logs, line_cap = c->pend.G, np = c->dp.n_pat;
@@ -1649,6 +1669,7 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
         CK(cudaMemcpyAsync(c->prior.p, prior_count, (size_t)np * 8, cudaMemcpyHostToDevice, st));
         prior_d = c->prior.as<unsigned long long>();
     }
+    if (prior_dev) prior_d = prior_dev;
     const uint32_t gb = blocks_for(mc, 256);
     const uint32_t n_slots = (uint32_t)c->plan.slot_first_pat.size();
     k_event_prep<<<gb, 256, 0, st>>>(c->ev_key.as<unsigned long long>(), ctr, mc, c->dp, c->first_line.as<uint32_t>(), n_logs, n_slots,
@@ -1997,6 +2018,58 @@ int lp_batch_score(lp_ctx* c, const uint64_t* prior_count, lp_result** out) {
             throw LimitFail("internal: estimates validated by lp_batch_scan_device were exceeded in lp_batch_score");
         }
     });
+}
+
+// Two-phase form with the exchange left on the device: nothing is read back between the phases.
+int lp_batch_scan_device_async(lp_ctx* c, const uint8_t* d_logs, const uint64_t* offsets, size_t n_logs, int options, uint64_t* d_counts_out) {
+    if (!c || !d_counts_out) { g_last_error = "NULL argument"; return LP_ERR_INVALID; }
+    return guarded(c, [&] {
+        if (!offsets) throw std::invalid_argument("offsets is NULL");
+        std::lock_guard<std::mutex> lk(c->mu);
+        try {
+            run_scan(c, d_logs, offsets[n_logs], offsets, (uint32_t)n_logs, options);
+        } catch (const Retry&) { throw LimitFail("internal: run_scan does not synchronise"); }
+        const uint32_t np = c->dp.n_pat;
+        unsigned long long* dst = reinterpret_cast<unsigned long long*>(d_counts_out);
+        CK(cudaMemsetAsync(dst, 0, ((size_t)np + 1) * 8, c->stream));
+        k_count_per_pattern<<<c->n_sm * 4, 256, 0, c->stream>>>(c->recs.as<unsigned long long>(), c->counters.as<Counters>(), c->dp, dst, 0u, 0u);
+        k_publish_overflow<<<1, 1, 0, c->stream>>>(c->counters.as<Counters>(), dst + np);
+        c->launches += 2;
+        CK(cudaGetLastError());
+    });
+}
+int lp_batch_score_gathered(lp_ctx* c, const uint64_t* d_all_counts, uint32_t rank, uint32_t world, const uint64_t* prior_count, lp_result** out) {
+    if (!c || !out || !d_all_counts) { g_last_error = "NULL argument"; return LP_ERR_INVALID; }
+    *out = nullptr;
+    bool again = false;
+    const int rc = guarded(c, [&] {
+        std::lock_guard<std::mutex> lk(c->mu);
+        if (!c->pend.valid) throw std::invalid_argument("no scan is pending on this context");
+        if (rank >= world) throw std::invalid_argument("rank >= world");
+        const uint32_t np = c->dp.n_pat;
+        c->prior_eff.ensure((size_t)std::max<uint32_t>(np, 1) * 8);
+        c->any_flag.ensure(8);
+        const unsigned long long* prior_in = nullptr;
+        if (prior_count && np) {
+            c->prior.ensure((size_t)np * 8);
+            CK(cudaMemcpyAsync(c->prior.p, prior_count, (size_t)np * 8, cudaMemcpyHostToDevice, c->stream));
+            prior_in = c->prior.as<unsigned long long>();
+        }
+        k_prior_prefix<<<blocks_for(std::max<uint32_t>(np, 1), 128), 128, 0, c->stream>>>(
+            reinterpret_cast<const unsigned long long*>(d_all_counts), np, rank, world, prior_in, c->prior_eff.as<unsigned long long>(),
+            c->any_flag.as<unsigned long long>());
+        c->launches += 1;
+        std::unique_ptr<lp_result> res;
+        try {
+            res.reset(run_score(c, nullptr, nullptr, c->prior_eff.as<unsigned long long>()));
+        } catch (const Retry&) { again = true; return; }      // this rank's buffers were too small (now regrown)
+        unsigned long long flag = 0;
+        CK(cudaMemcpy(&flag, c->any_flag.p, 8, cudaMemcpyDeviceToHost));
+        if (flag & 16u) throw std::overflow_error("backtracking verifier exceeded its step/stack budget on another rank");
+        if (flag) { again = true; return; }                   // another rank's counts were incomplete
+        *out = res.release();
+    });
+    return rc != LP_OK ? rc : (again ? LP_RETRY : LP_OK);
 }
 
 // ---- one log sharded by line range (second mode)

@@ -94,6 +94,49 @@ class GpuBatchEngine:
         return self.lp.batch_score(prior)
 
 
+
+class DeviceExchange:
+    """The by-log exchange kept on the device (lp_batch_scan_device_async / lp_batch_score_gathered):
+    this rank's [P counts, status word] are written by the scan phase straight into a device buffer,
+    all-gathered with NCCL ordered on the library's stream, and turned into the exclusive prefix by a
+    kernel of the score phase. No host round trip between the phases; one synchronisation per step.
+    Call close() before the parser is closed (the buffers are tied to the parser's stream)."""
+
+    def __init__(self, parser, rank: int, world_size: int, group=None):
+        import torch
+
+        self.lp, self.rank, self.world, self.group = parser, rank, world_size, group
+        dev = torch.device("cuda", torch.cuda.current_device())
+        n = parser.n_patterns + 1
+        self.mine = torch.zeros(n, dtype=torch.int64, device=dev)
+        self.all = torch.zeros(world_size * n, dtype=torch.int64, device=dev)
+        self.stream = torch.cuda.ExternalStream(parser.stream_ptr(), device=dev)
+        torch.cuda.synchronize()
+
+    def step(self, dev_ptr: int, offsets, prior_count=None, options: int = 0, max_rounds: int = 16):
+        import torch
+        import torch.distributed as dist
+
+        for _ in range(max_rounds):
+            self.lp.batch_scan_device_async(dev_ptr, offsets, self.mine.data_ptr(), options)
+            with torch.cuda.stream(self.stream):
+                if self.world > 1:
+                    dist.all_gather_into_tensor(self.all, self.mine, group=self.group)
+                else:
+                    self.all.copy_(self.mine)
+            res = self.lp.batch_score_gathered(self.all.data_ptr(), self.rank, self.world, prior_count)
+            if res is not None:
+                return res                      # None: some rank regrew its buffers; every rank repeats the step
+        raise RuntimeError("scratch estimates did not settle")
+
+    def close(self):
+        import torch
+
+        torch.cuda.synchronize()
+        self.mine = self.all = None
+        torch.cuda.synchronize()
+
+
 # ------------------------------------------------------------------------------------------------
 # One log sharded by line range (SURVEY §8e, second mode; lp_range_* in include/logparser_b200.h)
 # ------------------------------------------------------------------------------------------------

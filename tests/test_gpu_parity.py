@@ -413,3 +413,60 @@ def test_line_range_sequence_chain_spans_shards(parser):
         assert len(results) == world and min(len(r.line) for r in results) > 0
         np.testing.assert_array_equal(np.concatenate([r.line for r in results]), whole.line)
         np.testing.assert_array_equal(np.concatenate([r.score for r in results]), whole.score)
+
+
+def test_device_side_exchange_equals_one_batch(parser):
+    """lp_batch_scan_device_async / lp_batch_score_gathered: the by-log exchange without a host round
+    trip. Two contexts play two ranks; each scan phase writes its [counts, status] straight into its
+    slot of the gathered buffer (what the NCCL all-gather produces)."""
+    import torch
+    from log_parser_b200 import parallel
+
+    wl = synth.make_patterns(40, 778, noliteral=1)
+    logs = [synth.make_log(wl, n, 320 + i, pool_blocks=400, hit_rate=0.06) for i, n in enumerate([500, 200, 900, 50, 400, 300])]
+    prior = (np.arange(len(wl.patterns)) % 5).astype(np.uint64)
+    parser.load_patterns(wl.patterns)
+    whole = parser.analyze_batch(logs, prior_count=prior)
+    bounds = parallel.shard_bounds([len(x) for x in logs], 2)
+    lps = [binding.LogParser(ScoringConfig()) for _ in range(2)]
+    try:
+        for lp in lps:
+            lp.load_patterns(wl.patterns)
+        n = len(wl.patterns) + 1
+        gathered = torch.zeros(2 * n, dtype=torch.int64, device="cuda")
+        texts, offs = [], []
+        for lo, hi in bounds:
+            blob = b"".join(logs[lo:hi])
+            off = np.zeros(hi - lo + 1, np.uint64)
+            np.cumsum([len(x) for x in logs[lo:hi]], out=off[1:])
+            texts.append(torch.from_numpy(np.frombuffer(blob, dtype=np.uint8).copy()).cuda())
+            offs.append(off)
+        rounds = 0
+        while True:
+            rounds += 1
+            assert rounds < 10
+            for r in range(2):
+                lps[r].batch_scan_device_async(texts[r].data_ptr(), offs[r], gathered[r * n:].data_ptr())
+            torch.cuda.synchronize()
+            results = [lps[r].batch_score_gathered(gathered.data_ptr(), r, 2, prior) for r in range(2)]
+            assert (results[0] is None) == (results[1] is None)       # every rank sees the same status words
+            if results[0] is not None:
+                break
+        counts = gathered.cpu().numpy().reshape(2, n)
+        assert (counts[:, -1] == 0).all()
+        np.testing.assert_array_equal(np.concatenate([r.line for r in results]), whole.line)
+        np.testing.assert_array_equal(np.concatenate([r.pattern for r in results]), whole.pattern)
+        np.testing.assert_array_equal(np.concatenate([r.score for r in results]), whole.score)
+        np.testing.assert_array_equal(counts[:, :-1].sum(axis=0).astype(np.uint64), whole.freq_delta)
+        # world_size 1 through the helper
+        ex = parallel.DeviceExchange(lps[0], 0, 1)
+        blob = b"".join(logs)
+        off = np.zeros(len(logs) + 1, np.uint64)
+        np.cumsum([len(x) for x in logs], out=off[1:])
+        t = torch.from_numpy(np.frombuffer(blob, dtype=np.uint8).copy()).cuda()
+        one = ex.step(t.data_ptr(), off, prior)
+        ex.close()
+        np.testing.assert_array_equal(one.score, whole.score)
+    finally:
+        for lp in lps:
+            lp.close()
