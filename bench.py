@@ -238,6 +238,7 @@ def main():
     build.build()
     torch.cuda.set_device(local_rank)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")     # keep stdout for the one JSON line
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
 
     wl, log = build_workload(args, 0 if by_lines else rank)
