@@ -137,6 +137,8 @@ def load_library() -> C.CDLL:
     L.lp_debug_rx_match.argtypes = [vp, C.c_char_p, C.c_size_t]
     L.lp_debug_rx_literals.restype = C.c_size_t
     L.lp_debug_rx_literals.argtypes = [vp, C.c_char_p, C.c_size_t]
+    L.lp_debug_rx_anchor.argtypes = [vp]
+    L.lp_debug_rx_match_anchored.argtypes = [vp, C.c_char_p, C.c_size_t]
     _lib = L
     return L
 
@@ -412,11 +414,11 @@ def split_lines_noalloc(device: int, d_log: int, nbytes: int, d_line_start: int,
 class DebugRegex:
     """Host-compiler introspection for the CPU-only test tier (never part of analyze)."""
 
-    def __init__(self, pattern: str, flags: int = 0, force_vm: bool = False):
+    def __init__(self, pattern: str, flags: int = 0, force_vm: bool = False, min_literal: int = 0):
         self.L = load_library()
         err = C.create_string_buffer(512)
         kind = C.c_int(0)
-        self.h = self.L.lp_debug_rx_compile(pattern.encode("utf-8"), flags, 1 if force_vm else 0, err, 512, C.byref(kind))
+        self.h = self.L.lp_debug_rx_compile(pattern.encode("utf-8"), flags, (1 if force_vm else 0) | (min_literal << 8), err, 512, C.byref(kind))
         if not self.h:
             msg = err.value.decode("utf-8", "replace")
             if kind.value == 1:
@@ -436,6 +438,16 @@ class DebugRegex:
     def match(self, text) -> int:
         b = text.encode("utf-8") if isinstance(text, str) else bytes(text)
         return self.L.lp_debug_rx_match(self.h, b, len(b))
+
+    @property
+    def anchor(self) -> int:
+        """0: verified by walking the whole line; 1 / 2: decided at the literal occurrences by the
+        forward / backward anchored automaton."""
+        return int(self.L.lp_debug_rx_anchor(self.h))
+
+    def match_anchored(self, text) -> int:
+        b = text.encode("utf-8") if isinstance(text, str) else bytes(text)
+        return int(self.L.lp_debug_rx_match_anchored(self.h, b, len(b)))
 
     def literals(self):
         n = self.L.lp_debug_rx_literals(self.h, None, 0)

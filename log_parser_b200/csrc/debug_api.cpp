@@ -8,6 +8,7 @@
 #include "plan.h"
 #include "vm.h"
 
+namespace lpx { extern thread_local unsigned long long g_anchor_steps; }
 using namespace lpx;
 
 namespace {
@@ -18,6 +19,8 @@ struct DebugRx {
     bool has_vm = false;
     VmProgram vm;
     std::vector<Literal> lits;
+    int anchor = 0;          // 0 none, 1 forward, 2 backward
+    Dfa adfa;
 };
 void put_err(char* err, size_t n, const std::string& m) {
     if (!err || !n) return;
@@ -36,9 +39,12 @@ void* lp_debug_rx_compile(const char* regex, int flags, int force_vm, char* err,
         DebugRx* d = new DebugRx();
         try {
             d->parsed = parse_java_regex(regex, flags);
+            const size_t min_lit = (force_vm >> 8) ? (size_t)(force_vm >> 8) : 4;   // tests lower it to exercise short literals
+            force_vm &= 1;
             if (d->parsed.regular && !force_vm) d->has_dfa = build_dfa(*d->parsed.root, d->dfa);
             if (!d->has_dfa) { build_vm(d->parsed, d->vm); d->has_vm = true; }
-            d->lits = required_literals(*d->parsed.root, 4);
+            d->lits = required_literals(*d->parsed.root, min_lit);
+            if (d->has_dfa) d->anchor = choose_anchor(*d->parsed.root, d->lits, d->adfa);
         } catch (...) { delete d; throw; }
         return d;
     } catch (const RegexSyntaxError& e) {
@@ -65,6 +71,29 @@ int lp_debug_rx_match(void* h, const uint8_t* s, size_t n) {
     DebugRx* d = static_cast<DebugRx*>(h);
     if (d->has_dfa) return d->dfa.match(s, n) ? 1 : 0;
     return vm_match_host(d->vm, s, n);
+}
+unsigned long long lp_debug_anchor_steps(int reset) { unsigned long long v = lpx::g_anchor_steps; if (reset) lpx::g_anchor_steps = 0; return v; }
+int lp_debug_rx_anchor(void* h) { return static_cast<DebugRx*>(h)->anchor; }
+// What k_confirm decides for an anchored regex: some occurrence of one of its literals at which the
+// anchored automaton accepts. -2 when the regex is not verified that way.
+int lp_debug_rx_match_anchored(void* h, const uint8_t* s, size_t n) {
+    DebugRx* d = static_cast<DebugRx*>(h);
+    if (!d->anchor) return -2;
+    int hit = 0;       // every occurrence is walked, as on the device
+    for (const auto& l : d->lits) {
+        const size_t m = l.bytes.size();
+        for (size_t p = 0; p + m <= n; ++p) {
+            bool ok = true;
+            for (size_t j = 0; j < m && ok; ++j) {
+                uint8_t b = s[p + j];
+                if (l.icase && b >= 'A' && b <= 'Z') b += 32;
+                ok = b == (uint8_t)l.bytes[j];
+            }
+            if (!ok) continue;
+            if (d->anchor == 1 ? d->adfa.match_from(s, n, p) : d->adfa.match_ending_at(s, n, p + m)) hit = 1;
+        }
+    }
+    return hit;
 }
 size_t lp_debug_rx_literals(void* h, char* buf, size_t cap) {
     DebugRx* d = static_cast<DebugRx*>(h);

@@ -514,12 +514,109 @@ __device__ __forceinline__ void stage_flush(QStage& sg, Counters* ctr, unsigned 
     __syncthreads();
 }
 
-// ------------------------------------------------------------------ K3: confirm gram hits -> (line, regex) tasks
+// ------------------------------------------------------------------ K3: confirm gram hits, resolve literal occurrences
+// Two kernels with a queue between them, so that the lanes of a warp do the same kind of work
+// (one thread per candidate doing everything serially ran with ~6 of 32 lanes active):
+//   k_confirm  thread per candidate: gram table probe, literal comparison in 4-byte words; every
+//              (occurrence, regex) pair becomes an item in the queue of its verification class
+//   k_resolve  thread per item, a block works on one class at a time: line lookup, then
+//              class 0 boundary test | 1 anchored automaton forwards | 2 backwards | 3 hand over to
+//              k_verify / k_verify_vm (walk of the whole line)
+constexpr int N_CLASSES = 4;
+constexpr uint32_t ITEM_STAGE = 1024;      // items staged per class and block
+struct ItemStage { unsigned long long buf[N_CLASSES][ITEM_STAGE]; uint32_t n[N_CLASSES], base[N_CLASSES]; };
+
 struct ConfirmArgs {
     const uint8_t* text;
     uint64_t len;
     const uint32_t* cand;
     uint32_t cand_cap;
+    unsigned long long* items;       // [N_CLASSES][item_cap]: s << 32 | literal length << 24 | entry of lit_rx_packed
+    uint32_t item_cap;
+    Counters* ctr;
+};
+__device__ __forceinline__ bool dev_word(uint32_t b) { return (b >= '0' && b <= '9') || (b >= 'A' && b <= 'Z') || b == '_' || (b >= 'a' && b <= 'z'); }
+// 4 bytes at any position p; bytes at or beyond len read as zero
+__device__ __forceinline__ uint32_t load4_unaligned(const uint8_t* __restrict__ text, uint32_t p, uint64_t len) {
+    const uint32_t b = p & ~3u;
+    if ((uint64_t)b + 8 <= len) {
+        const uint32_t lo = __ldg(reinterpret_cast<const uint32_t*>(text + b)), hi = __ldg(reinterpret_cast<const uint32_t*>(text + b + 4));
+        return __funnelshift_r(lo, hi, (p & 3u) * 8);
+    }
+    uint32_t w = 0;
+    for (int i = 0; i < 4; ++i) if ((uint64_t)p + i < len) w |= (uint32_t)text[p + i] << (8 * i);
+    return w;
+}
+// ASCII 'A'..'Z' -> lower case in all four bytes, everything else unchanged
+__device__ __forceinline__ uint32_t lower4(uint32_t t) {
+    const uint32_t y = t & 0x7F7F7F7Fu;
+    const uint32_t up = (y + 0x3F3F3F3Fu) & ~(y + 0x25252525u) & ~t & 0x80808080u;
+    return t | (up >> 2);
+}
+__global__ void __launch_bounds__(256) k_confirm(ConfirmArgs a, DevPlan P) {
+    __shared__ ItemStage sg;
+    if (threadIdx.x < N_CLASSES) sg.n[threadIdx.x] = 0;
+    __syncthreads();
+    const uint32_t n = min(a.ctr->n_cand, a.cand_cap);
+    const uint32_t stride = gridDim.x * blockDim.x;
+    const uint32_t tmask = (1u << P.table_bits) - 1u;
+    for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < n; c += stride) {
+        const uint32_t pos = a.cand[c];
+        const uint32_t w = load4_unaligned(a.text, pos, a.len);
+        const uint32_t f = w | 0x20202020u;
+        uint32_t slot = (f * GRAM_MUL2) >> (32 - P.table_bits);
+        uint4 gs;
+        while ((gs = __ldg(&P.gram_slots[slot])).x != 0 && gs.x != f) slot = (slot + 1) & tmask;
+        for (uint32_t q = 0; q < gs.z; ++q) {       // gs.z == 0 on an empty slot
+            const uint4 ld = __ldg(&P.lit_desc[gs.y + q]);
+            const uint32_t ll = ld.y & 0xFFu, go = (ld.y >> 8) & 0xFFu;
+            if (pos < go) continue;
+            const uint32_t s = pos - go;
+            if ((uint64_t)s + ll > a.len) continue;
+            const uint32_t* __restrict__ lit = reinterpret_cast<const uint32_t*>(P.lit_bytes8 + ld.x);
+            const bool icase = (ld.y >> 16) & 1u;
+            bool ok = true;
+            for (uint32_t j = 0; j < ll && ok; j += 4) {
+                uint32_t t = (j == go) ? w : load4_unaligned(a.text, s + j, a.len);
+                if (icase) t = lower4(t);
+                const uint32_t rem = ll - j;
+                const uint32_t mask = rem >= 4 ? 0xFFFFFFFFu : (1u << (8 * rem)) - 1u;
+                ok = ((t ^ __ldg(lit + (j >> 2))) & mask) == 0;
+            }
+            if (!ok) continue;
+            for (uint32_t j = ld.z; j < ld.z + ld.w; ++j) {
+                const uint32_t mode = __ldg(&P.lit_rx_packed[j]) >> 24;
+                const uint32_t cls = (mode & 1u) ? 0u : (mode & 8u) ? 1u : (mode & 16u) ? 2u : 3u;
+                const unsigned long long item = ((unsigned long long)s << 32) | ((unsigned long long)ll << 24) | j;
+                const uint32_t idx = atomicAdd(&sg.n[cls], 1u);
+                if (idx < ITEM_STAGE) sg.buf[cls][idx] = item;
+                else {      // staging full: straight to the global queue
+                    const uint32_t gi = atomicAdd(&a.ctr->n_items[cls], 1u);
+                    if (gi < a.item_cap) a.items[(size_t)cls * a.item_cap + gi] = item; else atomicOr(&a.ctr->overflow, 128u);
+                }
+            }
+        }
+    }
+    __syncthreads();
+    if (threadIdx.x < N_CLASSES) {
+        const uint32_t staged = min(sg.n[threadIdx.x], ITEM_STAGE);
+        sg.base[threadIdx.x] = staged ? atomicAdd(&a.ctr->n_items[threadIdx.x], staged) : 0u;
+    }
+    __syncthreads();
+    for (int cls = 0; cls < N_CLASSES; ++cls) {
+        const uint32_t staged = min(sg.n[cls], ITEM_STAGE), base = sg.base[cls];
+        for (uint32_t q = threadIdx.x; q < staged; q += blockDim.x) {
+            if (base + q < a.item_cap) a.items[(size_t)cls * a.item_cap + base + q] = sg.buf[cls][q];
+            else atomicOr(&a.ctr->overflow, 128u);
+        }
+    }
+}
+
+struct ResolveArgs {
+    const uint8_t* text;
+    uint64_t len;
+    const unsigned long long* items;
+    uint32_t item_cap;
     const uint32_t* tile_prefix;     // exclusive newline count before each 32 KiB tile
     uint32_t n_tiles;
     const uint64_t* log_off;
@@ -535,86 +632,86 @@ struct ConfirmArgs {
     uint32_t rec_cap;
     Counters* ctr;
 };
-__device__ __forceinline__ bool dev_word(uint8_t b) { return (b >= '0' && b <= '9') || (b >= 'A' && b <= 'Z') || b == '_' || (b >= 'a' && b <= 'z'); }
-__global__ void __launch_bounds__(256) k_confirm(ConfirmArgs a, DevPlan P) {
+constexpr uint32_t ANCHOR_BUDGET = 24;     // automaton steps an item may spend here before it is handed to k_verify
+__global__ void __launch_bounds__(256) k_resolve(ResolveArgs a, DevPlan P) {
     __shared__ QStage s_rec, s_task;
     if (threadIdx.x == 0) { s_rec.n = 0; s_task.n = 0; }
     __syncthreads();
-    const uint32_t n = min(a.ctr->n_cand, a.cand_cap);
-    const uint32_t stride = gridDim.x * blockDim.x;
-    const uint32_t rounds = (n + stride - 1) / stride;
-    uint32_t c = blockIdx.x * blockDim.x + threadIdx.x;
-    for (uint32_t round = 0; round < rounds; ++round, c += stride) {
-      if (round) {
-          stage_flush(s_rec, a.ctr, &a.ctr->n_recs, a.recs, a.rec_cap, 4u, false);
-          stage_flush(s_task, a.ctr, &a.ctr->n_tasks, a.tasks, a.task_cap, 2u, false);
-      }
-      if (c < n) do {
-        const uint32_t pos = a.cand[c];
-        uint32_t w = 0;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) if ((uint64_t)pos + i < a.len) w |= (uint32_t)a.text[pos + i] << (8 * i);
-        const uint32_t f = w | 0x20202020u;
-        const uint32_t tmask = (1u << P.table_bits) - 1u;
-        uint32_t slot = (f * GRAM_MUL2) >> (32 - P.table_bits);
-        uint32_t key;
-        while ((key = P.table_key[slot]) != 0 && key != f) slot = (slot + 1) & tmask;
-        if (key == 0) break;
-        // line of `pos`: the newline prefix of its tile (and its neighbour) brackets the index
-        const uint32_t t = pos / TILE_BYTES;
-        uint32_t glo = a.tile_prefix[t], ghi = (t + 1 < a.n_tiles ? a.tile_prefix[t + 1] : a.ctr->n_lines_total) + 1;
-        if (a.n_logs > 1) {
-            glo += upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, (uint64_t)t * TILE_BYTES) - 1;
-            ghi += upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, (uint64_t)(t + 1) * TILE_BYTES);
-        }
-        const uint32_t gmax = min(a.ctr->n_lines_total, a.n_lines_total);
-        ghi = min(ghi, gmax);
-        if (glo >= ghi) break;                    // beyond the (under-estimated) line arrays: the call is re-run
-        const uint32_t g = glo + upper_bound_dev<uint32_t>(a.line_start + glo, ghi - glo, pos) - 1;
-        if (g >= gmax || g + 1 == glo) break;
-        const uint32_t ls = a.line_start[g], le = a.line_end[g];
-        const uint32_t lb = P.table_begin[slot], lc = P.table_count[slot];
-        for (uint32_t q = 0; q < lc; ++q) {
-            const uint32_t l = P.gram_lits[lb + q];
-            const uint32_t go = P.lit_gram_off[l], ll = P.lit_len[l];
-            if (pos < ls + go) continue;
-            const uint32_t s = pos - go;
-            if (s + ll > le) continue;
-            const uint8_t* __restrict__ lit = P.lit_bytes + P.lit_off[l];
-            bool ok = true;
-            if (P.lit_icase[l]) {
-                for (uint32_t j = 0; j < ll && ok; ++j) {
-                    uint8_t b = a.text[s + j];
-                    if (b >= 'A' && b <= 'Z') b += 32;
-                    ok = b == lit[j];
-                }
-            } else {
-                for (uint32_t j = 0; j < ll && ok; ++j) ok = a.text[s + j] == lit[j];
+    const uint32_t n0 = min(a.ctr->n_items[0], a.item_cap), n1 = min(a.ctr->n_items[1], a.item_cap),
+                   n2 = min(a.ctr->n_items[2], a.item_cap), n3 = min(a.ctr->n_items[3], a.item_cap);
+    const uint32_t c1 = (n0 + blockDim.x - 1) / blockDim.x, c2 = c1 + (n1 + blockDim.x - 1) / blockDim.x,
+                   c3 = c2 + (n2 + blockDim.x - 1) / blockDim.x, c4 = c3 + (n3 + blockDim.x - 1) / blockDim.x;
+    const uint32_t gmax = min(a.ctr->n_lines_total, a.n_lines_total);
+    for (uint32_t ch = blockIdx.x; ch < c4; ch += gridDim.x) {
+        // a chunk of 256 items never straddles two classes: the block does one kind of work at a time
+        const uint32_t cls = ch >= c3 ? 3u : ch >= c2 ? 2u : ch >= c1 ? 1u : 0u;
+        const uint32_t first = cls == 3 ? c3 : cls == 2 ? c2 : cls == 1 ? c1 : 0u;
+        const uint32_t count = cls == 3 ? n3 : cls == 2 ? n2 : cls == 1 ? n1 : n0;
+        const uint32_t idx = (ch - first) * blockDim.x + threadIdx.x;
+        if (idx < count) do {
+            const unsigned long long item = a.items[(size_t)cls * a.item_cap + idx];
+            const uint32_t s = (uint32_t)(item >> 32), ll = (uint32_t)(item >> 24) & 0xFFu, e2 = s + ll;
+            const uint32_t packed = __ldg(&P.lit_rx_packed[(uint32_t)item & 0xFFFFFFu]);
+            const uint32_t r = packed & 0xFFFFFFu, mode = packed >> 24;
+            // line of the occurrence: the newline prefix of its tile (and its neighbour) brackets the index
+            const uint32_t t = s / TILE_BYTES;
+            uint32_t glo = a.tile_prefix[t], ghi = (t + 1 < a.n_tiles ? a.tile_prefix[t + 1] : a.ctr->n_lines_total) + 1;
+            if (a.n_logs > 1) {
+                glo += upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, (uint64_t)t * TILE_BYTES) - 1;
+                ghi += upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, (uint64_t)(t + 1) * TILE_BYTES);
             }
-            if (!ok) continue;
-            const uint32_t rb = P.lit_rx_begin[l], re = P.lit_rx_begin[l + 1];
-            for (uint32_t j = rb; j < re; ++j) {
-                const uint32_t r = P.lit_rx[j];
-                const uint32_t mode = P.lit_rx_mode[j];
-                if (mode & 1u) {
-                    // literal-with-boundaries pattern: decided right here at the occurrence
-                    const uint32_t e2 = s + ll;
-                    bool hit = true;
-                    if (mode & 2u) hit = (s > ls && dev_word(a.text[s - 1])) != dev_word(a.text[s]);
-                    if (hit && (mode & 4u)) hit = dev_word(a.text[e2 - 1]) != (e2 < le && dev_word(a.text[e2]));
-                    if (hit) stage_put(s_rec, a.ctr, &a.ctr->n_recs, a.recs, a.rec_cap, 4u, ((unsigned long long)r << P.gb) | g);
-                    continue;
-                }
-                if (P.rx_kind[r] == 0) {
-                    stage_put(s_task, a.ctr, &a.ctr->n_tasks, a.tasks, a.task_cap, 2u, ((unsigned long long)r << 32) | g);
-                } else {
-                    const uint32_t idx = atomicAdd(&a.ctr->n_vm_tasks, 1u);
-                    if (idx < a.vm_task_cap) a.vm_tasks[idx] = ((unsigned long long)r << 32) | g;
+            ghi = min(ghi, gmax);
+            if (glo >= ghi) break;                    // beyond the (under-estimated) line arrays: the call is re-run
+            const uint32_t g = glo + upper_bound_dev<uint32_t>(a.line_start + glo, ghi - glo, s) - 1;
+            if (g >= gmax || g + 1 == glo) break;
+            const uint32_t ls = a.line_start[g], le = a.line_end[g];
+            if (e2 > le) break;                       // the occurrence runs into the line separator
+            const unsigned long long rec = ((unsigned long long)r << P.gb) | g;
+            if (cls == 0) {
+                // literal-with-boundaries pattern (mode bits 2/4: \b required left/right; 32/64: the literal's
+                // first/last byte is a word byte)
+                bool hit = true;
+                if (mode & 2u) hit = (s > ls && dev_word(a.text[s - 1])) != ((mode & 32u) != 0);
+                if (hit && (mode & 4u)) hit = ((mode & 64u) != 0) != (e2 < le && dev_word(a.text[e2]));
+                if (hit) stage_put(s_rec, a.ctr, &a.ctr->n_recs, a.recs, a.rec_cap, 4u, rec);
+            } else if (cls == 3) {
+                if (P.rx_kind[r] == 0) stage_put(s_task, a.ctr, &a.ctr->n_tasks, a.tasks, a.task_cap, 2u, ((unsigned long long)r << 32) | g);
+                else {
+                    const uint32_t vi = atomicAdd(&a.ctr->n_vm_tasks, 1u);
+                    if (vi < a.vm_task_cap) a.vm_tasks[vi] = ((unsigned long long)r << 32) | g;
                     else atomicOr(&a.ctr->overflow, 32u);
                 }
+            } else {
+                // every match starts (class 1) / ends (class 2) with this literal: anchored automaton from the
+                // occurrence. Walks die or match within a few bytes; one that is still undecided after
+                // ANCHOR_BUDGET steps (".*" tails) goes to k_verify's walk of the whole line.
+                const uint4 ad = __ldg(&P.anchor_desc[r]);
+                const uint32_t nc = ad.y;
+                const uint16_t* __restrict__ T = P.dfa_trans + ad.x;
+                const uint8_t* __restrict__ cm = P.rx_acmap + (size_t)r * 256;
+                uint32_t st, budget = ANCHOR_BUDGET;
+                if (cls == 1) {
+                    st = s == ls ? (ad.z & 0xFFFFu) : dev_word(a.text[s - 1]) ? ad.w : (ad.z >> 16);
+                    const long tpos = tail_terminator(a.text, ls, le);
+                    uint32_t p2 = s;
+                    while (st > 1u && p2 < le && budget) {
+                        if ((long)p2 == tpos) { st = T[st * nc + nc - 2]; if (st <= 1u) break; }
+                        st = T[st * nc + cm[a.text[p2]]];
+                        ++p2; --budget;
+                    }
+                    if (st > 1u && p2 == le) st = T[st * nc + nc - 1];
+                } else {
+                    st = e2 == le ? (ad.z & 0xFFFFu) : dev_word(a.text[e2]) ? ad.w : (ad.z >> 16);
+                    uint32_t p2 = e2;
+                    while (st > 1u && p2 > ls && budget) { st = T[st * nc + cm[a.text[p2 - 1]]]; --p2; --budget; }
+                    if (st > 1u && p2 == ls) st = T[st * nc + nc - 1];
+                }
+                if (st == 1u) stage_put(s_rec, a.ctr, &a.ctr->n_recs, a.recs, a.rec_cap, 4u, rec);
+                else if (st > 1u) stage_put(s_task, a.ctr, &a.ctr->n_tasks, a.tasks, a.task_cap, 2u, ((unsigned long long)r << 32) | g);
             }
-        }
-      } while (false);
+        } while (false);
+        // no barrier per chunk: a block handles a few chunks and its output fits the staging buffers
+        // (entries beyond them go straight to the global queues)
     }
     stage_flush(s_rec, a.ctr, &a.ctr->n_recs, a.recs, a.rec_cap, 4u, true);
     stage_flush(s_task, a.ctr, &a.ctr->n_tasks, a.tasks, a.task_cap, 2u, true);
@@ -1256,7 +1353,8 @@ struct lp_ctx {
     std::vector<uint32_t> group_words;
     const uint8_t* d_rx_record = nullptr;
     uint32_t n_group_record_rx = 0;
-    DevBuf f_bitmap, f_key, f_begin, f_count, f_lits, f_goff;   // prefilter tables (re-uploaded by calibration)
+    DevBuf f_bitmap, f_key, f_lits;   // prefilter tables (re-uploaded by calibration)
+    std::vector<uint32_t> lit_off8;   // literal -> offset in the 8-byte aligned device copy of the literal bytes
     bool calibrated = false;
     int recalibrations = 0;
     DevPlan dp{};
@@ -1265,6 +1363,9 @@ struct lp_ctx {
 
     // scratch (grow-only)
     DevBuf text, log_off, tile_counts, counters, line_start, line_end, first_line, n_lines;
+    DevBuf items;
+    size_t est_items = 0;
+    int occ_confirm = 0, occ_resolve = 0;
     DevBuf cand, tasks, vm_tasks, vm_stack, recs, recs_alt, cub_tmp, rx_begin, ctx_flags;
     DevBuf ev_key, ev_key_alt, ev_log, slot_key, slot_key_alt, ev_idx, ev_idx_alt, rank_in_slot, freq_delta, prior;
     DevBuf out_line, out_pat, out_score, out_factors, sort_key, sort_key_alt, order, order_alt, log_sorted, log_sorted_alt;
@@ -1305,11 +1406,26 @@ void upload_filter(lp_ctx* c) {
     DevPlan& d = c->dp;
     d.bitmap = upload_into(c->f_bitmap, pl.bitmap);
     d.table_bits = pl.table_bits;
-    d.table_key = upload_into(c->f_key, pl.table_key);
-    d.table_begin = upload_into(c->f_begin, pl.table_begin);
-    d.table_count = upload_into(c->f_count, pl.table_count);
-    d.gram_lits = upload_into(c->f_lits, pl.gram_lits);
-    d.lit_gram_off = upload_into(c->f_goff, pl.lit_gram_off);
+    // literal descriptors grouped by gram slot (a literal has exactly one gram)
+    auto is_word = [](unsigned char b) { return (b >= '0' && b <= '9') || (b >= 'A' && b <= 'Z') || b == '_' || (b >= 'a' && b <= 'z'); };
+    std::vector<uint4> slots(pl.table_key.size()), descs;
+    descs.reserve(pl.lit_off.size());
+    for (size_t sl = 0; sl < pl.table_key.size(); ++sl) {
+        slots[sl] = make_uint4(pl.table_key[sl], (uint32_t)descs.size(), pl.table_key[sl] ? pl.table_count[sl] : 0u, 0u);
+        if (!pl.table_key[sl]) continue;
+        for (uint32_t q = 0; q < pl.table_count[sl]; ++q) {
+            const uint32_t l = pl.gram_lits[pl.table_begin[sl] + q];
+            const uint32_t len = pl.lit_len[l];
+            const unsigned char first = pl.lit_bytes[pl.lit_off[l]], last = pl.lit_bytes[pl.lit_off[l] + len - 1];
+            if (len > 255 || pl.lit_gram_off[l] > 255) throw std::logic_error("literal too long for the packed descriptor");
+            descs.push_back(make_uint4(c->lit_off8[l], len | (pl.lit_gram_off[l] << 8) | (pl.lit_icase[l] ? 1u << 16 : 0u) |
+                                                       (is_word(first) ? 1u << 17 : 0u) | (is_word(last) ? 1u << 18 : 0u),
+                                       pl.lit_rx_begin[l], pl.lit_rx_begin[l + 1] - pl.lit_rx_begin[l]));
+        }
+    }
+    if (descs.empty()) descs.push_back(make_uint4(0, 0, 0, 0));
+    d.gram_slots = upload_into(c->f_key, slots);
+    d.lit_desc = upload_into(c->f_lits, descs);
 }
 // One-time tuning of the literal prefilter against the first log this context sees: 4 x 1 MiB of
 // its text decide which 4-byte window of each literal is the rarest. Results never depend on it.
@@ -1344,18 +1460,42 @@ void upload_plan(lp_ctx* c) {
     d.rx_start = upload(K, pl.rx_start);
     d.dfa_trans = upload(K, pl.dfa_trans);
     d.rx_cmap = upload(K, pl.rx_cmap);
+    {
+        std::vector<uint4> ad(std::max<uint32_t>(pl.n_rx, 1));
+        for (uint32_t r = 0; r < pl.n_rx; ++r)
+            ad[r] = make_uint4(pl.rx_adfa_off[r], pl.rx_ancls[r], (uint32_t)pl.rx_astart[r * 3] | ((uint32_t)pl.rx_astart[r * 3 + 1] << 16),
+                               pl.rx_astart[r * 3 + 2]);
+        d.anchor_desc = upload(K, ad);
+    }
+    d.rx_acmap = upload(K, pl.rx_acmap);
     d.always_list = upload(K, pl.always_list);
     d.n_always = (uint32_t)pl.always_list.size();
     d.always_vm_list = upload(K, pl.always_vm_list);
     d.n_always_vm = (uint32_t)pl.always_vm_list.size();
+    {
+        std::vector<uint8_t> b8;
+        c->lit_off8.assign(pl.lit_off.size(), 0);
+        for (size_t l = 0; l < pl.lit_off.size(); ++l) {
+            c->lit_off8[l] = (uint32_t)b8.size();
+            b8.insert(b8.end(), pl.lit_bytes.begin() + pl.lit_off[l], pl.lit_bytes.begin() + pl.lit_off[l] + pl.lit_len[l]);
+            b8.resize((b8.size() + 7) & ~size_t(7), 0);
+        }
+        b8.resize(b8.size() + 8, 0);
+        d.lit_bytes8 = upload(K, b8);
+        std::vector<uint32_t> packed(pl.lit_rx.size());
+        if (pl.lit_rx.size() >= (1u << 24)) throw std::length_error("more than 2^24 (literal, regex) pairs");
+        auto is_word = [](unsigned char b) { return (b >= '0' && b <= '9') || (b >= 'A' && b <= 'Z') || b == '_' || (b >= 'a' && b <= 'z'); };
+        for (size_t l = 0; l < pl.lit_off.size(); ++l) {
+            const uint32_t edge = (is_word(pl.lit_bytes[pl.lit_off[l]]) ? 32u : 0u) | (is_word(pl.lit_bytes[pl.lit_off[l] + pl.lit_len[l] - 1]) ? 64u : 0u);
+            for (uint32_t j = pl.lit_rx_begin[l]; j < pl.lit_rx_begin[l + 1]; ++j) {
+                if (pl.lit_rx[j] >= (1u << 24)) throw std::length_error("more than 2^24 distinct regexes");
+                packed[j] = pl.lit_rx[j] | (((uint32_t)pl.lit_rx_mode[j] | edge) << 24);
+            }
+        }
+        if (packed.empty()) packed.push_back(0);
+        d.lit_rx_packed = upload(K, packed);
+    }
     upload_filter(c);
-    d.lit_bytes = upload(K, pl.lit_bytes);
-    d.lit_off = upload(K, pl.lit_off);
-    d.lit_len = upload(K, pl.lit_len);
-    d.lit_icase = upload(K, pl.lit_icase);
-    d.lit_rx_begin = upload(K, pl.lit_rx_begin);
-    d.lit_rx = upload(K, pl.lit_rx);
-    d.lit_rx_mode = upload(K, pl.lit_rx_mode);
     d.n_pat = pl.n_pat;
     d.pat_primary = upload(K, pl.pat_primary);
     d.pat_conf = upload(K, pl.pat_conf);
@@ -1435,10 +1575,12 @@ void check_estimates(lp_ctx* c, const Counters& h, uint32_t n_logs, bool events_
     if (h.n_cand > c->est_cand) { bump(c->est_cand, h.n_cand); retry = true; }
     if (h.n_tasks > c->est_tasks) { bump(c->est_tasks, h.n_tasks); retry = true; }
     if (h.n_vm_tasks > c->est_vm_tasks) { bump(c->est_vm_tasks, h.n_vm_tasks); retry = true; }
+    const uint32_t max_items = std::max(std::max(h.n_items[0], h.n_items[1]), std::max(h.n_items[2], h.n_items[3]));
+    if (max_items > c->est_items) { bump(c->est_items, max_items); retry = true; }
     if (h.n_recs > c->est_recs) { bump(c->est_recs, h.n_recs); retry = true; }
     if (events_too && h.n_events > c->est_events) { bump(c->est_events, h.n_events); retry = true; }
     if (!retry && (h.overflow & ~16u)) {   // a flag without a matching count: grow everything once
-        c->est_cand *= 2; c->est_tasks *= 2; c->est_recs *= 2; c->est_events *= 2; c->est_vm_tasks *= 2;
+        c->est_cand *= 2; c->est_tasks *= 2; c->est_recs *= 2; c->est_events *= 2; c->est_vm_tasks *= 2; c->est_items *= 2;
         retry = true;
     }
     if (retry) {
@@ -1448,7 +1590,7 @@ void check_estimates(lp_ctx* c, const Counters& h, uint32_t n_logs, bool events_
     c->retries = 0;
     // remember what this log needed (with headroom) for the next call
     bump(c->est_lines, G + 1); bump(c->est_cand, h.n_cand); bump(c->est_tasks, h.n_tasks);
-    bump(c->est_vm_tasks, h.n_vm_tasks); bump(c->est_recs, h.n_recs);
+    bump(c->est_vm_tasks, h.n_vm_tasks); bump(c->est_recs, h.n_recs); bump(c->est_items, max_items);
     if (events_too) bump(c->est_events, h.n_events);
 }
 
@@ -1481,6 +1623,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         c->est_lines = (size_t)(len / 64 + n_logs + 4096);
         c->est_cand = (size_t)(len / 256 + (1u << 16));
         c->est_tasks = (size_t)(len / 256 + (1u << 16));
+        c->est_items = (size_t)(len / 256 + (1u << 16));
         c->est_vm_tasks = (size_t)(len / 1024 + (1u << 14));
         c->est_recs = (size_t)(len / 256 + (1u << 16));
         c->est_events = (size_t)(len / 2048 + (1u << 14));
@@ -1504,6 +1647,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     c->ctx_flags.ensure((line_cap / 4 + 2) * 4);
     c->cand.ensure(c->est_cand * 4);
     c->tasks.ensure(c->est_tasks * 8);
+    c->items.ensure(c->est_items * 8 * N_CLASSES);
     if (has_vm) { c->vm_tasks.ensure(c->est_vm_tasks * 8); c->vm_stack.ensure((size_t)vm_grid * vm_block * lpx::VM_STACK_WORDS * 4); }
     c->recs.ensure(rec_cap * 8);
     c->recs_alt.ensure(rec_cap * 8);
@@ -1550,12 +1694,23 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     if (use_filter) {
         ConfirmArgs ca{};
         ca.text = d_text; ca.len = len; ca.cand = c->cand.as<uint32_t>(); ca.cand_cap = fa.cand_cap;
-        ca.tile_prefix = c->tile_counts.as<uint32_t>(); ca.n_tiles = n_tiles; ca.log_off = c->log_off.as<uint64_t>(); ca.n_logs = n_logs;
-        ca.line_start = c->line_start.as<uint32_t>(); ca.line_end = c->line_end.as<uint32_t>(); ca.n_lines_total = (uint32_t)line_cap;
-        ca.tasks = c->tasks.as<unsigned long long>(); ca.task_cap = va.task_cap; ca.ctr = ctr;
-        ca.vm_tasks = c->vm_tasks.as<unsigned long long>(); ca.vm_task_cap = va.vm_task_cap;
-        ca.recs = c->recs.as<unsigned long long>(); ca.rec_cap = (uint32_t)rec_cap;
-        k_confirm<<<c->n_sm * 8, 256, 0, st>>>(ca, c->dp);
+        ca.items = c->items.as<unsigned long long>(); ca.item_cap = (uint32_t)std::min<size_t>(c->est_items, 0xFFFFFFFFu); ca.ctr = ctr;
+        ResolveArgs ra{};
+        ra.text = d_text; ra.len = len; ra.items = ca.items; ra.item_cap = ca.item_cap;
+        ra.tile_prefix = c->tile_counts.as<uint32_t>(); ra.n_tiles = n_tiles; ra.log_off = c->log_off.as<uint64_t>(); ra.n_logs = n_logs;
+        ra.line_start = c->line_start.as<uint32_t>(); ra.line_end = c->line_end.as<uint32_t>(); ra.n_lines_total = (uint32_t)line_cap;
+        ra.tasks = c->tasks.as<unsigned long long>(); ra.task_cap = va.task_cap; ra.ctr = ctr;
+        ra.vm_tasks = c->vm_tasks.as<unsigned long long>(); ra.vm_task_cap = va.vm_task_cap;
+        ra.recs = c->recs.as<unsigned long long>(); ra.rec_cap = (uint32_t)rec_cap;
+        // grids of exactly one resident wave (grid-stride kernels; a partial second wave would run alone at the end)
+        if (!c->occ_confirm) {
+            CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c->occ_confirm, k_confirm, 256, 0));
+            CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c->occ_resolve, k_resolve, 256, 0));
+            c->occ_confirm = std::max(1, c->occ_confirm); c->occ_resolve = std::max(1, c->occ_resolve);
+        }
+        k_confirm<<<c->n_sm * c->occ_confirm, 256, 0, st>>>(ca, c->dp);
+        k_resolve<<<c->n_sm * c->occ_resolve, 256, 0, st>>>(ra, c->dp);
+        c->launches += 1;
         k_verify<<<c->n_sm * 8, 256, 0, st>>>(va, c->dp);
         c->launches += 2;
         if (has_vm) { k_verify_vm<<<vm_grid, vm_block, 0, st>>>(va, c->dp); c->launches += 1; }
@@ -1896,7 +2051,7 @@ void lp_destroy(lp_ctx* c) {
                      &c->ev_log, &c->slot_key, &c->slot_key_alt, &c->ev_idx, &c->ev_idx_alt, &c->rank_in_slot, &c->freq_delta, &c->prior,
                      &c->out_line, &c->out_pat, &c->out_score, &c->out_factors, &c->sort_key, &c->sort_key_alt, &c->order, &c->order_alt,
                      &c->log_sorted, &c->log_sorted_alt, &c->rank, &c->log_event_begin, &c->n_unique, &c->d_lut,
-                     &c->f_bitmap, &c->f_key, &c->f_begin, &c->f_count, &c->f_lits, &c->f_goff};
+                     &c->f_bitmap, &c->f_key, &c->f_lits, &c->items, &c->seq_tab_off, &c->seq_tab, &c->seq_T, &c->prior_eff, &c->any_flag};
     for (DevBuf* b : all) b->release();
     c->stage.release();
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);

@@ -30,25 +30,28 @@ struct DevPlan {
     const uint16_t* rx_start;
     const uint16_t* dfa_trans;
     const uint8_t* rx_cmap;
+    // anchored automata (verification at a literal occurrence): {offset into dfa_trans, n_classes,
+    // start(line edge) | start(after non-word) << 16, start(after word)} and a 256-byte class map per regex
+    const uint4* anchor_desc;
+    const uint8_t* rx_acmap;
     const uint32_t* always_list;      // DFA regexes without a usable literal
     uint32_t n_always;
     const uint32_t* always_vm_list;   // bytecode regexes without a usable literal
     uint32_t n_always_vm;
     // literals / gram filter
+    // Tables packed so that k_confirm, whose lanes all read different addresses, needs one load each:
+    //   gram_slots[2^table_bits]  {folded gram (0 = empty), first literal, literal count, -}
+    //   lit_desc[]                literals grouped by gram: {offset into lit_bytes8, len | gram offset << 8 |
+    //                             icase << 16 | first byte is a word byte << 17 | last << 18, first entry of
+    //                             lit_rx_packed, entry count}
+    //   lit_bytes8                literal bytes, each literal starting on an 8-byte boundary
+    //   lit_rx_packed[]           regex id | verification mode << 24
     const uint32_t* bitmap;
     uint32_t table_bits;
-    const uint32_t* table_key;
-    const uint32_t* table_begin;
-    const uint32_t* table_count;
-    const uint32_t* gram_lits;
-    const uint8_t* lit_bytes;
-    const uint32_t* lit_off;
-    const uint32_t* lit_len;
-    const uint32_t* lit_gram_off;
-    const uint8_t* lit_icase;
-    const uint32_t* lit_rx_begin;
-    const uint32_t* lit_rx;
-    const uint8_t* lit_rx_mode;
+    const uint4* gram_slots;
+    const uint4* lit_desc;
+    const uint8_t* lit_bytes8;
+    const uint32_t* lit_rx_packed;
     // patterns
     uint32_t n_pat;
     const uint32_t* pat_primary;
@@ -95,11 +98,11 @@ struct Counters {
     unsigned int n_tasks;
     unsigned int n_recs;
     unsigned int n_events;
-    unsigned int overflow;     // bit0 cand, bit1 tasks, bit2 recs, bit3 events, bit4 backtrack budget, bit5 vm tasks, bit6 line arrays
+    unsigned int overflow;     // bit0 cand, bit1 tasks, bit2 recs, bit3 events, bit4 backtrack budget, bit5 vm tasks, bit6 line arrays, bit7 item queues
     unsigned int n_unique;     // written by the unique pass (includes one sentinel group when padding was sorted)
     unsigned int n_vm_tasks;
     unsigned int n_lines_total;    // newlines + logs (G), published by k_scan_tiles
-    unsigned int pad[4];
+    unsigned int n_items[4];       // (literal occurrence, regex) pairs per verification class, k_confirm -> k_resolve
 };
 
 }  // namespace lpk

@@ -138,6 +138,9 @@ void build_plan(const std::vector<PlanPatternIn>& pats, Plan& pl, int64_t* bad) 
         pl.rx_vm_off.push_back(0); pl.rx_vm_len.push_back(0); pl.rx_vm_slots.push_back(0);
         pl.rx_vm_caps.push_back(0); pl.rx_vm_set_base.push_back(0);
         pl.rx_cmap.resize((size_t)pl.n_rx * 256, 0);
+        pl.rx_adfa_off.push_back(0); pl.rx_ancls.push_back(0);
+        pl.rx_astart.resize((size_t)pl.n_rx * 3, 0);
+        pl.rx_acmap.resize((size_t)pl.n_rx * 256, 0);
         if (is_dfa) {
             pl.rx_dfa_off[id] = (uint32_t)pl.dfa_trans.size();
             pl.rx_ncls[id] = dfa.n_classes;
@@ -169,6 +172,18 @@ void build_plan(const std::vector<PlanPatternIn>& pats, Plan& pl, int64_t* bad) 
         } else {
             lits = required_literals(*pr.root, 4);
             modes.assign(lits.size(), 0);
+            // every match starts (or ends) with one of the literals: verified at the occurrence by an
+            // anchored automaton, forwards from its first byte or backwards from its last
+            Dfa ad;
+            const int am = is_dfa ? choose_anchor(*pr.root, lits, ad) : 0;
+            if (am) {
+                modes.assign(lits.size(), (uint8_t)(am == 1 ? 8 : 16));
+                pl.rx_adfa_off[id] = (uint32_t)pl.dfa_trans.size();
+                pl.rx_ancls[id] = ad.n_classes;
+                for (int k = 0; k < 3; ++k) pl.rx_astart[(size_t)id * 3 + k] = ad.start_ctx[k];
+                pl.dfa_trans.insert(pl.dfa_trans.end(), ad.trans.begin(), ad.trans.end());
+                memcpy(&pl.rx_acmap[(size_t)id * 256], ad.classmap, 256);
+            }
         }
         pl.rx_always.push_back(lits.empty() ? 1 : 0);
         rx_lits.push_back(std::move(lits));
@@ -310,6 +325,7 @@ void build_plan(const std::vector<PlanPatternIn>& pats, Plan& pl, int64_t* bad) 
                 pl.lit_len.push_back((uint32_t)l.bytes.size());
                 pl.lit_icase.push_back(l.icase ? 1 : 0);
                 pl.lit_bytes.insert(pl.lit_bytes.end(), l.bytes.begin(), l.bytes.end());
+                for (unsigned char ch : l.bytes) if (ch == '\r' || ch == '\n') pl.lits_have_line_breaks = true;
                 lit_rx.emplace_back();
                 lit_mode.emplace_back();
                 pl.lit_gram_off.push_back(0);

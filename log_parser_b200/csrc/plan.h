@@ -42,6 +42,11 @@ struct Plan {
     std::vector<uint16_t> rx_start;
     std::vector<uint16_t> dfa_trans;
     std::vector<uint8_t> rx_cmap;         // 256 per regex
+    // anchored automaton (rx_compile.cpp: build_dfa_anchored) of regexes decided at their literal occurrences
+    std::vector<uint32_t> rx_adfa_off;    // offset into dfa_trans
+    std::vector<uint16_t> rx_ancls;
+    std::vector<uint16_t> rx_astart;      // 3 per regex: walk starts at the line edge / next to a non-word byte / next to a word byte
+    std::vector<uint8_t> rx_acmap;        // 256 per regex
     std::vector<uint32_t> always_list, always_vm_list;
     // bytecode programs (RXK_VM)
     std::vector<uint32_t> rx_vm_off, rx_vm_len, rx_vm_slots, rx_vm_caps, rx_vm_set_base;
@@ -64,8 +69,9 @@ struct Plan {
     std::vector<uint8_t> lit_bytes;
     std::vector<uint32_t> lit_off, lit_len, lit_gram_off;
     std::vector<uint8_t> lit_icase;
+    bool lits_have_line_breaks = false;               // some literal holds '\r' or '\n' (k_confirm then looks lines up eagerly)
     std::vector<uint32_t> lit_rx_begin, lit_rx;       // CSR literal -> regex ids
-    std::vector<uint8_t> lit_rx_mode;                 // per CSR entry: 0 verify by automaton; 1 | left\b<<1 | right\b<<2: decided at the occurrence
+    std::vector<uint8_t> lit_rx_mode;                 // per CSR entry: 0 walk the line; 1 | left\b<<1 | right\b<<2: boundary test at the occurrence; 8 / 16: anchored automaton forwards / backwards from the occurrence
     std::vector<uint32_t> bitmap;                     // 2^GRAM_BITS bits
     uint32_t table_bits = 0;
     std::vector<uint32_t> table_key;                  // folded gram, 0 = empty (0x20202020-folded grams are never 0)

@@ -80,10 +80,15 @@ bool cpset_has(const CpSet& s, uint32_t c);
 struct Dfa {
     uint16_t n_classes = 0;          // including the two virtual symbols
     uint16_t start = 0;
+    uint16_t start_ctx[3] = {0, 0, 0};   // anchored automata: start state when the walk begins at the line edge / after a non-word byte / after a word byte
     uint8_t classmap[256];
     std::vector<uint16_t> trans;     // n_states * n_classes
     uint32_t n_states() const { return n_classes ? (uint32_t)(trans.size() / n_classes) : 0; }
     bool match(const uint8_t* s, size_t n) const;  // host-side walk, identical to the device walker
+    // anchored automata (build_dfa_anchored), `s[0..n)` is the line: does a match START at `pos` /
+    // END at `pos`? Same loops as the device (k_confirm).
+    bool match_from(const uint8_t* s, size_t n, size_t pos) const;
+    bool match_ending_at(const uint8_t* s, size_t n, size_t pos) const;
 };
 constexpr uint16_t DFA_DEAD = 0, DFA_MATCH = 1;
 
@@ -91,6 +96,17 @@ constexpr uint16_t DFA_DEAD = 0, DFA_MATCH = 1;
 struct DfaLimits { uint32_t max_raw_states = 30000; uint32_t max_states = 8192; uint32_t max_nfa = 60000; };
 // Returns false (and leaves `out` empty) if the pattern exceeds the limits.
 bool build_dfa(const Ast& root, Dfa& out, const DfaLimits& lim = DfaLimits());
+// Automaton for verifying a match at a known literal occurrence instead of walking the whole line:
+// reverse = false: matches anchored at the walk's first byte; reverse = true: the reversed language,
+// walked from the end of a match towards the line start (refused for patterns using `$`/\Z).
+bool build_dfa_anchored(const Ast& root, bool reverse, Dfa& out, const DfaLimits& lim = DfaLimits());
+struct Literal;
+// True when every match accepted by the anchored automaton starts with (forward) / ends with (reverse)
+// a member of `lits` — so checking the literal occurrences alone decides Matcher.find() on the line.
+bool literals_cover(const Dfa& anchored, bool reverse, const std::vector<Literal>& lits);
+// 0: verify by walking the whole line; 1 / 2: `out` is the forward / backward anchored automaton and the
+// literal occurrences alone decide the line.
+int choose_anchor(const Ast& root, const std::vector<Literal>& lits, Dfa& out, const DfaLimits& lim = DfaLimits());
 
 // Product automaton of several regexes for the always-on scan (patterns without a usable literal):
 // one walk of a line decides all of them. A state carries the set of regexes already matched

@@ -78,12 +78,24 @@ void split_range(uint32_t lo, uint32_t hi, std::vector<Seq>& out) {
 
 struct Builder {
     Nfa& n;
-    explicit Builder(Nfa& nfa) : n(nfa) {}
+    bool rev;     // build the automaton of the reversed language (walked from a match's end towards the line start)
+    explicit Builder(Nfa& nfa, bool reversed = false) : n(nfa), rev(reversed) {}
 
     Frag set_frag(const CpSet& set) {
         int in = n.add(), out = n.add();
         std::vector<Seq> seqs;
         for (const auto& r : set) split_range(r.lo, std::min<uint32_t>(r.hi, 0x10FFFF), seqs);
+        if (rev) {      // bytes of each code point in reverse order; plain chains
+            for (const auto& s : seqs) {
+                int cur = in;
+                for (int i = s.n - 1; i >= 0; --i) {
+                    const int to = i == 0 ? out : n.add();
+                    n.st[cur].edges.push_back({s.lo[i], s.hi[i], to});
+                    cur = to;
+                }
+            }
+            return {in, out};
+        }
         // share continuation tails keyed by (remaining ranges) to keep big classes small
         std::map<std::vector<uint8_t>, int> tails;
         for (const auto& s : seqs) {
@@ -143,7 +155,11 @@ struct Builder {
             case AstKind::Group: return build(*a.kids[0]);
             case AstKind::Cat: {
                 Frag acc = empty_frag();
-                for (const auto& k : a.kids) { Frag f = build(*k); n.st[acc.out].eps.push_back(f.in); acc.out = f.out; }
+                for (size_t i = 0; i < a.kids.size(); ++i) {
+                    Frag f = build(*a.kids[rev ? a.kids.size() - 1 - i : i]);
+                    n.st[acc.out].eps.push_back(f.in);
+                    acc.out = f.out;
+                }
                 return acc;
             }
             case AstKind::Alt: {
@@ -157,7 +173,9 @@ struct Builder {
                     throw std::logic_error("multiline anchors are not DFA-representable here");
                 if (a.assert_kind == AssertKind::Eol) n.uses_eol = true;
                 int in = n.add(), out = n.add();
-                n.st[in].asserts.push_back({a.assert_kind, out});
+                AssertKind k = a.assert_kind;
+                if (rev) k = k == AssertKind::Begin ? AssertKind::End : k == AssertKind::End ? AssertKind::Begin : k;   // \b, \B are symmetric
+                n.st[in].asserts.push_back({k, out});
                 return {in, out};
             }
             default: throw std::logic_error("non-regular node in DFA build");
@@ -210,21 +228,25 @@ struct Subset {
 
 }  // namespace
 
-bool build_dfa(const Ast& root, Dfa& out, const DfaLimits& lim) {
+namespace {
+// mode 0: unanchored search from the line start. mode 1: a match must START at the walk's first byte;
+// mode 2: the reversed language, a match must END where the (backward) walk starts. Modes 1/2 get three
+// start states for the context on the other side of the starting point: line edge, non-word byte, word byte.
+bool build_dfa_impl(const Ast& root, Dfa& out, const DfaLimits& lim, int mode) {
     out = Dfa();
     Nfa nfa(lim.max_nfa);
     int start;
     try {
-        Builder b(nfa);
-        // unanchored search: a self-looping prefix state in front of the pattern
+        Builder b(nfa, mode == 2);
         start = nfa.add();
-        nfa.st[start].edges.push_back({0x00, 0xFF, start});
+        if (mode == 0) nfa.st[start].edges.push_back({0x00, 0xFF, start});   // unanchored search: a self-looping prefix state
         Frag f = b.build(root);
         nfa.st[start].eps.push_back(f.in);
         nfa.accept = f.out;
     } catch (const std::length_error&) {
         return false;
     }
+    if (mode == 2 && nfa.uses_eol) return false;      // `$` looks at what follows the match: not walkable backwards
 
     // byte classes from edge boundaries (+ word-byte boundaries for \b)
     bool cut[257];
@@ -263,6 +285,13 @@ bool build_dfa(const Ast& root, Dfa& out, const DfaLimits& lim) {
     Ctx c0;
     c0.at_begin = true;
     intern({start}, c0);
+    const int n_starts = mode == 0 ? 1 : 3;
+    if (mode != 0) {
+        Ctx c1, c2;
+        c2.prev_word = true;
+        const int s1 = intern({start}, c1), s2 = intern({start}, c2);
+        if (s1 != 1 || s2 != 2) throw std::logic_error("anchored start states");
+    }
     std::vector<int> clo, nxt;
     for (size_t si = 0; si < states.size(); ++si) {
         if (states.size() > lim.max_raw_states) return false;
@@ -324,12 +353,15 @@ bool build_dfa(const Ast& root, Dfa& out, const DfaLimits& lim) {
         if (nb2 == nblocks) break;
         nblocks = nb2;
     }
-    if (!live[0]) {  // pattern can never match
+    bool any_start_live = false;
+    for (int k = 0; k < n_starts; ++k) any_start_live |= live[k] != 0;
+    if (!any_start_live) {  // pattern can never match
         out.n_classes = 3;
         memset(out.classmap, 0, 256);
         out.trans.assign(2 * 3, DFA_DEAD);
         out.trans[1 * 3 + 0] = out.trans[1 * 3 + 1] = out.trans[1 * 3 + 2] = DFA_MATCH;
         out.start = DFA_DEAD;
+        out.start_ctx[0] = out.start_ctx[1] = out.start_ctx[2] = DFA_DEAD;
         return true;
     }
     // block table
@@ -366,9 +398,14 @@ bool build_dfa(const Ast& root, Dfa& out, const DfaLimits& lim) {
         row[nb2] = (uint16_t)bt[b][SYM_TPOS];
         row[nb2 + 1] = (uint16_t)bt[b][SYM_EOT];
     }
-    out.start = (uint16_t)(part[0] + 2);
+    out.start = live[0] ? (uint16_t)(part[0] + 2) : DFA_DEAD;
+    for (int k = 0; k < 3; ++k) out.start_ctx[k] = k < n_starts ? (live[k] ? (uint16_t)(part[k] + 2) : DFA_DEAD) : out.start;
     return true;
 }
+}  // namespace
+
+bool build_dfa(const Ast& root, Dfa& out, const DfaLimits& lim) { return build_dfa_impl(root, out, lim, 0); }
+bool build_dfa_anchored(const Ast& root, bool reverse, Dfa& out, const DfaLimits& lim) { return build_dfa_impl(root, out, lim, reverse ? 2 : 1); }
 
 bool build_multi_dfa(const std::vector<const Ast*>& roots, MultiDfa& out, uint32_t max_states, uint32_t max_nfa) {
     out = MultiDfa();
@@ -565,6 +602,104 @@ bool Dfa::match(const uint8_t* s, size_t n) const {
     }
     if (st > DFA_MATCH) st = trans[st * nc + nc - 1];
     return st == DFA_MATCH;
+}
+
+thread_local unsigned long long g_anchor_steps = 0;      // tuning aid: transitions taken by match_from / match_ending_at
+static inline bool word_byte_pub(int b) { return (b >= '0' && b <= '9') || (b >= 'A' && b <= 'Z') || b == '_' || (b >= 'a' && b <= 'z'); }
+
+bool Dfa::match_from(const uint8_t* s, size_t n, size_t pos) const {
+    if (!n_classes || pos > n) return false;
+    long tpos = -1;
+    if (n >= 1 && s[n - 1] == '\r') tpos = (long)n - 1;
+    else if (n >= 2 && s[n - 2] == 0xC2 && s[n - 1] == 0x85) tpos = (long)n - 2;
+    else if (n >= 3 && s[n - 3] == 0xE2 && s[n - 2] == 0x80 && (s[n - 1] == 0xA8 || s[n - 1] == 0xA9)) tpos = (long)n - 3;
+    const unsigned nc = n_classes;
+    unsigned st = start_ctx[pos == 0 ? 0 : word_byte_pub(s[pos - 1]) ? 2 : 1];
+    for (size_t i = pos; i < n && st > DFA_MATCH; ++i) {
+        if ((long)i == tpos) st = trans[st * nc + nc - 2];
+        st = trans[st * nc + classmap[s[i]]];
+        ++g_anchor_steps;
+    }
+    if (st > DFA_MATCH) st = trans[st * nc + nc - 1];
+    return st == DFA_MATCH;
+}
+bool Dfa::match_ending_at(const uint8_t* s, size_t n, size_t pos) const {
+    if (!n_classes || pos > n) return false;
+    const unsigned nc = n_classes;
+    unsigned st = start_ctx[pos == n ? 0 : word_byte_pub(s[pos]) ? 2 : 1];
+    for (size_t i = pos; i > 0 && st > DFA_MATCH; --i) { st = trans[st * nc + classmap[s[i - 1]]]; ++g_anchor_steps; }
+    if (st > DFA_MATCH) st = trans[st * nc + nc - 1];
+    return st == DFA_MATCH;
+}
+
+bool literals_cover(const Dfa& d, bool reverse, const std::vector<Literal>& lits) {
+    if (lits.empty() || !d.n_classes) return false;
+    // trie of the literals (reversed for the backward automaton); case-insensitive letters get both cases
+    struct Node { std::map<int, int> kid; bool end = false; };
+    std::vector<Node> trie(1);
+    for (const auto& l : lits) {
+        if (l.bytes.empty()) return false;
+        std::vector<int> cur{0};
+        for (size_t i = 0; i < l.bytes.size(); ++i) {
+            const unsigned char ch = (unsigned char)l.bytes[reverse ? l.bytes.size() - 1 - i : i];
+            std::vector<int> alts{ch};
+            if (l.icase && ch >= 'a' && ch <= 'z') alts.push_back(ch - 32);
+            std::vector<int> nxt;
+            for (int node : cur)
+                for (int b : alts) {
+                    auto it = trie[node].kid.find(b);
+                    int to;
+                    if (it == trie[node].kid.end()) { to = (int)trie.size(); trie[node].kid[b] = to; trie.emplace_back(); }
+                    else to = it->second;
+                    nxt.push_back(to);
+                }
+            cur.swap(nxt);
+            if (trie.size() > 200000) return false;
+        }
+        for (int node : cur) trie[node].end = true;
+    }
+    const unsigned nc = d.n_classes;
+    std::map<std::pair<unsigned, int>, char> seen;
+    // every way the automaton can stay alive from (state, trie node) must run through a complete literal
+    // before a match can be reported
+    std::vector<std::pair<unsigned, int>> stack;
+    for (int k = 0; k < 3; ++k) if (d.start_ctx[k] > DFA_MATCH) stack.push_back({d.start_ctx[k], 0});
+    for (int k = 0; k < 3; ++k) if (d.start_ctx[k] == DFA_MATCH) return false;
+    size_t budget = 2000000;
+    while (!stack.empty()) {
+        auto cur = stack.back();
+        stack.pop_back();
+        if (seen.count(cur)) continue;
+        seen[cur] = 1;
+        const unsigned st = cur.first;
+        const Node& nd = trie[cur.second];
+        if (nd.end) continue;
+        if (d.trans[st * nc + nc - 1] == DFA_MATCH) return false;             // match at end of line before a full literal
+        const unsigned tp = d.trans[st * nc + nc - 2];                           // the `$` position announcement consumes no text
+        if (tp == DFA_MATCH) return false;
+        if (tp > DFA_MATCH && tp != st) stack.push_back({tp, cur.second});
+        for (int b = 0; b < 256; ++b) {
+            const unsigned t = d.trans[st * nc + d.classmap[b]];
+            if (t == DFA_DEAD) continue;
+            if (t == DFA_MATCH) return false;                                    // a match completed before this byte
+            auto it = nd.kid.find(b);
+            if (it == nd.kid.end()) return false;                                // alive on a byte no literal continues with
+            stack.push_back({t, it->second});
+            if (--budget == 0) return false;
+        }
+    }
+    return true;
+}
+
+
+int choose_anchor(const Ast& root, const std::vector<Literal>& lits, Dfa& out, const DfaLimits& lim) {
+    if (lits.empty()) return 0;
+    for (int mode = 1; mode <= 2; ++mode) {
+        Dfa d;
+        if (!build_dfa_anchored(root, mode == 2, d, lim)) continue;
+        if (literals_cover(d, mode == 2, lits)) { out = std::move(d); return mode; }
+    }
+    return 0;
 }
 
 }  // namespace lpx

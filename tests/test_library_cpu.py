@@ -73,6 +73,47 @@ def test_dfa_tables_vs_oracle_random(lib, oracle):
     assert checked > 10000 and n_dfa > 1200
 
 
+def test_anchored_verification_equals_line_walk(lib, oracle):
+    """Regexes whose literals cover the start (or the end) of every match are decided in k_confirm at
+    the literal occurrences by an anchored automaton instead of a walk of the whole line. The host
+    mirrors of both walks must agree, and agree with the oracle. Literal length is lowered to 1-2 bytes
+    here so that the short random patterns exercise the cover test and both directions."""
+    rng = random.Random(777)
+    n_fwd = n_rev = checked = 0
+    for it in range(2500):
+        j, _p = Gen(rng, regular_only=True).regex()
+        try:
+            o = oracle.Regex(j)
+        except (oracle.OracleSyntaxError, oracle.OracleUnsupported):
+            continue
+        d = binding.DebugRegex(j, min_literal=1 + it % 3)
+        if not d.is_dfa or d.anchor == 0:
+            continue
+        n_fwd += d.anchor == 1
+        n_rev += d.anchor == 2
+        for _k in range(12):
+            t = gen_text(rng)
+            exp = o.find(t)
+            assert bool(d.match(t)) == exp, (j, t)
+            assert bool(d.match_anchored(t)) == exp, (j, t, d.anchor, d.literals())
+            checked += 1
+    assert n_fwd > 150 and n_rev > 40 and checked > 3000, (n_fwd, n_rev, checked)
+    # the shapes of the synthetic pattern set and of CAS:27-34
+    cases = [(r"\b\d{8,}ms\b", 2), (r"\b[45]\d\d \d+ms\b", 1), (r"retrying in \d+ms", 1), (r"\.\.\. \d+ more$", 0),
+             (r"\.\.\. \d+ more", 2), (r"(?i)timeout after \d+s$", 1), (r"caused by: \S+Error\b", 1), (r"^ab+cdef$", 0)]
+    texts = ["took 123456789ms", "x12345678ms", "12345678ms", "1234567ms!", "HTTP 503 12ms", "a503 12ms", "503 12msx", "retrying in 5ms",
+             "retrying in ms", "\t... 12 more", "... more", "Timeout After 30s", "timeout after 30s\r", "timeout after 30sx",
+             "caused by: java.lang.OutOfMemoryError", "caused by: Errors", "abbbcdef", "xabcdef", ""]
+    for pat, mode in cases:
+        d = binding.DebugRegex(pat)
+        assert d.anchor == mode, (pat, d.anchor)
+        o = oracle.Regex(pat)
+        for t in texts:
+            assert bool(d.match(t)) == o.find(t), (pat, t)
+            if mode:
+                assert bool(d.match_anchored(t)) == o.find(t), (pat, t)
+
+
 def test_backtracking_bytecode_vs_oracle_random(lib, oracle):
     """The interpreter of csrc/vm_exec.h (same code on host and device) against the oracle, on
     patterns with look-around, back-references, possessive/atomic constructs — and on regular ones
