@@ -73,6 +73,17 @@ __device__ __noinline__ uint32_t load4_tail(const uint8_t* __restrict__ text, ui
         if (pos + i < len) w |= (uint32_t)text[pos + i] << (i * 8);
     return w;
 }
+// 4 bytes at any position p (two aligned loads + funnel shift); bytes at or beyond len read as zero
+__device__ __forceinline__ uint32_t load4_any(const uint8_t* __restrict__ text, uint32_t p, uint64_t len) {
+    const uint32_t b = p & ~3u;
+    if ((uint64_t)b + 8 <= len) {
+        const uint32_t lo = __ldg(reinterpret_cast<const uint32_t*>(text + b)), hi = __ldg(reinterpret_cast<const uint32_t*>(text + b + 4));
+        return __funnelshift_r(lo, hi, (p & 3u) * 8);
+    }
+    uint32_t w = 0;
+    for (int i = 0; i < 4; ++i) if ((uint64_t)p + i < len) w |= (uint32_t)text[p + i] << (8 * i);
+    return w;
+}
 __device__ __forceinline__ uint32_t load4_safe(const uint8_t* __restrict__ text, uint64_t pos, uint64_t len) {
     if (pos + 4 <= len) return __ldg(reinterpret_cast<const uint32_t*>(text + pos));  // pos is 4-aligned here
     return load4_tail(text, pos, len);
@@ -139,22 +150,23 @@ struct FilterArgs {
     uint32_t n_tiles;
     uint32_t* tile_counts;
     const uint32_t* bitmap;
+    const uint8_t* byte_table;
     uint32_t* cand;                   // candidate byte positions
     uint32_t cand_cap;
     Counters* ctr;
     int use_filter;
 };
 __global__ void __launch_bounds__(SCAN_THREADS) k_filter_count(FilterArgs a) {
-    extern __shared__ uint32_t s_bitmap[];
+    extern __shared__ uint8_t s_tab[];      // 2^16 one-byte slots: 1 if some literal gram hashes here
     __shared__ uint32_t warp_sum[SCAN_THREADS / 32];
     __shared__ uint32_t s_cand[CAND_STAGE];
-    __shared__ uint32_t s_ncand, s_gbase;
+    __shared__ uint32_t s_ncand, s_gbase, s_nkeep;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) s_ncand = 0;
     if (a.use_filter) {
-        const uint4* src = reinterpret_cast<const uint4*>(a.bitmap);
-        uint4* dst = reinterpret_cast<uint4*>(s_bitmap);
-        for (uint32_t i = threadIdx.x; i < GRAM_WORDS / 4; i += SCAN_THREADS) dst[i] = __ldg(src + i);
+        const uint4* src = reinterpret_cast<const uint4*>(a.byte_table);
+        uint4* dst = reinterpret_cast<uint4*>(s_tab);
+        for (uint32_t i = threadIdx.x; i < 65536 / 16; i += SCAN_THREADS) dst[i] = __ldg(src + i);
     }
     __syncthreads();
     for (uint32_t tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
@@ -162,42 +174,36 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_filter_count(FilterArgs a) {
         uint32_t cnt = 0;
         const uint64_t pos0 = tile_base + (uint64_t)threadIdx.x * 16;
         uint4 vnext = pos0 < a.len ? load16(a.text, pos0, a.len) : make_uint4(0, 0, 0, 0);
+        // the 4 bytes after a warp's 512-byte span (needed by lane 31's last windows) are prefetched the same way
+        uint32_t tnext = (lane == 31 && a.use_filter && pos0 + 16 < a.len) ? load4_safe(a.text, pos0 + 16, a.len) : 0u;
 #pragma unroll 1
         for (int it = 0; it < SCAN_ITERS; ++it) {
             const uint64_t pos = tile_base + ((uint64_t)it * SCAN_THREADS + threadIdx.x) * 16;
             const uint4 v = vnext;
+            const uint32_t tail = tnext;
             {   // the next iteration's 16 bytes are requested before this iteration's work starts
                 const uint64_t pn = pos + (uint64_t)SCAN_THREADS * 16;
-                vnext = (it + 1 < SCAN_ITERS && pn < a.len) ? load16(a.text, pn, a.len) : make_uint4(0, 0, 0, 0);
+                const bool more = it + 1 < SCAN_ITERS && pn < a.len;
+                vnext = more ? load16(a.text, pn, a.len) : make_uint4(0, 0, 0, 0);
+                tnext = (more && lane == 31 && a.use_filter && pn + 16 < a.len) ? load4_safe(a.text, pn + 16, a.len) : 0u;
             }
             cnt += __popc(zero_byte_flags(v.x ^ 0x0A0A0A0Au)) + __popc(zero_byte_flags(v.y ^ 0x0A0A0A0Au)) +
                    __popc(zero_byte_flags(v.z ^ 0x0A0A0A0Au)) + __popc(zero_byte_flags(v.w ^ 0x0A0A0A0Au));
             if (!a.use_filter) continue;
             uint32_t nxt = __shfl_down_sync(0xffffffffu, v.x, 1);
-            if (lane == 31) nxt = (pos + 16 < a.len) ? load4_safe(a.text, pos + 16, a.len) : 0u;
+            if (lane == 31) nxt = tail;
             const uint32_t w[5] = {v.x | 0x20202020u, v.y | 0x20202020u, v.z | 0x20202020u, v.w | 0x20202020u, nxt | 0x20202020u};
             uint32_t hits = 0;
 #pragma unroll
             for (int i = 15; i >= 0; --i) {
                 const uint32_t win = (i & 3) ? __funnelshift_r(w[i >> 2], w[(i >> 2) + 1], (i & 3) * 8) : w[i >> 2];
-                const uint32_t h = win * GRAM_MUL;
-                const uint32_t word = s_bitmap[h >> (32 - GRAM_BITS + 5)];
-                hits = (hits << 1) | (__funnelshift_r(word, 0u, h >> (32 - GRAM_BITS)) & 1u);
+                hits = hits * 2u + s_tab[(win * GRAM_MUL) >> 16];       // 5 instructions per window: SHF, IMAD, SHF, LDS.U8, LEA
             }
             if (pos >= a.len) hits = 0;
-            if (hits) {
-                uint32_t hm = hits;
-                while (hm) {
-                    const int i = __ffs(hm) - 1;
-                    hm &= hm - 1;
-                    const uint32_t win = (i & 3) ? __funnelshift_r(w[i >> 2], w[(i >> 2) + 1], (i & 3) * 8) : w[i >> 2];
-                    const uint32_t h2 = win * GRAM_MUL2;
-                    const uint32_t word = s_bitmap[h2 >> (32 - GRAM_BITS + 5)];
-                    if (!((word >> ((h2 >> (32 - GRAM_BITS)) & 31u)) & 1u)) hits &= ~(1u << i);
-                }
-            }
-            // hits go to a per-block staging buffer in shared memory (one shared-memory atomic per
-            // warp and iteration); the block publishes them with ONE global atomic per tile
+            // first-stage hits (about 1-2 % of the positions) go to a per-block staging buffer in shared
+            // memory (one shared-memory atomic per warp and iteration); at the end of the tile the whole
+            // block checks them against the two-probe Bloom bitmap with every lane busy, and publishes the
+            // survivors with ONE global atomic
             const uint32_t n = __popc(hits);
             if (__ballot_sync(0xffffffffu, n != 0)) {
                 uint32_t hinc = n;
@@ -224,17 +230,45 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_filter_count(FilterArgs a) {
         for (int o = 16; o; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
         if (lane == 0) warp_sum[warp] = cnt;
         __syncthreads();
+        const uint32_t staged = min(s_ncand, CAND_STAGE);
         if (threadIdx.x == 0) {
             uint32_t sum = 0;
             for (int q = 0; q < SCAN_THREADS / 32; ++q) sum += warp_sum[q];
             a.tile_counts[tile] = sum;
-            const uint32_t staged = min(s_ncand, CAND_STAGE);
-            s_gbase = staged ? atomicAdd(&a.ctr->n_cand, staged) : 0u;
+            s_nkeep = 0;
+        }
+        // second stage: both Bloom probes for every staged position (CAND_STAGE / SCAN_THREADS entries per thread)
+        uint32_t kept[CAND_STAGE / SCAN_THREADS];
+        uint32_t keep_mask = 0;
+#pragma unroll
+        for (int k = 0; k < (int)(CAND_STAGE / SCAN_THREADS); ++k) {
+            const uint32_t q = threadIdx.x + k * SCAN_THREADS;
+            if (q < staged) {
+                const uint32_t p = s_cand[q];
+                const uint32_t win = load4_any(a.text, p, a.len) | 0x20202020u;
+                const uint32_t h1 = (win * GRAM_MUL) >> (32 - GRAM_BITS), h2 = (win * GRAM_MUL2) >> (32 - GRAM_BITS);
+                kept[k] = p;
+                if ((__ldg(a.bitmap + (h1 >> 5)) >> (h1 & 31u)) & (__ldg(a.bitmap + (h2 >> 5)) >> (h2 & 31u)) & 1u) keep_mask |= 1u << k;
+            }
+        }
+        __syncthreads();        // every staged entry has been read: the buffer is compacted in place
+#pragma unroll
+        for (int k = 0; k < (int)(CAND_STAGE / SCAN_THREADS); ++k) {
+            const bool keep = (keep_mask >> k) & 1u;
+            const unsigned votes = __ballot_sync(0xffffffffu, keep);
+            if (votes) {
+                uint32_t base = 0;
+                if (lane == 0) base = atomicAdd(&s_nkeep, (uint32_t)__popc(votes));
+                base = __shfl_sync(0xffffffffu, base, 0);
+                if (keep) s_cand[base + __popc(votes & ((1u << lane) - 1u))] = kept[k];
+            }
         }
         __syncthreads();
+        if (threadIdx.x == 0) s_gbase = s_nkeep ? atomicAdd(&a.ctr->n_cand, s_nkeep) : 0u;
+        __syncthreads();
         {
-            const uint32_t staged = min(s_ncand, CAND_STAGE), gbase = s_gbase;
-            for (uint32_t q = threadIdx.x; q < staged; q += SCAN_THREADS) {
+            const uint32_t nk = s_nkeep, gbase = s_gbase;
+            for (uint32_t q = threadIdx.x; q < nk; q += SCAN_THREADS) {
                 if (gbase + q < a.cand_cap) a.cand[gbase + q] = s_cand[q];
                 else atomicOr(&a.ctr->overflow, 1u);
             }
@@ -1353,7 +1387,8 @@ struct lp_ctx {
     std::vector<uint32_t> group_words;
     const uint8_t* d_rx_record = nullptr;
     uint32_t n_group_record_rx = 0;
-    DevBuf f_bitmap, f_key, f_lits;   // prefilter tables (re-uploaded by calibration)
+    DevBuf f_bitmap, f_key, f_lits, f_bytes;   // prefilter tables (re-uploaded by calibration)
+    const uint8_t* d_byte_table = nullptr;
     std::vector<uint32_t> lit_off8;   // literal -> offset in the 8-byte aligned device copy of the literal bytes
     bool calibrated = false;
     int recalibrations = 0;
@@ -1405,6 +1440,11 @@ void upload_filter(lp_ctx* c) {
     const lpx::Plan& pl = c->plan;
     DevPlan& d = c->dp;
     d.bitmap = upload_into(c->f_bitmap, pl.bitmap);
+    {   // first-stage table of k_filter_count: one byte per 16-bit hash of a folded gram
+        std::vector<uint8_t> bt(65536, 0);
+        for (uint32_t key : pl.table_key) if (key) bt[(key * GRAM_MUL) >> 16] = 1;
+        c->d_byte_table = upload_into(c->f_bytes, bt);
+    }
     d.table_bits = pl.table_bits;
     // literal descriptors grouped by gram slot (a literal has exactly one gram)
     auto is_word = [](unsigned char b) { return (b >= '0' && b <= '9') || (b >= 'A' && b <= 'Z') || b == '_' || (b >= 'a' && b <= 'z'); };
@@ -1663,9 +1703,9 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     if (!c->plan.ctx_any_in_groups) CK(cudaMemsetAsync(c->ctx_flags.p, 0, (line_cap / 4 + 2) * 4, st));   // else k_dfa_scan writes every byte
 
     CK(cudaEventRecord(c->ev[0], st));
-    const size_t smem = use_filter ? GRAM_WORDS * 4 : 0;
+    const size_t smem = use_filter ? 65536 : 0;
     FilterArgs fa{};
-    fa.text = d_text; fa.len = len; fa.n_tiles = n_tiles; fa.tile_counts = c->tile_counts.as<uint32_t>(); fa.bitmap = c->dp.bitmap;
+    fa.text = d_text; fa.len = len; fa.n_tiles = n_tiles; fa.tile_counts = c->tile_counts.as<uint32_t>(); fa.bitmap = c->dp.bitmap; fa.byte_table = c->d_byte_table;
     fa.cand = c->cand.as<uint32_t>(); fa.cand_cap = (uint32_t)std::min<size_t>(c->est_cand, 0xFFFFFFFFu); fa.ctr = ctr;
     fa.use_filter = use_filter ? 1 : 0;
     CK(cudaEventRecord(c->ev[1], st));
@@ -2051,7 +2091,7 @@ void lp_destroy(lp_ctx* c) {
                      &c->ev_log, &c->slot_key, &c->slot_key_alt, &c->ev_idx, &c->ev_idx_alt, &c->rank_in_slot, &c->freq_delta, &c->prior,
                      &c->out_line, &c->out_pat, &c->out_score, &c->out_factors, &c->sort_key, &c->sort_key_alt, &c->order, &c->order_alt,
                      &c->log_sorted, &c->log_sorted_alt, &c->rank, &c->log_event_begin, &c->n_unique, &c->d_lut,
-                     &c->f_bitmap, &c->f_key, &c->f_lits, &c->items, &c->seq_tab_off, &c->seq_tab, &c->seq_T, &c->prior_eff, &c->any_flag};
+                     &c->f_bitmap, &c->f_key, &c->f_lits, &c->f_bytes, &c->items, &c->seq_tab_off, &c->seq_tab, &c->seq_T, &c->prior_eff, &c->any_flag};
     for (DevBuf* b : all) b->release();
     c->stage.release();
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
