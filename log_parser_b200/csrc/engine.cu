@@ -1290,6 +1290,75 @@ __global__ void k_prior_prefix(const unsigned long long* __restrict__ all, uint3
     }
 }
 __global__ void k_publish_overflow(const Counters* ctr, unsigned long long* __restrict__ dst) { *dst = ctr->overflow; }
+// ------------------------------------------------------------------ sorting a few ten thousand keys
+// The event list and the score ranking hold ~10^4 keys: a device-wide radix sort spends 8-10 us per
+// digit pass on them (13 passes for these two sorts), all of it launch and look-back latency. Here
+// tiles of 2048 keys are sorted in shared memory (cub::BlockRadixSort, stable) by one kernel, and a
+// second kernel finds every key's final position by counting, in each other tile, the keys that
+// precede it (binary searches; earlier tiles win ties, which keeps the sort stable).
+constexpr int SS_THREADS = 256, SS_ITEMS = 8, SS_TILE = SS_THREADS * SS_ITEMS;
+constexpr uint32_t SS_MAX_TILES = 64;
+constexpr int SS_GROUP = 16;              // tiles searched in lockstep by k_tile_rank (independent probes in flight)      // beyond 131072 keys the counting pass costs more than radix passes
+__global__ void __launch_bounds__(SS_THREADS) k_tile_sort(const unsigned long long* __restrict__ in, uint32_t n, int end_bit,
+                                                          unsigned long long* __restrict__ tile_keys, uint32_t* __restrict__ tile_idx) {
+    using Sorter = cub::BlockRadixSort<unsigned long long, SS_THREADS, SS_ITEMS, uint32_t, 6>;
+    __shared__ typename Sorter::TempStorage tmp;
+    unsigned long long k[SS_ITEMS];
+    uint32_t v[SS_ITEMS];
+    const uint32_t base = blockIdx.x * SS_TILE + threadIdx.x * SS_ITEMS;
+#pragma unroll
+    for (int i = 0; i < SS_ITEMS; ++i) { k[i] = base + i < n ? in[base + i] : ~0ull; v[i] = base + i; }
+    Sorter(tmp).Sort(k, v, 0, end_bit);
+#pragma unroll
+    for (int i = 0; i < SS_ITEMS; ++i) { tile_keys[base + i] = k[i]; tile_idx[base + i] = v[i]; }
+}
+// out_sorted (optional): keys scattered to their final positions; out_rank (optional): final position of
+// original element i, written for i < *n_valid.
+__global__ void __launch_bounds__(256) k_tile_rank(const unsigned long long* __restrict__ tile_keys, const uint32_t* __restrict__ tile_idx,
+                                                   uint32_t n_tiles, uint32_t n, unsigned long long* __restrict__ out_sorted,
+                                                   uint32_t* __restrict__ out_rank, const unsigned int* __restrict__ n_valid) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n_tiles * SS_TILE) return;
+    const uint32_t t0 = j / SS_TILE;
+    const unsigned long long key = tile_keys[j];
+    uint32_t r = j - t0 * SS_TILE;
+    // branch-free binary searches over the 2048 keys of each other tile, SS_GROUP tiles in lockstep so
+    // that their (dependent) probes overlap: keys <= key in earlier tiles, keys < key in later ones
+    for (uint32_t tb = 0; tb < n_tiles; tb += SS_GROUP) {
+        uint32_t pos[SS_GROUP];
+        const unsigned long long* base[SS_GROUP];
+        // earlier tiles count keys <= key, i.e. keys < key + 1 (key + 1 cannot overflow there: a key equal to
+        // the all-ones padding in an earlier tile is handled by the saturation below)
+        unsigned long long bound[SS_GROUP];
+#pragma unroll
+        for (int q = 0; q < SS_GROUP; ++q) {
+            const uint32_t t = min(tb + q, n_tiles - 1);
+            pos[q] = 0;
+            base[q] = tile_keys + (size_t)t * SS_TILE;
+            bound[q] = (t < t0 && key != ~0ull) ? key + 1 : key;      // count keys < bound
+        }
+#pragma unroll 1
+        for (uint32_t step = SS_TILE / 2; step > 0; step >>= 1) {
+            unsigned long long v[SS_GROUP];
+#pragma unroll
+            for (int q = 0; q < SS_GROUP; ++q) v[q] = base[q][pos[q] + step - 1];
+#pragma unroll
+            for (int q = 0; q < SS_GROUP; ++q) pos[q] += v[q] < bound[q] ? step : 0u;
+        }
+        unsigned long long v[SS_GROUP];
+#pragma unroll
+        for (int q = 0; q < SS_GROUP; ++q) v[q] = base[q][pos[q]];
+#pragma unroll
+        for (int q = 0; q < SS_GROUP; ++q) {
+            const uint32_t t = tb + q;
+            uint32_t cnt = pos[q] + (v[q] < bound[q] ? 1u : 0u);
+            if (t < t0 && key == ~0ull) cnt = SS_TILE;                  // every key of an earlier tile is <= the padding key
+            if (t < n_tiles && t != t0) r += cnt;
+        }
+    }
+    if (out_sorted && r < n) out_sorted[r] = key;
+    if (out_rank) { const uint32_t i = tile_idx[j]; if (i < *n_valid) out_rank[i] = r; }
+}
 __global__ void k_count_per_pattern(const unsigned long long* __restrict__ keys, const Counters* ctr, DevPlan P, unsigned long long* __restrict__ counts,
                                     uint32_t core_lo, uint32_t halo_after) {
     const uint32_t n = ctr->n_unique;
@@ -1398,7 +1467,7 @@ struct lp_ctx {
 
     // scratch (grow-only)
     DevBuf text, log_off, tile_counts, counters, line_start, line_end, first_line, n_lines;
-    DevBuf items;
+    DevBuf items, ss_keys, ss_idx;
     size_t est_items = 0;
     int occ_confirm = 0, occ_resolve = 0;
     DevBuf cand, tasks, vm_tasks, vm_stack, recs, recs_alt, cub_tmp, rx_begin, ctx_flags;
@@ -1593,6 +1662,19 @@ void sort_pairs(lp_ctx* c, K* kin, K* kout, V* vin, V* vout, uint32_t n, int end
     c->cub_tmp.ensure(tmp);
     CK(cub::DeviceRadixSort::SortPairs(c->cub_tmp.p, tmp, kin, kout, vin, vout, (int)n, 0, end_bit, c->stream));
     c->launches += 3;
+}
+// n <= SS_MAX_TILES * SS_TILE keys: tile sort + counting rank (see k_tile_sort). Exactly one of out_sorted / out_rank is used.
+bool small_sort(lp_ctx* c, const unsigned long long* in, uint32_t n, int end_bit, unsigned long long* out_sorted, uint32_t* out_rank,
+                const unsigned int* n_valid) {
+    const uint32_t n_tiles = (n + SS_TILE - 1) / SS_TILE;
+    if (n == 0 || n_tiles > SS_MAX_TILES) return false;
+    c->ss_keys.ensure((size_t)n_tiles * SS_TILE * 8);
+    c->ss_idx.ensure((size_t)n_tiles * SS_TILE * 4);
+    k_tile_sort<<<n_tiles, SS_THREADS, 0, c->stream>>>(in, n, end_bit, c->ss_keys.as<unsigned long long>(), c->ss_idx.as<uint32_t>());
+    k_tile_rank<<<blocks_for(n_tiles * SS_TILE, 256), 256, 0, c->stream>>>(c->ss_keys.as<unsigned long long>(), c->ss_idx.as<uint32_t>(), n_tiles, n,
+                                                                          out_sorted, out_rank, n_valid);
+    c->launches += 2;
+    return true;
 }
 int bits_for(uint64_t v) { int b = 1; while (b < 64 && (v >> b)) ++b; return b; }
 
@@ -1809,8 +1891,10 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     // ---- events in discovery order (global line, pattern index)
     k_emit_events<<<c->n_sm * 4, 256, 0, st>>>(c->recs.as<unsigned long long>(), c->dp, c->ev_key_alt.as<unsigned long long>(), (uint32_t)ev_cap, ctr,
                                               rg ? rg->halo_before : 0u, rg ? rg->halo_after : 0u);
-    sort_keys<unsigned long long>(c, c->ev_key_alt.as<unsigned long long>(), c->ev_key.as<unsigned long long>(), (uint32_t)ev_cap,
-                                  std::min<int>(64, (int)c->dp.gb + (int)c->dp.pb + 1));
+    if (!small_sort(c, c->ev_key_alt.as<unsigned long long>(), (uint32_t)ev_cap, std::min<int>(64, (int)c->dp.gb + (int)c->dp.pb + 1),
+                    c->ev_key.as<unsigned long long>(), nullptr, nullptr))
+        sort_keys<unsigned long long>(c, c->ev_key_alt.as<unsigned long long>(), c->ev_key.as<unsigned long long>(), (uint32_t)ev_cap,
+                                      std::min<int>(64, (int)c->dp.gb + (int)c->dp.pb + 1));
     c->launches += 1;
 
     c->pend.valid = true;
@@ -1891,7 +1975,10 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
     k_log_event_begin<<<blocks_for(n_logs + 1, 128), 128, 0, st>>>(c->ev_key.as<unsigned long long>(), ctr, c->first_line.as<uint32_t>(),
                                                                    n_logs, c->dp.pb, c->log_event_begin.as<unsigned long long>());
     c->launches += 3;
-    if (!(options & LP_OPT_NO_RANK)) {
+    if (!(options & LP_OPT_NO_RANK) && n_logs == 1 &&
+        small_sort(c, c->sort_key.as<unsigned long long>(), mc, 64, nullptr, c->rank.as<uint32_t>(), &ctr->n_events)) {
+        // one log, few events: ranks by tile sort + counting (descending score, ties keep discovery order)
+    } else if (!(options & LP_OPT_NO_RANK)) {
         // stable sort by descending score (ties keep discovery order), then stably by log
         sort_pairs<unsigned long long, uint32_t>(c, c->sort_key.as<unsigned long long>(), c->sort_key_alt.as<unsigned long long>(),
                                                  c->ev_idx.as<uint32_t>(), c->order.as<uint32_t>(), mc, 64);
@@ -2091,7 +2178,7 @@ void lp_destroy(lp_ctx* c) {
                      &c->ev_log, &c->slot_key, &c->slot_key_alt, &c->ev_idx, &c->ev_idx_alt, &c->rank_in_slot, &c->freq_delta, &c->prior,
                      &c->out_line, &c->out_pat, &c->out_score, &c->out_factors, &c->sort_key, &c->sort_key_alt, &c->order, &c->order_alt,
                      &c->log_sorted, &c->log_sorted_alt, &c->rank, &c->log_event_begin, &c->n_unique, &c->d_lut,
-                     &c->f_bitmap, &c->f_key, &c->f_lits, &c->f_bytes, &c->items, &c->seq_tab_off, &c->seq_tab, &c->seq_T, &c->prior_eff, &c->any_flag};
+                     &c->f_bitmap, &c->f_key, &c->f_lits, &c->f_bytes, &c->items, &c->ss_keys, &c->ss_idx, &c->seq_tab_off, &c->seq_tab, &c->seq_T, &c->prior_eff, &c->any_flag};
     for (DevBuf* b : all) b->release();
     c->stage.release();
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
