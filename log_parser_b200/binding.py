@@ -210,6 +210,34 @@ def _arr(ptr, n, dtype):
     return np.ctypeslib.as_array(ptr, (n,)).astype(dtype, copy=True)
 
 
+class _ResultOwner:
+    """Keeps an lp_result alive while numpy views of its columns exist; lp_result_free when the last one goes."""
+
+    def __init__(self, L, handle):
+        self.L, self.h = L, handle
+
+    def __del__(self):
+        try:
+            if self.h:
+                self.L.lp_result_free(self.h)
+                self.h = None
+        except Exception:
+            pass
+
+
+_CT = {np.dtype(np.uint32): C.c_uint32, np.dtype(np.uint64): C.c_uint64, np.dtype(np.float64): C.c_double}
+
+
+def _view(ptr, n, dtype, owner):
+    """Zero-copy column view (the memory is the page-locked buffer the device wrote into)."""
+    n = int(n)
+    if n == 0 or not ptr:
+        return np.zeros(0, dtype)
+    buf = (_CT[np.dtype(dtype)] * n).from_address(C.cast(ptr, C.c_void_p).value)
+    buf._owner = owner          # the buffer object is the array's base: it pins the result
+    return np.frombuffer(buf, dtype=dtype)
+
+
 class LogParser:
     """One lp_ctx: scoring.* configuration + loaded pattern set bound to one CUDA device."""
 
@@ -263,16 +291,16 @@ class LogParser:
         if rc != LP_OK:
             _raise(rc)
         m, nl = v.n_events, v.n_logs
+        owner = _ResultOwner(self.L, out)       # columns are views into the result; it is freed with the last of them
         res = Result(
             n_logs=nl, log_n_lines=_arr(v.log_n_lines, nl, np.uint64), log_event_begin=_arr(v.log_event_begin, nl + 1, np.uint64),
-            line=_arr(v.line, m, np.uint32), pattern=_arr(v.pattern, m, np.uint32), score=_arr(v.score, m, np.float64),
-            rank=_arr(v.rank, m, np.uint32), freq_delta=_arr(v.freq_delta, v.n_patterns, np.uint64))
+            line=_view(v.line, m, np.uint32, owner), pattern=_view(v.pattern, m, np.uint32, owner), score=_view(v.score, m, np.float64, owner),
+            rank=_view(v.rank, m, np.uint32, owner), freq_delta=_view(v.freq_delta, v.n_patterns, np.uint64, owner))
         if v.factors:
-            res.factors = _arr(v.factors, m * 7, np.float64).reshape(m, 7)
+            res.factors = _view(v.factors, m * 7, np.float64, owner).reshape(m, 7)
         if v.line_start:
             res.line_start = _arr(v.line_start, v.total_lines + 1, np.uint32)
             res.line_end = _arr(v.line_end, v.total_lines, np.uint32)
-        self.L.lp_result_free(out)
         return res
 
     # ---- the hot path

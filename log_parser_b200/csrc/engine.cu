@@ -1434,12 +1434,43 @@ const T* upload(std::vector<DevBuf>& keep, const std::vector<T>& v) {
 
 }  // namespace
 
+// Page-locked buffers travel between a context and the results it hands out: the device writes a
+// call's outputs into one, the lp_result then owns it (no copy) and gives it back when it is freed.
+struct StagePool {
+    std::mutex mu;
+    std::vector<PinnedBuf> free_list;
+    bool closed = false;
+    PinnedBuf acquire() {
+        std::lock_guard<std::mutex> lk(mu);
+        if (free_list.empty()) return PinnedBuf();
+        PinnedBuf b = free_list.back();
+        free_list.pop_back();
+        return b;
+    }
+    void give_back(PinnedBuf b) {
+        std::lock_guard<std::mutex> lk(mu);
+        if (closed || free_list.size() >= 4) b.release(); else free_list.push_back(b);
+    }
+    void close() {
+        std::lock_guard<std::mutex> lk(mu);
+        closed = true;
+        for (auto& b : free_list) b.release();
+        free_list.clear();
+    }
+};
+
 struct lp_result {
-    std::vector<uint64_t> log_n_lines, log_event_begin, freq_delta;
-    std::vector<uint32_t> line, pattern, rank, line_start, line_end;
-    std::vector<double> score, factors;
+    PinnedBuf hold;                           // event columns live here (pinned, written by the device)
+    std::shared_ptr<StagePool> pool;
+    const uint32_t *line = nullptr, *pattern = nullptr, *rank = nullptr;
+    const double *score = nullptr, *factors = nullptr;
+    const uint64_t* freq_delta = nullptr;
+    uint64_t n_patterns = 0;
+    std::vector<uint64_t> log_n_lines, log_event_begin;
+    std::vector<uint32_t> line_start, line_end, zero_rank;
     uint64_t n_logs = 0, n_events = 0, total_lines = 0;
     bool has_factors = false, has_offsets = false;
+    ~lp_result() { if (hold.p) { if (pool) pool->give_back(hold); else hold.release(); } }
 };
 
 struct lp_ctx {
@@ -1475,6 +1506,7 @@ struct lp_ctx {
     DevBuf out_line, out_pat, out_score, out_factors, sort_key, sort_key_alt, order, order_alt, log_sorted, log_sorted_alt;
     DevBuf rank, log_event_begin, n_unique;
     PinnedBuf stage;
+    std::shared_ptr<StagePool> pool = std::make_shared<StagePool>();
     size_t est_lines = 0, est_cand = 0, est_tasks = 0, est_vm_tasks = 0, est_recs = 0, est_events = 0;
     int retries = 0;
 
@@ -2006,6 +2038,7 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
     const size_t o_ctr = take(sizeof(Counters)), o_line = take((size_t)mc * 4), o_pat = take((size_t)mc * 4), o_score = take((size_t)mc * 8),
                  o_rank = take(want_rank ? (size_t)mc * 4 : 0), o_fac = take(want_factors ? (size_t)mc * 56 : 0),
                  o_delta = take((size_t)np * 8), o_nl = take((size_t)n_logs * 4), o_leb = take((size_t)(n_logs + 1) * 8);
+    if (!c->stage.p) c->stage = c->pool->acquire();
     c->stage.ensure(off);
     uint8_t* hs = c->stage.p;
     CK(cudaMemcpyAsync(hs + o_ctr, ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
@@ -2029,13 +2062,15 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
     const uint32_t G = (uint32_t)(h.total_nl + n_logs);
     res->n_events = m;
     res->total_lines = G;
-    res->line.assign(reinterpret_cast<uint32_t*>(hs + o_line), reinterpret_cast<uint32_t*>(hs + o_line) + m);
-    res->pattern.assign(reinterpret_cast<uint32_t*>(hs + o_pat), reinterpret_cast<uint32_t*>(hs + o_pat) + m);
-    res->score.assign(reinterpret_cast<double*>(hs + o_score), reinterpret_cast<double*>(hs + o_score) + m);
-    if (want_rank) res->rank.assign(reinterpret_cast<uint32_t*>(hs + o_rank), reinterpret_cast<uint32_t*>(hs + o_rank) + m);
-    else res->rank.assign(m, 0);
-    if (want_factors) { res->has_factors = true; res->factors.assign(reinterpret_cast<double*>(hs + o_fac), reinterpret_cast<double*>(hs + o_fac) + (size_t)m * 7); }
-    res->freq_delta.assign(reinterpret_cast<uint64_t*>(hs + o_delta), reinterpret_cast<uint64_t*>(hs + o_delta) + np);
+    // the result takes the staging buffer over: its columns are read in place
+    res->line = reinterpret_cast<uint32_t*>(hs + o_line);
+    res->pattern = reinterpret_cast<uint32_t*>(hs + o_pat);
+    res->score = reinterpret_cast<double*>(hs + o_score);
+    if (want_rank) res->rank = reinterpret_cast<uint32_t*>(hs + o_rank);
+    else { res->zero_rank.assign(m, 0); res->rank = res->zero_rank.data(); }
+    if (want_factors) { res->has_factors = true; res->factors = reinterpret_cast<double*>(hs + o_fac); }
+    res->freq_delta = reinterpret_cast<uint64_t*>(hs + o_delta);
+    res->n_patterns = np;
     res->log_n_lines.resize(n_logs);
     for (uint32_t k = 0; k < n_logs; ++k) res->log_n_lines[k] = reinterpret_cast<uint32_t*>(hs + o_nl)[k];
     if (rgl) res->log_n_lines[0] = (uint64_t)rgl->n_global;      // a shard reports the whole log's line count
@@ -2064,6 +2099,9 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
     c->tm.dfa_scan_bytes = c->d_group_blob.empty() ? 0 : c->pend.len + 8ull * ((uint64_t)G + 1) + (uint64_t)G;
     if (!c->plan.lit_off.empty() && (uint64_t)h.n_cand * 2 > (uint64_t)G + 1024 && c->recalibrations < 2) { c->calibrated = false; ++c->recalibrations; }
     c->pend.valid = false;
+    res->hold = c->stage;          // ownership moves to the result; the next call draws a buffer from the pool
+    res->pool = c->pool;
+    c->stage = PinnedBuf();
     return res.release();
 }
 
@@ -2181,6 +2219,7 @@ void lp_destroy(lp_ctx* c) {
                      &c->f_bitmap, &c->f_key, &c->f_lits, &c->f_bytes, &c->items, &c->ss_keys, &c->ss_idx, &c->seq_tab_off, &c->seq_tab, &c->seq_T, &c->prior_eff, &c->any_flag};
     for (DevBuf* b : all) b->release();
     c->stage.release();
+    c->pool->close();
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -2494,13 +2533,13 @@ int lp_result_get(const lp_result* r, lp_result_view* v) {
     v->n_events = r->n_events;
     v->log_n_lines = r->log_n_lines.data();
     v->log_event_begin = r->log_event_begin.data();
-    v->line = r->line.data();
-    v->pattern = r->pattern.data();
-    v->score = r->score.data();
-    v->rank = r->rank.data();
-    v->factors = r->has_factors ? r->factors.data() : nullptr;
-    v->freq_delta = r->freq_delta.data();
-    v->n_patterns = r->freq_delta.size();
+    v->line = r->line;
+    v->pattern = r->pattern;
+    v->score = r->score;
+    v->rank = r->rank;
+    v->factors = r->has_factors ? r->factors : nullptr;
+    v->freq_delta = r->freq_delta;
+    v->n_patterns = r->n_patterns;
     v->line_start = r->has_offsets ? r->line_start.data() : nullptr;
     v->line_end = r->has_offsets ? r->line_end.data() : nullptr;
     v->total_lines = r->total_lines;
