@@ -148,6 +148,7 @@ struct FilterArgs {
     const uint8_t* text;
     uint64_t len;
     uint32_t n_tiles;
+    uint32_t tile_begin, tile_end;    // this launch's tiles (a log arriving from the host is scanned chunk by chunk)
     uint32_t* tile_counts;
     const uint32_t* bitmap;
     const uint8_t* byte_table;
@@ -169,7 +170,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_filter_count(FilterArgs a) {
         for (uint32_t i = threadIdx.x; i < 65536 / 16; i += SCAN_THREADS) dst[i] = __ldg(src + i);
     }
     __syncthreads();
-    for (uint32_t tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+    for (uint32_t tile = a.tile_begin + blockIdx.x; tile < a.tile_end; tile += gridDim.x) {
         const uint64_t tile_base = (uint64_t)tile * TILE_BYTES;
         uint32_t cnt = 0;
         const uint64_t pos0 = tile_base + (uint64_t)threadIdx.x * 16;
@@ -1505,6 +1506,9 @@ struct lp_ctx {
     DevBuf ev_key, ev_key_alt, ev_log, slot_key, slot_key_alt, ev_idx, ev_idx_alt, rank_in_slot, freq_delta, prior;
     DevBuf out_line, out_pat, out_score, out_factors, sort_key, sort_key_alt, order, order_alt, log_sorted, log_sorted_alt;
     DevBuf rank, log_event_begin, n_unique;
+    const uint8_t* host_src = nullptr;      // set by lp_analyze*: the log still has to be copied in (run_scan does it piecewise)
+    cudaStream_t copy_stream = nullptr;
+    std::vector<cudaEvent_t> chunk_ev;
     PinnedBuf stage;
     std::shared_ptr<StagePool> pool = std::make_shared<StagePool>();
     size_t est_lines = 0, est_cand = 0, est_tasks = 0, est_vm_tasks = 0, est_recs = 0, est_events = 0;
@@ -1823,7 +1827,33 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     fa.cand = c->cand.as<uint32_t>(); fa.cand_cap = (uint32_t)std::min<size_t>(c->est_cand, 0xFFFFFFFFu); fa.ctr = ctr;
     fa.use_filter = use_filter ? 1 : 0;
     CK(cudaEventRecord(c->ev[1], st));
-    k_filter_count<<<std::min<uint32_t>(n_tiles, (uint32_t)c->n_sm * 3), SCAN_THREADS, smem, st>>>(fa);
+    if (c->host_src) {
+        // The log is still in (page-locked) host memory: it is copied in up to 8 pieces on a second
+        // stream and each piece is scanned as soon as it has landed, so the copy hides the scan. A piece
+        // carries 16 bytes of its successor for the windows that straddle the cut.
+        const uint8_t* host = c->host_src;
+        c->host_src = nullptr;                  // a re-run of this call finds the text on the device
+        uint8_t* dst = const_cast<uint8_t*>(d_text);
+        const uint64_t piece = std::max<uint64_t>(((len / 8 + TILE_BYTES) / TILE_BYTES) * TILE_BYTES, 256 * (uint64_t)TILE_BYTES);
+        CK(cudaEventRecord(c->ev[5], c->copy_stream));
+        uint32_t k = 0;
+        for (uint64_t off = 0; off < len || k == 0; off += piece, ++k) {
+            const uint64_t n = std::min<uint64_t>(piece, len - off), n_copy = std::min<uint64_t>(n + 16, len - off);
+            if (n_copy) CK(cudaMemcpyAsync(dst + off, host + off, n_copy, cudaMemcpyHostToDevice, c->copy_stream));
+            if (k >= c->chunk_ev.size()) { cudaEvent_t e; CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); c->chunk_ev.push_back(e); }
+            CK(cudaEventRecord(c->chunk_ev[k], c->copy_stream));
+            CK(cudaStreamWaitEvent(st, c->chunk_ev[k], 0));
+            fa.tile_begin = (uint32_t)(off / TILE_BYTES);
+            fa.tile_end = off + n >= len ? n_tiles : (uint32_t)((off + n) / TILE_BYTES);
+            k_filter_count<<<std::min<uint32_t>(fa.tile_end - fa.tile_begin, (uint32_t)c->n_sm * 3), SCAN_THREADS, smem, st>>>(fa);
+            if (len == 0) break;
+        }
+        CK(cudaEventRecord(c->ev[8], c->copy_stream));
+        c->launches += k - 1;
+    } else {
+        fa.tile_begin = 0; fa.tile_end = n_tiles;
+        k_filter_count<<<std::min<uint32_t>(n_tiles, (uint32_t)c->n_sm * 3), SCAN_THREADS, smem, st>>>(fa);
+    }
     CK(cudaEventRecord(c->ev[2], st));
     k_scan_tiles<<<1, 1024, 0, st>>>(c->tile_counts.as<uint32_t>(), n_tiles, n_logs, ctr);
     ScanArgs sa{};
@@ -2115,6 +2145,9 @@ lp_result* run_all(lp_ctx* c, Stage&& stage_text, uint64_t len, const uint64_t* 
             return run_score(c, prior);
         } catch (const Retry&) {
             continue;
+        } catch (...) {
+            c->host_src = nullptr;      // never leave a caller's host pointer behind
+            throw;
         }
     }
 }
@@ -2151,6 +2184,11 @@ int guarded(lp_ctx* c, F&& f) {
 
 const uint8_t* stage_host_log(lp_ctx* c, const uint8_t* host, uint64_t len) {
     c->text.ensure(len + 64);
+    c->host_src = nullptr;
+    if (c->calibrated && !c->plan.lit_off.empty() && len >= (8u << 20)) {
+        c->host_src = host;             // run_scan copies it piecewise, overlapped with the prefilter scan
+        return c->text.as<uint8_t>();
+    }
     CK(cudaEventRecord(c->ev[5], c->stream));
     if (len) CK(cudaMemcpyAsync(c->text.p, host, len, cudaMemcpyHostToDevice, c->stream));
     CK(cudaEventRecord(c->ev[8], c->stream));
@@ -2183,6 +2221,7 @@ lp_ctx* lp_create(const lp_scoring_cfg* cfg, int device) {
         ctx->cfg = *cfg;
         ctx->cfg.decay_lut = nullptr;
         CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+        CK(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
         for (auto& e : ctx->ev) CK(cudaEventCreate(&e));
         cudaDeviceProp prop;
         CK(cudaGetDeviceProperties(&prop, device));
@@ -2221,6 +2260,8 @@ void lp_destroy(lp_ctx* c) {
     c->stage.release();
     c->pool->close();
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
+    for (auto& e : c->chunk_ev) cudaEventDestroy(e);
+    if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
 }

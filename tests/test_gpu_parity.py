@@ -470,3 +470,26 @@ def test_device_side_exchange_equals_one_batch(parser):
     finally:
         for lp in lps:
             lp.close()
+
+
+def test_piecewise_host_copy_equals_device_resident(parser):
+    """lp_analyze on a log of more than 8 MB copies it in pieces on a second stream and scans each piece
+    as it lands (after the prefilter has been calibrated by a first call): same result as the
+    device-resident path, including candidates that straddle a cut."""
+    import torch
+
+    wl = synth.make_patterns(60, 909, noliteral=1)
+    log = synth.make_log(wl, 90_000, 910, hit_rate=0.03)
+    assert len(log) > (8 << 20)
+    parser.load_patterns(wl.patterns)
+    first = parser.analyze(log)                       # calibrates; plain copy
+    second = parser.analyze(log)                      # piecewise copy overlapped with the scan
+    dev = torch.from_numpy(np.frombuffer(log, dtype=np.uint8).copy()).cuda()
+    resident = parser.analyze_device(dev.data_ptr(), len(log))
+    assert resident.n_events > 1000
+    for r in (first, second):
+        np.testing.assert_array_equal(r.line, resident.line)
+        np.testing.assert_array_equal(r.pattern, resident.pattern)
+        np.testing.assert_array_equal(r.score, resident.score)
+        np.testing.assert_array_equal(r.rank, resident.rank)
+    assert parser.timings()["kernel_launches"] > 0
