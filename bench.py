@@ -338,6 +338,11 @@ def main():
 
     if rank == 0:
         peak, peak_src = _peaks()
+        traffic, traffic_src = None, None          # DRAM bytes of one k_filter_count launch from the committed ncu --set full capture (C2 only)
+        tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_v6_traffic.json")
+        if os.path.exists(tpath) and args.lines == 1_000_000 and args.patterns == 500 and not by_lines:
+            tj = json.load(open(tpath))
+            traffic, traffic_src = int(tj["dram_bytes_read"]) + int(tj["dram_bytes_write"]), tj["source"]
         scan_s = sum(scan_ms) / 1e3 / len(scan_ms)
         achieved = (sum(scan_bytes) / len(scan_bytes)) / scan_s / 1e9
         line = {
@@ -350,8 +355,8 @@ def main():
             "phase_ms": {"scan": sum(scan_ms) / len(scan_ms), "verify": sum(ver_ms) / len(ver_ms), "score": sum(sc_ms) / len(sc_ms),
                          "dfa_scan (inside verify)": sum(ds_ms) / len(ds_ms), "device_total": sum(tot_dev_ms) / len(tot_dev_ms)},
             "roofline": {"bound": "hbm", "kernel": "k_filter_count (newline count + literal-gram prefilter over every byte)", "achieved": achieved,
-                         "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-                         "algorithmic_bytes_per_launch": int(sum(scan_bytes) / len(scan_bytes))},
+                         "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
+                         "peak_source": peak_src, "algorithmic_bytes_per_launch": int(sum(scan_bytes) / len(scan_bytes))},
             "e2e": {"value": e2e_value, "unit": "lines/s", "h2d_bytes_per_step": int(nbytes), "d2h_bytes_per_step": d2h,
                     "gb_per_s": e2e_value * nbytes / args.lines / 1e9, "steps": e2e_steps},
             "gpu_launches": int(launches), "clocks": clocks,
