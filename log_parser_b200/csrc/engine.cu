@@ -110,34 +110,7 @@ __device__ __forceinline__ uint32_t lower_bound_dev(const T* __restrict__ a, uin
     return lo;
 }
 
-// ------------------------------------------------------------------ K1: newline count per tile
-__global__ void __launch_bounds__(SCAN_THREADS) k_count_nl(const uint8_t* __restrict__ text, uint64_t len,
-                                                             uint32_t n_tiles, uint32_t* __restrict__ tile_counts) {
-    __shared__ uint32_t warp_sum[SCAN_THREADS / 32];
-    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
-        const uint64_t base = (uint64_t)tile * TILE_BYTES + (uint64_t)threadIdx.x * 16;
-        uint32_t cnt = 0;
-        uint4 v[SCAN_ITERS];
-#pragma unroll
-        for (int it = 0; it < SCAN_ITERS; ++it) {
-            uint64_t pos = base + (uint64_t)it * SCAN_THREADS * 16;
-            v[it] = pos < len ? load16(text, pos, len) : make_uint4(0, 0, 0, 0);
-        }
-#pragma unroll
-        for (int it = 0; it < SCAN_ITERS; ++it) cnt += __popc(nl_mask16(v[it]));
-        for (int o = 16; o; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-        if ((threadIdx.x & 31) == 0) warp_sum[threadIdx.x >> 5] = cnt;
-        __syncthreads();
-        if (threadIdx.x == 0) {
-            uint32_t s = 0;
-            for (int w = 0; w < SCAN_THREADS / 32; ++w) s += warp_sum[w];
-            tile_counts[tile] = s;
-        }
-        __syncthreads();
-    }
-}
-
-// ------------------------------------------------------------------ K1': newline count per tile + gram prefilter
+// ------------------------------------------------------------------ K1: newline count per tile + gram prefilter
 // The streaming kernel of the scan: one pass over the log, 16 bytes per thread and iteration.
 // It needs no line structure: newlines are only counted per tile (for the offsets pass that
 // follows), and every 4-byte window is tested against the literal-gram Bloom bitmap in shared
@@ -1020,14 +993,6 @@ __global__ void k_event_prep(const unsigned long long* __restrict__ ev_key, cons
     slot_key[e] = P.pat_slot[p] < 0 ? n_slots : (uint32_t)P.pat_slot[p];     // untracked patterns sort after every slot
     ev_idx[e] = e;
     atomicAdd(&freq_delta[p], 1ull);
-}
-__global__ void k_slot_rank(const uint32_t* __restrict__ sorted_slot, const uint32_t* __restrict__ sorted_idx, uint32_t m, uint32_t n_slots,
-                            uint32_t* __restrict__ rank_in_slot) {
-    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= m) return;
-    const uint32_t s = sorted_slot[j];
-    if (s >= n_slots) { rank_in_slot[sorted_idx[j]] = 0; return; }   // untracked pattern or padding
-    rank_in_slot[sorted_idx[j]] = j - lower_bound_dev<uint32_t>(sorted_slot, m, s);
 }
 __global__ void k_log_event_begin(const unsigned long long* __restrict__ ev_key, const Counters* ctr, const uint32_t* __restrict__ first_line,
                                   uint32_t n_logs, uint32_t pb, unsigned long long* __restrict__ begin) {

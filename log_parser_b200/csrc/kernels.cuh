@@ -1,10 +1,12 @@
 // Device kernels of the B200 hot path (sm_100a). HBM-bound byte/integer work: no tensor cores.
 //
-//   k_count_nl / k_scan_tiles / k_lines_filter   String.split("\\r?\\n")  AnalysisService.java:53
-//                                                + multi-literal gram prefilter for :89-95
-//   k_confirm / k_verify / k_verify_always       Matcher.find() per (line, regex)  AS:93-95,
-//                                                SS:281,300,330, CAS:64-79
-//   k_score                                      ScoringService.java:63-347, CAS:46-117, FTS:64-93
+//   k_filter_count / k_scan_tiles / k_lines / k_log_meta   String.split("\\r?\\n")  AnalysisService.java:53
+//                                                          + literal-gram prefilter for :89-95
+//   k_confirm / k_resolve / k_verify / k_verify_vm /       Matcher.find() per (line, regex)  AS:93-95,
+//   k_dfa_scan / k_verify_always / k_verify_vm_always      SS:281,300,330, CAS:64-79
+//   k_emit_events / k_tile_sort / k_tile_rank              event list in discovery order AS:100-109, ranking
+//   k_score                                                ScoringService.java:63-347, CAS:46-117, FTS:64-93
+//   k_range_tables / k_prior_prefix                        multi-GPU composition (no reference counterpart)
 #pragma once
 #include <cstdint>
 #include <cuda_runtime.h>
