@@ -91,12 +91,18 @@ typedef struct lp_result_view {
     const uint32_t* line_start;     /* [total_lines+1] byte offsets, NULL unless LP_OPT_LINE_OFFSETS */
     const uint32_t* line_end;       /* [total_lines]                                              */
     uint64_t total_lines;
+    /* LP_OPT_SPANS (extension; the reference uses find() as a boolean, AS:95): Matcher.start() and
+     * Matcher.end() of the first find() of the event's primary regex on its line, as UTF-8 byte
+     * offsets from the start of the line (equal to Java's UTF-16 offsets on ASCII lines). */
+    const uint32_t* span_start;     /* [n_events], NULL unless LP_OPT_SPANS                       */
+    const uint32_t* span_end;       /* [n_events]                                                 */
 } lp_result_view;
 
 enum {
     LP_OPT_FACTORS = 1,        /* also return the seven factors per event                        */
     LP_OPT_LINE_OFFSETS = 2,   /* also return line_start/line_end for context slicing (AS:132-156) */
-    LP_OPT_NO_RANK = 4         /* skip the ranking sort                                          */
+    LP_OPT_NO_RANK = 4,        /* skip the ranking sort                                          */
+    LP_OPT_SPANS = 8           /* also return the match span of every event (backtracking engine) */
 };
 
 /* ---- lifecycle ------------------------------------------------------------------------- */

@@ -17,7 +17,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.path.join(_HERE, "liblogparser_b200.so")
 
 LP_OK, LP_ERR_INVALID, LP_ERR_SYNTAX, LP_ERR_UNSUPPORTED, LP_ERR_CUDA, LP_ERR_LIMIT, LP_ERR_BACKTRACK = 0, -1, -2, -3, -4, -5, -6
-OPT_FACTORS, OPT_LINE_OFFSETS, OPT_NO_RANK = 1, 2, 4
+OPT_FACTORS, OPT_LINE_OFFSETS, OPT_NO_RANK, OPT_SPANS = 1, 2, 4, 8
 
 
 class LpError(RuntimeError):
@@ -68,6 +68,7 @@ class ResultView(C.Structure):
         ("score", C.POINTER(C.c_double)), ("rank", C.POINTER(C.c_uint32)), ("factors", C.POINTER(C.c_double)),
         ("freq_delta", C.POINTER(C.c_uint64)), ("n_patterns", C.c_uint64), ("line_start", C.POINTER(C.c_uint32)),
         ("line_end", C.POINTER(C.c_uint32)), ("total_lines", C.c_uint64),
+        ("span_start", C.POINTER(C.c_uint32)), ("span_end", C.POINTER(C.c_uint32)),
     ]
 
 
@@ -138,6 +139,7 @@ def load_library() -> C.CDLL:
     L.lp_debug_rx_literals.restype = C.c_size_t
     L.lp_debug_rx_literals.argtypes = [vp, C.c_char_p, C.c_size_t]
     L.lp_debug_rx_anchor.argtypes = [vp]
+    L.lp_debug_rx_span.argtypes = [vp, C.c_char_p, C.c_size_t, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
     L.lp_debug_rx_match_anchored.argtypes = [vp, C.c_char_p, C.c_size_t]
     _lib = L
     return L
@@ -194,6 +196,8 @@ class Result:
     factors: Optional[np.ndarray] = None
     line_start: Optional[np.ndarray] = None
     line_end: Optional[np.ndarray] = None
+    span_start: Optional[np.ndarray] = None     # OPT_SPANS: Matcher.start()/end() as byte offsets within the line
+    span_end: Optional[np.ndarray] = None
 
     @property
     def n_lines(self) -> int:
@@ -298,6 +302,9 @@ class LogParser:
             rank=_view(v.rank, m, np.uint32, owner), freq_delta=_view(v.freq_delta, v.n_patterns, np.uint64, owner))
         if v.factors:
             res.factors = _view(v.factors, m * 7, np.float64, owner).reshape(m, 7)
+        if v.span_start:
+            res.span_start = _view(v.span_start, m, np.uint32, owner)
+            res.span_end = _view(v.span_end, m, np.uint32, owner)
         if v.line_start:
             res.line_start = _arr(v.line_start, v.total_lines + 1, np.uint32)
             res.line_end = _arr(v.line_end, v.total_lines, np.uint32)
@@ -476,6 +483,15 @@ class DebugRegex:
     def match_anchored(self, text) -> int:
         b = text.encode("utf-8") if isinstance(text, str) else bytes(text)
         return int(self.L.lp_debug_rx_match_anchored(self.h, b, len(b)))
+
+    def span(self, text):
+        """(start, end) byte offsets of the first find(), or None."""
+        b = text.encode("utf-8") if isinstance(text, str) else bytes(text)
+        s, e = C.c_uint32(0), C.c_uint32(0)
+        r = self.L.lp_debug_rx_span(self.h, b, len(b), C.byref(s), C.byref(e))
+        if r < 0:
+            raise LpError(LP_ERR_BACKTRACK, "backtracking budget exceeded")
+        return (s.value, e.value) if r else None
 
     def literals(self):
         n = self.L.lp_debug_rx_literals(self.h, None, 0)

@@ -21,6 +21,7 @@ struct DebugRx {
     std::vector<Literal> lits;
     int anchor = 0;          // 0 none, 1 forward, 2 backward
     Dfa adfa;
+    VmProgram span_vm;       // every regex has a bytecode program: spans come from the backtracking engine
 };
 void put_err(char* err, size_t n, const std::string& m) {
     if (!err || !n) return;
@@ -43,6 +44,7 @@ void* lp_debug_rx_compile(const char* regex, int flags, int force_vm, char* err,
             force_vm &= 1;
             if (d->parsed.regular && !force_vm) d->has_dfa = build_dfa(*d->parsed.root, d->dfa);
             if (!d->has_dfa) { build_vm(d->parsed, d->vm); d->has_vm = true; }
+            build_vm(d->parsed, d->span_vm);
             d->lits = required_literals(*d->parsed.root, min_lit);
             if (d->has_dfa) d->anchor = choose_anchor(*d->parsed.root, d->lits, d->adfa);
         } catch (...) { delete d; throw; }
@@ -73,6 +75,13 @@ int lp_debug_rx_match(void* h, const uint8_t* s, size_t n) {
     return vm_match_host(d->vm, s, n);
 }
 unsigned long long lp_debug_anchor_steps(int reset) { unsigned long long v = lpx::g_anchor_steps; if (reset) lpx::g_anchor_steps = 0; return v; }
+// Byte offsets of the first find() (what k_spans computes); returns 1/0, <0 on a budget overflow.
+int lp_debug_rx_span(void* h, const uint8_t* s, size_t n, uint32_t* start, uint32_t* end) {
+    uint32_t span[2] = {0, 0};
+    const int r = vm_span_host(static_cast<DebugRx*>(h)->span_vm, s, n, span);
+    if (r > 0) { *start = span[0]; *end = span[1]; }
+    return r;
+}
 int lp_debug_rx_anchor(void* h) { return static_cast<DebugRx*>(h)->anchor; }
 // What k_confirm decides for an anchored regex: some occurrence of one of its literals at which the
 // anchored automaton accepts. -2 when the regex is not verified that way.

@@ -800,6 +800,30 @@ __device__ __forceinline__ bool vm_eval(const DevPlan& P, uint32_t r, const uint
     if (res < 0) atomicOr(&ctr->overflow, 16u);
     return res > 0;
 }
+// LP_OPT_SPANS: Matcher.start()/end() of the first find() of each event's primary regex on its line.
+__global__ void __launch_bounds__(128) k_spans(const unsigned long long* __restrict__ ev_key, const Counters* ctr, uint32_t m_cap, DevPlan P,
+                                               const uint8_t* __restrict__ text, const uint32_t* __restrict__ line_start,
+                                               const uint32_t* __restrict__ line_end, uint32_t* __restrict__ vm_stack, Counters* ctr_w,
+                                               uint32_t* __restrict__ span_start, uint32_t* __restrict__ span_end) {
+    const uint32_t m = min(ctr->n_events, m_cap);
+    const uint32_t stride = gridDim.x * blockDim.x;
+    uint32_t* stack = vm_stack + (size_t)(blockIdx.x * blockDim.x + threadIdx.x) * lpx::VM_STACK_WORDS;
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < m; e += stride) {
+        const unsigned long long k = ev_key[e];
+        const uint32_t g = (uint32_t)(k >> P.pb), p = (uint32_t)(k & ((1ull << P.pb) - 1ull));
+        const uint32_t r = P.pat_primary[p], ls = line_start[g], le = line_end[g];
+        lpx::VmView v;
+        v.code = reinterpret_cast<const lpx::VmCode*>(P.vm_code) + P.rx_vm_off[r];
+        v.set_off = P.vm_set_off + P.rx_vm_set_base[r];
+        v.set_data = P.vm_set_ranges;
+        v.n_slots = P.rx_vm_slots[r];
+        uint32_t span[2] = {ls, ls};
+        const int res = lpx::vm_find(v, text, ls, le, stack, lpx::VM_STACK_WORDS, lpx::VM_MAX_STEPS, span);
+        if (res < 0) atomicOr(&ctr_w->overflow, 16u);
+        span_start[e] = res > 0 ? span[0] - ls : 0xFFFFFFFFu;     // the automaton said the line matches; a miss here would be a bug
+        span_end[e] = res > 0 ? span[1] - ls : 0xFFFFFFFFu;
+    }
+}
 __global__ void __launch_bounds__(128) k_verify_vm(VerifyArgs a, DevPlan P) {
     const uint32_t n = min(a.ctr->n_vm_tasks, a.vm_task_cap);
     const uint32_t stride = gridDim.x * blockDim.x;
@@ -1428,7 +1452,7 @@ struct StagePool {
 struct lp_result {
     PinnedBuf hold;                           // event columns live here (pinned, written by the device)
     std::shared_ptr<StagePool> pool;
-    const uint32_t *line = nullptr, *pattern = nullptr, *rank = nullptr;
+    const uint32_t *line = nullptr, *pattern = nullptr, *rank = nullptr, *span_start = nullptr, *span_end = nullptr;
     const double *score = nullptr, *factors = nullptr;
     const uint64_t* freq_delta = nullptr;
     uint64_t n_patterns = 0;
@@ -1464,7 +1488,7 @@ struct lp_ctx {
 
     // scratch (grow-only)
     DevBuf text, log_off, tile_counts, counters, line_start, line_end, first_line, n_lines;
-    DevBuf items, ss_keys, ss_idx;
+    DevBuf items, ss_keys, ss_idx, span_start, span_end;
     size_t est_items = 0;
     int occ_confirm = 0, occ_resolve = 0;
     DevBuf cand, tasks, vm_tasks, vm_stack, recs, recs_alt, cub_tmp, rx_begin, ctx_flags;
@@ -2021,6 +2045,17 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
                                                           c->rank.as<uint32_t>());
         c->launches += 1;
     }
+    const bool want_spans = (options & LP_OPT_SPANS) != 0;
+    if (want_spans) {
+        const uint32_t sg = (uint32_t)c->n_sm * 2, sb = 128;
+        c->vm_stack.ensure((size_t)sg * sb * lpx::VM_STACK_WORDS * 4);
+        c->span_start.ensure((size_t)std::max<uint32_t>(mc, 1) * 4);
+        c->span_end.ensure((size_t)std::max<uint32_t>(mc, 1) * 4);
+        k_spans<<<sg, sb, 0, st>>>(c->ev_key.as<unsigned long long>(), ctr, mc, c->dp, c->pend.d_text, c->line_start.as<uint32_t>(),
+                                   c->line_end.as<uint32_t>(), c->vm_stack.as<uint32_t>(), ctr, c->span_start.as<uint32_t>(),
+                                   c->span_end.as<uint32_t>());
+        c->launches += 1;
+    }
     CK(cudaEventRecord(c->ev[4], st));
 
     // ---- download into page-locked staging (asynchronous copies, one synchronisation), sizes from
@@ -2032,7 +2067,8 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
     auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 63) & ~size_t(63); return o; };
     const size_t o_ctr = take(sizeof(Counters)), o_line = take((size_t)mc * 4), o_pat = take((size_t)mc * 4), o_score = take((size_t)mc * 8),
                  o_rank = take(want_rank ? (size_t)mc * 4 : 0), o_fac = take(want_factors ? (size_t)mc * 56 : 0),
-                 o_delta = take((size_t)np * 8), o_nl = take((size_t)n_logs * 4), o_leb = take((size_t)(n_logs + 1) * 8);
+                 o_delta = take((size_t)np * 8), o_nl = take((size_t)n_logs * 4), o_leb = take((size_t)(n_logs + 1) * 8),
+                 o_ss = take(want_spans ? (size_t)mc * 4 : 0), o_se = take(want_spans ? (size_t)mc * 4 : 0);
     if (!c->stage.p) c->stage = c->pool->acquire();
     c->stage.ensure(off);
     uint8_t* hs = c->stage.p;
@@ -2043,6 +2079,10 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
         CK(cudaMemcpyAsync(hs + o_score, c->out_score.p, (size_t)mc * 8, cudaMemcpyDeviceToHost, st));
         if (want_rank) CK(cudaMemcpyAsync(hs + o_rank, c->rank.p, (size_t)mc * 4, cudaMemcpyDeviceToHost, st));
         if (want_factors) CK(cudaMemcpyAsync(hs + o_fac, c->out_factors.p, (size_t)mc * 56, cudaMemcpyDeviceToHost, st));
+        if (want_spans) {
+            CK(cudaMemcpyAsync(hs + o_ss, c->span_start.p, (size_t)mc * 4, cudaMemcpyDeviceToHost, st));
+            CK(cudaMemcpyAsync(hs + o_se, c->span_end.p, (size_t)mc * 4, cudaMemcpyDeviceToHost, st));
+        }
     }
     if (np) CK(cudaMemcpyAsync(hs + o_delta, c->freq_delta.p, (size_t)np * 8, cudaMemcpyDeviceToHost, st));
     CK(cudaMemcpyAsync(hs + o_nl, c->n_lines.p, (size_t)n_logs * 4, cudaMemcpyDeviceToHost, st));
@@ -2064,6 +2104,7 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
     if (want_rank) res->rank = reinterpret_cast<uint32_t*>(hs + o_rank);
     else { res->zero_rank.assign(m, 0); res->rank = res->zero_rank.data(); }
     if (want_factors) { res->has_factors = true; res->factors = reinterpret_cast<double*>(hs + o_fac); }
+    if (want_spans) { res->span_start = reinterpret_cast<uint32_t*>(hs + o_ss); res->span_end = reinterpret_cast<uint32_t*>(hs + o_se); }
     res->freq_delta = reinterpret_cast<uint64_t*>(hs + o_delta);
     res->n_patterns = np;
     res->log_n_lines.resize(n_logs);
@@ -2220,7 +2261,7 @@ void lp_destroy(lp_ctx* c) {
                      &c->ev_log, &c->slot_key, &c->slot_key_alt, &c->ev_idx, &c->ev_idx_alt, &c->rank_in_slot, &c->freq_delta, &c->prior,
                      &c->out_line, &c->out_pat, &c->out_score, &c->out_factors, &c->sort_key, &c->sort_key_alt, &c->order, &c->order_alt,
                      &c->log_sorted, &c->log_sorted_alt, &c->rank, &c->log_event_begin, &c->n_unique, &c->d_lut,
-                     &c->f_bitmap, &c->f_key, &c->f_lits, &c->f_bytes, &c->items, &c->ss_keys, &c->ss_idx, &c->seq_tab_off, &c->seq_tab, &c->seq_T, &c->prior_eff, &c->any_flag};
+                     &c->f_bitmap, &c->f_key, &c->f_lits, &c->f_bytes, &c->items, &c->ss_keys, &c->ss_idx, &c->span_start, &c->span_end, &c->seq_tab_off, &c->seq_tab, &c->seq_T, &c->prior_eff, &c->any_flag};
     for (DevBuf* b : all) b->release();
     c->stage.release();
     c->pool->close();
@@ -2549,6 +2590,8 @@ int lp_result_get(const lp_result* r, lp_result_view* v) {
     v->line_start = r->has_offsets ? r->line_start.data() : nullptr;
     v->line_end = r->has_offsets ? r->line_end.data() : nullptr;
     v->total_lines = r->total_lines;
+    v->span_start = r->span_start;
+    v->span_end = r->span_end;
     return LP_OK;
 }
 void lp_result_free(lp_result* r) { delete r; }

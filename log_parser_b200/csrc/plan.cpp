@@ -245,6 +245,22 @@ void build_plan(const std::vector<PlanPatternIn>& pats, Plan& pl, int64_t* bad) 
         for (auto& v : members) { pl.slot_pats.insert(pl.slot_pats.end(), v.begin(), v.end()); pl.slot_begin.push_back((uint32_t)pl.slot_pats.size()); }
     }
     by_primary.resize(pl.n_rx);
+    // Match spans (LP_OPT_SPANS) come from the backtracking engine, whose priorities are java.util.regex's:
+    // every primary regex gets a bytecode program, also those whose existence is decided by a DFA.
+    for (uint32_t r : pl.pat_primary) {
+        if (pl.rx_vm_len[r]) continue;
+        VmProgram vp;
+        build_vm(parsed[r], vp);
+        pl.rx_vm_off[r] = (uint32_t)pl.vm_code.size();
+        pl.rx_vm_len[r] = (uint32_t)vp.code.size();
+        pl.rx_vm_slots[r] = vp.n_slots;
+        pl.rx_vm_caps[r] = vp.n_caps;
+        pl.rx_vm_set_base[r] = (uint32_t)pl.vm_set_off.size();
+        const uint32_t base = (uint32_t)pl.vm_set_ranges.size();
+        for (uint32_t o : vp.set_off) pl.vm_set_off.push_back(o + base);
+        pl.vm_set_ranges.insert(pl.vm_set_ranges.end(), vp.set_ranges.begin(), vp.set_ranges.end());
+        pl.vm_code.insert(pl.vm_code.end(), vp.code.begin(), vp.code.end());
+    }
     pl.rxp_begin.assign(pl.n_rx + 1, 0);
     for (uint32_t r = 0; r < pl.n_rx; ++r) {
         pl.rxp_begin[r + 1] = pl.rxp_begin[r] + (uint32_t)by_primary[r].size();

@@ -195,5 +195,14 @@ int vm_match_host(const VmProgram& p, const uint8_t* s, size_t n) {
     std::vector<uint32_t> stack(VM_STACK_WORDS);
     return vm_find(v, s, 0, (uint32_t)n, stack.data(), (uint32_t)stack.size(), VM_MAX_STEPS);
 }
+int vm_span_host(const VmProgram& p, const uint8_t* s, size_t n, uint32_t* span) {
+    VmView v;
+    v.code = reinterpret_cast<const VmCode*>(p.code.data());
+    v.set_off = p.set_off.data();
+    v.set_data = p.set_ranges.data();
+    v.n_slots = p.n_slots;
+    std::vector<uint32_t> stack(VM_STACK_WORDS);
+    return vm_find(v, s, 0, (uint32_t)n, stack.data(), (uint32_t)stack.size(), VM_MAX_STEPS, span);
+}
 
 }  // namespace lpx

@@ -120,7 +120,7 @@ LPX_HD bool vm_assert(int kind, bool unix_lines, const uint8_t* s, uint32_t ls, 
 // Runs the program anchored at `start`. Returns 1 match, 0 no match, -1 budget exhausted.
 // `stack` holds `cap` 32-bit words; `steps` is decremented.
 LPX_HD int vm_run(const VmView& v, const uint8_t* s, uint32_t ls, uint32_t le, uint32_t start, long tpos,
-                  uint32_t* slots, uint32_t* stack, uint32_t cap, int& steps) {
+                  uint32_t* slots, uint32_t* stack, uint32_t cap, int& steps, uint32_t* end_out = nullptr) {
     uint32_t sp = 0, pc = 0, pos = start;
 #define VM_PUSH(w0, w1) do { if (sp + 2 > cap) return -1; stack[sp++] = (w0); stack[sp++] = (w1); } while (0)
     for (;;) {
@@ -237,7 +237,7 @@ LPX_HD int vm_run(const VmView& v, const uint8_t* s, uint32_t ls, uint32_t le, u
             case VM_POSEQ:
                 if (pos == slots[in.a]) ++pc; else fail = true;
                 break;
-            case VM_MATCH: return 1;
+            case VM_MATCH: if (end_out) *end_out = pos; return 1;
             default: return -1;
         }
         if (!fail) continue;
@@ -280,7 +280,9 @@ LPX_HD int vm_run(const VmView& v, const uint8_t* s, uint32_t ls, uint32_t le, u
 }
 
 // Matcher.find(): try every start position (code point boundaries), leftmost first.
-LPX_HD int vm_find(const VmView& v, const uint8_t* s, uint32_t ls, uint32_t le, uint32_t* stack, uint32_t cap, int max_steps) {
+// span (optional, 2 words): Matcher.start() / Matcher.end() of that first match, as byte offsets into s.
+LPX_HD int vm_find(const VmView& v, const uint8_t* s, uint32_t ls, uint32_t le, uint32_t* stack, uint32_t cap, int max_steps,
+                   uint32_t* span = nullptr) {
     long tpos = -1;
     const uint32_t n = le - ls;
     if (n >= 1 && s[le - 1] == '\r') tpos = (long)le - 1;
@@ -291,7 +293,8 @@ LPX_HD int vm_find(const VmView& v, const uint8_t* s, uint32_t ls, uint32_t le, 
     uint32_t start = ls;
     for (uint32_t i = 0; i < v.n_slots; ++i) slots[i] = VM_NONE;   // once per find(), as Matcher.search() does
     for (;;) {
-        const int r = vm_run(v, s, ls, le, start, tpos, slots, stack, cap, steps);
+        const int r = vm_run(v, s, ls, le, start, tpos, slots, stack, cap, steps, span ? span + 1 : nullptr);
+        if (r > 0 && span) span[0] = start;
         if (r != 0) return r;
         if (start >= le) return 0;
         uint32_t l;

@@ -493,3 +493,46 @@ def test_piecewise_host_copy_equals_device_resident(parser):
         np.testing.assert_array_equal(r.score, resident.score)
         np.testing.assert_array_equal(r.rank, resident.rank)
     assert parser.timings()["kernel_launches"] > 0
+
+
+def test_match_spans_equal_oracle(parser, oracle):
+    """LP_OPT_SPANS (SURVEY §8-R extension; north_star: spans bit-exact): Matcher.start()/end() of the
+    first find() of each event's primary regex, from the device backtracking engine, against the
+    oracle's java.util.regex restatement. Oracle offsets are code points, the library's are UTF-8 bytes."""
+    pats = [PatternSpec(id="a", primary_regex=r"\b\w*Exception\b", confidence=0.9, severity="HIGH"),
+            PatternSpec(id="b", primary_regex=r"(?:GET|POST) (/\S*?)(\?\S+)? HTTP", confidence=0.5, severity="LOW"),
+            PatternSpec(id="c", primary_regex=r"retry(?:ing)? in \d+?ms|timeout", confidence=0.5, severity="LOW"),
+            PatternSpec(id="d", primary_regex=r"(\w+)=\1", confidence=0.5, severity="LOW"),
+            PatternSpec(id="e", primary_regex=r"(?<=user=)\w++(?!\w)", confidence=0.5, severity="LOW"),
+            PatternSpec(id="f", primary_regex=r"é+x|a.c$", confidence=0.5, severity="LOW"),
+            PatternSpec(id="g", primary_regex=r"^$", confidence=0.5, severity="LOW")]
+    lines = ["java.lang.NullPointerException at x", "GET /a/b?q=1 HTTP/1.1", "POST / HTTP", "retrying in 250ms then timeout",
+             "timeout; retry in 5ms", "k=k v=w w=w", "login user=alice ok", "ééx then abc", "abc\r", "", "nothing here",
+             "xException yException", "préfix NullPointerException é"]
+    log = "\n".join(lines).encode("utf-8") + b"\n"
+    parser.load_patterns(pats)
+    res = parser.analyze(log, options=binding.OPT_SPANS)
+    ora = oracle.analyze(ScoringConfig(), pats, log)
+    np.testing.assert_array_equal(res.line, ora.line)
+    np.testing.assert_array_equal(res.pattern, ora.pattern)
+    assert res.n_events >= 12 and res.span_start is not None
+    rx = [oracle.Regex(p.primary_regex) for p in pats]
+    for k in range(res.n_events):
+        text = lines[int(res.line[k]) - 1]
+        s, e = rx[int(res.pattern[k])].span(text)
+        exp = (len(text[:s].encode("utf-8")), len(text[:e].encode("utf-8")))
+        assert (int(res.span_start[k]), int(res.span_end[k])) == exp, (pats[int(res.pattern[k])].primary_regex, text)
+    # a larger log: every span lies inside its line and the spanned text matches on its own
+    wl = synth.make_patterns(40, 1212, noliteral=1)
+    log = synth.make_log(wl, 4000, 1213, hit_rate=0.05, pool_blocks=600)
+    parser.load_patterns(wl.patterns)
+    res = parser.analyze(log, options=binding.OPT_SPANS | binding.OPT_LINE_OFFSETS)
+    assert res.n_events > 100
+    rx = {}
+    for k in range(0, res.n_events, 7):
+        g = int(res.line[k]) - 1
+        text = log[int(res.line_start[g]):int(res.line_end[g])].decode("utf-8")
+        p = int(res.pattern[k])
+        o = rx.setdefault(p, oracle.Regex(wl.patterns[p].primary_regex))
+        s, e = o.span(text)
+        assert (int(res.span_start[k]), int(res.span_end[k])) == (len(text[:s].encode()), len(text[:e].encode()))

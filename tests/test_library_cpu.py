@@ -114,6 +114,36 @@ def test_anchored_verification_equals_line_walk(lib, oracle):
                 assert bool(d.match_anchored(t)) == o.find(t), (pat, t)
 
 
+def test_match_spans_vs_oracle_random(lib, oracle):
+    """Matcher.start()/end() of the first find() from the bytecode engine (what k_spans runs) against the
+    oracle: leftmost start, end by java.util.regex's priorities (ordered alternation, greedy/lazy/possessive)."""
+    rng = random.Random(31337)
+    checked = with_match = 0
+    for it in range(900):
+        j, _p = Gen(rng, regular_only=(it % 2 == 0)).regex()
+        try:
+            o = oracle.Regex(j)
+        except (oracle.OracleSyntaxError, oracle.OracleUnsupported):
+            continue
+        try:
+            d = binding.DebugRegex(j)
+        except binding.UnsupportedRegexError:
+            continue
+        for _k in range(8):
+            t = gen_text(rng)
+            exp = o.span(t)
+            if exp is not None:      # oracle offsets are code points
+                exp = (len(t[:exp[0]].encode("utf-8")), len(t[:exp[1]].encode("utf-8")))
+                with_match += 1
+            try:
+                got = d.span(t)
+            except binding.LpError:
+                continue
+            assert got == exp, (j, t)
+            checked += 1
+    assert checked > 5000 and with_match > 1500
+
+
 def test_backtracking_bytecode_vs_oracle_random(lib, oracle):
     """The interpreter of csrc/vm_exec.h (same code on host and device) against the oracle, on
     patterns with look-around, back-references, possessive/atomic constructs — and on regular ones
