@@ -536,3 +536,37 @@ def test_match_spans_equal_oracle(parser, oracle):
         o = rx.setdefault(p, oracle.Regex(wl.patterns[p].primary_regex))
         s, e = o.span(text)
         assert (int(res.span_start[k]), int(res.span_end[k])) == (len(text[:s].encode()), len(text[:e].encode()))
+
+
+def test_c5_shape_many_logs_in_one_batch(parser, oracle):
+    """configs[4] shape at a size the oracle finishes: a batch of 1500 pod logs of very different sizes
+    (empty, separators only, no final newline, \\r\\n) processed as the reference would process the
+    requests one after the other, frequency counts carried across them; per-log ranks."""
+    rnd = random.Random(5005)
+    wl = synth.make_patterns(30, 5006, noliteral=1)
+    pool = synth.make_log(wl, 6000, 5007, hit_rate=0.06, pool_blocks=900).split(b"\n")
+    logs = []
+    for k in range(1500):
+        r = rnd.random()
+        if r < 0.03:
+            logs.append(b"")
+        elif r < 0.05:
+            logs.append(rnd.choice([b"\n", b"\r\n\n", b"\n\n\n"]))
+        else:
+            n = rnd.choice([1, 2, 5, 20, 60, 150])
+            at = rnd.randrange(0, len(pool) - n)
+            sep = b"\r\n" if rnd.random() < 0.1 else b"\n"
+            body = sep.join(pool[at:at + n])
+            logs.append(body + (b"" if rnd.random() < 0.3 else sep))
+    parser.load_patterns(wl.patterns)
+    res = parser.analyze_batch(logs)
+    assert res.n_logs == len(logs) and res.n_events > 2000
+    prior = np.zeros(len(wl.patterns), np.uint64)
+    for k, lg in enumerate(logs):
+        ora = oracle.analyze(ScoringConfig(), wl.patterns, lg, prior_count=prior)
+        _check(res, ora, log_index=k, check_factors=False)
+        b, e = int(res.log_event_begin[k]), int(res.log_event_begin[k + 1])
+        np.testing.assert_array_equal(res.score[b:e], ora.score)
+        prior = prior + ora.freq_delta
+    np.testing.assert_array_equal(res.freq_delta, prior)
+    assert (prior > 10).any()          # the frequency penalty is in play across requests
