@@ -179,7 +179,20 @@ def cpu_reference_run(args, wl, log, steps: int, warmup: int):
     }
 
 
+def _emit(line: dict) -> None:
+    """The one JSON line, written to the process's original stdout."""
+    os.write(_STDOUT_FD, (json.dumps(line) + "\n").encode())
+
+
+_STDOUT_FD = 1
+
+
 def main():
+    # Libraries (NCCL's version banner, torchrun) write to fd 1: keep it for the JSON line alone.
+    global _STDOUT_FD
+    sys.stdout.flush()
+    _STDOUT_FD = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
@@ -223,7 +236,7 @@ def main():
                 "e2e": {"value": r["value"], "unit": "lines/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gb_per_s": r["value"] * r["bytes_per_line"] / 1e9,
                 "note": "JVM absent in this image: the reference arm is the in-repo C++ restatement of the reference's java.util.regex + scoring path"}
-        print(json.dumps(line))
+        _emit(line)
         return 0
 
     import numpy as np
@@ -364,7 +377,7 @@ def main():
         if world == 1 and not args.no_cpu_baseline:
             r = cpu_reference_run(args, wl, log, steps=1, warmup=0)
             line["cpu_baseline"] = {"value": r["value"], "unit": "lines/s", "cores": r["cores"], "kind": r["kind"], "sample": r["sample"]}
-        print(json.dumps(line))
+        _emit(line)
     if exchange is not None:
         exchange.close()
     if world > 1:
