@@ -204,6 +204,8 @@ def main():
     ap.add_argument("--ref-threads", type=int, default=0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true", help="skip the host-buffer leg (profiling runs)")
+    ap.add_argument("--exchange", default="nccl", choices=["nccl", "torch"],
+                    help="N>1, --shard logs: nccl = lp_analyze_batch_dist_device (NCCL inside the library), torch = all-gather via torch.distributed")
     ap.add_argument("--shard", default="logs", choices=["logs", "lines"],
                     help="N>1 only. logs: one C2 log per GPU (weak scaling, the default); lines: ONE C2 log cut by line range "
                          "with halos over the GPUs (strong scaling, lp_range_*)")
@@ -272,7 +274,12 @@ def main():
     off = np.array([0, nbytes], dtype=np.uint64)
     lib_stream = torch.cuda.ExternalStream(lp.stream_ptr(), device=torch.device("cuda", local_rank))
 
-    exchange = parallel.DeviceExchange(lp, rank, world) if (world > 1 and not by_lines) else None
+    exchange = None
+    if world > 1 and not by_lines:
+        if args.exchange == "torch":
+            exchange = parallel.DeviceExchange(lp, rank, world)       # all-gather issued from torch.distributed
+        else:
+            parallel.init_library_comm(lp, rank, world)               # the library's own NCCL communicator
 
     def step_device(i):
         d = copies[i % len(copies)]
@@ -281,7 +288,9 @@ def main():
         if by_lines:
             summary = lp.range_scan_device(d.data_ptr(), nbytes, halo_b, halo_a)
             return lp.range_score(parallel.gather_summaries(summary, world), rank, world)
-        return exchange.step(d.data_ptr(), off)       # scan -> NCCL all-gather of (P + 1) x int64 on the device -> score
+        if exchange is not None:
+            return exchange.step(d.data_ptr(), off)
+        return lp.analyze_batch_dist_device(d.data_ptr(), off)   # scan -> ncclAllGather of (P + 1) x u64 -> score, one call
 
     def barrier():
         if world > 1:
@@ -327,9 +336,11 @@ def main():
     r2 = res
 
     def step_host():
-        if not by_lines:
+        if world == 1:
             return lp.analyze_host_ptr(host.data_ptr(), nbytes)
-        copies[0].copy_(host, non_blocking=False)             # own range + halos, pinned host -> device
+        copies[0].copy_(host, non_blocking=False)             # this rank's share, pinned host -> device
+        if not by_lines:
+            return step_device(0)                             # the same exchange as the device-resident steps
         summary = lp.range_scan_device(copies[0].data_ptr(), nbytes, halo_b, halo_a)
         return lp.range_score(parallel.gather_summaries(summary, world), rank, world)
 

@@ -160,6 +160,17 @@ int lp_batch_scan_device_async(lp_ctx* ctx, const uint8_t* d_logs, const uint64_
 int lp_batch_score_gathered(lp_ctx* ctx, const uint64_t* d_all_counts, uint32_t rank, uint32_t world,
                             const uint64_t* prior_count, lp_result** out);
 
+/* The same batch step as ONE collective call: scan, ncclAllGather of the n_patterns + 1 words on
+ * lp_stream() over NVLink, prefix and score, with the repeat-on-LP_RETRY loop inside. NCCL
+ * (libnccl.so.2) is loaded at run time on the first lp_comm_* call; hosts that never call them need
+ * no NCCL. Set-up: rank 0 calls lp_comm_unique_id() (128 bytes, ncclUniqueId) and hands the bytes to
+ * the other ranks by whatever means the service has; every rank then calls lp_comm_init(). One
+ * process per GPU; every rank calls lp_analyze_batch_dist_device once per step, in the same order. */
+int lp_comm_unique_id(uint8_t* id128);
+int lp_comm_init(lp_ctx* ctx, const uint8_t* id128, uint32_t rank, uint32_t world);
+int lp_analyze_batch_dist_device(lp_ctx* ctx, const uint8_t* d_logs, const uint64_t* offsets, size_t n_logs,
+                                 const uint64_t* prior_count, int options, lp_result** out);
+
 /* ONE log sharded by line range over several GPUs (second mode; the reference walks
  * the whole log on one thread, AS:89-113). The host first removes the log's trailing separators
  * (the trailing empty strings String.split drops, AS:53), cuts the rest on line boundaries into

@@ -86,7 +86,8 @@ EXPORTS = [
     "lp_create", "lp_destroy", "lp_last_error", "lp_version", "lp_load_patterns", "lp_analyze", "lp_analyze_device",
     "lp_analyze_batch", "lp_analyze_batch_device", "lp_batch_scan_device", "lp_batch_score", "lp_result_get",
     "lp_result_free", "lp_get_timings", "lp_stream", "lp_split_lines_noalloc",
-    "lp_batch_scan_device_async", "lp_batch_score_gathered", "lp_range_halo_lines", "lp_range_summary_words", "lp_range_scan_device", "lp_range_score",
+    "lp_batch_scan_device_async", "lp_batch_score_gathered", "lp_comm_unique_id", "lp_comm_init",
+    "lp_analyze_batch_dist_device", "lp_range_halo_lines", "lp_range_summary_words", "lp_range_scan_device", "lp_range_score",
 ]
 
 _lib = None
@@ -121,6 +122,9 @@ def load_library() -> C.CDLL:
     L.lp_stream.argtypes = [vp]
     L.lp_batch_scan_device_async.argtypes = [vp, u8p, u64p, C.c_size_t, C.c_int, vp]
     L.lp_batch_score_gathered.argtypes = [vp, vp, C.c_uint32, C.c_uint32, u64p, C.POINTER(vp)]
+    L.lp_comm_unique_id.argtypes = [vp]
+    L.lp_comm_init.argtypes = [vp, vp, C.c_uint32, C.c_uint32]
+    L.lp_analyze_batch_dist_device.argtypes = [vp, u8p, u64p, C.c_size_t, u64p, C.c_int, C.POINTER(vp)]
     L.lp_range_halo_lines.restype = C.c_uint32
     L.lp_range_halo_lines.argtypes = [vp]
     L.lp_range_summary_words.restype = C.c_size_t
@@ -393,6 +397,30 @@ class LogParser:
         rc = self.L.lp_batch_score_gathered(self.h, all_counts_dev_ptr, rank, world, pp, C.byref(out))
         if rc == 1:
             return None
+        if rc != LP_OK:
+            _raise(rc)
+        return self._take(out)
+
+    # ---- NCCL inside the library
+    def comm_unique_id(self) -> bytes:
+        buf = C.create_string_buffer(128)
+        rc = self.L.lp_comm_unique_id(buf)
+        if rc != LP_OK:
+            _raise(rc)
+        return buf.raw
+
+    def comm_init(self, unique_id: bytes, rank: int, world: int) -> None:
+        assert len(unique_id) == 128
+        rc = self.L.lp_comm_init(self.h, C.create_string_buffer(unique_id, 128), rank, world)
+        if rc != LP_OK:
+            _raise(rc)
+
+    def analyze_batch_dist_device(self, dev_ptr: int, offsets, prior_count=None, options: int = 0) -> Result:
+        """Collective: this rank's block of a batch sharded by log (scan -> ncclAllGather -> score in one call)."""
+        oa, op = self._offsets(offsets)
+        keep, pp = self._prior(prior_count)
+        out = C.c_void_p()
+        rc = self.L.lp_analyze_batch_dist_device(self.h, dev_ptr, op, len(oa) - 1, pp, options, C.byref(out))
         if rc != LP_OK:
             _raise(rc)
         return self._take(out)

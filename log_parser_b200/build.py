@@ -37,7 +37,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
         _nvcc(), "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
         "-fmad=false",  # Java is strict IEEE-754 without contraction (JEP 306); scores must not use FMA
         "-Xcompiler", "-fPIC", "-shared", "-o", SO,
-    ] + [os.path.join(CSRC, s) for s in SOURCES]
+    ] + [os.path.join(CSRC, s) for s in SOURCES] + ["-ldl"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)

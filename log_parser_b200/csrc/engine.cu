@@ -7,6 +7,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <dlfcn.h>
 #include <limits>
 #include <memory>
 #include <mutex>
@@ -1279,7 +1280,16 @@ __global__ void k_prior_prefix(const unsigned long long* __restrict__ all, uint3
         *any_flag = f;
     }
 }
-__global__ void k_publish_overflow(const Counters* ctr, unsigned long long* __restrict__ dst) { *dst = ctr->overflow; }
+// Status word of a scan for the other ranks: non-zero exactly when check_estimates() on this rank will ask for a re-run.
+struct EstCaps { unsigned long long lines, cand, tasks, vm_tasks, recs, items, events; };
+__global__ void k_publish_overflow(const Counters* ctr, EstCaps cap, unsigned long long* __restrict__ dst) {
+    unsigned long long st = ctr->overflow;
+    const unsigned int mi = max(max(ctr->n_items[0], ctr->n_items[1]), max(ctr->n_items[2], ctr->n_items[3]));
+    if ((unsigned long long)ctr->n_lines_total + 1 > cap.lines || ctr->n_cand > cap.cand || ctr->n_tasks > cap.tasks ||
+        ctr->n_vm_tasks > cap.vm_tasks || ctr->n_recs > cap.recs || mi > cap.items || ctr->n_events > cap.events)
+        st |= 1ull << 32;
+    *dst = st;
+}
 // ------------------------------------------------------------------ sorting a few ten thousand keys
 // The event list and the score ranking hold ~10^4 keys: a device-wide radix sort spends 8-10 us per
 // digit pass on them (13 passes for these two sorts), all of it launch and look-back latency. Here
@@ -1513,7 +1523,9 @@ struct lp_ctx {
         bool range = false;                 // line-range shard: events only for the lines between the halos
         uint32_t halo_before = 0, halo_after = 0;
     } pend;
-    DevBuf seq_tab_off, seq_tab, seq_T, prior_eff, any_flag;
+    DevBuf seq_tab_off, seq_tab, seq_T, prior_eff, any_flag, dist_mine, dist_all;
+    void* nccl_comm = nullptr;              // ncclComm_t of lp_comm_init (NCCL is loaded at run time, see NcclApi)
+    uint32_t comm_rank = 0, comm_world = 1;
     std::vector<uint32_t> h_seq_tab_off;    // per sequence, offset of its chain table in a shard summary
     uint32_t n_seq = 0;
 
@@ -1739,6 +1751,10 @@ void check_estimates(lp_ctx* c, const Counters& h, uint32_t n_logs, bool events_
     bump(c->est_lines, G + 1); bump(c->est_cand, h.n_cand); bump(c->est_tasks, h.n_tasks);
     bump(c->est_vm_tasks, h.n_vm_tasks); bump(c->est_recs, h.n_recs); bump(c->est_items, max_items);
     if (events_too) bump(c->est_events, h.n_events);
+}
+
+EstCaps est_caps(const lp_ctx* c) {
+    return EstCaps{c->est_lines, c->est_cand, c->est_tasks, c->est_vm_tasks, c->est_recs, c->est_items, c->est_events};
 }
 
 // ---- phase 1: split + prefilter + verify + sorted unique records + events in discovery order.
@@ -1976,7 +1992,8 @@ void per_pattern_counts(lp_ctx* c, uint64_t* counts_out) {
 struct RangeGlobal { long long line_base, n_global; const long long* seq_T; };   // seq_T: host array [n_seq]
 
 lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* rgl = nullptr,
-                     const unsigned long long* prior_dev = nullptr) {
+                     const unsigned long long* prior_dev = nullptr, const unsigned long long* flag_dev = nullptr,
+                     unsigned long long* flag_out = nullptr) {
     if (!c->pend.valid) throw std::invalid_argument("no scan is pending on this context");
     cudaStream_t st = c->stream;
     const uint32_t mc = c->pend.m, n_logs = c->pend.n_logs, line_cap = c->pend.G, np = c->dp.n_pat;
@@ -2068,11 +2085,12 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
     const size_t o_ctr = take(sizeof(Counters)), o_line = take((size_t)mc * 4), o_pat = take((size_t)mc * 4), o_score = take((size_t)mc * 8),
                  o_rank = take(want_rank ? (size_t)mc * 4 : 0), o_fac = take(want_factors ? (size_t)mc * 56 : 0),
                  o_delta = take((size_t)np * 8), o_nl = take((size_t)n_logs * 4), o_leb = take((size_t)(n_logs + 1) * 8),
-                 o_ss = take(want_spans ? (size_t)mc * 4 : 0), o_se = take(want_spans ? (size_t)mc * 4 : 0);
+                 o_ss = take(want_spans ? (size_t)mc * 4 : 0), o_se = take(want_spans ? (size_t)mc * 4 : 0), o_flag = take(8);
     if (!c->stage.p) c->stage = c->pool->acquire();
     c->stage.ensure(off);
     uint8_t* hs = c->stage.p;
     CK(cudaMemcpyAsync(hs + o_ctr, ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
+    if (flag_dev) CK(cudaMemcpyAsync(hs + o_flag, flag_dev, 8, cudaMemcpyDeviceToHost, st));
     if (mc) {
         CK(cudaMemcpyAsync(hs + o_line, c->out_line.p, (size_t)mc * 4, cudaMemcpyDeviceToHost, st));
         CK(cudaMemcpyAsync(hs + o_pat, c->out_pat.p, (size_t)mc * 4, cudaMemcpyDeviceToHost, st));
@@ -2091,6 +2109,7 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
     CK(cudaGetLastError());
     Counters h;
     memcpy(&h, hs + o_ctr, sizeof h);
+    if (flag_dev && flag_out) memcpy(flag_out, hs + o_flag, 8);
     check_estimates(c, h, n_logs, true);       // throws Retry when a buffer was too small
 
     const uint32_t m = h.n_events;
@@ -2251,6 +2270,7 @@ lp_ctx* lp_create(const lp_scoring_cfg* cfg, int device) {
     return rc == LP_OK ? c : nullptr;
 }
 
+static void nccl_comm_destroy(void* comm);
 void lp_destroy(lp_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
@@ -2261,8 +2281,9 @@ void lp_destroy(lp_ctx* c) {
                      &c->ev_log, &c->slot_key, &c->slot_key_alt, &c->ev_idx, &c->ev_idx_alt, &c->rank_in_slot, &c->freq_delta, &c->prior,
                      &c->out_line, &c->out_pat, &c->out_score, &c->out_factors, &c->sort_key, &c->sort_key_alt, &c->order, &c->order_alt,
                      &c->log_sorted, &c->log_sorted_alt, &c->rank, &c->log_event_begin, &c->n_unique, &c->d_lut,
-                     &c->f_bitmap, &c->f_key, &c->f_lits, &c->f_bytes, &c->items, &c->ss_keys, &c->ss_idx, &c->span_start, &c->span_end, &c->seq_tab_off, &c->seq_tab, &c->seq_T, &c->prior_eff, &c->any_flag};
+                     &c->f_bitmap, &c->f_key, &c->f_lits, &c->f_bytes, &c->items, &c->ss_keys, &c->ss_idx, &c->span_start, &c->span_end, &c->seq_tab_off, &c->seq_tab, &c->seq_T, &c->prior_eff, &c->any_flag, &c->dist_mine, &c->dist_all};
     for (DevBuf* b : all) b->release();
+    if (c->nccl_comm) nccl_comm_destroy(c->nccl_comm);
     c->stage.release();
     c->pool->close();
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
@@ -2388,6 +2409,113 @@ int lp_batch_score(lp_ctx* c, const uint64_t* prior_count, lp_result** out) {
     });
 }
 
+// ---- NCCL inside the library: scan -> ncclAllGather -> score in one call, all on the context's stream.
+// libnccl.so.2 is resolved at run time (dlopen), so the library has no link-time dependency on it and a
+// single-GPU host needs no NCCL at all; in a process that already loaded NCCL (torch) the same copy is used.
+namespace {
+struct NcclApi {
+    typedef struct { char internal[128]; } UniqueId;
+    int (*GetUniqueId)(UniqueId*) = nullptr;
+    int (*CommInitRank)(void**, int, UniqueId, int) = nullptr;
+    int (*AllGather)(const void*, void*, size_t, int, void*, cudaStream_t) = nullptr;
+    int (*CommDestroy)(void*) = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+    bool ok = false;
+    std::string why;
+    NcclApi() {
+        void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) { why = std::string("libnccl.so.2 could not be loaded: ") + dlerror(); return; }
+        GetUniqueId = reinterpret_cast<decltype(GetUniqueId)>(dlsym(h, "ncclGetUniqueId"));
+        CommInitRank = reinterpret_cast<decltype(CommInitRank)>(dlsym(h, "ncclCommInitRank"));
+        AllGather = reinterpret_cast<decltype(AllGather)>(dlsym(h, "ncclAllGather"));
+        CommDestroy = reinterpret_cast<decltype(CommDestroy)>(dlsym(h, "ncclCommDestroy"));
+        GetErrorString = reinterpret_cast<decltype(GetErrorString)>(dlsym(h, "ncclGetErrorString"));
+        ok = GetUniqueId && CommInitRank && AllGather && CommDestroy && GetErrorString;
+        if (!ok) why = "libnccl.so.2 lacks an expected symbol";
+    }
+};
+NcclApi& nccl() { static NcclApi api; return api; }
+void nccl_check(int rc, const char* what) {
+    if (rc != 0) throw CudaFail(std::string(what) + ": " + (nccl().GetErrorString ? nccl().GetErrorString(rc) : "NCCL error"));
+}
+constexpr int NCCL_UINT64 = 5;      // ncclUint64 (nccl.h)
+}  // namespace
+static void nccl_comm_destroy(void* comm) { if (nccl().ok) nccl().CommDestroy(comm); }
+
+int lp_comm_unique_id(uint8_t* id128) {
+    if (!id128) { g_last_error = "NULL argument"; return LP_ERR_INVALID; }
+    return guarded(nullptr, [&] {
+        if (!nccl().ok) throw CudaFail(nccl().why);
+        NcclApi::UniqueId id;
+        nccl_check(nccl().GetUniqueId(&id), "ncclGetUniqueId");
+        memcpy(id128, id.internal, 128);
+    });
+}
+int lp_comm_init(lp_ctx* c, const uint8_t* id128, uint32_t rank, uint32_t world) {
+    if (!c || !id128) { g_last_error = "NULL argument"; return LP_ERR_INVALID; }
+    return guarded(c, [&] {
+        std::lock_guard<std::mutex> lk(c->mu);
+        if (rank >= world) throw std::invalid_argument("rank >= world");
+        if (!nccl().ok) throw CudaFail(nccl().why);
+        if (c->nccl_comm) { nccl().CommDestroy(c->nccl_comm); c->nccl_comm = nullptr; }
+        NcclApi::UniqueId id;
+        memcpy(id.internal, id128, 128);
+        nccl_check(nccl().CommInitRank(&c->nccl_comm, (int)world, id, (int)rank), "ncclCommInitRank");
+        c->comm_rank = rank; c->comm_world = world;
+    });
+}
+// This rank's block of a batch that is sharded by log over the communicator of lp_comm_init: scan,
+// all-gather of [per-pattern counts, status] over NVLink, exclusive prefix, score. Collective: every
+// rank calls it once per step (with n_logs >= 1). A rank whose scratch estimates were too small makes
+// all ranks repeat the step, which they agree on through the gathered status words.
+int lp_analyze_batch_dist_device(lp_ctx* c, const uint8_t* d_logs, const uint64_t* offsets, size_t n_logs, const uint64_t* prior_count,
+                                 int options, lp_result** out) {
+    if (!c || !out) { g_last_error = "NULL argument"; return LP_ERR_INVALID; }
+    *out = nullptr;
+    return guarded(c, [&] {
+        if (!offsets) throw std::invalid_argument("offsets is NULL");
+        std::lock_guard<std::mutex> lk(c->mu);
+        if (!c->nccl_comm) throw std::invalid_argument("lp_comm_init has not been called on this context");
+        const uint32_t np = c->dp.n_pat, world = c->comm_world, rank = c->comm_rank;
+        const size_t words = (size_t)np + 1;
+        c->dist_mine.ensure(words * 8);
+        c->dist_all.ensure(words * 8 * world);
+        c->prior_eff.ensure((size_t)std::max<uint32_t>(np, 1) * 8);
+        c->any_flag.ensure(8);
+        for (int round = 0;; ++round) {
+            if (round > 16) throw LimitFail("scratch estimates did not settle");
+            run_scan(c, d_logs, offsets[n_logs], offsets, (uint32_t)n_logs, options);
+            unsigned long long* mine = c->dist_mine.as<unsigned long long>();
+            CK(cudaMemsetAsync(mine, 0, words * 8, c->stream));
+            k_count_per_pattern<<<c->n_sm * 4, 256, 0, c->stream>>>(c->recs.as<unsigned long long>(), c->counters.as<Counters>(), c->dp, mine, 0u, 0u);
+            k_publish_overflow<<<1, 1, 0, c->stream>>>(c->counters.as<Counters>(), est_caps(c), mine + np);
+            nccl_check(nccl().AllGather(mine, c->dist_all.p, words, NCCL_UINT64, c->nccl_comm, c->stream), "ncclAllGather");
+            const unsigned long long* prior_in = nullptr;
+            if (prior_count && np) {
+                c->prior.ensure((size_t)np * 8);
+                CK(cudaMemcpyAsync(c->prior.p, prior_count, (size_t)np * 8, cudaMemcpyHostToDevice, c->stream));
+                prior_in = c->prior.as<unsigned long long>();
+            }
+            k_prior_prefix<<<blocks_for(std::max<uint32_t>(np, 1), 128), 128, 0, c->stream>>>(
+                c->dist_all.as<unsigned long long>(), np, rank, world, prior_in, c->prior_eff.as<unsigned long long>(),
+                c->any_flag.as<unsigned long long>());
+            c->launches += 4;
+            std::unique_ptr<lp_result> res;
+            bool again = false;
+            unsigned long long flag = 0;
+            try {
+                res.reset(run_score(c, nullptr, nullptr, c->prior_eff.as<unsigned long long>(), c->any_flag.as<unsigned long long>(), &flag));
+            } catch (const Retry&) { again = true; }
+            if (again) continue;                // this rank's status word was non-zero: the others repeat as well
+            if (flag & 16u) throw std::overflow_error("backtracking verifier exceeded its step/stack budget");
+            if (flag) continue;                 // every rank sees the same words: all of them repeat
+            *out = res.release();
+            return;
+        }
+    });
+}
+
 // Two-phase form with the exchange left on the device: nothing is read back between the phases.
 int lp_batch_scan_device_async(lp_ctx* c, const uint8_t* d_logs, const uint64_t* offsets, size_t n_logs, int options, uint64_t* d_counts_out) {
     if (!c || !d_counts_out) { g_last_error = "NULL argument"; return LP_ERR_INVALID; }
@@ -2401,7 +2529,7 @@ int lp_batch_scan_device_async(lp_ctx* c, const uint8_t* d_logs, const uint64_t*
         unsigned long long* dst = reinterpret_cast<unsigned long long*>(d_counts_out);
         CK(cudaMemsetAsync(dst, 0, ((size_t)np + 1) * 8, c->stream));
         k_count_per_pattern<<<c->n_sm * 4, 256, 0, c->stream>>>(c->recs.as<unsigned long long>(), c->counters.as<Counters>(), c->dp, dst, 0u, 0u);
-        k_publish_overflow<<<1, 1, 0, c->stream>>>(c->counters.as<Counters>(), dst + np);
+        k_publish_overflow<<<1, 1, 0, c->stream>>>(c->counters.as<Counters>(), est_caps(c), dst + np);
         c->launches += 2;
         CK(cudaGetLastError());
     });
@@ -2428,11 +2556,10 @@ int lp_batch_score_gathered(lp_ctx* c, const uint64_t* d_all_counts, uint32_t ra
             c->any_flag.as<unsigned long long>());
         c->launches += 1;
         std::unique_ptr<lp_result> res;
-        try {
-            res.reset(run_score(c, nullptr, nullptr, c->prior_eff.as<unsigned long long>()));
-        } catch (const Retry&) { again = true; return; }      // this rank's buffers were too small (now regrown)
         unsigned long long flag = 0;
-        CK(cudaMemcpy(&flag, c->any_flag.p, 8, cudaMemcpyDeviceToHost));
+        try {
+            res.reset(run_score(c, nullptr, nullptr, c->prior_eff.as<unsigned long long>(), c->any_flag.as<unsigned long long>(), &flag));
+        } catch (const Retry&) { again = true; return; }      // this rank's buffers were too small (now regrown)
         if (flag & 16u) throw std::overflow_error("backtracking verifier exceeded its step/stack budget on another rank");
         if (flag) { again = true; return; }                   // another rank's counts were incomplete
         *out = res.release();

@@ -95,6 +95,18 @@ class GpuBatchEngine:
 
 
 
+def init_library_comm(parser, rank: int, world_size: int, group=None) -> None:
+    """Creates the library's own NCCL communicator (lp_comm_init): rank 0's ncclUniqueId travels to the
+    other ranks through torch.distributed, after which lp_analyze_batch_dist_device needs no host-side
+    collective at all."""
+    import torch.distributed as dist
+
+    box = [parser.comm_unique_id() if rank == 0 else None]
+    if world_size > 1:
+        dist.broadcast_object_list(box, src=0, group=group)
+    parser.comm_init(box[0], rank, world_size)
+
+
 class DeviceExchange:
     """The by-log exchange kept on the device (lp_batch_scan_device_async / lp_batch_score_gathered):
     this rank's [P counts, status word] are written by the scan phase straight into a device buffer,

@@ -2,6 +2,7 @@
 seeded inputs. Bar (BASELINE.json north_star): pattern ids and line numbers bit-exact, discovery
 order identical, scores <= 1e-9 relative (they are in fact compared for bit equality first), final
 ranking identical."""
+import os
 import random
 
 import numpy as np
@@ -570,3 +571,57 @@ def test_c5_shape_many_logs_in_one_batch(parser, oracle):
         prior = prior + ora.freq_delta
     np.testing.assert_array_equal(res.freq_delta, prior)
     assert (prior > 10).any()          # the frequency penalty is in play across requests
+
+
+def _dist_worker(rank, world, port, path):
+    import os
+    import torch
+    import torch.distributed as dist
+    from log_parser_b200 import parallel
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("gloo", rank=rank, world_size=world)      # only carries the ncclUniqueId
+    wl = synth.make_patterns(40, 778, noliteral=1)
+    logs = [synth.make_log(wl, n, 320 + i, pool_blocks=400, hit_rate=0.06) for i, n in enumerate([500, 200, 900, 50, 400, 300])]
+    prior = (np.arange(len(wl.patterns)) % 5).astype(np.uint64)
+    lo, hi = parallel.shard_bounds([len(x) for x in logs], world)[rank]
+    lp = binding.LogParser(ScoringConfig(), device=rank)
+    lp.load_patterns(wl.patterns)
+    parallel.init_library_comm(lp, rank, world)
+    blob = b"".join(logs[lo:hi])
+    off = np.zeros(hi - lo + 1, np.uint64)
+    np.cumsum([len(x) for x in logs[lo:hi]], out=off[1:])
+    text = torch.from_numpy(np.frombuffer(blob, dtype=np.uint8).copy()).cuda()
+    for _ in range(3):       # the first steps repeat internally while the scratch estimates settle
+        r = lp.analyze_batch_dist_device(text.data_ptr(), off, prior)
+    np.savez(os.path.join(path, f"d{rank}.npz"), line=np.array(r.line), pattern=np.array(r.pattern), score=np.array(r.score))
+    dist.barrier()
+    dist.destroy_process_group()
+    lp.close()
+
+
+def test_library_nccl_batch_two_gpus(parser, tmp_path):
+    """lp_comm_init + lp_analyze_batch_dist_device on two GPUs (skipped on a one-GPU box): two ranks, one
+    collective call per step, concatenate to the single-batch result."""
+    import socket
+    import torch
+    import torch.multiprocessing as mp
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    wl = synth.make_patterns(40, 778, noliteral=1)
+    logs = [synth.make_log(wl, n, 320 + i, pool_blocks=400, hit_rate=0.06) for i, n in enumerate([500, 200, 900, 50, 400, 300])]
+    prior = (np.arange(len(wl.patterns)) % 5).astype(np.uint64)
+    parser.load_patterns(wl.patterns)
+    whole = parser.analyze_batch(logs, prior_count=prior)
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    mp.spawn(_dist_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    parts = [np.load(os.path.join(tmp_path, f"d{r}.npz")) for r in range(2)]
+    np.testing.assert_array_equal(np.concatenate([p["line"] for p in parts]), whole.line)
+    np.testing.assert_array_equal(np.concatenate([p["pattern"] for p in parts]), whole.pattern)
+    np.testing.assert_array_equal(np.concatenate([p["score"] for p in parts]), whole.score)
