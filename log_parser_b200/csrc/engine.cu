@@ -433,7 +433,17 @@ struct LineWalker {
         uint32_t lo = a - base;
         for (;;) {
             const uint32_t hi = min(8u, b - base);
-            if (lo == 0 && hi == 8) {
+            if constexpr (NG == 1) {
+                // one automaton: the eight class lookups do not depend on the state, so they are issued
+                // together and only the transition loads form a dependent chain
+                uint32_t cls[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) cls[k] = cm[0][(uint32_t)(cur >> (8 * k)) & 0xFFu];
+#pragma unroll
+                for (int k = 0; k < 8; ++k)
+                    if ((uint32_t)k >= lo && (uint32_t)k < hi && live(0)) st[0] = T[0][st[0] * nc[0] + cls[k]];
+                if (!live(0)) return false;
+            } else if (lo == 0 && hi == 8) {
                 const uint32_t x = (uint32_t)cur, y = (uint32_t)(cur >> 32);
                 bool any = true;
 #pragma unroll
@@ -450,6 +460,28 @@ struct LineWalker {
             lo = 0;
             cur = nxt;
             nxt = (base + 8 < b) ? load8_any(text, (uint64_t)base + 8, len) : 0ull;
+        }
+    }
+    // bytes [a, b) of text from b-1 down to a (automaton of the reversed language); NG == 1 only
+    __device__ __forceinline__ bool segment_rev(const uint8_t* __restrict__ text, uint64_t len, uint32_t a, uint32_t b) {
+        if (a >= b) return true;
+        uint32_t base = (b - 1) & ~7u;
+        unsigned long long cur = load8_any(text, base, len);
+        unsigned long long prv = (base >= 8 && base > a) ? load8_any(text, (uint64_t)base - 8, len) : 0ull;
+        for (;;) {
+            const uint32_t hi = min(8u, b - base), lo = a > base ? a - base : 0u;
+            uint32_t cls[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) cls[k] = cm[0][(uint32_t)(cur >> (8 * k)) & 0xFFu];
+#pragma unroll
+            for (int k = 7; k >= 0; --k)
+                if ((uint32_t)k >= lo && (uint32_t)k < hi && live(0)) st[0] = T[0][st[0] * nc[0] + cls[k]];
+            if (!live(0)) return false;
+            if (base <= a) return true;
+            base -= 8;
+            b = base + 8;
+            cur = prv;
+            prv = (base >= 8 && base > a) ? load8_any(text, (uint64_t)base - 8, len) : 0ull;
         }
     }
     __device__ __forceinline__ void run(const uint8_t* __restrict__ text, uint64_t len, uint32_t ls, uint32_t le) {
@@ -698,23 +730,22 @@ __global__ void __launch_bounds__(256) k_resolve(ResolveArgs a, DevPlan P) {
                 const uint32_t nc = ad.y;
                 const uint16_t* __restrict__ T = P.dfa_trans + ad.x;
                 const uint8_t* __restrict__ cm = P.rx_acmap + (size_t)r * 256;
-                uint32_t st, budget = ANCHOR_BUDGET;
+                LineWalker<1, true> w;
+                w.nc[0] = nc; w.T[0] = T; w.cm[0] = cm; w.ff[0] = 0;
                 if (cls == 1) {
-                    st = s == ls ? (ad.z & 0xFFFFu) : dev_word(a.text[s - 1]) ? ad.w : (ad.z >> 16);
+                    w.st[0] = s == ls ? (ad.z & 0xFFFFu) : dev_word(a.text[s - 1]) ? ad.w : (ad.z >> 16);
+                    const uint32_t stop = min(le, s + ANCHOR_BUDGET);
                     const long tpos = tail_terminator(a.text, ls, le);
-                    uint32_t p2 = s;
-                    while (st > 1u && p2 < le && budget) {
-                        if ((long)p2 == tpos) { st = T[st * nc + nc - 2]; if (st <= 1u) break; }
-                        st = T[st * nc + cm[a.text[p2]]];
-                        ++p2; --budget;
-                    }
-                    if (st > 1u && p2 == le) st = T[st * nc + nc - 1];
+                    if (tpos < 0 || (long)s > tpos || (long)stop <= tpos) w.segment(a.text, a.len, s, stop);
+                    else if (w.segment(a.text, a.len, s, (uint32_t)tpos)) { w.symbol(2); w.segment(a.text, a.len, (uint32_t)tpos, stop); }
+                    if (stop == le) w.symbol(1);
                 } else {
-                    st = e2 == le ? (ad.z & 0xFFFFu) : dev_word(a.text[e2]) ? ad.w : (ad.z >> 16);
-                    uint32_t p2 = e2;
-                    while (st > 1u && p2 > ls && budget) { st = T[st * nc + cm[a.text[p2 - 1]]]; --p2; --budget; }
-                    if (st > 1u && p2 == ls) st = T[st * nc + nc - 1];
+                    w.st[0] = e2 == le ? (ad.z & 0xFFFFu) : dev_word(a.text[e2]) ? ad.w : (ad.z >> 16);
+                    const uint32_t stop = e2 - ls > ANCHOR_BUDGET ? e2 - ANCHOR_BUDGET : ls;
+                    w.segment_rev(a.text, a.len, stop, e2);
+                    if (stop == ls) w.symbol(1);
                 }
+                const uint32_t st = w.st[0];
                 if (st == 1u) stage_put(s_rec, a.ctr, &a.ctr->n_recs, a.recs, a.rec_cap, 4u, rec);
                 else if (st > 1u) stage_put(s_task, a.ctr, &a.ctr->n_tasks, a.tasks, a.task_cap, 2u, ((unsigned long long)r << 32) | g);
             }
