@@ -828,6 +828,7 @@ __device__ __forceinline__ bool vm_eval(const DevPlan& P, uint32_t r, const uint
     v.set_off = P.vm_set_off + P.rx_vm_set_base[r];
     v.set_data = P.vm_set_ranges;
     v.n_slots = P.rx_vm_slots[r];
+    v.first = P.rx_vm_first + (size_t)r * 8;
     const int res = lpx::vm_find(v, text, ls, le, stack, lpx::VM_STACK_WORDS, lpx::VM_MAX_STEPS);
     if (res < 0) atomicOr(&ctr->overflow, 16u);
     return res > 0;
@@ -849,6 +850,7 @@ __global__ void __launch_bounds__(128) k_spans(const unsigned long long* __restr
         v.set_off = P.vm_set_off + P.rx_vm_set_base[r];
         v.set_data = P.vm_set_ranges;
         v.n_slots = P.rx_vm_slots[r];
+        v.first = P.rx_vm_first + (size_t)r * 8;
         uint32_t span[2] = {ls, ls};
         const int res = lpx::vm_find(v, text, ls, le, stack, lpx::VM_STACK_WORDS, lpx::VM_MAX_STEPS, span);
         if (res < 0) atomicOr(&ctr_w->overflow, 16u);
@@ -1698,6 +1700,7 @@ void upload_plan(lp_ctx* c) {
     d.rx_vm_len = upload(K, pl.rx_vm_len);
     d.rx_vm_slots = upload(K, pl.rx_vm_slots);
     d.rx_vm_caps = upload(K, pl.rx_vm_caps);
+    d.rx_vm_first = upload(K, pl.rx_vm_first);
     d.rx_vm_set_base = upload(K, pl.rx_vm_set_base);
     d.vm_code = upload(K, pl.vm_code);
     d.vm_set_off = upload(K, pl.vm_set_off);
@@ -1968,10 +1971,8 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
 
     // ---- sort + unique the (regex, line) records; rec_cap slots are sorted, unused ones are sentinels
     {
-        const int kb = 64;   // sentinels are all-ones: sort the full key
-        (void)kb;
         sort_keys<unsigned long long>(c, c->recs.as<unsigned long long>(), c->recs_alt.as<unsigned long long>(), (uint32_t)rec_cap,
-                                      std::min<int>(64, (int)c->dp.gb + bits_for(c->dp.n_rx) + 1));
+                                      std::min<int>(64, (int)c->dp.gb + bits_for(c->dp.n_rx)));     // the all-ones padding has regex field 2^bits - 1 > n_rx - 1: it sorts last without an extra bit
         size_t tmp = 0;
         cub::DeviceSelect::Unique(nullptr, tmp, c->recs_alt.as<unsigned long long>(), c->recs.as<unsigned long long>(),
                                   &ctr->n_unique, (int)rec_cap, st);

@@ -81,6 +81,7 @@ struct DevPlan {
     const uint32_t* rx_vm_len;
     const uint32_t* rx_vm_slots;
     const uint32_t* rx_vm_caps;
+    const uint32_t* rx_vm_first;      // 8 words per regex
     const uint32_t* rx_vm_set_base;
     const void* vm_code;
     const uint32_t* vm_set_off;

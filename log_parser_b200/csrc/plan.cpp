@@ -138,6 +138,7 @@ void build_plan(const std::vector<PlanPatternIn>& pats, Plan& pl, int64_t* bad) 
         pl.rx_vm_off.push_back(0); pl.rx_vm_len.push_back(0); pl.rx_vm_slots.push_back(0);
         pl.rx_vm_caps.push_back(0); pl.rx_vm_set_base.push_back(0);
         pl.rx_cmap.resize((size_t)pl.n_rx * 256, 0);
+        pl.rx_vm_first.resize((size_t)pl.n_rx * 8, ~0u);
         pl.rx_adfa_off.push_back(0); pl.rx_ancls.push_back(0);
         pl.rx_astart.resize((size_t)pl.n_rx * 3, 0);
         pl.rx_acmap.resize((size_t)pl.n_rx * 256, 0);
@@ -153,6 +154,7 @@ void build_plan(const std::vector<PlanPatternIn>& pats, Plan& pl, int64_t* bad) 
             pl.rx_vm_off[id] = (uint32_t)pl.vm_code.size();
             pl.rx_vm_len[id] = (uint32_t)vp.code.size();
             pl.rx_vm_slots[id] = vp.n_slots;
+            for (int w = 0; w < 8; ++w) pl.rx_vm_first[(size_t)id * 8 + w] = vp.first[w];
             pl.rx_vm_caps[id] = vp.n_caps;
             pl.rx_vm_set_base[id] = (uint32_t)pl.vm_set_off.size();
             uint32_t base = (uint32_t)pl.vm_set_ranges.size();
@@ -254,6 +256,7 @@ void build_plan(const std::vector<PlanPatternIn>& pats, Plan& pl, int64_t* bad) 
         pl.rx_vm_off[r] = (uint32_t)pl.vm_code.size();
         pl.rx_vm_len[r] = (uint32_t)vp.code.size();
         pl.rx_vm_slots[r] = vp.n_slots;
+        for (int w = 0; w < 8; ++w) pl.rx_vm_first[(size_t)r * 8 + w] = vp.first[w];
         pl.rx_vm_caps[r] = vp.n_caps;
         pl.rx_vm_set_base[r] = (uint32_t)pl.vm_set_off.size();
         const uint32_t base = (uint32_t)pl.vm_set_ranges.size();

@@ -42,6 +42,7 @@ struct Plan {
     std::vector<uint16_t> rx_start;
     std::vector<uint16_t> dfa_trans;
     std::vector<uint8_t> rx_cmap;         // 256 per regex
+    std::vector<uint32_t> rx_vm_first;    // 8 per regex: bytes a match of the bytecode program can begin with
     // anchored automaton (rx_compile.cpp: build_dfa_anchored) of regexes decided at their literal occurrences
     std::vector<uint32_t> rx_adfa_off;    // offset into dfa_trans
     std::vector<uint16_t> rx_ancls;

@@ -174,8 +174,64 @@ struct Emitter {
 
 }  // namespace
 
+namespace {
+struct FirstSet { uint32_t b[8] = {0, 0, 0, 0, 0, 0, 0, 0}; bool nullable = true; bool unknown = false; };
+void fs_add(FirstSet& f, uint32_t byte) { f.b[byte >> 5] |= 1u << (byte & 31u); }
+uint32_t lead_byte(uint32_t c) { return c < 0x80 ? c : c < 0x800 ? 0xC0 | (c >> 6) : c < 0x10000 ? 0xE0 | (c >> 12) : 0xF0 | (c >> 18); }
+FirstSet first_set(const Ast& a) {
+    FirstSet r;
+    switch (a.kind) {
+        case AstKind::Empty: case AstKind::Assert: case AstKind::Look: return r;          // zero-width
+        case AstKind::Backref: r.unknown = true; return r;
+        case AstKind::Set:
+            r.nullable = false;
+            for (const auto& x : a.set) {
+                const uint32_t hi = std::min<uint32_t>(x.hi, 0x10FFFF);
+                if (x.lo > hi) continue;
+                // lead bytes are monotonic in the code point: every lead byte between the two ends can occur
+                for (uint32_t b = lead_byte(x.lo); b <= lead_byte(hi); ++b) fs_add(r, b);
+            }
+            return r;
+        case AstKind::Group: case AstKind::Atomic: return first_set(*a.kids[0]);
+        case AstKind::Cat:
+            for (const auto& k : a.kids) {
+                FirstSet f = first_set(*k);
+                for (int i = 0; i < 8; ++i) r.b[i] |= f.b[i];
+                r.unknown |= f.unknown;
+                if (!f.nullable) { r.nullable = false; break; }
+            }
+            return r;
+        case AstKind::Alt:
+            r.nullable = false;
+            for (const auto& k : a.kids) {
+                FirstSet f = first_set(*k);
+                for (int i = 0; i < 8; ++i) r.b[i] |= f.b[i];
+                r.unknown |= f.unknown;
+                r.nullable |= f.nullable;
+            }
+            return r;
+        case AstKind::Repeat: {
+            r = first_set(*a.kids[0]);
+            if (a.min == 0) r.nullable = true;
+            return r;
+        }
+    }
+    r.unknown = true;
+    return r;
+}
+bool has_backref(const Ast& a) {
+    if (a.kind == AstKind::Backref) return true;
+    for (const auto& k : a.kids) if (has_backref(*k)) return true;
+    return false;
+}
+}  // namespace
+
 void build_vm(const ParsedRegex& rx, VmProgram& out) {
     out = VmProgram();
+    {
+        const FirstSet f = first_set(*rx.root);
+        if (!f.nullable && !f.unknown && !has_backref(*rx.root)) for (int i = 0; i < 8; ++i) out.first[i] = f.b[i];
+    }
     Emitter e(out, rx.n_groups);
     e.gen(*rx.root);
     e.emit(VM_MATCH);
@@ -192,6 +248,7 @@ int vm_match_host(const VmProgram& p, const uint8_t* s, size_t n) {
     v.set_off = p.set_off.data();
     v.set_data = p.set_ranges.data();
     v.n_slots = p.n_slots;
+    v.first = p.first;
     std::vector<uint32_t> stack(VM_STACK_WORDS);
     return vm_find(v, s, 0, (uint32_t)n, stack.data(), (uint32_t)stack.size(), VM_MAX_STEPS);
 }
@@ -201,6 +258,7 @@ int vm_span_host(const VmProgram& p, const uint8_t* s, size_t n, uint32_t* span)
     v.set_off = p.set_off.data();
     v.set_data = p.set_ranges.data();
     v.n_slots = p.n_slots;
+    v.first = p.first;
     std::vector<uint32_t> stack(VM_STACK_WORDS);
     return vm_find(v, s, 0, (uint32_t)n, stack.data(), (uint32_t)stack.size(), VM_MAX_STEPS, span);
 }

@@ -25,6 +25,11 @@ struct VmProgram {
     std::vector<uint32_t> set_ranges;
     uint32_t n_slots = 0;            // capture slots + loop marks
     uint32_t n_caps = 0;             // 2 * groups
+    // Bytes a match can begin with (bit b of first[b >> 5]); all ones when the pattern can match the
+    // empty string or uses back-references. find() skips start positions whose byte is not in the set:
+    // an attempt there fails before it consumes anything, and without back-references a failed attempt
+    // leaves nothing behind that a later one could observe.
+    uint32_t first[8] = {~0u, ~0u, ~0u, ~0u, ~0u, ~0u, ~0u, ~0u};
 };
 
 // Throws RegexUnsupported for constructs the bytecode cannot express.

@@ -47,6 +47,7 @@ struct VmView {
     const uint32_t* set_off;     // per set: offset into set_data; set_off[i+1] bounds it
     const uint32_t* set_data;    // per set: 4 words ASCII bitmap, then (lo,hi) pairs
     uint32_t n_slots;
+    const uint32_t* first;       // 8 words: bytes a match can begin with, or nullptr (no skipping)
 };
 
 constexpr uint32_t VM_MAX_SLOTS = 64;
@@ -292,7 +293,18 @@ LPX_HD int vm_find(const VmView& v, const uint8_t* s, uint32_t ls, uint32_t le, 
     int steps = max_steps;
     uint32_t start = ls;
     for (uint32_t i = 0; i < v.n_slots; ++i) slots[i] = VM_NONE;   // once per find(), as Matcher.search() does
+    uint32_t f[8];
+    bool skip = v.first != nullptr;
+    if (skip) {
+        uint32_t all = ~0u;
+        for (int i = 0; i < 8; ++i) { f[i] = v.first[i]; all &= f[i]; }
+        skip = all != ~0u;
+    }
     for (;;) {
+        if (skip) {       // next start position whose byte a match can begin with (none: no match; such patterns are not nullable)
+            while (start < le && !((f[s[start] >> 5] >> (s[start] & 31u)) & 1u)) ++start;
+            if (start >= le) return 0;
+        }
         const int r = vm_run(v, s, ls, le, start, tpos, slots, stack, cap, steps, span ? span + 1 : nullptr);
         if (r > 0 && span) span[0] = start;
         if (r != 0) return r;
