@@ -253,6 +253,10 @@ LPX_HD int vm_run(const VmView& v, const uint8_t* s, uint32_t ls, uint32_t le, u
             if (kind == VK_RANGE) {
                 const uint32_t lo = stack[sp - 1];
                 uint32_t hi = vm_prev_start(s, w1, ls);
+                // The continuation begins with a literal ASCII byte: give back straight to its previous
+                // occurrence. Every position skipped would fail at that VM_CHAR at once, with no side
+                // effect; an ASCII byte is always a code point boundary.
+                if (v.code[arg].op == VM_CHAR) { const uint8_t c = (uint8_t)v.code[arg].a; while (hi > lo && s[hi] != c) --hi; }
                 if (hi > lo) { stack[sp + 1] = hi; sp += 2; }   // keep the entry for the next give-back
                 else sp -= 2;                                   // exhausted: drop the DATA word too
                 pc = arg; pos = hi;
