@@ -1853,12 +1853,9 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     c->ev_key_alt.ensure(ev_cap * 8 + 8);
     Counters* ctr = c->counters.as<Counters>();
 
-    CK(cudaMemcpyAsync(c->log_off.p, h_off, (n_logs + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
+    // only the counters have to be clear before the first kernel; everything else is queued behind it so
+    // that the GPU starts on the log as early as possible
     CK(cudaMemsetAsync(ctr, 0, sizeof(Counters), st));
-    CK(cudaMemsetAsync(c->recs.p, 0xFF, rec_cap * 8, st));            // padding sentinels sort last
-    CK(cudaMemsetAsync(c->ev_key_alt.p, 0xFF, ev_cap * 8, st));
-    if (!c->plan.ctx_any_in_groups) CK(cudaMemsetAsync(c->ctx_flags.p, 0, (line_cap / 4 + 2) * 4, st));   // else k_dfa_scan writes every byte
-
     CK(cudaEventRecord(c->ev[0], st));
     const size_t smem = use_filter ? 65536 : 0;
     FilterArgs fa{};
@@ -1894,6 +1891,10 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         k_filter_count<<<std::min<uint32_t>(n_tiles, (uint32_t)c->n_sm * 3), SCAN_THREADS, smem, st>>>(fa);
     }
     CK(cudaEventRecord(c->ev[2], st));
+    CK(cudaMemcpyAsync(c->log_off.p, h_off, (n_logs + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
+    CK(cudaMemsetAsync(c->recs.p, 0xFF, rec_cap * 8, st));            // padding sentinels sort last
+    CK(cudaMemsetAsync(c->ev_key_alt.p, 0xFF, ev_cap * 8, st));
+    if (!c->plan.ctx_any_in_groups) CK(cudaMemsetAsync(c->ctx_flags.p, 0, (line_cap / 4 + 2) * 4, st));   // else k_dfa_scan writes every byte
     k_scan_tiles<<<1, 1024, 0, st>>>(c->tile_counts.as<uint32_t>(), n_tiles, n_logs, ctr);
     ScanArgs sa{};
     sa.text = d_text; sa.len = len; sa.n_tiles = n_tiles; sa.tile_prefix = c->tile_counts.as<uint32_t>();
