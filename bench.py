@@ -363,7 +363,7 @@ def main():
     if rank == 0:
         peak, peak_src = _peaks()
         traffic, traffic_src = None, None          # DRAM bytes of one k_filter_count launch from the committed ncu --set full capture (C2 only)
-        tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_v6_traffic.json")
+        tpath = os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_v8_traffic.json")
         if os.path.exists(tpath) and args.lines == 1_000_000 and args.patterns == 500 and not by_lines:
             tj = json.load(open(tpath))
             traffic, traffic_src = int(tj["dram_bytes_read"]) + int(tj["dram_bytes_write"]), tj["source"]

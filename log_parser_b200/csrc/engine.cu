@@ -1347,7 +1347,7 @@ __global__ void __launch_bounds__(SS_THREADS) k_tile_sort(const unsigned long lo
 }
 // out_sorted (optional): keys scattered to their final positions; out_rank (optional): final position of
 // original element i, written for i < *n_valid.
-__global__ void __launch_bounds__(256) k_tile_rank(const unsigned long long* __restrict__ tile_keys, const uint32_t* __restrict__ tile_idx,
+__global__ void __launch_bounds__(128) k_tile_rank(const unsigned long long* __restrict__ tile_keys, const uint32_t* __restrict__ tile_idx,
                                                    uint32_t n_tiles, uint32_t n, unsigned long long* __restrict__ out_sorted,
                                                    uint32_t* __restrict__ out_rank, const unsigned int* __restrict__ n_valid) {
     const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
@@ -1742,7 +1742,7 @@ bool small_sort(lp_ctx* c, const unsigned long long* in, uint32_t n, int end_bit
     c->ss_keys.ensure((size_t)n_tiles * SS_TILE * 8);
     c->ss_idx.ensure((size_t)n_tiles * SS_TILE * 4);
     k_tile_sort<<<n_tiles, SS_THREADS, 0, c->stream>>>(in, n, end_bit, c->ss_keys.as<unsigned long long>(), c->ss_idx.as<uint32_t>());
-    k_tile_rank<<<blocks_for(n_tiles * SS_TILE, 256), 256, 0, c->stream>>>(c->ss_keys.as<unsigned long long>(), c->ss_idx.as<uint32_t>(), n_tiles, n,
+    k_tile_rank<<<blocks_for(n_tiles * SS_TILE, 128), 128, 0, c->stream>>>(c->ss_keys.as<unsigned long long>(), c->ss_idx.as<uint32_t>(), n_tiles, n,
                                                                           out_sorted, out_rank, n_valid);
     c->launches += 2;
     return true;
