@@ -165,7 +165,10 @@ int lp_batch_score_gathered(lp_ctx* ctx, const uint64_t* d_all_counts, uint32_t 
  * (libnccl.so.2) is loaded at run time on the first lp_comm_* call; hosts that never call them need
  * no NCCL. Set-up: rank 0 calls lp_comm_unique_id() (128 bytes, ncclUniqueId) and hands the bytes to
  * the other ranks by whatever means the service has; every rank then calls lp_comm_init(). One
- * process per GPU; every rank calls lp_analyze_batch_dist_device once per step, in the same order. */
+ * process per GPU; every rank calls lp_analyze_batch_dist_device once per step, in the same order.
+ * The exchange is started as soon as this rank's match records are final and overlaps the rest of the
+ * scan phase. As with any collective, an error return on one rank leaves the others waiting in their
+ * next call: treat it as fatal for the communicator (lp_destroy on every rank, then start over). */
 int lp_comm_unique_id(uint8_t* id128);
 int lp_comm_init(lp_ctx* ctx, const uint8_t* id128, uint32_t rank, uint32_t world);
 int lp_analyze_batch_dist_device(lp_ctx* ctx, const uint8_t* d_logs, const uint64_t* offsets, size_t n_logs,

@@ -8,6 +8,7 @@
 #include <cstdio>
 #include <cstring>
 #include <dlfcn.h>
+#include <functional>
 #include <limits>
 #include <memory>
 #include <mutex>
@@ -1315,11 +1316,22 @@ __global__ void k_prior_prefix(const unsigned long long* __restrict__ all, uint3
 }
 // Status word of a scan for the other ranks: non-zero exactly when check_estimates() on this rank will ask for a re-run.
 struct EstCaps { unsigned long long lines, cand, tasks, vm_tasks, recs, items, events; };
-__global__ void k_publish_overflow(const Counters* ctr, EstCaps cap, unsigned long long* __restrict__ dst) {
+// `counts` are this rank's per-pattern event counts: their sum is the number of events k_emit_events
+// produces (same records, same line range), so the events queue is judged even when this runs before it.
+__global__ void __launch_bounds__(128) k_publish_overflow(const Counters* ctr, EstCaps cap, const unsigned long long* __restrict__ counts,
+                                                          uint32_t n_pat, unsigned long long* __restrict__ dst) {
+    __shared__ unsigned long long part[128];
+    unsigned long long sum = 0;
+    for (uint32_t p = threadIdx.x; p < n_pat; p += blockDim.x) sum += counts[p];
+    part[threadIdx.x] = sum;
+    __syncthreads();
+    for (int o = 64; o; o >>= 1) { if ((int)threadIdx.x < o) part[threadIdx.x] += part[threadIdx.x + o]; __syncthreads(); }
+    if (threadIdx.x != 0) return;
     unsigned long long st = ctr->overflow;
     const unsigned int mi = max(max(ctr->n_items[0], ctr->n_items[1]), max(ctr->n_items[2], ctr->n_items[3]));
     if ((unsigned long long)ctr->n_lines_total + 1 > cap.lines || ctr->n_cand > cap.cand || ctr->n_tasks > cap.tasks ||
-        ctr->n_vm_tasks > cap.vm_tasks || ctr->n_recs > cap.recs || mi > cap.items || ctr->n_events > cap.events)
+        ctr->n_vm_tasks > cap.vm_tasks || ctr->n_recs > cap.recs || mi > cap.items ||
+        max((unsigned long long)ctr->n_events, part[0]) > cap.events)
         st |= 1ull << 32;
     *dst = st;
 }
@@ -1558,6 +1570,8 @@ struct lp_ctx {
     } pend;
     DevBuf seq_tab_off, seq_tab, seq_T, prior_eff, any_flag, dist_mine, dist_all;
     void* nccl_comm = nullptr;              // ncclComm_t of lp_comm_init (NCCL is loaded at run time, see NcclApi)
+    std::function<void()> after_unique;     // run_scan calls it once the unique records exist (the collective starts its exchange there)
+    cudaEvent_t dist_ev[2] = {nullptr, nullptr};
     uint32_t comm_rank = 0, comm_world = 1;
     std::vector<uint32_t> h_seq_tab_off;    // per sequence, offset of its chain table in a shard summary
     uint32_t n_seq = 0;
@@ -1982,6 +1996,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
                                      &ctr->n_unique, (int)rec_cap, st));
         c->launches += 2;
     }
+    if (c->after_unique) c->after_unique();
     k_rx_bounds<<<blocks_for(c->dp.n_rx + 1, 128), 128, 0, st>>>(c->recs.as<unsigned long long>(), ctr, c->dp.n_rx, c->dp.gb, c->rx_begin.as<uint32_t>());
     c->launches += 1;
     if (!c->plan.ctx_in_groups) {
@@ -2026,7 +2041,7 @@ struct RangeGlobal { long long line_base, n_global; const long long* seq_T; };  
 
 lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* rgl = nullptr,
                      const unsigned long long* prior_dev = nullptr, const unsigned long long* flag_dev = nullptr,
-                     unsigned long long* flag_out = nullptr) {
+                     unsigned long long* flag_out = nullptr, cudaEvent_t wait_before_score = nullptr) {
     if (!c->pend.valid) throw std::invalid_argument("no scan is pending on this context");
     cudaStream_t st = c->stream;
     const uint32_t mc = c->pend.m, n_logs = c->pend.n_logs, line_cap = c->pend.G, np = c->dp.n_pat;
@@ -2072,6 +2087,7 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
             sa.seq_T = c->seq_T.as<long long>();
         }
     }
+    if (wait_before_score) CK(cudaStreamWaitEvent(st, wait_before_score, 0));     // the prior counts arrive on another stream
     k_score<<<blocks_for(mc, 128), 128, 0, st>>>(sa, c->dp, c->sc);
     k_log_event_begin<<<blocks_for(n_logs + 1, 128), 128, 0, st>>>(c->ev_key.as<unsigned long long>(), ctr, c->first_line.as<uint32_t>(),
                                                                    n_logs, c->dp.pb, c->log_event_begin.as<unsigned long long>());
@@ -2321,6 +2337,7 @@ void lp_destroy(lp_ctx* c) {
     c->pool->close();
     for (auto& e : c->ev) if (e) cudaEventDestroy(e);
     for (auto& e : c->chunk_ev) cudaEventDestroy(e);
+    for (auto& e : c->dist_ev) if (e) cudaEventDestroy(e);
     if (c->copy_stream) cudaStreamDestroy(c->copy_stream);
     if (c->stream) cudaStreamDestroy(c->stream);
     delete c;
@@ -2516,31 +2533,48 @@ int lp_analyze_batch_dist_device(lp_ctx* c, const uint8_t* d_logs, const uint64_
         c->dist_all.ensure(words * 8 * world);
         c->prior_eff.ensure((size_t)std::max<uint32_t>(np, 1) * 8);
         c->any_flag.ensure(8);
-        for (int round = 0;; ++round) {
-            if (round > 16) throw LimitFail("scratch estimates did not settle");
-            run_scan(c, d_logs, offsets[n_logs], offsets, (uint32_t)n_logs, options);
+        for (int k = 0; k < 2; ++k) if (!c->dist_ev[k]) CK(cudaEventCreateWithFlags(&c->dist_ev[k], cudaEventDisableTiming));
+        const unsigned long long* prior_in = nullptr;
+        if (prior_count && np) {
+            c->prior.ensure((size_t)np * 8);
+            CK(cudaMemcpyAsync(c->prior.p, prior_count, (size_t)np * 8, cudaMemcpyHostToDevice, c->stream));
+            prior_in = c->prior.as<unsigned long long>();
+        }
+        // The exchange starts as soon as the unique records exist and runs on the second stream, next to
+        // the kernels that do not need the other ranks' counts (context flags, event list, its sort);
+        // k_score waits for it. The status word covers every queue, the events queue through the sum of
+        // the counts, so all ranks always agree on whether the step is repeated.
+        struct Unhook { lp_ctx* c; ~Unhook() { c->after_unique = nullptr; } } unhook{c};
+        c->after_unique = [&, c] {
             unsigned long long* mine = c->dist_mine.as<unsigned long long>();
             CK(cudaMemsetAsync(mine, 0, words * 8, c->stream));
             k_count_per_pattern<<<c->n_sm * 4, 256, 0, c->stream>>>(c->recs.as<unsigned long long>(), c->counters.as<Counters>(), c->dp, mine, 0u, 0u);
-            k_publish_overflow<<<1, 1, 0, c->stream>>>(c->counters.as<Counters>(), est_caps(c), mine + np);
-            nccl_check(nccl().AllGather(mine, c->dist_all.p, words, NCCL_UINT64, c->nccl_comm, c->stream), "ncclAllGather");
-            const unsigned long long* prior_in = nullptr;
-            if (prior_count && np) {
-                c->prior.ensure((size_t)np * 8);
-                CK(cudaMemcpyAsync(c->prior.p, prior_count, (size_t)np * 8, cudaMemcpyHostToDevice, c->stream));
-                prior_in = c->prior.as<unsigned long long>();
-            }
-            k_prior_prefix<<<blocks_for(std::max<uint32_t>(np, 1), 128), 128, 0, c->stream>>>(
+            k_publish_overflow<<<1, 128, 0, c->stream>>>(c->counters.as<Counters>(), est_caps(c), mine, np, mine + np);
+            CK(cudaEventRecord(c->dist_ev[0], c->stream));
+            CK(cudaStreamWaitEvent(c->copy_stream, c->dist_ev[0], 0));
+            nccl_check(nccl().AllGather(mine, c->dist_all.p, words, NCCL_UINT64, c->nccl_comm, c->copy_stream), "ncclAllGather");
+            k_prior_prefix<<<blocks_for(std::max<uint32_t>(np, 1), 128), 128, 0, c->copy_stream>>>(
                 c->dist_all.as<unsigned long long>(), np, rank, world, prior_in, c->prior_eff.as<unsigned long long>(),
                 c->any_flag.as<unsigned long long>());
+            CK(cudaEventRecord(c->dist_ev[1], c->copy_stream));
             c->launches += 4;
+        };
+        for (int round = 0;; ++round) {
+            if (round > 16) throw LimitFail("scratch estimates did not settle");
+            run_scan(c, d_logs, offsets[n_logs], offsets, (uint32_t)n_logs, options);
             std::unique_ptr<lp_result> res;
             bool again = false;
             unsigned long long flag = 0;
             try {
-                res.reset(run_score(c, nullptr, nullptr, c->prior_eff.as<unsigned long long>(), c->any_flag.as<unsigned long long>(), &flag));
+                res.reset(run_score(c, nullptr, nullptr, c->prior_eff.as<unsigned long long>(), c->any_flag.as<unsigned long long>(), &flag,
+                                    c->dist_ev[1]));
             } catch (const Retry&) { again = true; }
-            if (again) continue;                // this rank's status word was non-zero: the others repeat as well
+            if (again) {
+                // this rank's own status word was non-zero, so the others repeat as well; read it to be sure
+                CK(cudaMemcpy(&flag, c->any_flag.p, 8, cudaMemcpyDeviceToHost));
+                if (!flag) throw LimitFail("internal: a repeat was requested that the other ranks cannot see");
+                continue;
+            }
             if (flag & 16u) throw std::overflow_error("backtracking verifier exceeded its step/stack budget");
             if (flag) continue;                 // every rank sees the same words: all of them repeat
             *out = res.release();
@@ -2562,7 +2596,7 @@ int lp_batch_scan_device_async(lp_ctx* c, const uint8_t* d_logs, const uint64_t*
         unsigned long long* dst = reinterpret_cast<unsigned long long*>(d_counts_out);
         CK(cudaMemsetAsync(dst, 0, ((size_t)np + 1) * 8, c->stream));
         k_count_per_pattern<<<c->n_sm * 4, 256, 0, c->stream>>>(c->recs.as<unsigned long long>(), c->counters.as<Counters>(), c->dp, dst, 0u, 0u);
-        k_publish_overflow<<<1, 1, 0, c->stream>>>(c->counters.as<Counters>(), est_caps(c), dst + np);
+        k_publish_overflow<<<1, 128, 0, c->stream>>>(c->counters.as<Counters>(), est_caps(c), dst, np, dst + np);
         c->launches += 2;
         CK(cudaGetLastError());
     });

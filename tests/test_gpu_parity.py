@@ -625,3 +625,33 @@ def test_library_nccl_batch_two_gpus(parser, tmp_path):
     np.testing.assert_array_equal(np.concatenate([p["line"] for p in parts]), whole.line)
     np.testing.assert_array_equal(np.concatenate([p["pattern"] for p in parts]), whole.pattern)
     np.testing.assert_array_equal(np.concatenate([p["score"] for p in parts]), whole.score)
+
+
+def test_library_nccl_single_rank_equals_batch(parser):
+    """lp_analyze_batch_dist_device with a communicator of one rank: the exchange path (count after the
+    unique pass, all-gather and prefix on the second stream, k_score waiting for it, the repeat loop on
+    a fresh context) must give exactly lp_analyze_batch's result."""
+    import torch
+
+    wl = synth.make_patterns(40, 4242, noliteral=1)
+    logs = [synth.make_log(wl, n, 700 + i, pool_blocks=400, hit_rate=0.06) for i, n in enumerate([800, 30, 1500, 400])]
+    prior = (np.arange(len(wl.patterns)) % 9).astype(np.uint64)
+    parser.load_patterns(wl.patterns)
+    whole = parser.analyze_batch(logs, prior_count=prior, options=binding.OPT_FACTORS)
+    lp = binding.LogParser(ScoringConfig())
+    try:
+        lp.load_patterns(wl.patterns)
+        lp.comm_init(lp.comm_unique_id(), 0, 1)
+        blob = b"".join(logs)
+        off = np.zeros(len(logs) + 1, np.uint64)
+        np.cumsum([len(x) for x in logs], out=off[1:])
+        text = torch.from_numpy(np.frombuffer(blob, dtype=np.uint8).copy()).cuda()
+        for _ in range(3):
+            r = lp.analyze_batch_dist_device(text.data_ptr(), off, prior, options=binding.OPT_FACTORS)
+            np.testing.assert_array_equal(r.line, whole.line)
+            np.testing.assert_array_equal(r.pattern, whole.pattern)
+            np.testing.assert_array_equal(r.score, whole.score)
+            np.testing.assert_array_equal(r.rank, whole.rank)
+            np.testing.assert_array_equal(r.freq_delta, whole.freq_delta)
+    finally:
+        lp.close()
