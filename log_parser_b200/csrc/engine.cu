@@ -115,9 +115,10 @@ __device__ __forceinline__ uint32_t lower_bound_dev(const T* __restrict__ a, uin
 // ------------------------------------------------------------------ K1: newline count per tile + gram prefilter
 // The streaming kernel of the scan: one pass over the log, 16 bytes per thread and iteration.
 // It needs no line structure: newlines are only counted per tile (for the offsets pass that
-// follows), and every 4-byte window is tested against the literal-gram Bloom bitmap in shared
-// memory (first probe for all windows, second probe only for first-probe hits); surviving window
-// positions go to the candidate queue with one warp-aggregated atomic per warp and iteration.
+// follows), and every 4-byte window is looked up in a one-byte-per-slot table of literal-gram hashes
+// held in shared memory (first stage). First-stage hits are staged per block; at the end of a tile all
+// threads check them against the two-probe Bloom bitmap (second stage) and the survivors go to the
+// candidate queue with one global atomic per tile.
 constexpr uint32_t CAND_STAGE = 2048;      // candidates staged per block and tile in shared memory
 struct FilterArgs {
     const uint8_t* text;
@@ -284,10 +285,10 @@ __global__ void __launch_bounds__(1024) k_scan_tiles(uint32_t* __restrict__ tile
     if (threadIdx.x == 0) { ctr->total_nl = carry; ctr->n_lines_total = carry + n_logs; }
 }
 
-// ------------------------------------------------------------------ K2: line offsets + gram prefilter
-// One pass over the log: every '\n' yields line_end[g] / line_start[g+1] (with the \r?\n rule and
-// the log boundaries of a batch), and every 4-byte window is tested against the literal-gram
-// bitmap held in shared memory; hits are appended to the candidate queue (warp-aggregated atomics).
+// ------------------------------------------------------------------ K2: line offsets
+// Second pass over the log: every '\n' yields line_end[g] / line_start[g+1] (with the \r?\n rule and
+// the log boundaries of a batch), at the global line index given by the scanned tile counts. (The
+// kernel can also run the gram filter itself, `use_filter`; the pipeline does that in k_filter_count.)
 struct ScanArgs {
     const uint8_t* text;
     uint64_t len;
