@@ -137,9 +137,10 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_filter_count(FilterArgs a) {
     extern __shared__ uint8_t s_tab[];      // 2^16 one-byte slots: 1 if some literal gram hashes here
     __shared__ uint32_t warp_sum[SCAN_THREADS / 32];
     __shared__ uint32_t s_cand[CAND_STAGE];
-    __shared__ uint32_t s_ncand, s_gbase, s_nkeep;
+    __shared__ uint32_t s_ncand[2];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (threadIdx.x == 0) s_ncand = 0;
+    if (threadIdx.x == 0) { s_ncand[0] = 0; s_ncand[1] = 0; }
+    uint32_t par = 0;
     if (a.use_filter) {
         const uint4* src = reinterpret_cast<const uint4*>(a.byte_table);
         uint4* dst = reinterpret_cast<uint4*>(s_tab);
@@ -188,7 +189,7 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_filter_count(FilterArgs a) {
                 for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, hinc, o); if (lane >= o) hinc += t; }
                 const uint32_t total = __shfl_sync(0xffffffffu, hinc, 31);
                 uint32_t base = 0;
-                if (lane == 0) base = atomicAdd(&s_ncand, total);
+                if (lane == 0) base = atomicAdd(&s_ncand[par], total);
                 base = __shfl_sync(0xffffffffu, base, 0) + hinc - n;
                 uint32_t hm = hits;
                 while (hm) {
@@ -207,52 +208,39 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_filter_count(FilterArgs a) {
         for (int o = 16; o; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
         if (lane == 0) warp_sum[warp] = cnt;
         __syncthreads();
-        const uint32_t staged = min(s_ncand, CAND_STAGE);
+        const uint32_t staged = min(s_ncand[par], CAND_STAGE);
         if (threadIdx.x == 0) {
             uint32_t sum = 0;
             for (int q = 0; q < SCAN_THREADS / 32; ++q) sum += warp_sum[q];
             a.tile_counts[tile] = sum;
-            s_nkeep = 0;
+            s_ncand[par ^ 1] = 0;       // the next tile stages behind the other counter: no reset barrier
         }
-        // second stage: both Bloom probes for every staged position (CAND_STAGE / SCAN_THREADS entries per thread)
-        uint32_t kept[CAND_STAGE / SCAN_THREADS];
-        uint32_t keep_mask = 0;
+        // second stage: both Bloom probes for every staged position (CAND_STAGE / SCAN_THREADS entries per
+        // thread); each warp appends its survivors to the global queue with one atomic
 #pragma unroll
         for (int k = 0; k < (int)(CAND_STAGE / SCAN_THREADS); ++k) {
             const uint32_t q = threadIdx.x + k * SCAN_THREADS;
+            bool keep = false;
+            uint32_t p = 0;
             if (q < staged) {
-                const uint32_t p = s_cand[q];
+                p = s_cand[q];
                 const uint32_t win = load4_any(a.text, p, a.len) | 0x20202020u;
                 const uint32_t h1 = (win * GRAM_MUL) >> (32 - GRAM_BITS), h2 = (win * GRAM_MUL2) >> (32 - GRAM_BITS);
-                kept[k] = p;
-                if ((__ldg(a.bitmap + (h1 >> 5)) >> (h1 & 31u)) & (__ldg(a.bitmap + (h2 >> 5)) >> (h2 & 31u)) & 1u) keep_mask |= 1u << k;
+                keep = ((__ldg(a.bitmap + (h1 >> 5)) >> (h1 & 31u)) & (__ldg(a.bitmap + (h2 >> 5)) >> (h2 & 31u)) & 1u) != 0;
             }
-        }
-        __syncthreads();        // every staged entry has been read: the buffer is compacted in place
-#pragma unroll
-        for (int k = 0; k < (int)(CAND_STAGE / SCAN_THREADS); ++k) {
-            const bool keep = (keep_mask >> k) & 1u;
             const unsigned votes = __ballot_sync(0xffffffffu, keep);
             if (votes) {
                 uint32_t base = 0;
-                if (lane == 0) base = atomicAdd(&s_nkeep, (uint32_t)__popc(votes));
-                base = __shfl_sync(0xffffffffu, base, 0);
-                if (keep) s_cand[base + __popc(votes & ((1u << lane) - 1u))] = kept[k];
+                if (lane == 0) base = atomicAdd(&a.ctr->n_cand, (uint32_t)__popc(votes));
+                base = __shfl_sync(0xffffffffu, base, 0) + __popc(votes & ((1u << lane) - 1u));
+                if (keep) {
+                    if (base < a.cand_cap) a.cand[base] = p;
+                    else atomicOr(&a.ctr->overflow, 1u);
+                }
             }
         }
-        __syncthreads();
-        if (threadIdx.x == 0) s_gbase = s_nkeep ? atomicAdd(&a.ctr->n_cand, s_nkeep) : 0u;
-        __syncthreads();
-        {
-            const uint32_t nk = s_nkeep, gbase = s_gbase;
-            for (uint32_t q = threadIdx.x; q < nk; q += SCAN_THREADS) {
-                if (gbase + q < a.cand_cap) a.cand[gbase + q] = s_cand[q];
-                else atomicOr(&a.ctr->overflow, 1u);
-            }
-        }
-        __syncthreads();
-        if (threadIdx.x == 0) s_ncand = 0;
-        __syncthreads();
+        __syncthreads();        // every staged entry has been read before the next tile overwrites the buffer
+        par ^= 1;
     }
 }
 
