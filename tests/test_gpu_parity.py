@@ -655,3 +655,22 @@ def test_library_nccl_single_rank_equals_batch(parser):
             np.testing.assert_array_equal(r.freq_delta, whole.freq_delta)
     finally:
         lp.close()
+
+
+@pytest.mark.parametrize("seed", [11, 12, 13, 14])
+def test_medium_logs_all_paths_vs_oracle(parser, oracle, seed):
+    """20 000-line logs with a mixed pattern set (literal, class-expanded, anchored forwards/backwards,
+    look-around / back-reference, literal-free) and enough events for more than one sort tile: every event,
+    score and rank against the oracle."""
+    wl = synth.make_patterns(60, 9000 + seed, nonregular_frac=0.12 if seed % 2 else 0.0, scoring_heavy=(seed % 3 == 0), noliteral=2)
+    log = synth.make_log(wl, 20_000, 9100 + seed, hit_rate=0.25, symptom_rate=0.2, phase_rate=0.02, pool_blocks=3000)
+    if seed == 12:
+        log = log.replace(b"\n", b"\r\n", 4000)
+    parser.load_patterns(wl.patterns)
+    prior = (np.arange(len(wl.patterns)) % 4).astype(np.uint64) * 3
+    res = parser.analyze(log, prior_count=prior, options=binding.OPT_FACTORS)
+    ora = oracle.analyze(ScoringConfig(), wl.patterns, log, prior_count=prior)
+    assert len(ora.line) > 2100          # more than one 2048-key sort tile
+    _check(res, ora)
+    np.testing.assert_array_equal(res.score, ora.score)
+    np.testing.assert_array_equal(res.freq_delta, ora.freq_delta)
