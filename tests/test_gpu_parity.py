@@ -674,3 +674,24 @@ def test_medium_logs_all_paths_vs_oracle(parser, oracle, seed):
     _check(res, ora)
     np.testing.assert_array_equal(res.score, ora.score)
     np.testing.assert_array_equal(res.freq_delta, ora.freq_delta)
+
+
+def test_many_events_device_radix_path_equals_tile_sort_path(parser):
+    """More than 131 072 events in one log: the event list and the ranking go through the device-wide radix
+    sorts instead of the tile sort. The same log cut into line-range shards keeps every shard on the tile-sort
+    path; both must agree bit for bit (events, scores, merged ranking)."""
+    from log_parser_b200 import parallel
+
+    cfg = ScoringConfig()
+    wl = synth.make_patterns(30, 6006, noliteral=1)
+    log = synth.make_log(wl, 260_000, 6007, hit_rate=0.9, symptom_rate=0.3, pool_blocks=4000)
+    parser.load_patterns(wl.patterns)
+    whole = parser.analyze(log)
+    if whole.n_events <= 131072:
+        pytest.skip(f"only {whole.n_events} events")
+    results, _ = _range_sharded(cfg, wl.patterns, log, 4)
+    assert max(len(r.line) for r in results) < 131072
+    np.testing.assert_array_equal(np.concatenate([r.line for r in results]), whole.line)
+    np.testing.assert_array_equal(np.concatenate([r.pattern for r in results]), whole.pattern)
+    np.testing.assert_array_equal(np.concatenate([r.score for r in results]), whole.score)
+    np.testing.assert_array_equal(np.concatenate(parallel.merge_ranks([r.score for r in results])), whole.rank)
