@@ -9,7 +9,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 SO = os.path.join(HERE, "liblogparser_b200.so")
 SOURCES = ["engine.cu", "noalloc.cu", "plan.cpp", "rx_parse.cpp", "rx_compile.cpp", "rx_literal.cpp", "vm.cpp", "debug_api.cpp"]
-HEADERS = ["kernels.cuh", "plan.h", "rx.h", "vm.h", "vm_exec.h", os.path.join("..", "..", "include", "logparser_b200.h")]
+HEADERS = ["kernels.cuh", "k_scan.cuh", "k_verify.cuh", "k_score.cuh", "k_sort.cuh", "plan.h", "rx.h", "vm.h", "vm_exec.h", os.path.join("..", "..", "include", "logparser_b200.h")]
 
 
 def _nvcc() -> str:

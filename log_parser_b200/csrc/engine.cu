@@ -27,1385 +27,10 @@ using namespace lpk;
 //                                         device code
 // ============================================================================================
 namespace {
-
-__device__ __forceinline__ uint32_t zero_byte_flags(uint32_t x) {
-    // exact per-byte "== 0" detector: bit 7 of each byte set iff that byte of x is zero
-    uint32_t t = ((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x;
-    return ~(t | 0x7F7F7F7Fu);
-}
-__device__ __forceinline__ uint32_t nl_mask4(uint32_t w) {
-    uint32_t m = (zero_byte_flags(w ^ 0x0A0A0A0Au) >> 7);
-    return ((m * 0x00204081u) >> 21) & 0xFu;
-}
-__device__ __forceinline__ uint32_t nl_mask16(const uint4& v) {
-    return nl_mask4(v.x) | (nl_mask4(v.y) << 4) | (nl_mask4(v.z) << 8) | (nl_mask4(v.w) << 12);
-}
-
-// 16 bytes at `pos`; bytes at or beyond `len` read as zero. `text` is 16-byte aligned. The
-// byte-wise tail is kept out of line so that it is not if-converted into every caller's hot loop.
-__device__ __noinline__ uint4 load16_tail(const uint8_t* __restrict__ text, uint64_t pos, uint64_t len) {
-    uint32_t w[4] = {0, 0, 0, 0};
-    for (int i = 0; i < 16; ++i)
-        if (pos + i < len) w[i >> 2] |= (uint32_t)text[pos + i] << ((i & 3) * 8);
-    return make_uint4(w[0], w[1], w[2], w[3]);
-}
-__device__ __forceinline__ uint4 load16(const uint8_t* __restrict__ text, uint64_t pos, uint64_t len) {
-    if (pos + 16 <= len) return __ldg(reinterpret_cast<const uint4*>(text + pos));
-    return load16_tail(text, pos, len);
-}
-__device__ __forceinline__ uint4 load16_any(const uint8_t* __restrict__ text, uint64_t pos, uint64_t len) {
-    if (pos + 16 <= len) return __ldg(reinterpret_cast<const uint4*>(text + pos));
-    if (pos >= len) return make_uint4(0, 0, 0, 0);
-    return load16(text, pos, len);
-}
-__device__ __noinline__ unsigned long long load8_tail(const uint8_t* __restrict__ text, uint64_t pos, uint64_t len) {
-    unsigned long long w = 0;
-    for (int i = 0; i < 8; ++i)
-        if (pos + i < len) w |= (unsigned long long)text[pos + i] << (i * 8);
-    return w;
-}
-// 8 bytes at the 8-aligned `pos`; bytes at or beyond `len` read as zero
-__device__ __forceinline__ unsigned long long load8_any(const uint8_t* __restrict__ text, uint64_t pos, uint64_t len) {
-    if (pos + 8 <= len) { const uint2 v = __ldg(reinterpret_cast<const uint2*>(text + pos)); return ((unsigned long long)v.y << 32) | v.x; }
-    return load8_tail(text, pos, len);
-}
-__device__ __noinline__ uint32_t load4_tail(const uint8_t* __restrict__ text, uint64_t pos, uint64_t len) {
-    uint32_t w = 0;
-    for (int i = 0; i < 4; ++i)
-        if (pos + i < len) w |= (uint32_t)text[pos + i] << (i * 8);
-    return w;
-}
-// 4 bytes at any position p (two aligned loads + funnel shift); bytes at or beyond len read as zero
-__device__ __forceinline__ uint32_t load4_any(const uint8_t* __restrict__ text, uint32_t p, uint64_t len) {
-    const uint32_t b = p & ~3u;
-    if ((uint64_t)b + 8 <= len) {
-        const uint32_t lo = __ldg(reinterpret_cast<const uint32_t*>(text + b)), hi = __ldg(reinterpret_cast<const uint32_t*>(text + b + 4));
-        return __funnelshift_r(lo, hi, (p & 3u) * 8);
-    }
-    uint32_t w = 0;
-    for (int i = 0; i < 4; ++i) if ((uint64_t)p + i < len) w |= (uint32_t)text[p + i] << (8 * i);
-    return w;
-}
-__device__ __forceinline__ uint32_t load4_safe(const uint8_t* __restrict__ text, uint64_t pos, uint64_t len) {
-    if (pos + 4 <= len) return __ldg(reinterpret_cast<const uint32_t*>(text + pos));  // pos is 4-aligned here
-    return load4_tail(text, pos, len);
-}
-
-// number of elements of a[0..n) that are <= v   (upper bound)
-template <class T>
-__device__ __forceinline__ uint32_t upper_bound_dev(const T* __restrict__ a, uint32_t n, T v) {
-    uint32_t lo = 0, hi = n;
-    while (lo < hi) {
-        uint32_t mid = (lo + hi) >> 1;
-        if (a[mid] <= v) lo = mid + 1; else hi = mid;
-    }
-    return lo;
-}
-// number of elements of a[0..n) that are < v   (lower bound)
-template <class T>
-__device__ __forceinline__ uint32_t lower_bound_dev(const T* __restrict__ a, uint32_t n, T v) {
-    uint32_t lo = 0, hi = n;
-    while (lo < hi) {
-        uint32_t mid = (lo + hi) >> 1;
-        if (a[mid] < v) lo = mid + 1; else hi = mid;
-    }
-    return lo;
-}
-
-// ------------------------------------------------------------------ K1: newline count per tile + gram prefilter
-// The streaming kernel of the scan: one pass over the log, 16 bytes per thread and iteration.
-// It needs no line structure: newlines are only counted per tile (for the offsets pass that
-// follows), and every 4-byte window is looked up in a one-byte-per-slot table of literal-gram hashes
-// held in shared memory (first stage). First-stage hits are staged per block; at the end of a tile all
-// threads check them against the two-probe Bloom bitmap (second stage) and the survivors go to the
-// candidate queue with one global atomic per tile.
-constexpr uint32_t CAND_STAGE = 2048;      // candidates staged per block and tile in shared memory
-struct FilterArgs {
-    const uint8_t* text;
-    uint64_t len;
-    uint32_t n_tiles;
-    uint32_t tile_begin, tile_end;    // this launch's tiles (a log arriving from the host is scanned chunk by chunk)
-    uint32_t* tile_counts;
-    const uint32_t* bitmap;
-    const uint8_t* byte_table;
-    uint32_t* cand;                   // candidate byte positions
-    uint32_t cand_cap;
-    Counters* ctr;
-    int use_filter;
-};
-__global__ void __launch_bounds__(SCAN_THREADS) k_filter_count(FilterArgs a) {
-    extern __shared__ uint8_t s_tab[];      // 2^16 one-byte slots: 1 if some literal gram hashes here
-    __shared__ uint32_t warp_sum[SCAN_THREADS / 32];
-    __shared__ uint32_t s_cand[CAND_STAGE];
-    __shared__ uint32_t s_ncand[2];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (threadIdx.x == 0) { s_ncand[0] = 0; s_ncand[1] = 0; }
-    uint32_t par = 0;
-    if (a.use_filter) {
-        const uint4* src = reinterpret_cast<const uint4*>(a.byte_table);
-        uint4* dst = reinterpret_cast<uint4*>(s_tab);
-        for (uint32_t i = threadIdx.x; i < 65536 / 16; i += SCAN_THREADS) dst[i] = __ldg(src + i);
-    }
-    __syncthreads();
-    for (uint32_t tile = a.tile_begin + blockIdx.x; tile < a.tile_end; tile += gridDim.x) {
-        const uint64_t tile_base = (uint64_t)tile * TILE_BYTES;
-        uint32_t cnt = 0;
-        const uint64_t pos0 = tile_base + (uint64_t)threadIdx.x * 16;
-        uint4 vnext = pos0 < a.len ? load16(a.text, pos0, a.len) : make_uint4(0, 0, 0, 0);
-        // the 4 bytes after a warp's 512-byte span (needed by lane 31's last windows) are prefetched the same way
-        uint32_t tnext = (lane == 31 && a.use_filter && pos0 + 16 < a.len) ? load4_safe(a.text, pos0 + 16, a.len) : 0u;
-#pragma unroll 1
-        for (int it = 0; it < SCAN_ITERS; ++it) {
-            const uint64_t pos = tile_base + ((uint64_t)it * SCAN_THREADS + threadIdx.x) * 16;
-            const uint4 v = vnext;
-            const uint32_t tail = tnext;
-            {   // the next iteration's 16 bytes are requested before this iteration's work starts
-                const uint64_t pn = pos + (uint64_t)SCAN_THREADS * 16;
-                const bool more = it + 1 < SCAN_ITERS && pn < a.len;
-                vnext = more ? load16(a.text, pn, a.len) : make_uint4(0, 0, 0, 0);
-                tnext = (more && lane == 31 && a.use_filter && pn + 16 < a.len) ? load4_safe(a.text, pn + 16, a.len) : 0u;
-            }
-            cnt += __popc(zero_byte_flags(v.x ^ 0x0A0A0A0Au)) + __popc(zero_byte_flags(v.y ^ 0x0A0A0A0Au)) +
-                   __popc(zero_byte_flags(v.z ^ 0x0A0A0A0Au)) + __popc(zero_byte_flags(v.w ^ 0x0A0A0A0Au));
-            if (!a.use_filter) continue;
-            uint32_t nxt = __shfl_down_sync(0xffffffffu, v.x, 1);
-            if (lane == 31) nxt = tail;
-            const uint32_t w[5] = {v.x | 0x20202020u, v.y | 0x20202020u, v.z | 0x20202020u, v.w | 0x20202020u, nxt | 0x20202020u};
-            uint32_t hits = 0;
-#pragma unroll
-            for (int i = 15; i >= 0; --i) {
-                const uint32_t win = (i & 3) ? __funnelshift_r(w[i >> 2], w[(i >> 2) + 1], (i & 3) * 8) : w[i >> 2];
-                hits = hits * 2u + s_tab[(win * GRAM_MUL) >> 16];       // 5 instructions per window: SHF, IMAD, SHF, LDS.U8, LEA
-            }
-            if (pos >= a.len) hits = 0;
-            // first-stage hits (about 1-2 % of the positions) go to a per-block staging buffer in shared
-            // memory (one shared-memory atomic per warp and iteration); at the end of the tile the whole
-            // block checks them against the two-probe Bloom bitmap with every lane busy, and publishes the
-            // survivors with ONE global atomic
-            const uint32_t n = __popc(hits);
-            if (__ballot_sync(0xffffffffu, n != 0)) {
-                uint32_t hinc = n;
-#pragma unroll
-                for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, hinc, o); if (lane >= o) hinc += t; }
-                const uint32_t total = __shfl_sync(0xffffffffu, hinc, 31);
-                uint32_t base = 0;
-                if (lane == 0) base = atomicAdd(&s_ncand[par], total);
-                base = __shfl_sync(0xffffffffu, base, 0) + hinc - n;
-                uint32_t hm = hits;
-                while (hm) {
-                    const int i = __ffs(hm) - 1;
-                    hm &= hm - 1;
-                    if (base < CAND_STAGE) s_cand[base] = (uint32_t)(pos + i);
-                    else {      // staging full (a tile dense with hits): straight to the global queue
-                        const uint32_t gi = atomicAdd(&a.ctr->n_cand, 1u);
-                        if (gi < a.cand_cap) a.cand[gi] = (uint32_t)(pos + i);
-                        else atomicOr(&a.ctr->overflow, 1u);
-                    }
-                    ++base;
-                }
-            }
-        }
-        for (int o = 16; o; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
-        if (lane == 0) warp_sum[warp] = cnt;
-        __syncthreads();
-        const uint32_t staged = min(s_ncand[par], CAND_STAGE);
-        if (threadIdx.x == 0) {
-            uint32_t sum = 0;
-            for (int q = 0; q < SCAN_THREADS / 32; ++q) sum += warp_sum[q];
-            a.tile_counts[tile] = sum;
-            s_ncand[par ^ 1] = 0;       // the next tile stages behind the other counter: no reset barrier
-        }
-        // second stage: both Bloom probes for every staged position (CAND_STAGE / SCAN_THREADS entries per
-        // thread); each warp appends its survivors to the global queue with one atomic
-#pragma unroll
-        for (int k = 0; k < (int)(CAND_STAGE / SCAN_THREADS); ++k) {
-            const uint32_t q = threadIdx.x + k * SCAN_THREADS;
-            bool keep = false;
-            uint32_t p = 0;
-            if (q < staged) {
-                p = s_cand[q];
-                const uint32_t win = load4_any(a.text, p, a.len) | 0x20202020u;
-                const uint32_t h1 = (win * GRAM_MUL) >> (32 - GRAM_BITS), h2 = (win * GRAM_MUL2) >> (32 - GRAM_BITS);
-                keep = ((__ldg(a.bitmap + (h1 >> 5)) >> (h1 & 31u)) & (__ldg(a.bitmap + (h2 >> 5)) >> (h2 & 31u)) & 1u) != 0;
-            }
-            const unsigned votes = __ballot_sync(0xffffffffu, keep);
-            if (votes) {
-                uint32_t base = 0;
-                if (lane == 0) base = atomicAdd(&a.ctr->n_cand, (uint32_t)__popc(votes));
-                base = __shfl_sync(0xffffffffu, base, 0) + __popc(votes & ((1u << lane) - 1u));
-                if (keep) {
-                    if (base < a.cand_cap) a.cand[base] = p;
-                    else atomicOr(&a.ctr->overflow, 1u);
-                }
-            }
-        }
-        __syncthreads();        // every staged entry has been read before the next tile overwrites the buffer
-        par ^= 1;
-    }
-}
-
-// exclusive scan of tile counts (one block); also publishes the total
-__global__ void __launch_bounds__(1024) k_scan_tiles(uint32_t* __restrict__ tile_counts, uint32_t n_tiles, uint32_t n_logs, Counters* ctr) {
-    __shared__ uint32_t warp_tot[32];
-    __shared__ uint32_t carry;
-    if (threadIdx.x == 0) carry = 0;
-    __syncthreads();
-    for (uint32_t base = 0; base < n_tiles; base += 1024) {
-        uint32_t i = base + threadIdx.x;
-        uint32_t v = i < n_tiles ? tile_counts[i] : 0;
-        uint32_t inc = v;
-        for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, inc, o); if ((threadIdx.x & 31) >= o) inc += t; }
-        if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = inc;
-        __syncthreads();
-        if (threadIdx.x < 32) {
-            uint32_t w = warp_tot[threadIdx.x];
-            uint32_t wi = w;
-            for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, wi, o); if (threadIdx.x >= o) wi += t; }
-            warp_tot[threadIdx.x] = wi - w;  // exclusive
-        }
-        __syncthreads();
-        uint32_t excl = carry + warp_tot[threadIdx.x >> 5] + inc - v;
-        if (i < n_tiles) tile_counts[i] = excl;
-        __syncthreads();
-        if (threadIdx.x == 1023) carry = excl + v;
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) { ctr->total_nl = carry; ctr->n_lines_total = carry + n_logs; }
-}
-
-// ------------------------------------------------------------------ K2: line offsets
-// Second pass over the log: every '\n' yields line_end[g] / line_start[g+1] (with the \r?\n rule and
-// the log boundaries of a batch), at the global line index given by the scanned tile counts. (The
-// kernel can also run the gram filter itself, `use_filter`; the pipeline does that in k_filter_count.)
-struct ScanArgs {
-    const uint8_t* text;
-    uint64_t len;
-    uint32_t n_tiles;
-    const uint32_t* tile_prefix;      // exclusive newline count before each tile
-    const uint64_t* log_off;          // [n_logs+1]
-    uint32_t n_logs;
-    uint32_t* line_start;             // [G]
-    uint32_t* line_end;               // [G]
-    uint32_t* first_line;             // [n_logs+1]
-    uint32_t line_cap;                // capacity of line_start / line_end (optimistic; overflow -> retry)
-    const uint32_t* bitmap;           // GRAM_WORDS words
-    unsigned long long* cand;         // candidates: (global line << 32) | byte position
-    uint32_t cand_cap;
-    Counters* ctr;
-    int use_filter;
-};
-
-// Line offsets: every '\n' at p ends line g (at p, or p-1 after a '\r') and starts line g+1 at p+1;
-// log boundaries of a batch act as line breaks. One thread owns 64 contiguous bytes, so a tile
-// needs a single block-wide prefix of the per-thread newline counts.
-constexpr uint32_t LN_SPAN = 64;                                   // bytes per thread
-constexpr uint32_t LN_TILE_THREADS = TILE_BYTES / LN_SPAN;         // 512 threads cover one 32 KiB tile
-__global__ void __launch_bounds__(LN_TILE_THREADS) k_lines(ScanArgs a) {
-    __shared__ uint32_t s_warp[LN_TILE_THREADS / 32];
-    __shared__ uint32_t s_k0, s_inner, s_events;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (uint32_t tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
-        const uint64_t tile_base = (uint64_t)tile * TILE_BYTES;
-        const uint64_t tile_end = tile_base + TILE_BYTES;
-        if (threadIdx.x == 0) {
-            uint32_t j0 = upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, tile_base);
-            s_k0 = j0 - 1;
-            s_inner = (j0 <= a.n_logs && a.log_off[j0] < tile_end) ? 1u : 0u;
-            uint32_t j1 = lower_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, tile_base);
-            s_events = (j1 <= a.n_logs && a.log_off[j1] < tile_end) ? 1u : 0u;
-        }
-        const uint64_t pos = tile_base + (uint64_t)threadIdx.x * LN_SPAN;
-        unsigned long long nl = 0;        // bit i: byte pos+i is '\n'
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-            const uint64_t cp = pos + 16 * q;
-            if (cp < a.len) {
-                const uint4 v = load16(a.text, cp, a.len);
-                const uint32_t f = zero_byte_flags(v.x ^ 0x0A0A0A0Au) | zero_byte_flags(v.y ^ 0x0A0A0A0Au) |
-                                   zero_byte_flags(v.z ^ 0x0A0A0A0Au) | zero_byte_flags(v.w ^ 0x0A0A0A0Au);
-                if (f) nl |= (unsigned long long)nl_mask16(v) << (16 * q);
-            }
-        }
-        const uint32_t cnt = __popcll(nl);
-        uint32_t inc = cnt;
-#pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += t; }
-        if (lane == 31) s_warp[warp] = inc;
-        __syncthreads();
-        uint32_t wbase = 0;
-#pragma unroll
-        for (int w = 0; w < LN_TILE_THREADS / 32; ++w) { const uint32_t t = s_warp[w]; if (w < warp) wbase += t; }
-        const uint32_t excl = a.tile_prefix[tile] + wbase + inc - cnt;     // newlines before this thread's bytes
-        const uint32_t k0 = s_k0;
-        const bool inner = s_inner != 0, events = s_events != 0;
-        unsigned long long m = nl;
-        while (m) {
-            const int i = __ffsll((long long)m) - 1;
-            m &= m - 1;
-            const uint64_t p = pos + i;
-            uint32_t k = k0;
-            if (inner) k = upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, p) - 1;
-            const uint32_t g = excl + __popcll(nl & ((1ull << i) - 1ull)) + k;
-            const bool cr = p > a.log_off[k] && a.text[p - 1] == '\r';
-            if (g + 1 < a.line_cap) {
-                a.line_end[g] = (uint32_t)(p - (cr ? 1 : 0));
-                a.line_start[g + 1] = (uint32_t)(p + 1);
-            } else atomicOr(&a.ctr->overflow, 64u);
-        }
-        if (events && pos <= a.len) {     // start of log j / end of log j-1 inside this thread's bytes
-            uint32_t j = lower_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, pos);
-            while (j <= a.n_logs && a.log_off[j] < pos + LN_SPAN) {
-                const uint64_t b = a.log_off[j];
-                const uint32_t nlb = excl + __popcll(nl & ((1ull << (uint32_t)(b - pos)) - 1ull));
-                a.first_line[j] = nlb + j;
-                if (nlb + j < a.line_cap) {
-                    if (j < a.n_logs) { a.line_start[nlb + j] = (uint32_t)b; }
-                    if (j > 0) a.line_end[nlb + j - 1] = (uint32_t)b;
-                } else atomicOr(&a.ctr->overflow, 64u);
-                ++j;
-            }
-        }
-        __syncthreads();
-    }
-}
-
-// Java's Pattern.split(…, 0) drops trailing empty strings; no separator at all keeps [input].
-__global__ void k_log_meta(const uint32_t* __restrict__ first_line, const uint32_t* __restrict__ line_start,
-                           const uint32_t* __restrict__ line_end, uint32_t n_logs, uint32_t line_cap, uint32_t no_trim,
-                           uint32_t* __restrict__ n_lines) {
-    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= n_logs) return;
-    const uint32_t f = first_line[k];
-    uint32_t n = first_line[k + 1] - f;
-    if (first_line[k + 1] > line_cap) { n_lines[k] = 0; return; }     // line arrays overflowed: the call is retried
-    if (n > 1 && !no_trim) {      // a line-range shard is cut from a log whose trailing empty lines are already gone
-        while (n > 0 && line_end[f + n - 1] == line_start[f + n - 1]) --n;
-    }
-    n_lines[k] = n;
-}
-
-// ------------------------------------------------------------------ DFA walker (same loop as lpx::Dfa::match)
-__device__ __forceinline__ long tail_terminator(const uint8_t* __restrict__ s, uint32_t ls, uint32_t le) {
-    const uint32_t n = le - ls;
-    if (n >= 1 && s[le - 1] == '\r') return (long)le - 1;
-    if (n >= 2 && s[le - 2] == 0xC2 && s[le - 1] == 0x85) return (long)le - 2;
-    if (n >= 3 && s[le - 3] == 0xE2 && s[le - 2] == 0x80 && (s[le - 1] == 0xA8 || s[le - 1] == 0xA9)) return (long)le - 3;
-    return -1;
-}
-// NG automata over one line. The line is consumed 8 bytes per (aligned) load with the eight
-// transitions unrolled; unaligned head/tail bytes are stepped one by one. `LOWFINAL` selects the
-// single-DFA convention (states 0/1 = DEAD/MATCH are final) or the product-DFA one (states >= ff).
-template <int NG, bool LOWFINAL>
-struct LineWalker {
-    const uint8_t* __restrict__ cm[NG];
-    const uint16_t* __restrict__ T[NG];
-    uint32_t nc[NG], ff[NG], st[NG];
-
-    __device__ __forceinline__ bool live(int q) const { return LOWFINAL ? st[q] > 1u : st[q] < ff[q]; }
-    __device__ __forceinline__ bool step(uint32_t b) {
-        bool any = false;
-#pragma unroll
-        for (int q = 0; q < NG; ++q)
-            if (live(q)) { st[q] = T[q][st[q] * nc[q] + cm[q][b]]; any = true; }
-        return any;
-    }
-    __device__ __forceinline__ void symbol(uint32_t col_from_end) {     // 2 = TPOS, 1 = EOT
-#pragma unroll
-        for (int q = 0; q < NG; ++q) if (live(q)) st[q] = T[q][st[q] * nc[q] + nc[q] - col_from_end];
-    }
-    // bytes [a, b) of text; returns false once every automaton is final. Aligned 8-byte words,
-    // one word prefetched ahead; partial first/last words are stepped byte by byte from registers.
-    __device__ __forceinline__ bool segment(const uint8_t* __restrict__ text, uint64_t len, uint32_t a, uint32_t b) {
-        if (a >= b) return true;
-        uint32_t base = a & ~7u;
-        unsigned long long cur = load8_any(text, base, len);
-        unsigned long long nxt = (base + 8 < b) ? load8_any(text, (uint64_t)base + 8, len) : 0ull;
-        uint32_t lo = a - base;
-        for (;;) {
-            const uint32_t hi = min(8u, b - base);
-            if constexpr (NG == 1) {
-                // one automaton: the eight class lookups do not depend on the state, so they are issued
-                // together and only the transition loads form a dependent chain
-                uint32_t cls[8];
-#pragma unroll
-                for (int k = 0; k < 8; ++k) cls[k] = cm[0][(uint32_t)(cur >> (8 * k)) & 0xFFu];
-#pragma unroll
-                for (int k = 0; k < 8; ++k)
-                    if ((uint32_t)k >= lo && (uint32_t)k < hi && live(0)) st[0] = T[0][st[0] * nc[0] + cls[k]];
-                if (!live(0)) return false;
-            } else if (lo == 0 && hi == 8) {
-                const uint32_t x = (uint32_t)cur, y = (uint32_t)(cur >> 32);
-                bool any = true;
-#pragma unroll
-                for (int k = 0; k < 4; ++k) any = step((x >> (8 * k)) & 0xFFu);
-#pragma unroll
-                for (int k = 0; k < 4; ++k) any = step((y >> (8 * k)) & 0xFFu);
-                if (!any) return false;
-            } else {
-                for (uint32_t k = lo; k < hi; ++k)
-                    if (!step((uint32_t)(cur >> (8 * k)) & 0xFFu)) return false;
-            }
-            base += 8;
-            if (base >= b) return true;
-            lo = 0;
-            cur = nxt;
-            nxt = (base + 8 < b) ? load8_any(text, (uint64_t)base + 8, len) : 0ull;
-        }
-    }
-    // bytes [a, b) of text from b-1 down to a (automaton of the reversed language); NG == 1 only
-    __device__ __forceinline__ bool segment_rev(const uint8_t* __restrict__ text, uint64_t len, uint32_t a, uint32_t b) {
-        if (a >= b) return true;
-        uint32_t base = (b - 1) & ~7u;
-        unsigned long long cur = load8_any(text, base, len);
-        unsigned long long prv = (base >= 8 && base > a) ? load8_any(text, (uint64_t)base - 8, len) : 0ull;
-        for (;;) {
-            const uint32_t hi = min(8u, b - base), lo = a > base ? a - base : 0u;
-            uint32_t cls[8];
-#pragma unroll
-            for (int k = 0; k < 8; ++k) cls[k] = cm[0][(uint32_t)(cur >> (8 * k)) & 0xFFu];
-#pragma unroll
-            for (int k = 7; k >= 0; --k)
-                if ((uint32_t)k >= lo && (uint32_t)k < hi && live(0)) st[0] = T[0][st[0] * nc[0] + cls[k]];
-            if (!live(0)) return false;
-            if (base <= a) return true;
-            base -= 8;
-            b = base + 8;
-            cur = prv;
-            prv = (base >= 8 && base > a) ? load8_any(text, (uint64_t)base - 8, len) : 0ull;
-        }
-    }
-    __device__ __forceinline__ void run(const uint8_t* __restrict__ text, uint64_t len, uint32_t ls, uint32_t le) {
-        if (le > ls) {
-            const long tpos = tail_terminator(text, ls, le);
-            if (tpos < 0) segment(text, len, ls, le);
-            else if (segment(text, len, ls, (uint32_t)tpos)) { symbol(2); segment(text, len, (uint32_t)tpos, le); }
-        }
-        symbol(1);
-    }
-};
-
-// One regex over one line (tables in global memory, L1/L2-cached).
-__device__ bool dfa_walk(const DevPlan& P, uint32_t r, const uint8_t* __restrict__ text, uint64_t len, uint32_t ls, uint32_t le) {
-    LineWalker<1, true> w;
-    w.nc[0] = P.rx_ncls[r];
-    w.T[0] = P.dfa_trans + P.rx_dfa_off[r];
-    w.cm[0] = P.rx_cmap + (size_t)r * 256;
-    w.ff[0] = 0;
-    w.st[0] = P.rx_start[r];
-    w.run(text, len, ls, le);
-    return w.st[0] == 1;
-}
-
-__device__ __forceinline__ void emit_record(Counters* ctr, unsigned long long* recs, uint32_t cap, uint32_t gb, bool hit, uint32_t r, uint32_t g) {
-    const unsigned mask = 0xffffffffu;   // callers keep all 32 lanes in the loop
-    const unsigned votes = __ballot_sync(mask, hit);
-    if (!votes) return;
-    const int lane = threadIdx.x & 31;
-    const int leader = __ffs(votes) - 1;
-    uint32_t base = 0;
-    if (lane == leader) base = atomicAdd(&ctr->n_recs, (unsigned)__popc(votes));
-    base = __shfl_sync(mask, base, leader);
-    if (hit) {
-        const uint32_t idx = base + __popc(votes & ((1u << lane) - 1u));
-        if (idx < cap) recs[idx] = ((unsigned long long)r << gb) | g;
-        else atomicOr(&ctr->overflow, 4u);
-    }
-}
-
-// Block-level staging of queue output: entries are collected in shared memory (shared-memory
-// atomics only) and published with one global atomic per flush, so no warp waits on a global atomic.
-constexpr uint32_t Q_STAGE = 2048;
-struct QStage {
-    unsigned long long buf[Q_STAGE];
-    uint32_t n, base;
-};
-__device__ __forceinline__ void stage_put(QStage& sg, Counters* ctr, unsigned int* gcount, unsigned long long* gbuf, uint32_t cap,
-                                          uint32_t overflow_bit, unsigned long long key) {
-    const uint32_t idx = atomicAdd(&sg.n, 1u);
-    if (idx < Q_STAGE) sg.buf[idx] = key;
-    else {      // staging full: straight to the global queue
-        const uint32_t gi = atomicAdd(gcount, 1u);
-        if (gi < cap) gbuf[gi] = key; else atomicOr(&ctr->overflow, overflow_bit);
-    }
-}
-// all threads of the block; `force` flushes whatever is staged, otherwise only a nearly full buffer
-__device__ __forceinline__ void stage_flush(QStage& sg, Counters* ctr, unsigned int* gcount, unsigned long long* gbuf, uint32_t cap,
-                                            uint32_t overflow_bit, bool force) {
-    __syncthreads();
-    const uint32_t staged = min(sg.n, Q_STAGE);
-    if (staged == 0 || (!force && staged < Q_STAGE - 2 * blockDim.x)) return;     // block-uniform
-    if (threadIdx.x == 0) sg.base = atomicAdd(gcount, staged);
-    __syncthreads();
-    const uint32_t base = sg.base;
-    for (uint32_t q = threadIdx.x; q < staged; q += blockDim.x) {
-        if (base + q < cap) gbuf[base + q] = sg.buf[q]; else atomicOr(&ctr->overflow, overflow_bit);
-    }
-    __syncthreads();
-    if (threadIdx.x == 0) sg.n = 0;
-    __syncthreads();
-}
-
-// ------------------------------------------------------------------ K3: confirm gram hits, resolve literal occurrences
-// Two kernels with a queue between them, so that the lanes of a warp do the same kind of work
-// (one thread per candidate doing everything serially ran with ~6 of 32 lanes active):
-//   k_confirm  thread per candidate: gram table probe, literal comparison in 4-byte words; every
-//              (occurrence, regex) pair becomes an item in the queue of its verification class
-//   k_resolve  thread per item, a block works on one class at a time: line lookup, then
-//              class 0 boundary test | 1 anchored automaton forwards | 2 backwards | 3 hand over to
-//              k_verify / k_verify_vm (walk of the whole line)
-constexpr int N_CLASSES = 4;
-constexpr uint32_t ITEM_STAGE = 1024;      // items staged per class and block
-struct ItemStage { unsigned long long buf[N_CLASSES][ITEM_STAGE]; uint32_t n[N_CLASSES], base[N_CLASSES]; };
-
-struct ConfirmArgs {
-    const uint8_t* text;
-    uint64_t len;
-    const uint32_t* cand;
-    uint32_t cand_cap;
-    unsigned long long* items;       // [N_CLASSES][item_cap]: s << 32 | literal length << 24 | entry of lit_rx_packed
-    uint32_t item_cap;
-    Counters* ctr;
-};
-__device__ __forceinline__ bool dev_word(uint32_t b) { return (b >= '0' && b <= '9') || (b >= 'A' && b <= 'Z') || b == '_' || (b >= 'a' && b <= 'z'); }
-// 4 bytes at any position p; bytes at or beyond len read as zero
-__device__ __forceinline__ uint32_t load4_unaligned(const uint8_t* __restrict__ text, uint32_t p, uint64_t len) {
-    const uint32_t b = p & ~3u;
-    if ((uint64_t)b + 8 <= len) {
-        const uint32_t lo = __ldg(reinterpret_cast<const uint32_t*>(text + b)), hi = __ldg(reinterpret_cast<const uint32_t*>(text + b + 4));
-        return __funnelshift_r(lo, hi, (p & 3u) * 8);
-    }
-    uint32_t w = 0;
-    for (int i = 0; i < 4; ++i) if ((uint64_t)p + i < len) w |= (uint32_t)text[p + i] << (8 * i);
-    return w;
-}
-// ASCII 'A'..'Z' -> lower case in all four bytes, everything else unchanged
-__device__ __forceinline__ uint32_t lower4(uint32_t t) {
-    const uint32_t y = t & 0x7F7F7F7Fu;
-    const uint32_t up = (y + 0x3F3F3F3Fu) & ~(y + 0x25252525u) & ~t & 0x80808080u;
-    return t | (up >> 2);
-}
-__global__ void __launch_bounds__(256) k_confirm(ConfirmArgs a, DevPlan P) {
-    __shared__ ItemStage sg;
-    if (threadIdx.x < N_CLASSES) sg.n[threadIdx.x] = 0;
-    __syncthreads();
-    const uint32_t n = min(a.ctr->n_cand, a.cand_cap);
-    const uint32_t stride = gridDim.x * blockDim.x;
-    const uint32_t tmask = (1u << P.table_bits) - 1u;
-    for (uint32_t c = blockIdx.x * blockDim.x + threadIdx.x; c < n; c += stride) {
-        const uint32_t pos = a.cand[c];
-        const uint32_t w = load4_unaligned(a.text, pos, a.len);
-        const uint32_t f = w | 0x20202020u;
-        uint32_t slot = (f * GRAM_MUL2) >> (32 - P.table_bits);
-        uint4 gs;
-        while ((gs = __ldg(&P.gram_slots[slot])).x != 0 && gs.x != f) slot = (slot + 1) & tmask;
-        for (uint32_t q = 0; q < gs.z; ++q) {       // gs.z == 0 on an empty slot
-            const uint4 ld = __ldg(&P.lit_desc[gs.y + q]);
-            const uint32_t ll = ld.y & 0xFFu, go = (ld.y >> 8) & 0xFFu;
-            if (pos < go) continue;
-            const uint32_t s = pos - go;
-            if ((uint64_t)s + ll > a.len) continue;
-            const uint32_t* __restrict__ lit = reinterpret_cast<const uint32_t*>(P.lit_bytes8 + ld.x);
-            const bool icase = (ld.y >> 16) & 1u;
-            bool ok = true;
-            for (uint32_t j = 0; j < ll && ok; j += 4) {
-                uint32_t t = (j == go) ? w : load4_unaligned(a.text, s + j, a.len);
-                if (icase) t = lower4(t);
-                const uint32_t rem = ll - j;
-                const uint32_t mask = rem >= 4 ? 0xFFFFFFFFu : (1u << (8 * rem)) - 1u;
-                ok = ((t ^ __ldg(lit + (j >> 2))) & mask) == 0;
-            }
-            if (!ok) continue;
-            for (uint32_t j = ld.z; j < ld.z + ld.w; ++j) {
-                const uint32_t mode = __ldg(&P.lit_rx_packed[j]) >> 24;
-                const uint32_t cls = (mode & 1u) ? 0u : (mode & 8u) ? 1u : (mode & 16u) ? 2u : 3u;
-                const unsigned long long item = ((unsigned long long)s << 32) | ((unsigned long long)ll << 24) | j;
-                const uint32_t idx = atomicAdd(&sg.n[cls], 1u);
-                if (idx < ITEM_STAGE) sg.buf[cls][idx] = item;
-                else {      // staging full: straight to the global queue
-                    const uint32_t gi = atomicAdd(&a.ctr->n_items[cls], 1u);
-                    if (gi < a.item_cap) a.items[(size_t)cls * a.item_cap + gi] = item; else atomicOr(&a.ctr->overflow, 128u);
-                }
-            }
-        }
-    }
-    __syncthreads();
-    if (threadIdx.x < N_CLASSES) {
-        const uint32_t staged = min(sg.n[threadIdx.x], ITEM_STAGE);
-        sg.base[threadIdx.x] = staged ? atomicAdd(&a.ctr->n_items[threadIdx.x], staged) : 0u;
-    }
-    __syncthreads();
-    for (int cls = 0; cls < N_CLASSES; ++cls) {
-        const uint32_t staged = min(sg.n[cls], ITEM_STAGE), base = sg.base[cls];
-        for (uint32_t q = threadIdx.x; q < staged; q += blockDim.x) {
-            if (base + q < a.item_cap) a.items[(size_t)cls * a.item_cap + base + q] = sg.buf[cls][q];
-            else atomicOr(&a.ctr->overflow, 128u);
-        }
-    }
-}
-
-struct ResolveArgs {
-    const uint8_t* text;
-    uint64_t len;
-    const unsigned long long* items;
-    uint32_t item_cap;
-    const uint32_t* tile_prefix;     // exclusive newline count before each 32 KiB tile
-    uint32_t n_tiles;
-    const uint64_t* log_off;
-    uint32_t n_logs;
-    const uint32_t* line_start;
-    const uint32_t* line_end;
-    uint32_t n_lines_total;
-    unsigned long long* tasks;
-    uint32_t task_cap;
-    unsigned long long* vm_tasks;
-    uint32_t vm_task_cap;
-    unsigned long long* recs;
-    uint32_t rec_cap;
-    Counters* ctr;
-};
-constexpr uint32_t ANCHOR_BUDGET = 24;     // automaton steps an item may spend here before it is handed to k_verify
-__global__ void __launch_bounds__(256) k_resolve(ResolveArgs a, DevPlan P) {
-    __shared__ QStage s_rec, s_task;
-    if (threadIdx.x == 0) { s_rec.n = 0; s_task.n = 0; }
-    __syncthreads();
-    const uint32_t n0 = min(a.ctr->n_items[0], a.item_cap), n1 = min(a.ctr->n_items[1], a.item_cap),
-                   n2 = min(a.ctr->n_items[2], a.item_cap), n3 = min(a.ctr->n_items[3], a.item_cap);
-    const uint32_t c1 = (n0 + blockDim.x - 1) / blockDim.x, c2 = c1 + (n1 + blockDim.x - 1) / blockDim.x,
-                   c3 = c2 + (n2 + blockDim.x - 1) / blockDim.x, c4 = c3 + (n3 + blockDim.x - 1) / blockDim.x;
-    const uint32_t gmax = min(a.ctr->n_lines_total, a.n_lines_total);
-    for (uint32_t ch = blockIdx.x; ch < c4; ch += gridDim.x) {
-        // a chunk of 256 items never straddles two classes: the block does one kind of work at a time
-        const uint32_t cls = ch >= c3 ? 3u : ch >= c2 ? 2u : ch >= c1 ? 1u : 0u;
-        const uint32_t first = cls == 3 ? c3 : cls == 2 ? c2 : cls == 1 ? c1 : 0u;
-        const uint32_t count = cls == 3 ? n3 : cls == 2 ? n2 : cls == 1 ? n1 : n0;
-        const uint32_t idx = (ch - first) * blockDim.x + threadIdx.x;
-        if (idx < count) do {
-            const unsigned long long item = a.items[(size_t)cls * a.item_cap + idx];
-            const uint32_t s = (uint32_t)(item >> 32), ll = (uint32_t)(item >> 24) & 0xFFu, e2 = s + ll;
-            const uint32_t packed = __ldg(&P.lit_rx_packed[(uint32_t)item & 0xFFFFFFu]);
-            const uint32_t r = packed & 0xFFFFFFu, mode = packed >> 24;
-            // line of the occurrence: the newline prefix of its tile (and its neighbour) brackets the index
-            const uint32_t t = s / TILE_BYTES;
-            uint32_t glo = a.tile_prefix[t], ghi = (t + 1 < a.n_tiles ? a.tile_prefix[t + 1] : a.ctr->n_lines_total) + 1;
-            if (a.n_logs > 1) {
-                glo += upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, (uint64_t)t * TILE_BYTES) - 1;
-                ghi += upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, (uint64_t)(t + 1) * TILE_BYTES);
-            }
-            ghi = min(ghi, gmax);
-            if (glo >= ghi) break;                    // beyond the (under-estimated) line arrays: the call is re-run
-            const uint32_t g = glo + upper_bound_dev<uint32_t>(a.line_start + glo, ghi - glo, s) - 1;
-            if (g >= gmax || g + 1 == glo) break;
-            const uint32_t ls = a.line_start[g], le = a.line_end[g];
-            if (e2 > le) break;                       // the occurrence runs into the line separator
-            const unsigned long long rec = ((unsigned long long)r << P.gb) | g;
-            if (cls == 0) {
-                // literal-with-boundaries pattern (mode bits 2/4: \b required left/right; 32/64: the literal's
-                // first/last byte is a word byte)
-                bool hit = true;
-                if (mode & 2u) hit = (s > ls && dev_word(a.text[s - 1])) != ((mode & 32u) != 0);
-                if (hit && (mode & 4u)) hit = ((mode & 64u) != 0) != (e2 < le && dev_word(a.text[e2]));
-                if (hit) stage_put(s_rec, a.ctr, &a.ctr->n_recs, a.recs, a.rec_cap, 4u, rec);
-            } else if (cls == 3) {
-                if (P.rx_kind[r] == 0) stage_put(s_task, a.ctr, &a.ctr->n_tasks, a.tasks, a.task_cap, 2u, ((unsigned long long)r << 32) | g);
-                else {
-                    const uint32_t vi = atomicAdd(&a.ctr->n_vm_tasks, 1u);
-                    if (vi < a.vm_task_cap) a.vm_tasks[vi] = ((unsigned long long)r << 32) | g;
-                    else atomicOr(&a.ctr->overflow, 32u);
-                }
-            } else {
-                // every match starts (class 1) / ends (class 2) with this literal: anchored automaton from the
-                // occurrence. Walks die or match within a few bytes; one that is still undecided after
-                // ANCHOR_BUDGET steps (".*" tails) goes to k_verify's walk of the whole line.
-                const uint4 ad = __ldg(&P.anchor_desc[r]);
-                const uint32_t nc = ad.y;
-                const uint16_t* __restrict__ T = P.dfa_trans + ad.x;
-                const uint8_t* __restrict__ cm = P.rx_acmap + (size_t)r * 256;
-                LineWalker<1, true> w;
-                w.nc[0] = nc; w.T[0] = T; w.cm[0] = cm; w.ff[0] = 0;
-                if (cls == 1) {
-                    w.st[0] = s == ls ? (ad.z & 0xFFFFu) : dev_word(a.text[s - 1]) ? ad.w : (ad.z >> 16);
-                    const uint32_t stop = min(le, s + ANCHOR_BUDGET);
-                    const long tpos = tail_terminator(a.text, ls, le);
-                    if (tpos < 0 || (long)s > tpos || (long)stop <= tpos) w.segment(a.text, a.len, s, stop);
-                    else if (w.segment(a.text, a.len, s, (uint32_t)tpos)) { w.symbol(2); w.segment(a.text, a.len, (uint32_t)tpos, stop); }
-                    if (stop == le) w.symbol(1);
-                } else {
-                    w.st[0] = e2 == le ? (ad.z & 0xFFFFu) : dev_word(a.text[e2]) ? ad.w : (ad.z >> 16);
-                    const uint32_t stop = e2 - ls > ANCHOR_BUDGET ? e2 - ANCHOR_BUDGET : ls;
-                    w.segment_rev(a.text, a.len, stop, e2);
-                    if (stop == ls) w.symbol(1);
-                }
-                const uint32_t st = w.st[0];
-                if (st == 1u) stage_put(s_rec, a.ctr, &a.ctr->n_recs, a.recs, a.rec_cap, 4u, rec);
-                else if (st > 1u) stage_put(s_task, a.ctr, &a.ctr->n_tasks, a.tasks, a.task_cap, 2u, ((unsigned long long)r << 32) | g);
-            }
-        } while (false);
-        // no barrier per chunk: a block handles a few chunks and its output fits the staging buffers
-        // (entries beyond them go straight to the global queues)
-    }
-    stage_flush(s_rec, a.ctr, &a.ctr->n_recs, a.recs, a.rec_cap, 4u, true);
-    stage_flush(s_task, a.ctr, &a.ctr->n_tasks, a.tasks, a.task_cap, 2u, true);
-}
-
-// ------------------------------------------------------------------ K4: verify tasks
-struct VerifyArgs {
-    const uint8_t* text;
-    uint64_t len;
-    const uint32_t* line_start;
-    const uint32_t* line_end;
-    const unsigned long long* tasks;
-    uint32_t task_cap;
-    unsigned long long* recs;
-    uint32_t rec_cap;
-    Counters* ctr;
-    // always-candidates pass
-    uint32_t n_lines_total;
-    const uint32_t* first_line;
-    const uint32_t* n_lines;
-    uint32_t n_logs;
-    // backtracking verifier
-    const unsigned long long* vm_tasks;
-    uint32_t vm_task_cap;
-    uint32_t* vm_stack;               // VM_STACK_WORDS words per thread of the VM grid
-};
-__global__ void __launch_bounds__(256) k_verify(VerifyArgs a, DevPlan P) {
-    __shared__ QStage sg;
-    if (threadIdx.x == 0) sg.n = 0;
-    __syncthreads();
-    const uint32_t n = min(a.ctr->n_tasks, a.task_cap);
-    const uint32_t stride = gridDim.x * blockDim.x;
-    const uint32_t rounds = (n + stride - 1) / stride;
-    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    for (uint32_t it = 0; it < rounds; ++it, t += stride) {
-        if (t < n) {
-            const unsigned long long task = a.tasks[t];
-            const uint32_t r = (uint32_t)(task >> 32), g = (uint32_t)task;
-            if (P.rx_kind[r] == 0 && dfa_walk(P, r, a.text, a.len, a.line_start[g], a.line_end[g]))
-                stage_put(sg, a.ctr, &a.ctr->n_recs, a.recs, a.rec_cap, 4u, ((unsigned long long)r << P.gb) | g);
-        }
-        stage_flush(sg, a.ctr, &a.ctr->n_recs, a.recs, a.rec_cap, 4u, false);
-    }
-    stage_flush(sg, a.ctr, &a.ctr->n_recs, a.recs, a.rec_cap, 4u, true);
-}
-// regexes without a usable literal: every (untrimmed) line is a candidate
-__global__ void __launch_bounds__(256) k_verify_always(VerifyArgs a, DevPlan P) {
-    a.n_lines_total = min(a.ctr->n_lines_total, a.n_lines_total);     // host passes the capacity
-    const uint32_t stride = gridDim.x * blockDim.x;
-    const uint32_t rounds = (a.n_lines_total + stride - 1) / stride;
-    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
-    for (uint32_t it = 0; it < rounds; ++it, g += stride) {
-        bool live = g < a.n_lines_total;
-        uint32_t ls = 0, le = 0;
-        if (live) {
-            uint32_t k = a.n_logs == 1 ? 0 : upper_bound_dev<uint32_t>(a.first_line, a.n_logs + 1, g) - 1;
-            live = k < a.n_logs && g - a.first_line[k] < a.n_lines[k];
-            if (live) { ls = a.line_start[g]; le = a.line_end[g]; }
-        }
-        for (uint32_t q = 0; q < P.n_always; ++q) {
-            const uint32_t r = P.always_list[q];
-            bool hit = false;
-            if (live && P.rx_kind[r] == 0) hit = dfa_walk(P, r, a.text, a.len, ls, le);
-            emit_record(a.ctr, a.recs, a.rec_cap, P.gb, hit, r, g);
-        }
-    }
-}
-
-// backtracking verifier: look-around, back-references, possessive/atomic, MULTILINE anchors, DFA blow-ups
-__device__ __forceinline__ bool vm_eval(const DevPlan& P, uint32_t r, const uint8_t* __restrict__ text, uint32_t ls, uint32_t le,
-                                        uint32_t* stack, Counters* ctr) {
-    lpx::VmView v;
-    v.code = reinterpret_cast<const lpx::VmCode*>(P.vm_code) + P.rx_vm_off[r];
-    v.set_off = P.vm_set_off + P.rx_vm_set_base[r];
-    v.set_data = P.vm_set_ranges;
-    v.n_slots = P.rx_vm_slots[r];
-    v.first = P.rx_vm_first + (size_t)r * 8;
-    const int res = lpx::vm_find(v, text, ls, le, stack, lpx::VM_STACK_WORDS, lpx::VM_MAX_STEPS);
-    if (res < 0) atomicOr(&ctr->overflow, 16u);
-    return res > 0;
-}
-// LP_OPT_SPANS: Matcher.start()/end() of the first find() of each event's primary regex on its line.
-__global__ void __launch_bounds__(128) k_spans(const unsigned long long* __restrict__ ev_key, const Counters* ctr, uint32_t m_cap, DevPlan P,
-                                               const uint8_t* __restrict__ text, const uint32_t* __restrict__ line_start,
-                                               const uint32_t* __restrict__ line_end, uint32_t* __restrict__ vm_stack, Counters* ctr_w,
-                                               uint32_t* __restrict__ span_start, uint32_t* __restrict__ span_end) {
-    const uint32_t m = min(ctr->n_events, m_cap);
-    const uint32_t stride = gridDim.x * blockDim.x;
-    uint32_t* stack = vm_stack + (size_t)(blockIdx.x * blockDim.x + threadIdx.x) * lpx::VM_STACK_WORDS;
-    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < m; e += stride) {
-        const unsigned long long k = ev_key[e];
-        const uint32_t g = (uint32_t)(k >> P.pb), p = (uint32_t)(k & ((1ull << P.pb) - 1ull));
-        const uint32_t r = P.pat_primary[p], ls = line_start[g], le = line_end[g];
-        lpx::VmView v;
-        v.code = reinterpret_cast<const lpx::VmCode*>(P.vm_code) + P.rx_vm_off[r];
-        v.set_off = P.vm_set_off + P.rx_vm_set_base[r];
-        v.set_data = P.vm_set_ranges;
-        v.n_slots = P.rx_vm_slots[r];
-        v.first = P.rx_vm_first + (size_t)r * 8;
-        uint32_t span[2] = {ls, ls};
-        const int res = lpx::vm_find(v, text, ls, le, stack, lpx::VM_STACK_WORDS, lpx::VM_MAX_STEPS, span);
-        if (res < 0) atomicOr(&ctr_w->overflow, 16u);
-        span_start[e] = res > 0 ? span[0] - ls : 0xFFFFFFFFu;     // the automaton said the line matches; a miss here would be a bug
-        span_end[e] = res > 0 ? span[1] - ls : 0xFFFFFFFFu;
-    }
-}
-__global__ void __launch_bounds__(128) k_verify_vm(VerifyArgs a, DevPlan P) {
-    const uint32_t n = min(a.ctr->n_vm_tasks, a.vm_task_cap);
-    const uint32_t stride = gridDim.x * blockDim.x;
-    const uint32_t rounds = (n + stride - 1) / stride;
-    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t* stack = a.vm_stack + (size_t)t * lpx::VM_STACK_WORDS;
-    for (uint32_t it = 0; it < rounds; ++it, t += stride) {
-        bool hit = false;
-        uint32_t r = 0, g = 0;
-        if (t < n) {
-            const unsigned long long task = a.vm_tasks[t];
-            r = (uint32_t)(task >> 32);
-            g = (uint32_t)task;
-            hit = vm_eval(P, r, a.text, a.line_start[g], a.line_end[g], stack, a.ctr);
-        }
-        emit_record(a.ctr, a.recs, a.rec_cap, P.gb, hit, r, g);
-    }
-}
-__global__ void __launch_bounds__(128) k_verify_vm_always(VerifyArgs a, DevPlan P) {
-    a.n_lines_total = min(a.ctr->n_lines_total, a.n_lines_total);
-    const uint32_t stride = gridDim.x * blockDim.x;
-    const uint32_t rounds = (a.n_lines_total + stride - 1) / stride;
-    uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t* stack = a.vm_stack + (size_t)g * lpx::VM_STACK_WORDS;
-    for (uint32_t it = 0; it < rounds; ++it, g += stride) {
-        bool live = g < a.n_lines_total;
-        uint32_t ls = 0, le = 0;
-        if (live) {
-            uint32_t k = a.n_logs == 1 ? 0 : upper_bound_dev<uint32_t>(a.first_line, a.n_logs + 1, g) - 1;
-            live = k < a.n_logs && g - a.first_line[k] < a.n_lines[k];
-            if (live) { ls = a.line_start[g]; le = a.line_end[g]; }
-        }
-        for (uint32_t q = 0; q < P.n_always_vm; ++q) {
-            const uint32_t r = P.always_vm_list[q];
-            const bool hit = live && vm_eval(P, r, a.text, ls, le, stack, a.ctr);
-            emit_record(a.ctr, a.recs, a.rec_cap, P.gb, hit, r, g);
-        }
-    }
-}
-
-
-// ------------------------------------------------------------------ always-on DFA scan
-// The multi-pattern DFA scan proper: every line is walked once through up to DS_MAXG product
-// automata (context regexes of CAS:27-34 + every DFA pattern without a usable literal, AS:93-95).
-// Transition tables, class maps and result masks are resident in shared memory for the life of the
-// CTA. One thread walks one line; it streams the line through registers with 16-byte loads, one
-// chunk prefetched ahead. (A TMA-staged shared-memory tile variant was measured first: with ~240
-// lines per 32 KiB tile the per-tile barrier left most threads idle — profiles/r01_v2_*.)
-constexpr uint32_t DS_THREADS = 256, DS_MAXG = 4;
-
-struct DfaScanArgs {
-    const uint8_t* text;
-    uint64_t len;
-    const uint32_t* line_start;
-    const uint32_t* line_end;
-    uint32_t n_lines_total;
-    const uint32_t* first_line;
-    const uint32_t* n_lines;
-    uint32_t n_logs;
-    const uint32_t* blob[DS_MAXG];
-    uint32_t blob_words[DS_MAXG];
-    uint32_t n_groups;
-    const uint8_t* rx_record;
-    uint8_t* ctx_flags;          // written for every line when write_flags
-    int write_flags;
-    unsigned long long* recs;
-    uint32_t rec_cap;
-    uint32_t gb;
-    Counters* ctr;
-};
-
-template <int NG>
-__global__ void __launch_bounds__(DS_THREADS) k_dfa_scan(DfaScanArgs a) {
-    extern __shared__ __align__(16) uint32_t ds_tabs[];
-    __shared__ uint32_t s_goff[DS_MAXG], s_recmask[DS_MAXG];
-    __shared__ int s_ctxbit[DS_MAXG][4];
-    {
-        uint32_t off = 0;
-        for (int g = 0; g < NG; ++g) {
-            for (uint32_t i = threadIdx.x; i < a.blob_words[g]; i += DS_THREADS) ds_tabs[off + i] = __ldg(a.blob[g] + i);
-            if (threadIdx.x == 0) s_goff[g] = off;
-            off += (a.blob_words[g] + 3u) & ~3u;
-        }
-    }
-    __syncthreads();
-    if (threadIdx.x < NG) {
-        const uint32_t* h = ds_tabs + s_goff[threadIdx.x];
-        uint32_t rm = 0;
-        int cb[4] = {-1, -1, -1, -1};
-        for (uint32_t k = 0; k < h[4]; ++k) {
-            const uint32_t r = h[5 + k];
-            if (a.rx_record[r]) rm |= 1u << k;
-            if (r < 4) cb[r] = (int)k;
-        }
-        s_recmask[threadIdx.x] = rm;
-        for (int c = 0; c < 4; ++c) s_ctxbit[threadIdx.x][c] = cb[c];
-    }
-    __syncthreads();
-
-    const uint8_t* cm[NG];
-    const uint16_t* T[NG];
-    const uint32_t* smask[NG];
-    uint32_t nc[NG], ff[NG], st0[NG];
-#pragma unroll
-    for (int g = 0; g < NG; ++g) {
-        const uint32_t* h = ds_tabs + s_goff[g];
-        nc[g] = h[1]; st0[g] = h[2]; ff[g] = h[3];
-        cm[g] = reinterpret_cast<const uint8_t*>(h + 37);
-        smask[g] = h + 101;
-        T[g] = reinterpret_cast<const uint16_t*>(h + 101 + h[0]);
-    }
-
-    const uint32_t stride = gridDim.x * DS_THREADS;
-    const uint32_t n_total = min(a.ctr->n_lines_total, a.n_lines_total);     // host passes the capacity
-    for (uint32_t g = blockIdx.x * DS_THREADS + threadIdx.x; g < n_total; g += stride) {
-        const uint32_t k = a.n_logs == 1 ? 0 : upper_bound_dev<uint32_t>(a.first_line, a.n_logs + 1, g) - 1;
-        const bool live = k < a.n_logs && g - a.first_line[k] < a.n_lines[k];
-        uint32_t flags = 0;
-        if (live) {
-            const uint32_t ls = a.line_start[g], le = a.line_end[g];
-            LineWalker<NG, false> w;
-#pragma unroll
-            for (int q = 0; q < NG; ++q) { w.cm[q] = cm[q]; w.T[q] = T[q]; w.nc[q] = nc[q]; w.ff[q] = ff[q]; w.st[q] = st0[q]; }
-            w.run(a.text, a.len, ls, le);
-#pragma unroll
-            for (int q = 0; q < NG; ++q) {
-                const uint32_t mask = smask[q][w.st[q]];
-#pragma unroll
-                for (int c = 0; c < 4; ++c) { const int bit = s_ctxbit[q][c]; if (bit >= 0) flags |= ((mask >> bit) & 1u) << c; }
-                uint32_t pend = mask & s_recmask[q];
-                const uint32_t* rxs = ds_tabs + s_goff[q] + 5;
-                while (pend) {        // records of literal-free user patterns are sparse: one atomic each
-                    const uint32_t r = rxs[__ffs(pend) - 1];
-                    pend &= pend - 1;
-                    const uint32_t idx = atomicAdd(&a.ctr->n_recs, 1u);
-                    if (idx < a.rec_cap) a.recs[idx] = ((unsigned long long)r << a.gb) | g;
-                    else atomicOr(&a.ctr->overflow, 4u);
-                }
-            }
-        }
-        if (a.write_flags) a.ctx_flags[g] = (uint8_t)flags;
-    }
-}
-
-// ------------------------------------------------------------------ record post-processing
-__global__ void k_rx_bounds(const unsigned long long* __restrict__ keys, const Counters* ctr, uint32_t n_rx, uint32_t gb, uint32_t* __restrict__ rx_begin) {
-    uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
-    if (r > n_rx) return;
-    const uint32_t n = ctr->n_unique;
-    rx_begin[r] = lower_bound_dev<unsigned long long>(keys, n, (unsigned long long)r << gb);
-}
-__global__ void k_ctx_flags(const unsigned long long* __restrict__ keys, const uint32_t* __restrict__ rx_begin, uint32_t gb, uint32_t* __restrict__ flags32) {
-    const uint32_t n = rx_begin[4];
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const unsigned long long k = keys[i];
-        const uint32_t r = (uint32_t)(k >> gb), g = (uint32_t)(k & ((1ull << gb) - 1ull));
-        atomicOr(&flags32[g >> 2], (1u << r) << ((g & 3) * 8));
-    }
-}
-// Events are emitted for lines [core_lo, G - halo_after): the whole text unless it is a line-range
-// shard, whose halo lines only feed the windows of its own lines.
-__global__ void k_emit_events(const unsigned long long* __restrict__ keys, DevPlan P,
-                              unsigned long long* __restrict__ ev_key, uint32_t ev_cap, Counters* ctr, uint32_t core_lo, uint32_t halo_after) {
-    const uint32_t n = ctr->n_unique;
-    const uint32_t core_hi = ctr->n_lines_total > halo_after ? ctr->n_lines_total - halo_after : 0;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const unsigned long long k = keys[i];
-        const uint32_t r = (uint32_t)min(k >> P.gb, 0xFFFFFFFFull), g = (uint32_t)(k & ((1ull << P.gb) - 1ull));
-        if (r >= P.n_rx) continue;     // padding sentinel
-        if (g < core_lo || g >= core_hi) continue;
-        const uint32_t pb = P.rxp_begin[r], pe = P.rxp_begin[r + 1];
-        if (pb == pe) continue;
-        const uint32_t base = atomicAdd(&ctr->n_events, pe - pb);
-        for (uint32_t j = pb; j < pe; ++j) {
-            const uint32_t idx = base + (j - pb);
-            if (idx < ev_cap) ev_key[idx] = ((unsigned long long)g << P.pb) | P.rxp_pat[j];
-            else atomicOr(&ctr->overflow, 8u);
-        }
-    }
-}
-__global__ void k_event_prep(const unsigned long long* __restrict__ ev_key, const Counters* ctr, uint32_t m_cap, DevPlan P,
-                             const uint32_t* __restrict__ first_line, uint32_t n_logs, uint32_t n_slots,
-                             uint32_t* __restrict__ ev_log, uint32_t* __restrict__ slot_key, uint32_t* __restrict__ ev_idx,
-                             unsigned long long* __restrict__ freq_delta) {
-    uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= m_cap) return;
-    if (e >= ctr->n_events) { ev_log[e] = n_logs; slot_key[e] = n_slots; ev_idx[e] = e; return; }   // padding
-    const unsigned long long k = ev_key[e];
-    const uint32_t g = (uint32_t)(k >> P.pb), p = (uint32_t)(k & ((1ull << P.pb) - 1ull));
-    ev_log[e] = n_logs == 1 ? 0 : upper_bound_dev<uint32_t>(first_line, n_logs + 1, g) - 1;
-    slot_key[e] = P.pat_slot[p] < 0 ? n_slots : (uint32_t)P.pat_slot[p];     // untracked patterns sort after every slot
-    ev_idx[e] = e;
-    atomicAdd(&freq_delta[p], 1ull);
-}
-__global__ void k_log_event_begin(const unsigned long long* __restrict__ ev_key, const Counters* ctr, const uint32_t* __restrict__ first_line,
-                                  uint32_t n_logs, uint32_t pb, unsigned long long* __restrict__ begin) {
-    uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;
-    if (k > n_logs) return;
-    const uint32_t m = ctr->n_events;
-    begin[k] = lower_bound_dev<unsigned long long>(ev_key, m, (unsigned long long)first_line[k] << pb);
-}
-
-// ------------------------------------------------------------------ K5: scoring (fp64, no contraction)
-struct ScoreArgs {
-    const unsigned long long* ev_key;
-    uint32_t m_cap;                        // threads launched; the live count comes from ctr->n_events
-    const Counters* ctr;
-    const uint32_t* ev_log;
-    const uint32_t* rank_in_slot;
-    const unsigned long long* prior;      // [n_pat] in-window counts at call start (+ lower ranks), may be null
-    const uint32_t* first_line;
-    const uint32_t* n_lines;
-    const unsigned long long* keys;       // unique (regex, line) records
-    const uint32_t* rx_begin;
-    const uint8_t* ctx_flags;
-    uint32_t* out_line;
-    uint32_t* out_pat;
-    double* out_score;
-    double* out_factors;                  // may be null
-    unsigned long long* sort_key;         // descending-score key for ranking
-    // line-range shard (n_global != 0): position of text line 0 in the whole log, the whole log's line
-    // count, the first own line, and the per-sequence chain thresholds composed over all shards
-    long long line_base;
-    long long n_global;
-    uint32_t core_lo;
-    const long long* seq_T;
-};
-
-__device__ __forceinline__ bool list_any_in(const unsigned long long* __restrict__ keys, uint32_t b, uint32_t e, uint32_t r, uint32_t gb,
-                                            uint32_t lo, uint32_t hi /* [lo,hi) global lines */) {
-    if (lo >= hi) return false;
-    const uint32_t i = b + lower_bound_dev<unsigned long long>(keys + b, e - b, ((unsigned long long)r << gb) | lo);
-    return i < e && (uint32_t)(keys[i] & ((1ull << gb) - 1ull)) < hi;
-}
-
-__global__ void __launch_bounds__(128) k_score(ScoreArgs a, DevPlan P, ScoreCfg C) {
-    const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= a.m_cap) return;
-    if (e >= a.ctr->n_events) { a.sort_key[e] = ~0ull; return; }      // padding sorts last
-    const unsigned long long ek = a.ev_key[e];
-    const uint32_t g = (uint32_t)(ek >> P.pb), p = (uint32_t)(ek & ((1ull << P.pb) - 1ull));
-    const unsigned long long gmask = (1ull << P.gb) - 1ull;
-    const uint32_t k = a.ev_log[e];
-    const uint32_t first = a.first_line[k];
-    const long long N = a.n_lines[k];
-    const long long i = (long long)g - first;
-
-    const double base = P.pat_conf[p];
-    const double sev = P.pat_sev[p];
-
-    // chronological factor, SS:123-151
-    const double pos = a.n_global ? __ddiv_rn((double)(i + a.line_base), (double)a.n_global) : __ddiv_rn((double)i, (double)N);
-    double chrono;
-    if (pos <= C.early) {
-        const double range = __dsub_rn(C.max_early, 1.5);
-        chrono = __dadd_rn(1.5, __dmul_rn(__dsub_rn(C.early, pos), __ddiv_rn(range, C.early)));
-    } else if (pos <= C.penalty) {
-        const double mid = __dsub_rn(C.penalty, C.early);
-        chrono = __dadd_rn(1.0, __dmul_rn(__dsub_rn(C.penalty, pos), __ddiv_rn(0.5, mid)));
-    } else {
-        chrono = __dadd_rn(0.5, __dsub_rn(1.0, pos));
-    }
-
-    // proximity factor, SS:161-190 + 315-347: closest hit of each secondary inside its window
-    double prox = 1.0;
-    {
-        const uint32_t sb = P.sec_begin[p], se = P.sec_begin[p + 1];
-        if (sb != se) {
-            double total = 0.0;
-            for (uint32_t s = sb; s < se; ++s) {
-                const long long win = min((long long)C.max_window, (long long)P.sec_window[s]);
-                const long long lo = max(0ll, i - win), hi = min(N, i + win + 1);   // local [lo,hi)
-                if (lo >= hi) continue;
-                const uint32_t r = P.sec_rx[s];
-                const uint32_t b = a.rx_begin[r], en = a.rx_begin[r + 1];
-                const unsigned long long* kk = a.keys + b;
-                const uint32_t cnt = en - b;
-                const unsigned long long self = ((unsigned long long)r << P.gb) | g;
-                const uint32_t at = lower_bound_dev<unsigned long long>(kk, cnt, self);
-                long long best = -1;
-                if (at > 0) {
-                    const long long l = (long long)(uint32_t)(kk[at - 1] & gmask) - first;
-                    if (l >= lo) best = i - l;
-                }
-                uint32_t nx = at;
-                if (nx < cnt && kk[nx] == self) ++nx;
-                if (nx < cnt) {
-                    const long long l = (long long)(uint32_t)(kk[nx] & gmask) - first;
-                    if (l < hi) { const long long d = l - i; if (best < 0 || d < best) best = d; }
-                }
-                if (best >= 0) total = __dadd_rn(total, __dmul_rn(P.sec_weight[s], C.decay_lut[best]));
-            }
-            prox = __dadd_rn(1.0, total);
-        }
-    }
-
-    // temporal factor, SS:199-305 (backward greedy walk == forward threshold)
-    double temporal = 1.0;
-    {
-        const uint32_t qb = P.seq_begin[p], qe = P.seq_begin[p + 1];
-        if (qb != qe) {
-            double total = 0.0;
-            for (uint32_t q = qb; q < qe; ++q) {
-                const uint32_t eb = P.seq_ev_begin[q], ee = P.seq_ev_begin[q + 1];
-                if (eb == ee) continue;                                  // SS:233-235
-                const uint32_t rl = P.ev_rx[ee - 1];
-                const long long nlo = max(0ll, i - 5), nhi = min(N, i + 6);  // SS:275-277
-                if (!list_any_in(a.keys, a.rx_begin[rl], a.rx_begin[rl + 1], rl, P.gb, first + (uint32_t)nlo, first + (uint32_t)nhi)) continue;
-                bool ok = true;
-                long long T = -1;   // local line of the earliest feasible position of the previous event
-                if (a.seq_T) ok = a.seq_T[q] < i + a.line_base;
-                else for (uint32_t j = eb; j + 1 < ee && ok; ++j) {
-                    const uint32_t r = P.ev_rx[j];
-                    const uint32_t b = a.rx_begin[r], en = a.rx_begin[r + 1];
-                    const unsigned long long want = ((unsigned long long)r << P.gb) | (uint32_t)(first + T + 1);
-                    const uint32_t at = b + lower_bound_dev<unsigned long long>(a.keys + b, en - b, want);
-                    if (at >= en) { ok = false; break; }
-                    const long long l = (long long)(uint32_t)(a.keys[at] & gmask) - first;
-                    if (l >= i) { ok = false; break; }     // must end strictly before the primary line
-                    T = l;
-                }
-                if (ok) total = __dadd_rn(total, P.seq_bonus[q]);
-            }
-            temporal = __dadd_rn(1.0, total);
-        }
-    }
-
-    // context factor, CAS:46-117, accumulated in the reference's per-line order
-    double ctx;
-    {
-        long long b0 = i, a1 = i + 1;
-        if (P.pat_has_ctx[p]) { b0 = max(0ll, i - (long long)P.pat_before[p]); a1 = min(N, i + 1 + (long long)P.pat_after[p]); }
-        double score = 0.0;
-        int err = 0, stack = 0;
-        const uint8_t* __restrict__ fl = a.ctx_flags + first;
-        for (long long l = b0; l < a1; ++l) {
-            const uint32_t f = fl[l];
-            if (f & 1u) { ++err; score = __dadd_rn(score, 0.4); }
-            else if (f & 2u) { score = __dadd_rn(score, 0.2); }
-            if (f & 4u) { ++stack; score = __dadd_rn(score, 0.1); }
-            if (f & 8u) { score = __dadd_rn(score, 0.3); }
-        }
-        if (stack > 0) score = __dadd_rn(score, fmin(__dmul_rn((double)stack, 0.1), 0.5));
-        const int total = (int)(a1 - b0);
-        if (total > 10 && (double)(stack + err) > __dmul_rn((double)total, 0.7)) score = __dmul_rn(score, 0.8);
-        ctx = __dadd_rn(1.0, score);
-        if (ctx > C.max_ctx) ctx = C.max_ctx;
-        if (total <= 0) ctx = 1.0;
-    }
-
-    // frequency penalty, FTS:64-93 with the count read before this match is recorded (SS:84-88)
-    double pen = 0.0;
-    {
-        const int slot = P.pat_slot[p];
-        if (slot >= 0) {
-            const unsigned long long pr = a.prior ? a.prior[P.slot_first_pat[slot]] : 0ull;
-            // events of this frequency slot that come earlier in discovery order (whole batch): for
-            // every pattern q sharing the id, the records of its primary on earlier lines, plus the
-            // one on this line when q precedes p
-            unsigned long long earlier = 0;
-            for (uint32_t j = P.slot_begin[slot]; j < P.slot_begin[slot + 1]; ++j) {
-                const uint32_t q = P.slot_pats[j], rq = P.pat_primary[q];
-                const uint32_t b = a.rx_begin[rq], cnt2 = a.rx_begin[rq + 1] - b;
-                const unsigned long long want = ((unsigned long long)rq << P.gb) | g;
-                const uint32_t at = lower_bound_dev<unsigned long long>(a.keys + b, cnt2, want);
-                earlier += at;
-                if (a.n_global) earlier -= lower_bound_dev<unsigned long long>(a.keys + b, cnt2, ((unsigned long long)rq << P.gb) | a.core_lo);
-                if (q < p && at < cnt2 && a.keys[b + at] == want) earlier += 1;
-            }
-            const unsigned long long cnt = pr + earlier;
-            if (cnt > 0) {
-                const double rate = __ddiv_rn((double)cnt, (double)C.hours);
-                if (rate > C.freq_thr) pen = fmin(C.max_pen, __ddiv_rn(__dsub_rn(rate, C.freq_thr), C.freq_thr));
-            }
-        }
-    }
-
-    double s = __dmul_rn(base, sev);
-    s = __dmul_rn(s, chrono);
-    s = __dmul_rn(s, prox);
-    s = __dmul_rn(s, temporal);
-    s = __dmul_rn(s, ctx);
-    s = __dmul_rn(s, __dsub_rn(1.0, pen));
-
-    a.out_line[e] = (uint32_t)(i + a.line_base + 1);
-    a.out_pat[e] = p;
-    a.out_score[e] = s;
-    if (a.out_factors) {
-        double* f = a.out_factors + (size_t)e * 7;
-        f[0] = base; f[1] = sev; f[2] = chrono; f[3] = prox; f[4] = temporal; f[5] = ctx; f[6] = pen;
-    }
-    // order-preserving key: larger score first; -0.0/+0.0 and NaN keep IEEE total order
-    unsigned long long bits = (unsigned long long)__double_as_longlong(s);
-    bits = (bits & 0x8000000000000000ull) ? ~bits : (bits | 0x8000000000000000ull);
-    a.sort_key[e] = ~bits;
-}
-__global__ void k_write_rank(const uint32_t* __restrict__ order, const uint32_t* __restrict__ ev_log,
-                             const unsigned long long* __restrict__ log_begin, const Counters* ctr, uint32_t* __restrict__ rank) {
-    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= ctr->n_events) return;
-    const uint32_t e = order[j];
-    rank[e] = j - (uint32_t)log_begin[ev_log[e]];
-}
-__global__ void k_gather_u32(const uint32_t* __restrict__ src, const uint32_t* __restrict__ idx, uint32_t n, uint32_t* __restrict__ dst) {
-    uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j < n) dst[j] = src[idx[j]];
-}
-// Line-range shards: the sequence chain of SS:250-258 (forward form) restricted to this
-// shard's own lines, for every state the chain can be in when it enters the shard. tab[off[q] + s] =
-// (state on exit) << 32 | (1 + own-line index where the last-but-one event was reached, 0 if not reached).
-__global__ void k_range_tables(const unsigned long long* __restrict__ keys, const uint32_t* __restrict__ rx_begin, DevPlan P, const Counters* ctr,
-                               uint32_t n_seq, const uint32_t* __restrict__ tab_off, uint32_t core_lo, uint32_t halo_after,
-                               unsigned long long* __restrict__ tab) {
-    const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
-    if (q >= n_seq) return;
-    const uint32_t core_hi = ctr->n_lines_total > halo_after ? ctr->n_lines_total - halo_after : 0;
-    const uint32_t eb = P.seq_ev_begin[q], ee = P.seq_ev_begin[q + 1];
-    const uint32_t k = ee - eb;
-    if (k < 2) return;
-    const unsigned long long gmask = (1ull << P.gb) - 1ull;
-    for (uint32_t s = 0; s + 1 < k; ++s) {
-        uint32_t j = s;
-        long long T = (long long)core_lo - 1;
-        while (j + 1 < k) {
-            const uint32_t r = P.ev_rx[eb + j];
-            const uint32_t b = rx_begin[r], en = rx_begin[r + 1];
-            const unsigned long long want = ((unsigned long long)r << P.gb) | (uint32_t)(T + 1);
-            const uint32_t at = b + lower_bound_dev<unsigned long long>(keys + b, en - b, want);
-            if (at >= en) break;
-            const uint32_t l = (uint32_t)(keys[at] & gmask);
-            if (l >= core_hi) break;
-            T = l;
-            ++j;
-        }
-        tab[tab_off[q] + s] = ((unsigned long long)j << 32) | (j + 1 == k ? (unsigned long long)(T - core_lo + 1) : 0ull);
-    }
-}
-// Multi-GPU batches with the exchange kept on the device: `all` holds every rank's [n_pat counts, overflow word]
-// (all-gathered); prior_out[p] = window prior + the counts of the lower ranks; *any_flag = OR of the overflow words.
-__global__ void k_prior_prefix(const unsigned long long* __restrict__ all, uint32_t n_pat, uint32_t rank, uint32_t world,
-                               const unsigned long long* __restrict__ prior_in, unsigned long long* __restrict__ prior_out,
-                               unsigned long long* __restrict__ any_flag) {
-    const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
-    const size_t stride = (size_t)n_pat + 1;
-    if (p < n_pat) {
-        unsigned long long v = prior_in ? prior_in[p] : 0ull;
-        for (uint32_t r = 0; r < rank; ++r) v += all[r * stride + p];
-        prior_out[p] = v;
-    }
-    if (p == 0) {
-        unsigned long long f = 0;
-        for (uint32_t r = 0; r < world; ++r) f |= all[r * stride + n_pat];
-        *any_flag = f;
-    }
-}
-// Status word of a scan for the other ranks: non-zero exactly when check_estimates() on this rank will ask for a re-run.
-struct EstCaps { unsigned long long lines, cand, tasks, vm_tasks, recs, items, events; };
-// `counts` are this rank's per-pattern event counts: their sum is the number of events k_emit_events
-// produces (same records, same line range), so the events queue is judged even when this runs before it.
-__global__ void __launch_bounds__(128) k_publish_overflow(const Counters* ctr, EstCaps cap, const unsigned long long* __restrict__ counts,
-                                                          uint32_t n_pat, unsigned long long* __restrict__ dst) {
-    __shared__ unsigned long long part[128];
-    unsigned long long sum = 0;
-    for (uint32_t p = threadIdx.x; p < n_pat; p += blockDim.x) sum += counts[p];
-    part[threadIdx.x] = sum;
-    __syncthreads();
-    for (int o = 64; o; o >>= 1) { if ((int)threadIdx.x < o) part[threadIdx.x] += part[threadIdx.x + o]; __syncthreads(); }
-    if (threadIdx.x != 0) return;
-    unsigned long long st = ctr->overflow;
-    const unsigned int mi = max(max(ctr->n_items[0], ctr->n_items[1]), max(ctr->n_items[2], ctr->n_items[3]));
-    if ((unsigned long long)ctr->n_lines_total + 1 > cap.lines || ctr->n_cand > cap.cand || ctr->n_tasks > cap.tasks ||
-        ctr->n_vm_tasks > cap.vm_tasks || ctr->n_recs > cap.recs || mi > cap.items ||
-        max((unsigned long long)ctr->n_events, part[0]) > cap.events)
-        st |= 1ull << 32;
-    *dst = st;
-}
-// ------------------------------------------------------------------ sorting a few ten thousand keys
-// The event list and the score ranking hold ~10^4 keys: a device-wide radix sort spends 8-10 us per
-// digit pass on them (13 passes for these two sorts), all of it launch and look-back latency. Here
-// tiles of 2048 keys are sorted in shared memory (cub::BlockRadixSort, stable) by one kernel, and a
-// second kernel finds every key's final position by counting, in each other tile, the keys that
-// precede it (binary searches; earlier tiles win ties, which keeps the sort stable).
-constexpr int SS_THREADS = 256, SS_ITEMS = 8, SS_TILE = SS_THREADS * SS_ITEMS;
-constexpr uint32_t SS_MAX_TILES = 64;
-constexpr int SS_GROUP = 16;              // tiles searched in lockstep by k_tile_rank (independent probes in flight)      // beyond 131072 keys the counting pass costs more than radix passes
-__global__ void __launch_bounds__(SS_THREADS) k_tile_sort(const unsigned long long* __restrict__ in, uint32_t n, int end_bit,
-                                                          unsigned long long* __restrict__ tile_keys, uint32_t* __restrict__ tile_idx) {
-    using Sorter = cub::BlockRadixSort<unsigned long long, SS_THREADS, SS_ITEMS, uint32_t, 6>;
-    __shared__ typename Sorter::TempStorage tmp;
-    unsigned long long k[SS_ITEMS];
-    uint32_t v[SS_ITEMS];
-    const uint32_t base = blockIdx.x * SS_TILE + threadIdx.x * SS_ITEMS;
-#pragma unroll
-    for (int i = 0; i < SS_ITEMS; ++i) { k[i] = base + i < n ? in[base + i] : ~0ull; v[i] = base + i; }
-    Sorter(tmp).Sort(k, v, 0, end_bit);
-#pragma unroll
-    for (int i = 0; i < SS_ITEMS; ++i) { tile_keys[base + i] = k[i]; tile_idx[base + i] = v[i]; }
-}
-// out_sorted (optional): keys scattered to their final positions; out_rank (optional): final position of
-// original element i, written for i < *n_valid.
-__global__ void __launch_bounds__(128) k_tile_rank(const unsigned long long* __restrict__ tile_keys, const uint32_t* __restrict__ tile_idx,
-                                                   uint32_t n_tiles, uint32_t n, unsigned long long* __restrict__ out_sorted,
-                                                   uint32_t* __restrict__ out_rank, const unsigned int* __restrict__ n_valid) {
-    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-    if (j >= n_tiles * SS_TILE) return;
-    const uint32_t t0 = j / SS_TILE;
-    const unsigned long long key = tile_keys[j];
-    uint32_t r = j - t0 * SS_TILE;
-    // branch-free binary searches over the 2048 keys of each other tile, SS_GROUP tiles in lockstep so
-    // that their (dependent) probes overlap: keys <= key in earlier tiles, keys < key in later ones
-    for (uint32_t tb = 0; tb < n_tiles; tb += SS_GROUP) {
-        uint32_t pos[SS_GROUP];
-        const unsigned long long* base[SS_GROUP];
-        // earlier tiles count keys <= key, i.e. keys < key + 1 (key + 1 cannot overflow there: a key equal to
-        // the all-ones padding in an earlier tile is handled by the saturation below)
-        unsigned long long bound[SS_GROUP];
-#pragma unroll
-        for (int q = 0; q < SS_GROUP; ++q) {
-            const uint32_t t = min(tb + q, n_tiles - 1);
-            pos[q] = 0;
-            base[q] = tile_keys + (size_t)t * SS_TILE;
-            bound[q] = (t < t0 && key != ~0ull) ? key + 1 : key;      // count keys < bound
-        }
-#pragma unroll 1
-        for (uint32_t step = SS_TILE / 2; step > 0; step >>= 1) {
-            unsigned long long v[SS_GROUP];
-#pragma unroll
-            for (int q = 0; q < SS_GROUP; ++q) v[q] = base[q][pos[q] + step - 1];
-#pragma unroll
-            for (int q = 0; q < SS_GROUP; ++q) pos[q] += v[q] < bound[q] ? step : 0u;
-        }
-        unsigned long long v[SS_GROUP];
-#pragma unroll
-        for (int q = 0; q < SS_GROUP; ++q) v[q] = base[q][pos[q]];
-#pragma unroll
-        for (int q = 0; q < SS_GROUP; ++q) {
-            const uint32_t t = tb + q;
-            uint32_t cnt = pos[q] + (v[q] < bound[q] ? 1u : 0u);
-            if (t < t0 && key == ~0ull) cnt = SS_TILE;                  // every key of an earlier tile is <= the padding key
-            if (t < n_tiles && t != t0) r += cnt;
-        }
-    }
-    if (out_sorted && r < n) out_sorted[r] = key;
-    if (out_rank) { const uint32_t i = tile_idx[j]; if (i < *n_valid) out_rank[i] = r; }
-}
-__global__ void k_count_per_pattern(const unsigned long long* __restrict__ keys, const Counters* ctr, DevPlan P, unsigned long long* __restrict__ counts,
-                                    uint32_t core_lo, uint32_t halo_after) {
-    const uint32_t n = ctr->n_unique;
-    const uint32_t core_hi = ctr->n_lines_total > halo_after ? ctr->n_lines_total - halo_after : 0;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const uint32_t r = (uint32_t)min(keys[i] >> P.gb, 0xFFFFFFFFull);
-        if (r >= P.n_rx) continue;
-        const uint32_t g = (uint32_t)(keys[i] & ((1ull << P.gb) - 1ull));
-        if (g < core_lo || g >= core_hi) continue;
-        for (uint32_t j = P.rxp_begin[r]; j < P.rxp_begin[r + 1]; ++j) atomicAdd(&counts[P.rxp_pat[j]], 1ull);
-    }
-}
-
+#include "k_scan.cuh"
+#include "k_verify.cuh"
+#include "k_score.cuh"
+#include "k_sort.cuh"
 }  // namespace
 
 // ============================================================================================
