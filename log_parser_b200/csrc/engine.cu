@@ -157,13 +157,13 @@ struct lp_ctx {
 
     // scratch (grow-only)
     DevBuf text, log_off, tile_counts, counters, line_start, line_end, first_line, n_lines;
-    DevBuf items, ss_keys, ss_idx, span_start, span_end;
+    DevBuf items, ss_keys, ss_idx;
     size_t est_items = 0;
     int occ_confirm = 0, occ_resolve = 0;
     DevBuf cand, tasks, vm_tasks, vm_stack, recs, recs_alt, cub_tmp, rx_begin, ctx_flags;
     DevBuf ev_key, ev_key_alt, ev_log, slot_key, slot_key_alt, ev_idx, ev_idx_alt, rank_in_slot, freq_delta, prior;
-    DevBuf out_line, out_pat, out_score, out_factors, sort_key, sort_key_alt, order, order_alt, log_sorted, log_sorted_alt;
-    DevBuf rank, log_event_begin, n_unique;
+    DevBuf out_arena, sort_key, sort_key_alt, order, order_alt, log_sorted, log_sorted_alt;
+    DevBuf log_event_begin, n_unique;
     const uint8_t* host_src = nullptr;      // set by lp_analyze*: the log still has to be copied in (run_scan does it piecewise)
     cudaStream_t copy_stream = nullptr;
     std::vector<cudaEvent_t> chunk_ev;
@@ -667,11 +667,21 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
     c->log_event_begin.ensure((size_t)(n_logs + 1) * 8);
     c->ev_log.ensure((size_t)mc * 4); c->slot_key.ensure((size_t)mc * 4); c->slot_key_alt.ensure((size_t)mc * 4);
     c->ev_idx.ensure((size_t)mc * 4); c->ev_idx_alt.ensure((size_t)mc * 4); c->rank_in_slot.ensure((size_t)mc * 4);
-    c->out_line.ensure((size_t)mc * 4); c->out_pat.ensure((size_t)mc * 4); c->out_score.ensure((size_t)mc * 8);
+    // Everything the host reads back lives in ONE device arena with the layout of the page-locked buffer it is
+    // copied to, so a call ends with a single device->host copy (small copies cost ~4 us each on the stream).
+    const bool want_rank = !(options & LP_OPT_NO_RANK), want_factors = (options & LP_OPT_FACTORS) != 0, want_spans = (options & LP_OPT_SPANS) != 0;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 63) & ~size_t(63); return o; };
+    const size_t o_ctr = take(sizeof(Counters)), o_line = take((size_t)mc * 4), o_pat = take((size_t)mc * 4), o_score = take((size_t)mc * 8),
+                 o_rank = take((size_t)mc * 4), o_fac = take(want_factors ? (size_t)mc * 56 : 0),
+                 o_delta = take((size_t)np * 8), o_nl = take((size_t)n_logs * 4), o_leb = take((size_t)(n_logs + 1) * 8),
+                 o_ss = take(want_spans ? (size_t)mc * 4 : 0), o_se = take(want_spans ? (size_t)mc * 4 : 0), o_flag = take(8);
+    c->out_arena.ensure(off);
+    uint8_t* const arena = c->out_arena.as<uint8_t>();
+    uint32_t* const d_rank = reinterpret_cast<uint32_t*>(arena + o_rank);
     c->sort_key.ensure((size_t)mc * 8); c->sort_key_alt.ensure((size_t)mc * 8);
-    c->order.ensure((size_t)mc * 4); c->order_alt.ensure((size_t)mc * 4); c->rank.ensure((size_t)mc * 4);
+    c->order.ensure((size_t)mc * 4); c->order_alt.ensure((size_t)mc * 4);
     c->log_sorted.ensure((size_t)mc * 4); c->log_sorted_alt.ensure((size_t)mc * 4);
-    if (options & LP_OPT_FACTORS) c->out_factors.ensure((size_t)mc * 7 * 8);
     const unsigned long long* prior_d = nullptr;
     if (prior_count && np) {
         c->prior.ensure((size_t)np * 8);
@@ -690,8 +700,9 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
     sa.first_line = c->first_line.as<uint32_t>(); sa.n_lines = c->n_lines.as<uint32_t>();
     sa.keys = c->recs.as<unsigned long long>(); sa.rx_begin = c->rx_begin.as<uint32_t>();
     sa.ctx_flags = c->ctx_flags.as<uint8_t>();
-    sa.out_line = c->out_line.as<uint32_t>(); sa.out_pat = c->out_pat.as<uint32_t>(); sa.out_score = c->out_score.as<double>();
-    sa.out_factors = (options & LP_OPT_FACTORS) ? c->out_factors.as<double>() : nullptr;
+    sa.out_line = reinterpret_cast<uint32_t*>(arena + o_line); sa.out_pat = reinterpret_cast<uint32_t*>(arena + o_pat);
+    sa.out_score = reinterpret_cast<double*>(arena + o_score);
+    sa.out_factors = want_factors ? reinterpret_cast<double*>(arena + o_fac) : nullptr;
     sa.sort_key = c->sort_key.as<unsigned long long>();
     if (rgl) {
         sa.line_base = rgl->line_base; sa.n_global = rgl->n_global; sa.core_lo = c->pend.halo_before;
@@ -707,7 +718,7 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
                                                                    n_logs, c->dp.pb, c->log_event_begin.as<unsigned long long>());
     c->launches += 3;
     if (!(options & LP_OPT_NO_RANK) && n_logs == 1 &&
-        small_sort(c, c->sort_key.as<unsigned long long>(), mc, 64, nullptr, c->rank.as<uint32_t>(), &ctr->n_events)) {
+        small_sort(c, c->sort_key.as<unsigned long long>(), mc, 64, nullptr, d_rank, &ctr->n_events)) {
         // one log, few events: ranks by tile sort + counting (descending score, ties keep discovery order)
     } else if (!(options & LP_OPT_NO_RANK)) {
         // stable sort by descending score (ties keep discovery order), then stably by log
@@ -722,18 +733,15 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
             c->launches += 1;
         }
         k_write_rank<<<blocks_for(mc, 256), 256, 0, st>>>(order, c->ev_log.as<uint32_t>(), c->log_event_begin.as<unsigned long long>(), ctr,
-                                                          c->rank.as<uint32_t>());
+                                                          d_rank);
         c->launches += 1;
     }
-    const bool want_spans = (options & LP_OPT_SPANS) != 0;
     if (want_spans) {
         const uint32_t sg = (uint32_t)c->n_sm * 2, sb = 128;
         c->vm_stack.ensure((size_t)sg * sb * lpx::VM_STACK_WORDS * 4);
-        c->span_start.ensure((size_t)std::max<uint32_t>(mc, 1) * 4);
-        c->span_end.ensure((size_t)std::max<uint32_t>(mc, 1) * 4);
         k_spans<<<sg, sb, 0, st>>>(c->ev_key.as<unsigned long long>(), ctr, mc, c->dp, c->pend.d_text, c->line_start.as<uint32_t>(),
-                                   c->line_end.as<uint32_t>(), c->vm_stack.as<uint32_t>(), ctr, c->span_start.as<uint32_t>(),
-                                   c->span_end.as<uint32_t>());
+                                   c->line_end.as<uint32_t>(), c->vm_stack.as<uint32_t>(), ctr, reinterpret_cast<uint32_t*>(arena + o_ss),
+                                   reinterpret_cast<uint32_t*>(arena + o_se));
         c->launches += 1;
     }
     CK(cudaEventRecord(c->ev[4], st));
@@ -742,32 +750,17 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
     // the estimates; trimmed after the counters arrive
     std::unique_ptr<lp_result> res(new lp_result());
     res->n_logs = n_logs;
-    const bool want_rank = !(options & LP_OPT_NO_RANK), want_factors = (options & LP_OPT_FACTORS) != 0;
-    size_t off = 0;
-    auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 63) & ~size_t(63); return o; };
-    const size_t o_ctr = take(sizeof(Counters)), o_line = take((size_t)mc * 4), o_pat = take((size_t)mc * 4), o_score = take((size_t)mc * 8),
-                 o_rank = take(want_rank ? (size_t)mc * 4 : 0), o_fac = take(want_factors ? (size_t)mc * 56 : 0),
-                 o_delta = take((size_t)np * 8), o_nl = take((size_t)n_logs * 4), o_leb = take((size_t)(n_logs + 1) * 8),
-                 o_ss = take(want_spans ? (size_t)mc * 4 : 0), o_se = take(want_spans ? (size_t)mc * 4 : 0), o_flag = take(8);
+    // the small items (counters, per-pattern counts, per-log line counts and event ranges, status word) are
+    // packed behind the event columns by one tiny kernel, then the arena goes to the host in one copy
+    k_pack_tail<<<1, 256, 0, st>>>(ctr, c->freq_delta.as<unsigned long long>(), np, c->n_lines.as<uint32_t>(), n_logs,
+                                   c->log_event_begin.as<unsigned long long>(), flag_dev, reinterpret_cast<Counters*>(arena + o_ctr),
+                                   reinterpret_cast<unsigned long long*>(arena + o_delta), reinterpret_cast<uint32_t*>(arena + o_nl),
+                                   reinterpret_cast<unsigned long long*>(arena + o_leb), reinterpret_cast<unsigned long long*>(arena + o_flag));
+    c->launches += 1;
     if (!c->stage.p) c->stage = c->pool->acquire();
     c->stage.ensure(off);
     uint8_t* hs = c->stage.p;
-    CK(cudaMemcpyAsync(hs + o_ctr, ctr, sizeof(Counters), cudaMemcpyDeviceToHost, st));
-    if (flag_dev) CK(cudaMemcpyAsync(hs + o_flag, flag_dev, 8, cudaMemcpyDeviceToHost, st));
-    if (mc) {
-        CK(cudaMemcpyAsync(hs + o_line, c->out_line.p, (size_t)mc * 4, cudaMemcpyDeviceToHost, st));
-        CK(cudaMemcpyAsync(hs + o_pat, c->out_pat.p, (size_t)mc * 4, cudaMemcpyDeviceToHost, st));
-        CK(cudaMemcpyAsync(hs + o_score, c->out_score.p, (size_t)mc * 8, cudaMemcpyDeviceToHost, st));
-        if (want_rank) CK(cudaMemcpyAsync(hs + o_rank, c->rank.p, (size_t)mc * 4, cudaMemcpyDeviceToHost, st));
-        if (want_factors) CK(cudaMemcpyAsync(hs + o_fac, c->out_factors.p, (size_t)mc * 56, cudaMemcpyDeviceToHost, st));
-        if (want_spans) {
-            CK(cudaMemcpyAsync(hs + o_ss, c->span_start.p, (size_t)mc * 4, cudaMemcpyDeviceToHost, st));
-            CK(cudaMemcpyAsync(hs + o_se, c->span_end.p, (size_t)mc * 4, cudaMemcpyDeviceToHost, st));
-        }
-    }
-    if (np) CK(cudaMemcpyAsync(hs + o_delta, c->freq_delta.p, (size_t)np * 8, cudaMemcpyDeviceToHost, st));
-    CK(cudaMemcpyAsync(hs + o_nl, c->n_lines.p, (size_t)n_logs * 4, cudaMemcpyDeviceToHost, st));
-    CK(cudaMemcpyAsync(hs + o_leb, c->log_event_begin.p, (size_t)(n_logs + 1) * 8, cudaMemcpyDeviceToHost, st));
+    CK(cudaMemcpyAsync(hs, arena, off, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     CK(cudaGetLastError());
     Counters h;
@@ -942,9 +935,9 @@ void lp_destroy(lp_ctx* c) {
     DevBuf* all[] = {&c->text, &c->log_off, &c->tile_counts, &c->counters, &c->line_start, &c->line_end, &c->first_line, &c->n_lines,
                      &c->cand, &c->tasks, &c->vm_tasks, &c->vm_stack, &c->recs, &c->recs_alt, &c->cub_tmp, &c->rx_begin, &c->ctx_flags, &c->ev_key, &c->ev_key_alt,
                      &c->ev_log, &c->slot_key, &c->slot_key_alt, &c->ev_idx, &c->ev_idx_alt, &c->rank_in_slot, &c->freq_delta, &c->prior,
-                     &c->out_line, &c->out_pat, &c->out_score, &c->out_factors, &c->sort_key, &c->sort_key_alt, &c->order, &c->order_alt,
-                     &c->log_sorted, &c->log_sorted_alt, &c->rank, &c->log_event_begin, &c->n_unique, &c->d_lut,
-                     &c->f_bitmap, &c->f_key, &c->f_lits, &c->f_bytes, &c->items, &c->ss_keys, &c->ss_idx, &c->span_start, &c->span_end, &c->seq_tab_off, &c->seq_tab, &c->seq_T, &c->prior_eff, &c->any_flag, &c->dist_mine, &c->dist_all};
+                     &c->out_arena, &c->sort_key, &c->sort_key_alt, &c->order, &c->order_alt,
+                     &c->log_sorted, &c->log_sorted_alt, &c->log_event_begin, &c->n_unique, &c->d_lut,
+                     &c->f_bitmap, &c->f_key, &c->f_lits, &c->f_bytes, &c->items, &c->ss_keys, &c->ss_idx, &c->seq_tab_off, &c->seq_tab, &c->seq_T, &c->prior_eff, &c->any_flag, &c->dist_mine, &c->dist_all};
     for (DevBuf* b : all) b->release();
     if (c->nccl_comm) nccl_comm_destroy(c->nccl_comm);
     c->stage.release();

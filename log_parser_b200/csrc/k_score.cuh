@@ -332,3 +332,14 @@ __global__ void __launch_bounds__(128) k_publish_overflow(const Counters* ctr, E
         st |= 1ull << 32;
     *dst = st;
 }
+
+// Copies the small read-back items behind the event columns of the output arena (one block).
+__global__ void k_pack_tail(const Counters* ctr, const unsigned long long* __restrict__ freq_delta, uint32_t n_pat,
+                            const uint32_t* __restrict__ n_lines, uint32_t n_logs, const unsigned long long* __restrict__ log_event_begin,
+                            const unsigned long long* flag, Counters* o_ctr, unsigned long long* __restrict__ o_delta,
+                            uint32_t* __restrict__ o_nl, unsigned long long* __restrict__ o_leb, unsigned long long* o_flag) {
+    if (threadIdx.x == 0) { *o_ctr = *ctr; *o_flag = flag ? *flag : 0ull; }
+    for (uint32_t p = threadIdx.x; p < n_pat; p += blockDim.x) o_delta[p] = freq_delta[p];
+    for (uint32_t k = threadIdx.x; k < n_logs; k += blockDim.x) o_nl[k] = n_lines[k];
+    for (uint32_t k = threadIdx.x; k <= n_logs; k += blockDim.x) o_leb[k] = log_event_begin[k];
+}
