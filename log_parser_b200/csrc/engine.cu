@@ -6,6 +6,7 @@
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
+#include <chrono>
 #include <cstring>
 #include <dlfcn.h>
 #include <functional>
@@ -650,6 +651,20 @@ void per_pattern_counts(lp_ctx* c, uint64_t* counts_out) {
     check_estimates(c, h, c->pend.n_logs, true);
 }
 
+// The one synchronisation of a call. The pipeline runs for well under a millisecond on typical logs, so the
+// calling thread polls the stream for up to 1 ms (a blocking wait costs 10-20 us of wake-up latency) and falls
+// back to a blocking wait when the work takes longer (a log that is still being copied from the host).
+void wait_for_stream(cudaStream_t st) {
+    const auto t0 = std::chrono::steady_clock::now();
+    for (;;) {
+        const cudaError_t q = cudaStreamQuery(st);
+        if (q == cudaSuccess) return;
+        if (q != cudaErrorNotReady) CK(q);
+        if (std::chrono::steady_clock::now() - t0 > std::chrono::milliseconds(1)) break;
+    }
+    CK(cudaStreamSynchronize(st));
+}
+
 // ---- phase 2: frequency ranks, scoring, ranking, result download (one synchronisation)
 struct RangeGlobal { long long line_base, n_global; const long long* seq_T; };   // seq_T: host array [n_seq]
 
@@ -761,7 +776,7 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
     c->stage.ensure(off);
     uint8_t* hs = c->stage.p;
     CK(cudaMemcpyAsync(hs, arena, off, cudaMemcpyDeviceToHost, st));
-    CK(cudaStreamSynchronize(st));
+    wait_for_stream(st);
     CK(cudaGetLastError());
     Counters h;
     memcpy(&h, hs + o_ctr, sizeof h);
