@@ -695,3 +695,58 @@ def test_many_events_device_radix_path_equals_tile_sort_path(parser):
     np.testing.assert_array_equal(np.concatenate([r.pattern for r in results]), whole.pattern)
     np.testing.assert_array_equal(np.concatenate([r.score for r in results]), whole.score)
     np.testing.assert_array_equal(np.concatenate(parallel.merge_ranks([r.score for r in results])), whole.rank)
+
+
+def test_random_regexes_with_literals_through_the_pipeline(parser, oracle):
+    """Adversarial patterns end to end: random regex fragments (classes, anchors, \\b, lazy / possessive
+    quantifiers, look-around, back-references) glued around fixed words, so that the literal prefilter,
+    the cover test for anchored verification, the boundary test, the line walkers and the backtracking
+    engine all see shapes the synthetic pattern set never produces. Every (line, pattern) event against
+    the oracle's find() on that line."""
+    from rxgen import Gen
+
+    rng = random.Random(20261107)
+    words = ["ERRx", "abc_1", "Exception", "timeout", "x-1:E", "R.E.c"]
+    alphabet = "abcERx_1 .-:"
+    checked = n_events = 0
+    for rnd_i in range(25):
+        pats, rxs = [], []
+        while len(pats) < 14:
+            g = Gen(rng, regular_only=(len(pats) % 3 != 0), max_depth=2)
+            a, _pa = g.regex()
+            b, _pb = Gen(rng, regular_only=True, max_depth=1).regex()
+            w = rng.choice(words)
+            wj = "".join("\\" + ch if ch in ".-:" else ch for ch in w)
+            shape = rng.randrange(5)
+            j = [wj + a, a + wj, a + wj + b, "\\b" + wj + "\\b", "(?:" + a + "|" + wj + b + ")"][shape]
+            try:
+                o = oracle.Regex(j)
+                binding.DebugRegex(j)
+            except Exception:
+                continue
+            pats.append(PatternSpec(id=f"p{len(pats)}", primary_regex=j, confidence=0.5, severity="LOW"))
+            rxs.append(o)
+        lines = []
+        for _ in range(400):
+            parts = []
+            for _k in range(rng.randint(0, 4)):
+                parts.append(rng.choice(words) if rng.random() < 0.5 else "".join(rng.choice(alphabet) for _ in range(rng.randint(0, 6))))
+            lines.append("".join(parts))
+        log = ("\n".join(lines) + "\n").encode()
+        try:
+            parser.load_patterns(pats)
+        except binding.UnsupportedRegexError:
+            continue
+        res = parser.analyze(log, options=binding.OPT_NO_RANK)
+        got = set(zip(res.line.tolist(), res.pattern.tolist()))
+        exp = set()
+        for i, ln in enumerate(lines):
+            if i >= res.n_lines:
+                break
+            for p, o in enumerate(rxs):
+                if o.find(ln):
+                    exp.add((i + 1, p))
+        assert got == exp, (rnd_i, sorted(got ^ exp)[:5], [pats[p].primary_regex for _l, p in sorted(got ^ exp)[:3]])
+        checked += 1
+        n_events += len(exp)
+    assert checked >= 20 and n_events > 2000
