@@ -143,6 +143,7 @@ def load_library() -> C.CDLL:
     L.lp_debug_rx_literals.restype = C.c_size_t
     L.lp_debug_rx_literals.argtypes = [vp, C.c_char_p, C.c_size_t]
     L.lp_debug_rx_anchor.argtypes = [vp]
+    L.lp_debug_rx_match_local.argtypes = [vp, C.c_char_p, C.c_size_t]
     L.lp_debug_rx_span.argtypes = [vp, C.c_char_p, C.c_size_t, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
     L.lp_debug_rx_match_anchored.argtypes = [vp, C.c_char_p, C.c_size_t]
     _lib = L
@@ -507,6 +508,11 @@ class DebugRegex:
         """0: verified by walking the whole line; 1 / 2: decided at the literal occurrences by the
         forward / backward anchored automaton."""
         return int(self.L.lp_debug_rx_anchor(self.h))
+
+    def match_local(self, text) -> int:
+        """1/0 as the boundary test at the literal occurrences decides; -2 if the regex is not of that form."""
+        b = text.encode("utf-8") if isinstance(text, str) else bytes(text)
+        return int(self.L.lp_debug_rx_match_local(self.h, b, len(b)))
 
     def match_anchored(self, text) -> int:
         b = text.encode("utf-8") if isinstance(text, str) else bytes(text)

@@ -21,6 +21,7 @@ struct DebugRx {
     std::vector<Literal> lits;
     int anchor = 0;          // 0 none, 1 forward, 2 backward
     Dfa adfa;
+    std::vector<LocalLiteral> local;      // non-empty: the regex is decided by boundary tests at its literal occurrences
     VmProgram span_vm;       // every regex has a bytecode program: spans come from the backtracking engine
 };
 void put_err(char* err, size_t n, const std::string& m) {
@@ -45,6 +46,7 @@ void* lp_debug_rx_compile(const char* regex, int flags, int force_vm, char* err,
             if (d->parsed.regular && !force_vm) d->has_dfa = build_dfa(*d->parsed.root, d->dfa);
             if (!d->has_dfa) { build_vm(d->parsed, d->vm); d->has_vm = true; }
             build_vm(d->parsed, d->span_vm);
+            if (d->has_dfa && !local_verify_form(*d->parsed.root, d->local, min_lit)) d->local.clear();
             d->lits = required_literals(*d->parsed.root, min_lit);
             if (d->has_dfa) d->anchor = choose_anchor(*d->parsed.root, d->lits, d->adfa);
         } catch (...) { delete d; throw; }
@@ -81,6 +83,29 @@ int lp_debug_rx_span(void* h, const uint8_t* s, size_t n, uint32_t* start, uint3
     const int r = vm_span_host(static_cast<DebugRx*>(h)->span_vm, s, n, span);
     if (r > 0) { *start = span[0]; *end = span[1]; }
     return r;
+}
+// What k_resolve's boundary class decides: some occurrence of one of the literals whose neighbours satisfy
+// the \\b conditions. -2 when the regex is not of that form.
+int lp_debug_rx_match_local(void* h, const uint8_t* s, size_t n) {
+    DebugRx* d = static_cast<DebugRx*>(h);
+    if (d->local.empty()) return -2;
+    auto word = [](uint8_t b) { return (b >= '0' && b <= '9') || (b >= 'A' && b <= 'Z') || b == '_' || (b >= 'a' && b <= 'z'); };
+    for (const auto& ll : d->local) {
+        const size_t m = ll.lit.bytes.size();
+        for (size_t p = 0; p + m <= n; ++p) {
+            bool ok = true;
+            for (size_t j = 0; j < m && ok; ++j) {
+                uint8_t b = s[p + j];
+                if (ll.lit.icase && b >= 'A' && b <= 'Z') b += 32;
+                ok = b == (uint8_t)ll.lit.bytes[j];
+            }
+            if (!ok) continue;
+            if (ll.left_boundary && ((p > 0 && word(s[p - 1])) == word(s[p]))) continue;
+            if (ll.right_boundary && (word(s[p + m - 1]) == (p + m < n && word(s[p + m])))) continue;
+            return 1;
+        }
+    }
+    return 0;
 }
 int lp_debug_rx_anchor(void* h) { return static_cast<DebugRx*>(h)->anchor; }
 // What k_confirm decides for an anchored regex: some occurrence of one of its literals at which the

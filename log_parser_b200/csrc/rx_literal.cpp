@@ -228,6 +228,15 @@ bool is_word_set(const CpSet& s) {
 }
 inline bool word_byte_l(unsigned char b) { return (b >= '0' && b <= '9') || (b >= 'A' && b <= 'Z') || b == '_' || (b >= 'a' && b <= 'z'); }
 
+// walk() treats zero-width nodes as the empty string, which is sound for "every match contains this
+// literal" but not for deciding a match: a branch that hides an assertion, a look-around or a
+// back-reference anywhere inside (e.g. `word(?: \A)`) is not a plain literal.
+bool has_zero_width_or_backref(const Ast& a) {
+    if (a.kind == AstKind::Assert || a.kind == AstKind::Look || a.kind == AstKind::Backref) return true;
+    for (const auto& k : a.kids) if (has_zero_width_or_backref(*k)) return true;
+    return false;
+}
+
 bool local_branch(const Ast* br, std::vector<LocalLiteral>& out, size_t min_len) {
     br = strip_groups(br);
     std::vector<const Ast*> kids;
@@ -242,7 +251,7 @@ bool local_branch(const Ast* br, std::vector<LocalLiteral>& out, size_t min_len)
     if (lo >= hi) return false;
     LitSet acc = EMPTY_WORD;
     for (size_t i = lo; i < hi; ++i) {
-        if (kids[i]->kind == AstKind::Assert || kids[i]->kind == AstKind::Look || kids[i]->kind == AstKind::Backref) return false;
+        if (has_zero_width_or_backref(*kids[i])) return false;
         Info ki = walk(*kids[i], min_len);
         if (!ki.exact) return false;
         LitSet nx;

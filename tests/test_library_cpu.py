@@ -114,6 +114,36 @@ def test_anchored_verification_equals_line_walk(lib, oracle):
                 assert bool(d.match_anchored(t)) == o.find(t), (pat, t)
 
 
+def test_boundary_form_decision_vs_oracle_random(lib, oracle):
+    """Regexes of the shape [\\b][\\w*]LITERAL[\\b] are decided on the device by looking at the bytes next to the
+    literal occurrence. The host mirror of that decision against the oracle, on patterns built to look
+    like that shape while hiding assertions, groups and alternations inside (`word(?: \\A)` once slipped
+    through: nested zero-width nodes must disqualify the form)."""
+    assert binding.DebugRegex("1234ms(?i: \\A)").match_local("x1234ms ") == -2
+    assert binding.DebugRegex("\\b(WARN|WARNING)\\b", 2).match_local("a warn b") == 1
+    rng = random.Random(5)
+    words = ["ERRx", "abc_1", "Exception", "x-1:E"]
+    checked = 0
+    for _ in range(2500):
+        a, _p = Gen(rng, regular_only=True, max_depth=2).regex()
+        w = rng.choice(words)
+        wj = "".join("\\" + c if c in ".-:" else c for c in w)
+        j = [wj + a, a + wj, "\\b" + wj + "\\b", "\\b\\w*" + wj + "\\b", "(?:" + a + "|" + wj + ")", wj + "(?:" + a + ")"][rng.randrange(6)]
+        try:
+            o = oracle.Regex(j)
+            d = binding.DebugRegex(j)
+        except Exception:
+            continue
+        for _k in range(6):
+            t = "".join(rng.choice([rng.choice(words), gen_text(rng, 5)]) for _ in range(rng.randint(0, 3)))
+            r = d.match_local(t)
+            if r == -2:
+                break
+            assert bool(r) == o.find(t), (j, t)
+            checked += 1
+    assert checked > 3000
+
+
 def test_match_spans_vs_oracle_random(lib, oracle):
     """Matcher.start()/end() of the first find() from the bytecode engine (what k_spans runs) against the
     oracle: leftmost start, end by java.util.regex's priorities (ordered alternation, greedy/lazy/possessive)."""
