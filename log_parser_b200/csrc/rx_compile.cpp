@@ -183,6 +183,28 @@ struct Builder {
     }
 };
 
+// Unanchored search: a prefix loop in front of the pattern that skips whole UTF-8 code points, so that a
+// match (and the zero-width assertions at its start) is only ever tried at a code point boundary -- the
+// positions java.util.regex knows. A byte-wise loop would let `\B` or an empty match succeed between the
+// two bytes of "é". Malformed sequences are skipped byte-wise.
+void add_search_loop(Nfa& nfa, int start) {
+    const int c1 = nfa.add(), c2 = nfa.add(), c3 = nfa.add();      // 1, 2, 3 continuation bytes still to come
+    auto lead_edges = [&](int from) {
+        nfa.st[from].edges.push_back({0x00, 0x7F, start});
+        nfa.st[from].edges.push_back({0xC0, 0xC1, start});
+        nfa.st[from].edges.push_back({0xC2, 0xDF, c1});
+        nfa.st[from].edges.push_back({0xE0, 0xEF, c2});
+        nfa.st[from].edges.push_back({0xF0, 0xF4, c3});
+        nfa.st[from].edges.push_back({0xF5, 0xFF, start});
+    };
+    lead_edges(start);
+    nfa.st[start].edges.push_back({0x80, 0xBF, start});             // stray continuation byte
+    lead_edges(c1); lead_edges(c2); lead_edges(c3);                 // truncated sequence: resynchronise
+    nfa.st[c1].edges.push_back({0x80, 0xBF, start});
+    nfa.st[c2].edges.push_back({0x80, 0xBF, c1});
+    nfa.st[c3].edges.push_back({0x80, 0xBF, c2});
+}
+
 struct Ctx {  // left context carried in a DFA state
     bool prev_word = false, at_begin = false, at_tpos = false;
     int bits() const { return (prev_word ? 1 : 0) | (at_begin ? 2 : 0) | (at_tpos ? 4 : 0); }
@@ -239,7 +261,7 @@ bool build_dfa_impl(const Ast& root, Dfa& out, const DfaLimits& lim, int mode) {
     try {
         Builder b(nfa, mode == 2);
         start = nfa.add();
-        if (mode == 0) nfa.st[start].edges.push_back({0x00, 0xFF, start});   // unanchored search: a self-looping prefix state
+        if (mode == 0) add_search_loop(nfa, start);
         Frag f = b.build(root);
         nfa.st[start].eps.push_back(f.in);
         nfa.accept = f.out;
@@ -418,7 +440,7 @@ bool build_multi_dfa(const std::vector<const Ast*>& roots, MultiDfa& out, uint32
         for (int k = 0; k < K; ++k) {
             const size_t first = nfa.st.size();
             starts[k] = nfa.add();
-            nfa.st[starts[k]].edges.push_back({0x00, 0xFF, starts[k]});
+            add_search_loop(nfa, starts[k]);
             Frag f = b.build(*roots[k]);
             nfa.st[starts[k]].eps.push_back(f.in);
             accepts[k] = f.out;

@@ -114,6 +114,44 @@ def test_anchored_verification_equals_line_walk(lib, oracle):
                 assert bool(d.match_anchored(t)) == o.find(t), (pat, t)
 
 
+def test_non_ascii_texts_vs_oracle_random(lib, oracle):
+    """The automata work on UTF-8 bytes, java.util.regex on UTF-16 units: on texts with two- and three-byte
+    characters and Java's extra line terminators the DFA, the anchored automata, the bytecode engine and the
+    spans must still agree with the oracle. (A pattern that can match the empty string next to `\\B` once
+    matched between the two bytes of a character: the search loop now advances by whole code points.)"""
+    j = "(?i)ERRxx\\-*|((1{0,2}a)x[_]|\\S|(a*?\\.?:).)\\-{2}?|((a{2}R{2,})?|(:{2}?)){2,}\\B"
+    assert binding.DebugRegex(j).match("x\u00e9E E") == 0 and not oracle.Regex(j).find("x\u00e9E E")
+    alphabet = "abcERx_1 .-:\r\u00e9\u20ac\u0085\u2028"
+    rng = random.Random(99)
+    checked = 0
+    for it in range(1200):
+        rx, _p = Gen(rng, regular_only=(it % 3 != 0)).regex()
+        try:
+            o = oracle.Regex(rx)
+            d = binding.DebugRegex(rx)
+        except Exception:
+            continue
+        for _k in range(8):
+            t = "".join(rng.choice(alphabet) for _ in range(rng.randint(0, 16)))
+            m = d.match(t)
+            if m < 0:
+                continue
+            e = o.find(t)
+            assert bool(m) == e, (rx, t)
+            if d.anchor:
+                assert bool(d.match_anchored(t)) == e, (rx, t, d.anchor)
+            try:
+                sp = d.span(t)
+            except binding.LpError:
+                continue
+            so = o.span(t)
+            if so is not None:
+                so = (len(t[:so[0]].encode("utf-8")), len(t[:so[1]].encode("utf-8")))
+            assert sp == so, (rx, t)
+            checked += 1
+    assert checked > 6000
+
+
 def test_boundary_form_decision_vs_oracle_random(lib, oracle):
     """Regexes of the shape [\\b][\\w*]LITERAL[\\b] are decided on the device by looking at the bytes next to the
     literal occurrence. The host mirror of that decision against the oracle, on patterns built to look
