@@ -1,3 +1,5 @@
+"""Wall time of one device-resident lp_analyze_device call: the raw C call, the Python wrapper, and the
+first-to-last-kernel time the library reports, on C2. Tuning aid (run on a GPU box)."""
 import sys, time, ctypes as C
 sys.path.insert(0, ".")
 import numpy as np, torch
