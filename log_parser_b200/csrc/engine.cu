@@ -161,7 +161,7 @@ struct lp_ctx {
     DevBuf items, ss_keys, ss_idx;
     size_t est_items = 0;
     int occ_confirm = 0, occ_resolve = 0;
-    DevBuf cand, tasks, vm_tasks, vm_stack, recs, recs_alt, cub_tmp, rx_begin, ctx_flags;
+    DevBuf cand, tasks, vm_tasks, vm_tasks_alt, vm_stack, recs, recs_alt, cub_tmp, rx_begin, ctx_flags;
     DevBuf ev_key, ev_key_alt, ev_log, slot_key, slot_key_alt, ev_idx, ev_idx_alt, rank_in_slot, freq_delta, prior;
     DevBuf out_arena, sort_key, sort_key_alt, order, order_alt, log_sorted, log_sorted_alt;
     DevBuf log_event_begin, n_unique;
@@ -442,6 +442,8 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     const uint32_t n_always = (uint32_t)c->plan.always_list.size();
     const uint32_t n_always_vm = (uint32_t)c->plan.always_vm_list.size();
     const bool has_vm = c->plan.n_vm > 0;
+    // one thread per (line, regex) evaluation with a private 16 KB backtracking stack (620 MB of stacks, allocated only
+    // when such patterns exist; four times as many threads measured no faster: the kernel is bound by divergence)
     const uint32_t vm_grid = (uint32_t)c->n_sm * 2, vm_block = 128;
 
     // first-call estimates (later calls reuse what earlier logs needed; an under-estimate costs one re-run)
@@ -474,7 +476,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     c->cand.ensure(c->est_cand * 4);
     c->tasks.ensure(c->est_tasks * 8);
     c->items.ensure(c->est_items * 8 * N_CLASSES);
-    if (has_vm) { c->vm_tasks.ensure(c->est_vm_tasks * 8); c->vm_stack.ensure((size_t)vm_grid * vm_block * lpx::VM_STACK_WORDS * 4); }
+    if (has_vm) { c->vm_tasks.ensure(c->est_vm_tasks * 8); c->vm_tasks_alt.ensure(c->est_vm_tasks * 8); c->vm_stack.ensure((size_t)vm_grid * vm_block * lpx::VM_STACK_WORDS * 4); }
     c->recs.ensure(rec_cap * 8);
     c->recs_alt.ensure(rec_cap * 8);
     c->rx_begin.ensure((size_t)(c->dp.n_rx + 2) * 4);
@@ -523,6 +525,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     CK(cudaMemcpyAsync(c->log_off.p, h_off, (n_logs + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
     CK(cudaMemsetAsync(c->recs.p, 0xFF, rec_cap * 8, st));            // padding sentinels sort last
     CK(cudaMemsetAsync(c->ev_key_alt.p, 0xFF, ev_cap * 8, st));
+    if (has_vm) CK(cudaMemsetAsync(c->vm_tasks.p, 0xFF, c->est_vm_tasks * 8, st));      // padding sorts behind the tasks
     if (!c->plan.ctx_any_in_groups) CK(cudaMemsetAsync(c->ctx_flags.p, 0, (line_cap / 4 + 2) * 4, st));   // else k_dfa_scan writes every byte
     k_scan_tiles<<<1, 1024, 0, st>>>(c->tile_counts.as<uint32_t>(), n_tiles, n_logs, ctr);
     ScanArgs sa{};
@@ -566,7 +569,15 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         c->launches += 1;
         k_verify<<<c->n_sm * 8, 256, 0, st>>>(va, c->dp);
         c->launches += 2;
-        if (has_vm) { k_verify_vm<<<vm_grid, vm_block, 0, st>>>(va, c->dp); c->launches += 1; }
+        if (has_vm) {
+            // tasks sorted by (regex, line): the lanes of a warp then interpret the same program on neighbouring
+            // lines and stay together far longer than with tasks in arrival order
+            sort_keys<unsigned long long>(c, c->vm_tasks.as<unsigned long long>(), c->vm_tasks_alt.as<unsigned long long>(), va.vm_task_cap,
+                                          std::min<int>(64, 32 + bits_for(c->dp.n_rx)));
+            va.vm_tasks = c->vm_tasks_alt.as<unsigned long long>();
+            k_verify_vm<<<vm_grid, vm_block, 0, st>>>(va, c->dp);
+            c->launches += 1;
+        }
     }
     if (n_always) { k_verify_always<<<std::min<uint32_t>(blocks_for(line_cap, 256), c->n_sm * 8), 256, 0, st>>>(va, c->dp); c->launches += 1; }
     if (n_always_vm) { k_verify_vm_always<<<vm_grid, vm_block, 0, st>>>(va, c->dp); c->launches += 1; }
@@ -948,7 +959,7 @@ void lp_destroy(lp_ctx* c) {
     cudaStreamSynchronize(c->stream);
     for (auto& b : c->plan_bufs) b.release();
     DevBuf* all[] = {&c->text, &c->log_off, &c->tile_counts, &c->counters, &c->line_start, &c->line_end, &c->first_line, &c->n_lines,
-                     &c->cand, &c->tasks, &c->vm_tasks, &c->vm_stack, &c->recs, &c->recs_alt, &c->cub_tmp, &c->rx_begin, &c->ctx_flags, &c->ev_key, &c->ev_key_alt,
+                     &c->cand, &c->tasks, &c->vm_tasks, &c->vm_tasks_alt, &c->vm_stack, &c->recs, &c->recs_alt, &c->cub_tmp, &c->rx_begin, &c->ctx_flags, &c->ev_key, &c->ev_key_alt,
                      &c->ev_log, &c->slot_key, &c->slot_key_alt, &c->ev_idx, &c->ev_idx_alt, &c->rank_in_slot, &c->freq_delta, &c->prior,
                      &c->out_arena, &c->sort_key, &c->sort_key_alt, &c->order, &c->order_alt,
                      &c->log_sorted, &c->log_sorted_alt, &c->log_event_begin, &c->n_unique, &c->d_lut,
