@@ -52,7 +52,7 @@ struct VmView {
 
 constexpr uint32_t VM_MAX_SLOTS = 64;
 constexpr uint32_t VM_STACK_WORDS = 4096;     // backtracking stack per (line, regex) evaluation: 2048 entries
-constexpr int VM_MAX_STEPS = 1 << 22;          // interpreter steps per (line, regex) evaluation
+constexpr int VM_MAX_STEPS = 1 << 26;          // interpreter steps per (line, regex) evaluation
 constexpr uint32_t VM_NONE = 0xFFFFFFFFu;
 
 // stack entry kinds (top 4 bits of word 0)
