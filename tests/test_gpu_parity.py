@@ -750,3 +750,44 @@ def test_random_regexes_with_literals_through_the_pipeline(parser, oracle):
         checked += 1
         n_events += len(exp)
     assert checked >= 20 and n_events > 2000
+
+
+def test_concurrent_requests_from_threads(parser):
+    """AnalysisService.analyze is called from several Quarkus worker threads at once (AS:35,50): calls on one
+    shared context serialise inside the library, calls on separate contexts overlap on the GPU; every
+    result must equal the single-threaded one, and results stay valid after later calls reused the buffers."""
+    import threading
+
+    wl = synth.make_patterns(40, 3131, noliteral=1)
+    logs = [synth.make_log(wl, 3000 + 500 * i, 3200 + i, hit_rate=0.05, pool_blocks=500) for i in range(4)]
+    parser.load_patterns(wl.patterns)
+    expect = [parser.analyze(lg) for lg in logs]
+    kept = [(np.array(r.line), np.array(r.pattern), np.array(r.score), np.array(r.rank)) for r in expect]
+    second = binding.LogParser(ScoringConfig())
+    second.load_patterns(wl.patterns)
+    out, errors = {}, []
+
+    def worker(tid, lp):
+        try:
+            for rep in range(6):
+                k = (tid + rep) % len(logs)
+                r = lp.analyze(logs[k])
+                out[(tid, rep)] = (k, r)
+        except Exception as e:      # noqa: BLE001
+            errors.append(e)
+
+    threads = [threading.Thread(target=worker, args=(t, parser if t < 3 else second)) for t in range(5)]
+    for th in threads:
+        th.start()
+    for th in threads:
+        th.join()
+    second.close()
+    assert not errors, errors
+    assert len(out) == 30
+    for (_tid, _rep), (k, r) in out.items():
+        np.testing.assert_array_equal(r.line, kept[k][0])
+        np.testing.assert_array_equal(r.pattern, kept[k][1])
+        np.testing.assert_array_equal(r.score, kept[k][2])
+        np.testing.assert_array_equal(r.rank, kept[k][3])
+    for r, kp in zip(expect, kept):        # the first results are still intact (each owns its page-locked buffer)
+        np.testing.assert_array_equal(r.score, kp[2])
