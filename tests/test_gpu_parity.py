@@ -791,3 +791,39 @@ def test_concurrent_requests_from_threads(parser):
         np.testing.assert_array_equal(r.rank, kept[k][3])
     for r, kp in zip(expect, kept):        # the first results are still intact (each owns its page-locked buffer)
         np.testing.assert_array_equal(r.score, kp[2])
+
+
+def test_argument_errors_are_reported_not_computed():
+    """Error behaviour at the boundary: bad calls come back as LP_ERR_INVALID with a message, never as a result."""
+    import torch
+
+    lp = binding.LogParser(ScoringConfig())
+    try:
+        with pytest.raises(binding.LpError) as e:
+            lp.analyze(b"x\n")                                      # no pattern set loaded
+        assert e.value.code == binding.LP_ERR_INVALID and "lp_load_patterns" in str(e.value)
+        lp.load_patterns([PatternSpec(id="a", primary_regex="x", confidence=0.5, severity="LOW")])
+        dev = torch.zeros(64, dtype=torch.uint8, device="cuda")
+        with pytest.raises(binding.LpError) as e:
+            lp.analyze_device(dev.data_ptr() + 1, 8)                # device pointer not 16-byte aligned
+        assert e.value.code == binding.LP_ERR_INVALID
+        with pytest.raises(binding.LpError) as e:
+            lp.analyze_batch_device(dev.data_ptr(), np.array([0, 8, 4], np.uint64))     # offsets go backwards
+        assert e.value.code == binding.LP_ERR_INVALID
+        with pytest.raises(binding.LpError) as e:
+            lp.batch_score()                                        # no scan pending
+        assert e.value.code == binding.LP_ERR_INVALID
+        with pytest.raises(binding.LpError) as e:
+            lp.range_score(np.zeros((1, lp.range_summary_words()), np.uint64), 0, 1)    # no range scan pending
+        assert e.value.code == binding.LP_ERR_INVALID
+        with pytest.raises(binding.LpError) as e:
+            lp.analyze_batch_dist_device(dev.data_ptr(), np.array([0, 8], np.uint64))   # lp_comm_init not called
+        assert e.value.code == binding.LP_ERR_INVALID
+        with pytest.raises(binding.LpError) as e:
+            lp.load_patterns([PatternSpec(id="a", primary_regex="x", confidence=0.5, severity="LOW", lines_before=-1, lines_after=2)])
+        assert e.value.code == binding.LP_ERR_INVALID
+        # the context is still usable after every one of them
+        lp.load_patterns([PatternSpec(id="a", primary_regex="x", confidence=0.5, severity="LOW")])
+        assert lp.analyze(b"x\ny\n").n_events == 1
+    finally:
+        lp.close()
