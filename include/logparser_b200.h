@@ -123,7 +123,10 @@ int lp_load_patterns(lp_ctx* ctx, const lp_pattern_desc* patterns, size_t n_patt
 /* ---- the hot path ------------------------------------------------------------------------ */
 /* Replaces AS:53-113 for one request: split, scan, score. `log` is host memory (UTF-8 of
  * PodFailureData.logs). prior_count[p] = matches of pattern p already inside the sliding
- * frequency window at request start (FTS state stays on the JVM); NULL = all zero. */
+ * frequency window at request start (FTS state stays on the JVM); NULL = all zero.
+ * FrequencyTrackingService keys its counts by pattern id (FTS:46-50): patterns that carry the same id
+ * share one count. Pass the id's count in the entry of every pattern with that id (the library reads
+ * the first one); freq_delta[] comes back per pattern, to be summed per id by the caller. */
 int lp_analyze(lp_ctx* ctx, const uint8_t* log, size_t len, const uint64_t* prior_count,
                int options, lp_result** out);
 
