@@ -149,6 +149,9 @@ int lp_analyze_batch_device(lp_ctx* ctx, const uint8_t* d_logs, const uint64_t* 
 int lp_batch_scan_device(lp_ctx* ctx, const uint8_t* d_logs, const uint64_t* offsets, size_t n_logs,
                          int options, uint64_t* counts_out /* [n_patterns] */);
 int lp_batch_score(lp_ctx* ctx, const uint64_t* prior_count, lp_result** out);
+/* For hosts that add the lower ranks' counts themselves: out[p] = sum of in[q] over the patterns q that carry
+ * pattern p's id (FTS:46-50 keys the counts by id; 0 for untracked patterns). Pure host code. */
+int lp_counts_by_id(const lp_ctx* ctx, const uint64_t* in /* [n_patterns] */, uint64_t* out /* [n_patterns] */);
 
 /* The same two phases with the exchange kept on the device (no host round trip between them):
  * phase 1 only enqueues work on lp_stream() and writes [n_patterns counts, 1 status word] to

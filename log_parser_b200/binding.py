@@ -86,7 +86,7 @@ EXPORTS = [
     "lp_create", "lp_destroy", "lp_last_error", "lp_version", "lp_load_patterns", "lp_analyze", "lp_analyze_device",
     "lp_analyze_batch", "lp_analyze_batch_device", "lp_batch_scan_device", "lp_batch_score", "lp_result_get",
     "lp_result_free", "lp_get_timings", "lp_stream", "lp_split_lines_noalloc",
-    "lp_batch_scan_device_async", "lp_batch_score_gathered", "lp_comm_unique_id", "lp_comm_init",
+    "lp_counts_by_id", "lp_batch_scan_device_async", "lp_batch_score_gathered", "lp_comm_unique_id", "lp_comm_init",
     "lp_analyze_batch_dist_device", "lp_range_halo_lines", "lp_range_summary_words", "lp_range_scan_device", "lp_range_score",
 ]
 
@@ -120,6 +120,7 @@ def load_library() -> C.CDLL:
     L.lp_get_timings.argtypes = [vp, C.POINTER(Timings)]
     L.lp_stream.restype = vp
     L.lp_stream.argtypes = [vp]
+    L.lp_counts_by_id.argtypes = [vp, u64p, u64p]
     L.lp_batch_scan_device_async.argtypes = [vp, u8p, u64p, C.c_size_t, C.c_int, vp]
     L.lp_batch_score_gathered.argtypes = [vp, vp, C.c_uint32, C.c_uint32, u64p, C.POINTER(vp)]
     L.lp_comm_unique_id.argtypes = [vp]
@@ -384,6 +385,15 @@ class LogParser:
         if rc != LP_OK:
             _raise(rc)
         return self._take(out)
+
+    def counts_by_id(self, counts) -> np.ndarray:
+        """Sums per-pattern counts over the patterns that share an id (the key of FrequencyTrackingService)."""
+        a = np.ascontiguousarray(counts, dtype=np.uint64)
+        out = np.zeros(max(1, self.n_patterns), np.uint64)
+        rc = self.L.lp_counts_by_id(self.h, a.ctypes.data_as(C.POINTER(C.c_uint64)), out.ctypes.data_as(C.POINTER(C.c_uint64)))
+        if rc != LP_OK:
+            _raise(rc)
+        return out[: self.n_patterns]
 
     def batch_scan_device_async(self, dev_ptr: int, offsets, counts_dev_ptr: int, options: int = 0) -> None:
         oa, op = self._offsets(offsets)

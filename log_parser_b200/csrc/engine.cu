@@ -1188,7 +1188,7 @@ int lp_analyze_batch_dist_device(lp_ctx* c, const uint8_t* d_logs, const uint64_
             nccl_check(nccl().AllGather(mine, c->dist_all.p, words, NCCL_UINT64, c->nccl_comm, c->copy_stream), "ncclAllGather");
             k_prior_prefix<<<blocks_for(std::max<uint32_t>(np, 1), 128), 128, 0, c->copy_stream>>>(
                 c->dist_all.as<unsigned long long>(), np, rank, world, prior_in, c->prior_eff.as<unsigned long long>(),
-                c->any_flag.as<unsigned long long>());
+                c->any_flag.as<unsigned long long>(), c->dp);
             CK(cudaEventRecord(c->dist_ev[1], c->copy_stream));
             c->launches += 4;
         };
@@ -1253,7 +1253,7 @@ int lp_batch_score_gathered(lp_ctx* c, const uint64_t* d_all_counts, uint32_t ra
         }
         k_prior_prefix<<<blocks_for(std::max<uint32_t>(np, 1), 128), 128, 0, c->stream>>>(
             reinterpret_cast<const unsigned long long*>(d_all_counts), np, rank, world, prior_in, c->prior_eff.as<unsigned long long>(),
-            c->any_flag.as<unsigned long long>());
+            c->any_flag.as<unsigned long long>(), c->dp);
         c->launches += 1;
         std::unique_ptr<lp_result> res;
         unsigned long long flag = 0;
@@ -1265,6 +1265,20 @@ int lp_batch_score_gathered(lp_ctx* c, const uint64_t* d_all_counts, uint32_t ra
         *out = res.release();
     });
     return rc != LP_OK ? rc : (again ? LP_RETRY : LP_OK);
+}
+
+// Host-side helper for callers that run the exchange themselves: frequency counts are kept per pattern id
+// (FTS:46-50), so the count a pattern sees is the sum over every pattern carrying its id.
+int lp_counts_by_id(const lp_ctx* c, const uint64_t* in, uint64_t* out) {
+    if (!c || !in || !out) { g_last_error = "NULL argument"; return LP_ERR_INVALID; }
+    if (!c->loaded) { g_last_error = "lp_load_patterns has not been called"; return LP_ERR_INVALID; }
+    for (uint32_t p = 0; p < c->plan.n_pat; ++p) {
+        const int slot = c->plan.pat_slot[p];
+        uint64_t v = 0;
+        if (slot >= 0) for (uint32_t j = c->plan.slot_begin[slot]; j < c->plan.slot_begin[slot + 1]; ++j) v += in[c->plan.slot_pats[j]];
+        out[p] = v;
+    }
+    return LP_OK;
 }
 
 // ---- one log sharded by line range (second mode)
@@ -1339,7 +1353,10 @@ int lp_range_score(lp_ctx* c, const uint64_t* summaries, uint32_t rank, uint32_t
         std::vector<uint64_t> prior(std::max<uint32_t>(np, 1), 0);
         for (uint32_t p = 0; p < np; ++p) {
             prior[p] = prior_count ? prior_count[p] : 0;
-            for (uint32_t r = 0; r < rank; ++r) prior[p] += summaries[(size_t)r * words + 2 + p];
+            const int slot = c->plan.pat_slot[p];          // counts are kept per pattern id (FTS:46-50): add the whole id's events
+            if (slot < 0) continue;
+            for (uint32_t j = c->plan.slot_begin[slot]; j < c->plan.slot_begin[slot + 1]; ++j)
+                for (uint32_t r = 0; r < rank; ++r) prior[p] += summaries[(size_t)r * words + 2 + c->plan.slot_pats[j]];
         }
         // per sequence: the line where its last-but-one event is first reachable, walking the shards in order
         std::vector<long long> seq_T(std::max<uint32_t>(c->n_seq, 1), -1);

@@ -297,12 +297,19 @@ __global__ void k_range_tables(const unsigned long long* __restrict__ keys, cons
 // (all-gathered); prior_out[p] = window prior + the counts of the lower ranks; *any_flag = OR of the overflow words.
 __global__ void k_prior_prefix(const unsigned long long* __restrict__ all, uint32_t n_pat, uint32_t rank, uint32_t world,
                                const unsigned long long* __restrict__ prior_in, unsigned long long* __restrict__ prior_out,
-                               unsigned long long* __restrict__ any_flag) {
+                               unsigned long long* __restrict__ any_flag, DevPlan P) {
     const uint32_t p = blockIdx.x * blockDim.x + threadIdx.x;
     const size_t stride = (size_t)n_pat + 1;
     if (p < n_pat) {
+        // FrequencyTrackingService keys its counts by pattern id: what the lower ranks add to pattern p's count
+        // is the sum over every pattern that carries p's id
         unsigned long long v = prior_in ? prior_in[p] : 0ull;
-        for (uint32_t r = 0; r < rank; ++r) v += all[r * stride + p];
+        const int slot = P.pat_slot[p];
+        if (slot >= 0)
+            for (uint32_t j = P.slot_begin[slot]; j < P.slot_begin[slot + 1]; ++j) {
+                const uint32_t q = P.slot_pats[j];
+                for (uint32_t r = 0; r < rank; ++r) v += all[r * stride + q];
+            }
         prior_out[p] = v;
     }
     if (p == 0) {

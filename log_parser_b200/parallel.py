@@ -68,6 +68,8 @@ def analyze_batch_sharded(engine: Engine, logs: Sequence[bytes], rank: int, worl
     n_pat = engine.n_patterns
     counts = np.asarray(engine.scan(logs[lo:hi]), dtype=np.uint64) if hi > lo else np.zeros(n_pat, np.uint64)
     before, total = exclusive_prefix(counts, rank, world_size, group)      # every rank takes part, even with no logs
+    if hasattr(engine, "by_id"):                                            # counts are kept per pattern id (FTS:46-50)
+        before = np.asarray(engine.by_id(before), dtype=np.uint64)
     prior = before if prior_count is None else before + np.asarray(prior_count, dtype=np.uint64)
     return (engine.score(prior) if hi > lo else None), (lo, hi), total
 
@@ -92,6 +94,9 @@ class GpuBatchEngine:
 
     def score(self, prior: np.ndarray):
         return self.lp.batch_score(prior)
+
+    def by_id(self, counts: np.ndarray) -> np.ndarray:
+        return self.lp.counts_by_id(counts)
 
 
 

@@ -827,3 +827,65 @@ def test_argument_errors_are_reported_not_computed():
         assert lp.analyze(b"x\ny\n").n_events == 1
     finally:
         lp.close()
+
+
+def test_shared_pattern_ids_across_shards(parser, oracle):
+    """FrequencyTrackingService keys its counts by pattern id (FTS:46-50), so several patterns can feed one
+    count. Sharded over ranks, what the lower ranks add to a pattern's count is the sum over every pattern
+    with its id -- checked for line-range shards and for the by-log exchange, against the whole-input
+    result and the oracle, with a low threshold so that the penalty is in play everywhere."""
+    import dataclasses
+    import torch
+    from log_parser_b200 import parallel
+
+    cfg = ScoringConfig(frequency_threshold=3.0)
+    wl = synth.make_patterns(24, 8181, noliteral=1)
+    pats = [dataclasses.replace(p, id=f"shared-{k % 4}") for k, p in enumerate(wl.patterns)]
+    log = synth.make_log(wl, 6000, 8182, hit_rate=0.08, pool_blocks=900)
+    lp = binding.LogParser(cfg)
+    lp.load_patterns(pats)
+    whole = lp.analyze(log, options=binding.OPT_FACTORS)
+    ora = oracle.analyze(cfg, pats, log)
+    _check(whole, ora)
+    assert (whole.factors[:, 6] > 0).mean() > 0.5
+    # one log by line range
+    results, _ = _range_sharded(cfg, pats, log, 3)
+    np.testing.assert_array_equal(np.concatenate([r.line for r in results]), whole.line)
+    np.testing.assert_array_equal(np.concatenate([r.score for r in results]), whole.score)
+    # a batch by log: two contexts play two ranks of the device-side exchange
+    logs = [synth.make_log(wl, n, 8190 + i, hit_rate=0.08, pool_blocks=400) for i, n in enumerate([700, 300, 900, 500])]
+    batch = lp.analyze_batch(logs)
+    lps = [binding.LogParser(cfg) for _ in range(2)]
+    try:
+        for q in lps:
+            q.load_patterns(pats)
+        n = len(pats) + 1
+        gathered = torch.zeros(2 * n, dtype=torch.int64, device="cuda")
+        bounds = parallel.shard_bounds([len(x) for x in logs], 2)
+        texts, offs = [], []
+        for lo, hi in bounds:
+            off = np.zeros(hi - lo + 1, np.uint64)
+            np.cumsum([len(x) for x in logs[lo:hi]], out=off[1:])
+            texts.append(torch.from_numpy(np.frombuffer(b"".join(logs[lo:hi]), dtype=np.uint8).copy()).cuda())
+            offs.append(off)
+        for _round in range(8):
+            for r in range(2):
+                lps[r].batch_scan_device_async(texts[r].data_ptr(), offs[r], gathered[r * n:].data_ptr())
+            torch.cuda.synchronize()
+            res = [lps[r].batch_score_gathered(gathered.data_ptr(), r, 2) for r in range(2)]
+            if res[0] is not None and res[1] is not None:
+                break
+        np.testing.assert_array_equal(np.concatenate([r.score for r in res]), batch.score)
+        # and with the counts passing through the host
+        eng = parallel.GpuBatchEngine(lps[0])
+        prior = np.zeros(len(pats), np.uint64)
+        scores = []
+        for lo, hi in bounds:
+            counts = eng.scan(logs[lo:hi])
+            scores.append(eng.score(prior).score)
+            prior = prior + eng.by_id(counts)
+        np.testing.assert_array_equal(np.concatenate(scores), batch.score)
+    finally:
+        for q in lps:
+            q.close()
+        lp.close()
