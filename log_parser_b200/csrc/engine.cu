@@ -595,7 +595,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
             tab_bytes += ((size_t)c->group_words[g0 + q] + 3) / 4 * 16;
         }
         da.rx_record = c->d_rx_record; da.ctx_flags = c->ctx_flags.as<uint8_t>();
-        da.write_flags = (g0 == 0 && c->plan.ctx_any_in_groups) ? 1 : 0;
+        da.write_flags = c->plan.ctx_any_in_groups ? (g0 == 0 ? 1 : 2) : 0;
         da.recs = c->recs.as<unsigned long long>(); da.rec_cap = (uint32_t)rec_cap; da.gb = c->dp.gb; da.ctr = ctr;
         const uint32_t per_sm = (uint32_t)std::max<size_t>(1, std::min<size_t>(8, (200 * 1024) / std::max<size_t>(tab_bytes, 1)));
         const uint32_t grid = std::min<uint32_t>(blocks_for(line_cap, DS_THREADS), (uint32_t)c->n_sm * per_sm);

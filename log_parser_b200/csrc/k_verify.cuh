@@ -527,8 +527,8 @@ struct DfaScanArgs {
     uint32_t blob_words[DS_MAXG];
     uint32_t n_groups;
     const uint8_t* rx_record;
-    uint8_t* ctx_flags;          // written for every line when write_flags
-    int write_flags;
+    uint8_t* ctx_flags;
+    int write_flags;             // 0 leave alone, 1 store every line's flag byte, 2 OR this launch's bits in
     unsigned long long* recs;
     uint32_t rec_cap;
     uint32_t gb;
@@ -604,6 +604,9 @@ __global__ void __launch_bounds__(DS_THREADS) k_dfa_scan(DfaScanArgs a) {
                 }
             }
         }
-        if (a.write_flags) a.ctx_flags[g] = (uint8_t)flags;
+        // every line's flag byte is stored by the first launch (it doubles as the clearing pass); further
+        // launches, when the groups do not fit one, add their bits (a line belongs to one thread)
+        if (a.write_flags == 1) a.ctx_flags[g] = (uint8_t)flags;
+        else if (a.write_flags == 2 && flags) a.ctx_flags[g] = (uint8_t)(a.ctx_flags[g] | flags);
     }
 }

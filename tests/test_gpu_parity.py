@@ -889,3 +889,25 @@ def test_shared_pattern_ids_across_shards(parser, oracle):
         for q in lps:
             q.close()
         lp.close()
+
+
+def test_context_flags_with_many_scan_groups(oracle):
+    """More literal-free regexes than one k_dfa_scan launch holds (4 groups): the stack-trace regex of
+    CAS:27-34 then sits in a later launch, whose flag bits must be added to the bytes the first launch
+    stored (they were once dropped). The case is seed 64 of scripts/fuzz_scoring_vs_oracle.py, which found
+    it: 5 scan groups, the stack-trace regex in the fifth; two more seeds ride along."""
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "scripts"))
+    from fuzz_scoring_vs_oracle import gen_case
+
+    for seed in (64, 18, 5):
+        cfg, pats, log, prior = gen_case(seed)
+        lp = binding.LogParser(cfg)
+        try:
+            lp.load_patterns(pats)
+            res = lp.analyze(log, prior_count=prior, options=binding.OPT_FACTORS)
+        finally:
+            lp.close()
+        ora = oracle.analyze(cfg, pats, log, prior_count=prior)
+        _check(res, ora)
+        np.testing.assert_array_equal(res.score, ora.score)
