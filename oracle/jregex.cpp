@@ -896,6 +896,16 @@ Regex::Regex(const std::string& pattern, int flags) {
     measure(r.get());
     check_lookbehind(r.get());
     ngroups_ = ps.ngroups;
+    {   // a back-reference can see a capture left behind by an attempt at an EARLIER start position (groups are
+        // cleared once per find()), so no start position may be skipped when the pattern has one
+        std::vector<const Node*> todo{r.get()};
+        while (!todo.empty()) {
+            const Node* x = todo.back();
+            todo.pop_back();
+            if (x->kind == N_BACKREF) has_backref_ = true;
+            for (const auto& k : x->kids) todo.push_back(k.get());
+        }
+    }
     bool any = false;
     CharSet fs;
     can_empty_ = first_of(r.get(), fs, any);
@@ -918,9 +928,10 @@ bool Regex::find_cp(const int* t, int n, int* start, int* end) const {
     cx.cap.assign(2 * (size_t)ngroups_, -1);
     int e = -1;
     auto fin = [&](int j) { e = j; return true; };
-    int last = anchored_begin_ && first_opt_ ? 0 : n;
+    const bool skip = first_opt_ && !has_backref_;
+    int last = anchored_begin_ && skip ? 0 : n;
     for (int s = 0; s <= last; ++s) {
-        if (first_opt_ && !can_empty_ && !first_any_) {
+        if (skip && !can_empty_ && !first_any_) {
             if (s >= n) break;
             if (!first_.has(t[s])) continue;
         }

@@ -100,6 +100,7 @@ private:
     NodeP root_;
     int ngroups_ = 1;
     bool first_opt_ = true;
+    bool has_backref_ = false;
     bool can_empty_ = true;
     CharSet first_;      // possible first code points when !can_empty_
     bool first_any_ = true;

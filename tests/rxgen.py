@@ -16,9 +16,12 @@ PY_EOL = "(?=[\\r\\x85\\u2028\\u2029]?\\Z)"
 
 
 class Gen:
-    def __init__(self, rng: random.Random, regular_only: bool = False, max_depth: int = 3):
+    def __init__(self, rng: random.Random, regular_only: bool = False, max_depth: int = 3,
+                 no_backrefs: bool = False, no_group_possessive: bool = False):
         self.rng = rng
         self.regular_only = regular_only
+        self.no_backrefs = no_backrefs                      # the PCRE2 differential keeps capture-state quirks out
+        self.no_group_possessive = no_group_possessive      # Java: X{n,m}+ on a group is atomic per iteration, PCRE2: as a whole
         self.max_depth = max_depth
         self.ngroups = 0
         self.open_groups = []
@@ -97,7 +100,7 @@ class Gen:
             k = self.rng.choice(["=", "!"])
             return "(?<" + k + j + ")", "(?<" + k + p + ")", 0
         closed = [g for g in getattr(self, "closed", []) if g not in self.open_groups]
-        if closed:
+        if closed and not self.no_backrefs:
             g = self.rng.choice(closed)
             return "\\%d" % g, "(?:\\%d)" % g, None
         return self.lit()
@@ -115,7 +118,7 @@ class Gen:
         suffix = ""
         if m < 0.2:
             suffix = "?"
-        elif m < 0.3 and not self.regular_only:
+        elif m < 0.3 and not self.regular_only and not (self.no_group_possessive and j.startswith("(")):
             suffix = "+"
         return j + q + suffix, p + q + suffix, None
 
