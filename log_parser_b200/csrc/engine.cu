@@ -29,6 +29,7 @@ using namespace lpk;
 // ============================================================================================
 namespace {
 #include "k_scan.cuh"
+#include "k_fscan.cuh"
 #include "k_verify.cuh"
 #include "k_score.cuh"
 #include "k_sort.cuh"
@@ -148,7 +149,10 @@ struct lp_ctx {
     const uint8_t* d_rx_record = nullptr;
     uint32_t n_group_record_rx = 0;
     DevBuf f_bitmap, f_key, f_lits, f_bytes;   // prefilter tables (re-uploaded by calibration)
+    DevBuf f_bits, f_gkeys, fs_state;          // fused scan: first-stage bit table, exact gram keys, tickets + look-back words
     const uint8_t* d_byte_table = nullptr;
+    int scan_mode = 0;                         // 0: fused single-pass scan (k_fscan); 1: k_filter_count + k_scan_tiles + k_lines (LP_SCAN_MODE=legacy)
+    int fscan_variant = 0;                     // first-stage lookup of k_fscan: 0 IMAD.HI hash, 1 IMAD+SHF hash, 2 byte table (LP_FSCAN_VARIANT)
     std::vector<uint32_t> lit_off8;   // literal -> offset in the 8-byte aligned device copy of the literal bytes
     bool calibrated = false;
     int recalibrations = 0;
@@ -213,6 +217,15 @@ void upload_filter(lp_ctx* c) {
         for (uint32_t key : pl.table_key) if (key) bt[(key * GRAM_MUL) >> 16] = 1;
         c->d_byte_table = upload_into(c->f_bytes, bt);
     }
+    if (c->fscan_variant != 2) {   // k_fscan: one bit per gram at (row, rotation - 1) of the per-lane table; every lane's copy is the same
+        std::vector<uint32_t> bits(fs::ROWS, 0);
+        for (uint32_t key : pl.table_key) if (key) {
+            const uint32_t H = fs::host_hash(c->fscan_variant, key);
+            bits[(H >> 7) & (fs::ROWS - 1)] |= 1u << ((H + 31u) & 31u);
+        }
+        upload_into(c->f_bits, bits);
+    }
+    upload_into(c->f_gkeys, pl.table_key);
     d.table_bits = pl.table_bits;
     // literal descriptors grouped by gram slot (a literal has exactly one gram)
     auto is_word = [](unsigned char b) { return (b >= '0' && b <= '9') || (b >= 'A' && b <= 'Z') || b == '_' || (b >= 'a' && b <= 'z'); };
@@ -464,7 +477,9 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     c->dp.gb = (uint32_t)bits_for(line_cap);          // record key = regex << gb | line
     c->dp.pb = (uint32_t)bits_for(std::max<uint32_t>(c->dp.n_pat, 1));   // event key = line << pb | pattern
 
-    const uint32_t n_tiles = (uint32_t)((len + 1 + TILE_BYTES - 1) / TILE_BYTES);   // covers position `len` too
+    const bool fused = c->scan_mode == 0;
+    const uint32_t tile_bytes = fused ? fs::TILE : TILE_BYTES;
+    const uint32_t n_tiles = (uint32_t)((len + 1 + tile_bytes - 1) / tile_bytes);   // covers position `len` too
     c->log_off.ensure((n_logs + 1) * sizeof(uint64_t));
     c->tile_counts.ensure((size_t)n_tiles * 4);
     c->counters.ensure(sizeof(Counters));
@@ -489,6 +504,36 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     CK(cudaMemsetAsync(ctr, 0, sizeof(Counters), st));
     CK(cudaEventRecord(c->ev[0], st));
     const size_t smem = use_filter ? 65536 : 0;
+    constexpr uint32_t FS_TICKETS = 32;
+    FscanArgs fz{};
+    if (fused) {
+        // tickets of up to FS_TICKETS launches, then one look-back word per tile; cleared once per call
+        const size_t state_bytes = FS_TICKETS * 4 + (size_t)n_tiles * 8;
+        c->fs_state.ensure(state_bytes);
+        CK(cudaMemsetAsync(c->fs_state.p, 0, state_bytes, st));
+        CK(cudaMemcpyAsync(c->log_off.p, h_off, (n_logs + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
+        fz.text = d_text; fz.len = len; fz.n_tiles = n_tiles;
+        fz.status = reinterpret_cast<unsigned long long*>(c->fs_state.as<uint8_t>() + FS_TICKETS * 4);
+        fz.tile_prefix = c->tile_counts.as<uint32_t>();
+        fz.log_off = c->log_off.as<uint64_t>(); fz.n_logs = n_logs;
+        fz.line_start = c->line_start.as<uint32_t>(); fz.line_end = c->line_end.as<uint32_t>();
+        fz.first_line = c->first_line.as<uint32_t>(); fz.line_cap = (uint32_t)line_cap;
+        fz.bit_table = c->fscan_variant == 2 ? reinterpret_cast<const uint32_t*>(c->d_byte_table) : c->f_bits.as<uint32_t>();
+        fz.gram_keys = c->f_gkeys.as<uint32_t>(); fz.table_bits = c->dp.table_bits;
+        fz.cand = c->cand.as<uint32_t>(); fz.cand_cap = (uint32_t)std::min<size_t>(c->est_cand, 0xFFFFFFFFu); fz.ctr = ctr;
+        fz.use_filter = use_filter ? 1 : 0;
+    }
+    uint32_t fs_launches = 0;
+    auto launch_fscan = [&](uint32_t tile_begin, uint32_t tile_end) {
+        if (fs_launches >= FS_TICKETS) throw std::logic_error("too many scan launches in one call");
+        fz.tile_begin = tile_begin; fz.tile_end = tile_end; fz.ticket = c->fs_state.as<uint32_t>() + fs_launches++;
+        const uint32_t grid = std::max<uint32_t>(1, std::min<uint32_t>((tile_end - tile_begin + 1) / 2, (uint32_t)c->n_sm));
+        switch (c->fscan_variant) {
+            case 1: k_fscan<1><<<grid, fs::THREADS, fs::SMEM_BYTES, st>>>(fz); break;
+            case 2: k_fscan<2><<<grid, fs::THREADS, fs::SMEM_BYTES, st>>>(fz); break;
+            default: k_fscan<0><<<grid, fs::THREADS, fs::SMEM_BYTES, st>>>(fz); break;
+        }
+    };
     FilterArgs fa{};
     fa.text = d_text; fa.len = len; fa.n_tiles = n_tiles; fa.tile_counts = c->tile_counts.as<uint32_t>(); fa.bitmap = c->dp.bitmap; fa.byte_table = c->d_byte_table;
     fa.cand = c->cand.as<uint32_t>(); fa.cand_cap = (uint32_t)std::min<size_t>(c->est_cand, 0xFFFFFFFFu); fa.ctr = ctr;
@@ -501,7 +546,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         const uint8_t* host = c->host_src;
         c->host_src = nullptr;                  // a re-run of this call finds the text on the device
         uint8_t* dst = const_cast<uint8_t*>(d_text);
-        const uint64_t piece = std::max<uint64_t>(((len / 8 + TILE_BYTES) / TILE_BYTES) * TILE_BYTES, 256 * (uint64_t)TILE_BYTES);
+        const uint64_t piece = std::max<uint64_t>(((len / 8 + TILE_BYTES) / TILE_BYTES) * TILE_BYTES, 256 * (uint64_t)TILE_BYTES);   // a multiple of both tile sizes
         CK(cudaEventRecord(c->ev[5], c->copy_stream));
         uint32_t k = 0;
         for (uint64_t off = 0; off < len || k == 0; off += piece, ++k) {
@@ -510,23 +555,26 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
             if (k >= c->chunk_ev.size()) { cudaEvent_t e; CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming)); c->chunk_ev.push_back(e); }
             CK(cudaEventRecord(c->chunk_ev[k], c->copy_stream));
             CK(cudaStreamWaitEvent(st, c->chunk_ev[k], 0));
-            fa.tile_begin = (uint32_t)(off / TILE_BYTES);
-            fa.tile_end = off + n >= len ? n_tiles : (uint32_t)((off + n) / TILE_BYTES);
-            k_filter_count<<<std::min<uint32_t>(fa.tile_end - fa.tile_begin, (uint32_t)c->n_sm * 3), SCAN_THREADS, smem, st>>>(fa);
+            fa.tile_begin = (uint32_t)(off / tile_bytes);
+            fa.tile_end = off + n >= len ? n_tiles : (uint32_t)((off + n) / tile_bytes);
+            if (fused) launch_fscan(fa.tile_begin, fa.tile_end);
+            else k_filter_count<<<std::min<uint32_t>(fa.tile_end - fa.tile_begin, (uint32_t)c->n_sm * 3), SCAN_THREADS, smem, st>>>(fa);
             if (len == 0) break;
         }
         CK(cudaEventRecord(c->ev[8], c->copy_stream));
         c->launches += k - 1;
     } else {
         fa.tile_begin = 0; fa.tile_end = n_tiles;
-        k_filter_count<<<std::min<uint32_t>(n_tiles, (uint32_t)c->n_sm * 3), SCAN_THREADS, smem, st>>>(fa);
+        if (fused) launch_fscan(0, n_tiles);
+        else k_filter_count<<<std::min<uint32_t>(n_tiles, (uint32_t)c->n_sm * 3), SCAN_THREADS, smem, st>>>(fa);
     }
     CK(cudaEventRecord(c->ev[2], st));
-    CK(cudaMemcpyAsync(c->log_off.p, h_off, (n_logs + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
+    if (!fused) CK(cudaMemcpyAsync(c->log_off.p, h_off, (n_logs + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
     CK(cudaMemsetAsync(c->recs.p, 0xFF, rec_cap * 8, st));            // padding sentinels sort last
     CK(cudaMemsetAsync(c->ev_key_alt.p, 0xFF, ev_cap * 8, st));
     if (has_vm) CK(cudaMemsetAsync(c->vm_tasks.p, 0xFF, c->est_vm_tasks * 8, st));      // padding sorts behind the tasks
     if (!c->plan.ctx_any_in_groups) CK(cudaMemsetAsync(c->ctx_flags.p, 0, (line_cap / 4 + 2) * 4, st));   // else k_dfa_scan writes every byte
+    if (!fused) {
     k_scan_tiles<<<1, 1024, 0, st>>>(c->tile_counts.as<uint32_t>(), n_tiles, n_logs, ctr);
     ScanArgs sa{};
     sa.text = d_text; sa.len = len; sa.n_tiles = n_tiles; sa.tile_prefix = c->tile_counts.as<uint32_t>();
@@ -536,9 +584,11 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     sa.cand = nullptr; sa.cand_cap = 0;
     sa.ctr = ctr; sa.use_filter = 0;      // offsets only: the prefilter ran in k_filter_count
     k_lines<<<std::min<uint32_t>(n_tiles, (uint32_t)c->n_sm * 4), LN_TILE_THREADS, 0, st>>>(sa);
+    c->launches += 2;
+    }
     k_log_meta<<<blocks_for(n_logs, 128), 128, 0, st>>>(c->first_line.as<uint32_t>(), c->line_start.as<uint32_t>(),
                                                          c->line_end.as<uint32_t>(), n_logs, (uint32_t)line_cap, rg ? 1u : 0u, c->n_lines.as<uint32_t>());
-    c->launches += 4;
+    c->launches += 2;
 
     VerifyArgs va{};
     va.text = d_text; va.len = len; va.line_start = c->line_start.as<uint32_t>(); va.line_end = c->line_end.as<uint32_t>();
@@ -553,7 +603,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         ca.items = c->items.as<unsigned long long>(); ca.item_cap = (uint32_t)std::min<size_t>(c->est_items, 0xFFFFFFFFu); ca.ctr = ctr;
         ResolveArgs ra{};
         ra.text = d_text; ra.len = len; ra.items = ca.items; ra.item_cap = ca.item_cap;
-        ra.tile_prefix = c->tile_counts.as<uint32_t>(); ra.n_tiles = n_tiles; ra.log_off = c->log_off.as<uint64_t>(); ra.n_logs = n_logs;
+        ra.tile_prefix = c->tile_counts.as<uint32_t>(); ra.n_tiles = n_tiles; ra.tile_bytes = tile_bytes; ra.log_off = c->log_off.as<uint64_t>(); ra.n_logs = n_logs;
         ra.line_start = c->line_start.as<uint32_t>(); ra.line_end = c->line_end.as<uint32_t>(); ra.n_lines_total = (uint32_t)line_cap;
         ra.tasks = c->tasks.as<unsigned long long>(); ra.task_cap = va.task_cap; ra.ctr = ctr;
         ra.vm_tasks = c->vm_tasks.as<unsigned long long>(); ra.vm_task_cap = va.vm_task_cap;
@@ -832,7 +882,10 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
     c->tm.candidates = h.n_cand;
     c->tm.verify_tasks = (uint64_t)h.n_tasks + h.n_vm_tasks + (uint64_t)G * (c->plan.always_list.size() + c->plan.always_vm_list.size());
     // k_filter_count: the log read once, one count per tile and one position per candidate written
-    c->tm.scan_bytes = c->pend.len + 4ull * ((c->pend.len + TILE_BYTES) / TILE_BYTES) + 4ull * h.n_cand;
+    // algorithmic bytes of the scan kernel(s) timed as scan_ms. Fused scan: the log read once, line_start + line_end
+    // written, one prefix per tile, one position per candidate. Legacy k_filter_count: log, tile counts, candidates.
+    if (c->scan_mode == 0) c->tm.scan_bytes = c->pend.len + 8ull * G + 4ull * ((c->pend.len + fs::TILE) / fs::TILE) + 4ull * h.n_cand;
+    else c->tm.scan_bytes = c->pend.len + 4ull * ((c->pend.len + TILE_BYTES) / TILE_BYTES) + 4ull * h.n_cand;
     c->tm.dfa_scan_bytes = c->d_group_blob.empty() ? 0 : c->pend.len + 8ull * ((uint64_t)G + 1) + (uint64_t)G;
     if (!c->plan.lit_off.empty() && (uint64_t)h.n_cand * 2 > (uint64_t)G + 1024 && c->recalibrations < 2) { c->calibrated = false; ++c->recalibrations; }
     c->pend.valid = false;
@@ -934,6 +987,11 @@ lp_ctx* lp_create(const lp_scoring_cfg* cfg, int device) {
         CK(cudaGetDeviceProperties(&prop, device));
         ctx->n_sm = prop.multiProcessorCount;
         CK(cudaFuncSetAttribute(k_filter_count, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(GRAM_WORDS * 4)));
+        CK(cudaFuncSetAttribute(k_fscan<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs::SMEM_BYTES));
+        CK(cudaFuncSetAttribute(k_fscan<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs::SMEM_BYTES));
+        CK(cudaFuncSetAttribute(k_fscan<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs::SMEM_BYTES));
+        if (const char* m = getenv("LP_SCAN_MODE")) ctx->scan_mode = strcmp(m, "legacy") == 0 ? 1 : 0;
+        if (const char* v = getenv("LP_FSCAN_VARIANT")) ctx->fscan_variant = std::max(0, std::min(2, atoi(v)));
         CK(cudaFuncSetAttribute(k_dfa_scan<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
         CK(cudaFuncSetAttribute(k_dfa_scan<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
         CK(cudaFuncSetAttribute(k_dfa_scan<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
@@ -963,7 +1021,7 @@ void lp_destroy(lp_ctx* c) {
                      &c->ev_log, &c->slot_key, &c->slot_key_alt, &c->ev_idx, &c->ev_idx_alt, &c->rank_in_slot, &c->freq_delta, &c->prior,
                      &c->out_arena, &c->sort_key, &c->sort_key_alt, &c->order, &c->order_alt,
                      &c->log_sorted, &c->log_sorted_alt, &c->log_event_begin, &c->n_unique, &c->d_lut,
-                     &c->f_bitmap, &c->f_key, &c->f_lits, &c->f_bytes, &c->items, &c->ss_keys, &c->ss_idx, &c->seq_tab_off, &c->seq_tab, &c->seq_T, &c->prior_eff, &c->any_flag, &c->dist_mine, &c->dist_all};
+                     &c->f_bitmap, &c->f_key, &c->f_lits, &c->f_bytes, &c->f_bits, &c->f_gkeys, &c->fs_state, &c->items, &c->ss_keys, &c->ss_idx, &c->seq_tab_off, &c->seq_tab, &c->seq_T, &c->prior_eff, &c->any_flag, &c->dist_mine, &c->dist_all};
     for (DevBuf* b : all) b->release();
     if (c->nccl_comm) nccl_comm_destroy(c->nccl_comm);
     c->stage.release();

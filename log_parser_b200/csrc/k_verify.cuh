@@ -264,8 +264,9 @@ struct ResolveArgs {
     uint64_t len;
     const unsigned long long* items;
     uint32_t item_cap;
-    const uint32_t* tile_prefix;     // exclusive newline count before each 32 KiB tile
+    const uint32_t* tile_prefix;     // exclusive newline count before each tile of the scan
     uint32_t n_tiles;
+    uint32_t tile_bytes;             // tile size of the scan that wrote tile_prefix
     const uint64_t* log_off;
     uint32_t n_logs;
     const uint32_t* line_start;
@@ -301,11 +302,11 @@ __global__ void __launch_bounds__(256) k_resolve(ResolveArgs a, DevPlan P) {
             const uint32_t packed = __ldg(&P.lit_rx_packed[(uint32_t)item & 0xFFFFFFu]);
             const uint32_t r = packed & 0xFFFFFFu, mode = packed >> 24;
             // line of the occurrence: the newline prefix of its tile (and its neighbour) brackets the index
-            const uint32_t t = s / TILE_BYTES;
+            const uint32_t t = s / a.tile_bytes;
             uint32_t glo = a.tile_prefix[t], ghi = (t + 1 < a.n_tiles ? a.tile_prefix[t + 1] : a.ctr->n_lines_total) + 1;
             if (a.n_logs > 1) {
-                glo += upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, (uint64_t)t * TILE_BYTES) - 1;
-                ghi += upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, (uint64_t)(t + 1) * TILE_BYTES);
+                glo += upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, (uint64_t)t * a.tile_bytes) - 1;
+                ghi += upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, (uint64_t)(t + 1) * a.tile_bytes);
             }
             ghi = min(ghi, gmax);
             if (glo >= ghi) break;                    // beyond the (under-estimated) line arrays: the call is re-run
