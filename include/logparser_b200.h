@@ -105,6 +105,18 @@ enum {
     LP_OPT_SPANS = 8           /* also return the match span of every event (backtracking engine) */
 };
 
+/* ---- host buffers --------------------------------------------------------------------------
+ * No counterpart in the reference (its request body is a Java String, Parse.java:44). A log handed to
+ * lp_analyze* in pageable memory is copied through a driver staging buffer while the calling thread
+ * waits; from page-locked memory the copy runs asynchronously, in pieces, under the scan. The JVM
+ * either takes its request buffer from lp_host_alloc (MemorySegment.reinterpret over the returned
+ * address, lp_host_free when the buffer pool shrinks) or page-locks a segment it owns with
+ * lp_host_register / lp_host_unregister. Both need a usable CUDA device. */
+void* lp_host_alloc(size_t bytes);              /* NULL on failure, lp_last_error() says why */
+void lp_host_free(void* p);
+int lp_host_register(void* p, size_t bytes);
+int lp_host_unregister(void* p);
+
 /* ---- lifecycle ------------------------------------------------------------------------- */
 /* Carries the scoring.* values into the library and binds it to one CUDA device
  * (replaces the @ConfigProperty injection of SS:38-51, CAS:24, FTS:27-34). NULL on failure. */
@@ -179,6 +191,11 @@ int lp_comm_unique_id(uint8_t* id128);
 int lp_comm_init(lp_ctx* ctx, const uint8_t* id128, uint32_t rank, uint32_t world);
 int lp_analyze_batch_dist_device(lp_ctx* ctx, const uint8_t* d_logs, const uint64_t* offsets, size_t n_logs,
                                  const uint64_t* prior_count, int options, lp_result** out);
+/* The same collective step with this rank's logs still in HOST memory (page-locked for real overlap, see
+ * lp_host_alloc): the host->device copy is cut in pieces on a second stream and each piece is scanned as it
+ * lands, exactly as lp_analyze does for one request (Parse.java:44 hands the service a host String). */
+int lp_analyze_batch_dist(lp_ctx* ctx, const uint8_t* logs, const uint64_t* offsets, size_t n_logs,
+                          const uint64_t* prior_count, int options, lp_result** out);
 
 /* ONE log sharded by line range over several GPUs (second mode; the reference walks
  * the whole log on one thread, AS:89-113). The host first removes the log's trailing separators
@@ -218,7 +235,9 @@ int lp_range_score(lp_ctx* ctx, const uint64_t* summaries /* [world][words] */, 
  *   d_line_end    device, `capacity` entries: end offset (exclusive; a '\r' before '\n' is dropped)
  *   d_counts      device, 3 entries: [0] lines after Java's trailing-empty trimming (logLines.length),
  *                 [1] line segments written (newlines + 1), [2] non-zero if `capacity` was too small
- *   stream        cudaStream_t to run on (NULL = default stream); the call returns after it drained
+ *   stream        cudaStream_t to run on (NULL = default stream). The call is synchronous: it reads the
+ *                 overflow flag back and returns only after `stream` has drained; the calling thread's
+ *                 current device is the same after the call as before
  *   err/errlen    optional buffer for a message when the return value is not LP_OK
  * The first call on each device looks up the scratch array's address; issue it before starting
  * any stream capture. All calls on one device share that array and it keeps the previous call's
@@ -234,16 +253,16 @@ void lp_result_free(lp_result* r);
 /* ---- measurement ------------------------------------------------------------------------- */
 typedef struct lp_timings {
     float total_ms;        /* first to last kernel of the last lp_analyze* call (CUDA events)     */
-    float scan_ms;         /* k_filter_count: newline count + literal prefilter, the dominant streaming kernel */
-    float verify_ms;       /* candidate confirmation + DFA / backtracking verification            */
+    float scan_ms;         /* k_fscan: the one pass over the log (newline lists + literal prefilter), the dominant streaming kernel */
+    float verify_ms;       /* line offsets (lines_ms) + candidate confirmation + DFA / backtracking verification */
     float score_ms;        /* sorting, event assembly, scoring, ranking                           */
     float h2d_ms;          /* host->device copy of the log (lp_analyze / lp_analyze_batch only)   */
     uint64_t kernel_launches;   /* kernels of this library launched by the last call             */
-    uint64_t scan_bytes;        /* its algorithmic bytes: B read + 4 per tile + 4 per candidate   */
+    uint64_t scan_bytes;        /* its algorithmic bytes: B read + 2 per newline + 4 per tile + 4 per candidate */
     uint64_t candidates;        /* gram-filter hits handed to confirmation                        */
     uint64_t verify_tasks;      /* (line, regex) pairs verified                                   */
     float dfa_scan_ms;          /* the always-on shared-memory product-DFA scan (part of verify_ms) */
-    float reserved;
+    float lines_ms;             /* tile-count scan + line_start/line_end from the newline lists + Java trimming (part of verify_ms) */
     uint64_t dfa_scan_bytes;    /* its algorithmic bytes: B + 8(G+1) + G                          */
 } lp_timings;
 int lp_get_timings(const lp_ctx* ctx, lp_timings* out);

@@ -76,7 +76,7 @@ class Timings(C.Structure):
     _fields_ = [
         ("total_ms", C.c_float), ("scan_ms", C.c_float), ("verify_ms", C.c_float), ("score_ms", C.c_float),
         ("h2d_ms", C.c_float), ("kernel_launches", C.c_uint64), ("scan_bytes", C.c_uint64),
-        ("candidates", C.c_uint64), ("verify_tasks", C.c_uint64), ("dfa_scan_ms", C.c_float), ("reserved", C.c_float),
+        ("candidates", C.c_uint64), ("verify_tasks", C.c_uint64), ("dfa_scan_ms", C.c_float), ("lines_ms", C.c_float),
         ("dfa_scan_bytes", C.c_uint64),
     ]
 
@@ -87,7 +87,8 @@ EXPORTS = [
     "lp_analyze_batch", "lp_analyze_batch_device", "lp_batch_scan_device", "lp_batch_score", "lp_result_get",
     "lp_result_free", "lp_get_timings", "lp_stream", "lp_split_lines_noalloc",
     "lp_counts_by_id", "lp_batch_scan_device_async", "lp_batch_score_gathered", "lp_comm_unique_id", "lp_comm_init",
-    "lp_analyze_batch_dist_device", "lp_range_halo_lines", "lp_range_summary_words", "lp_range_scan_device", "lp_range_score",
+    "lp_analyze_batch_dist_device", "lp_analyze_batch_dist", "lp_host_alloc", "lp_host_free", "lp_host_register",
+    "lp_host_unregister", "lp_range_halo_lines", "lp_range_summary_words", "lp_range_scan_device", "lp_range_score",
 ]
 
 _lib = None
@@ -126,6 +127,12 @@ def load_library() -> C.CDLL:
     L.lp_comm_unique_id.argtypes = [vp]
     L.lp_comm_init.argtypes = [vp, vp, C.c_uint32, C.c_uint32]
     L.lp_analyze_batch_dist_device.argtypes = [vp, u8p, u64p, C.c_size_t, u64p, C.c_int, C.POINTER(vp)]
+    L.lp_analyze_batch_dist.argtypes = [vp, u8p, u64p, C.c_size_t, u64p, C.c_int, C.POINTER(vp)]
+    L.lp_host_alloc.restype = vp
+    L.lp_host_alloc.argtypes = [C.c_size_t]
+    L.lp_host_free.argtypes = [vp]
+    L.lp_host_register.argtypes = [vp, C.c_size_t]
+    L.lp_host_unregister.argtypes = [vp]
     L.lp_range_halo_lines.restype = C.c_uint32
     L.lp_range_halo_lines.argtypes = [vp]
     L.lp_range_summary_words.restype = C.c_size_t
@@ -133,20 +140,6 @@ def load_library() -> C.CDLL:
     L.lp_range_scan_device.argtypes = [vp, u8p, C.c_size_t, C.c_uint32, C.c_uint32, C.c_int, u64p]
     L.lp_range_score.argtypes = [vp, u64p, C.c_uint32, C.c_uint32, u64p, C.POINTER(vp)]
     L.lp_split_lines_noalloc.argtypes = [C.c_int, vp, C.c_size_t, vp, vp, C.c_size_t, vp, vp, C.c_char_p, C.c_size_t]
-    # host-compiler introspection (CPU-only test tier)
-    L.lp_debug_rx_compile.restype = vp
-    L.lp_debug_rx_compile.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_char_p, C.c_size_t, C.POINTER(C.c_int)]
-    L.lp_debug_rx_free.argtypes = [vp]
-    L.lp_debug_rx_is_dfa.argtypes = [vp]
-    L.lp_debug_rx_states.restype = C.c_uint32
-    L.lp_debug_rx_states.argtypes = [vp]
-    L.lp_debug_rx_match.argtypes = [vp, C.c_char_p, C.c_size_t]
-    L.lp_debug_rx_literals.restype = C.c_size_t
-    L.lp_debug_rx_literals.argtypes = [vp, C.c_char_p, C.c_size_t]
-    L.lp_debug_rx_anchor.argtypes = [vp]
-    L.lp_debug_rx_match_local.argtypes = [vp, C.c_char_p, C.c_size_t]
-    L.lp_debug_rx_span.argtypes = [vp, C.c_char_p, C.c_size_t, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
-    L.lp_debug_rx_match_anchored.argtypes = [vp, C.c_char_p, C.c_size_t]
     _lib = L
     return L
 
@@ -436,6 +429,16 @@ class LogParser:
             _raise(rc)
         return self._take(out)
 
+    def analyze_batch_dist_host_ptr(self, host_ptr: int, offsets, prior_count=None, options: int = 0) -> Result:
+        """The same collective step with this rank's logs in (page-locked) host memory: the copy overlaps the scan."""
+        oa, op = self._offsets(offsets)
+        keep, pp = self._prior(prior_count)
+        out = C.c_void_p()
+        rc = self.L.lp_analyze_batch_dist(self.h, host_ptr, op, len(oa) - 1, pp, options, C.byref(out))
+        if rc != LP_OK:
+            _raise(rc)
+        return self._take(out)
+
     # ---- one log sharded by line range (lp_range_*)
     def range_halo_lines(self) -> int:
         return int(self.L.lp_range_halo_lines(self.h))
@@ -485,11 +488,53 @@ def split_lines_noalloc(device: int, d_log: int, nbytes: int, d_line_start: int,
         raise LpError(rc, err.value.decode("utf-8", "replace"))
 
 
+_dbg = None
+
+
+def load_debug_library() -> C.CDLL:
+    """liblogparser_b200_debug.so: host-compiler introspection for the CPU test tier (not part of the product library)."""
+    global _dbg
+    if _dbg is not None:
+        return _dbg
+    from . import build as _build
+
+    L = C.CDLL(_build.build_debug())
+    vp = C.c_void_p
+    L.lp_debug_rx_compile.restype = vp
+    L.lp_debug_rx_compile.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_char_p, C.c_size_t, C.POINTER(C.c_int)]
+    L.lp_debug_rx_free.argtypes = [vp]
+    L.lp_debug_rx_is_dfa.argtypes = [vp]
+    L.lp_debug_rx_states.restype = C.c_uint32
+    L.lp_debug_rx_states.argtypes = [vp]
+    L.lp_debug_rx_match.argtypes = [vp, C.c_char_p, C.c_size_t]
+    L.lp_debug_rx_literals.restype = C.c_size_t
+    L.lp_debug_rx_literals.argtypes = [vp, C.c_char_p, C.c_size_t]
+    L.lp_debug_rx_anchor.argtypes = [vp]
+    L.lp_debug_rx_match_local.argtypes = [vp, C.c_char_p, C.c_size_t]
+    L.lp_debug_rx_span.argtypes = [vp, C.c_char_p, C.c_size_t, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32)]
+    L.lp_debug_rx_match_anchored.argtypes = [vp, C.c_char_p, C.c_size_t]
+    L.lp_debug_plan_dump.restype = C.c_size_t
+    L.lp_debug_plan_dump.argtypes = [vp, C.c_size_t, C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t]
+    L.lp_debug_group_match.restype = C.c_uint32
+    L.lp_debug_group_match.argtypes = [C.POINTER(C.c_char_p), C.POINTER(C.c_int), C.c_size_t, C.c_char_p, C.c_size_t]
+    _dbg = L
+    return L
+
+
+def host_alloc(nbytes: int) -> int:
+    """Page-locked host memory from the library (lp_host_alloc); the address, 0 on failure."""
+    return int(load_library().lp_host_alloc(nbytes) or 0)
+
+
+def host_free(ptr: int) -> None:
+    load_library().lp_host_free(ptr)
+
+
 class DebugRegex:
     """Host-compiler introspection for the CPU-only test tier (never part of analyze)."""
 
     def __init__(self, pattern: str, flags: int = 0, force_vm: bool = False, min_literal: int = 0):
-        self.L = load_library()
+        self.L = load_debug_library()
         err = C.create_string_buffer(512)
         kind = C.c_int(0)
         self.h = self.L.lp_debug_rx_compile(pattern.encode("utf-8"), flags, (1 if force_vm else 0) | (min_literal << 8), err, 512, C.byref(kind))

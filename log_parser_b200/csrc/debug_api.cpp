@@ -1,6 +1,9 @@
-// Host-compiler introspection exported from liblogparser_b200.so for the CPU-only test tier
+// Host-compiler introspection for the CPU-only test tier, built into its own library
+// (liblogparser_b200_debug.so, host code only; the product library does not contain it)
 // (`pytest -m "not gpu"`): lets the tests diff the exact tables the device walks against the
 // oracle without a GPU. Never called by lp_analyze*; it is not a CPU fallback of the product path.
+#include <algorithm>
+#include <cstdio>
 #include <cstring>
 #include <string>
 
@@ -165,5 +168,43 @@ uint32_t lp_debug_group_match(const char* const* regexes, const int* flags, size
         return 0xFFFFFFFFu;
     }
 }
+
+// CPU-only introspection of the plan lp_load_patterns would build (tests / tuning; no GPU needed):
+// one text line per literal: "<gram hex>\t<icase>\t<literal>", then "#..." summary lines.
+size_t lp_debug_plan_dump(const lp_pattern_desc* pats, size_t n, const uint8_t* sample, size_t sample_len, char* buf, size_t cap) {
+    std::string out;
+    try {
+        lpx::Plan pl;
+        std::vector<lpx::PlanPatternIn> in = lpx::plan_input_from_desc(pats, n, nullptr);
+        lpx::build_plan(in, pl, nullptr);
+        if (sample && sample_len) lpx::select_grams(pl, sample, sample_len);
+        for (size_t l = 0; l < pl.lit_off.size(); ++l) {
+            char g[16];
+            const uint8_t* b = &pl.lit_bytes[pl.lit_off[l] + pl.lit_gram_off[l]];
+            snprintf(g, sizeof g, "%02x%02x%02x%02x", b[0], b[1], b[2], b[3]);
+            out += g; out += "\t"; out += pl.lit_icase[l] ? "1" : "0";
+            out += ":";
+            for (uint32_t j = pl.lit_rx_begin[l]; j < pl.lit_rx_begin[l + 1]; ++j) { out += std::to_string(pl.lit_rx[j]) + "/" + std::to_string((int)pl.lit_rx_mode[j]) + ","; }
+            out += "\t";
+            out.append(reinterpret_cast<const char*>(&pl.lit_bytes[pl.lit_off[l]]), pl.lit_len[l]);
+            out += "\n";
+        }
+        out += "#regexes " + std::to_string(pl.n_rx) + " vm " + std::to_string(pl.n_vm) + " literals " + std::to_string(pl.lit_off.size()) +
+               " groups " + std::to_string(pl.groups.size()) + " always_dfa " + std::to_string(pl.always_list.size()) +
+               " always_vm " + std::to_string(pl.always_vm_list.size()) + "\n";
+        for (const auto& g : pl.groups) {
+            out += "#group states " + std::to_string(g.blob[0]) + " classes " + std::to_string(g.blob[1]) + " bytes " + std::to_string(g.blob.size() * 4) + " rx";
+            for (uint32_t r : g.rx) out += " [" + pl.rx_src[r] + "]";
+            out += "\n";
+        }
+        for (uint32_t r : pl.always_list) out += "#always_dfa [" + pl.rx_src[r] + "]\n";
+        for (uint32_t r : pl.always_vm_list) out += "#always_vm [" + pl.rx_src[r] + "]\n";
+    } catch (const std::exception& e) {
+        out = std::string("!error ") + e.what() + "\n";
+    }
+    if (buf && cap) { size_t k = std::min(cap - 1, out.size()); memcpy(buf, out.data(), k); buf[k] = 0; }
+    return out.size();
+}
+
 
 }  // extern "C"

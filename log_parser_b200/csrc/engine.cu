@@ -149,7 +149,7 @@ struct lp_ctx {
     const uint8_t* d_rx_record = nullptr;
     uint32_t n_group_record_rx = 0;
     DevBuf f_bitmap, f_key, f_lits, f_bytes;   // prefilter tables (re-uploaded by calibration)
-    DevBuf f_bits, f_gkeys, fs_state;          // fused scan: first-stage bit table, exact gram keys, tickets + look-back words
+    DevBuf f_bits, f_gkeys, fs_state, fs_lists; // fused scan: first-stage bit table, exact gram keys, ticket counters, per-tile newline lists
     const uint8_t* d_byte_table = nullptr;
     int scan_mode = 0;                         // 0: fused single-pass scan (k_fscan); 1: k_filter_count + k_scan_tiles + k_lines (LP_SCAN_MODE=legacy)
     int fscan_variant = 0;                     // first-stage lookup of k_fscan: 0 IMAD.HI hash, 1 IMAD+SHF hash, 2 byte table (LP_FSCAN_VARIANT)
@@ -195,7 +195,7 @@ struct lp_ctx {
     std::vector<uint32_t> h_seq_tab_off;    // per sequence, offset of its chain table in a shard summary
     uint32_t n_seq = 0;
 
-    cudaEvent_t ev[9]{};
+    cudaEvent_t ev[10]{};
     lp_timings tm{};
     uint64_t launches = 0;
 };
@@ -507,17 +507,16 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     constexpr uint32_t FS_TICKETS = 32;
     FscanArgs fz{};
     if (fused) {
-        // tickets of up to FS_TICKETS launches, then one look-back word per tile; cleared once per call
-        const size_t state_bytes = FS_TICKETS * 4 + (size_t)n_tiles * 8;
-        c->fs_state.ensure(state_bytes);
-        CK(cudaMemsetAsync(c->fs_state.p, 0, state_bytes, st));
-        CK(cudaMemcpyAsync(c->log_off.p, h_off, (n_logs + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
+        // one ticket counter per launch of this call (a log arriving from the host is scanned piece by piece)
+        c->fs_state.ensure(FS_TICKETS * 4);
+        CK(cudaMemsetAsync(c->fs_state.p, 0, FS_TICKETS * 4, st));
+        // per tile: 16 span counts, then per tile 16 lists of fs::WLIST entries
+        c->fs_lists.ensure((size_t)n_tiles * 16 * 2 + (size_t)n_tiles * 16 * fs::WLIST * 2);
         fz.text = d_text; fz.len = len; fz.n_tiles = n_tiles;
-        fz.status = reinterpret_cast<unsigned long long*>(c->fs_state.as<uint8_t>() + FS_TICKETS * 4);
-        fz.tile_prefix = c->tile_counts.as<uint32_t>();
-        fz.log_off = c->log_off.as<uint64_t>(); fz.n_logs = n_logs;
-        fz.line_start = c->line_start.as<uint32_t>(); fz.line_end = c->line_end.as<uint32_t>();
-        fz.first_line = c->first_line.as<uint32_t>(); fz.line_cap = (uint32_t)line_cap;
+        fz.tma_tiles = len >= fs::TILE + fs::HALO ? (uint32_t)((len - fs::HALO) / fs::TILE) : 0u;
+        fz.tile_counts = c->tile_counts.as<uint32_t>();
+        fz.warp_counts = c->fs_lists.as<uint16_t>();
+        fz.nl_lists = c->fs_lists.as<uint16_t>() + (size_t)n_tiles * 16;
         fz.bit_table = c->fscan_variant == 2 ? reinterpret_cast<const uint32_t*>(c->d_byte_table) : c->f_bits.as<uint32_t>();
         fz.gram_keys = c->f_gkeys.as<uint32_t>(); fz.table_bits = c->dp.table_bits;
         fz.cand = c->cand.as<uint32_t>(); fz.cand_cap = (uint32_t)std::min<size_t>(c->est_cand, 0xFFFFFFFFu); fz.ctr = ctr;
@@ -569,13 +568,20 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         else k_filter_count<<<std::min<uint32_t>(n_tiles, (uint32_t)c->n_sm * 3), SCAN_THREADS, smem, st>>>(fa);
     }
     CK(cudaEventRecord(c->ev[2], st));
-    if (!fused) CK(cudaMemcpyAsync(c->log_off.p, h_off, (n_logs + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
+    CK(cudaMemcpyAsync(c->log_off.p, h_off, (n_logs + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
     CK(cudaMemsetAsync(c->recs.p, 0xFF, rec_cap * 8, st));            // padding sentinels sort last
     CK(cudaMemsetAsync(c->ev_key_alt.p, 0xFF, ev_cap * 8, st));
     if (has_vm) CK(cudaMemsetAsync(c->vm_tasks.p, 0xFF, c->est_vm_tasks * 8, st));      // padding sorts behind the tasks
     if (!c->plan.ctx_any_in_groups) CK(cudaMemsetAsync(c->ctx_flags.p, 0, (line_cap / 4 + 2) * 4, st));   // else k_dfa_scan writes every byte
-    if (!fused) {
     k_scan_tiles<<<1, 1024, 0, st>>>(c->tile_counts.as<uint32_t>(), n_tiles, n_logs, ctr);
+    if (fused) {
+        ExpandArgs ea{};
+        ea.text = d_text; ea.len = len; ea.n_tiles = n_tiles; ea.tile_prefix = c->tile_counts.as<uint32_t>(); ea.warp_counts = c->fs_lists.as<uint16_t>(); ea.nl_lists = c->fs_lists.as<uint16_t>() + (size_t)n_tiles * 16;
+        ea.log_off = c->log_off.as<uint64_t>(); ea.n_logs = n_logs;
+        ea.line_start = c->line_start.as<uint32_t>(); ea.line_end = c->line_end.as<uint32_t>();
+        ea.first_line = c->first_line.as<uint32_t>(); ea.line_cap = (uint32_t)line_cap; ea.ctr = ctr;
+        k_expand<<<std::min<uint32_t>(n_tiles, (uint32_t)c->n_sm * 16), EX_THREADS, 0, st>>>(ea);
+    } else {
     ScanArgs sa{};
     sa.text = d_text; sa.len = len; sa.n_tiles = n_tiles; sa.tile_prefix = c->tile_counts.as<uint32_t>();
     sa.log_off = c->log_off.as<uint64_t>(); sa.n_logs = n_logs;
@@ -584,10 +590,11 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     sa.cand = nullptr; sa.cand_cap = 0;
     sa.ctr = ctr; sa.use_filter = 0;      // offsets only: the prefilter ran in k_filter_count
     k_lines<<<std::min<uint32_t>(n_tiles, (uint32_t)c->n_sm * 4), LN_TILE_THREADS, 0, st>>>(sa);
-    c->launches += 2;
     }
+    c->launches += 2;
     k_log_meta<<<blocks_for(n_logs, 128), 128, 0, st>>>(c->first_line.as<uint32_t>(), c->line_start.as<uint32_t>(),
                                                          c->line_end.as<uint32_t>(), n_logs, (uint32_t)line_cap, rg ? 1u : 0u, c->n_lines.as<uint32_t>());
+    CK(cudaEventRecord(c->ev[9], st));
     c->launches += 2;
 
     VerifyArgs va{};
@@ -878,13 +885,14 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
     cudaEventElapsedTime(&ms, c->ev[2], c->ev[3]); c->tm.verify_ms = ms;
     cudaEventElapsedTime(&ms, c->ev[3], c->ev[4]); c->tm.score_ms = ms;
     cudaEventElapsedTime(&ms, c->ev[6], c->ev[7]); c->tm.dfa_scan_ms = ms;
+    cudaEventElapsedTime(&ms, c->ev[2], c->ev[9]); c->tm.lines_ms = ms;
     c->tm.kernel_launches = c->launches;
     c->tm.candidates = h.n_cand;
     c->tm.verify_tasks = (uint64_t)h.n_tasks + h.n_vm_tasks + (uint64_t)G * (c->plan.always_list.size() + c->plan.always_vm_list.size());
     // k_filter_count: the log read once, one count per tile and one position per candidate written
-    // algorithmic bytes of the scan kernel(s) timed as scan_ms. Fused scan: the log read once, line_start + line_end
-    // written, one prefix per tile, one position per candidate. Legacy k_filter_count: log, tile counts, candidates.
-    if (c->scan_mode == 0) c->tm.scan_bytes = c->pend.len + 8ull * G + 4ull * ((c->pend.len + fs::TILE) / fs::TILE) + 4ull * h.n_cand;
+    // algorithmic bytes of the scan kernel timed as scan_ms. k_fscan: the log read once; written: one 2-byte list entry per
+    // newline, 1 + 16 counts per tile, one position per candidate. Legacy k_filter_count: log, tile counts, candidates.
+    if (c->scan_mode == 0) c->tm.scan_bytes = c->pend.len + 2ull * h.total_nl + 36ull * ((c->pend.len + fs::TILE) / fs::TILE) + 4ull * h.n_cand;
     else c->tm.scan_bytes = c->pend.len + 4ull * ((c->pend.len + TILE_BYTES) / TILE_BYTES) + 4ull * h.n_cand;
     c->tm.dfa_scan_bytes = c->d_group_blob.empty() ? 0 : c->pend.len + 8ull * ((uint64_t)G + 1) + (uint64_t)G;
     if (!c->plan.lit_off.empty() && (uint64_t)h.n_cand * 2 > (uint64_t)G + 1024 && c->recalibrations < 2) { c->calibrated = false; ++c->recalibrations; }
@@ -1021,7 +1029,7 @@ void lp_destroy(lp_ctx* c) {
                      &c->ev_log, &c->slot_key, &c->slot_key_alt, &c->ev_idx, &c->ev_idx_alt, &c->rank_in_slot, &c->freq_delta, &c->prior,
                      &c->out_arena, &c->sort_key, &c->sort_key_alt, &c->order, &c->order_alt,
                      &c->log_sorted, &c->log_sorted_alt, &c->log_event_begin, &c->n_unique, &c->d_lut,
-                     &c->f_bitmap, &c->f_key, &c->f_lits, &c->f_bytes, &c->f_bits, &c->f_gkeys, &c->fs_state, &c->items, &c->ss_keys, &c->ss_idx, &c->seq_tab_off, &c->seq_tab, &c->seq_T, &c->prior_eff, &c->any_flag, &c->dist_mine, &c->dist_all};
+                     &c->f_bitmap, &c->f_key, &c->f_lits, &c->f_bytes, &c->f_bits, &c->f_gkeys, &c->fs_state, &c->fs_lists, &c->items, &c->ss_keys, &c->ss_idx, &c->seq_tab_off, &c->seq_tab, &c->seq_T, &c->prior_eff, &c->any_flag, &c->dist_mine, &c->dist_all};
     for (DevBuf* b : all) b->release();
     if (c->nccl_comm) nccl_comm_destroy(c->nccl_comm);
     c->stage.release();
@@ -1034,40 +1042,13 @@ void lp_destroy(lp_ctx* c) {
     delete c;
 }
 
-static std::vector<lpx::PlanPatternIn> to_plan_input(const lp_pattern_desc* pats, size_t n, int64_t* bad_pattern) {
-    std::vector<lpx::PlanPatternIn> in(n);
-    for (size_t i = 0; i < n; ++i) {
-        const lp_pattern_desc& d = pats[i];
-        if (!d.primary_regex) { if (bad_pattern) *bad_pattern = (int64_t)i; throw std::invalid_argument("primary_regex is NULL"); }
-        in[i].has_id = d.id != nullptr;
-        if (d.id) in[i].id = d.id;
-        in[i].primary = d.primary_regex;
-        in[i].confidence = d.confidence; in[i].severity = d.severity_multiplier;
-        in[i].has_context = d.has_context; in[i].before = d.lines_before; in[i].after = d.lines_after;
-        for (uint32_t s = 0; s < d.n_secondaries; ++s) {
-            if (!d.secondaries[s].regex) { if (bad_pattern) *bad_pattern = (int64_t)i; throw std::invalid_argument("secondary regex is NULL"); }
-            in[i].secs.push_back({d.secondaries[s].regex, d.secondaries[s].weight, d.secondaries[s].proximity_window});
-        }
-        for (uint32_t s = 0; s < d.n_sequences; ++s) {
-            lpx::PlanPatternIn::Seq q;
-            q.bonus = d.sequences[s].bonus_multiplier;
-            for (uint32_t e = 0; e < d.sequences[s].n_events; ++e) {
-                if (!d.sequences[s].event_regex[e]) { if (bad_pattern) *bad_pattern = (int64_t)i; throw std::invalid_argument("sequence event regex is NULL"); }
-                q.events.push_back(d.sequences[s].event_regex[e]);
-            }
-            in[i].seqs.push_back(std::move(q));
-        }
-    }
-    return in;
-}
-
 int lp_load_patterns(lp_ctx* c, const lp_pattern_desc* pats, size_t n, int64_t* bad_pattern) {
     if (bad_pattern) *bad_pattern = -1;
     if (!c) { g_last_error = "ctx is NULL"; return LP_ERR_INVALID; }
     return guarded(c, [&] {
         if (n && !pats) throw std::invalid_argument("patterns is NULL");
         std::lock_guard<std::mutex> lk(c->mu);
-        std::vector<lpx::PlanPatternIn> in = to_plan_input(pats, n, bad_pattern);
+        std::vector<lpx::PlanPatternIn> in = lpx::plan_input_from_desc(pats, n, bad_pattern);
         c->loaded = false;
         c->calibrated = false;
         c->recalibrations = 0;
@@ -1083,43 +1064,6 @@ int lp_load_patterns(lp_ctx* c, const lp_pattern_desc* pats, size_t n, int64_t* 
         upload_into(c->seq_tab_off, c->h_seq_tab_off);
         c->loaded = true;
     });
-}
-
-// CPU-only introspection of the plan lp_load_patterns would build (tests / tuning; no GPU needed):
-// one text line per literal: "<gram hex>\t<icase>\t<literal>", then "#..." summary lines.
-size_t lp_debug_plan_dump(const lp_pattern_desc* pats, size_t n, const uint8_t* sample, size_t sample_len, char* buf, size_t cap) {
-    std::string out;
-    try {
-        lpx::Plan pl;
-        std::vector<lpx::PlanPatternIn> in = to_plan_input(pats, n, nullptr);
-        lpx::build_plan(in, pl, nullptr);
-        if (sample && sample_len) lpx::select_grams(pl, sample, sample_len);
-        for (size_t l = 0; l < pl.lit_off.size(); ++l) {
-            char g[16];
-            const uint8_t* b = &pl.lit_bytes[pl.lit_off[l] + pl.lit_gram_off[l]];
-            snprintf(g, sizeof g, "%02x%02x%02x%02x", b[0], b[1], b[2], b[3]);
-            out += g; out += "\t"; out += pl.lit_icase[l] ? "1" : "0";
-            out += ":";
-            for (uint32_t j = pl.lit_rx_begin[l]; j < pl.lit_rx_begin[l + 1]; ++j) { out += std::to_string(pl.lit_rx[j]) + "/" + std::to_string((int)pl.lit_rx_mode[j]) + ","; }
-            out += "\t";
-            out.append(reinterpret_cast<const char*>(&pl.lit_bytes[pl.lit_off[l]]), pl.lit_len[l]);
-            out += "\n";
-        }
-        out += "#regexes " + std::to_string(pl.n_rx) + " vm " + std::to_string(pl.n_vm) + " literals " + std::to_string(pl.lit_off.size()) +
-               " groups " + std::to_string(pl.groups.size()) + " always_dfa " + std::to_string(pl.always_list.size()) +
-               " always_vm " + std::to_string(pl.always_vm_list.size()) + "\n";
-        for (const auto& g : pl.groups) {
-            out += "#group states " + std::to_string(g.blob[0]) + " classes " + std::to_string(g.blob[1]) + " bytes " + std::to_string(g.blob.size() * 4) + " rx";
-            for (uint32_t r : g.rx) out += " [" + pl.rx_src[r] + "]";
-            out += "\n";
-        }
-        for (uint32_t r : pl.always_list) out += "#always_dfa [" + pl.rx_src[r] + "]\n";
-        for (uint32_t r : pl.always_vm_list) out += "#always_vm [" + pl.rx_src[r] + "]\n";
-    } catch (const std::exception& e) {
-        out = std::string("!error ") + e.what() + "\n";
-    }
-    if (buf && cap) { size_t k = std::min(cap - 1, out.size()); memcpy(buf, out.data(), k); buf[k] = 0; }
-    return out.size();
 }
 
 int lp_batch_scan_device(lp_ctx* c, const uint8_t* d_logs, const uint64_t* offsets, size_t n_logs, int options, uint64_t* counts_out) {
@@ -1210,13 +1154,17 @@ int lp_comm_init(lp_ctx* c, const uint8_t* id128, uint32_t rank, uint32_t world)
 // all-gather of [per-pattern counts, status] over NVLink, exclusive prefix, score. Collective: every
 // rank calls it once per step (with n_logs >= 1). A rank whose scratch estimates were too small makes
 // all ranks repeat the step, which they agree on through the gathered status words.
-int lp_analyze_batch_dist_device(lp_ctx* c, const uint8_t* d_logs, const uint64_t* offsets, size_t n_logs, const uint64_t* prior_count,
-                                 int options, lp_result** out) {
+static int analyze_batch_dist(lp_ctx* c, const uint8_t* logs, bool on_host, const uint64_t* offsets, size_t n_logs, const uint64_t* prior_count,
+                              int options, lp_result** out) {
     if (!c || !out) { g_last_error = "NULL argument"; return LP_ERR_INVALID; }
     *out = nullptr;
     return guarded(c, [&] {
         if (!offsets) throw std::invalid_argument("offsets is NULL");
         std::lock_guard<std::mutex> lk(c->mu);
+        if (on_host && offsets[n_logs] && !logs) throw std::invalid_argument("logs is NULL");
+        // host input: the copy to the device is cut in pieces and overlapped with the scan of the pieces already there
+        const uint8_t* d_logs = on_host ? stage_host_log(c, logs, offsets[n_logs]) : logs;
+        struct DropHostSrc { lp_ctx* c; ~DropHostSrc() { c->host_src = nullptr; } } drop{c};
         if (!c->nccl_comm) throw std::invalid_argument("lp_comm_init has not been called on this context");
         const uint32_t np = c->dp.n_pat, world = c->comm_world, rank = c->comm_rank;
         const size_t words = (size_t)np + 1;
@@ -1269,9 +1217,22 @@ int lp_analyze_batch_dist_device(lp_ctx* c, const uint8_t* d_logs, const uint64_
             if (flag & 16u) throw std::overflow_error("backtracking verifier exceeded its step/stack budget");
             if (flag) continue;                 // every rank sees the same words: all of them repeat
             *out = res.release();
+            if (on_host) {
+                float ms = 0;
+                cudaEventElapsedTime(&ms, c->ev[5], c->ev[8]);
+                c->tm.h2d_ms = ms;
+            }
             return;
         }
     });
+}
+int lp_analyze_batch_dist_device(lp_ctx* c, const uint8_t* d_logs, const uint64_t* offsets, size_t n_logs, const uint64_t* prior_count,
+                                 int options, lp_result** out) {
+    return analyze_batch_dist(c, d_logs, false, offsets, n_logs, prior_count, options, out);
+}
+int lp_analyze_batch_dist(lp_ctx* c, const uint8_t* logs, const uint64_t* offsets, size_t n_logs, const uint64_t* prior_count,
+                          int options, lp_result** out) {
+    return analyze_batch_dist(c, logs, true, offsets, n_logs, prior_count, options, out);
 }
 
 // Two-phase form with the exchange left on the device: nothing is read back between the phases.
@@ -1473,6 +1434,25 @@ int lp_analyze_device(lp_ctx* c, const uint8_t* d_log, size_t len, const uint64_
 int lp_analyze(lp_ctx* c, const uint8_t* log, size_t len, const uint64_t* prior_count, int options, lp_result** out) {
     const uint64_t off[2] = {0, (uint64_t)len};
     return lp_analyze_batch(c, log, off, 1, prior_count, options, out);
+}
+
+// Page-locked host memory for the caller's log buffers. cudaMemcpyAsync from pageable memory is staged through a
+// driver buffer and blocks the calling thread; from page-locked memory the piecewise copy of lp_analyze* really
+// overlaps the scan. The JVM either lets the library allocate (and wraps the pointer in a MemorySegment) or
+// registers a segment it already owns.
+void* lp_host_alloc(size_t bytes) {
+    void* p = nullptr;
+    const int rc = guarded(nullptr, [&] { CK(cudaHostAlloc(&p, std::max<size_t>(bytes, 1), cudaHostAllocPortable)); });
+    return rc == LP_OK ? p : nullptr;
+}
+void lp_host_free(void* p) { if (p) cudaFreeHost(p); }
+int lp_host_register(void* p, size_t bytes) {
+    if (!p || !bytes) { g_last_error = "NULL or empty range"; return LP_ERR_INVALID; }
+    return guarded(nullptr, [&] { CK(cudaHostRegister(p, bytes, cudaHostRegisterPortable)); });
+}
+int lp_host_unregister(void* p) {
+    if (!p) { g_last_error = "NULL argument"; return LP_ERR_INVALID; }
+    return guarded(nullptr, [&] { CK(cudaHostUnregister(p)); });
 }
 
 int lp_result_get(const lp_result* r, lp_result_view* v) {

@@ -27,8 +27,11 @@ constexpr uint32_t ROWS = 1024;                                      // first-st
 constexpr uint32_t LIST = 1024;                                      // entries per compaction list and pass
 constexpr uint32_t MUL1 = 0x9E3779B1u;
 constexpr size_t TABLE_BYTES = (size_t)ROWS * 128;
-constexpr size_t HALF_BYTES = 2 * STAGE_BYTES + LIST * 2 + LIST * 2 + LIST * 4 + 256;
-constexpr size_t SMEM_BYTES = TABLE_BYTES + 2 * HALF_BYTES;
+constexpr uint32_t WLIST = 64;                                       // newline list entries per warp (1 KiB of log) and tile
+constexpr uint32_t OUT_CAP = 1024;                                   // survivors staged per half and tile
+constexpr uint32_t KEY_BYTES = 8192;                                 // exact gram keys kept in shared memory when 4 << table_bits fits
+constexpr size_t HALF_BYTES = 2 * STAGE_BYTES + 2 * OUT_CAP * 4 + 256;   // stages, survivors (two tiles), state
+constexpr size_t SMEM_BYTES = TABLE_BYTES + KEY_BYTES + 2 * HALF_BYTES;
 
 // row = (H >> 7) & (ROWS - 1), rotation = H & 31; the table bit of a gram is bit (rotation - 1) & 31
 template <int V>
@@ -45,9 +48,7 @@ inline uint32_t host_hash(int variant, uint32_t folded) { return variant == 0 ? 
 struct HalfState {
     unsigned long long bar[2];      // mbarriers of the two stages
     uint32_t tile[2];               // tile index loaded (or to be filled) into each stage
-    uint32_t wtot[16], wex[16];
-    uint32_t total, prefix, ncand;
-    uint32_t k0, inner, events;
+    uint32_t ncand[2], n_nl[2];     // survivors and newlines of the tile in each stage
 };
 static_assert(sizeof(HalfState) <= 256, "HalfState must fit its slot");
 }  // namespace fs
@@ -58,14 +59,10 @@ struct FscanArgs {
     uint32_t n_tiles;                 // tiles of the whole text (the last one covers position `len`)
     uint32_t tile_begin, tile_end;    // this launch's tiles (a log arriving from the host is scanned piece by piece)
     uint32_t* ticket;                 // zeroed counter of this launch
-    unsigned long long* status;       // [n_tiles] look-back words, zeroed per call: flag << 32 | newline count
-    uint32_t* tile_prefix;            // [n_tiles] out: newlines before each tile (k_resolve brackets its line search with it)
-    const uint64_t* log_off;          // [n_logs+1]
-    uint32_t n_logs;
-    uint32_t* line_start;             // [line_cap]
-    uint32_t* line_end;
-    uint32_t* first_line;             // [n_logs+1]
-    uint32_t line_cap;
+    uint32_t tma_tiles;               // tiles [0, tma_tiles) lie, with their halo, inside the text: loaded by bulk copy
+    uint32_t* tile_counts;            // [n_tiles] out: newlines per tile (k_scan_tiles turns them into prefixes)
+    uint16_t* warp_counts;            // [n_tiles][16] out: newlines per 1 KiB warp span; above fs::WLIST the span's list was not written
+    uint16_t* nl_lists;               // [n_tiles][16][fs::WLIST] out: the newlines of each warp span, see k_expand
     const uint32_t* bit_table;        // fs::ROWS words (variants 0/1) or the 64 KiB byte table (variant 2)
     const uint32_t* gram_keys;        // 2^table_bits folded grams, 0 = empty
     uint32_t table_bits;
@@ -143,18 +140,22 @@ template <int V>
 __global__ void __launch_bounds__(fs::THREADS, 1) k_fscan(FscanArgs a) {
     extern __shared__ __align__(128) uint8_t fs_smem[];
     const int half = threadIdx.x >> 9, t = threadIdx.x & (fs::HALF - 1), lane = t & 31, warp = t >> 5;
-    uint8_t* const hbase = fs_smem + fs::TABLE_BYTES + (size_t)half * fs::HALF_BYTES;
+    uint32_t* const s_keys = reinterpret_cast<uint32_t*>(fs_smem + fs::TABLE_BYTES);          // exact gram keys (when they fit)
+    uint8_t* const hbase = fs_smem + fs::TABLE_BYTES + fs::KEY_BYTES + (size_t)half * fs::HALF_BYTES;
     uint8_t* const stages = hbase;
-    uint16_t* const s_nll = reinterpret_cast<uint16_t*>(hbase + 2 * fs::STAGE_BYTES);
-    uint16_t* const s_hl = s_nll + fs::LIST;
-    uint32_t* const s_out = reinterpret_cast<uint32_t*>(s_hl + fs::LIST);
-    fs::HalfState* const hs = reinterpret_cast<fs::HalfState*>(s_out + fs::LIST);
+    uint32_t* const s_outs = reinterpret_cast<uint32_t*>(hbase + 2 * fs::STAGE_BYTES);        // survivors, one buffer per stage
+    fs::HalfState* const hs = reinterpret_cast<fs::HalfState*>(s_outs + 2 * fs::OUT_CAP);
     const uint32_t lane4 = (uint32_t)lane * 4u;
     const uint32_t full = 0xffffffffu;
+    const bool keys_in_smem = (4u << a.table_bits) <= fs::KEY_BYTES;
+    const uint32_t* const keys = keys_in_smem ? s_keys : a.gram_keys;
+    const uint32_t tmask = (1u << a.table_bits) - 1u, kshift = 32 - a.table_bits;
 
     if (t == 0) {
         fs_mbar_init(&hs->bar[0], 1);
         fs_mbar_init(&hs->bar[1], 1);
+        hs->ncand[0] = hs->ncand[1] = 0;
+        hs->n_nl[0] = hs->n_nl[1] = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (a.use_filter) {
@@ -166,16 +167,17 @@ __global__ void __launch_bounds__(fs::THREADS, 1) k_fscan(FscanArgs a) {
             uint32_t* dst = reinterpret_cast<uint32_t*>(fs_smem);
             for (uint32_t i = threadIdx.x; i < fs::ROWS * 32; i += fs::THREADS) dst[i] = __ldg(a.bit_table + (i >> 5));
         }
+        if (keys_in_smem)
+            for (uint32_t i = threadIdx.x; i <= tmask; i += fs::THREADS) s_keys[i] = __ldg(a.gram_keys + i);
     }
     __syncthreads();
-    if (t == 0) {
-        for (int s = 0; s < 2; ++s) {
-            const uint32_t tile = a.tile_begin + atomicAdd(a.ticket, 1u);
-            hs->tile[s] = tile;
-            if (tile < a.tile_end && fs_tma_ok(tile, a.len))
-                fs_tma_load(stages + s * fs::STAGE_BYTES, a.text + (uint64_t)tile * fs::TILE, fs::TILE + fs::HALO, &hs->bar[s]);
-        }
-    }
+    auto next_tile = [&](int s) {       // thread 0 of the half: take a ticket and start the copy into stage s
+        const uint32_t tile = a.tile_begin + atomicAdd(a.ticket, 1u);
+        hs->tile[s] = tile;
+        if (tile < a.tile_end && tile < a.tma_tiles)
+            fs_tma_load(stages + s * fs::STAGE_BYTES, a.text + (uint64_t)tile * fs::TILE, fs::TILE + fs::HALO, &hs->bar[s]);
+    };
+    if (t == 0) { next_tile(0); next_tile(1); }
     fs_half_sync(half);
 
     uint32_t parity = 0;
@@ -185,7 +187,8 @@ __global__ void __launch_bounds__(fs::THREADS, 1) k_fscan(FscanArgs a) {
         if (tile >= a.tile_end) break;
         const uint64_t base = (uint64_t)tile * fs::TILE;
         uint8_t* const stage = stages + s * fs::STAGE_BYTES;
-        const bool tma = fs_tma_ok(tile, a.len);
+        uint32_t* const s_out = s_outs + s * fs::OUT_CAP;
+        const bool tma = tile < a.tma_tiles;
         if (tma) {
             fs_mbar_wait(&hs->bar[s], (parity >> s) & 1u);
             parity ^= 1u << s;
@@ -193,14 +196,6 @@ __global__ void __launch_bounds__(fs::THREADS, 1) k_fscan(FscanArgs a) {
             for (uint32_t i = t; i < fs::STAGE_BYTES / 16; i += fs::HALF)
                 reinterpret_cast<uint4*>(stage)[i] = load16_any(a.text, base + 16ull * i, a.len);
             fs_half_sync(half);
-        }
-        if (t == 32) {      // where the logs of a batch begin, relative to this tile
-            const uint64_t tile_end = base + fs::TILE;
-            const uint32_t j0 = upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, base);
-            hs->k0 = j0 - 1;
-            hs->inner = (j0 <= a.n_logs && a.log_off[j0] < tile_end) ? 1u : 0u;
-            const uint32_t j1 = lower_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, base);
-            hs->events = (j1 <= a.n_logs && a.log_off[j1] < tile_end) ? 1u : 0u;
         }
 
         // ---- phase A: 32 contiguous bytes per thread
@@ -219,176 +214,207 @@ __global__ void __launch_bounds__(fs::THREADS, 1) k_fscan(FscanArgs a) {
             }
         }
 
-        // ---- phase B: block scan of (newlines, hits)
-        const uint32_t cn = __popc(P), ch = __popc(hm);
-        const uint32_t packed = cn | (ch << 16);
-        uint32_t inc = packed;
+        // ---- phase B, newlines: position in the tile | ('\r' before it) << 15, in position order, into this warp's slot of
+        // the tile's newline lists (no block-wide rank needed: k_expand adds the counts of the warps in front). A warp
+        // with more newlines than its slot holds marks the tile dense; k_expand then re-reads that tile from the text.
+        {
+            const uint32_t cn = __popc(P);
+            uint32_t inc = cn;
 #pragma unroll
-        for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(full, inc, o); if (lane >= o) inc += y; }
-        if (lane == 31) hs->wtot[warp] = inc;
-        fs_half_sync(half);
-        if (warp == 0) {
-            const uint32_t w = lane < 16 ? hs->wtot[lane] : 0u;
-            uint32_t wi = w;
-#pragma unroll
-            for (int o = 1; o < 16; o <<= 1) { const uint32_t y = __shfl_up_sync(full, wi, o); if (lane >= o) wi += y; }
-            if (lane < 16) hs->wex[lane] = wi - w;
-            if (lane == 15) {
-                hs->total = wi;
-                hs->ncand = 0;
-                // the tile's newline count is published as early as possible: later tiles look back at it
-                volatile unsigned long long* stw = a.status + tile;
-                if (tile != 0) *stw = (1ull << 32) | (wi & 0xFFFFu);
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(full, inc, o); if (lane >= o) inc += y; }
+            const uint32_t wtotal = __shfl_sync(full, inc, 31);
+            if (wtotal) {
+                uint16_t* const wl = a.nl_lists + ((size_t)tile * 16 + warp) * fs::WLIST;
+                if (wtotal <= fs::WLIST) {
+                    const uint32_t excl = inc - cn;
+                    uint32_t m = P;
+                    while (m) {
+                        const uint32_t b = __ffs(m) - 1;
+                        m &= m - 1;
+                        const uint32_t nq = b & 7u, j = b >> 3;
+                        const uint32_t lt = (((1u << nq) - 1u) * 0x01010101u) | ((0x01010101u << nq) & ((1u << (8u * j)) - 1u));
+                        const uint32_t pt = 32 * t + 4 * nq + j;
+                        const uint32_t prev = pt ? stage[pt - 1] : (base ? a.text[base - 1] : 0u);
+                        wl[excl + __popc(P & lt)] = (uint16_t)(pt | (prev == '\r' ? 0x8000u : 0u));
+                    }
+                }
+                if (lane == 0) atomicAdd(&hs->n_nl[s], wtotal);
+            }
+            if (lane == 0) a.warp_counts[(size_t)tile * 16 + warp] = (uint16_t)min(wtotal, 0xFFFFu);
+        }
+        // ---- phase B, first-stage hits against the exact gram keys (shared memory when they fit); the window is
+        // re-read from the staged tile. Survivors are staged per half and flushed with one global atomic per tile.
+        while (hm) {
+            const uint32_t i = __ffs(hm) - 1;
+            hm &= hm - 1;
+            const uint32_t pt = 32 * t + i, al = pt & ~3u;
+            const uint32_t wlo = *reinterpret_cast<const uint32_t*>(stage + al), whi = *reinterpret_cast<const uint32_t*>(stage + al + 4);
+            const uint32_t f = __funnelshift_r(wlo, whi, (pt & 3u) * 8u) | 0x20202020u;
+            uint32_t slot = (f * GRAM_MUL2) >> kshift;
+            uint32_t key;
+            while ((key = keys[slot]) != 0u && key != f) slot = (slot + 1) & tmask;
+            if (key == f) {
+                const uint32_t ob = atomicAdd(&hs->ncand[s], 1u);
+                if (ob < fs::OUT_CAP) s_out[ob] = (uint32_t)(base + pt);
+                else {      // a tile dense with gram occurrences: straight to the global queue
+                    const uint32_t gi = atomicAdd(&a.ctr->n_cand, 1u);
+                    if (gi < a.cand_cap) a.cand[gi] = (uint32_t)(base + pt);
+                    else atomicOr(&a.ctr->overflow, 1u);
+                }
             }
         }
-        fs_half_sync(half);
-        const uint32_t excl = hs->wex[warp] + inc - packed;
-        const uint32_t excl_nl = excl & 0xFFFFu, excl_hit = excl >> 16;
-        const uint32_t n_nl = hs->total & 0xFFFFu, n_hit = hs->total >> 16;
-        const uint32_t passes = max(1u, max((n_nl + fs::LIST - 1) / fs::LIST, (n_hit + fs::LIST - 1) / fs::LIST));
-        uint32_t prefix = 0;
-        for (uint32_t pass = 0; pass < passes; ++pass) {
-            const uint32_t lo = pass * fs::LIST;
-            // compaction: position-in-tile of every newline / first-stage hit, in position order
-            {
-                uint32_t m = P;
-                while (m) {
-                    const uint32_t b = __ffs(m) - 1;
-                    m &= m - 1;
-                    const uint32_t nq = b & 7u, j = b >> 3;
-                    const uint32_t lt = (((1u << nq) - 1u) * 0x01010101u) | ((0x01010101u << nq) & ((1u << (8u * j)) - 1u));
-                    const uint32_t r = excl_nl + __popc(P & lt) - lo;
-                    if (r < fs::LIST) s_nll[r] = (uint16_t)(32 * t + 4 * nq + j);
-                }
-                m = hm;
-                uint32_t r = excl_hit - lo;
-                while (m) {
-                    const uint32_t i = __ffs(m) - 1;
-                    m &= m - 1;
-                    if (r < fs::LIST) s_hl[r] = (uint16_t)(32 * t + i);
-                    ++r;
+        fs_half_sync(half);       // every warp is done with the stage; the tile's counts and survivors are complete
+        // (the only barrier of a tile: counters and survivors are kept per stage, so the next tile starts at once)
+        if (t == 0) {
+            a.tile_counts[tile] = hs->n_nl[s];
+            hs->n_nl[s] = 0;
+            next_tile(s);         // refill the stage
+        }
+        if (warp == 15) {       // survivors -> candidate queue, one global atomic
+            const uint32_t nc = min(hs->ncand[s], fs::OUT_CAP);
+            if (nc) {
+                uint32_t gb = 0;
+                if (lane == 0) gb = atomicAdd(&a.ctr->n_cand, nc);
+                gb = __shfl_sync(full, gb, 0);
+                for (uint32_t q = lane; q < nc; q += 32) {
+                    if (gb + q < a.cand_cap) a.cand[gb + q] = s_out[q];
+                    else atomicOr(&a.ctr->overflow, 1u);
                 }
             }
-            fs_half_sync(half);
-            if (warp == 0) {
-                if (pass == 0) {
-                    // decoupled look-back over the tiles' newline counts. The halves run in lock step, so the
-                    // nearest published prefix is usually a whole wave (~2 x SM count tiles) back: each round
-                    // loads LB_U x 32 status words at once (independent loads, one L2 round trip) instead of
-                    // walking back 32 tiles per round trip. Lane i of group u inspects tile look - 32 u - i.
-                    const uint32_t aggregate = n_nl;
-                    uint32_t run = 0;
-                    if (tile != 0) {
-                        constexpr int LB_U = 10;
-                        int look = (int)tile - 1;
-                        bool done = false;
-                        while (!done) {
-                            unsigned long long sw[LB_U];
+            __syncwarp();
+            if (lane == 0) hs->ncand[s] = 0;
+        }
+    }
+}
+
+// ------------------------------------------------------------------ line offsets from the newline lists
+// After k_scan_tiles has turned the tiles' newline counts into exclusive prefixes: every '\n' at p ends line g
+// (at p, or p-1 after a '\r') and starts line g+1 at p+1; the log boundaries of a batch act as line breaks.
+// One block per tile. A tile whose 16 warp spans all fit their list slots is expanded from the lists (no access
+// to the text); a denser tile is re-read from the text, 64 bytes per thread, with one block-wide prefix.
+struct ExpandArgs {
+    const uint8_t* text;
+    uint64_t len;
+    uint32_t n_tiles;
+    const uint32_t* tile_prefix;      // exclusive newline count before each tile (tile_counts after k_scan_tiles)
+    const uint16_t* warp_counts;      // [n_tiles][16]
+    const uint16_t* nl_lists;         // [n_tiles][16][fs::WLIST]
+    const uint64_t* log_off;          // [n_logs+1]
+    uint32_t n_logs;
+    uint32_t* line_start;
+    uint32_t* line_end;
+    uint32_t* first_line;             // [n_logs+1]
+    uint32_t line_cap;
+    Counters* ctr;
+};
+constexpr int EX_THREADS = 256;
+__global__ void __launch_bounds__(EX_THREADS) k_expand(ExpandArgs a) {
+    __shared__ uint32_t s_warp[EX_THREADS / 32];
+    __shared__ uint32_t s_pre[17];      // exclusive prefix of the 16 span counts; [16] = the tile's total
+    __shared__ uint32_t s_dense;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (uint32_t tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
+        const uint64_t base = (uint64_t)tile * fs::TILE, tile_end = base + fs::TILE;
+        const uint32_t prefix = a.tile_prefix[tile];
+        __syncthreads();        // the previous tile's shared values have been read
+        if (threadIdx.x < 32) {
+            const uint32_t c = lane < 16 ? a.warp_counts[(size_t)tile * 16 + lane] : 0u;
+            uint32_t inc = c;
 #pragma unroll
-                            for (int u = 0; u < LB_U; ++u) {
-                                const int tt = look - 32 * u - lane;
-                                sw[u] = tt >= 0 ? *(volatile unsigned long long*)(a.status + tt) : (2ull << 32);
-                            }
-                            uint32_t add = 0;       // per-lane partial sum of the groups accepted in this round
-                            int accepted = 0;
-                            bool stall = false;
+            for (int o = 1; o < 16; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += y; }
+            if (lane < 16) s_pre[lane] = inc - c;
+            if (lane == 15) s_pre[16] = inc;
+            const unsigned over = __ballot_sync(0xffffffffu, c > fs::WLIST);
+            if (lane == 0) s_dense = over != 0;
+        }
+        __syncthreads();
+        const uint32_t count = s_pre[16];
+        // where the logs begin relative to this tile (a single log: no loads)
+        uint32_t k0 = 0;
+        bool inner = false, events = false;
+        if (a.n_logs == 1) {
+            k0 = base == a.len ? 1u : 0u;
+            events = base == 0 || a.len < tile_end;
+        } else {
+            const uint32_t j0 = upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, base);
+            k0 = j0 - 1;
+            inner = j0 <= a.n_logs && a.log_off[j0] < tile_end;
+            const uint32_t j1 = lower_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, base);
+            events = j1 <= a.n_logs && a.log_off[j1] < tile_end;
+        }
+        if (!s_dense) {
+            const uint16_t* __restrict__ lists = a.nl_lists + (size_t)tile * 16 * fs::WLIST;
+            for (uint32_t e = threadIdx.x; e < count; e += EX_THREADS) {
+                uint32_t w = 0;         // the span that holds the tile's e-th newline
 #pragma unroll
-                            for (int u = 0; u < LB_U; ++u) {
-                                if (done || stall) continue;
-                                const uint32_t flag = (uint32_t)(sw[u] >> 32), val = (uint32_t)sw[u];
-                                const unsigned pm = __ballot_sync(full, flag == 2u), zm = __ballot_sync(full, flag == 0u);
-                                if (pm) {
-                                    const int fp = __ffs(pm) - 1;
-                                    const unsigned upto = fp == 31 ? 0xFFFFFFFFu : ((2u << fp) - 1u);
-                                    if ((zm & upto) == 0) { if (lane <= fp) add += val; done = true; }
-                                    else stall = true;
-                                } else if (zm == 0) { add += val; ++accepted; }
-                                else stall = true;
-                            }
-#pragma unroll
-                            for (int o = 16; o; o >>= 1) add += __shfl_xor_sync(full, add, o);
-                            run += add;
-                            look -= 32 * accepted;
-                            if (stall) __nanosleep(100);
-                        }
-                    }
-                    if (lane == 0) {
-                        *(volatile unsigned long long*)(a.status + tile) = (2ull << 32) | (unsigned long long)(run + aggregate);
-                        hs->prefix = run;
-                        a.tile_prefix[tile] = run;
-                        if (tile + 1 == a.n_tiles) { a.ctr->total_nl = run + aggregate; a.ctr->n_lines_total = run + aggregate + a.n_logs; }
-                    }
-                }
-            } else {
-                // first-stage hits against the exact gram keys; the window is re-read from the staged tile
-                const uint32_t cnt = min(n_hit - min(n_hit, lo), fs::LIST);
-                const uint32_t tmask = (1u << a.table_bits) - 1u;
-                for (uint32_t e0 = (uint32_t)(warp - 1) * 32u; e0 < cnt; e0 += 15u * 32u) {
-                    const uint32_t e = e0 + lane;
-                    bool keep = false;
-                    uint32_t pt = 0;
-                    if (e < cnt) {
-                        pt = s_hl[e];
-                        const uint32_t al = pt & ~3u;
-                        const uint32_t wlo = *reinterpret_cast<const uint32_t*>(stage + al), whi = *reinterpret_cast<const uint32_t*>(stage + al + 4);
-                        const uint32_t f = __funnelshift_r(wlo, whi, (pt & 3u) * 8u) | 0x20202020u;
-                        uint32_t slot = (f * GRAM_MUL2) >> (32 - a.table_bits);
-                        uint32_t key;
-                        while ((key = __ldg(a.gram_keys + slot)) != 0u && key != f) slot = (slot + 1) & tmask;
-                        keep = key == f;
-                    }
-                    const unsigned votes = __ballot_sync(full, keep);
-                    if (votes) {
-                        uint32_t ob = 0;
-                        if (lane == 0) ob = atomicAdd(&hs->ncand, (uint32_t)__popc(votes));
-                        ob = __shfl_sync(full, ob, 0) + __popc(votes & ((1u << lane) - 1u));
-                        if (keep) s_out[ob] = (uint32_t)(base + pt);
-                    }
-                }
+                for (int q = 8; q; q >>= 1) if (s_pre[w + q] <= e) w += q;
+                const uint32_t ent = lists[w * fs::WLIST + (e - s_pre[w])];
+                const uint64_t p = base + (ent & 0x3FFFu);
+                uint32_t k = k0;
+                if (inner) k = upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, p) - 1;
+                const uint32_t g = prefix + e + k;
+                const uint64_t log_begin = a.n_logs == 1 ? 0ull : a.log_off[k];
+                const bool cr = (ent >> 15) != 0 && p > log_begin;
+                if (g + 1 < a.line_cap) {
+                    a.line_end[g] = (uint32_t)(p - (cr ? 1 : 0));
+                    a.line_start[g + 1] = (uint32_t)(p + 1);
+                } else atomicOr(&a.ctr->overflow, 64u);
             }
-            fs_half_sync(half);
-            if (pass == 0) prefix = hs->prefix;
-            {   // newlines -> line_end[g] / line_start[g+1] (the \r?\n rule; log boundaries of a batch shift the index)
-                const uint32_t cnt = min(n_nl - min(n_nl, lo), fs::LIST);
-                const uint32_t k0 = hs->k0;
-                const bool inner = hs->inner != 0;
-                for (uint32_t e = t; e < cnt; e += fs::HALF) {
-                    const uint32_t pt = s_nll[e];
-                    const uint64_t p = base + pt;
-                    uint32_t k = k0;
-                    if (inner) k = upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, p) - 1;
-                    const uint32_t g = prefix + lo + e + k;
-                    bool cr = false;
-                    if (p > a.log_off[k]) cr = (pt ? stage[pt - 1] : a.text[p - 1]) == '\r';
-                    if (g + 1 < a.line_cap) {
-                        a.line_end[g] = (uint32_t)(p - (cr ? 1 : 0));
-                        a.line_start[g + 1] = (uint32_t)(p + 1);
+            if (events) {       // start of log j / end of log j-1 inside this tile: newlines before it = spans in front + a binary search in its span
+                uint32_t j = lower_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, base) + threadIdx.x;
+                for (; j <= a.n_logs && a.log_off[j] < tile_end; j += EX_THREADS) {
+                    const uint64_t b = a.log_off[j];
+                    const uint32_t want = (uint32_t)(b - base), w = want >> 10;
+                    const uint16_t* __restrict__ list = lists + w * fs::WLIST;
+                    uint32_t lo = 0, hi = s_pre[w + 1] - s_pre[w];
+                    while (lo < hi) { const uint32_t mid = (lo + hi) >> 1; if ((list[mid] & 0x3FFFu) < want) lo = mid + 1; else hi = mid; }
+                    const uint32_t nlb = prefix + s_pre[w] + lo;
+                    a.first_line[j] = nlb + j;
+                    if (nlb + j < a.line_cap) {
+                        if (j < a.n_logs) a.line_start[nlb + j] = (uint32_t)b;
+                        if (j > 0) a.line_end[nlb + j - 1] = (uint32_t)b;
                     } else atomicOr(&a.ctr->overflow, 64u);
                 }
             }
-            if (warp == 15) {   // survivors of this pass -> candidate queue, one global atomic
-                const uint32_t nc = hs->ncand;
-                if (nc) {
-                    uint32_t gb = 0;
-                    if (lane == 0) gb = atomicAdd(&a.ctr->n_cand, nc);
-                    gb = __shfl_sync(full, gb, 0);
-                    for (uint32_t q = lane; q < nc; q += 32) {
-                        if (gb + q < a.cand_cap) a.cand[gb + q] = s_out[q];
-                        else atomicOr(&a.ctr->overflow, 1u);
-                    }
-                }
-            }
-            if (pass + 1 < passes) {
-                fs_half_sync(half);
-                if (t == 0) hs->ncand = 0;
-            }
+            continue;
         }
-        if (hs->events && base + 32ull * t <= a.len) {      // start of log j / end of log j-1 inside this thread's bytes
-            const uint64_t pos = base + 32ull * t;
+        // dense tile: from the text
+        const uint64_t pos = base + (uint64_t)threadIdx.x * 64;
+        unsigned long long nl = 0;        // bit i: byte pos+i is '\n'
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const uint64_t cp = pos + 16 * q;
+            if (cp < a.len) nl |= (unsigned long long)nl_mask16(load16(a.text, cp, a.len)) << (16 * q);
+        }
+        const uint32_t cnt = __popcll(nl);
+        uint32_t inc = cnt;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { uint32_t y = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += y; }
+        if (lane == 31) s_warp[warp] = inc;
+        __syncthreads();
+        uint32_t wbase = 0;
+#pragma unroll
+        for (int w = 0; w < EX_THREADS / 32; ++w) { const uint32_t y = s_warp[w]; if (w < warp) wbase += y; }
+        const uint32_t excl = prefix + wbase + inc - cnt;     // newlines before this thread's bytes
+        unsigned long long m = nl;
+        while (m) {
+            const int i = __ffsll((long long)m) - 1;
+            m &= m - 1;
+            const uint64_t p = pos + i;
+            uint32_t k = k0;
+            if (inner) k = upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, p) - 1;
+            const uint32_t g = excl + __popcll(nl & ((1ull << i) - 1ull)) + k;
+            const bool cr = p > a.log_off[k] && a.text[p - 1] == '\r';
+            if (g + 1 < a.line_cap) {
+                a.line_end[g] = (uint32_t)(p - (cr ? 1 : 0));
+                a.line_start[g + 1] = (uint32_t)(p + 1);
+            } else atomicOr(&a.ctr->overflow, 64u);
+        }
+        if (events && pos <= a.len) {
             uint32_t j = lower_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, pos);
-            while (j <= a.n_logs && a.log_off[j] < pos + 32) {
+            while (j <= a.n_logs && a.log_off[j] < pos + 64) {
                 const uint64_t b = a.log_off[j];
-                const uint32_t nlb = prefix + excl_nl + __popc(P & fs_below((uint32_t)(b - pos)));
+                const uint32_t nlb = excl + __popcll(nl & ((1ull << (uint32_t)(b - pos)) - 1ull));
                 a.first_line[j] = nlb + j;
                 if (nlb + j < a.line_cap) {
                     if (j < a.n_logs) a.line_start[nlb + j] = (uint32_t)b;
@@ -396,13 +422,6 @@ __global__ void __launch_bounds__(fs::THREADS, 1) k_fscan(FscanArgs a) {
                 } else atomicOr(&a.ctr->overflow, 64u);
                 ++j;
             }
-        }
-        fs_half_sync(half);       // the stage and the lists are free again
-        if (t == 0) {
-            const uint32_t nt = a.tile_begin + atomicAdd(a.ticket, 1u);
-            hs->tile[s] = nt;
-            if (nt < a.tile_end && fs_tma_ok(nt, a.len))
-                fs_tma_load(stage, a.text + (uint64_t)nt * fs::TILE, fs::TILE + fs::HALO, &hs->bar[s]);
         }
     }
 }

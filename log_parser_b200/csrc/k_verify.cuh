@@ -510,9 +510,10 @@ __global__ void __launch_bounds__(128) k_verify_vm_always(VerifyArgs a, DevPlan 
 // The multi-pattern DFA scan proper: every line is walked once through up to DS_MAXG product
 // automata (context regexes of CAS:27-34 + every DFA pattern without a usable literal, AS:93-95).
 // Transition tables, class maps and result masks are resident in shared memory for the life of the
-// CTA. One thread walks one line; it streams the line through registers with 16-byte loads, one
-// chunk prefetched ahead. (A TMA-staged shared-memory tile variant was measured first: with ~240
-// lines per 32 KiB tile the per-tile barrier left most threads idle — profiles/r01_v2_*.)
+// CTA. One thread walks one line; it streams the line through registers with 8-byte loads, one
+// word prefetched ahead. (Lines are ~135 bytes and a walk is one dependent shared-memory lookup per
+// byte, so the kernel is bound by that chain, not by how the text arrives; the TMA-staged tiles of
+// the scan are used by k_fscan, where every byte of a tile is needed.)
 constexpr uint32_t DS_THREADS = 256, DS_MAXG = 4;
 
 struct DfaScanArgs {

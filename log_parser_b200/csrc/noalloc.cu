@@ -15,6 +15,8 @@
 //     LP_ERR_LIMIT before anything is launched;
 //   * the first call on a given device resolves the scratch array's device address
 //     (cudaGetSymbolAddress). Make that first call outside of any CUDA stream capture;
+//   * every call is synchronous: it reads the overflow flag back and waits for `stream` to drain
+//     before it returns (the caller's current device is left as it was);
 //   * all calls on one device share the one scratch array. Two calls whose kernels may overlap on
 //     the GPU (different streams, different host threads) race on it: serialise them yourself;
 //   * the scratch keeps whatever the previous call left behind; the words that must start at zero
@@ -35,7 +37,7 @@ constexpr uint32_t NA_TILE = NA_THREADS * 16 * NA_ITERS;                       /
 constexpr unsigned long long NA_MAX_BYTES = 1ull << 30;                        // 1 GiB per call
 constexpr uint32_t NA_MAX_TILES = (uint32_t)(NA_MAX_BYTES / NA_TILE) + 1;
 constexpr uint32_t NA_HDR_WORDS = 64;                                          // 256-byte header
-// header words: [0] newline total, [1] capacity-overflow flag; the rest is spare.
+// header words: [0] newline total, [1] capacity-overflow flag, [2] 1 + index of the last non-empty segment; the rest is spare.
 // then one exclusive newline count per tile.
 static __device__ __align__(256) uint32_t g_split_scratch[NA_HDR_WORDS + NA_MAX_TILES];
 
@@ -154,6 +156,18 @@ __global__ void __launch_bounds__(NA_THREADS) na_write(const uint8_t* __restrict
     }
 }
 
+// 1 + index of the last non-empty segment, found by all threads (a log may end in millions of blank lines)
+__global__ void na_last_nonempty(uint32_t* __restrict__ scratch, const uint32_t* __restrict__ line_start,
+                                 const uint32_t* __restrict__ line_end, unsigned long long cap) {
+    const unsigned long long segments = (unsigned long long)scratch[0] + 1;
+    if (segments > cap) return;
+    uint32_t best = 0;
+    for (unsigned long long g = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; g < segments; g += (unsigned long long)gridDim.x * blockDim.x)
+        if (line_end[g] != line_start[g]) best = (uint32_t)g + 1;      // g grows along the loop: the last hit is this thread's largest
+    for (int o = 16; o; o >>= 1) best = max(best, __shfl_xor_sync(0xffffffffu, best, o));
+    if ((threadIdx.x & 31) == 0 && best) atomicMax(&scratch[2], best);
+}
+
 // String.split's limit-0 rule: drop trailing empty strings; an input without any separator stays [input]
 __global__ void na_finish(const uint32_t* __restrict__ scratch, const uint32_t* __restrict__ line_start,
                           const uint32_t* __restrict__ line_end, unsigned long long cap, unsigned long long* __restrict__ counts) {
@@ -161,10 +175,7 @@ __global__ void na_finish(const uint32_t* __restrict__ scratch, const uint32_t* 
     counts[1] = segments;
     counts[2] = scratch[1];
     if (scratch[1]) { counts[0] = 0; return; }
-    unsigned long long n = segments;
-    if (n > 1)
-        while (n > 0 && line_end[n - 1] == line_start[n - 1]) --n;
-    counts[0] = n;
+    counts[0] = segments > 1 ? (unsigned long long)scratch[2] : segments;
 }
 
 std::mutex g_setup_mu;
@@ -195,6 +206,12 @@ extern "C" int lp_split_lines_noalloc(int device, const uint8_t* d_log, size_t l
         return LP_ERR_LIMIT;
     }
     if (capacity == 0) { say(err, errlen, "capacity is 0: even an empty log has one line segment"); return LP_ERR_LIMIT; }
+    // the caller's current device is put back on every way out
+    struct DeviceGuard {
+        int prev = -1;
+        ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+    } guard;
+    if (cudaGetDevice(&guard.prev) != cudaSuccess) guard.prev = -1;
     cudaError_t e = cudaSetDevice(device);
     if (e != cudaSuccess) return cuda_fail(err, errlen, "cudaSetDevice", e);
 
@@ -222,6 +239,7 @@ extern "C" int lp_split_lines_noalloc(int device, const uint8_t* d_log, size_t l
     if (n_tiles) na_count<<<grid, NA_THREADS, 0, st>>>(d_log, len, n_tiles, scratch);
     na_scan<<<1, 1024, 0, st>>>(scratch, n_tiles, len, d_line_start, d_line_end, capacity);
     if (n_tiles) na_write<<<grid, NA_THREADS, 0, st>>>(d_log, len, n_tiles, scratch, d_line_start, d_line_end, capacity);
+    na_last_nonempty<<<grid, NA_THREADS, 0, st>>>(scratch, d_line_start, d_line_end, capacity);
     na_finish<<<1, 1, 0, st>>>(scratch, d_line_start, d_line_end, capacity, reinterpret_cast<unsigned long long*>(d_counts));
     e = cudaGetLastError();
     if (e != cudaSuccess) return cuda_fail(err, errlen, "kernel launch", e);

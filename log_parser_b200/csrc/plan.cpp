@@ -4,6 +4,7 @@
 #include <algorithm>
 #include <cstring>
 #include <map>
+#include <stdexcept>
 
 namespace lpx {
 namespace {
@@ -40,6 +41,34 @@ bool blank(const std::string& s) {
 }  // namespace
 
 void select_grams(Plan& pl, const uint8_t* sample, size_t sample_len);
+
+std::vector<PlanPatternIn> plan_input_from_desc(const lp_pattern_desc* pats, size_t n, int64_t* bad_pattern) {
+    std::vector<PlanPatternIn> in(n);
+    for (size_t i = 0; i < n; ++i) {
+        const lp_pattern_desc& d = pats[i];
+        if (!d.primary_regex) { if (bad_pattern) *bad_pattern = (int64_t)i; throw std::invalid_argument("primary_regex is NULL"); }
+        in[i].has_id = d.id != nullptr;
+        if (d.id) in[i].id = d.id;
+        in[i].primary = d.primary_regex;
+        in[i].confidence = d.confidence; in[i].severity = d.severity_multiplier;
+        in[i].has_context = d.has_context; in[i].before = d.lines_before; in[i].after = d.lines_after;
+        for (uint32_t s = 0; s < d.n_secondaries; ++s) {
+            if (!d.secondaries[s].regex) { if (bad_pattern) *bad_pattern = (int64_t)i; throw std::invalid_argument("secondary regex is NULL"); }
+            in[i].secs.push_back({d.secondaries[s].regex, d.secondaries[s].weight, d.secondaries[s].proximity_window});
+        }
+        for (uint32_t s = 0; s < d.n_sequences; ++s) {
+            PlanPatternIn::Seq q;
+            q.bonus = d.sequences[s].bonus_multiplier;
+            for (uint32_t e = 0; e < d.sequences[s].n_events; ++e) {
+                if (!d.sequences[s].event_regex[e]) { if (bad_pattern) *bad_pattern = (int64_t)i; throw std::invalid_argument("sequence event regex is NULL"); }
+                q.events.push_back(d.sequences[s].event_regex[e]);
+            }
+            in[i].seqs.push_back(std::move(q));
+        }
+    }
+    return in;
+}
+
 
 void serialise_group(const std::vector<uint32_t>& rx, const MultiDfa& d, std::vector<uint32_t>& blob) {
     const uint32_t ns = d.n_states(), nc = d.n_classes, nbyte = nc - 2;

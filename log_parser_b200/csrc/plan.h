@@ -8,6 +8,7 @@
 #include <string>
 #include <vector>
 
+#include "../../include/logparser_b200.h"
 #include "rx.h"
 #include "vm.h"
 
@@ -95,6 +96,8 @@ struct Plan {
     uint32_t n_vm = 0;
 };
 
+// lp_pattern_desc[] of the C ABI -> owned strings; throws std::invalid_argument on a NULL regex (*bad = its pattern).
+std::vector<PlanPatternIn> plan_input_from_desc(const lp_pattern_desc* pats, size_t n, int64_t* bad);
 // Throws RegexSyntaxError / RegexUnsupported; *bad receives the flat pattern index.
 void build_plan(const std::vector<PlanPatternIn>& pats, Plan& out, int64_t* bad);
 void serialise_group(const std::vector<uint32_t>& rx, const MultiDfa& d, std::vector<uint32_t>& blob);

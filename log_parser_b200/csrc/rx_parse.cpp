@@ -68,6 +68,41 @@ void close_case(CpSet& s) {
     cpset_normalize(s);
 }
 
+#include "unicode_tables.inc"
+
+// names are compared upper-cased with ' ', '_' and '-' removed (UnicodeScript.forName / UnicodeBlock.forName are lenient)
+std::string uni_norm(const std::string& name) {
+    std::string o;
+    for (unsigned char ch : name) {
+        if (ch == ' ' || ch == '_' || ch == '-') continue;
+        o.push_back((char)((ch >= 'a' && ch <= 'z') ? ch - 32 : ch));
+    }
+    return o;
+}
+bool uni_find(const UniProp* tab, const std::string& norm, CpSet& out) {
+    for (; tab->name; ++tab) {
+        if (norm != tab->name) continue;
+        out.clear();
+        for (unsigned i = 0; i < tab->n; ++i) out.push_back({tab->r[i].lo, tab->r[i].hi});
+        return true;
+    }
+    return false;
+}
+CpSet uni_get(const UniProp* tab, const char* norm) {
+    CpSet s;
+    if (!uni_find(tab, norm, s)) throw std::logic_error(std::string("missing Unicode table ") + norm);
+    return s;
+}
+// UNICODE_CASE closure: every code point whose simple case folding equals that of a member joins the set
+void close_case_unicode(CpSet& s) {
+    cpset_normalize(s);
+    CpSet extra;
+    for (unsigned i = 0; i < UNI_CASE_PAIRS_N; ++i)
+        if (cpset_has(s, UNI_CASE_PAIRS[i][0]) && !cpset_has(s, UNI_CASE_PAIRS[i][1])) extra.push_back({UNI_CASE_PAIRS[i][1], UNI_CASE_PAIRS[i][1]});
+    s.insert(s.end(), extra.begin(), extra.end());
+    cpset_normalize(s);
+}
+
 std::vector<uint32_t> utf8_to_cps(const std::string& in) {
     std::vector<uint32_t> out;
     const unsigned char* s = reinterpret_cast<const unsigned char*>(in.data());
@@ -115,10 +150,10 @@ public:
     uint32_t raw(size_t k = 0) const { return at + k < src.size() ? src[at + k] : END; }
     uint32_t take() { ws(); return at < src.size() ? src[at++] : END; }
 
-    void flags_ok() const {
-        if (on(RXF_UNICODE_CASE)) throw RegexUnsupported("(?u) UNICODE_CASE");
-        if (on(RXF_UNICODE_CLASS)) throw RegexUnsupported("(?U) UNICODE_CHARACTER_CLASS");
-    }
+    // (?U) UNICODE_CHARACTER_CLASS implies UNICODE_CASE (Pattern.java: "flags |= UNICODE_CASE" wherever it is switched on)
+    void flags_ok() { if (on(RXF_UNICODE_CLASS)) fl |= RXF_UNICODE_CASE; }
+    bool ucase() const { return on(RXF_ICASE) && on(RXF_UNICODE_CASE); }
+    void fold(CpSet& s) const { if (ucase()) close_case_unicode(s); else if (on(RXF_ICASE)) close_case(s); }
 
     // \Q..\E -> backslash-escaped literals, as Pattern.RemoveQEQuoting does before parsing
     void unquote() {
@@ -150,7 +185,8 @@ public:
     AstP set_node(CpSet s) { cpset_normalize(s); AstP a = node(AstKind::Set); a->set = std::move(s); return a; }
     AstP literal(uint32_t c) {
         CpSet s{{c, c}};
-        if (on(RXF_ICASE) && is_alpha(c)) s.push_back({flip_case(c), flip_case(c)});
+        if (ucase()) close_case_unicode(s);
+        else if (on(RXF_ICASE) && is_alpha(c)) s.push_back({flip_case(c), flip_case(c)});
         return set_node(std::move(s));
     }
     AstP assertion(AssertKind k) { AstP a = node(AstKind::Assert); a->assert_kind = k; return a; }
@@ -298,13 +334,14 @@ public:
     static CpSet vspace() { return {{10, 13}, {0x85, 0x85}, {0x2028, 0x2029}}; }
 
     bool shorthand(uint32_t c, CpSet& out) {
+        const bool U = on(RXF_UNICODE_CLASS);      // (?U): \d = Nd, \w = Alphabetic|M|Nd|Pc|Join_Control, \s = White_Space
         switch (c) {
-            case 'd': out = digits(); return true;
-            case 'D': out = cpset_negate(digits()); return true;
-            case 'w': out = word(); return true;
-            case 'W': out = cpset_negate(word()); return true;
-            case 's': out = space(); return true;
-            case 'S': out = cpset_negate(space()); return true;
+            case 'd': out = U ? uni_get(UNI_PROP, "DIGIT") : digits(); return true;
+            case 'D': out = cpset_negate(U ? uni_get(UNI_PROP, "DIGIT") : digits()); return true;
+            case 'w': out = U ? uni_get(UNI_PROP, "WORD") : word(); return true;
+            case 'W': out = cpset_negate(U ? uni_get(UNI_PROP, "WORD") : word()); return true;
+            case 's': out = U ? uni_get(UNI_PROP, "WHITESPACE") : space(); return true;
+            case 'S': out = cpset_negate(U ? uni_get(UNI_PROP, "WHITESPACE") : space()); return true;
             case 'h': out = hspace(); return true;
             case 'H': out = cpset_negate(hspace()); return true;
             case 'v': out = vspace(); return true;
@@ -322,12 +359,75 @@ public:
             if (raw() == END) bad("Illegal character family");
             name.push_back((char)src[at++]);
         }
+        CpSet s = family(name);
+        cpset_normalize(s);
+        return negate ? cpset_negate(s) : s;
+    }
+    // Pattern.family(): \\p{InBlock}, \\p{IsScript|IsCategory|IsBinaryProperty}, \\p{sc=..|blk=..|gc=..}, general categories,
+    // POSIX names (ASCII, or their Unicode versions under (?U)), java.lang.Character predicates
+    CpSet family(const std::string& name) {
+        const bool ci = on(RXF_ICASE);
+        CpSet s;
+        const size_t eq = name.find('=');
+        if (eq != std::string::npos) {
+            const std::string key = uni_norm(name.substr(0, eq)), value = name.substr(eq + 1);
+            if (key == "SC" || key == "SCRIPT") { if (!uni_find(UNI_SCRIPT, uni_norm(value), s)) bad("Unknown character script name {" + value + "}"); }
+            else if (key == "BLK" || key == "BLOCK") { if (!uni_find(UNI_BLOCK, uni_norm(value), s)) bad("Unknown character block name {" + value + "}"); }
+            else if (key == "GC" || key == "GENERALCATEGORY") { if (!property(value, ci, s)) bad("Unknown Unicode property {name=<" + name.substr(0, eq) + ">, value=<" + value + ">}"); }
+            else bad("Unknown Unicode property {name=<" + name.substr(0, eq) + ">, value=<" + value + ">}");
+            return s;
+        }
+        if (name.rfind("In", 0) == 0) {
+            if (!uni_find(UNI_BLOCK, uni_norm(name.substr(2)), s)) bad("Unknown character block name {" + name.substr(2) + "}");
+            return s;
+        }
+        if (name.rfind("Is", 0) == 0) {
+            const std::string sh = name.substr(2);
+            if (unicode_property(sh, ci, s) || property(sh, ci, s) || uni_find(UNI_SCRIPT, uni_norm(sh), s)) return s;
+            bad("Unknown character property name {" + name + "}");
+        }
+        if (on(RXF_UNICODE_CLASS) && posix_unicode(name, ci, s)) return s;
+        if (property(name, ci, s)) return s;
+        bad("Unknown character property name {" + name + "}");
+    }
+    // CharPredicates.forUnicodeProperty: binary properties, name matched without regard to case
+    bool unicode_property(const std::string& name, bool ci, CpSet& s) {
+        std::string n;
+        for (unsigned char ch : name) n.push_back((char)((ch >= 'a' && ch <= 'z') ? ch - 32 : ch));
+        static const char* const known[] = {"ALPHABETIC", "ASSIGNED", "CONTROL", "EMOJI", "EMOJI_PRESENTATION", "EMOJI_MODIFIER", "EMOJI_MODIFIER_BASE",
+                                            "EMOJI_COMPONENT", "EXTENDED_PICTOGRAPHIC", "HEXDIGIT", "HEX_DIGIT", "IDEOGRAPHIC", "JOINCONTROL", "JOIN_CONTROL",
+                                            "LETTER", "LOWERCASE", "NONCHARACTERCODEPOINT", "NONCHARACTER_CODE_POINT", "TITLECASE", "PUNCTUATION", "UPPERCASE",
+                                            "WHITESPACE", "WHITE_SPACE", "WORD", "DIGIT", "ALNUM", "BLANK", "GRAPH", "PRINT"};
+        bool ok = false;
+        for (const char* k : known) ok = ok || n == k;
+        if (!ok) return false;
+        if (ci && (n == "LOWERCASE" || n == "UPPERCASE" || n == "TITLECASE")) {       // Pattern: case-insensitive -> any cased letter
+            s = uni_get(UNI_PROP, "LOWERCASE");
+            CpSet u = uni_get(UNI_PROP, "UPPERCASE"), t = uni_get(UNI_PROP, "TITLECASE");
+            s.insert(s.end(), u.begin(), u.end());
+            s.insert(s.end(), t.begin(), t.end());
+            return true;
+        }
+        return uni_find(UNI_PROP, uni_norm(n), s);
+    }
+    // CharPredicates.forPOSIXName under UNICODE_CHARACTER_CLASS
+    bool posix_unicode(const std::string& name, bool ci, CpSet& s) {
+        static const char* const map[][2] = {{"ALPHA", "ALPHABETIC"}, {"LOWER", "LOWERCASE"}, {"UPPER", "UPPERCASE"}, {"SPACE", "WHITESPACE"},
+                                             {"PUNCT", "PUNCTUATION"}, {"XDIGIT", "HEXDIGIT"}, {"ALNUM", "ALNUM"}, {"CNTRL", "CONTROL"},
+                                             {"DIGIT", "DIGIT"}, {"BLANK", "BLANK"}, {"GRAPH", "GRAPH"}, {"PRINT", "PRINT"}};
+        std::string n;
+        for (unsigned char ch : name) n.push_back((char)((ch >= 'a' && ch <= 'z') ? ch - 32 : ch));
+        for (const auto& m : map) if (n == m[0]) return unicode_property(m[1], ci, s);
+        return false;
+    }
+    // CharPredicates.forProperty: general categories, POSIX names (ASCII), L1/all/LC/LD, javaXxx; names are case-sensitive
+    bool property(const std::string& name, bool ci, CpSet& s) {
         static const CpSet lower{{'a', 'z'}}, upper{{'A', 'Z'}}, alpha{{'A', 'Z'}, {'a', 'z'}};
         static const CpSet punct{{0x21, 0x2F}, {0x3A, 0x40}, {0x5B, 0x60}, {0x7B, 0x7E}};
-        CpSet s;
         auto add = [&](const CpSet& o) { s.insert(s.end(), o.begin(), o.end()); };
-        if (name == "Lower") add(on(RXF_ICASE) ? alpha : lower);
-        else if (name == "Upper") add(on(RXF_ICASE) ? alpha : upper);
+        s.clear();
+        if (name == "Lower") add(ci ? alpha : lower);
+        else if (name == "Upper") add(ci ? alpha : upper);
         else if (name == "ASCII") s = {{0, 0x7F}};
         else if (name == "Alpha") add(alpha);
         else if (name == "Digit") add(digits());
@@ -339,9 +439,21 @@ public:
         else if (name == "Cntrl") s = {{0, 0x1F}, {0x7F, 0x7F}};
         else if (name == "XDigit") s = {{'0', '9'}, {'A', 'F'}, {'a', 'f'}};
         else if (name == "Space") add(space());
-        else nope("\\p{" + name + "}");
-        cpset_normalize(s);
-        return negate ? cpset_negate(s) : s;
+        else if (name == "L1") s = {{0, 0xFF}};
+        else if (name == "all") s = {{0, 0x10FFFF}};
+        else if (name == "LD") { add(uni_get(UNI_GC, "L")); add(uni_get(UNI_GC, "ND")); }
+        else if (ci && (name == "Lu" || name == "Ll" || name == "Lt")) { add(uni_get(UNI_GC, "LU")); add(uni_get(UNI_GC, "LL")); add(uni_get(UNI_GC, "LT")); }
+        else if (ci && (name == "javaLowerCase" || name == "javaUpperCase" || name == "javaTitleCase")) {
+            add(uni_get(UNI_JAVA, "JAVALOWERCASE")); add(uni_get(UNI_JAVA, "JAVAUPPERCASE")); add(uni_get(UNI_JAVA, "JAVATITLECASE"));
+        } else if (name.rfind("java", 0) == 0) return uni_find(UNI_JAVA, uni_norm(name), s);
+        else {
+            // general categories: exactly "L", "Lu", "LC", ... (a lower-case or longer spelling is an error in Java)
+            const bool shape = (name.size() == 1 && name[0] >= 'A' && name[0] <= 'Z') ||
+                               (name.size() == 2 && name[0] >= 'A' && name[0] <= 'Z' && ((name[1] >= 'a' && name[1] <= 'z') || name == "LC"));
+            if (!shape) return false;
+            return uni_find(UNI_GC, uni_norm(name), s);
+        }
+        return true;
     }
     static int hex(uint32_t c) {
         if (is_digit(c)) return (int)c - '0';
@@ -419,12 +531,17 @@ public:
         switch (c) {
             case 'p': return set_node(posix(false));
             case 'P': return set_node(posix(true));
-            case 'b': if (raw() == '{') nope("\\b{g}"); return assertion(AssertKind::WordB);
-            case 'B': return assertion(AssertKind::NotWordB);
+            case 'b':
+                if (raw() == '{') nope("\\b{g}");
+                if (on(RXF_UNICODE_CLASS)) nope("(?U) with \\b (Unicode word boundaries)");
+                return assertion(AssertKind::WordB);
+            case 'B':
+                if (on(RXF_UNICODE_CLASS)) nope("(?U) with \\B (Unicode word boundaries)");
+                return assertion(AssertKind::NotWordB);
             case 'A': return assertion(AssertKind::Begin);
             case 'z': return assertion(AssertKind::End);
             case 'Z': return assertion(on(RXF_UNIX_LINES) ? AssertKind::End : AssertKind::Eol);
-            case 'G': nope("\\G");
+            case 'G': return assertion(AssertKind::Begin);     // end of the previous match: for the one find() per line, position 0
             case 'X': nope("\\X");
             case 'N': nope("\\N{name}");
             case 'R': {  // \r\n | [\n\x0B\f\r\x85  ]
@@ -445,6 +562,7 @@ public:
                 auto it = named.find(name);
                 if (it == named.end()) bad("named capturing group <" + name + "> does not exist");
                 regular = false;
+                if (ucase()) nope("back-reference under (?iu)");
                 AstP b = node(AstKind::Backref); b->group = it->second; b->icase = on(RXF_ICASE); return b;
             }
             default: break;
@@ -458,6 +576,7 @@ public:
                 ref = wider; ++at;
             }
             regular = false;
+            if (ucase()) nope("back-reference under (?iu)");
             AstP b = node(AstKind::Backref); b->group = ref; b->icase = on(RXF_ICASE); return b;
         }
         if (is_alpha(c)) bad("Illegal/unsupported escape sequence");
@@ -493,12 +612,12 @@ public:
             if (look() == '-' && raw(1) != ']' && raw(1) != END && raw(1) != '[') {
                 take();
                 uint32_t b; CpSet cs2;
-                if (!member(b, cs2)) { plain.push_back({a, a}); plain.push_back({'-', '-'}); sets.insert(sets.end(), cs2.begin(), cs2.end()); continue; }
+                if (!member(b, cs2)) bad("Illegal character range");      // Pattern.range(): a class escape as the end point gives -1 < ch
                 if (b < a) bad("Illegal character range");
                 plain.push_back({a, b});
             } else plain.push_back({a, a});
         }
-        if (on(RXF_ICASE)) close_case(plain);
+        fold(plain);
         plain.insert(plain.end(), sets.begin(), sets.end());
         cpset_normalize(plain);
         return plain;

@@ -110,7 +110,7 @@ def assemble_result(line: np.ndarray, pattern: np.ndarray, score: np.ndarray, lo
     rank = lambda s: SEVERITY_ORDER.index(s) if s in SEVERITY_ORDER else -1   # List.indexOf -> -1 for unknown severities
     best = sev[0]
     for s in sev[1:]:
-        if rank(s) >= rank(best):   # Stream.max keeps the last of equal maxima
+        if rank(s) > rank(best):    # Stream.max reduces with BinaryOperator.maxBy: (a, b) -> cmp(a, b) >= 0 ? a : b, the FIRST of equal maxima stays
             best = s
     result["summary"] = {"significantEvents": len(events), "severityDistribution": dist, "highestSeverity": best}
     return result

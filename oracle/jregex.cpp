@@ -10,6 +10,7 @@
 #include <algorithm>
 #include <climits>
 #include <map>
+#include <stdexcept>
 
 namespace orx {
 
@@ -115,6 +116,40 @@ static void decode_pattern(const std::string& p, std::vector<int>& out) {
 // ------------------------------------------------------------------ Parser
 namespace {
 
+#include "unicode_tables.inc"
+
+// java.lang.Character.UnicodeScript.forName / UnicodeBlock.forName ignore case; blocks also accept the name with its
+// spaces removed: compare upper-cased, without ' ', '_' and '-'
+static std::string squash(const std::string& n) {
+    std::string o;
+    for (unsigned char ch : n) if (ch != ' ' && ch != '_' && ch != '-') o.push_back((char)toupper(ch));
+    return o;
+}
+static bool table_lookup(const UniProp* t, const std::string& squashed, CharSet& out) {
+    for (; t->name; ++t)
+        if (squashed == t->name) {
+            out = CharSet();
+            for (unsigned i = 0; i < t->n; ++i) out.add((int)t->r[i].lo, (int)t->r[i].hi);
+            return true;
+        }
+    return false;
+}
+static CharSet table_get(const UniProp* t, const char* name) {
+    CharSet s;
+    if (!table_lookup(t, name, s)) throw std::logic_error(std::string("oracle: missing table ") + name);
+    return s;
+}
+// UNICODE_CASE: ch matches c when toLowerCase(toUpperCase(ch)) == toLowerCase(toUpperCase(c)) (Pattern.SingleU); the table
+// lists, per code point, the others of its class
+static void close_unicode_case(CharSet& s) {
+    s.normalize();
+    CharSet extra;
+    for (unsigned i = 0; i < UNI_CASE_PAIRS_N; ++i)
+        if (s.has((int)UNI_CASE_PAIRS[i][0]) && !s.has((int)UNI_CASE_PAIRS[i][1])) extra.add((int)UNI_CASE_PAIRS[i][1], (int)UNI_CASE_PAIRS[i][1]);
+    s.add(extra);
+    s.normalize();
+}
+
 struct Parser {
     std::vector<int> p;
     int pos = 0;
@@ -142,10 +177,9 @@ struct Parser {
     int raw_peek(int off = 0) const { return pos + off < len() ? p[pos + off] : -1; }
     int next() { skip_comments(); return pos < len() ? p[pos++] : -1; }
 
-    void check_flags() {
-        if (has(F_UNICODE_CASE)) unsup("UNICODE_CASE (?u) is not modelled");
-        if (has(F_UNICODE_CLASS)) unsup("UNICODE_CHARACTER_CLASS (?U) is not modelled");
-    }
+    // Pattern.java switches UNICODE_CASE on together with UNICODE_CHARACTER_CLASS
+    void check_flags() { if (has(F_UNICODE_CLASS)) flags |= F_UNICODE_CASE; }
+    bool unicode_ci() const { return has(F_CASE_INSENSITIVE) && has(F_UNICODE_CASE); }
 
     // RemoveQEQuoting: \Q...\E becomes escaped literals (Pattern.RemoveQEQuoting).
     void remove_qe() {
@@ -206,6 +240,11 @@ struct Parser {
     }
 
     NodeP lit(int c) {
+        if (unicode_ci()) {       // SingleU: any code point of the same case-folding class
+            CharSet s; s.add(c, c);
+            close_unicode_case(s);
+            if (s.r.size() != 1 || s.r[0].lo != s.r[0].hi) return setnode(std::move(s));
+        }
         NodeP n = mk(N_CHAR);
         n->c = c;
         n->icase = has(F_CASE_INSENSITIVE) && c < 128 && ascii_lower(c) != ascii_upper(c);
@@ -354,13 +393,14 @@ struct Parser {
 
     bool predefined(int ch, CharSet& out) {
         bool neg = false;
+        const bool U = has(F_UNICODE_CLASS);      // CharPredicates.DIGIT() / WORD() / WHITE_SPACE() instead of the ASCII ones
         switch (ch) {
-            case 'd': out = cls_digit(); break;
-            case 'D': out = cls_digit(); neg = true; break;
-            case 'w': out = cls_word(); break;
-            case 'W': out = cls_word(); neg = true; break;
-            case 's': out = cls_space(); break;
-            case 'S': out = cls_space(); neg = true; break;
+            case 'd': out = U ? table_get(UNI_PROP, "DIGIT") : cls_digit(); break;
+            case 'D': out = U ? table_get(UNI_PROP, "DIGIT") : cls_digit(); neg = true; break;
+            case 'w': out = U ? table_get(UNI_PROP, "WORD") : cls_word(); break;
+            case 'W': out = U ? table_get(UNI_PROP, "WORD") : cls_word(); neg = true; break;
+            case 's': out = U ? table_get(UNI_PROP, "WHITESPACE") : cls_space(); break;
+            case 'S': out = U ? table_get(UNI_PROP, "WHITESPACE") : cls_space(); neg = true; break;
             case 'h': out = cls_hspace(); break;
             case 'H': out = cls_hspace(); neg = true; break;
             case 'v': out = cls_vspace(); break;
@@ -384,10 +424,61 @@ struct Parser {
             name.push_back((char)p[pos++]);
         }
         CharSet s;
+        const bool ci = has(F_CASE_INSENSITIVE);
+        const size_t eq = name.find('=');
+        if (eq != std::string::npos) {                       // \\p{name=value}
+            const std::string key = squash(name.substr(0, eq)), val = name.substr(eq + 1);
+            bool ok = false;
+            if (key == "SC" || key == "SCRIPT") { ok = table_lookup(UNI_SCRIPT, squash(val), s); if (!ok) err("Unknown character script name {" + val + "}"); }
+            else if (key == "BLK" || key == "BLOCK") { ok = table_lookup(UNI_BLOCK, squash(val), s); if (!ok) err("Unknown character block name {" + val + "}"); }
+            else if (key == "GC" || key == "GENERALCATEGORY") ok = for_property(val, ci, s);
+            if (!ok) err("Unknown Unicode property {name=<" + name.substr(0, eq) + ">, value=<" + val + ">}");
+        } else if (name.compare(0, 2, "In") == 0) {          // \\p{InBlockName}
+            if (!table_lookup(UNI_BLOCK, squash(name.substr(2)), s)) err("Unknown character block name {" + name.substr(2) + "}");
+        } else if (name.compare(0, 2, "Is") == 0) {          // \\p{IsGeneralCategory}, \\p{IsBinaryProperty}, \\p{IsScriptName}
+            const std::string sh = name.substr(2);
+            if (!for_unicode_property(sh, ci, s) && !for_property(sh, ci, s) && !table_lookup(UNI_SCRIPT, squash(sh), s))
+                err("Unknown character property name {" + name + "}");
+        } else {
+            bool ok = has(F_UNICODE_CLASS) && for_posix_unicode(name, ci, s);
+            if (!ok) ok = for_property(name, ci, s);
+            if (!ok) err("Unknown character property name {" + name + "}");
+        }
+        if (neg) s.negate(); else s.normalize();
+        return s;
+    }
+    static std::string upper_ascii(const std::string& n) { std::string o; for (unsigned char ch : n) o.push_back((char)toupper(ch)); return o; }
+    // CharPredicates.forUnicodeProperty (the name is upper-cased first)
+    bool for_unicode_property(const std::string& name, bool ci, CharSet& s) {
+        const std::string n = upper_ascii(name);
+        static const char* const names[] = {"ALPHABETIC", "LETTER", "IDEOGRAPHIC", "LOWERCASE", "UPPERCASE", "TITLECASE", "WHITE_SPACE", "WHITESPACE",
+                                            "CONTROL", "PUNCTUATION", "HEX_DIGIT", "HEXDIGIT", "ASSIGNED", "NONCHARACTER_CODE_POINT", "NONCHARACTERCODEPOINT",
+                                            "DIGIT", "ALNUM", "BLANK", "GRAPH", "PRINT", "WORD", "JOIN_CONTROL", "JOINCONTROL", "EMOJI", "EMOJI_PRESENTATION",
+                                            "EMOJI_MODIFIER", "EMOJI_MODIFIER_BASE", "EMOJI_COMPONENT", "EXTENDED_PICTOGRAPHIC"};
+        bool known = false;
+        for (const char* k : names) if (n == k) known = true;
+        if (!known) return false;
+        if (ci && (n == "LOWERCASE" || n == "UPPERCASE" || n == "TITLECASE")) {
+            s = table_get(UNI_PROP, "LOWERCASE"); s.add(table_get(UNI_PROP, "UPPERCASE")); s.add(table_get(UNI_PROP, "TITLECASE"));
+            return true;
+        }
+        return table_lookup(UNI_PROP, squash(n), s);
+    }
+    // CharPredicates.forPOSIXName: the POSIX names under UNICODE_CHARACTER_CLASS
+    bool for_posix_unicode(const std::string& name, bool ci, CharSet& s) {
+        const std::string n = upper_ascii(name);
+        const char* to = n == "ALPHA" ? "ALPHABETIC" : n == "LOWER" ? "LOWERCASE" : n == "UPPER" ? "UPPERCASE" : n == "SPACE" ? "WHITE_SPACE"
+                       : n == "PUNCT" ? "PUNCTUATION" : n == "XDIGIT" ? "HEX_DIGIT" : n == "ALNUM" ? "ALNUM" : n == "CNTRL" ? "CONTROL"
+                       : n == "DIGIT" ? "DIGIT" : n == "BLANK" ? "BLANK" : n == "GRAPH" ? "GRAPH" : n == "PRINT" ? "PRINT" : nullptr;
+        return to && for_unicode_property(to, ci, s);
+    }
+    // CharPredicates.forProperty: the `props` map (general categories, POSIX ASCII classes, L1, all, LC, LD, javaXxx); exact names
+    bool for_property(const std::string& name, bool ci, CharSet& s) {
+        s = CharSet();
         auto alpha = [&]() { s.add('a', 'z'); s.add('A', 'Z'); };
         auto punct = [&]() { s.add(0x21, 0x2F); s.add(0x3A, 0x40); s.add(0x5B, 0x60); s.add(0x7B, 0x7E); };
-        if (name == "Lower") s.add('a', 'z');
-        else if (name == "Upper") s.add('A', 'Z');
+        if (name == "Lower") { if (ci) alpha(); else s.add('a', 'z'); }
+        else if (name == "Upper") { if (ci) alpha(); else s.add('A', 'Z'); }
         else if (name == "ASCII") s.add(0, 0x7F);
         else if (name == "Alpha") alpha();
         else if (name == "Digit") s.add('0', '9');
@@ -399,10 +490,19 @@ struct Parser {
         else if (name == "Cntrl") { s.add(0, 0x1F); s.add(0x7F, 0x7F); }
         else if (name == "XDigit") { s.add('0', '9'); s.add('a', 'f'); s.add('A', 'F'); }
         else if (name == "Space") { s.add(' ', ' '); s.add(9, 13); }
-        else unsup("Unicode property \\p{" + name + "} is not modelled");
-        if (has(F_CASE_INSENSITIVE) && (name == "Lower" || name == "Upper")) { s = CharSet(); alpha(); }
-        if (neg) s.negate(); else s.normalize();
-        return s;
+        else if (name == "L1") s.add(0, 0xFF);
+        else if (name == "all") s.add(0, 0x10FFFF);
+        else if (name == "LD") { s = table_get(UNI_GC, "L"); s.add(table_get(UNI_GC, "ND")); }
+        else if (ci && (name == "Lu" || name == "Ll" || name == "Lt")) { s = table_get(UNI_GC, "LU"); s.add(table_get(UNI_GC, "LL")); s.add(table_get(UNI_GC, "LT")); }
+        else if (ci && (name == "javaLowerCase" || name == "javaUpperCase" || name == "javaTitleCase")) {
+            s = table_get(UNI_JAVA, "JAVALOWERCASE"); s.add(table_get(UNI_JAVA, "JAVAUPPERCASE")); s.add(table_get(UNI_JAVA, "JAVATITLECASE"));
+        } else if (name.compare(0, 4, "java") == 0) return table_lookup(UNI_JAVA, squash(name), s);
+        else {
+            const bool cat = (name.size() == 1 && isupper((unsigned char)name[0])) ||
+                             (name.size() == 2 && isupper((unsigned char)name[0]) && (islower((unsigned char)name[1]) || name == "LC"));
+            return cat && table_lookup(UNI_GC, squash(name), s);
+        }
+        return true;
     }
 
     int hexval(int c) {
@@ -493,13 +593,16 @@ struct Parser {
             case 'P': return setnode(property(true));
             case 'b': {
                 if (raw_peek() == '{') unsup("\\b{g}");
+                if (has(F_UNICODE_CLASS)) unsup("\\b under (?U) (Unicode word boundaries are not modelled)");
                 return mk(N_WORDB);
             }
-            case 'B': return mk(N_NWORDB);
+            case 'B':
+                if (has(F_UNICODE_CLASS)) unsup("\\B under (?U) (Unicode word boundaries are not modelled)");
+                return mk(N_NWORDB);
             case 'A': return mk(N_BEGIN);
             case 'z': return mk(N_END);
             case 'Z': { NodeP n = mk(N_EOL); n->flags = flags & F_UNIX_LINES; return n; }
-            case 'G': unsup("\\G");
+            case 'G': return mk(N_BEGIN);        // LastMatch: oldLast is the search start for the first find() of a Matcher
             case 'X': unsup("\\X");
             case 'N': unsup("\\N{name}");
             case 'R': return linebreak();
@@ -511,6 +614,7 @@ struct Parser {
                 ++pos;
                 auto it = names.find(name);
                 if (it == names.end()) err("named capturing group <" + name + "> does not exist");
+                if (unicode_ci()) unsup("back-reference under (?iu)");
                 NodeP n = mk(N_BACKREF); n->group = it->second; n->icase = has(F_CASE_INSENSITIVE); return n;
             }
             default: break;
@@ -525,6 +629,7 @@ struct Parser {
                 if (ngroups - 1 < nr) break;
                 ref = nr; ++pos;
             }
+            if (unicode_ci()) unsup("back-reference under (?iu)");
             NodeP n = mk(N_BACKREF); n->group = ref; n->icase = has(F_CASE_INSENSITIVE); return n;
         }
         if ((ch >= 'a' && ch <= 'z') || (ch >= 'A' && ch <= 'Z')) err("Illegal/unsupported escape sequence");
@@ -563,12 +668,12 @@ struct Parser {
             if (peek() == '-' && raw_peek(1) != ']' && raw_peek(1) != -1 && raw_peek(1) != '[') {
                 next();
                 int cp2 = 0; CharSet cs2;
-                if (!class_item(cp2, cs2)) { lits.add(cp, cp); lits.add('-', '-'); preds.add(cs2); continue; }
+                if (!class_item(cp2, cs2)) err("Illegal character range");     // Pattern.range(): escape(..) returns -1 for a class, and -1 < ch
                 if (cp2 < cp) err("Illegal character range");
                 lits.add(cp, cp2);
             } else lits.add(cp, cp);
         }
-        if (has(F_CASE_INSENSITIVE)) lits.close_ascii_case();
+        if (unicode_ci()) close_unicode_case(lits); else if (has(F_CASE_INSENSITIVE)) lits.close_ascii_case();
         lits.add(preds);
         lits.normalize();
         return lits;

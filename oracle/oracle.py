@@ -59,7 +59,7 @@ def build(force: bool = False) -> str:
     """Compile the oracle with the committed Makefile (g++)."""
     if force or not os.path.exists(_SO) or any(
         os.path.getmtime(os.path.join(_HERE, f)) > os.path.getmtime(_SO)
-        for f in ("jregex.cpp", "jregex.hpp", "analyze.cpp", "oracle_api.h", "Makefile")
+        for f in ("jregex.cpp", "jregex.hpp", "analyze.cpp", "oracle_api.h", "Makefile", "unicode_tables.inc")
     ):
         subprocess.run(["make", "-C", _HERE], check=True, capture_output=True)
     return _SO

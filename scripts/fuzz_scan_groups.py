@@ -17,7 +17,7 @@ ALPHA = "abcERx_1 .-:\r\u00e9\u20ac\u0085\u2028"
 def main():
     seed = int(sys.argv[1]) if len(sys.argv) > 1 else 1
     rounds = int(sys.argv[2]) if len(sys.argv) > 2 else 600
-    L = binding.load_library()
+    L = binding.load_debug_library()
     L.lp_debug_group_match.restype = C.c_uint32
     L.lp_debug_group_match.argtypes = [C.POINTER(C.c_char_p), C.POINTER(C.c_int), C.c_size_t, C.c_char_p, C.c_size_t]
     rng = random.Random(seed)

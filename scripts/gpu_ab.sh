@@ -1,6 +1,6 @@
 #!/bin/bash
 # A/B of the scan variants on one B200: parity tests first, then the bench line of each variant.
-mkdir -p gpurun_out
+mkdir -p gpurun_out; export LP_NO_REBUILD=1
 timeout 300 python __graft_entry__.py smoke > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" | tee -a gpurun_out/smoke.log
 tail -3 gpurun_out/smoke.log
 timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?"

@@ -1,7 +1,7 @@
 #!/bin/bash
 # bench line + ncu capture of the scan kernel (one GPU). Usage: gpu_prof.sh <tag> [kernel regex]
 TAG=${1:-x}; KRE=${2:-k_fscan}
-mkdir -p gpurun_out
+mkdir -p gpurun_out; export LP_NO_REBUILD=1
 timeout 600 python -m pytest tests/test_gpu_parity.py -m gpu -x -q -k "split or c1 or batch or range or piecewise" > gpurun_out/pytest_$TAG.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/pytest_$TAG.log
 timeout 300 python bench.py --steps 20 --warmup 5 > gpurun_out/bench_$TAG.json 2> gpurun_out/bench_$TAG.err; echo "bench rc=$?"
 python - <<PY

@@ -9,7 +9,7 @@ from log_parser_b200 import binding, synth  # noqa: E402
 
 
 def plan_dump(patterns, sample: bytes) -> str:
-    L = binding.load_library()
+    L = binding.load_debug_library()
     tab = binding.PatternTable(patterns)
     L.lp_debug_plan_dump.restype = C.c_size_t
     L.lp_debug_plan_dump.argtypes = [C.c_void_p, C.c_size_t, C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t]

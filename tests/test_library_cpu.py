@@ -31,6 +31,11 @@ def test_header_symbols_exported(lib):
         assert hasattr(lib, name), f"{name} is declared in the header but not exported"
 
 
+def test_debug_hooks_are_not_in_the_product_library(lib):
+    assert not hasattr(lib, "lp_debug_rx_compile") and not hasattr(lib, "lp_debug_plan_dump")
+    assert hasattr(binding.load_debug_library(), "lp_debug_rx_compile")
+
+
 def test_version_and_error_string(lib):
     assert b"sm_100a" in lib.lp_version()
     assert isinstance(lib.lp_last_error(), bytes)
@@ -287,7 +292,9 @@ def test_syntax_errors_surface_like_java(lib):
     for bad in ["a{,2}", "(a", "[a", "*a", "a{3,2}", "\\k<x>", "(?<=a*)b"]:
         with pytest.raises(binding.PatternSyntaxError):
             binding.DebugRegex(bad)
-    for unsup in ["\\X", "\\G", "\\p{L}", "(?u)a"]:
+    for ok in ["\\G", "\\p{L}", "(?u)a", "(?U)\\w", "\\p{IsGreek}"]:        # legal Java the reference serves: accepted since round 2
+        binding.DebugRegex(ok)
+    for unsup in ["\\X", "\\b{g}", "(?U)\\bx"]:
         with pytest.raises(binding.UnsupportedRegexError):
             binding.DebugRegex(unsup)
 
@@ -318,8 +325,7 @@ def test_scan_group_product_dfa_vs_oracle(lib, oracle):
     tables, including the idle-state fast path, are checked here on the host against the oracle."""
     import ctypes as C
 
-    lib.lp_debug_group_match.restype = C.c_uint32
-    lib.lp_debug_group_match.argtypes = [C.POINTER(C.c_char_p), C.POINTER(C.c_int), C.c_size_t, C.c_char_p, C.c_size_t]
+    lib = binding.load_debug_library()
     groups = [
         ([r"\b(ERROR|FATAL|CRITICAL|SEVERE)\b", r"\b(WARN|WARNING)\b", r"\b\w*Exception\b|\b\w*Error\b", r"\b\d{8,}ms\b"], [2, 2, 0, 0]),
         ([r"\b[45]\d\d \d+ \d+\.\d{3}$", r"^\s*at\s+[\w\.\$]+\(.*\)\s*$"], [0, 0]),

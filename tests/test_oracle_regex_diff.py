@@ -112,17 +112,85 @@ def test_java_specific_cases(oracle, pat, text, exp):
 
 @pytest.mark.parametrize("bad", [
     "a{,2}", "a{", "{", "*a", "+", "?", "(a", "a)", "[a", "a**", "\\", "[z-a]", "a{3,2}", "(?<n>a)(?<n>b)",
-    "\\k<nope>", "(?<=a*)b", "\\y", "\\1", "(?<1a>x)", "a{2", "(?z)a",
+    "\\k<nope>", "(?<=a*)b", "\\y", "\\1", "(?<1a>x)", "a{2", "(?z)a", "[a-\\d]", "[a-\\w]", "[--\\s]",
 ])
 def test_syntax_errors(oracle, bad):
     with pytest.raises(oracle.OracleSyntaxError):
         oracle.Regex(bad)
 
 
-@pytest.mark.parametrize("pat", ["\\X", "\\G", "\\p{L}", "(?u)a", "(?U)\\w", "\\b{g}", "\\N{DIGIT ONE}"])
+@pytest.mark.parametrize("pat", ["\\X", "\\b{g}", "\\N{DIGIT ONE}", "(?U)\\bx", "(?U)x\\B", "(?iu)(a)\\1"])
 def test_declared_unsupported(oracle, pat):
     with pytest.raises(oracle.OracleUnsupported):
         oracle.Regex(pat)
+
+
+def _assigned_sample():
+    import unicodedata
+
+    cps = [c for c in range(0, 0x30000, 7) if not 0xD800 <= c <= 0xDFFF]
+    cps += list(range(0x00, 0x250)) + list(range(0x370, 0x530)) + list(range(0x2000, 0x2100)) + list(range(0x3040, 0x3100))
+    return [c for c in sorted(set(cps)) if unicodedata.category(chr(c)) != "Cn"]      # Python 3.12 carries Unicode 15.0, as Java 21 does
+
+
+@pytest.mark.parametrize("java,third", [
+    ("\\p{L}", "\\p{L}"), ("\\p{Lu}", "\\p{Lu}"), ("\\p{Ll}", "\\p{Ll}"), ("\\p{Lt}", "\\p{Lt}"), ("\\p{M}", "\\p{M}"), ("\\p{N}", "\\p{N}"),
+    ("\\p{Nd}", "\\p{Nd}"), ("\\p{P}", "\\p{P}"), ("\\p{Sc}", "\\p{Sc}"), ("\\p{Zs}", "\\p{Zs}"), ("\\p{Cc}", "\\p{Cc}"), ("\\P{L}", "\\P{L}"),
+    ("\\p{IsL}", "\\p{L}"), ("\\p{gc=Lu}", "\\p{Lu}"), ("\\pL", "\\p{L}"), ("\\p{LC}", "[\\p{Lu}\\p{Ll}\\p{Lt}]"),
+    ("\\p{IsAlphabetic}", "\\p{Alphabetic}"), ("\\p{IsUppercase}", "\\p{Uppercase}"), ("\\p{IsLowercase}", "\\p{Lowercase}"),
+    ("\\p{IsWhite_Space}", "\\p{White_Space}"), ("\\p{IsIdeographic}", "\\p{Ideographic}"), ("\\p{IsHex_Digit}", "\\p{Hex_Digit}"),
+    ("\\p{IsLatin}", "\\p{Script=Latin}"), ("\\p{IsGreek}", "\\p{Script=Greek}"), ("\\p{script=Cyrillic}", "\\p{Script=Cyrillic}"),
+    ("\\p{sc=Han}", "\\p{Script=Han}"), ("\\p{IsHiragana}", "\\p{Script=Hiragana}"), ("\\p{IsCommon}", "\\p{Script=Common}"),
+    ("\\p{InGreek}", "\\p{Block=Greek_And_Coptic}"), ("\\p{InBasicLatin}", "\\p{Block=Basic_Latin}"), ("\\p{block=Cyrillic}", "\\p{Block=Cyrillic}"),
+    ("\\p{InCJKUnifiedIdeographs}", "\\p{Block=CJK_Unified_Ideographs}"), ("\\p{blk=GeneralPunctuation}", "\\p{Block=General_Punctuation}"),
+    ("\\p{javaLowerCase}", "\\p{Lowercase}"), ("\\p{javaUpperCase}", "\\p{Uppercase}"), ("\\p{javaLetter}", "\\p{L}"), ("\\p{javaDigit}", "\\p{Nd}"),
+    ("(?U)\\d", "\\p{Nd}"), ("(?U)\\s", "\\p{White_Space}"), ("(?U)\\w", "[\\p{Alphabetic}\\p{M}\\p{Nd}\\p{Pc}\\u200c\\u200d]"),
+    ("(?U)\\p{Alpha}", "\\p{Alphabetic}"), ("(?U)\\p{Punct}", "\\p{P}"), ("\\p{Alpha}", "[A-Za-z]"), ("\\p{L1}", "[\\x00-\\xff]"),
+])
+def test_unicode_properties_vs_regex_module(oracle, java, third):
+    """\\p{..} families of Pattern.family() against the third-party `regex` module on the code points assigned in Unicode 15.0
+    (the tables come from perl's Unicode::UCD 15.0.0; `regex` carries its own copy of the UCD)."""
+    from log_parser_b200 import binding
+
+    o = oracle.Regex(java)
+    d = binding.DebugRegex(java)
+    c = rx.compile(third)
+    bad = []
+    for cp in _assigned_sample():
+        ch = chr(cp)
+        exp = c.match(ch) is not None
+        if o.find(ch) != exp or bool(d.match(ch)) != exp:
+            bad.append((hex(cp), exp, o.find(ch), bool(d.match(ch))))
+    # `regex` carries a newer UCD than Java 21's 15.0: a couple of reclassified code points are tolerated, and the combining
+    # marks that Unicode 16 added to Other_Alphabetic (U+0363.., U+1DD3..; perl 15.0 agrees with the tables here)
+    import unicodedata
+
+    marks_only = all(unicodedata.category(chr(int(b[0], 16))) == "Mn" for b in bad)
+    assert len(bad) <= 2 or (marks_only and len(bad) <= 60), (java, bad[:10])
+
+
+@pytest.mark.parametrize("pat,text,exp", [
+    ("(?iu)\u00c9COLE", "\u00e9cole", True), ("(?i)\u00c9COLE", "\u00e9cole", False), ("(?iu)[\u00e0-\u00fd]x", "\u00c0x", True), ("(?iu)stra\u00dfe", "STRASSE", False),
+    ("(?iu)\u03c3", "\u03c2", True), ("(?iu)\u03a3", "\u03c2", True), ("(?iu)k", "\u212a", True), ("(?i)k", "\u212a", False), ("(?iu)\u0131", "I", True),
+    ("(?U)\\w+$", "\u0434\u0430\u043d\u043d\u044b\u0435", True), ("\\w+$", "\u0434\u0430\u043d\u043d\u044b\u0435", False), ("(?U)(?i)\u00e9", "\u00c9", True),
+    ("\\Gab", "ab", True), ("\\Gb", "ab", False), ("a\\Gb", "ab", False), ("(?i)\\p{Lu}", "a", True), ("\\p{Lu}", "a", False), ("(?i)\\p{IsLowercase}", "A", True),
+    ("[\\p{L}&&[^\\p{IsLatin}]]", "a\u03b1", True), ("[\\p{L}&&[^\\p{IsLatin}]]", "abc", False), ("\\p{IsEmoji}", "\U0001F600", True),
+])
+def test_unicode_flags_cases(oracle, pat, text, exp):
+    from log_parser_b200 import binding
+
+    assert oracle.Regex(pat).find(text) == exp
+    assert bool(binding.DebugRegex(pat).match(text)) == exp
+
+
+@pytest.mark.parametrize("bad", ["\\p{lu}", "\\p{IsFoo}", "\\p{InNowhere}", "\\p{sc=Nope}", "\\p{foo=bar}", "\\p{Latin}", "\\p{javaFoo}", "\\p{"])
+def test_unknown_property_names_are_syntax_errors(oracle, bad):
+    from log_parser_b200 import binding
+
+    with pytest.raises(oracle.OracleSyntaxError):
+        oracle.Regex(bad)
+    with pytest.raises(binding.PatternSyntaxError):
+        binding.DebugRegex(bad)
 
 
 def test_vs_regex_module_sets(oracle):

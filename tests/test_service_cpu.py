@@ -65,6 +65,18 @@ def test_result_assembly_matches_reference_shape(tmp_path, oracle):
     assert empty["summary"] == {"significantEvents": 0, "highestSeverity": "NONE", "severityDistribution": {}}
 
 
+def test_highest_severity_keeps_first_of_equal_maxima():
+    """AS:204-209: Stream.max(comparingInt(order::indexOf)); unknown severities all compare as -1 and the first one wins."""
+    raw = [{"id": "a", "severity": "strange"}, {"id": "b", "severity": "odd"}, {"id": "c", "severity": "info"}]
+    sets = []
+    res = service.assemble_result(np.array([1, 2], np.uint32), np.array([0, 1], np.uint32), np.array([1.0, 1.0]), "x\ny\n", raw, sets, 0.0, 2)
+    assert res["summary"]["highestSeverity"] == "STRANGE"
+    res = service.assemble_result(np.array([1, 2, 2], np.uint32), np.array([1, 0, 2], np.uint32), np.array([1.0, 1.0, 1.0]), "x\ny\n", raw, sets, 0.0, 2)
+    assert res["summary"]["highestSeverity"] == "INFO"          # INFO (index 0) beats the unknowns (-1)
+    res = service.assemble_result(np.array([1, 2], np.uint32), np.array([1, 0], np.uint32), np.array([1.0, 1.0]), "x\ny\n", raw, sets, 0.0, 2)
+    assert res["summary"]["highestSeverity"] == "ODD"
+
+
 def test_frequency_tracker_window():
     now = [1000.0]
     ft = service.FrequencyTracker(ScoringConfig(time_window_hours=1), clock=lambda: now[0])

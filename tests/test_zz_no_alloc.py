@@ -3,8 +3,9 @@ with a fixed device-memory plan, a plugin inside someone else's allocator): its 
 array inside the loaded module instead of a cudaMalloc'ed pool.
 
 Checked here through the C ABI against the existing entry point that computes the same thing,
-lp_analyze with LP_OPT_LINE_OFFSETS: line starts, line ends and the Java-trimmed line count must be
-identical (integers: bit-exact, like the other parity tests). Two calls in a row on the same device,
+lp_analyze with LP_OPT_LINE_OFFSETS, and directly against the oracle's String.split restatement: line
+starts, line ends and the Java-trimmed line count must be identical (integers: bit-exact, like the
+other parity tests). Two calls in a row on the same device,
 the second on a different, shorter log, prove that what the first call left in the shared scratch
 does not leak into the next one. All device buffers are allocated by the test, outside the call.
 This file sorts last on purpose: a run with -x has already executed every other test.
@@ -44,7 +45,10 @@ def test_noalloc_split_matches_analyze_twice_in_a_row():
     small = b"first\r\nsecond\n\nlast line without newline"
     lp = binding.LogParser(ScoringConfig())
     lp.load_patterns([PatternSpec(id="p", primary_regex="never-matches-anything-here", confidence=1.0)])
-    for log in (big, small, b"", b"\n\n\n", b"a\n\r\n\n"):      # consecutive calls share the in-module scratch
+    from oracle import oracle as O
+
+    blank_tail = b"x\r\n" + b"\n" * 70000 + b"\r\n\n"      # the trailing-empty rule has to look back over 70k blank lines
+    for log in (big, small, b"", b"\n\n\n", b"a\n\r\n\n", blank_tail):      # consecutive calls share the in-module scratch
         exp_s, exp_e, exp_n, exp_total = _reference_offsets(lp, log)
         got_s, got_e, got_n, got_total, overflow = _noalloc_offsets(log, capacity=exp_total + 7)
         assert overflow == 0
@@ -52,6 +56,9 @@ def test_noalloc_split_matches_analyze_twice_in_a_row():
         assert got_n == exp_n
         np.testing.assert_array_equal(got_s, exp_s)
         np.testing.assert_array_equal(got_e, exp_e)
+        ora = O.split(log)                              # the kept lines of String.split("\\r?\\n")
+        assert got_n == len(ora)
+        assert [(int(a), int(b)) for a, b in zip(got_s[:got_n], got_e[:got_n])] == [(int(a), int(b)) for a, b in ora]
     lp.close()
 
 
