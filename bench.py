@@ -102,6 +102,11 @@ def build_workload(args, rank: int, batch: bool):
 
     from log_parser_b200 import synth
 
+    if not batch and args.config != "c2":      # the other single-log configs of BASELINE.json (parity cases; timed for profiles/)
+        maker = {"c1": lambda: synth.config_c1(), "c3": lambda: synth.config_c3(args.lines, args.patterns),
+                 "c4": lambda: synth.config_c4(args.lines, args.patterns)}[args.config]
+        wl, log = maker()
+        return wl, log, np.array([0, len(log)], dtype=np.uint64)
     wl = synth.make_patterns(args.patterns, synth.MASTER_SEED ^ 2, n_sets=5)
     if not batch:
         log = synth.make_log(wl, args.lines, synth.MASTER_SEED ^ 2 ^ 0x5252)
@@ -181,7 +186,7 @@ def cpu_reference_run(args, wl, text, offsets, steps: int, warmup: int, batch: b
                 break
         reqs.append(piece if cut < 0 else piece[:cut + 1])
     table = O.PatternTable(wl.patterns)
-    cfg = ScoringConfig()
+    cfg = ScoringConfig(max_window=1000) if args.config == "c4" and not batch else ScoringConfig()
     times, total = [], 0
     for it in range(warmup + steps):
         t0 = time.perf_counter()
@@ -201,7 +206,7 @@ def cpu_reference_run(args, wl, text, offsets, steps: int, warmup: int, batch: b
     }
 
 
-def parity_check(lp, wl, text, offsets, rank: int, world: int, batch: bool, min_lines: int = 20000):
+def parity_check(lp, wl, text, offsets, rank: int, world: int, batch: bool, scfg=None, min_lines: int = 20000):
     """A slice of the timed input through the timed entry point vs the oracle: lines and patterns bit-exact, scores
     to 1e-9 relative (they are bit-identical in practice). At N>1 every rank checks its own slice through the
     collective call, against the oracle primed with the counts of the lower ranks (FTS read-before-increment order)."""
@@ -239,7 +244,7 @@ def parity_check(lp, wl, text, offsets, rank: int, world: int, batch: bool, min_
         prior = sum((c.cpu().numpy() for c in allc[:rank]), np.zeros(len(wl.patterns), np.int64)) if rank else None
     ok, lines, detail = True, 0, ""
     eb = res.log_event_begin
-    cfg = ScoringConfig()
+    cfg = scfg or ScoringConfig()
     table = O.PatternTable(wl.patterns)
     run_prior = None if prior is None else prior.astype(np.uint64)
     for j in range(len(off) - 1):       # the logs of the slice one after the other, as the reference would serve them
@@ -292,6 +297,9 @@ def main():
     ap.add_argument("--patterns", type=int, default=500)
     ap.add_argument("--logs-per-gpu", type=int, default=50, help="N>1: logs in each rank's batch")
     ap.add_argument("--lines-per-log", type=int, default=20_000, help="N>1: lines per log of the batch (configs[4])")
+    ap.add_argument("--config", default="c2", choices=["c1", "c2", "c3", "c4"],
+                    help="single-log workload: c2 = the headline config; c1 (10k lines x 50 patterns), c3 (look-around / back-reference "
+                         "patterns), c4 (windows up to 1000 lines; use with --shard lines at N>1) for profiles/")
     ap.add_argument("--batch", action="store_true", help="use the batch workload at N=1 too (profiling the C5 shape on one GPU)")
     ap.add_argument("--ref-lines", type=int, default=4000, help="lines of one CPU request in the reference arm / cpu_baseline")
     ap.add_argument("--ref-threads", type=int, default=0)
@@ -316,8 +324,13 @@ def main():
                   "patterns": args.patterns, "lines_per_log": args.lines_per_log, "logs_per_gpu": args.logs_per_gpu,
                   "parallelism": f"batch sharded by log over {world} GPU(s); per-pattern frequency counts all-gathered over NCCL inside the library"}
     else:
-        config = {"workload": f"C2: single {args.lines}-line synthetic Java pod log (~{{:.0f}} MB) vs {args.patterns} DFA-only patterns",
-                  "patterns": args.patterns, "lines_per_log": args.lines, "logs_per_gpu": 1, "parallelism": "1 GPU"}
+        what = {"c1": "C1: single 10000-line synthetic Java pod log (~{:.1f} MB) vs 50 patterns",
+                "c2": f"C2: single {args.lines}-line synthetic Java pod log (~{{:.0f}} MB) vs {args.patterns} DFA-only patterns",
+                "c3": f"C3: single {args.lines}-line log (~{{:.0f}} MB) vs {args.patterns} patterns, 12 % with look-around / back-references / possessive groups",
+                "c4": f"C4: single {args.lines}-line log (~{{:.0f}} MB), dense secondary matches, proximity / context windows up to 1000 lines, {args.patterns} patterns"}[args.config]
+        if args.config == "c1":
+            args.lines = 10_000
+        config = {"workload": what, "patterns": args.patterns, "lines_per_log": args.lines, "logs_per_gpu": 1, "parallelism": "1 GPU"}
     config["l2"] = "3 device copies of the input at distinct addresses, rotated per step (3 x 135 MB > 126 MB L2)"
     if by_lines:
         config["logs_per_gpu"] = 1.0 / world
@@ -359,7 +372,8 @@ def main():
     wl, text, offsets = build_workload(args, 0 if by_lines else rank, batch)
     nbytes = len(text)
     config["workload"] = config["workload"].format(nbytes / 1e6)
-    lp = binding.LogParser(ScoringConfig(), device=local_rank)
+    scfg = ScoringConfig(max_window=1000) if args.config == "c4" and not batch else ScoringConfig()
+    lp = binding.LogParser(scfg, device=local_rank)
     lp.load_patterns(wl.patterns)
     P = len(wl.patterns)
     if world > 1 and not by_lines:
@@ -416,7 +430,7 @@ def main():
         res = step_device(i)
     parity = None
     if not args.no_parity and not by_lines:
-        parity = parity_check(lp, wl, text, offsets, rank, world, batch)
+        parity = parity_check(lp, wl, text, offsets, rank, world, batch, scfg)
         for i in range(2):
             res = step_device(i)        # back to the estimates of the full-size input
     barrier()
@@ -486,31 +500,31 @@ def main():
         h2d_ceiling = {"lines_per_s": lines_all / float(tt[0]), "gb_per_s_per_gpu": nbytes / float(tt[0]) / 1e9,
                        "what": f"{world} concurrent pinned host->device copies of one step's input, nothing else running"}
 
-    # ---- the same call from two request threads, each with its own context (what the reference's worker threads
-    # would do): one request's host->device copy overlaps the other's kernels. Informational.
+    # ---- the same call from two request threads on the ONE context (what the reference's worker threads do with the
+    # @ApplicationScoped service, AS:35): the context's workers let one request's host->device copy run under the other's
+    # kernels. Informational; `e2e.value` stays the single synchronous caller.
     e2e_two = None
     if world == 1 and not args.no_e2e and not batch:
-        lp2 = binding.LogParser(ScoringConfig(), device=local_rank)
-        lp2.load_patterns(wl.patterns)
-        parsers = [lp, lp2]
-        for q in parsers:
+        hptr2 = binding.host_alloc(max(nbytes, 1))
+        ctypes.memmove(hptr2, hptr, nbytes)
+        for hp in (hptr, hptr2):
             for _ in range(3):
-                q.analyze_host_ptr(hptr, nbytes)
+                lp.analyze_host_ptr(hp, nbytes)
         torch.cuda.synchronize()
 
-        def worker(q):
+        def worker(hp):
             for _ in range(e2e_steps):
-                q.analyze_host_ptr(hptr, nbytes)
+                lp.analyze_host_ptr(hp, nbytes)
 
-        threads = [threading.Thread(target=worker, args=(q,)) for q in parsers]
+        threads = [threading.Thread(target=worker, args=(hp,)) for hp in (hptr, hptr2)]
         t0 = time.perf_counter()
         for th in threads:
             th.start()
         for th in threads:
             th.join()
         torch.cuda.synchronize()
-        e2e_two = args.lines * len(parsers) * e2e_steps / (time.perf_counter() - t0)
-        lp2.close()
+        e2e_two = args.lines * len(threads) * e2e_steps / (time.perf_counter() - t0)
+        binding.host_free(hptr2)
 
     if by_lines:
         nbytes = nbytes_all

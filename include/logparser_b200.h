@@ -96,13 +96,18 @@ typedef struct lp_result_view {
      * offsets from the start of the line (equal to Java's UTF-16 offsets on ASCII lines). */
     const uint32_t* span_start;     /* [n_events], NULL unless LP_OPT_SPANS                       */
     const uint32_t* span_end;       /* [n_events]                                                 */
+    /* (line, regex) evaluations that the backtracking verifier abandoned after LP_VM_MAX_STEPS (2^26) steps or on
+     * stack exhaustion; such a pair counts as "no match". java.util.regex would keep backtracking (or throw
+     * StackOverflowError). 0 for every pattern set that stays on the automaton path. See LP_OPT_STRICT_BUDGET. */
+    uint64_t budget_exceeded;
 } lp_result_view;
 
 enum {
     LP_OPT_FACTORS = 1,        /* also return the seven factors per event                        */
     LP_OPT_LINE_OFFSETS = 2,   /* also return line_start/line_end for context slicing (AS:132-156) */
     LP_OPT_NO_RANK = 4,        /* skip the ranking sort                                          */
-    LP_OPT_SPANS = 8           /* also return the match span of every event (backtracking engine) */
+    LP_OPT_SPANS = 8,          /* also return the match span of every event (backtracking engine) */
+    LP_OPT_STRICT_BUDGET = 16  /* fail the call with LP_ERR_BACKTRACK instead of reporting budget_exceeded > 0 */
 };
 
 /* ---- host buffers --------------------------------------------------------------------------

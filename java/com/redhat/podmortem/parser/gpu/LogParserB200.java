@@ -37,7 +37,7 @@ import java.util.regex.PatternSyntaxException;
  */
 public final class LogParserB200 implements AutoCloseable {
 
-    public static final int OPT_FACTORS = 1, OPT_LINE_OFFSETS = 2, OPT_NO_RANK = 4, OPT_SPANS = 8;
+    public static final int OPT_FACTORS = 1, OPT_LINE_OFFSETS = 2, OPT_NO_RANK = 4, OPT_SPANS = 8, OPT_STRICT_BUDGET = 16;
     private static final int LP_ERR_SYNTAX = -2;
 
     private static final Linker LINKER = Linker.nativeLinker();
@@ -64,13 +64,13 @@ public final class LogParserB200 implements AutoCloseable {
             JAVA_DOUBLE.withName("severity_multiplier"), JAVA_INT.withName("has_context"), JAVA_INT.withName("lines_before"),
             JAVA_INT.withName("lines_after"), JAVA_INT.withName("n_secondaries"), ADDRESS.withName("secondaries"),
             JAVA_INT.withName("n_sequences"), MemoryLayout.paddingLayout(4), ADDRESS.withName("sequences"));
-    // lp_result_view (16 fields of 8 bytes)
+    // lp_result_view (17 fields of 8 bytes)
     static final StructLayout VIEW = MemoryLayout.structLayout(
             JAVA_LONG.withName("n_logs"), JAVA_LONG.withName("n_events"), ADDRESS.withName("log_n_lines"),
             ADDRESS.withName("log_event_begin"), ADDRESS.withName("line"), ADDRESS.withName("pattern"), ADDRESS.withName("score"),
             ADDRESS.withName("rank"), ADDRESS.withName("factors"), ADDRESS.withName("freq_delta"), JAVA_LONG.withName("n_patterns"),
             ADDRESS.withName("line_start"), ADDRESS.withName("line_end"), JAVA_LONG.withName("total_lines"),
-            ADDRESS.withName("span_start"), ADDRESS.withName("span_end"));
+            ADDRESS.withName("span_start"), ADDRESS.withName("span_end"), JAVA_LONG.withName("budget_exceeded"));
 
     private static final MethodHandle CREATE = h("lp_create", FunctionDescriptor.of(ADDRESS, ADDRESS, JAVA_INT));
     private static final MethodHandle DESTROY = h("lp_destroy", FunctionDescriptor.ofVoid(ADDRESS));
@@ -89,7 +89,7 @@ public final class LogParserB200 implements AutoCloseable {
                                double frequencyThreshold, double maxPenalty) {}
 
     /** Columns of one request's result, copied out of the library's page-locked buffer. */
-    public record Columns(int totalLines, int[] line, int[] pattern, double[] score, int[] rank, long[] freqDelta) {}
+    public record Columns(int totalLines, int[] line, int[] pattern, double[] score, int[] rank, long[] freqDelta, long budgetExceeded) {}
 
     // ScoringService.java:30-36
     private static final Map<String, Double> SEVERITY_MULTIPLIERS =
@@ -238,7 +238,8 @@ public final class LogParserB200 implements AutoCloseable {
                 double[] score = v.get(ADDRESS, 48).reinterpret(8L * m).toArray(JAVA_DOUBLE);
                 int[] rank = v.get(ADDRESS, 56).reinterpret(4L * m).toArray(JAVA_INT);
                 long[] delta = v.get(ADDRESS, 72).reinterpret(8L * nPatterns).toArray(JAVA_LONG);
-                return new Columns(total, line, pat, score, rank, delta);
+                long abandoned = v.get(JAVA_LONG, 128);      // evaluations the backtracking verifier gave up on (count as no match)
+                return new Columns(total, line, pat, score, rank, delta, abandoned);
             } finally {
                 FREE.invokeExact(res);
             }

@@ -17,7 +17,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.path.join(_HERE, "liblogparser_b200.so")
 
 LP_OK, LP_ERR_INVALID, LP_ERR_SYNTAX, LP_ERR_UNSUPPORTED, LP_ERR_CUDA, LP_ERR_LIMIT, LP_ERR_BACKTRACK = 0, -1, -2, -3, -4, -5, -6
-OPT_FACTORS, OPT_LINE_OFFSETS, OPT_NO_RANK, OPT_SPANS = 1, 2, 4, 8
+OPT_FACTORS, OPT_LINE_OFFSETS, OPT_NO_RANK, OPT_SPANS, OPT_STRICT_BUDGET = 1, 2, 4, 8, 16
 
 
 class LpError(RuntimeError):
@@ -68,7 +68,7 @@ class ResultView(C.Structure):
         ("score", C.POINTER(C.c_double)), ("rank", C.POINTER(C.c_uint32)), ("factors", C.POINTER(C.c_double)),
         ("freq_delta", C.POINTER(C.c_uint64)), ("n_patterns", C.c_uint64), ("line_start", C.POINTER(C.c_uint32)),
         ("line_end", C.POINTER(C.c_uint32)), ("total_lines", C.c_uint64),
-        ("span_start", C.POINTER(C.c_uint32)), ("span_end", C.POINTER(C.c_uint32)),
+        ("span_start", C.POINTER(C.c_uint32)), ("span_end", C.POINTER(C.c_uint32)), ("budget_exceeded", C.c_uint64),
     ]
 
 
@@ -197,6 +197,7 @@ class Result:
     line_end: Optional[np.ndarray] = None
     span_start: Optional[np.ndarray] = None     # OPT_SPANS: Matcher.start()/end() as byte offsets within the line
     span_end: Optional[np.ndarray] = None
+    budget_exceeded: int = 0                    # (line, regex) evaluations abandoned by the backtracking verifier (count as no match)
 
     @property
     def n_lines(self) -> int:
@@ -299,6 +300,7 @@ class LogParser:
             n_logs=nl, log_n_lines=_arr(v.log_n_lines, nl, np.uint64), log_event_begin=_arr(v.log_event_begin, nl + 1, np.uint64),
             line=_view(v.line, m, np.uint32, owner), pattern=_view(v.pattern, m, np.uint32, owner), score=_view(v.score, m, np.float64, owner),
             rank=_view(v.rank, m, np.uint32, owner), freq_delta=_view(v.freq_delta, v.n_patterns, np.uint64, owner))
+        res.budget_exceeded = int(v.budget_exceeded)
         if v.factors:
             res.factors = _view(v.factors, m * 7, np.float64, owner).reshape(m, 7)
         if v.span_start:
@@ -350,6 +352,16 @@ class LogParser:
         keep, pp = self._prior(prior_count)
         out = C.c_void_p()
         rc = self.L.lp_analyze_batch(self.h, buf.ctypes.data if buf.size else None, op, len(logs), pp, options, C.byref(out))
+        if rc != LP_OK:
+            _raise(rc)
+        return self._take(out)
+
+    def analyze_batch_host_ptr(self, host_ptr: int, offsets, prior_count=None, options: int = 0) -> Result:
+        """lp_analyze_batch on a caller-owned host buffer (page-locked for a truly asynchronous copy) that holds the concatenated logs."""
+        oa, op = self._offsets(offsets)
+        keep, pp = self._prior(prior_count)
+        out = C.c_void_p()
+        rc = self.L.lp_analyze_batch(self.h, host_ptr, op, len(oa) - 1, pp, options, C.byref(out))
         if rc != LP_OK:
             _raise(rc)
         return self._take(out)
@@ -517,6 +529,7 @@ def load_debug_library() -> C.CDLL:
     L.lp_debug_plan_dump.argtypes = [vp, C.c_size_t, C.c_char_p, C.c_size_t, C.c_char_p, C.c_size_t]
     L.lp_debug_group_match.restype = C.c_uint32
     L.lp_debug_group_match.argtypes = [C.POINTER(C.c_char_p), C.POINTER(C.c_int), C.c_size_t, C.c_char_p, C.c_size_t]
+    L.lp_debug_group_skip.argtypes = [C.POINTER(C.c_char_p), C.POINTER(C.c_int), C.c_size_t, C.POINTER(C.c_uint32)]
     _dbg = L
     return L
 

@@ -151,6 +151,25 @@ size_t lp_debug_rx_literals(void* h, char* buf, size_t cap) {
 // Builds one scan group (product DFA) from `n` regexes and walks `text` through its serialised
 // tables exactly as k_dfa_scan does. Returns the hit mask (bit k = regex k), or 0xFFFFFFFF when the
 // group cannot be built.
+// The first-byte skip set of the scan group built from `n` regexes (k_dfa_scan does not walk a non-empty line whose
+// first byte is in it). Returns 0, or -1 when the group cannot be built.
+int lp_debug_group_skip(const char* const* regexes, const int* flags, size_t n, uint32_t* out8) {
+    try {
+        std::vector<ParsedRegex> pr;
+        std::vector<const Ast*> roots;
+        for (size_t i = 0; i < n; ++i) pr.push_back(parse_java_regex(regexes[i], flags ? flags[i] : 0));
+        for (auto& p : pr) { if (!p.regular) return -1; roots.push_back(p.root.get()); }
+        MultiDfa d;
+        if (!build_multi_dfa(roots, d, 8192)) return -1;
+        std::vector<uint32_t> rx(n), blob;
+        for (size_t i = 0; i < n; ++i) rx[i] = (uint32_t)i + 4;
+        serialise_group(rx, d, blob);
+        group_skip_set(blob, out8);
+        return 0;
+    } catch (const std::exception&) {
+        return -1;
+    }
+}
 uint32_t lp_debug_group_match(const char* const* regexes, const int* flags, size_t n, const uint8_t* text, size_t len) {
     try {
         std::vector<ParsedRegex> pr;

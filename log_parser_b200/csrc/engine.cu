@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdio>
 #include <chrono>
@@ -129,7 +130,7 @@ struct lp_result {
     uint64_t n_patterns = 0;
     std::vector<uint64_t> log_n_lines, log_event_begin;
     std::vector<uint32_t> line_start, line_end, zero_rank;
-    uint64_t n_logs = 0, n_events = 0, total_lines = 0;
+    uint64_t n_logs = 0, n_events = 0, total_lines = 0, budget_exceeded = 0;
     bool has_factors = false, has_offsets = false;
     ~lp_result() { if (hold.p) { if (pool) pool->give_back(hold); else hold.release(); } }
 };
@@ -149,6 +150,7 @@ struct lp_ctx {
     const uint8_t* d_rx_record = nullptr;
     uint32_t n_group_record_rx = 0;
     DevBuf f_bitmap, f_key, f_lits, f_bytes;   // prefilter tables (re-uploaded by calibration)
+    DevBuf line_skip;                          // per line: the always-on scan need not walk it (written by k_expand)
     DevBuf f_bits, f_gkeys, fs_state, fs_lists; // fused scan: first-stage bit table, exact gram keys, ticket counters, per-tile newline lists
     const uint8_t* d_byte_table = nullptr;
     int scan_mode = 0;                         // 0: fused single-pass scan (k_fscan); 1: k_filter_count + k_scan_tiles + k_lines (LP_SCAN_MODE=legacy)
@@ -198,6 +200,15 @@ struct lp_ctx {
     cudaEvent_t ev[10]{};
     lp_timings tm{};
     uint64_t launches = 0;
+
+    // Further workers of this context: same pattern set and configuration, own stream, scratch and estimates. A stateless
+    // request (lp_analyze, lp_analyze_device, lp_analyze_batch*) runs on whichever worker is free, so that requests from
+    // several threads overlap on the GPU (one's host->device copy under another's kernels). The two-phase, collective and
+    // line-range calls keep state between calls and stay on the context itself.
+    std::vector<lp_ctx*> extra;
+    lp_ctx* owner = nullptr;                    // the context this worker belongs to (itself for the context)
+    std::atomic<uint32_t> next_worker{0};
+    std::atomic<lp_ctx*> last_used{nullptr};
 };
 
 namespace {
@@ -383,7 +394,7 @@ bool small_sort(lp_ctx* c, const unsigned long long* in, uint32_t n, int end_bit
     if (n == 0 || n_tiles > SS_MAX_TILES) return false;
     c->ss_keys.ensure((size_t)n_tiles * SS_TILE * 8);
     c->ss_idx.ensure((size_t)n_tiles * SS_TILE * 4);
-    k_tile_sort<<<n_tiles, SS_THREADS, 0, c->stream>>>(in, n, end_bit, c->ss_keys.as<unsigned long long>(), c->ss_idx.as<uint32_t>());
+    k_tile_sort<<<n_tiles, SS_THREADS, sizeof(SsSorter::TempStorage), c->stream>>>(in, n, end_bit, c->ss_keys.as<unsigned long long>(), c->ss_idx.as<uint32_t>());
     k_tile_rank<<<blocks_for(n_tiles * SS_TILE, 128), 128, 0, c->stream>>>(c->ss_keys.as<unsigned long long>(), c->ss_idx.as<uint32_t>(), n_tiles, n,
                                                                           out_sorted, out_rank, n_valid);
     c->launches += 2;
@@ -400,12 +411,19 @@ int bits_for(uint64_t v) { int b = 1; while (b < 64 && (v >> b)) ++b; return b; 
 struct Retry {};
 
 void bump(size_t& est, uint64_t observed) { est = std::max<size_t>(est, (size_t)(observed + observed / 4 + 1024)); }
+// After a call that fitted: the estimate follows what the log needed, dropping by at most a quarter per call. Sorts and
+// scans run over the estimated capacities, so a first guess that was several times too large (or one huge log) must not
+// tax every later call; the slow decay keeps a workload that alternates between log sizes from re-running every time.
+void settle(size_t& est, uint64_t observed) {
+    const size_t need = (size_t)(observed + observed / 4 + 1024);
+    est = std::max(need, est - est / 4);
+}
 
-void check_estimates(lp_ctx* c, const Counters& h, uint32_t n_logs, bool events_too) {
+void check_estimates(lp_ctx* c, const Counters& h, uint32_t n_logs, bool events_too, int options) {
     bool retry = false;
     const uint64_t G = (uint64_t)h.total_nl + n_logs;
     if (G >= 0xFFFFFFF0ull) throw LimitFail("too many lines");
-    if (h.overflow & 16u) throw std::overflow_error("backtracking verifier exceeded its step/stack budget");
+    if ((h.overflow & 16u) && (options & LP_OPT_STRICT_BUDGET)) throw std::overflow_error("backtracking verifier exceeded its step/stack budget");
     if (G + 1 > c->est_lines) { bump(c->est_lines, G + 1); retry = true; }
     if (h.n_cand > c->est_cand) { bump(c->est_cand, h.n_cand); retry = true; }
     if (h.n_tasks > c->est_tasks) { bump(c->est_tasks, h.n_tasks); retry = true; }
@@ -424,9 +442,9 @@ void check_estimates(lp_ctx* c, const Counters& h, uint32_t n_logs, bool events_
     }
     c->retries = 0;
     // remember what this log needed (with headroom) for the next call
-    bump(c->est_lines, G + 1); bump(c->est_cand, h.n_cand); bump(c->est_tasks, h.n_tasks);
-    bump(c->est_vm_tasks, h.n_vm_tasks); bump(c->est_recs, h.n_recs); bump(c->est_items, max_items);
-    if (events_too) bump(c->est_events, h.n_events);
+    settle(c->est_lines, G + 1); settle(c->est_cand, h.n_cand); settle(c->est_tasks, h.n_tasks);
+    settle(c->est_vm_tasks, h.n_vm_tasks); settle(c->est_recs, h.n_recs); settle(c->est_items, max_items);
+    if (events_too) settle(c->est_events, h.n_events);
 }
 
 EstCaps est_caps(const lp_ctx* c) {
@@ -446,6 +464,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     for (uint32_t k = 0; k < n_logs; ++k) if (h_off[k] > h_off[k + 1]) throw std::invalid_argument("offsets must be non-decreasing");
     if (h_off[0] != 0 || h_off[n_logs] != len) throw std::invalid_argument("offsets[0] must be 0 and offsets[n_logs] the total size");
     cudaStream_t st = c->stream;
+    c->owner->last_used.store(c);               // lp_get_timings reports the worker that ran last
     c->pend = lp_ctx::Pending();
     c->launches = 0;
     c->tm = lp_timings();
@@ -521,6 +540,10 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         fz.gram_keys = c->f_gkeys.as<uint32_t>(); fz.table_bits = c->dp.table_bits;
         fz.cand = c->cand.as<uint32_t>(); fz.cand_cap = (uint32_t)std::min<size_t>(c->est_cand, 0xFFFFFFFFu); fz.ctr = ctr;
         fz.use_filter = use_filter ? 1 : 0;
+        // a line is left out of the always-on scan when ALL its groups are decided, without a hit, by its first byte
+        for (int w = 0; w < 8; ++w) fz.skip1[w] = c->plan.groups.empty() ? 0u : 0xFFFFFFFFu;
+        for (const auto& g : c->plan.groups) for (int w = 0; w < 8; ++w) fz.skip1[w] &= g.skip1[w];
+        c->line_skip.ensure(line_cap + 16);
     }
     uint32_t fs_launches = 0;
     auto launch_fscan = [&](uint32_t tile_begin, uint32_t tile_end) {
@@ -580,6 +603,8 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         ea.log_off = c->log_off.as<uint64_t>(); ea.n_logs = n_logs;
         ea.line_start = c->line_start.as<uint32_t>(); ea.line_end = c->line_end.as<uint32_t>();
         ea.first_line = c->first_line.as<uint32_t>(); ea.line_cap = (uint32_t)line_cap; ea.ctr = ctr;
+        ea.line_skip = c->plan.groups.empty() ? nullptr : c->line_skip.as<uint8_t>();
+        for (int w = 0; w < 8; ++w) ea.skip1[w] = fz.skip1[w];
         k_expand<<<std::min<uint32_t>(n_tiles, (uint32_t)c->n_sm * 16), EX_THREADS, 0, st>>>(ea);
     } else {
     ScanArgs sa{};
@@ -610,7 +635,8 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         ca.items = c->items.as<unsigned long long>(); ca.item_cap = (uint32_t)std::min<size_t>(c->est_items, 0xFFFFFFFFu); ca.ctr = ctr;
         ResolveArgs ra{};
         ra.text = d_text; ra.len = len; ra.items = ca.items; ra.item_cap = ca.item_cap;
-        ra.tile_prefix = c->tile_counts.as<uint32_t>(); ra.n_tiles = n_tiles; ra.tile_bytes = tile_bytes; ra.log_off = c->log_off.as<uint64_t>(); ra.n_logs = n_logs;
+        ra.tile_prefix = c->tile_counts.as<uint32_t>(); ra.n_tiles = n_tiles; ra.tile_bytes = tile_bytes;
+        ra.span_counts = fused ? c->fs_lists.as<uint16_t>() : nullptr; ra.log_off = c->log_off.as<uint64_t>(); ra.n_logs = n_logs;
         ra.line_start = c->line_start.as<uint32_t>(); ra.line_end = c->line_end.as<uint32_t>(); ra.n_lines_total = (uint32_t)line_cap;
         ra.tasks = c->tasks.as<unsigned long long>(); ra.task_cap = va.task_cap; ra.ctr = ctr;
         ra.vm_tasks = c->vm_tasks.as<unsigned long long>(); ra.vm_task_cap = va.vm_task_cap;
@@ -647,7 +673,10 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         da.first_line = c->first_line.as<uint32_t>(); da.n_lines = c->n_lines.as<uint32_t>(); da.n_logs = n_logs;
         size_t tab_bytes = 0;
         da.n_groups = (uint32_t)std::min<size_t>(DS_MAXG, c->d_group_blob.size() - g0);
+        for (int w = 0; w < 8; ++w) da.skip1[w] = 0xFFFFFFFFu;
+        da.line_skip = fused ? c->line_skip.as<uint8_t>() : nullptr;      // the flags hold for every group (k_fscan used the intersection)
         for (uint32_t q = 0; q < da.n_groups; ++q) {
+            for (int w = 0; w < 8; ++w) da.skip1[w] &= c->plan.groups[g0 + q].skip1[w];
             da.blob[q] = c->d_group_blob[g0 + q]; da.blob_words[q] = c->group_words[g0 + q];
             tab_bytes += ((size_t)c->group_words[g0 + q] + 3) / 4 * 16;
         }
@@ -680,7 +709,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         c->launches += 2;
     }
     if (c->after_unique) c->after_unique();
-    k_rx_bounds<<<blocks_for(c->dp.n_rx + 1, 128), 128, 0, st>>>(c->recs.as<unsigned long long>(), ctr, c->dp.n_rx, c->dp.gb, c->rx_begin.as<uint32_t>());
+    k_rx_bounds<<<blocks_for((uint64_t)(c->dp.n_rx + 1) * 32, 128), 128, 0, st>>>(c->recs.as<unsigned long long>(), ctr, c->dp.n_rx, c->dp.gb, c->rx_begin.as<uint32_t>());
     c->launches += 1;
     if (!c->plan.ctx_in_groups) {
         k_ctx_flags<<<c->n_sm * 4, 256, 0, st>>>(c->recs.as<unsigned long long>(), c->rx_begin.as<uint32_t>(), c->dp.gb, c->ctx_flags.as<uint32_t>());
@@ -716,7 +745,7 @@ void per_pattern_counts(lp_ctx* c, uint64_t* counts_out) {
     if (np) CK(cudaMemcpyAsync(counts_out, c->freq_delta.p, (size_t)np * 8, cudaMemcpyDeviceToHost, st));
     CK(cudaStreamSynchronize(st));
     CK(cudaGetLastError());
-    check_estimates(c, h, c->pend.n_logs, true);
+    check_estimates(c, h, c->pend.n_logs, true, c->pend.options);
 }
 
 // The one synchronisation of a call. The pipeline runs for well under a millisecond on typical logs, so the
@@ -772,13 +801,9 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
         prior_d = c->prior.as<unsigned long long>();
     }
     if (prior_dev) prior_d = prior_dev;
-    const uint32_t gb = blocks_for(mc, 256);
-    const uint32_t n_slots = (uint32_t)c->plan.slot_first_pat.size();
-    k_event_prep<<<gb, 256, 0, st>>>(c->ev_key.as<unsigned long long>(), ctr, mc, c->dp, c->first_line.as<uint32_t>(), n_logs, n_slots,
-                                     c->ev_log.as<uint32_t>(), c->slot_key.as<uint32_t>(), c->ev_idx.as<uint32_t>(),
-                                     c->freq_delta.as<unsigned long long>());
     ScoreArgs sa{};
     sa.ev_key = c->ev_key.as<unsigned long long>(); sa.m_cap = mc; sa.ctr = ctr; sa.ev_log = c->ev_log.as<uint32_t>();
+    sa.ev_idx = c->ev_idx.as<uint32_t>(); sa.freq_delta = c->freq_delta.as<unsigned long long>(); sa.n_logs = n_logs;
     sa.rank_in_slot = c->rank_in_slot.as<uint32_t>(); sa.prior = prior_d;
     sa.first_line = c->first_line.as<uint32_t>(); sa.n_lines = c->n_lines.as<uint32_t>();
     sa.keys = c->recs.as<unsigned long long>(); sa.rx_begin = c->rx_begin.as<uint32_t>();
@@ -797,9 +822,12 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
     }
     if (wait_before_score) CK(cudaStreamWaitEvent(st, wait_before_score, 0));     // the prior counts arrive on another stream
     k_score<<<blocks_for(mc, 128), 128, 0, st>>>(sa, c->dp, c->sc);
-    k_log_event_begin<<<blocks_for(n_logs + 1, 128), 128, 0, st>>>(c->ev_key.as<unsigned long long>(), ctr, c->first_line.as<uint32_t>(),
-                                                                   n_logs, c->dp.pb, c->log_event_begin.as<unsigned long long>());
-    c->launches += 3;
+    if (n_logs > 1 || mc > SS_MAX_TILES * (uint32_t)SS_TILE) {      // per-log event ranges: trivial for one log unless the large-sort ranking path needs them on the device
+        k_log_event_begin<<<blocks_for(n_logs + 1, 128), 128, 0, st>>>(c->ev_key.as<unsigned long long>(), ctr, c->first_line.as<uint32_t>(),
+                                                                       n_logs, c->dp.pb, c->log_event_begin.as<unsigned long long>());
+        c->launches += 1;
+    }
+    c->launches += 1;
     if (!(options & LP_OPT_NO_RANK) && n_logs == 1 &&
         small_sort(c, c->sort_key.as<unsigned long long>(), mc, 64, nullptr, d_rank, &ctr->n_events)) {
         // one log, few events: ranks by tile sort + counting (descending score, ties keep discovery order)
@@ -849,12 +877,13 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
     Counters h;
     memcpy(&h, hs + o_ctr, sizeof h);
     if (flag_dev && flag_out) memcpy(flag_out, hs + o_flag, 8);
-    check_estimates(c, h, n_logs, true);       // throws Retry when a buffer was too small
+    check_estimates(c, h, n_logs, true, options);       // throws Retry when a buffer was too small
 
     const uint32_t m = h.n_events;
     const uint32_t G = (uint32_t)(h.total_nl + n_logs);
     res->n_events = m;
     res->total_lines = G;
+    res->budget_exceeded = h.n_budget;
     // the result takes the staging buffer over: its columns are read in place
     res->line = reinterpret_cast<uint32_t*>(hs + o_line);
     res->pattern = reinterpret_cast<uint32_t*>(hs + o_pat);
@@ -963,6 +992,23 @@ const uint8_t* stage_host_log(lp_ctx* c, const uint8_t* host, uint64_t len) {
     return c->text.as<uint8_t>();
 }
 
+// A free worker of the context (itself or one of its extras), locked; when all are busy, the next one in turn.
+struct WorkerLock {
+    lp_ctx* w;
+    std::unique_lock<std::mutex> lk;
+};
+WorkerLock pick_worker(lp_ctx* c) {
+    const size_t n = 1 + c->extra.size();
+    for (size_t i = 0; i < n; ++i) {            // the context itself first: a single caller always lands on the same, warm scratch
+        lp_ctx* w = i == 0 ? c : c->extra[i - 1];
+        std::unique_lock<std::mutex> lk(w->mu, std::try_to_lock);
+        if (lk.owns_lock()) return WorkerLock{w, std::move(lk)};
+    }
+    const uint32_t turn = c->next_worker.fetch_add(1, std::memory_order_relaxed) % n;
+    lp_ctx* w = turn == 0 ? c : c->extra[turn - 1];
+    return WorkerLock{w, std::unique_lock<std::mutex>(w->mu)};
+}
+
 }  // namespace
 
 // ============================================================================================
@@ -972,6 +1018,32 @@ extern "C" {
 
 const char* lp_last_error(void) { return g_last_error.c_str(); }
 const char* lp_version(void) { return "logparser_b200 0.1 (sm_100a)"; }
+
+static lp_ctx* create_worker(const lp_scoring_cfg* cfg, int device) {
+    std::unique_ptr<lp_ctx> ctx(new lp_ctx());
+    ctx->owner = ctx.get();
+    ctx->device = device;
+    ctx->cfg = *cfg;
+    ctx->cfg.decay_lut = nullptr;
+    CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
+    CK(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    for (auto& e : ctx->ev) CK(cudaEventCreate(&e));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device));
+    ctx->n_sm = prop.multiProcessorCount;
+    if (const char* m = getenv("LP_SCAN_MODE")) ctx->scan_mode = strcmp(m, "legacy") == 0 ? 1 : 0;
+    if (const char* v = getenv("LP_FSCAN_VARIANT")) ctx->fscan_variant = std::max(0, std::min(2, atoi(v)));
+    std::vector<double> lut((size_t)cfg->max_window + 1);
+    for (int d = 0; d <= cfg->max_window; ++d)
+        lut[d] = cfg->decay_lut ? cfg->decay_lut[d] : std::exp(-(double)d / cfg->decay_constant);   // SS:177
+    ctx->d_lut.ensure(lut.size() * 8);
+    CK(cudaMemcpy(ctx->d_lut.p, lut.data(), lut.size() * 8, cudaMemcpyHostToDevice));
+    ScoreCfg& s = ctx->sc;
+    s.early = cfg->early_bonus_threshold; s.max_early = cfg->max_early_bonus; s.penalty = cfg->penalty_threshold;
+    s.max_ctx = cfg->max_context_factor; s.freq_thr = cfg->frequency_threshold; s.max_pen = cfg->max_penalty;
+    s.max_window = cfg->max_window; s.hours = cfg->time_window_hours; s.decay_lut = ctx->d_lut.as<double>();
+    return ctx.release();
+}
 
 lp_ctx* lp_create(const lp_scoring_cfg* cfg, int device) {
     lp_ctx* c = nullptr;
@@ -984,35 +1056,19 @@ lp_ctx* lp_create(const lp_scoring_cfg* cfg, int device) {
         if (n <= 0) throw CudaFail("no CUDA device visible");
         if (device < 0 || device >= n) throw std::invalid_argument("device index out of range");
         CK(cudaSetDevice(device));
-        std::unique_ptr<lp_ctx> ctx(new lp_ctx());
-        ctx->device = device;
-        ctx->cfg = *cfg;
-        ctx->cfg.decay_lut = nullptr;
-        CK(cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking));
-        CK(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
-        for (auto& e : ctx->ev) CK(cudaEventCreate(&e));
-        cudaDeviceProp prop;
-        CK(cudaGetDeviceProperties(&prop, device));
-        ctx->n_sm = prop.multiProcessorCount;
         CK(cudaFuncSetAttribute(k_filter_count, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(GRAM_WORDS * 4)));
         CK(cudaFuncSetAttribute(k_fscan<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs::SMEM_BYTES));
         CK(cudaFuncSetAttribute(k_fscan<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs::SMEM_BYTES));
         CK(cudaFuncSetAttribute(k_fscan<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs::SMEM_BYTES));
-        if (const char* m = getenv("LP_SCAN_MODE")) ctx->scan_mode = strcmp(m, "legacy") == 0 ? 1 : 0;
-        if (const char* v = getenv("LP_FSCAN_VARIANT")) ctx->fscan_variant = std::max(0, std::min(2, atoi(v)));
+        CK(cudaFuncSetAttribute(k_tile_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SsSorter::TempStorage)));
         CK(cudaFuncSetAttribute(k_dfa_scan<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
         CK(cudaFuncSetAttribute(k_dfa_scan<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
         CK(cudaFuncSetAttribute(k_dfa_scan<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
         CK(cudaFuncSetAttribute(k_dfa_scan<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
-        std::vector<double> lut((size_t)cfg->max_window + 1);
-        for (int d = 0; d <= cfg->max_window; ++d)
-            lut[d] = cfg->decay_lut ? cfg->decay_lut[d] : std::exp(-(double)d / cfg->decay_constant);   // SS:177
-        ctx->d_lut.ensure(lut.size() * 8);
-        CK(cudaMemcpy(ctx->d_lut.p, lut.data(), lut.size() * 8, cudaMemcpyHostToDevice));
-        ScoreCfg& s = ctx->sc;
-        s.early = cfg->early_bonus_threshold; s.max_early = cfg->max_early_bonus; s.penalty = cfg->penalty_threshold;
-        s.max_ctx = cfg->max_context_factor; s.freq_thr = cfg->frequency_threshold; s.max_pen = cfg->max_penalty;
-        s.max_window = cfg->max_window; s.hours = cfg->time_window_hours; s.decay_lut = ctx->d_lut.as<double>();
+        std::unique_ptr<lp_ctx, void (*)(lp_ctx*)> ctx(create_worker(cfg, device), lp_destroy);
+        int workers = 2;        // LP_WORKERS: requests that may be in flight at once on this context
+        if (const char* w = getenv("LP_WORKERS")) workers = std::max(1, std::min(8, atoi(w)));
+        for (int k = 1; k < workers; ++k) { ctx->extra.push_back(create_worker(cfg, device)); ctx->extra.back()->owner = ctx.get(); }
         c = ctx.release();
     });
     return rc == LP_OK ? c : nullptr;
@@ -1021,6 +1077,8 @@ lp_ctx* lp_create(const lp_scoring_cfg* cfg, int device) {
 static void nccl_comm_destroy(void* comm);
 void lp_destroy(lp_ctx* c) {
     if (!c) return;
+    for (lp_ctx* e : c->extra) lp_destroy(e);
+    c->extra.clear();
     cudaSetDevice(c->device);
     cudaStreamSynchronize(c->stream);
     for (auto& b : c->plan_bufs) b.release();
@@ -1029,7 +1087,7 @@ void lp_destroy(lp_ctx* c) {
                      &c->ev_log, &c->slot_key, &c->slot_key_alt, &c->ev_idx, &c->ev_idx_alt, &c->rank_in_slot, &c->freq_delta, &c->prior,
                      &c->out_arena, &c->sort_key, &c->sort_key_alt, &c->order, &c->order_alt,
                      &c->log_sorted, &c->log_sorted_alt, &c->log_event_begin, &c->n_unique, &c->d_lut,
-                     &c->f_bitmap, &c->f_key, &c->f_lits, &c->f_bytes, &c->f_bits, &c->f_gkeys, &c->fs_state, &c->fs_lists, &c->items, &c->ss_keys, &c->ss_idx, &c->seq_tab_off, &c->seq_tab, &c->seq_T, &c->prior_eff, &c->any_flag, &c->dist_mine, &c->dist_all};
+                     &c->f_bitmap, &c->f_key, &c->f_lits, &c->f_bytes, &c->f_bits, &c->f_gkeys, &c->fs_state, &c->fs_lists, &c->line_skip, &c->items, &c->ss_keys, &c->ss_idx, &c->seq_tab_off, &c->seq_tab, &c->seq_T, &c->prior_eff, &c->any_flag, &c->dist_mine, &c->dist_all};
     for (DevBuf* b : all) b->release();
     if (c->nccl_comm) nccl_comm_destroy(c->nccl_comm);
     c->stage.release();
@@ -1063,6 +1121,16 @@ int lp_load_patterns(lp_ctx* c, const lp_pattern_desc* pats, size_t n, int64_t* 
         }
         upload_into(c->seq_tab_off, c->h_seq_tab_off);
         c->loaded = true;
+        for (lp_ctx* e : c->extra) {       // the other workers get their own copy of the (small) tables
+            std::lock_guard<std::mutex> le(e->mu);
+            e->loaded = false; e->calibrated = false; e->recalibrations = 0;
+            e->plan = c->plan;
+            upload_plan(e);
+            e->n_seq = c->n_seq; e->h_seq_tab_off = c->h_seq_tab_off;
+            upload_into(e->seq_tab_off, e->h_seq_tab_off);
+            e->est_lines = e->est_cand = e->est_tasks = e->est_vm_tasks = e->est_recs = e->est_items = e->est_events = 0;
+            e->loaded = true;
+        }
     });
 }
 
@@ -1214,8 +1282,8 @@ static int analyze_batch_dist(lp_ctx* c, const uint8_t* logs, bool on_host, cons
                 if (!flag) throw LimitFail("internal: a repeat was requested that the other ranks cannot see");
                 continue;
             }
-            if (flag & 16u) throw std::overflow_error("backtracking verifier exceeded its step/stack budget");
-            if (flag) continue;                 // every rank sees the same words: all of them repeat
+            if ((flag & 16u) && (options & LP_OPT_STRICT_BUDGET)) throw std::overflow_error("backtracking verifier exceeded its step/stack budget");
+            if (flag & ~16ull) continue;                 // every rank sees the same words: all of them repeat
             *out = res.release();
             if (on_host) {
                 float ms = 0;
@@ -1279,8 +1347,8 @@ int lp_batch_score_gathered(lp_ctx* c, const uint64_t* d_all_counts, uint32_t ra
         try {
             res.reset(run_score(c, nullptr, nullptr, c->prior_eff.as<unsigned long long>(), c->any_flag.as<unsigned long long>(), &flag));
         } catch (const Retry&) { again = true; return; }      // this rank's buffers were too small (now regrown)
-        if (flag & 16u) throw std::overflow_error("backtracking verifier exceeded its step/stack budget on another rank");
-        if (flag) { again = true; return; }                   // another rank's counts were incomplete
+        if ((flag & 16u) && (c->pend.options & LP_OPT_STRICT_BUDGET)) throw std::overflow_error("backtracking verifier exceeded its step/stack budget on another rank");
+        if (flag & ~16ull) { again = true; return; }                   // another rank's counts were incomplete
         *out = res.release();
     });
     return rc != LP_OK ? rc : (again ? LP_RETRY : LP_OK);
@@ -1406,8 +1474,8 @@ int lp_analyze_batch_device(lp_ctx* c, const uint8_t* d_logs, const uint64_t* of
     if (!c || !out) { g_last_error = "NULL argument"; return LP_ERR_INVALID; }
     return guarded(c, [&] {
         if (!offsets) throw std::invalid_argument("offsets is NULL");
-        std::lock_guard<std::mutex> lk(c->mu);
-        *out = run_all(c, [&] { return d_logs; }, offsets[n_logs], offsets, (uint32_t)n_logs, prior_count, options);
+        WorkerLock wl = pick_worker(c);
+        *out = run_all(wl.w, [&] { return d_logs; }, offsets[n_logs], offsets, (uint32_t)n_logs, prior_count, options);
     });
 }
 int lp_analyze_batch(lp_ctx* c, const uint8_t* logs, const uint64_t* offsets, size_t n_logs, const uint64_t* prior_count, int options,
@@ -1415,16 +1483,17 @@ int lp_analyze_batch(lp_ctx* c, const uint8_t* logs, const uint64_t* offsets, si
     if (!c || !out) { g_last_error = "NULL argument"; return LP_ERR_INVALID; }
     return guarded(c, [&] {
         if (!offsets) throw std::invalid_argument("offsets is NULL");
-        std::lock_guard<std::mutex> lk(c->mu);
+        WorkerLock wl = pick_worker(c);
+        lp_ctx* const w = wl.w;
         const uint64_t len = offsets[n_logs];
         if (len && !logs) throw std::invalid_argument("logs is NULL");
         bool staged = false;
         const uint8_t* d = nullptr;
-        *out = run_all(c, [&] { if (!staged) { d = stage_host_log(c, logs, len); staged = true; } return d; }, len, offsets, (uint32_t)n_logs,
+        *out = run_all(w, [&] { if (!staged) { d = stage_host_log(w, logs, len); staged = true; } return d; }, len, offsets, (uint32_t)n_logs,
                        prior_count, options);
         float ms = 0;
-        cudaEventElapsedTime(&ms, c->ev[5], c->ev[8]);
-        c->tm.h2d_ms = ms;
+        cudaEventElapsedTime(&ms, w->ev[5], w->ev[8]);
+        w->tm.h2d_ms = ms;
     });
 }
 int lp_analyze_device(lp_ctx* c, const uint8_t* d_log, size_t len, const uint64_t* prior_count, int options, lp_result** out) {
@@ -1474,13 +1543,15 @@ int lp_result_get(const lp_result* r, lp_result_view* v) {
     v->total_lines = r->total_lines;
     v->span_start = r->span_start;
     v->span_end = r->span_end;
+    v->budget_exceeded = r->budget_exceeded;
     return LP_OK;
 }
 void lp_result_free(lp_result* r) { delete r; }
 
 int lp_get_timings(const lp_ctx* c, lp_timings* out) {
     if (!c || !out) { g_last_error = "NULL argument"; return LP_ERR_INVALID; }
-    *out = c->tm;
+    const lp_ctx* w = c->last_used.load();       // the worker that ran the most recent stateless request, if any
+    *out = w ? w->tm : c->tm;
     return LP_OK;
 }
 

@@ -70,6 +70,7 @@ struct FscanArgs {
     uint32_t cand_cap;
     Counters* ctr;
     int use_filter;
+    uint32_t skip1[8];                // first bytes on which every always-on scan group is decided without a hit (k_dfa_scan skips such lines)
 };
 
 __device__ __forceinline__ uint32_t fs_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -148,7 +149,6 @@ __global__ void __launch_bounds__(fs::THREADS, 1) k_fscan(FscanArgs a) {
     const uint32_t lane4 = (uint32_t)lane * 4u;
     const uint32_t full = 0xffffffffu;
     const bool keys_in_smem = (4u << a.table_bits) <= fs::KEY_BYTES;
-    const uint32_t* const keys = keys_in_smem ? s_keys : a.gram_keys;
     const uint32_t tmask = (1u << a.table_bits) - 1u, kshift = 32 - a.table_bits;
 
     if (t == 0) {
@@ -186,6 +186,7 @@ __global__ void __launch_bounds__(fs::THREADS, 1) k_fscan(FscanArgs a) {
         const uint32_t tile = hs->tile[s];
         if (tile >= a.tile_end) break;
         const uint64_t base = (uint64_t)tile * fs::TILE;
+        const uint32_t base32 = tile * fs::TILE;          // texts are below 4 GiB
         uint8_t* const stage = stages + s * fs::STAGE_BYTES;
         uint32_t* const s_out = s_outs + s * fs::OUT_CAP;
         const bool tma = tile < a.tma_tiles;
@@ -235,7 +236,9 @@ __global__ void __launch_bounds__(fs::THREADS, 1) k_fscan(FscanArgs a) {
                         const uint32_t lt = (((1u << nq) - 1u) * 0x01010101u) | ((0x01010101u << nq) & ((1u << (8u * j)) - 1u));
                         const uint32_t pt = 32 * t + 4 * nq + j;
                         const uint32_t prev = pt ? stage[pt - 1] : (base ? a.text[base - 1] : 0u);
-                        wl[excl + __popc(P & lt)] = (uint16_t)(pt | (prev == '\r' ? 0x8000u : 0u));
+                        const uint32_t nb = stage[pt + 1];            // first byte of the line that starts here (the halo covers pt + 1 == TILE)
+                        const uint32_t skip = (nb != '\n' && nb != 0u) ? ((a.skip1[nb >> 5] >> (nb & 31u)) & 1u) : 0u;
+                        wl[excl + __popc(P & lt)] = (uint16_t)(pt | (skip << 14) | (prev == '\r' ? 0x8000u : 0u));
                     }
                 }
                 if (lane == 0) atomicAdd(&hs->n_nl[s], wtotal);
@@ -252,10 +255,11 @@ __global__ void __launch_bounds__(fs::THREADS, 1) k_fscan(FscanArgs a) {
             const uint32_t f = __funnelshift_r(wlo, whi, (pt & 3u) * 8u) | 0x20202020u;
             uint32_t slot = (f * GRAM_MUL2) >> kshift;
             uint32_t key;
-            while ((key = keys[slot]) != 0u && key != f) slot = (slot + 1) & tmask;
+            if (keys_in_smem) { while ((key = s_keys[slot]) != 0u && key != f) slot = (slot + 1) & tmask; }
+            else { while ((key = __ldg(a.gram_keys + slot)) != 0u && key != f) slot = (slot + 1) & tmask; }
             if (key == f) {
                 const uint32_t ob = atomicAdd(&hs->ncand[s], 1u);
-                if (ob < fs::OUT_CAP) s_out[ob] = (uint32_t)(base + pt);
+                if (ob < fs::OUT_CAP) s_out[ob] = base32 + pt;
                 else {      // a tile dense with gram occurrences: straight to the global queue
                     const uint32_t gi = atomicAdd(&a.ctr->n_cand, 1u);
                     if (gi < a.cand_cap) a.cand[gi] = (uint32_t)(base + pt);
@@ -303,6 +307,8 @@ struct ExpandArgs {
     uint32_t n_logs;
     uint32_t* line_start;
     uint32_t* line_end;
+    uint8_t* line_skip;               // [line_cap] out (may be NULL): 1 = the always-on scan need not walk this line
+    uint32_t skip1[8];
     uint32_t* first_line;             // [n_logs+1]
     uint32_t line_cap;
     Counters* ctr;
@@ -358,6 +364,7 @@ __global__ void __launch_bounds__(EX_THREADS) k_expand(ExpandArgs a) {
                 if (g + 1 < a.line_cap) {
                     a.line_end[g] = (uint32_t)(p - (cr ? 1 : 0));
                     a.line_start[g + 1] = (uint32_t)(p + 1);
+                    if (a.line_skip) a.line_skip[g + 1] = (uint8_t)((ent >> 14) & 1u);
                 } else atomicOr(&a.ctr->overflow, 64u);
             }
             if (events) {       // start of log j / end of log j-1 inside this tile: newlines before it = spans in front + a binary search in its span
@@ -371,7 +378,7 @@ __global__ void __launch_bounds__(EX_THREADS) k_expand(ExpandArgs a) {
                     const uint32_t nlb = prefix + s_pre[w] + lo;
                     a.first_line[j] = nlb + j;
                     if (nlb + j < a.line_cap) {
-                        if (j < a.n_logs) a.line_start[nlb + j] = (uint32_t)b;
+                        if (j < a.n_logs) { a.line_start[nlb + j] = (uint32_t)b; if (a.line_skip) a.line_skip[nlb + j] = 0; }   // first line of a log: always walked
                         if (j > 0) a.line_end[nlb + j - 1] = (uint32_t)b;
                     } else atomicOr(&a.ctr->overflow, 64u);
                 }
@@ -408,6 +415,10 @@ __global__ void __launch_bounds__(EX_THREADS) k_expand(ExpandArgs a) {
             if (g + 1 < a.line_cap) {
                 a.line_end[g] = (uint32_t)(p - (cr ? 1 : 0));
                 a.line_start[g + 1] = (uint32_t)(p + 1);
+                if (a.line_skip) {
+                    const uint32_t nb = p + 1 < a.len ? a.text[p + 1] : 0u;
+                    a.line_skip[g + 1] = (uint8_t)((nb != '\n' && nb != 0u) ? ((a.skip1[nb >> 5] >> (nb & 31u)) & 1u) : 0u);
+                }
             } else atomicOr(&a.ctr->overflow, 64u);
         }
         if (events && pos <= a.len) {
@@ -417,7 +428,7 @@ __global__ void __launch_bounds__(EX_THREADS) k_expand(ExpandArgs a) {
                 const uint32_t nlb = excl + __popcll(nl & ((1ull << (uint32_t)(b - pos)) - 1ull));
                 a.first_line[j] = nlb + j;
                 if (nlb + j < a.line_cap) {
-                    if (j < a.n_logs) a.line_start[nlb + j] = (uint32_t)b;
+                    if (j < a.n_logs) { a.line_start[nlb + j] = (uint32_t)b; if (a.line_skip) a.line_skip[nlb + j] = 0; }
                     if (j > 0) a.line_end[nlb + j - 1] = (uint32_t)b;
                 } else atomicOr(&a.ctr->overflow, 64u);
                 ++j;

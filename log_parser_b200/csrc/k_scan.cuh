@@ -221,6 +221,29 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_filter_count(FilterArgs a) {
 __global__ void __launch_bounds__(1024) k_scan_tiles(uint32_t* __restrict__ tile_counts, uint32_t n_tiles, uint32_t n_logs, Counters* ctr) {
     __shared__ uint32_t warp_tot[32];
     __shared__ uint32_t carry;
+    if (n_tiles <= 1024 * 16) {
+        // the usual case (texts up to 256 MiB): every thread owns up to 16 consecutive tiles, one block-wide prefix in all
+        const uint32_t per = (n_tiles + 1023) / 1024, first = threadIdx.x * per;
+        uint32_t v[16], sum = 0;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) { v[k] = ((uint32_t)k < per && first + k < n_tiles) ? tile_counts[first + k] : 0u; sum += v[k]; }
+        uint32_t inc = sum;
+        for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, inc, o); if ((threadIdx.x & 31) >= o) inc += t; }
+        if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = inc;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            uint32_t w = warp_tot[threadIdx.x];
+            uint32_t wi = w;
+            for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, wi, o); if (threadIdx.x >= o) wi += t; }
+            warp_tot[threadIdx.x] = wi - w;  // exclusive
+            if (threadIdx.x == 31) { ctr->total_nl = wi; ctr->n_lines_total = wi + n_logs; }
+        }
+        __syncthreads();
+        uint32_t run = warp_tot[threadIdx.x >> 5] + inc - sum;
+#pragma unroll
+        for (int k = 0; k < 16; ++k) if ((uint32_t)k < per && first + k < n_tiles) { tile_counts[first + k] = run; run += v[k]; }
+        return;
+    }
     if (threadIdx.x == 0) carry = 0;
     __syncthreads();
     for (uint32_t base = 0; base < n_tiles; base += 1024) {

@@ -1,11 +1,24 @@
 // Record post-processing, event list, scoring (ScoringService / ContextAnalysisService / FrequencyTrackingService arithmetic), multi-GPU composition kernels.
 // Part of engine.cu's translation unit (included inside its anonymous namespace); not a stand-alone header.
 // ------------------------------------------------------------------ record post-processing
+// rx_begin[r] = first record of regex r in the sorted unique records. One warp per regex: a 32-ary search, so the chain
+// of dependent loads is 4 long for 10^6 records instead of 20 (the kernel is pure load latency).
 __global__ void k_rx_bounds(const unsigned long long* __restrict__ keys, const Counters* ctr, uint32_t n_rx, uint32_t gb, uint32_t* __restrict__ rx_begin) {
-    uint32_t r = blockIdx.x * blockDim.x + threadIdx.x;
-    if (r > n_rx) return;
-    const uint32_t n = ctr->n_unique;
-    rx_begin[r] = lower_bound_dev<unsigned long long>(keys, n, (unsigned long long)r << gb);
+    const uint32_t r = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+    if (r > n_rx) return;       // warp-uniform
+    const unsigned long long want = (unsigned long long)r << gb;
+    uint32_t lo = 0, hi = ctr->n_unique;          // answer in [lo, hi]
+    while (hi - lo > 32) {
+        const uint32_t step = (hi - lo + 32) / 33;                                  // probes at lo + step * (lane + 1) - 1
+        const uint32_t at = min(lo + step * (lane + 1) - 1, hi - 1);
+        const unsigned below = __ballot_sync(0xffffffffu, keys[at] < want);       // monotone: a prefix of the lanes
+        const uint32_t k = __popc(below);
+        const uint32_t nlo = k ? min(lo + step * k, hi) : lo;                     // keys[nlo - 1] < want
+        hi = k < 32 ? min(lo + step * (k + 1) - 1, hi - 1) : hi;                  // keys[hi] >= want (or hi is the end)
+        lo = nlo;
+    }
+    const unsigned below = __ballot_sync(0xffffffffu, lo + lane < hi && keys[lo + lane] < want);
+    if (lane == 0) rx_begin[r] = lo + __popc(below);
 }
 __global__ void k_ctx_flags(const unsigned long long* __restrict__ keys, const uint32_t* __restrict__ rx_begin, uint32_t gb, uint32_t* __restrict__ flags32) {
     const uint32_t n = rx_begin[4];
@@ -63,7 +76,10 @@ struct ScoreArgs {
     const unsigned long long* ev_key;
     uint32_t m_cap;                        // threads launched; the live count comes from ctr->n_events
     const Counters* ctr;
-    const uint32_t* ev_log;
+    uint32_t* ev_log;                     // out: log of each event (padding: n_logs), for the per-log ranking
+    uint32_t* ev_idx;                     // out: identity permutation, the value column of the ranking sort
+    unsigned long long* freq_delta;       // out: events per pattern (zeroed before the launch)
+    uint32_t n_logs;
     const uint32_t* rank_in_slot;
     const unsigned long long* prior;      // [n_pat] in-window counts at call start (+ lower ranks), may be null
     const uint32_t* first_line;
@@ -94,11 +110,14 @@ __device__ __forceinline__ bool list_any_in(const unsigned long long* __restrict
 __global__ void __launch_bounds__(128) k_score(ScoreArgs a, DevPlan P, ScoreCfg C) {
     const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= a.m_cap) return;
-    if (e >= a.ctr->n_events) { a.sort_key[e] = ~0ull; return; }      // padding sorts last
+    a.ev_idx[e] = e;
+    if (e >= a.ctr->n_events) { a.sort_key[e] = ~0ull; a.ev_log[e] = a.n_logs; return; }      // padding sorts last
     const unsigned long long ek = a.ev_key[e];
     const uint32_t g = (uint32_t)(ek >> P.pb), p = (uint32_t)(ek & ((1ull << P.pb) - 1ull));
     const unsigned long long gmask = (1ull << P.gb) - 1ull;
-    const uint32_t k = a.ev_log[e];
+    const uint32_t k = a.n_logs == 1 ? 0u : upper_bound_dev<uint32_t>(a.first_line, a.n_logs + 1, g) - 1;
+    a.ev_log[e] = k;
+    atomicAdd(&a.freq_delta[p], 1ull);        // FTS:41-56: one recordPatternMatch per event, applied by the host after the call
     const uint32_t first = a.first_line[k];
     const long long N = a.n_lines[k];
     const long long i = (long long)g - first;
@@ -348,5 +367,6 @@ __global__ void k_pack_tail(const Counters* ctr, const unsigned long long* __res
     if (threadIdx.x == 0) { *o_ctr = *ctr; *o_flag = flag ? *flag : 0ull; }
     for (uint32_t p = threadIdx.x; p < n_pat; p += blockDim.x) o_delta[p] = freq_delta[p];
     for (uint32_t k = threadIdx.x; k < n_logs; k += blockDim.x) o_nl[k] = n_lines[k];
-    for (uint32_t k = threadIdx.x; k <= n_logs; k += blockDim.x) o_leb[k] = log_event_begin[k];
+    // a single log: its events are all of them (k_log_event_begin is not launched)
+    for (uint32_t k = threadIdx.x; k <= n_logs; k += blockDim.x) o_leb[k] = n_logs == 1 ? (k ? (unsigned long long)ctr->n_events : 0ull) : log_event_begin[k];
 }

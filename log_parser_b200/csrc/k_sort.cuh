@@ -3,16 +3,18 @@
 // ------------------------------------------------------------------ sorting a few ten thousand keys
 // The event list and the score ranking hold ~10^4 keys: a device-wide radix sort spends 8-10 us per
 // digit pass on them (13 passes for these two sorts), all of it launch and look-back latency. Here
-// tiles of 2048 keys are sorted in shared memory (cub::BlockRadixSort, stable) by one kernel, and a
+// tiles of 4096 keys are sorted in shared memory (cub::BlockRadixSort, stable) by one kernel, and a
 // second kernel finds every key's final position by counting, in each other tile, the keys that
 // precede it (binary searches; earlier tiles win ties, which keeps the sort stable).
-constexpr int SS_THREADS = 256, SS_ITEMS = 8, SS_TILE = SS_THREADS * SS_ITEMS;
-constexpr uint32_t SS_MAX_TILES = 64;
+constexpr int SS_THREADS = 512, SS_ITEMS = 8, SS_TILE = SS_THREADS * SS_ITEMS;       // 4096 keys per tile: ~6 tiles for the C2 event list,
+constexpr uint32_t SS_MAX_TILES = 32;                                                // so the counting pass searches 5 other tiles, not 10
 constexpr int SS_GROUP = 16;              // tiles searched in lockstep by k_tile_rank (independent probes in flight)      // beyond 131072 keys the counting pass costs more than radix passes
+using SsSorter = cub::BlockRadixSort<unsigned long long, SS_THREADS, SS_ITEMS, uint32_t, 6>;
 __global__ void __launch_bounds__(SS_THREADS) k_tile_sort(const unsigned long long* __restrict__ in, uint32_t n, int end_bit,
                                                           unsigned long long* __restrict__ tile_keys, uint32_t* __restrict__ tile_idx) {
-    using Sorter = cub::BlockRadixSort<unsigned long long, SS_THREADS, SS_ITEMS, uint32_t, 6>;
-    __shared__ typename Sorter::TempStorage tmp;
+    using Sorter = SsSorter;
+    extern __shared__ __align__(16) unsigned char ss_smem[];      // sizeof(Sorter::TempStorage) exceeds the 48 KiB static limit
+    typename Sorter::TempStorage& tmp = *reinterpret_cast<typename Sorter::TempStorage*>(ss_smem);
     unsigned long long k[SS_ITEMS];
     uint32_t v[SS_ITEMS];
     const uint32_t base = blockIdx.x * SS_TILE + threadIdx.x * SS_ITEMS;
@@ -32,7 +34,7 @@ __global__ void __launch_bounds__(128) k_tile_rank(const unsigned long long* __r
     const uint32_t t0 = j / SS_TILE;
     const unsigned long long key = tile_keys[j];
     uint32_t r = j - t0 * SS_TILE;
-    // branch-free binary searches over the 2048 keys of each other tile, SS_GROUP tiles in lockstep so
+    // branch-free binary searches over the SS_TILE keys of each other tile, SS_GROUP tiles in lockstep so
     // that their (dependent) probes overlap: keys <= key in earlier tiles, keys < key in later ones
     for (uint32_t tb = 0; tb < n_tiles; tb += SS_GROUP) {
         uint32_t pos[SS_GROUP];

@@ -267,6 +267,7 @@ struct ResolveArgs {
     const uint32_t* tile_prefix;     // exclusive newline count before each tile of the scan
     uint32_t n_tiles;
     uint32_t tile_bytes;             // tile size of the scan that wrote tile_prefix
+    const uint16_t* span_counts;     // [n_tiles][16] newlines per 1 KiB span of a tile (k_fscan), or NULL
     const uint64_t* log_off;
     uint32_t n_logs;
     const uint32_t* line_start;
@@ -304,6 +305,21 @@ __global__ void __launch_bounds__(256) k_resolve(ResolveArgs a, DevPlan P) {
             // line of the occurrence: the newline prefix of its tile (and its neighbour) brackets the index
             const uint32_t t = s / a.tile_bytes;
             uint32_t glo = a.tile_prefix[t], ghi = (t + 1 < a.n_tiles ? a.tile_prefix[t + 1] : a.ctr->n_lines_total) + 1;
+            if (a.span_counts) {        // the scan also counted the newlines of every 1 KiB span: bracket the line within its span
+                const uint4* row = reinterpret_cast<const uint4*>(a.span_counts + (size_t)t * 16);
+                const uint4 c0 = __ldg(row), c1 = __ldg(row + 1);
+                const uint32_t cw[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+                const uint32_t w = (s - t * a.tile_bytes) >> 10;
+                uint32_t before = 0, mine = 0;
+#pragma unroll
+                for (int q = 0; q < 16; ++q) {
+                    const uint32_t v = (cw[q >> 1] >> ((q & 1) * 16)) & 0xFFFFu;
+                    before += (uint32_t)q < w ? v : 0u;
+                    mine = (uint32_t)q == w ? v : mine;
+                }
+                glo += before;
+                ghi = glo + mine + 1;
+            }
             if (a.n_logs > 1) {
                 glo += upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, (uint64_t)t * a.tile_bytes) - 1;
                 ghi += upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, (uint64_t)(t + 1) * a.tile_bytes);
@@ -437,7 +453,7 @@ __device__ __forceinline__ bool vm_eval(const DevPlan& P, uint32_t r, const uint
     v.n_slots = P.rx_vm_slots[r];
     v.first = P.rx_vm_first + (size_t)r * 8;
     const int res = lpx::vm_find(v, text, ls, le, stack, lpx::VM_STACK_WORDS, lpx::VM_MAX_STEPS);
-    if (res < 0) atomicOr(&ctr->overflow, 16u);
+    if (res < 0) { atomicOr(&ctr->overflow, 16u); atomicAdd(&ctr->n_budget, 1u); }
     return res > 0;
 }
 // LP_OPT_SPANS: Matcher.start()/end() of the first find() of each event's primary regex on its line.
@@ -460,7 +476,7 @@ __global__ void __launch_bounds__(128) k_spans(const unsigned long long* __restr
         v.first = P.rx_vm_first + (size_t)r * 8;
         uint32_t span[2] = {ls, ls};
         const int res = lpx::vm_find(v, text, ls, le, stack, lpx::VM_STACK_WORDS, lpx::VM_MAX_STEPS, span);
-        if (res < 0) atomicOr(&ctr_w->overflow, 16u);
+        if (res < 0) { atomicOr(&ctr_w->overflow, 16u); atomicAdd(&ctr_w->n_budget, 1u); }
         span_start[e] = res > 0 ? span[0] - ls : 0xFFFFFFFFu;     // the automaton said the line matches; a miss here would be a bug
         span_end[e] = res > 0 ? span[1] - ls : 0xFFFFFFFFu;
     }
@@ -531,6 +547,8 @@ struct DfaScanArgs {
     const uint8_t* rx_record;
     uint8_t* ctx_flags;
     int write_flags;             // 0 leave alone, 1 store every line's flag byte, 2 OR this launch's bits in
+    uint32_t skip1[8];           // first bytes on which every group of this launch is decided without a hit: such lines are not walked
+    const uint8_t* line_skip;    // [lines] 1 = k_fscan saw such a first byte while the text was in shared memory (NULL: look at the text here)
     unsigned long long* recs;
     uint32_t rec_cap;
     uint32_t gb;
@@ -584,8 +602,14 @@ __global__ void __launch_bounds__(DS_THREADS) k_dfa_scan(DfaScanArgs a) {
         const uint32_t k = a.n_logs == 1 ? 0 : upper_bound_dev<uint32_t>(a.first_line, a.n_logs + 1, g) - 1;
         const bool live = k < a.n_logs && g - a.first_line[k] < a.n_lines[k];
         uint32_t flags = 0;
+        bool walk = live;
+        uint32_t ls = 0, le = 0;
         if (live) {
-            const uint32_t ls = a.line_start[g], le = a.line_end[g];
+            ls = a.line_start[g]; le = a.line_end[g];
+            if (a.line_skip) walk = a.line_skip[g] == 0;
+            else if (le > ls) { const uint32_t b = a.text[ls]; walk = ((a.skip1[b >> 5] >> (b & 31u)) & 1u) == 0; }
+        }
+        if (walk) {
             LineWalker<NG, false> w;
 #pragma unroll
             for (int q = 0; q < NG; ++q) { w.cm[q] = cm[q]; w.T[q] = T[q]; w.nc[q] = nc[q]; w.ff[q] = ff[q]; w.st[q] = st0[q]; }

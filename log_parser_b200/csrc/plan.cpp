@@ -142,6 +142,23 @@ uint32_t run_group_blob(const std::vector<uint32_t>& blob, const uint8_t* s, siz
     return smask[T[st * nc + nc - 1]];
 }
 
+// Lines that the group's automaton rejects on their first byte (begin-anchored patterns: the stack-trace regex of CAS:31
+// dies on anything but white space or 'a') need not be walked, nor even read beyond that byte. The bytes that can start a
+// final line terminator (\r, U+0085, U+2028/9: the walker feeds a virtual symbol in front of them) are never skipped.
+void group_skip_set(const std::vector<uint32_t>& blob, uint32_t out[8]) {
+    const uint32_t ns = blob[0], nc = blob[1], ff = blob[3];
+    const uint8_t* cm = reinterpret_cast<const uint8_t*>(&blob[37]);
+    const uint32_t* smask = &blob[101];
+    const uint16_t* T = reinterpret_cast<const uint16_t*>(&blob[101 + ns]);
+    for (int w = 0; w < 8; ++w) out[w] = 0;
+    if (blob[2] >= ff) return;          // decided before the first byte: leave it to the walker
+    for (uint32_t b = 0; b < 256; ++b) {
+        if (b == '\r' || b == 0xC2 || b == 0xE2) continue;
+        const uint32_t st = T[blob[2] * nc + cm[b]];
+        if (st >= ff && smask[T[st * nc + nc - 1]] == 0) out[b >> 5] |= 1u << (b & 31);
+    }
+}
+
 void build_plan(const std::vector<PlanPatternIn>& pats, Plan& pl, int64_t* bad) {
     pl = Plan();
     if (bad) *bad = -1;
@@ -325,6 +342,7 @@ void build_plan(const std::vector<PlanPatternIn>& pats, Plan& pl, int64_t* bad) 
             Plan::ScanGroup g;
             g.rx = cur;
             serialise(cur, cur_dfa, g.blob);
+            group_skip_set(g.blob, g.skip1);
             total += g.blob.size() * 4;
             for (uint32_t r : cur) pl.rx_in_group[r] = 1;
             pl.groups.push_back(std::move(g));

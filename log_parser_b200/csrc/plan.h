@@ -60,6 +60,7 @@ struct Plan {
     struct ScanGroup {
         std::vector<uint32_t> rx;        // regex ids, bit k of the group's mask <-> rx[k]
         std::vector<uint32_t> blob;      // serialised tables (see k_dfa_scan)
+        uint32_t skip1[8] = {0, 0, 0, 0, 0, 0, 0, 0};   // bit b: a non-empty line whose first byte is b is decided, with no hit, after that byte
     };
     std::vector<ScanGroup> groups;
     std::vector<uint8_t> rx_in_group;    // 1: decided by a scan group
@@ -102,6 +103,8 @@ std::vector<PlanPatternIn> plan_input_from_desc(const lp_pattern_desc* pats, siz
 void build_plan(const std::vector<PlanPatternIn>& pats, Plan& out, int64_t* bad);
 void serialise_group(const std::vector<uint32_t>& rx, const MultiDfa& d, std::vector<uint32_t>& blob);
 uint32_t run_group_blob(const std::vector<uint32_t>& blob, const uint8_t* s, size_t n);
+// bit b set: from the start state, byte b leads to a final state whose hit mask is empty (group_first_byte_dead)
+void group_skip_set(const std::vector<uint32_t>& blob, uint32_t out[8]);
 // Re-picks the filter grams (optionally against a sample of real log text) and rebuilds the filter tables.
 void select_grams(Plan& pl, const uint8_t* sample, size_t sample_len);
 

@@ -188,6 +188,22 @@ def test_device_resident_equals_host_path(parser):
     assert t["kernel_launches"] > 5 and t["scan_ms"] > 0
 
 
+def test_backtracking_budget_degrades_to_a_count(parser):
+    """A (line, regex) evaluation that exhausts the verifier's step budget (catastrophic backtracking; java.util.regex
+    would keep going) no longer fails the request: the pair counts as no match and the result says how many evaluations
+    were abandoned. LP_OPT_STRICT_BUDGET brings the old behaviour (LP_ERR_BACKTRACK) back."""
+    pats = [PatternSpec(id="boom", primary_regex=r"(a+)+b\1", confidence=0.5), PatternSpec(id="plain", primary_regex="needle-here", confidence=0.5)]
+    log = b"aba\n" + b"a" * 48 + b"c\nxx needle-here\n"
+    parser.load_patterns(pats)
+    res = parser.analyze(log)
+    assert res.budget_exceeded >= 1
+    assert [(int(l), int(p)) for l, p in zip(res.line, res.pattern)] == [(1, 0), (3, 1)]
+    with pytest.raises(binding.LpError) as ei:
+        parser.analyze(log, options=binding.OPT_STRICT_BUDGET)
+    assert ei.value.code == binding.LP_ERR_BACKTRACK
+    assert parser.analyze(b"aba\nneedle-here\n").budget_exceeded == 0
+
+
 def test_c3_nonregular_patterns(parser, oracle):
     """configs[2] shape: look-around / back-reference / possessive+atomic primaries take the
     backtracking verifier on prefiltered candidate lines; results must still equal the oracle's."""
@@ -754,8 +770,9 @@ def test_random_regexes_with_literals_through_the_pipeline(parser, oracle):
 
 def test_concurrent_requests_from_threads(parser):
     """AnalysisService.analyze is called from several Quarkus worker threads at once (AS:35,50): calls on one
-    shared context serialise inside the library, calls on separate contexts overlap on the GPU; every
-    result must equal the single-threaded one, and results stay valid after later calls reused the buffers."""
+    shared context run on its workers (two by default, each with its own stream and scratch) and overlap on the
+    GPU, as do calls on separate contexts; every result must equal the single-threaded one, and results stay
+    valid after later calls reused the buffers."""
     import threading
 
     wl = synth.make_patterns(40, 3131, noliteral=1)

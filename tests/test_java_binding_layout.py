@@ -33,7 +33,7 @@ def test_pattern_desc_offsets_match():
 def test_result_view_and_cfg_offsets_match():
     src = open(JAVA).read()
     v = _offsets(binding.ResultView)
-    assert C.sizeof(binding.ResultView) == 128
+    assert C.sizeof(binding.ResultView) == 136 and v["budget_exceeded"] == 128 and "v.get(JAVA_LONG, 128)" in src
     for field, pat in {"n_events": r"v\.get\(JAVA_LONG, %d\)", "log_n_lines": r"v\.get\(ADDRESS, %d\)\.reinterpret\(8\)", "line": r"int\[\] line = v\.get\(ADDRESS, %d\)",
                        "pattern": r"int\[\] pat = v\.get\(ADDRESS, %d\)", "score": r"double\[\] score = v\.get\(ADDRESS, %d\)", "rank": r"int\[\] rank = v\.get\(ADDRESS, %d\)",
                        "freq_delta": r"long\[\] delta = v\.get\(ADDRESS, %d\)"}.items():

@@ -351,3 +351,36 @@ def test_scan_group_product_dfa_vs_oracle(lib, oracle):
             assert got < 0xFFFFFFF0, (regs, t, hex(got))
             exp = sum((1 << k) for k, o in enumerate(oracles) if o.find(t))
             assert got == exp, (regs, t, bin(got), bin(exp))
+
+
+def test_scan_group_first_byte_skip_set(oracle):
+    """k_dfa_scan does not walk a non-empty line whose first byte decides every regex of its groups without a hit
+    (the stack-trace regex of CAS:31 dies on anything but white space or 'a'): for every byte of the skip set, no
+    line that starts with it may match any regex of the group."""
+    import ctypes as C
+    import random
+
+    lib = binding.load_debug_library()
+    groups = [[r"^\s*at\s+[\w\.\$]+\(.*\)\s*$"], [r"^\s*at\s+[\w\.\$]+\(.*\)\s*$", r"^\d+ errors?$", r"^Caused by"],
+              [r"^\s*at\s+[\w\.\$]+\(.*\)\s*$", r"x\d"], [r"^$|^a"], [r"\Aabc\z", r"^ab*$"]]
+    rng = random.Random(8)
+    for regs in groups:
+        arr = (C.c_char_p * len(regs))(*[r.encode() for r in regs])
+        fl = (C.c_int * len(regs))(*([0] * len(regs)))
+        skip = (C.c_uint32 * 8)()
+        assert lib.lp_debug_group_skip(arr, fl, len(regs), skip) == 0
+        in_set = [b for b in range(256) if (skip[b >> 5] >> (b & 31)) & 1]
+        assert 13 not in in_set and 0xC2 not in in_set and 0xE2 not in in_set
+        if regs == groups[0]:
+            assert ord("2") in in_set and ord("C") in in_set and ord("\t") not in in_set and ord("a") not in in_set and ord(" ") not in in_set
+        if regs == groups[2]:
+            assert not in_set                      # an unanchored member keeps every line alive
+        ors = [oracle.Regex(r) for r in regs]
+        for b in in_set:
+            if b >= 0x80:
+                continue                            # keep the texts valid UTF-8
+            for _ in range(6):
+                t = chr(b) + "".join(rng.choice("at com.x.Y(Z.java:1) 123 errors\tCaused by\rabc$") for _ in range(rng.randint(0, 30)))
+                tb = t.encode()
+                assert lib.lp_debug_group_match(arr, fl, len(regs), tb, len(tb)) == 0, (regs, t)
+                assert not any(o.find(t) for o in ors), (regs, t)
