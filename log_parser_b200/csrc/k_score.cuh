@@ -49,20 +49,6 @@ __global__ void k_emit_events(const unsigned long long* __restrict__ keys, DevPl
         }
     }
 }
-__global__ void k_event_prep(const unsigned long long* __restrict__ ev_key, const Counters* ctr, uint32_t m_cap, DevPlan P,
-                             const uint32_t* __restrict__ first_line, uint32_t n_logs, uint32_t n_slots,
-                             uint32_t* __restrict__ ev_log, uint32_t* __restrict__ slot_key, uint32_t* __restrict__ ev_idx,
-                             unsigned long long* __restrict__ freq_delta) {
-    uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
-    if (e >= m_cap) return;
-    if (e >= ctr->n_events) { ev_log[e] = n_logs; slot_key[e] = n_slots; ev_idx[e] = e; return; }   // padding
-    const unsigned long long k = ev_key[e];
-    const uint32_t g = (uint32_t)(k >> P.pb), p = (uint32_t)(k & ((1ull << P.pb) - 1ull));
-    ev_log[e] = n_logs == 1 ? 0 : upper_bound_dev<uint32_t>(first_line, n_logs + 1, g) - 1;
-    slot_key[e] = P.pat_slot[p] < 0 ? n_slots : (uint32_t)P.pat_slot[p];     // untracked patterns sort after every slot
-    ev_idx[e] = e;
-    atomicAdd(&freq_delta[p], 1ull);
-}
 __global__ void k_log_event_begin(const unsigned long long* __restrict__ ev_key, const Counters* ctr, const uint32_t* __restrict__ first_line,
                                   uint32_t n_logs, uint32_t pb, unsigned long long* __restrict__ begin) {
     uint32_t k = blockIdx.x * blockDim.x + threadIdx.x;

@@ -489,10 +489,11 @@ def test_device_side_exchange_equals_one_batch(parser):
             lp.close()
 
 
-def test_piecewise_host_copy_equals_device_resident(parser):
+def test_piecewise_host_copy_equals_device_resident(parser, oracle):
     """lp_analyze on a log of more than 8 MB copies it in pieces on a second stream and scans each piece
     as it lands (after the prefilter has been calibrated by a first call): same result as the
-    device-resident path, including candidates that straddle a cut."""
+    device-resident path, including candidates that straddle a cut, and both equal to the oracle
+    (Parse.java:44 -> AnalysisService.java:53 is one host string there)."""
     import torch
 
     wl = synth.make_patterns(60, 909, noliteral=1)
@@ -510,6 +511,62 @@ def test_piecewise_host_copy_equals_device_resident(parser):
         np.testing.assert_array_equal(r.score, resident.score)
         np.testing.assert_array_equal(r.rank, resident.rank)
     assert parser.timings()["kernel_launches"] > 0
+    ora = oracle.analyze(ScoringConfig(), wl.patterns, log)
+    _check(second, ora, check_factors=False)
+    np.testing.assert_array_equal(second.score, ora.score)
+
+
+def test_service_analyze_on_device_equals_oracle_fed_assembly(tmp_path, oracle):
+    """SURVEY §8f N1+N2 through the GPU: a YAML pattern directory and a PodFailureData-shaped dict go through
+    service.AnalysisService.analyze (lp_analyze underneath); the whole AnalysisResult (events with their
+    context strings, metadata.totalLines / patternsUsed, summary) equals the assembly fed with the oracle's
+    columns (AnalysisService.java:53-121, 132-156, 166-215). A second request sees the first one's
+    frequency state (FrequencyTrackingService.java:41-93)."""
+    import yaml
+
+    from log_parser_b200 import patterns, service
+
+    set_a = {"metadata": {"library_id": "lib-a"}, "patterns": [
+        {"id": "oom", "name": "OOM", "severity": "critical", "primary_pattern": {"regex": "OutOfMemoryError", "confidence": 0.9},
+         "secondary_patterns": [{"regex": "GC overhead", "weight": 0.6, "proximity_window": 20}],
+         "sequence_patterns": [{"description": "heap grows", "bonus_multiplier": 0.3, "events": [{"regex": "heap"}, {"regex": "OutOfMemory"}]}],
+         "context_extraction": {"lines_before": 1, "lines_after": 2, "include_stack_trace": True}},
+        {"id": "warn", "name": "Warn", "severity": "LOW", "primary_pattern": {"regex": "\\bWARN\\b", "confidence": 0.4}},
+        {"id": "uni", "name": "Unicode word", "severity": "medium", "primary_pattern": {"regex": "\\p{Lu}\\p{L}+Exception", "confidence": 0.7},
+         "context_extraction": {"lines_before": 2, "lines_after": 0}}]}
+    set_b = {"metadata": {"library_id": "lib-b"}, "patterns": [
+        {"id": "odd", "name": "Odd", "severity": "weird", "primary_pattern": {"regex": "^x$", "confidence": 0.5},
+         "context_extraction": {"lines_before": 0, "lines_after": 0}}]}
+    (tmp_path / "a.yml").write_text(yaml.safe_dump(set_a))
+    (tmp_path / "b.yaml").write_text(yaml.safe_dump(set_b))
+    sets = patterns.load_pattern_directory(str(tmp_path))
+    assert len(sets) == 2
+    rng = random.Random(77)
+    filler = ["INFO request served", "heap usage 71%", "WARN slow call", "x", "java.lang.OutOfMemoryError: GC overhead limit exceeded",
+              "\tat com.example.Svc.run(Svc.java:42)", "Ünexpected ÉtatException raised", "", "WARNING not a word match", "GC overhead high"]
+    body = [rng.choice(filler) for _ in range(400)]
+    logs = "\r\n".join(body[:200]) + "\n" + "\n".join(body[200:]) + "\n\n"
+    now = [1_000_000.0]
+    svc = service.AnalysisService(sets, clock=lambda: now[0])
+    specs, raw = patterns.flatten(sets)
+    prior = np.zeros(len(specs), np.uint64)
+    for request in range(2):
+        got = svc.analyze({"podName": "p", "logs": logs})
+        ora = oracle.analyze(ScoringConfig(), specs, logs.encode("utf-8"), prior_count=prior)
+        assert len(ora.line) > 50
+        exp = service.assemble_result(ora.line, ora.pattern, ora.score, logs, raw, sets, 0.0, ora.n_lines)
+        assert got["metadata"]["totalLines"] == exp["metadata"]["totalLines"]
+        assert got["metadata"]["patternsUsed"] == exp["metadata"]["patternsUsed"]
+        assert got["summary"] == exp["summary"]
+        assert len(got["events"]) == len(exp["events"])
+        for g, e in zip(got["events"], exp["events"]):
+            assert g["lineNumber"] == e["lineNumber"] and g["matchedPattern"] == e["matchedPattern"] and g["context"] == e["context"]
+            assert abs(g["score"] - e["score"]) <= REL_TOL * abs(e["score"])
+        assert {k: v for k, v in svc.freq.get_frequency_stats().items()} == \
+               {s.id: int(prior[i] + ora.freq_delta[i]) for i, s in enumerate(specs) if prior[i] + ora.freq_delta[i] > 0}
+        prior = prior + ora.freq_delta.astype(np.uint64)
+        now[0] += 60.0
+    svc.parser.close()
 
 
 def test_match_spans_equal_oracle(parser, oracle):
