@@ -151,9 +151,10 @@ struct lp_ctx {
     uint32_t n_group_record_rx = 0;
     DevBuf f_bitmap, f_key, f_lits, f_bytes;   // prefilter tables (re-uploaded by calibration)
     DevBuf line_skip;                          // per line: the always-on scan need not walk it (written by k_expand)
-    DevBuf f_bits, f_gkeys, fs_state, fs_lists; // fused scan: first-stage bit table, exact gram keys, ticket counters, per-tile newline lists
+    DevBuf f_bits, f_gkeys, fs_lists;           // fused scan: first-stage bit table, exact gram keys, per-span newline counts and lists
     const uint8_t* d_byte_table = nullptr;
     int scan_mode = 0;                         // 0: fused single-pass scan (k_fscan); 1: k_filter_count + k_scan_tiles + k_lines (LP_SCAN_MODE=legacy)
+    uint32_t f_mul = fs::MUL1;                 // first-stage hash multiplier of k_fscan (pick_multiplier)
     int fscan_variant = 0;                     // first-stage lookup of k_fscan: 0 IMAD.HI hash, 1 IMAD+SHF hash, 2 byte table (LP_FSCAN_VARIANT)
     std::vector<uint32_t> lit_off8;   // literal -> offset in the 8-byte aligned device copy of the literal bytes
     bool calibrated = false;
@@ -231,8 +232,8 @@ void upload_filter(lp_ctx* c) {
     if (c->fscan_variant != 2) {   // k_fscan: one bit per gram at (row, rotation - 1) of the per-lane table; every lane's copy is the same
         std::vector<uint32_t> bits(fs::ROWS, 0);
         for (uint32_t key : pl.table_key) if (key) {
-            const uint32_t H = fs::host_hash(c->fscan_variant, key);
-            bits[(H >> 7) & (fs::ROWS - 1)] |= 1u << ((H + 31u) & 31u);
+            const uint32_t H = fs::host_hash(c->fscan_variant, key, c->f_mul);
+            bits[fs::host_row(H)] |= 1u << ((H + 31u) & 31u);
         }
         upload_into(c->f_bits, bits);
     }
@@ -259,6 +260,43 @@ void upload_filter(lp_ctx* c) {
     d.gram_slots = upload_into(c->f_key, slots);
     d.lit_desc = upload_into(c->f_lits, descs);
 }
+// The first-stage table of k_fscan holds one bit per gram at a place given by one multiplicative hash, so a window
+// of the log that is no gram passes it when its hash lands on a set bit. The 4-byte windows of log text are few and
+// heavily repeated; among 256 odd multipliers the one whose set bits are hit by the least sampled text wins (the
+// mass of false first-stage hits varies several-fold between multipliers). Results never depend on the choice: every
+// first-stage hit is checked against the exact gram keys.
+void pick_multiplier(lp_ctx* c, const std::vector<uint8_t>& sample) {
+    c->f_mul = fs::MUL1;
+    if (c->fscan_variant == 2 || sample.size() < 4096) return;
+    const size_t n = std::min<size_t>(sample.size(), (size_t)1 << 20) - 3;
+    std::vector<uint32_t> grams(n);
+    for (size_t i = 0; i < n; ++i)
+        grams[i] = ((uint32_t)sample[i] | ((uint32_t)sample[i + 1] << 8) | ((uint32_t)sample[i + 2] << 16) | ((uint32_t)sample[i + 3] << 24)) | 0x20202020u;
+    std::sort(grams.begin(), grams.end());
+    std::vector<uint32_t> keys;
+    for (uint32_t k : c->plan.table_key) if (k) keys.push_back(k);
+    std::sort(keys.begin(), keys.end());
+    std::vector<std::pair<uint32_t, uint32_t>> text;      // distinct windows of the sample that are no gram, with their counts
+    for (size_t i = 0; i < n;) {
+        size_t j = i;
+        while (j < n && grams[j] == grams[i]) ++j;
+        if (!std::binary_search(keys.begin(), keys.end(), grams[i])) text.emplace_back(grams[i], (uint32_t)(j - i));
+        i = j;
+    }
+    uint64_t best = ~0ull;
+    std::vector<uint32_t> bits(fs::ROWS);
+    uint32_t m = fs::MUL1;
+    for (int trial = 0; trial < 256; ++trial, m = (m * 0x2C1B3C6Du + 0x297A2D39u) | 1u) {
+        std::fill(bits.begin(), bits.end(), 0u);
+        for (uint32_t k : keys) { const uint32_t H = fs::host_hash(c->fscan_variant, k, m); bits[fs::host_row(H)] |= 1u << ((H + 31u) & 31u); }
+        uint64_t mass = 0;
+        for (const auto& g : text) {
+            const uint32_t H = fs::host_hash(c->fscan_variant, g.first, m);
+            if ((bits[fs::host_row(H)] >> ((H + 31u) & 31u)) & 1u) mass += g.second;
+        }
+        if (mass < best) { best = mass; c->f_mul = m; }
+    }
+}
 // One-time tuning of the literal prefilter against the first log this context sees: 4 x 1 MiB of
 // its text decide which 4-byte window of each literal is the rarest. Results never depend on it.
 void calibrate_filter(lp_ctx* c, const uint8_t* d_text, uint64_t len) {
@@ -276,6 +314,7 @@ void calibrate_filter(lp_ctx* c, const uint8_t* d_text, uint64_t len) {
     }
     CK(cudaStreamSynchronize(c->stream));
     lpx::select_grams(c->plan, sample.data(), sample.size());
+    pick_multiplier(c, sample);
     upload_filter(c);
     c->calibrated = true;
 }
@@ -523,19 +562,15 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     CK(cudaMemsetAsync(ctr, 0, sizeof(Counters), st));
     CK(cudaEventRecord(c->ev[0], st));
     const size_t smem = use_filter ? 65536 : 0;
-    constexpr uint32_t FS_TICKETS = 32;
     FscanArgs fz{};
     if (fused) {
-        // one ticket counter per launch of this call (a log arriving from the host is scanned piece by piece)
-        c->fs_state.ensure(FS_TICKETS * 4);
-        CK(cudaMemsetAsync(c->fs_state.p, 0, FS_TICKETS * 4, st));
         // per tile: 16 span counts, then per tile 16 lists of fs::WLIST entries
         c->fs_lists.ensure((size_t)n_tiles * 16 * 2 + (size_t)n_tiles * 16 * fs::WLIST * 2);
         fz.text = d_text; fz.len = len; fz.n_tiles = n_tiles;
-        fz.tma_tiles = len >= fs::TILE + fs::HALO ? (uint32_t)((len - fs::HALO) / fs::TILE) : 0u;
-        fz.tile_counts = c->tile_counts.as<uint32_t>();
         fz.warp_counts = c->fs_lists.as<uint16_t>();
         fz.nl_lists = c->fs_lists.as<uint16_t>() + (size_t)n_tiles * 16;
+        fz.mul = c->f_mul;
+        { const uint32_t kk[8] = {1u, 1024u, 128u, 1u << 25, 1u << 26, 1u << 27, 1u << 28, 1u << 15}; for (int q = 0; q < 8; ++q) fz.k[q] = kk[q]; }
         fz.bit_table = c->fscan_variant == 2 ? reinterpret_cast<const uint32_t*>(c->d_byte_table) : c->f_bits.as<uint32_t>();
         fz.gram_keys = c->f_gkeys.as<uint32_t>(); fz.table_bits = c->dp.table_bits;
         fz.cand = c->cand.as<uint32_t>(); fz.cand_cap = (uint32_t)std::min<size_t>(c->est_cand, 0xFFFFFFFFu); fz.ctr = ctr;
@@ -545,16 +580,17 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         for (const auto& g : c->plan.groups) for (int w = 0; w < 8; ++w) fz.skip1[w] &= g.skip1[w];
         c->line_skip.ensure(line_cap + 16);
     }
-    uint32_t fs_launches = 0;
     auto launch_fscan = [&](uint32_t tile_begin, uint32_t tile_end) {
-        if (fs_launches >= FS_TICKETS) throw std::logic_error("too many scan launches in one call");
-        fz.tile_begin = tile_begin; fz.tile_end = tile_end; fz.ticket = c->fs_state.as<uint32_t>() + fs_launches++;
-        const uint32_t grid = std::max<uint32_t>(1, std::min<uint32_t>((tile_end - tile_begin + 1) / 2, (uint32_t)c->n_sm));
+        fz.tile_begin = tile_begin; fz.tile_end = tile_end;
+        // one CTA (32 warps, a pipeline each) per SM; fewer when the piece has less than one span per warp
+        const uint32_t grid = std::max<uint32_t>(1, std::min<uint32_t>(((tile_end - tile_begin) * fs::SPANS + 31) / 32, (uint32_t)c->n_sm));
         switch (c->fscan_variant) {
             case 1: k_fscan<1><<<grid, fs::THREADS, fs::SMEM_BYTES, st>>>(fz); break;
             case 2: k_fscan<2><<<grid, fs::THREADS, fs::SMEM_BYTES, st>>>(fz); break;
+            case 3: k_fscan<3><<<grid, fs::THREADS, fs::SMEM_BYTES, st>>>(fz); break;
             default: k_fscan<0><<<grid, fs::THREADS, fs::SMEM_BYTES, st>>>(fz); break;
         }
+        CK(cudaGetLastError());
     };
     FilterArgs fa{};
     fa.text = d_text; fa.len = len; fa.n_tiles = n_tiles; fa.tile_counts = c->tile_counts.as<uint32_t>(); fa.bitmap = c->dp.bitmap; fa.byte_table = c->d_byte_table;
@@ -596,7 +632,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     CK(cudaMemsetAsync(c->ev_key_alt.p, 0xFF, ev_cap * 8, st));
     if (has_vm) CK(cudaMemsetAsync(c->vm_tasks.p, 0xFF, c->est_vm_tasks * 8, st));      // padding sorts behind the tasks
     if (!c->plan.ctx_any_in_groups) CK(cudaMemsetAsync(c->ctx_flags.p, 0, (line_cap / 4 + 2) * 4, st));   // else k_dfa_scan writes every byte
-    k_scan_tiles<<<1, 1024, 0, st>>>(c->tile_counts.as<uint32_t>(), n_tiles, n_logs, ctr);
+    k_scan_tiles<<<1, 1024, 0, st>>>(c->tile_counts.as<uint32_t>(), fused ? c->fs_lists.as<uint16_t>() : nullptr, n_tiles, n_logs, ctr);
     if (fused) {
         ExpandArgs ea{};
         ea.text = d_text; ea.len = len; ea.n_tiles = n_tiles; ea.tile_prefix = c->tile_counts.as<uint32_t>(); ea.warp_counts = c->fs_lists.as<uint16_t>(); ea.nl_lists = c->fs_lists.as<uint16_t>() + (size_t)n_tiles * 16;
@@ -1032,7 +1068,7 @@ static lp_ctx* create_worker(const lp_scoring_cfg* cfg, int device) {
     CK(cudaGetDeviceProperties(&prop, device));
     ctx->n_sm = prop.multiProcessorCount;
     if (const char* m = getenv("LP_SCAN_MODE")) ctx->scan_mode = strcmp(m, "legacy") == 0 ? 1 : 0;
-    if (const char* v = getenv("LP_FSCAN_VARIANT")) ctx->fscan_variant = std::max(0, std::min(2, atoi(v)));
+    if (const char* v = getenv("LP_FSCAN_VARIANT")) ctx->fscan_variant = std::max(0, std::min(3, atoi(v)));
     std::vector<double> lut((size_t)cfg->max_window + 1);
     for (int d = 0; d <= cfg->max_window; ++d)
         lut[d] = cfg->decay_lut ? cfg->decay_lut[d] : std::exp(-(double)d / cfg->decay_constant);   // SS:177
@@ -1060,6 +1096,7 @@ lp_ctx* lp_create(const lp_scoring_cfg* cfg, int device) {
         CK(cudaFuncSetAttribute(k_fscan<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs::SMEM_BYTES));
         CK(cudaFuncSetAttribute(k_fscan<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs::SMEM_BYTES));
         CK(cudaFuncSetAttribute(k_fscan<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs::SMEM_BYTES));
+        CK(cudaFuncSetAttribute(k_fscan<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs::SMEM_BYTES));
         CK(cudaFuncSetAttribute(k_tile_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SsSorter::TempStorage)));
         CK(cudaFuncSetAttribute(k_dfa_scan<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
         CK(cudaFuncSetAttribute(k_dfa_scan<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
@@ -1087,7 +1124,7 @@ void lp_destroy(lp_ctx* c) {
                      &c->ev_log, &c->slot_key, &c->slot_key_alt, &c->ev_idx, &c->ev_idx_alt, &c->rank_in_slot, &c->freq_delta, &c->prior,
                      &c->out_arena, &c->sort_key, &c->sort_key_alt, &c->order, &c->order_alt,
                      &c->log_sorted, &c->log_sorted_alt, &c->log_event_begin, &c->n_unique, &c->d_lut,
-                     &c->f_bitmap, &c->f_key, &c->f_lits, &c->f_bytes, &c->f_bits, &c->f_gkeys, &c->fs_state, &c->fs_lists, &c->line_skip, &c->items, &c->ss_keys, &c->ss_idx, &c->seq_tab_off, &c->seq_tab, &c->seq_T, &c->prior_eff, &c->any_flag, &c->dist_mine, &c->dist_all};
+                     &c->f_bitmap, &c->f_key, &c->f_lits, &c->f_bytes, &c->f_bits, &c->f_gkeys, &c->fs_lists, &c->line_skip, &c->items, &c->ss_keys, &c->ss_idx, &c->seq_tab_off, &c->seq_tab, &c->seq_T, &c->prior_eff, &c->any_flag, &c->dist_mine, &c->dist_all};
     for (DevBuf* b : all) b->release();
     if (c->nccl_comm) nccl_comm_destroy(c->nccl_comm);
     c->stage.release();
@@ -1110,6 +1147,7 @@ int lp_load_patterns(lp_ctx* c, const lp_pattern_desc* pats, size_t n, int64_t* 
         c->loaded = false;
         c->calibrated = false;
         c->recalibrations = 0;
+        c->f_mul = fs::MUL1;
         lpx::build_plan(in, c->plan, bad_pattern);
         upload_plan(c);
         // line-range shards: where each sequence's chain table sits in a shard summary
@@ -1123,7 +1161,7 @@ int lp_load_patterns(lp_ctx* c, const lp_pattern_desc* pats, size_t n, int64_t* 
         c->loaded = true;
         for (lp_ctx* e : c->extra) {       // the other workers get their own copy of the (small) tables
             std::lock_guard<std::mutex> le(e->mu);
-            e->loaded = false; e->calibrated = false; e->recalibrations = 0;
+            e->loaded = false; e->calibrated = false; e->recalibrations = 0; e->f_mul = fs::MUL1;
             e->plan = c->plan;
             upload_plan(e);
             e->n_seq = c->n_seq; e->h_seq_tab_off = c->h_seq_tab_off;

@@ -2,55 +2,65 @@
 // N x P find() loop (AS:89-95) in ONE pass over the log. Replaces k_filter_count + k_scan_tiles + k_lines.
 // Part of engine.cu's translation unit (included inside its anonymous namespace); not a stand-alone header.
 //
-// Shape: one CTA of 1024 threads per SM, split into two independent halves of 512 threads. A half owns a
-// two-stage ring of 16 KiB log tiles in shared memory, filled by 1-D TMA bulk copies
-// (cp.async.bulk ... mbarrier::complete_tx; the source is always this GPU's own memory) while the
-// other tile is being worked on, so the bytes in flight do not depend on registers. Tiles are handed
-// out by a ticket counter, which also makes the look-back below deadlock-free.
+// Shape: one CTA of 1024 threads per SM; every warp is a pipeline of its own. A warp owns two buffers of one
+// 1 KiB span (+ 16 bytes of halo) of the log in shared memory, filled by 1-D TMA bulk copies
+// (cp.async.bulk ... mbarrier::complete_tx; the source is always this GPU's own memory) while the warp works on
+// the other one, so the bytes in flight do not depend on registers. Spans are dealt round-robin to the warps of
+// the grid. After the first-stage table has been loaded there is no barrier between warps at all: the table
+// lookups of one warp (integer-ALU bound) overlap the sparse, latency-bound loops of another. (Two earlier
+// shapes, 16-KiB tiles shared by 16 warps behind a barrier or behind a last-arriver counter, lost 13-25 % of
+// the issue slots to waiting: profiles/r02_fscan_spanlists_* and r02_fscan_lastarriver_*.)
 //
-// Per tile, a thread owns 32 contiguous bytes:
+// Per span, a lane owns 32 contiguous bytes:
 //   phase A  newline mask by SWAR, and for each of its 32 positions one lookup of the 4-byte window in the
 //            first-stage gram table. The table is a bit table replicated per lane: row = hash bits, the
 //            word of lane L lives in bank L, so the 32 lookups of a warp never conflict (the byte table of
 //            k_filter_count lost 55 % of its shared-memory wavefronts to bank conflicts). The wanted bit
 //            is rotated to bit 31 and funnel-shifted into the hit mask: 6 instructions per position.
-//   phase B  one block scan of (newlines, hits) per tile; the set bits are compacted into two lists in
-//            shared memory so that the sparse work runs with full warps: first-stage hits are checked
-//            against the exact gram key table (windows re-read from the staged tile) and survivors go to
-//            the candidate queue with one global atomic per tile; newlines become line_end[g] /
-//            line_start[g+1] at the global line index given by a decoupled look-back over the tiles'
-//            newline counts (single pass: no second read of the log for the offsets).
+//   phase B  newlines: one warp scan; position | first-byte skip flag | '\r' flag of every newline goes, in
+//            order, to the warp span's slot of the tile's newline lists (k_expand turns the lists into
+//            line_start / line_end after k_scan_tiles has summed and scanned the spans' counts: the log is not read
+//            again for the offsets). First-stage hits are checked against the exact gram keys (shared
+//            memory when they fit; windows re-read from the staged span); survivors collect in the warp's
+//            list and go to the candidate queue with one global atomic per ~32 of them.
 namespace fs {
-constexpr int HALF = 512, THREADS = 1024;
-constexpr uint32_t TILE = 16384, HALO = 16, STAGE_BYTES = 16512;      // tile + halo, rounded up to 128
+constexpr int THREADS = 1024;
+constexpr uint32_t TILE = 16384, HALO = 16;                          // a tile is the unit of the newline prefix (k_scan_tiles, k_expand)
+constexpr uint32_t SPAN = 1024, SPANS = TILE / SPAN;                 // a span is what one warp stages and scans at a time: 32 bytes per lane
+constexpr uint32_t SPAN_STRIDE = 1152;                               // span + halo, rounded up to 128
 constexpr uint32_t ROWS = 1024;                                      // first-stage table rows (one word per lane and row)
-constexpr uint32_t LIST = 1024;                                      // entries per compaction list and pass
 constexpr uint32_t MUL1 = 0x9E3779B1u;
 constexpr size_t TABLE_BYTES = (size_t)ROWS * 128;
-constexpr uint32_t WLIST = 64;                                       // newline list entries per warp (1 KiB of log) and tile
-constexpr uint32_t OUT_CAP = 1024;                                   // survivors staged per half and tile
+constexpr uint32_t WLIST = 64;                                       // newline list entries per span
+constexpr uint32_t OUT_CAP = 64;                                     // survivors staged per warp
 constexpr uint32_t KEY_BYTES = 8192;                                 // exact gram keys kept in shared memory when 4 << table_bits fits
-constexpr size_t HALF_BYTES = 2 * STAGE_BYTES + 2 * OUT_CAP * 4 + 256;   // stages, survivors (two tiles), state
-constexpr size_t SMEM_BYTES = TABLE_BYTES + KEY_BYTES + 2 * HALF_BYTES;
+constexpr size_t WARP_BYTES = 2 * SPAN_STRIDE + OUT_CAP * 4 + 128;   // two span buffers, survivors, state
+constexpr size_t SMEM_BYTES = TABLE_BYTES + KEY_BYTES + (THREADS / 32) * WARP_BYTES;
 
-// row = (H >> 7) & (ROWS - 1), rotation = H & 31; the table bit of a gram is bit (rotation - 1) & 31
+// row = (H >> 7) & (ROWS - 1), rotation = H & 31; the table bit of a gram is bit (rotation - 1) & 31.
+// `mul` is an odd multiplier picked per pattern set (and per first log, see pick_multiplier in engine.cu);
+// MUL1 is the default.
 template <int V>
-__host__ __device__ __forceinline__ uint32_t hash(uint32_t folded) {
+__host__ __device__ __forceinline__ uint32_t hash(uint32_t folded, uint32_t mul) {
 #ifdef __CUDA_ARCH__
-    if (V == 0) return __umulhi(folded, MUL1);
+    if (V == 0) return __umulhi(folded, mul);
 #else
-    if (V == 0) return (uint32_t)(((unsigned long long)folded * MUL1) >> 32);
+    if (V == 0) return (uint32_t)(((unsigned long long)folded * mul) >> 32);
 #endif
-    return (folded * MUL1) >> 15;
+    return (folded * mul) >> 15;
 }
-inline uint32_t host_hash(int variant, uint32_t folded) { return variant == 0 ? hash<0>(folded) : hash<1>(folded); }
+inline uint32_t host_hash(int variant, uint32_t folded, uint32_t mul) { return variant == 1 ? hash<1>(folded, mul) : hash<0>(folded, mul); }
+// table row of a hash: bits 7..16 (the middle bits of the 64-bit product are the well-mixed ones; its top ten bits
+// follow the window's last byte and gave four times the false hits). Variants 0/1 mask them in place (one LOP3
+// builds the address); variant 3 isolates them with multiplies (H * 2^15, IMAD.HI by 1024, IMAD by 128 plus the
+// lane's offset): the FMA pipe, which has slack, instead of the ALU pipe, which is the bound.
+inline uint32_t host_row(uint32_t H) { return (H >> 7) & (ROWS - 1); }
 
-struct HalfState {
-    unsigned long long bar[2];      // mbarriers of the two stages
-    uint32_t tile[2];               // tile index loaded (or to be filled) into each stage
-    uint32_t ncand[2], n_nl[2];     // survivors and newlines of the tile in each stage
+struct WarpState {
+    unsigned long long bar[2];      // mbarriers of the warp's two span buffers
+    uint32_t ncand;                 // survivors waiting in the warp's list
 };
-static_assert(sizeof(HalfState) <= 256, "HalfState must fit its slot");
+static_assert(sizeof(WarpState) <= 128, "WarpState must fit its slot");
 }  // namespace fs
 
 struct FscanArgs {
@@ -58,14 +68,13 @@ struct FscanArgs {
     uint64_t len;
     uint32_t n_tiles;                 // tiles of the whole text (the last one covers position `len`)
     uint32_t tile_begin, tile_end;    // this launch's tiles (a log arriving from the host is scanned piece by piece)
-    uint32_t* ticket;                 // zeroed counter of this launch
-    uint32_t tma_tiles;               // tiles [0, tma_tiles) lie, with their halo, inside the text: loaded by bulk copy
-    uint32_t* tile_counts;            // [n_tiles] out: newlines per tile (k_scan_tiles turns them into prefixes)
     uint16_t* warp_counts;            // [n_tiles][16] out: newlines per 1 KiB warp span; above fs::WLIST the span's list was not written
     uint16_t* nl_lists;               // [n_tiles][16][fs::WLIST] out: the newlines of each warp span, see k_expand
     const uint32_t* bit_table;        // fs::ROWS words (variants 0/1) or the 64 KiB byte table (variant 2)
     const uint32_t* gram_keys;        // 2^table_bits folded grams, 0 = empty
     uint32_t table_bits;
+    uint32_t mul;                     // first-stage hash multiplier (fs::hash)
+    uint32_t k[8];                    // variant 3: {1, 1024, 128, 1<<25, 1<<26, 1<<27, 1<<28, 1<<15}, passed as arguments so that ptxas keeps the multiplies (FMA pipe) instead of turning them into shifts and adds (ALU pipe, the kernel's bound)
     uint32_t* cand;
     uint32_t cand_cap;
     Counters* ctr;
@@ -74,7 +83,6 @@ struct FscanArgs {
 };
 
 __device__ __forceinline__ uint32_t fs_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void fs_half_sync(int half) { asm volatile("bar.sync %0, %1;" ::"r"(1 + half), "n"(fs::HALF) : "memory"); }
 __device__ __forceinline__ void fs_mbar_init(void* bar, uint32_t count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(fs_smem_u32(bar)), "r"(count) : "memory");
 }
@@ -93,7 +101,9 @@ __device__ __forceinline__ void fs_tma_load(void* dst, const void* src, uint32_t
     asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                  ::"r"(fs_smem_u32(dst)), "l"(__cvta_generic_to_global(src)), "r"(bytes), "r"(fs_smem_u32(bar)) : "memory");
 }
-__device__ __forceinline__ bool fs_tma_ok(uint32_t tile, uint64_t len) { return (uint64_t)tile * fs::TILE + fs::TILE + fs::HALO <= len; }
+__device__ __forceinline__ void fs_mbar_arrive(void* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(fs_smem_u32(bar)) : "memory");
+}
 
 // Bit 7 of each byte: set iff that byte of w is '\n' (exact). (y - 0x01..) & ~y flags zero bytes of y, and, through
 // the borrow, a byte 0x01 that follows one; bit 0 of such a byte (y << 7) clears the false flag. Bits other
@@ -111,6 +121,18 @@ __device__ __forceinline__ uint32_t fs_nl_spread(const uint4& v) {
     return ((fs_nl_flags_raw(v.x) >> 7) & 0x01010101u) | ((fs_nl_flags_raw(v.y) >> 6) & 0x02020202u) |
            ((fs_nl_flags_raw(v.z) >> 5) & 0x04040404u) | ((fs_nl_flags_raw(v.w) >> 4) & 0x08080808u);
 }
+// the same with the subtraction and the right shifts as multiplies by kernel arguments (k[0] = 1, k[3..6] = 2^25..2^28)
+__device__ __forceinline__ uint32_t fs_nl_flags_fma(uint32_t w, uint32_t one) {
+    const uint32_t y = w ^ 0x0A0A0A0Au;
+    uint32_t t, u;
+    asm("mad.lo.u32 %0, %1, %2, 0xFEFEFEFF;" : "=r"(t) : "r"(y), "r"(one));
+    asm("mul.lo.u32 %0, %1, 128;" : "=r"(u) : "r"(y));
+    return t & ~y & ~u;
+}
+__device__ __forceinline__ uint32_t fs_nl_spread_fma(const uint4& v, const uint32_t (&k)[8]) {
+    return (__umulhi(fs_nl_flags_fma(v.x, k[0]), k[3]) & 0x01010101u) | (__umulhi(fs_nl_flags_fma(v.y, k[0]), k[4]) & 0x02020202u) |
+           (__umulhi(fs_nl_flags_fma(v.z, k[0]), k[5]) & 0x04040404u) | (__umulhi(fs_nl_flags_fma(v.w, k[0]), k[6]) & 0x08080808u);
+}
 // With two 16-byte chunks packed as lo | hi << 4, bit b stands for byte 4 (b & 7) + (b >> 3) of the 32 bytes.
 // Mask of the packed bits whose byte position is below x (0..32).
 __device__ __forceinline__ uint32_t fs_below(uint32_t x) {
@@ -120,7 +142,7 @@ __device__ __forceinline__ uint32_t fs_below(uint32_t x) {
 
 // first-stage lookups of the 16 windows starting in one 16-byte chunk; w4 = the word that follows the chunk
 template <int V>
-__device__ __forceinline__ uint32_t fs_probe16(const uint4& v, uint32_t w4, const uint8_t* __restrict__ tab, uint32_t lane4) {
+__device__ __forceinline__ uint32_t fs_probe16(const uint4& v, uint32_t w4, const uint8_t* __restrict__ tab, uint32_t lane4, uint32_t mul, const uint32_t (&k)[8]) {
     const uint32_t w[5] = {v.x | 0x20202020u, v.y | 0x20202020u, v.z | 0x20202020u, v.w | 0x20202020u, w4 | 0x20202020u};
     uint32_t acc = 0;
 #pragma unroll
@@ -128,8 +150,12 @@ __device__ __forceinline__ uint32_t fs_probe16(const uint4& v, uint32_t w4, cons
         const uint32_t win = (i & 3) ? __funnelshift_r(w[i >> 2], w[(i >> 2) + 1], (i & 3) * 8) : w[i >> 2];
         if (V == 2) {
             acc = acc * 2u + tab[(win * GRAM_MUL) >> 16];
+        } else if (V == 3) {
+            const uint32_t H = __umulhi(win, mul);
+            const uint32_t word = *reinterpret_cast<const uint32_t*>(tab + (__umulhi(H * k[7], k[1]) * k[2] + lane4));
+            acc = __funnelshift_l(__funnelshift_r(word, word, H), acc, 1);
         } else {
-            const uint32_t H = fs::hash<V>(win);
+            const uint32_t H = fs::hash<V>(win, mul);
             const uint32_t word = *reinterpret_cast<const uint32_t*>(tab + ((H & ((fs::ROWS - 1u) << 7)) | lane4));
             acc = __funnelshift_l(__funnelshift_r(word, word, H), acc, 1);      // table bit -> bit 31 -> shifted into the mask
         }
@@ -140,24 +166,44 @@ __device__ __forceinline__ uint32_t fs_probe16(const uint4& v, uint32_t w4, cons
 template <int V>
 __global__ void __launch_bounds__(fs::THREADS, 1) k_fscan(FscanArgs a) {
     extern __shared__ __align__(128) uint8_t fs_smem[];
-    const int half = threadIdx.x >> 9, t = threadIdx.x & (fs::HALF - 1), lane = t & 31, warp = t >> 5;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t* const s_keys = reinterpret_cast<uint32_t*>(fs_smem + fs::TABLE_BYTES);          // exact gram keys (when they fit)
-    uint8_t* const hbase = fs_smem + fs::TABLE_BYTES + fs::KEY_BYTES + (size_t)half * fs::HALF_BYTES;
-    uint8_t* const stages = hbase;
-    uint32_t* const s_outs = reinterpret_cast<uint32_t*>(hbase + 2 * fs::STAGE_BYTES);        // survivors, one buffer per stage
-    fs::HalfState* const hs = reinterpret_cast<fs::HalfState*>(s_outs + 2 * fs::OUT_CAP);
+    uint8_t* const wbase = fs_smem + fs::TABLE_BYTES + fs::KEY_BYTES + (size_t)warp * fs::WARP_BYTES;
+    uint32_t* const w_out = reinterpret_cast<uint32_t*>(wbase + 2 * fs::SPAN_STRIDE);         // this warp's survivors
+    fs::WarpState* const ws = reinterpret_cast<fs::WarpState*>(w_out + fs::OUT_CAP);
     const uint32_t lane4 = (uint32_t)lane * 4u;
     const uint32_t full = 0xffffffffu;
     const bool keys_in_smem = (4u << a.table_bits) <= fs::KEY_BYTES;
     const uint32_t tmask = (1u << a.table_bits) - 1u, kshift = 32 - a.table_bits;
 
-    if (t == 0) {
-        fs_mbar_init(&hs->bar[0], 1);
-        fs_mbar_init(&hs->bar[1], 1);
-        hs->ncand[0] = hs->ncand[1] = 0;
-        hs->n_nl[0] = hs->n_nl[1] = 0;
+    if (lane == 0) {
+        fs_mbar_init(&ws->bar[0], 1);
+        fs_mbar_init(&ws->bar[1], 1);
+        ws->ncand = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
+    __syncwarp();
+    // Spans of this launch, dealt round-robin to all warps of the grid: warp gw owns spans gw, gw + W, gw + 2W, ...
+    // (131 552 spans over 4 736 warps on C2: 27 or 28 each, so a static deal is balanced to 1 %).
+    const uint32_t span_begin = a.tile_begin * fs::SPANS, span_end = a.tile_end * fs::SPANS;
+    const uint32_t W = gridDim.x * (fs::THREADS / 32);
+    uint32_t span = span_begin + blockIdx.x * (fs::THREADS / 32) + warp;
+    // Fill buffer b with span sp: one bulk copy of the span and its halo when they lie inside the text, else (the
+    // last spans of the text) a bounds-checked copy by the warp; bytes at or beyond `len` read as zero.
+    auto fill = [&](uint32_t sp, int b) {
+        if (sp >= span_end) return;
+        uint8_t* const dst = wbase + b * fs::SPAN_STRIDE;
+        const uint64_t pos = (uint64_t)sp * fs::SPAN;
+        if (pos + fs::SPAN + fs::HALO <= a.len) {
+            if (lane == 0) fs_tma_load(dst, a.text + pos, fs::SPAN + fs::HALO, &ws->bar[b]);
+        } else {
+            for (uint32_t i = lane; i < (fs::SPAN + fs::HALO) / 16; i += 32) reinterpret_cast<uint4*>(dst)[i] = load16_any(a.text, pos + 16ull * i, a.len);
+            __syncwarp();
+            if (lane == 0) fs_mbar_arrive(&ws->bar[b]);
+        }
+    };
+    fill(span, 0);
+    fill(span + W, 1);      // in flight while the table is loaded
     if (a.use_filter) {
         if (V == 2) {
             const uint4* src = reinterpret_cast<const uint4*>(a.bit_table);
@@ -170,87 +216,83 @@ __global__ void __launch_bounds__(fs::THREADS, 1) k_fscan(FscanArgs a) {
         if (keys_in_smem)
             for (uint32_t i = threadIdx.x; i <= tmask; i += fs::THREADS) s_keys[i] = __ldg(a.gram_keys + i);
     }
-    __syncthreads();
-    auto next_tile = [&](int s) {       // thread 0 of the half: take a ticket and start the copy into stage s
-        const uint32_t tile = a.tile_begin + atomicAdd(a.ticket, 1u);
-        hs->tile[s] = tile;
-        if (tile < a.tile_end && tile < a.tma_tiles)
-            fs_tma_load(stages + s * fs::STAGE_BYTES, a.text + (uint64_t)tile * fs::TILE, fs::TILE + fs::HALO, &hs->bar[s]);
+    __syncthreads();        // the only block-wide barrier: from here on every warp is a pipeline of its own
+
+    // survivors of this warp -> candidate queue, one global atomic
+    auto flush = [&]() {
+        __syncwarp();
+        const uint32_t nc = min(ws->ncand, fs::OUT_CAP);
+        if (nc) {
+            uint32_t gb = 0;
+            if (lane == 0) gb = atomicAdd(&a.ctr->n_cand, nc);
+            gb = __shfl_sync(full, gb, 0);
+            for (uint32_t q = lane; q < nc; q += 32) {
+                if (gb + q < a.cand_cap) a.cand[gb + q] = w_out[q];
+                else atomicOr(&a.ctr->overflow, 1u);
+            }
+        }
+        __syncwarp();
+        if (lane == 0) ws->ncand = 0;
+        __syncwarp();
     };
-    if (t == 0) { next_tile(0); next_tile(1); }
-    fs_half_sync(half);
 
     uint32_t parity = 0;
-    for (uint32_t n = 0;; ++n) {
-        const int s = n & 1;
-        const uint32_t tile = hs->tile[s];
-        if (tile >= a.tile_end) break;
-        const uint64_t base = (uint64_t)tile * fs::TILE;
-        const uint32_t base32 = tile * fs::TILE;          // texts are below 4 GiB
-        uint8_t* const stage = stages + s * fs::STAGE_BYTES;
-        uint32_t* const s_out = s_outs + s * fs::OUT_CAP;
-        const bool tma = tile < a.tma_tiles;
-        if (tma) {
-            fs_mbar_wait(&hs->bar[s], (parity >> s) & 1u);
-            parity ^= 1u << s;
-        } else {        // the last tiles of the text: bounds-checked fill, bytes at or beyond `len` read as zero
-            for (uint32_t i = t; i < fs::STAGE_BYTES / 16; i += fs::HALF)
-                reinterpret_cast<uint4*>(stage)[i] = load16_any(a.text, base + 16ull * i, a.len);
-            fs_half_sync(half);
-        }
+    for (uint32_t n = 0; span < span_end; ++n, span += W) {
+        const int b = n & 1;
+        uint8_t* const stage = wbase + b * fs::SPAN_STRIDE;
+        const uint64_t base = (uint64_t)span * fs::SPAN;
+        const uint32_t base32 = span * fs::SPAN;          // texts are below 4 GiB
+        fs_mbar_wait(&ws->bar[b], (parity >> b) & 1u);
+        parity ^= 1u << b;
 
         // ---- phase A: 32 contiguous bytes per thread
-        const uint4 v0 = *reinterpret_cast<const uint4*>(stage + 32 * t);
-        const uint4 v1 = *reinterpret_cast<const uint4*>(stage + 32 * t + 16);
-        const uint32_t P = fs_nl_spread(v0) | (fs_nl_spread(v1) << 4);
+        const uint4 v0 = *reinterpret_cast<const uint4*>(stage + 32 * lane);
+        const uint4 v1 = *reinterpret_cast<const uint4*>(stage + 32 * lane + 16);
+        const uint32_t P = V == 3 ? fs_nl_spread_fma(v0, a.k) | (fs_nl_spread_fma(v1, a.k) << 4) : fs_nl_spread(v0) | (fs_nl_spread(v1) << 4);
         uint32_t hm = 0;
         if (a.use_filter) {
             uint32_t nxt = __shfl_down_sync(full, v0.x, 1);
-            if (lane == 31) nxt = *reinterpret_cast<const uint32_t*>(stage + 32 * (t + 1));
-            hm = fs_probe16<V>(v0, v1.x, fs_smem, lane4) | (fs_probe16<V>(v1, nxt, fs_smem, lane4) << 16);
-            if (!tma) {     // windows that start at or beyond `len`
-                const uint64_t p0 = base + 32ull * t;
-                if (p0 >= a.len) hm = 0;
-                else if (a.len - p0 < 32) hm &= (1u << (uint32_t)(a.len - p0)) - 1u;
-            }
+            if (lane == 31) nxt = *reinterpret_cast<const uint32_t*>(stage + fs::SPAN);
+            hm = fs_probe16<V>(v0, v1.x, fs_smem, lane4, a.mul, a.k) | (fs_probe16<V>(v1, nxt, fs_smem, lane4, a.mul, a.k) << 16);
+            const uint64_t p0 = base + 32ull * lane;      // windows that start at or beyond `len`
+            if (p0 + 32 > a.len) hm = p0 >= a.len ? 0u : hm & ((1u << (uint32_t)(a.len - p0)) - 1u);
         }
 
-        // ---- phase B, newlines: position in the tile | ('\r' before it) << 15, in position order, into this warp's slot of
-        // the tile's newline lists (no block-wide rank needed: k_expand adds the counts of the warps in front). A warp
-        // with more newlines than its slot holds marks the tile dense; k_expand then re-reads that tile from the text.
+        // ---- phase B, newlines: position in the tile | skip flag << 14 | ('\r' before it) << 15, in position order, into
+        // this span's slot of the newline lists (no block-wide rank needed: k_expand adds the counts of the spans in
+        // front). A span with more newlines than its slot holds writes only its count; k_expand then re-reads that
+        // tile from the text.
         {
             const uint32_t cn = __popc(P);
             uint32_t inc = cn;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(full, inc, o); if (lane >= o) inc += y; }
             const uint32_t wtotal = __shfl_sync(full, inc, 31);
-            if (wtotal) {
-                uint16_t* const wl = a.nl_lists + ((size_t)tile * 16 + warp) * fs::WLIST;
-                if (wtotal <= fs::WLIST) {
-                    const uint32_t excl = inc - cn;
-                    uint32_t m = P;
-                    while (m) {
-                        const uint32_t b = __ffs(m) - 1;
-                        m &= m - 1;
-                        const uint32_t nq = b & 7u, j = b >> 3;
-                        const uint32_t lt = (((1u << nq) - 1u) * 0x01010101u) | ((0x01010101u << nq) & ((1u << (8u * j)) - 1u));
-                        const uint32_t pt = 32 * t + 4 * nq + j;
-                        const uint32_t prev = pt ? stage[pt - 1] : (base ? a.text[base - 1] : 0u);
-                        const uint32_t nb = stage[pt + 1];            // first byte of the line that starts here (the halo covers pt + 1 == TILE)
-                        const uint32_t skip = (nb != '\n' && nb != 0u) ? ((a.skip1[nb >> 5] >> (nb & 31u)) & 1u) : 0u;
-                        wl[excl + __popc(P & lt)] = (uint16_t)(pt | (skip << 14) | (prev == '\r' ? 0x8000u : 0u));
-                    }
+            if (wtotal && wtotal <= fs::WLIST) {
+                uint16_t* const wl = a.nl_lists + (size_t)span * fs::WLIST;
+                const uint32_t excl = inc - cn, tpos = (span & (fs::SPANS - 1)) * fs::SPAN;      // span's offset in its tile
+                uint32_t m = P;
+                while (m) {
+                    const uint32_t bi = __ffs(m) - 1;
+                    m &= m - 1;
+                    const uint32_t nq = bi & 7u, j = bi >> 3;
+                    const uint32_t lt = (((1u << nq) - 1u) * 0x01010101u) | ((0x01010101u << nq) & ((1u << (8u * j)) - 1u));
+                    const uint32_t pt = 32 * lane + 4 * nq + j;
+                    uint32_t prev;
+                    if (pt) prev = stage[pt - 1]; else prev = base ? a.text[base - 1] : 0u;     // (two branches: a select would make both loads generic)
+                    const uint32_t nb = stage[pt + 1];            // first byte of the line that starts here (the halo covers pt + 1 == SPAN)
+                    const uint32_t skip = (nb != '\n' && nb != 0u) ? ((a.skip1[nb >> 5] >> (nb & 31u)) & 1u) : 0u;
+                    wl[excl + __popc(P & lt)] = (uint16_t)((tpos + pt) | (skip << 14) | (prev == '\r' ? 0x8000u : 0u));
                 }
-                if (lane == 0) atomicAdd(&hs->n_nl[s], wtotal);
             }
-            if (lane == 0) a.warp_counts[(size_t)tile * 16 + warp] = (uint16_t)min(wtotal, 0xFFFFu);
+            if (lane == 0) a.warp_counts[span] = (uint16_t)wtotal;
         }
         // ---- phase B, first-stage hits against the exact gram keys (shared memory when they fit); the window is
-        // re-read from the staged tile. Survivors are staged per half and flushed with one global atomic per tile.
+        // re-read from the staged span. Survivors collect in the warp's list, flushed when half full.
         while (hm) {
             const uint32_t i = __ffs(hm) - 1;
             hm &= hm - 1;
-            const uint32_t pt = 32 * t + i, al = pt & ~3u;
+            const uint32_t pt = 32 * lane + i, al = pt & ~3u;
             const uint32_t wlo = *reinterpret_cast<const uint32_t*>(stage + al), whi = *reinterpret_cast<const uint32_t*>(stage + al + 4);
             const uint32_t f = __funnelshift_r(wlo, whi, (pt & 3u) * 8u) | 0x20202020u;
             uint32_t slot = (f * GRAM_MUL2) >> kshift;
@@ -258,37 +300,20 @@ __global__ void __launch_bounds__(fs::THREADS, 1) k_fscan(FscanArgs a) {
             if (keys_in_smem) { while ((key = s_keys[slot]) != 0u && key != f) slot = (slot + 1) & tmask; }
             else { while ((key = __ldg(a.gram_keys + slot)) != 0u && key != f) slot = (slot + 1) & tmask; }
             if (key == f) {
-                const uint32_t ob = atomicAdd(&hs->ncand[s], 1u);
-                if (ob < fs::OUT_CAP) s_out[ob] = base32 + pt;
-                else {      // a tile dense with gram occurrences: straight to the global queue
+                const uint32_t ob = atomicAdd(&ws->ncand, 1u);
+                if (ob < fs::OUT_CAP) w_out[ob] = base32 + pt;
+                else {      // a span dense with gram occurrences: straight to the global queue
                     const uint32_t gi = atomicAdd(&a.ctr->n_cand, 1u);
-                    if (gi < a.cand_cap) a.cand[gi] = (uint32_t)(base + pt);
+                    if (gi < a.cand_cap) a.cand[gi] = base32 + pt;
                     else atomicOr(&a.ctr->overflow, 1u);
                 }
             }
         }
-        fs_half_sync(half);       // every warp is done with the stage; the tile's counts and survivors are complete
-        // (the only barrier of a tile: counters and survivors are kept per stage, so the next tile starts at once)
-        if (t == 0) {
-            a.tile_counts[tile] = hs->n_nl[s];
-            hs->n_nl[s] = 0;
-            next_tile(s);         // refill the stage
-        }
-        if (warp == 15) {       // survivors -> candidate queue, one global atomic
-            const uint32_t nc = min(hs->ncand[s], fs::OUT_CAP);
-            if (nc) {
-                uint32_t gb = 0;
-                if (lane == 0) gb = atomicAdd(&a.ctr->n_cand, nc);
-                gb = __shfl_sync(full, gb, 0);
-                for (uint32_t q = lane; q < nc; q += 32) {
-                    if (gb + q < a.cand_cap) a.cand[gb + q] = s_out[q];
-                    else atomicOr(&a.ctr->overflow, 1u);
-                }
-            }
-            __syncwarp();
-            if (lane == 0) hs->ncand[s] = 0;
-        }
+        __syncwarp();       // every lane is done with the buffer
+        fill(span + 2 * W, b);
+        if (ws->ncand >= fs::OUT_CAP / 2) flush();
     }
+    flush();
 }
 
 // ------------------------------------------------------------------ line offsets from the newline lists

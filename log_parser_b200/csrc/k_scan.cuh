@@ -218,7 +218,15 @@ __global__ void __launch_bounds__(SCAN_THREADS) k_filter_count(FilterArgs a) {
 }
 
 // exclusive scan of tile counts (one block); also publishes the total
-__global__ void __launch_bounds__(1024) k_scan_tiles(uint32_t* __restrict__ tile_counts, uint32_t n_tiles, uint32_t n_logs, Counters* ctr) {
+// `span_counts` (k_fscan: 16 newline counts per tile, one per 1 KiB span) replaces tile_counts as the input when given.
+__device__ __forceinline__ uint32_t tile_count_in(const uint32_t* __restrict__ tile_counts, const uint16_t* __restrict__ span_counts, uint32_t i) {
+    if (!span_counts) return tile_counts[i];
+    const uint4 a = __ldg(reinterpret_cast<const uint4*>(span_counts) + 2 * (size_t)i), b = __ldg(reinterpret_cast<const uint4*>(span_counts) + 2 * (size_t)i + 1);
+    const uint32_t lo = (a.x & 0xFFFFu) + (a.y & 0xFFFFu) + (a.z & 0xFFFFu) + (a.w & 0xFFFFu) + (b.x & 0xFFFFu) + (b.y & 0xFFFFu) + (b.z & 0xFFFFu) + (b.w & 0xFFFFu);
+    const uint32_t hi = (a.x >> 16) + (a.y >> 16) + (a.z >> 16) + (a.w >> 16) + (b.x >> 16) + (b.y >> 16) + (b.z >> 16) + (b.w >> 16);
+    return lo + hi;
+}
+__global__ void __launch_bounds__(1024) k_scan_tiles(uint32_t* __restrict__ tile_counts, const uint16_t* __restrict__ span_counts, uint32_t n_tiles, uint32_t n_logs, Counters* ctr) {
     __shared__ uint32_t warp_tot[32];
     __shared__ uint32_t carry;
     if (n_tiles <= 1024 * 16) {
@@ -226,7 +234,7 @@ __global__ void __launch_bounds__(1024) k_scan_tiles(uint32_t* __restrict__ tile
         const uint32_t per = (n_tiles + 1023) / 1024, first = threadIdx.x * per;
         uint32_t v[16], sum = 0;
 #pragma unroll
-        for (int k = 0; k < 16; ++k) { v[k] = ((uint32_t)k < per && first + k < n_tiles) ? tile_counts[first + k] : 0u; sum += v[k]; }
+        for (int k = 0; k < 16; ++k) { v[k] = ((uint32_t)k < per && first + k < n_tiles) ? tile_count_in(tile_counts, span_counts, first + k) : 0u; sum += v[k]; }
         uint32_t inc = sum;
         for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, inc, o); if ((threadIdx.x & 31) >= o) inc += t; }
         if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = inc;
@@ -248,7 +256,7 @@ __global__ void __launch_bounds__(1024) k_scan_tiles(uint32_t* __restrict__ tile
     __syncthreads();
     for (uint32_t base = 0; base < n_tiles; base += 1024) {
         uint32_t i = base + threadIdx.x;
-        uint32_t v = i < n_tiles ? tile_counts[i] : 0;
+        uint32_t v = i < n_tiles ? tile_count_in(tile_counts, span_counts, i) : 0;
         uint32_t inc = v;
         for (int o = 1; o < 32; o <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, inc, o); if ((threadIdx.x & 31) >= o) inc += t; }
         if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = inc;
