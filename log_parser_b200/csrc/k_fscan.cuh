@@ -32,10 +32,13 @@ constexpr uint32_t ROWS = 1024;                                      // first-st
 constexpr uint32_t MUL1 = 0x9E3779B1u;
 constexpr size_t TABLE_BYTES = (size_t)ROWS * 128;
 constexpr uint32_t WLIST = 64;                                       // newline list entries per span
-constexpr uint32_t OUT_CAP = 64;                                     // survivors staged per warp
+constexpr uint32_t OUT_CAP = 32;                                     // survivors staged per warp (flushed when half full)
+constexpr uint32_t HIT_CAP = 64;                                     // first-stage hits of a pair of spans compacted per warp
 constexpr uint32_t KEY_BYTES = 8192;                                 // exact gram keys kept in shared memory when 4 << table_bits fits
-constexpr size_t WARP_BYTES = 2 * SPAN_STRIDE + OUT_CAP * 4 + 128;   // two span buffers, survivors, state
+// per warp: two span buffers, the pair's newline positions (2 x WLIST u16), first-stage hits (u16), survivors, state
+constexpr size_t WARP_BYTES = 2 * SPAN_STRIDE + 2 * WLIST * 2 + HIT_CAP * 2 + OUT_CAP * 4 + 32;
 constexpr size_t SMEM_BYTES = TABLE_BYTES + KEY_BYTES + (THREADS / 32) * WARP_BYTES;
+static_assert(SMEM_BYTES <= 227 * 1024, "k_fscan shared memory");
 
 // row = (H >> 7) & (ROWS - 1), rotation = H & 31; the table bit of a gram is bit (rotation - 1) & 31.
 // `mul` is an odd multiplier picked per pattern set (and per first log, see pick_multiplier in engine.cu);
@@ -59,8 +62,9 @@ inline uint32_t host_row(uint32_t H) { return (H >> 7) & (ROWS - 1); }
 struct WarpState {
     unsigned long long bar[2];      // mbarriers of the warp's two span buffers
     uint32_t ncand;                 // survivors waiting in the warp's list
+    uint32_t nhit;                  // first-stage hits of the current pair of spans
 };
-static_assert(sizeof(WarpState) <= 128, "WarpState must fit its slot");
+static_assert(sizeof(WarpState) <= 32, "WarpState must fit its slot");
 }  // namespace fs
 
 struct FscanArgs {
@@ -169,7 +173,9 @@ __global__ void __launch_bounds__(fs::THREADS, 1) k_fscan(FscanArgs a) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     uint32_t* const s_keys = reinterpret_cast<uint32_t*>(fs_smem + fs::TABLE_BYTES);          // exact gram keys (when they fit)
     uint8_t* const wbase = fs_smem + fs::TABLE_BYTES + fs::KEY_BYTES + (size_t)warp * fs::WARP_BYTES;
-    uint32_t* const w_out = reinterpret_cast<uint32_t*>(wbase + 2 * fs::SPAN_STRIDE);         // this warp's survivors
+    uint16_t* const w_nl = reinterpret_cast<uint16_t*>(wbase + 2 * fs::SPAN_STRIDE);          // [2][WLIST] newline positions of the pair
+    uint16_t* const w_hit = w_nl + 2 * fs::WLIST;                                             // [HIT_CAP] buffer << 10 | position
+    uint32_t* const w_out = reinterpret_cast<uint32_t*>(w_hit + fs::HIT_CAP);                 // [OUT_CAP] this warp's survivors
     fs::WarpState* const ws = reinterpret_cast<fs::WarpState*>(w_out + fs::OUT_CAP);
     const uint32_t lane4 = (uint32_t)lane * 4u;
     const uint32_t full = 0xffffffffu;
@@ -180,11 +186,13 @@ __global__ void __launch_bounds__(fs::THREADS, 1) k_fscan(FscanArgs a) {
         fs_mbar_init(&ws->bar[0], 1);
         fs_mbar_init(&ws->bar[1], 1);
         ws->ncand = 0;
+        ws->nhit = 0;
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
     // Spans of this launch, dealt round-robin to all warps of the grid: warp gw owns spans gw, gw + W, gw + 2W, ...
-    // (131 552 spans over 4 736 warps on C2: 27 or 28 each, so a static deal is balanced to 1 %).
+    // (131 552 spans over 4 736 warps on C2: 27 or 28 each, so a static deal is balanced to 1 %), and works on
+    // two of them at a time, one per buffer.
     const uint32_t span_begin = a.tile_begin * fs::SPANS, span_end = a.tile_end * fs::SPANS;
     const uint32_t W = gridDim.x * (fs::THREADS / 32);
     uint32_t span = span_begin + blockIdx.x * (fs::THREADS / 32) + warp;
@@ -220,14 +228,13 @@ __global__ void __launch_bounds__(fs::THREADS, 1) k_fscan(FscanArgs a) {
 
     // survivors of this warp -> candidate queue, one global atomic
     auto flush = [&]() {
-        __syncwarp();
         const uint32_t nc = min(ws->ncand, fs::OUT_CAP);
         if (nc) {
             uint32_t gb = 0;
             if (lane == 0) gb = atomicAdd(&a.ctr->n_cand, nc);
             gb = __shfl_sync(full, gb, 0);
-            for (uint32_t q = lane; q < nc; q += 32) {
-                if (gb + q < a.cand_cap) a.cand[gb + q] = w_out[q];
+            if ((uint32_t)lane < nc) {
+                if (gb + lane < a.cand_cap) a.cand[gb + lane] = w_out[lane];
                 else atomicOr(&a.ctr->overflow, 1u);
             }
         }
@@ -235,84 +242,126 @@ __global__ void __launch_bounds__(fs::THREADS, 1) k_fscan(FscanArgs a) {
         if (lane == 0) ws->ncand = 0;
         __syncwarp();
     };
+    // one first-stage hit (buffer << 10 | position in the span) against the exact gram keys; the window is re-read
+    // from the staged span
+    auto check_hit = [&](uint32_t code, uint32_t span0) {
+        const uint32_t bsel = code >> 10, pt = code & 1023u, al = pt & ~3u;
+        const uint8_t* const st = wbase + bsel * fs::SPAN_STRIDE;
+        const uint32_t wlo = *reinterpret_cast<const uint32_t*>(st + al), whi = *reinterpret_cast<const uint32_t*>(st + al + 4);
+        const uint32_t f = __funnelshift_r(wlo, whi, (pt & 3u) * 8u) | 0x20202020u;
+        uint32_t slot = (f * GRAM_MUL2) >> kshift;
+        uint32_t key;
+        if (keys_in_smem) { while ((key = s_keys[slot]) != 0u && key != f) slot = (slot + 1) & tmask; }
+        else { while ((key = __ldg(a.gram_keys + slot)) != 0u && key != f) slot = (slot + 1) & tmask; }
+        if (key == f) {
+            const uint32_t pos = (span0 + bsel * W) * fs::SPAN + pt;          // texts are below 4 GiB
+            const uint32_t ob = atomicAdd(&ws->ncand, 1u);
+            if (ob < fs::OUT_CAP) w_out[ob] = pos;
+            else {      // spans dense with gram occurrences: straight to the global queue
+                const uint32_t gi = atomicAdd(&a.ctr->n_cand, 1u);
+                if (gi < a.cand_cap) a.cand[gi] = pos;
+                else atomicOr(&a.ctr->overflow, 1u);
+            }
+        }
+    };
 
-    uint32_t parity = 0;
-    for (uint32_t n = 0; span < span_end; ++n, span += W) {
-        const int b = n & 1;
-        uint8_t* const stage = wbase + b * fs::SPAN_STRIDE;
-        const uint64_t base = (uint64_t)span * fs::SPAN;
-        const uint32_t base32 = span * fs::SPAN;          // texts are below 4 GiB
-        fs_mbar_wait(&ws->bar[b], (parity >> b) & 1u);
-        parity ^= 1u << b;
-
-        // ---- phase A: 32 contiguous bytes per thread
-        const uint4 v0 = *reinterpret_cast<const uint4*>(stage + 32 * lane);
-        const uint4 v1 = *reinterpret_cast<const uint4*>(stage + 32 * lane + 16);
-        const uint32_t P = V == 3 ? fs_nl_spread_fma(v0, a.k) | (fs_nl_spread_fma(v1, a.k) << 4) : fs_nl_spread(v0) | (fs_nl_spread(v1) << 4);
-        uint32_t hm = 0;
-        if (a.use_filter) {
-            uint32_t nxt = __shfl_down_sync(full, v0.x, 1);
-            if (lane == 31) nxt = *reinterpret_cast<const uint32_t*>(stage + fs::SPAN);
-            hm = fs_probe16<V>(v0, v1.x, fs_smem, lane4, a.mul, a.k) | (fs_probe16<V>(v1, nxt, fs_smem, lane4, a.mul, a.k) << 16);
-            const uint64_t p0 = base + 32ull * lane;      // windows that start at or beyond `len`
-            if (p0 + 32 > a.len) hm = p0 >= a.len ? 0u : hm & ((1u << (uint32_t)(a.len - p0)) - 1u);
+    for (uint32_t n = 0; span < span_end; ++n, span += 2 * W) {
+        const bool two = span + W < span_end;      // the last round of a warp may hold one span only
+        uint32_t P[2], hm[2];
+        // ---- phase A on both buffers: 32 contiguous bytes per lane and span
+#pragma unroll
+        for (int b = 0; b < 2; ++b) {
+            P[b] = 0; hm[b] = 0;
+            if (b == 1 && !two) break;
+            const uint8_t* const stage = wbase + b * fs::SPAN_STRIDE;
+            const uint64_t base = (uint64_t)(span + b * W) * fs::SPAN;
+            fs_mbar_wait(&ws->bar[b], n & 1u);
+            const uint4 v0 = *reinterpret_cast<const uint4*>(stage + 32 * lane);
+            const uint4 v1 = *reinterpret_cast<const uint4*>(stage + 32 * lane + 16);
+            P[b] = V == 3 ? fs_nl_spread_fma(v0, a.k) | (fs_nl_spread_fma(v1, a.k) << 4) : fs_nl_spread(v0) | (fs_nl_spread(v1) << 4);
+            if (a.use_filter) {
+                uint32_t nxt = __shfl_down_sync(full, v0.x, 1);
+                if (lane == 31) nxt = *reinterpret_cast<const uint32_t*>(stage + fs::SPAN);
+                hm[b] = fs_probe16<V>(v0, v1.x, fs_smem, lane4, a.mul, a.k) | (fs_probe16<V>(v1, nxt, fs_smem, lane4, a.mul, a.k) << 16);
+                if (base + fs::SPAN > a.len) {      // the text ends in this span: no windows at or beyond `len`
+                    const uint64_t p0 = base + 32ull * lane;
+                    hm[b] = p0 >= a.len ? 0u : (a.len - p0 < 32 ? hm[b] & ((1u << (uint32_t)(a.len - p0)) - 1u) : hm[b]);
+                }
+            }
         }
 
-        // ---- phase B, newlines: position in the tile | skip flag << 14 | ('\r' before it) << 15, in position order, into
-        // this span's slot of the newline lists (no block-wide rank needed: k_expand adds the counts of the spans in
-        // front). A span with more newlines than its slot holds writes only its count; k_expand then re-reads that
-        // tile from the text.
+        // ---- phase B, newlines. One warp scan ranks the newlines of both spans (counts packed 16 + 16 bits); every lane
+        // drops the positions of its own into the warp's lists at their ranks; then the lists are finished by full
+        // warps: position in the tile | skip flag << 14 | ('\r' before it) << 15, in position order, into the span's slot
+        // of the global newline lists (coalesced). No block-wide rank is needed: k_expand adds the counts of the
+        // spans in front. A span with more newlines than its slot holds writes only its count; k_expand then re-reads
+        // that tile from the text.
         {
-            const uint32_t cn = __popc(P);
+            const uint32_t cn = __popc(P[0]) | (__popc(P[1]) << 16);
             uint32_t inc = cn;
 #pragma unroll
             for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(full, inc, o); if (lane >= o) inc += y; }
-            const uint32_t wtotal = __shfl_sync(full, inc, 31);
-            if (wtotal && wtotal <= fs::WLIST) {
-                uint16_t* const wl = a.nl_lists + (size_t)span * fs::WLIST;
-                const uint32_t excl = inc - cn, tpos = (span & (fs::SPANS - 1)) * fs::SPAN;      // span's offset in its tile
-                uint32_t m = P;
+            const uint32_t tot = __shfl_sync(full, inc, 31);
+            const uint32_t t0 = tot & 0xFFFFu, t1 = tot >> 16;
+            const uint32_t n0 = t0 <= fs::WLIST ? t0 : 0u, n1 = t1 <= fs::WLIST ? t1 : 0u;
+            const uint32_t excl = inc - cn;
+#pragma unroll
+            for (int b = 0; b < 2; ++b) {
+                uint32_t m = (b ? n1 : n0) ? P[b] : 0u;
+                const uint32_t ex = b ? excl >> 16 : excl & 0xFFFFu;
                 while (m) {
                     const uint32_t bi = __ffs(m) - 1;
                     m &= m - 1;
                     const uint32_t nq = bi & 7u, j = bi >> 3;
                     const uint32_t lt = (((1u << nq) - 1u) * 0x01010101u) | ((0x01010101u << nq) & ((1u << (8u * j)) - 1u));
-                    const uint32_t pt = 32 * lane + 4 * nq + j;
-                    uint32_t prev;
-                    if (pt) prev = stage[pt - 1]; else prev = base ? a.text[base - 1] : 0u;     // (two branches: a select would make both loads generic)
-                    const uint32_t nb = stage[pt + 1];            // first byte of the line that starts here (the halo covers pt + 1 == SPAN)
-                    const uint32_t skip = (nb != '\n' && nb != 0u) ? ((a.skip1[nb >> 5] >> (nb & 31u)) & 1u) : 0u;
-                    wl[excl + __popc(P & lt)] = (uint16_t)((tpos + pt) | (skip << 14) | (prev == '\r' ? 0x8000u : 0u));
+                    w_nl[b * fs::WLIST + ex + __popc(P[b] & lt)] = (uint16_t)(32 * lane + 4 * nq + j);
                 }
             }
-            if (lane == 0) a.warp_counts[span] = (uint16_t)wtotal;
-        }
-        // ---- phase B, first-stage hits against the exact gram keys (shared memory when they fit); the window is
-        // re-read from the staged span. Survivors collect in the warp's list, flushed when half full.
-        while (hm) {
-            const uint32_t i = __ffs(hm) - 1;
-            hm &= hm - 1;
-            const uint32_t pt = 32 * lane + i, al = pt & ~3u;
-            const uint32_t wlo = *reinterpret_cast<const uint32_t*>(stage + al), whi = *reinterpret_cast<const uint32_t*>(stage + al + 4);
-            const uint32_t f = __funnelshift_r(wlo, whi, (pt & 3u) * 8u) | 0x20202020u;
-            uint32_t slot = (f * GRAM_MUL2) >> kshift;
-            uint32_t key;
-            if (keys_in_smem) { while ((key = s_keys[slot]) != 0u && key != f) slot = (slot + 1) & tmask; }
-            else { while ((key = __ldg(a.gram_keys + slot)) != 0u && key != f) slot = (slot + 1) & tmask; }
-            if (key == f) {
-                const uint32_t ob = atomicAdd(&ws->ncand, 1u);
-                if (ob < fs::OUT_CAP) w_out[ob] = base32 + pt;
-                else {      // a span dense with gram occurrences: straight to the global queue
-                    const uint32_t gi = atomicAdd(&a.ctr->n_cand, 1u);
-                    if (gi < a.cand_cap) a.cand[gi] = base32 + pt;
-                    else atomicOr(&a.ctr->overflow, 1u);
-                }
+            __syncwarp();
+            for (uint32_t e = lane; e < n0 + n1; e += 32) {
+                const uint32_t bsel = e >= n0 ? 1u : 0u, idx = e - (bsel ? n0 : 0u);
+                const uint32_t sp = span + bsel * W;
+                const uint8_t* const st = wbase + bsel * fs::SPAN_STRIDE;
+                const uint32_t pt = w_nl[bsel * fs::WLIST + idx];
+                uint32_t prev;
+                if (pt) prev = st[pt - 1];
+                else prev = sp ? a.text[(uint64_t)sp * fs::SPAN - 1] : 0u;      // (two branches: a select would make both loads generic)
+                const uint32_t nb = st[pt + 1];             // first byte of the line that starts here (the halo covers pt + 1 == SPAN)
+                const uint32_t skip = (nb != '\n' && nb != 0u) ? ((a.skip1[nb >> 5] >> (nb & 31u)) & 1u) : 0u;
+                a.nl_lists[(size_t)sp * fs::WLIST + idx] = (uint16_t)(((sp & (fs::SPANS - 1)) * fs::SPAN + pt) | (skip << 14) | (prev == '\r' ? 0x8000u : 0u));
+            }
+            if (lane == 0) {
+                a.warp_counts[span] = (uint16_t)t0;
+                if (two) a.warp_counts[span + W] = (uint16_t)t1;
             }
         }
-        __syncwarp();       // every lane is done with the buffer
-        fill(span + 2 * W, b);
+        // ---- phase B, first-stage hits: compacted into the warp's list, then checked by full warps (the hits of a
+        // lane are few and uneven: a loop per lane ran with 2-3 of 32 lanes for most of its trips)
+        if (a.use_filter) {
+#pragma unroll
+            for (int b = 0; b < 2; ++b) {
+                uint32_t m = hm[b];
+                while (m) {
+                    const uint32_t i = __ffs(m) - 1;
+                    m &= m - 1;
+                    const uint32_t code = ((uint32_t)b << 10) | (32u * lane + i);
+                    const uint32_t at = atomicAdd(&ws->nhit, 1u);
+                    if (at < fs::HIT_CAP) w_hit[at] = (uint16_t)code;
+                    else check_hit(code, span);
+                }
+            }
+            __syncwarp();
+            const uint32_t nh = min(ws->nhit, fs::HIT_CAP);
+            for (uint32_t e = lane; e < nh; e += 32) check_hit(w_hit[e], span);
+            __syncwarp();
+            if (lane == 0) ws->nhit = 0;
+        }
+        __syncwarp();       // every lane is done with the buffers
+        fill(span + 2 * W, 0);
+        fill(span + 3 * W, 1);
         if (ws->ncand >= fs::OUT_CAP / 2) flush();
     }
+    __syncwarp();
     flush();
 }
 
