@@ -67,6 +67,7 @@ void* lp_debug_rx_compile(const char* regex, int flags, int force_vm, char* err,
     return nullptr;
 }
 void lp_debug_rx_free(void* h) { delete static_cast<DebugRx*>(h); }
+int lp_debug_rx_steps(void* h, const uint8_t* s, size_t n) { return lpx::vm_steps_host(static_cast<DebugRx*>(h)->span_vm, s, n); }
 int lp_debug_rx_is_dfa(void* h) { return static_cast<DebugRx*>(h)->has_dfa ? 1 : 0; }
 uint32_t lp_debug_rx_states(void* h) {
     DebugRx* d = static_cast<DebugRx*>(h);

@@ -154,6 +154,7 @@ struct lp_ctx {
     DevBuf f_bits, f_gkeys, fs_lists;           // fused scan: first-stage bit table, exact gram keys, per-span newline counts and lists
     const uint8_t* d_byte_table = nullptr;
     int scan_mode = 0;                         // 0: fused single-pass scan (k_fscan); 1: k_filter_count + k_scan_tiles + k_lines (LP_SCAN_MODE=legacy)
+    uint32_t vm_blocks_per_sm = 12;            // k_verify_vm: blocks of 4 warps per SM (40 registers: 48 resident warps); the more warps, the fewer evaluations each one serialises (LP_VM_BLOCKS)
     uint32_t f_mul = fs::MUL1;                 // first-stage hash multiplier of k_fscan (pick_multiplier)
     int fscan_variant = 0;                     // first-stage lookup of k_fscan: 0 IMAD.HI hash, 1 IMAD+SHF hash, 2 byte table (LP_FSCAN_VARIANT)
     std::vector<uint32_t> lit_off8;   // literal -> offset in the 8-byte aligned device copy of the literal bytes
@@ -411,11 +412,11 @@ void upload_plan(lp_ctx* c) {
 inline uint32_t blocks_for(uint64_t n, uint32_t threads) { return (uint32_t)std::max<uint64_t>(1, (n + threads - 1) / threads); }
 
 template <class K>
-void sort_keys(lp_ctx* c, K* in, K* out, uint32_t n, int end_bit) {
+void sort_keys(lp_ctx* c, K* in, K* out, uint32_t n, int end_bit, int begin_bit = 0) {
     size_t tmp = 0;
-    cub::DeviceRadixSort::SortKeys(nullptr, tmp, in, out, (int)n, 0, end_bit, c->stream);
+    cub::DeviceRadixSort::SortKeys(nullptr, tmp, in, out, (int)n, begin_bit, end_bit, c->stream);
     c->cub_tmp.ensure(tmp);
-    CK(cub::DeviceRadixSort::SortKeys(c->cub_tmp.p, tmp, in, out, (int)n, 0, end_bit, c->stream));
+    CK(cub::DeviceRadixSort::SortKeys(c->cub_tmp.p, tmp, in, out, (int)n, begin_bit, end_bit, c->stream));
     c->launches += 3;
 }
 template <class K, class V>
@@ -515,7 +516,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     const bool has_vm = c->plan.n_vm > 0;
     // one thread per (line, regex) evaluation with a private 16 KB backtracking stack (620 MB of stacks, allocated only
     // when such patterns exist; four times as many threads measured no faster: the kernel is bound by divergence)
-    const uint32_t vm_grid = (uint32_t)c->n_sm * 2, vm_block = 128;
+    const uint32_t vm_grid = (uint32_t)c->n_sm * c->vm_blocks_per_sm, vm_block = 128;
 
     // first-call estimates (later calls reuse what earlier logs needed; an under-estimate costs one re-run)
     if (c->est_lines == 0) {
@@ -549,7 +550,8 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     c->cand.ensure(c->est_cand * 4);
     c->tasks.ensure(c->est_tasks * 8);
     c->items.ensure(c->est_items * 8 * N_CLASSES);
-    if (has_vm) { c->vm_tasks.ensure(c->est_vm_tasks * 8); c->vm_tasks_alt.ensure(c->est_vm_tasks * 8); c->vm_stack.ensure((size_t)vm_grid * vm_block * lpx::VM_STACK_WORDS * 4); }
+    if (has_vm) { c->vm_tasks.ensure(c->est_vm_tasks * 8); c->vm_tasks_alt.ensure(c->est_vm_tasks * 8); }
+    if (has_vm || !c->plan.always_vm_list.empty()) c->vm_stack.ensure((size_t)VM_POOL_STACKS * lpx::VM_STACK_WORDS * 4);
     c->recs.ensure(rec_cap * 8);
     c->recs_alt.ensure(rec_cap * 8);
     c->rx_begin.ensure((size_t)(c->dp.n_rx + 2) * 4);
@@ -664,7 +666,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     va.recs = c->recs.as<unsigned long long>(); va.rec_cap = (uint32_t)rec_cap; va.ctr = ctr; va.n_lines_total = (uint32_t)line_cap;
     va.first_line = c->first_line.as<uint32_t>(); va.n_lines = c->n_lines.as<uint32_t>(); va.n_logs = n_logs;
     va.vm_tasks = c->vm_tasks.as<unsigned long long>(); va.vm_task_cap = (uint32_t)std::min<size_t>(c->est_vm_tasks, 0xFFFFFFFFu);
-    va.vm_stack = c->vm_stack.as<uint32_t>();
+    va.vm_stack = c->vm_stack.as<uint32_t>(); va.vm_pool_n = VM_POOL_STACKS;
     if (use_filter) {
         ConfirmArgs ca{};
         ca.text = d_text; ca.len = len; ca.cand = c->cand.as<uint32_t>(); ca.cand_cap = fa.cand_cap;
@@ -689,10 +691,10 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         k_verify<<<c->n_sm * 8, 256, 0, st>>>(va, c->dp);
         c->launches += 2;
         if (has_vm) {
-            // tasks sorted by (regex, line): the lanes of a warp then interpret the same program on neighbouring
-            // lines and stay together far longer than with tasks in arrival order
+            // tasks grouped by regex (a stable sort on the regex bits only: two radix passes instead of six): the lanes
+            // of a warp then interpret the same program and stay together far longer than with tasks in arrival order
             sort_keys<unsigned long long>(c, c->vm_tasks.as<unsigned long long>(), c->vm_tasks_alt.as<unsigned long long>(), va.vm_task_cap,
-                                          std::min<int>(64, 32 + bits_for(c->dp.n_rx)));
+                                          std::min<int>(64, 32 + bits_for(c->dp.n_rx)), 32);
             va.vm_tasks = c->vm_tasks_alt.as<unsigned long long>();
             k_verify_vm<<<vm_grid, vm_block, 0, st>>>(va, c->dp);
             c->launches += 1;
@@ -885,9 +887,9 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
     }
     if (want_spans) {
         const uint32_t sg = (uint32_t)c->n_sm * 2, sb = 128;
-        c->vm_stack.ensure((size_t)sg * sb * lpx::VM_STACK_WORDS * 4);
+        c->vm_stack.ensure((size_t)VM_POOL_STACKS * lpx::VM_STACK_WORDS * 4);
         k_spans<<<sg, sb, 0, st>>>(c->ev_key.as<unsigned long long>(), ctr, mc, c->dp, c->pend.d_text, c->line_start.as<uint32_t>(),
-                                   c->line_end.as<uint32_t>(), c->vm_stack.as<uint32_t>(), ctr, reinterpret_cast<uint32_t*>(arena + o_ss),
+                                   c->line_end.as<uint32_t>(), c->vm_stack.as<uint32_t>(), VM_POOL_STACKS, ctr, reinterpret_cast<uint32_t*>(arena + o_ss),
                                    reinterpret_cast<uint32_t*>(arena + o_se));
         c->launches += 1;
     }
@@ -1068,6 +1070,7 @@ static lp_ctx* create_worker(const lp_scoring_cfg* cfg, int device) {
     CK(cudaGetDeviceProperties(&prop, device));
     ctx->n_sm = prop.multiProcessorCount;
     if (const char* m = getenv("LP_SCAN_MODE")) ctx->scan_mode = strcmp(m, "legacy") == 0 ? 1 : 0;
+    if (const char* v = getenv("LP_VM_BLOCKS")) ctx->vm_blocks_per_sm = (uint32_t)std::max(1, std::min(16, atoi(v)));
     if (const char* v = getenv("LP_FSCAN_VARIANT")) ctx->fscan_variant = std::max(0, std::min(3, atoi(v)));
     std::vector<double> lut((size_t)cfg->max_window + 1);
     for (int d = 0; d <= cfg->max_window; ++d)

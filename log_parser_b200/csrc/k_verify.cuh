@@ -399,7 +399,8 @@ struct VerifyArgs {
     // backtracking verifier
     const unsigned long long* vm_tasks;
     uint32_t vm_task_cap;
-    uint32_t* vm_stack;               // VM_STACK_WORDS words per thread of the VM grid
+    uint32_t* vm_stack;               // pool of deep backtracking stacks, VM_STACK_WORDS words each
+    uint32_t vm_pool_n;               // stacks in the pool
 };
 __global__ void __launch_bounds__(256) k_verify(VerifyArgs a, DevPlan P) {
     __shared__ QStage sg;
@@ -444,57 +445,84 @@ __global__ void __launch_bounds__(256) k_verify_always(VerifyArgs a, DevPlan P) 
 }
 
 // backtracking verifier: look-around, back-references, possessive/atomic, MULTILINE anchors, DFA blow-ups
-__device__ __forceinline__ bool vm_eval(const DevPlan& P, uint32_t r, const uint8_t* __restrict__ text, uint32_t ls, uint32_t le,
-                                        uint32_t* stack, Counters* ctr) {
+// Backtracking stack of one evaluation on the device: the first VM_TOP_WORDS words live in the thread's local memory
+// (cached write-back in L1); an evaluation that needs more takes one deep stack (lpx::VM_STACK_WORDS words of global
+// memory) from a pool and gives up, counted in n_budget like an exhausted step budget, when the pool is empty.
+// Greedy loops push one range entry, not one entry per position, so almost every evaluation stays inside the
+// top part and the threads of the VM kernels cost no global memory.
+constexpr uint32_t VM_TOP_WORDS = 256;
+constexpr uint32_t VM_POOL_STACKS = 4096;
+struct VmStack {
+    uint32_t* top;          // VM_TOP_WORDS words, local memory
+    uint32_t** deep;        // the thread's deep stack once it has one (index i >= VM_TOP_WORDS lives there)
+    uint32_t* pool;
+    uint32_t pool_n;
+    Counters* ctr;
+    __device__ __forceinline__ uint32_t& operator[](uint32_t i) const { return i < VM_TOP_WORDS ? top[i] : (*deep)[i]; }
+};
+__device__ __noinline__ bool vm_stack_grow(VmStack& s, uint32_t& cap) {
+    if (cap >= lpx::VM_STACK_WORDS) return false;
+    if (!*s.deep) {
+        const uint32_t k = atomicAdd(&s.ctr->vm_pool_next, 1u);
+        if (k >= s.pool_n) return false;
+        *s.deep = s.pool + (size_t)k * lpx::VM_STACK_WORDS;
+    }
+    cap = lpx::VM_STACK_WORDS;
+    return true;
+}
+__device__ __forceinline__ int vm_eval_span(const DevPlan& P, uint32_t r, const uint8_t* __restrict__ text, uint32_t ls, uint32_t le,
+                                            uint32_t* pool, uint32_t pool_n, Counters* ctr, uint32_t* span) {
     lpx::VmView v;
     v.code = reinterpret_cast<const lpx::VmCode*>(P.vm_code) + P.rx_vm_off[r];
     v.set_off = P.vm_set_off + P.rx_vm_set_base[r];
     v.set_data = P.vm_set_ranges;
     v.n_slots = P.rx_vm_slots[r];
     v.first = P.rx_vm_first + (size_t)r * 8;
-    const int res = lpx::vm_find(v, text, ls, le, stack, lpx::VM_STACK_WORDS, lpx::VM_MAX_STEPS);
+    uint32_t top[VM_TOP_WORDS];
+    uint32_t* deep = nullptr;
+    const int res = lpx::vm_find(v, text, ls, le, VmStack{top, &deep, pool, pool_n, ctr}, VM_TOP_WORDS, lpx::VM_MAX_STEPS, span);
     if (res < 0) { atomicOr(&ctr->overflow, 16u); atomicAdd(&ctr->n_budget, 1u); }
-    return res > 0;
+    return res;
+}
+__device__ __forceinline__ bool vm_eval(const DevPlan& P, uint32_t r, const uint8_t* __restrict__ text, uint32_t ls, uint32_t le,
+                                        uint32_t* pool, uint32_t pool_n, Counters* ctr) {
+    return vm_eval_span(P, r, text, ls, le, pool, pool_n, ctr, nullptr) > 0;
 }
 // LP_OPT_SPANS: Matcher.start()/end() of the first find() of each event's primary regex on its line.
 __global__ void __launch_bounds__(128) k_spans(const unsigned long long* __restrict__ ev_key, const Counters* ctr, uint32_t m_cap, DevPlan P,
                                                const uint8_t* __restrict__ text, const uint32_t* __restrict__ line_start,
-                                               const uint32_t* __restrict__ line_end, uint32_t* __restrict__ vm_stack, Counters* ctr_w,
+                                               const uint32_t* __restrict__ line_end, uint32_t* __restrict__ vm_pool, uint32_t vm_pool_n, Counters* ctr_w,
                                                uint32_t* __restrict__ span_start, uint32_t* __restrict__ span_end) {
     const uint32_t m = min(ctr->n_events, m_cap);
     const uint32_t stride = gridDim.x * blockDim.x;
-    uint32_t* stack = vm_stack + (size_t)(blockIdx.x * blockDim.x + threadIdx.x) * lpx::VM_STACK_WORDS;
     for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < m; e += stride) {
         const unsigned long long k = ev_key[e];
         const uint32_t g = (uint32_t)(k >> P.pb), p = (uint32_t)(k & ((1ull << P.pb) - 1ull));
         const uint32_t r = P.pat_primary[p], ls = line_start[g], le = line_end[g];
-        lpx::VmView v;
-        v.code = reinterpret_cast<const lpx::VmCode*>(P.vm_code) + P.rx_vm_off[r];
-        v.set_off = P.vm_set_off + P.rx_vm_set_base[r];
-        v.set_data = P.vm_set_ranges;
-        v.n_slots = P.rx_vm_slots[r];
-        v.first = P.rx_vm_first + (size_t)r * 8;
         uint32_t span[2] = {ls, ls};
-        const int res = lpx::vm_find(v, text, ls, le, stack, lpx::VM_STACK_WORDS, lpx::VM_MAX_STEPS, span);
-        if (res < 0) { atomicOr(&ctr_w->overflow, 16u); atomicAdd(&ctr_w->n_budget, 1u); }
+        const int res = vm_eval_span(P, r, text, ls, le, vm_pool, vm_pool_n, ctr_w, span);
         span_start[e] = res > 0 ? span[0] - ls : 0xFFFFFFFFu;     // the automaton said the line matches; a miss here would be a bug
         span_end[e] = res > 0 ? span[1] - ls : 0xFFFFFFFFu;
     }
 }
+// One evaluation per lane, but only L lanes of a warp take one: the lanes of a warp interpret in lock step, so a warp
+// costs the SUM of its lanes' divergent paths, and with a few ten thousand evaluations on an otherwise idle GPU the
+// longest warp is the kernel's duration (424 us with 32 evaluations per warp on C3, whose longest single one takes
+// 215 interpreter steps). L = evaluations / resident warps, rounded up.
 __global__ void __launch_bounds__(128) k_verify_vm(VerifyArgs a, DevPlan P) {
     const uint32_t n = min(a.ctr->n_vm_tasks, a.vm_task_cap);
-    const uint32_t stride = gridDim.x * blockDim.x;
-    const uint32_t rounds = (n + stride - 1) / stride;
-    uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t* stack = a.vm_stack + (size_t)t * lpx::VM_STACK_WORDS;
-    for (uint32_t it = 0; it < rounds; ++it, t += stride) {
+    const uint32_t warps = gridDim.x * (blockDim.x >> 5);
+    const uint32_t L = min(32u, max(1u, (n + warps - 1) / warps));
+    const uint32_t lane = threadIdx.x & 31, w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    for (uint32_t base = 0; base < n; base += warps * L) {       // uniform trip count: emit_record is a warp collective
+        const uint32_t t = base + w * L + lane;
         bool hit = false;
         uint32_t r = 0, g = 0;
-        if (t < n) {
+        if (lane < L && t < n) {
             const unsigned long long task = a.vm_tasks[t];
             r = (uint32_t)(task >> 32);
             g = (uint32_t)task;
-            hit = vm_eval(P, r, a.text, a.line_start[g], a.line_end[g], stack, a.ctr);
+            hit = vm_eval(P, r, a.text, a.line_start[g], a.line_end[g], a.vm_stack, a.vm_pool_n, a.ctr);
         }
         emit_record(a.ctr, a.recs, a.rec_cap, P.gb, hit, r, g);
     }
@@ -504,7 +532,6 @@ __global__ void __launch_bounds__(128) k_verify_vm_always(VerifyArgs a, DevPlan 
     const uint32_t stride = gridDim.x * blockDim.x;
     const uint32_t rounds = (a.n_lines_total + stride - 1) / stride;
     uint32_t g = blockIdx.x * blockDim.x + threadIdx.x;
-    uint32_t* stack = a.vm_stack + (size_t)g * lpx::VM_STACK_WORDS;
     for (uint32_t it = 0; it < rounds; ++it, g += stride) {
         bool live = g < a.n_lines_total;
         uint32_t ls = 0, le = 0;
@@ -515,7 +542,7 @@ __global__ void __launch_bounds__(128) k_verify_vm_always(VerifyArgs a, DevPlan 
         }
         for (uint32_t q = 0; q < P.n_always_vm; ++q) {
             const uint32_t r = P.always_vm_list[q];
-            const bool hit = live && vm_eval(P, r, a.text, ls, le, stack, a.ctr);
+            const bool hit = live && vm_eval(P, r, a.text, ls, le, a.vm_stack, a.vm_pool_n, a.ctr);
             emit_record(a.ctr, a.recs, a.rec_cap, P.gb, hit, r, g);
         }
     }

@@ -107,6 +107,7 @@ struct Counters {
     unsigned int n_lines_total;    // newlines + logs (G), published by k_scan_tiles
     unsigned int n_items[4];       // (literal occurrence, regex) pairs per verification class, k_confirm -> k_resolve
     unsigned int n_budget;         // (line, regex) evaluations the backtracking verifier gave up on (step / stack budget)
+    unsigned int vm_pool_next;     // deep backtracking stacks handed out so far in this call
 };
 
 }  // namespace lpk

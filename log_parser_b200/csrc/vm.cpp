@@ -20,6 +20,7 @@ struct Emitter {
     explicit Emitter(VmProgram& prog, int n_groups) : p(prog), next_slot(2 * (uint32_t)n_groups) {}
 
     int pc() const { return (int)p.code.size(); }
+    bool seek_start = false;     // the next look-around generated tests its condition at the start of the match
     int emit(uint8_t op, int a = 0, int b = 0, uint8_t flag = 0) {
         if (p.code.size() >= MAX_CODE) throw RegexUnsupported("pattern expands to too much backtracking code");
         VmInsn i{};
@@ -144,7 +145,8 @@ struct Emitter {
             case AstKind::Backref: emit(VM_BACKREF, a.group, 0, a.icase ? 1 : 0); break;
             case AstKind::Look: {
                 const Ast& body = *a.kids[0];
-                const int begin = emit(VM_LOOK_BEGIN, 0, 0, a.neg ? 1 : 0);
+                const int begin = emit(VM_LOOK_BEGIN, 0, 0, (a.neg ? 1 : 0) | (seek_start ? 2 : 0));
+                seek_start = false;
                 if (!a.behind) {
                     gen(body);
                 } else {
@@ -219,9 +221,31 @@ FirstSet first_set(const Ast& a) {
     r.unknown = true;
     return r;
 }
+bool has_backref(const Ast& a);
+bool has_capture(const Ast& a) {
+    if (a.kind == AstKind::Group && a.group >= 0) return true;
+    for (const auto& k : a.kids) if (has_capture(*k)) return true;
+    return false;
+}
+bool has_unbounded_repeat(const Ast& a) {
+    if (a.kind == AstKind::Repeat && a.max < 0) return true;
+    for (const auto& k : a.kids) if (has_unbounded_repeat(*k)) return true;
+    return false;
+}
+bool deferrable_look(const Ast& a) {
+    return a.kind == AstKind::Look && !a.behind && !has_capture(*a.kids[0]) && !has_backref(*a.kids[0]) && has_unbounded_repeat(*a.kids[0]);
+}
 bool has_backref(const Ast& a) {
     if (a.kind == AstKind::Backref) return true;
     for (const auto& k : a.kids) if (has_backref(*k)) return true;
+    return false;
+}
+// Constructs that java.util.regex does not backtrack into: a capture made inside one survives the failure of what
+// follows it (Pattern.Pos / Neg / Behind / Ques-Curly possessive / atomic groups do not restore the groups), so an
+// attempt that fails at one start position can leave a group set for the attempt at the next one.
+bool keeps_captures_on_failure(const Ast& a) {
+    if (a.kind == AstKind::Look || a.kind == AstKind::Atomic || (a.kind == AstKind::Repeat && a.mode == 2)) return true;
+    for (const auto& k : a.kids) if (keeps_captures_on_failure(*k)) return true;
     return false;
 }
 }  // namespace
@@ -230,10 +254,29 @@ void build_vm(const ParsedRegex& rx, VmProgram& out) {
     out = VmProgram();
     {
         const FirstSet f = first_set(*rx.root);
-        if (!f.nullable && !f.unknown && !has_backref(*rx.root)) for (int i = 0; i < 8; ++i) out.first[i] = f.b[i];
+        // Start positions whose byte no match can begin with are skipped. With a back-reference that is only sound when
+        // failed attempts leave no captures behind: groups are cleared once per find(), not per start position, and
+        // GroupTail / GroupCurly restore them on failure, the constructs named above do not.
+        const bool leaky = has_backref(*rx.root) && keeps_captures_on_failure(*rx.root);
+        if (!f.nullable && !f.unknown && !leaky) for (int i = 0; i < 8; ++i) out.first[i] = f.b[i];
     }
     Emitter e(out, rx.n_groups);
-    e.gen(*rx.root);
+    // Leading look-arounds with an unbounded walk inside ((?=.*\[tag\])phrase ...) are tested after the rest of the
+    // pattern has matched instead of before it at every start position. A look-around is zero-width and, without
+    // groups or back-references inside, neither changes nor reads anything the rest can see, so "condition at the
+    // start AND rest from the start" gives the same answer, start and end in either order; only the cost moves:
+    // the rest usually fails after a byte or two. When the deferred condition fails no other way of matching the
+    // rest can help (the condition does not depend on it), so the attempt at this start position ends
+    // (VM_ABORT_MARK), as it would have in the written order.
+    size_t lead = 0;
+    const Ast& root = *rx.root;
+    if (root.kind == AstKind::Cat)
+        while (lead < root.kids.size() && deferrable_look(*root.kids[lead])) ++lead;
+    if (lead > 0 && lead < root.kids.size()) {
+        for (size_t k = lead; k < root.kids.size(); ++k) e.gen(*root.kids[k]);
+        e.emit(VM_ABORT_MARK);
+        for (size_t k = 0; k < lead; ++k) { e.seek_start = true; e.gen(*root.kids[k]); }
+    } else e.gen(root);
     e.emit(VM_MATCH);
     if (out.set_off.empty()) out.set_off.push_back(0);
     out.n_caps = 2 * (uint32_t)rx.n_groups;
@@ -251,6 +294,18 @@ int vm_match_host(const VmProgram& p, const uint8_t* s, size_t n) {
     v.first = p.first;
     std::vector<uint32_t> stack(VM_STACK_WORDS);
     return vm_find(v, s, 0, (uint32_t)n, stack.data(), (uint32_t)stack.size(), VM_MAX_STEPS);
+}
+int vm_steps_host(const VmProgram& p, const uint8_t* s, size_t n) {
+    VmView v;
+    v.code = reinterpret_cast<const VmCode*>(p.code.data());
+    v.set_off = p.set_off.data();
+    v.set_data = p.set_ranges.data();
+    v.n_slots = p.n_slots;
+    v.first = p.first;
+    std::vector<uint32_t> stack(VM_STACK_WORDS);
+    int used = 0;
+    vm_find(v, s, 0, (uint32_t)n, stack.data(), (uint32_t)stack.size(), VM_MAX_STEPS, nullptr, &used);
+    return used;
 }
 int vm_span_host(const VmProgram& p, const uint8_t* s, size_t n, uint32_t* span) {
     VmView v;

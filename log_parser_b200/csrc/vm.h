@@ -37,6 +37,8 @@ void build_vm(const ParsedRegex& rx, VmProgram& out);
 
 // 1 match, 0 no match, -1 backtracking budget exhausted.
 int vm_match_host(const VmProgram& p, const uint8_t* s, size_t n);
+// interpreter steps that find() took on this input (tuning aid)
+int vm_steps_host(const VmProgram& p, const uint8_t* s, size_t n);
 // Matcher.start()/end() of the first find() as byte offsets (span[0], span[1]); return value as vm_match_host.
 int vm_span_host(const VmProgram& p, const uint8_t* s, size_t n, uint32_t* span);
 

@@ -29,10 +29,11 @@ enum VmOp : uint8_t {
     VM_DATA,
     VM_ATOMIC_BEGIN,
     VM_ATOMIC_END,
-    VM_LOOK_BEGIN,    // flag bit0 = negative; a = pc after the matching VM_LOOK_END
+    VM_LOOK_BEGIN,    // flag bit0 = negative, bit1 = the condition is tested at the start of the match (a deferred leading look-around); a = pc after the matching VM_LOOK_END
     VM_LOOK_END,
     VM_BACK,          // a = code points to step back, b = slot with the position to step back from
     VM_POSEQ,         // a = slot: pos must equal slots[a]
+    VM_ABORT_MARK,    // from here on, running out of alternatives ends the attempt at this start position (see build_vm)
     VM_MATCH
 };
 
@@ -56,7 +57,7 @@ constexpr int VM_MAX_STEPS = 1 << 26;          // interpreter steps per (line, r
 constexpr uint32_t VM_NONE = 0xFFFFFFFFu;
 
 // stack entry kinds (top 4 bits of word 0)
-enum : uint32_t { VK_CHOICE = 1, VK_UNDO, VK_BARRIER, VK_LOOKPOS, VK_LOOKNEG, VK_RANGE, VK_LAZY, VK_DATA };
+enum : uint32_t { VK_CHOICE = 1, VK_UNDO, VK_BARRIER, VK_LOOKPOS, VK_LOOKNEG, VK_RANGE, VK_LAZY, VK_DATA, VK_ABORT };
 
 LPX_HD uint32_t vm_decode(const uint8_t* s, uint32_t pos, uint32_t le, uint32_t& len) {
     const uint32_t c = s[pos];
@@ -87,6 +88,63 @@ LPX_HD bool vm_set_has(const VmView& v, uint32_t set, uint32_t cp) {
 }
 LPX_HD bool vm_word(uint32_t c) { return (c >= '0' && c <= '9') || (c >= 'A' && c <= 'Z') || c == '_' || (c >= 'a' && c <= 'z'); }
 LPX_HD bool vm_term(uint32_t c) { return c == '\n' || c == '\r' || c == 0x85 || c == 0x2028 || c == 0x2029; }
+
+// ASCII fast path of the interpreter's byte loops (a `.*` inside a look-ahead walks the rest of the line at every start
+// position; one dependent load per byte, plus the set's words, made that walk the whole cost of a C3 evaluation).
+// m[0..3]: a 128-bit set of ASCII bytes. Returns how many bytes from p on are ASCII members of the set, looking at no
+// more than `limit` bytes and not beyond `end`. On the device the text is read a word at a time.
+LPX_HD bool vm_ascii_in(uint32_t c, uint32_t m0, uint32_t m1, uint32_t m2, uint32_t m3) {
+    const uint32_t w = (c & 64u) ? ((c & 32u) ? m3 : m2) : ((c & 32u) ? m1 : m0);
+    return c < 128u && ((w >> (c & 31u)) & 1u);
+}
+LPX_HD uint32_t vm_run_ascii(const uint8_t* s, uint32_t p, uint32_t end, uint32_t limit, uint32_t m0, uint32_t m1, uint32_t m2, uint32_t m3) {
+    const uint32_t p0 = p;
+    if (end - p > limit) end = p + limit;
+#ifdef __CUDA_ARCH__
+    while (p < end) {
+        if ((p & 3u) == 0 && p + 4 <= end) {
+            const uint32_t w = *reinterpret_cast<const uint32_t*>(s + p);
+            uint32_t k = 0;
+            if (vm_ascii_in(w & 0xFFu, m0, m1, m2, m3)) { k = 1;
+                if (vm_ascii_in((w >> 8) & 0xFFu, m0, m1, m2, m3)) { k = 2;
+                    if (vm_ascii_in((w >> 16) & 0xFFu, m0, m1, m2, m3)) { k = 3;
+                        if (vm_ascii_in(w >> 24, m0, m1, m2, m3)) k = 4; } } }
+            p += k;
+            if (k < 4) break;
+        } else {
+            if (!vm_ascii_in(s[p], m0, m1, m2, m3)) break;
+            ++p;
+        }
+    }
+#else
+    while (p < end && vm_ascii_in(s[p], m0, m1, m2, m3)) ++p;
+#endif
+    return p - p0;
+}
+// the same walking down: how many bytes before p (not below `lo`) are ASCII members of the set
+LPX_HD uint32_t vm_run_ascii_back(const uint8_t* s, uint32_t p, uint32_t lo, uint32_t m0, uint32_t m1, uint32_t m2, uint32_t m3) {
+    const uint32_t p0 = p;
+#ifdef __CUDA_ARCH__
+    while (p > lo) {
+        if ((p & 3u) == 0 && p >= lo + 4) {
+            const uint32_t w = *reinterpret_cast<const uint32_t*>(s + p - 4);
+            uint32_t k = 0;
+            if (vm_ascii_in(w >> 24, m0, m1, m2, m3)) { k = 1;
+                if (vm_ascii_in((w >> 16) & 0xFFu, m0, m1, m2, m3)) { k = 2;
+                    if (vm_ascii_in((w >> 8) & 0xFFu, m0, m1, m2, m3)) { k = 3;
+                        if (vm_ascii_in(w & 0xFFu, m0, m1, m2, m3)) k = 4; } } }
+            p -= k;
+            if (k < 4) break;
+        } else {
+            if (!vm_ascii_in(s[p - 1], m0, m1, m2, m3)) break;
+            --p;
+        }
+    }
+#else
+    while (p > lo && vm_ascii_in(s[p - 1], m0, m1, m2, m3)) --p;
+#endif
+    return p0 - p;
+}
 
 LPX_HD bool vm_assert(int kind, bool unix_lines, const uint8_t* s, uint32_t ls, uint32_t le, uint32_t pos, long tpos) {
     switch (kind) {
@@ -119,11 +177,16 @@ LPX_HD bool vm_assert(int kind, bool unix_lines, const uint8_t* s, uint32_t ls, 
 }
 
 // Runs the program anchored at `start`. Returns 1 match, 0 no match, -1 budget exhausted.
-// `stack` holds `cap` 32-bit words; `steps` is decremented.
+// `stack` holds `cap` 32-bit words (anything indexable: a plain array on the host, a two-level stack on the device
+// that starts small and asks vm_stack_grow for its deep part when it runs out); `steps` is decremented.
+template <class Stack>
+LPX_HD bool vm_stack_grow(Stack&, uint32_t&) { return false; }      // a plain array cannot grow
+template <class Stack>
 LPX_HD int vm_run(const VmView& v, const uint8_t* s, uint32_t ls, uint32_t le, uint32_t start, long tpos,
-                  uint32_t* slots, uint32_t* stack, uint32_t cap, int& steps, uint32_t* end_out = nullptr) {
+                  uint32_t* slots, Stack stack, uint32_t cap, int& steps, uint32_t* end_out = nullptr) {
     uint32_t sp = 0, pc = 0, pos = start;
-#define VM_PUSH(w0, w1) do { if (sp + 2 > cap) return -1; stack[sp++] = (w0); stack[sp++] = (w1); } while (0)
+    bool aborting = false;
+#define VM_PUSH(w0, w1) do { if (sp + 2 > cap && !vm_stack_grow(stack, cap)) return -1; stack[sp++] = (w0); stack[sp++] = (w1); } while (0)
     for (;;) {
         if (--steps < 0) return -1;
         const VmCode in = v.code[pc];
@@ -182,9 +245,19 @@ LPX_HD int vm_run(const VmView& v, const uint8_t* s, uint32_t ls, uint32_t le, u
                 int cnt = 0;
                 uint32_t p = pos, after_min = pos;
                 const int first_stop = in.flag == 1 ? mn : (mx < 0 ? 0x7FFFFFFF : mx);
+                const uint32_t* const sd = v.set_data + v.set_off[set];
+                const uint32_t a0 = sd[0], a1 = sd[1], a2 = sd[2], a3 = sd[3];      // the set's ASCII part
                 while (cnt < first_stop && p < le) {
+                    // ASCII members in one go (up to the minimum first, so that after_min is exact), anything else one code point at a time
+                    const int want = cnt < mn ? mn - cnt : first_stop - cnt;
+                    const uint32_t k = vm_run_ascii(s, p, le, (uint32_t)want, a0, a1, a2, a3);
+                    if (k) {
+                        p += k; cnt += (int)k;
+                        if (cnt == mn) after_min = p;
+                        continue;
+                    }
                     uint32_t l; const uint32_t cp = vm_decode(s, p, le, l);
-                    if (!vm_set_has(v, set, cp)) break;
+                    if (cp < 128 || !vm_set_has(v, set, cp)) break;
                     p += l; ++cnt;
                     if (cnt == mn) after_min = p;
                 }
@@ -212,6 +285,7 @@ LPX_HD int vm_run(const VmView& v, const uint8_t* s, uint32_t ls, uint32_t le, u
             case VM_LOOK_BEGIN:
                 if (in.flag & 1) VM_PUSH((VK_LOOKNEG << 28) | (uint32_t)in.a, pos);
                 else VM_PUSH((VK_LOOKPOS << 28), pos);
+                if (in.flag & 2) pos = start;
                 ++pc;
                 break;
             case VM_LOOK_END: {
@@ -238,6 +312,7 @@ LPX_HD int vm_run(const VmView& v, const uint8_t* s, uint32_t ls, uint32_t le, u
             case VM_POSEQ:
                 if (pos == slots[in.a]) ++pc; else fail = true;
                 break;
+            case VM_ABORT_MARK: VM_PUSH((VK_ABORT << 28), 0); ++pc; break;
             case VM_MATCH: if (end_out) *end_out = pos; return 1;
             default: return -1;
         }
@@ -249,6 +324,8 @@ LPX_HD int vm_run(const VmView& v, const uint8_t* s, uint32_t ls, uint32_t le, u
             const uint32_t w0 = stack[sp], w1 = stack[sp + 1];
             const uint32_t kind = w0 >> 28, arg = w0 & 0x0FFFFFFFu;
             if (kind == VK_UNDO) { slots[arg] = w1; continue; }
+            if (kind == VK_ABORT) aborting = true;      // a deferred leading look-around said no: no alternative of what came before
+            if (aborting) continue;                     // can change that; unwind (captures are restored), then the attempt fails
             if (kind == VK_CHOICE || kind == VK_LOOKNEG) { pc = arg; pos = w1; break; }
             if (kind == VK_RANGE) {
                 const uint32_t lo = stack[sp - 1];
@@ -256,7 +333,18 @@ LPX_HD int vm_run(const VmView& v, const uint8_t* s, uint32_t ls, uint32_t le, u
                 // The continuation begins with a literal ASCII byte: give back straight to its previous
                 // occurrence. Every position skipped would fail at that VM_CHAR at once, with no side
                 // effect; an ASCII byte is always a code point boundary.
-                if (v.code[arg].op == VM_CHAR) { const uint8_t c = (uint8_t)v.code[arg].a; while (hi > lo && s[hi] != c) --hi; }
+                if (v.code[arg].op == VM_CHAR) {
+                    const uint32_t c = (uint8_t)v.code[arg].a;
+                    if (c < 128 && hi > lo && s[hi] != c) {      // walk down over "any byte but c" a word at a time
+                        const uint32_t bit = 1u << (c & 31u);
+                        const uint32_t n0 = ~((c >> 5) == 0 ? bit : 0u), n1 = ~((c >> 5) == 1 ? bit : 0u), n2 = ~((c >> 5) == 2 ? bit : 0u), n3 = ~((c >> 5) == 3 ? bit : 0u);
+                        for (;;) {
+                            hi -= vm_run_ascii_back(s, hi + 1, lo + 1, n0, n1, n2, n3);        // bytes in (lo, hi] that are ASCII and not c
+                            if (hi <= lo || s[hi] == c) break;
+                            --hi;                                                               // a non-ASCII byte: step over it
+                        }
+                    } else while (hi > lo && s[hi] != c) --hi;
+                }
                 if (hi > lo) { stack[sp + 1] = hi; sp += 2; }   // keep the entry for the next give-back
                 else sp -= 2;                                   // exhausted: drop the DATA word too
                 pc = arg; pos = hi;
@@ -286,8 +374,9 @@ LPX_HD int vm_run(const VmView& v, const uint8_t* s, uint32_t ls, uint32_t le, u
 
 // Matcher.find(): try every start position (code point boundaries), leftmost first.
 // span (optional, 2 words): Matcher.start() / Matcher.end() of that first match, as byte offsets into s.
-LPX_HD int vm_find(const VmView& v, const uint8_t* s, uint32_t ls, uint32_t le, uint32_t* stack, uint32_t cap, int max_steps,
-                   uint32_t* span = nullptr) {
+template <class Stack>
+LPX_HD int vm_find(const VmView& v, const uint8_t* s, uint32_t ls, uint32_t le, Stack stack, uint32_t cap, int max_steps,
+                   uint32_t* span = nullptr, int* steps_used = nullptr) {
     long tpos = -1;
     const uint32_t n = le - ls;
     if (n >= 1 && s[le - 1] == '\r') tpos = (long)le - 1;
@@ -306,11 +395,16 @@ LPX_HD int vm_find(const VmView& v, const uint8_t* s, uint32_t ls, uint32_t le, 
     }
     for (;;) {
         if (skip) {       // next start position whose byte a match can begin with (none: no match; such patterns are not nullable)
-            while (start < le && !((f[s[start] >> 5] >> (s[start] & 31u)) & 1u)) ++start;
+            for (;;) {      // ASCII bytes that no match begins with, a word at a time; other bytes one by one
+                start += vm_run_ascii(s, start, le, le - start, ~f[0], ~f[1], ~f[2], ~f[3]);
+                if (start >= le || ((f[s[start] >> 5] >> (s[start] & 31u)) & 1u)) break;
+                ++start;
+            }
             if (start >= le) return 0;
         }
         const int r = vm_run(v, s, ls, le, start, tpos, slots, stack, cap, steps, span ? span + 1 : nullptr);
         if (r > 0 && span) span[0] = start;
+        if (steps_used) *steps_used = max_steps - steps;
         if (r != 0) return r;
         if (start >= le) return 0;
         uint32_t l;

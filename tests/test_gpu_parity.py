@@ -204,6 +204,27 @@ def test_backtracking_budget_degrades_to_a_count(parser):
     assert parser.analyze(b"aba\nneedle-here\n").budget_exceeded == 0
 
 
+def test_deep_backtracking_stack_comes_from_the_pool(parser, oracle):
+    """An evaluation whose backtracking stack outgrows the thread's local part (an alternation loop pushes one choice
+    per iteration) continues on a deep stack taken from the pool: same events as the oracle, nothing abandoned.
+    Many such lines at once, so that several threads hold a deep stack at the same time."""
+    pats = [PatternSpec(id="deep", primary_regex=r"(k)(?:a|b)*c\1", confidence=0.5), PatternSpec(id="plain", primary_regex="needle-here", confidence=0.5)]
+    rng = random.Random(5)
+    lines = []
+    for i in range(300):
+        body = "".join(rng.choice("ab") for _ in range(rng.randint(150, 700)))
+        lines.append("k" + body + ("ck" if i % 3 else "cz"))
+        if i % 50 == 0:
+            lines.append("xx needle-here")
+    log = ("\n".join(lines) + "\n").encode()
+    parser.load_patterns(pats)
+    res = parser.analyze(log)
+    ora = oracle.analyze(ScoringConfig(), pats, log)
+    assert len(ora.line) >= 200
+    assert res.budget_exceeded == 0
+    _check(res, ora)
+
+
 def test_c3_nonregular_patterns(parser, oracle):
     """configs[2] shape: look-around / back-reference / possessive+atomic primaries take the
     backtracking verifier on prefiltered candidate lines; results must still equal the oracle's."""

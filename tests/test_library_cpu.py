@@ -245,7 +245,43 @@ def test_backtracking_bytecode_vs_oracle_random(lib, oracle):
     assert checked > 5000 and budget < checked // 100
 
 
+def test_deferred_leading_lookaround_vs_oracle_random(lib, oracle):
+    """build_vm tests a leading look-ahead with an unbounded walk inside after the rest of the pattern has matched
+    (vm.cpp); the oracle evaluates it where java.util.regex does, first. Same find() result, same span; also with
+    captures and back-references in the rest, and with the look-ahead's own failure (VM_ABORT_MARK)."""
+    rng = random.Random(4)
+    checked = matched = 0
+    while checked < 6000:
+        def sub(regular):
+            return Gen(rng, regular_only=regular, max_depth=2).regex()[0]
+        cond = re.sub(r"\((?!\?)", "(?:", sub(True))
+        walk = rng.choice([".*", r"\w+", ".+?", "[^E]*", "(?:ab|c)*"])
+        look = rng.choice(["(?=", "(?!"]) + rng.choice([walk + cond, cond + walk, walk + cond + walk]) + ")"
+        if rng.random() < 0.3:
+            look += rng.choice(["(?=", "(?!"]) + walk + re.sub(r"\((?!\?)", "(?:", sub(True)) + ")"
+        j = look + sub(rng.random() < 0.5)
+        try:
+            o = oracle.Regex(j)
+            d = binding.DebugRegex(j)
+        except (oracle.OracleSyntaxError, oracle.OracleUnsupported, binding.UnsupportedRegexError, binding.PatternSyntaxError):
+            continue
+        for _k in range(8):
+            t = gen_text(rng, maxlen=24)
+            got = d.match(t)
+            if got < 0:
+                continue
+            assert bool(got) == o.find(t), (j, t)
+            checked += 1
+            if got:
+                matched += 1
+                cs, ce = o.span(t)
+                assert tuple(d.span(t)) == (len(t[:cs].encode()), len(t[:ce].encode())), (j, t)
+    assert matched > 300
+
+
 @pytest.mark.parametrize("pat,text", [
+    (r"(?=.*\[tag1\])(\w+) lost \1", "ab lost ab [tag1]"), (r"(?=.*\[tag1\])(\w+) lost \1", "ab lost ab [tag2]"),
+    (r"(?!.*skip)(?=.*x)a(b|c)d", "acd x"), (r"(?!.*skip)(?=.*x)a(b|c)d", "acd x skip"), (r"(?=.*z)(?:a|ab)(?:c|bcd)", "abcd z"),
     (r"(?<![\w.])FooError(?!\w)", "x FooError: y"), (r"(?<![\w.])FooError(?!\w)", "x.FooError"),
     (r"Foo: (\w+) .*\b\1\b", "Foo: abc failed for abc again"), (r"Foo: (\w+) .*\b\1\b", "Foo: abc failed for abd again"),
     (r"\bFoo(?>: \w++)", "a Foo: bar"), (r"(?m)^a", "b\ra"), (r"(?m)a$", "a\rb"), (r"(?m)^$", ""),
