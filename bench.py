@@ -274,6 +274,43 @@ def parity_check(lp, wl, text, offsets, rank: int, world: int, batch: bool, scfg
     return out
 
 
+def parity_check_lines(lp, wl, text, rank: int, world: int, scfg=None, min_lines: int = 20000):
+    """Line-range mode: the first `min_lines` lines of the log are cut over the ranks like the timed input and go
+    through the timed collective entry point; rank 0 puts the shards' events together and compares them with the
+    oracle's answer for the slice as one log."""
+    import numpy as np
+    import torch.distributed as dist
+
+    from log_parser_b200 import parallel
+    from log_parser_b200.model import ScoringConfig
+    from oracle import oracle as O
+
+    cut = -1
+    for _ in range(min_lines):
+        nxt = text.find(b"\n", cut + 1)
+        if nxt < 0:
+            break
+        cut = nxt
+    sl = text[:cut + 1] if cut >= 0 else text
+    res = parallel.analyze_range_dist(lp, sl, rank, world)
+    mine = {"line": np.array(res.line), "pattern": np.array(res.pattern), "score": np.array(res.score), "n": int(res.log_n_lines[0])}
+    parts = [None] * world
+    dist.all_gather_object(parts, mine)
+    out = {"checked_lines": 0, "events": 0, "ok": True, "ranks_checked": world,
+           "against": "oracle (C++ restatement of the reference path), through lp_analyze_range_dist_device (NCCL exchange, shards put together in rank order)"}
+    if rank == 0:
+        ora = O.analyze(scfg or ScoringConfig(), wl.patterns, sl)
+        line = np.concatenate([p["line"] for p in parts])
+        pat = np.concatenate([p["pattern"] for p in parts])
+        score = np.concatenate([p["score"] for p in parts])
+        ok = (all(p["n"] == ora.n_lines for p in parts) and len(line) == len(ora.line) and np.array_equal(line, ora.line)
+              and np.array_equal(pat, ora.pattern) and bool(np.all(np.abs(score - ora.score) <= 1e-9 * np.maximum(1.0, np.abs(ora.score)))))
+        out.update(checked_lines=int(ora.n_lines), events=int(len(ora.line)), ok=bool(ok))
+    box = [out]
+    dist.broadcast_object_list(box, src=0)
+    return box[0]
+
+
 def _emit(line: dict) -> None:
     """The one JSON line, written to the process's original stdout."""
     os.write(_STDOUT_FD, (json.dumps(line) + "\n").encode())
@@ -335,7 +372,7 @@ def main():
     if by_lines:
         config["logs_per_gpu"] = 1.0 / world
         config["parallelism"] = (f"ONE log cut by line range over {world} GPUs with halos of lp_range_halo_lines() lines; "
-                                 "one all-gather of the shard summaries (line counts, per-pattern counts, sequence-chain states)")
+                                 "one NCCL all-gather of the shard summaries (line counts, per-pattern counts, sequence-chain states) inside the library, composed on the device")
     if args.impl == "reference":
         if rank != 0:
             return 0
@@ -376,7 +413,7 @@ def main():
     lp = binding.LogParser(scfg, device=local_rank)
     lp.load_patterns(wl.patterns)
     P = len(wl.patterns)
-    if world > 1 and not by_lines:
+    if world > 1:
         parallel.init_library_comm(lp, rank, world)               # the library's own NCCL communicator
 
     log = text
@@ -400,9 +437,8 @@ def main():
 
     def step_device(i):
         d = copies[i % len(copies)]
-        if by_lines:
-            summary = lp.range_scan_device(d.data_ptr(), nbytes, halo_b, halo_a)
-            return lp.range_score(parallel.gather_summaries(summary, world), rank, world)
+        if by_lines:      # scan -> ncclAllGather of the shard summaries -> composition on the device -> score, one call
+            return lp.analyze_range_dist_device(d.data_ptr(), nbytes, halo_b, halo_a)
         if world > 1:
             return lp.analyze_batch_dist_device(d.data_ptr(), offsets)   # scan -> ncclAllGather of (P + 1) x u64 -> score, one call
         if batch:
@@ -411,9 +447,7 @@ def main():
 
     def step_host():
         if by_lines:
-            copies[0].copy_(host[:nbytes], non_blocking=False)
-            summary = lp.range_scan_device(copies[0].data_ptr(), nbytes, halo_b, halo_a)
-            return lp.range_score(parallel.gather_summaries(summary, world), rank, world)
+            return lp.analyze_range_dist_host_ptr(hptr, nbytes, halo_b, halo_a)
         if world > 1:
             return lp.analyze_batch_dist_host_ptr(hptr, offsets)         # the copy is cut in pieces and overlaps the scan
         if batch:
@@ -429,6 +463,10 @@ def main():
     for i in range(args.warmup):
         res = step_device(i)
     parity = None
+    if not args.no_parity and by_lines:
+        parity = parity_check_lines(lp, wl, text, rank, world, scfg)
+        for i in range(2):
+            res = step_device(i)
     if not args.no_parity and not by_lines:
         parity = parity_check(lp, wl, text, offsets, rank, world, batch, scfg)
         for i in range(2):
@@ -563,7 +601,7 @@ def main():
                                         "frac": phase_bytes / phase_s / 1e9 / peak}},
             "e2e": {"value": e2e_value, "unit": "lines/s", "h2d_bytes_per_step": int(nbytes), "d2h_bytes_per_step": d2h,
                     "gb_per_s": e2e_value * nbytes / lines_per_gpu / 1e9, "steps": e2e_steps,
-                    "entry_point": "lp_range_* after a blocking copy" if by_lines else "lp_analyze_batch_dist" if world > 1 else "lp_analyze_batch" if batch else "lp_analyze",
+                    "entry_point": "lp_analyze_range_dist" if by_lines else "lp_analyze_batch_dist" if world > 1 else "lp_analyze_batch" if batch else "lp_analyze",
                     "host_buffer": "page-locked, from lp_host_alloc", "h2d_ceiling": h2d_ceiling,
                     "two_request_threads": e2e_two},
             "parity": parity,

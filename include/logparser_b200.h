@@ -226,6 +226,16 @@ int lp_range_scan_device(lp_ctx* ctx, const uint8_t* d_text, size_t len, uint32_
                          uint32_t halo_after_lines, int options, uint64_t* summary_out);
 int lp_range_score(lp_ctx* ctx, const uint64_t* summaries /* [world][words] */, uint32_t rank, uint32_t world,
                    const uint64_t* prior_count, lp_result** out);
+/* The same with the exchange kept on the device, over the communicator of lp_comm_init (one process per GPU; every
+ * rank calls it once per step, ranks in text order): scan of this rank's piece, all-gather of the summaries over
+ * NVLink, composition on the device (prior counts, global line numbers, sequence thresholds), scoring. Nothing
+ * returns to the host between the scan and the events. Results as lp_range_scan_device + lp_range_score.
+ * lp_analyze_range_dist takes the piece in host memory (page-locked memory from lp_host_alloc lets the copy overlap
+ * the scan); `prior_count` is the window prior BEFORE the whole log, the same array on every rank. */
+int lp_analyze_range_dist_device(lp_ctx* ctx, const uint8_t* d_text, size_t len, uint32_t halo_before_lines,
+                                 uint32_t halo_after_lines, const uint64_t* prior_count, int options, lp_result** out);
+int lp_analyze_range_dist(lp_ctx* ctx, const uint8_t* text, size_t len, uint32_t halo_before_lines,
+                          uint32_t halo_after_lines, const uint64_t* prior_count, int options, lp_result** out);
 
 /* No counterpart in the reference. Line splitting (the String.split step only) for hosts that may
  * not allocate GPU memory themselves or let a library do it on their behalf: processes with a

@@ -88,7 +88,7 @@ EXPORTS = [
     "lp_result_free", "lp_get_timings", "lp_stream", "lp_split_lines_noalloc",
     "lp_counts_by_id", "lp_batch_scan_device_async", "lp_batch_score_gathered", "lp_comm_unique_id", "lp_comm_init",
     "lp_analyze_batch_dist_device", "lp_analyze_batch_dist", "lp_host_alloc", "lp_host_free", "lp_host_register",
-    "lp_host_unregister", "lp_range_halo_lines", "lp_range_summary_words", "lp_range_scan_device", "lp_range_score",
+    "lp_host_unregister", "lp_range_halo_lines", "lp_range_summary_words", "lp_range_scan_device", "lp_range_score", "lp_analyze_range_dist_device", "lp_analyze_range_dist",
 ]
 
 _lib = None
@@ -139,6 +139,8 @@ def load_library() -> C.CDLL:
     L.lp_range_summary_words.argtypes = [vp]
     L.lp_range_scan_device.argtypes = [vp, u8p, C.c_size_t, C.c_uint32, C.c_uint32, C.c_int, u64p]
     L.lp_range_score.argtypes = [vp, u64p, C.c_uint32, C.c_uint32, u64p, C.POINTER(vp)]
+    L.lp_analyze_range_dist_device.argtypes = [vp, u8p, C.c_size_t, C.c_uint32, C.c_uint32, u64p, C.c_int, C.POINTER(vp)]
+    L.lp_analyze_range_dist.argtypes = [vp, u8p, C.c_size_t, C.c_uint32, C.c_uint32, u64p, C.c_int, C.POINTER(vp)]
     L.lp_split_lines_noalloc.argtypes = [C.c_int, vp, C.c_size_t, vp, vp, C.c_size_t, vp, vp, C.c_char_p, C.c_size_t]
     _lib = L
     return L
@@ -471,6 +473,25 @@ class LogParser:
         keep, pp = self._prior(prior_count)
         out = C.c_void_p()
         rc = self.L.lp_range_score(self.h, sa.ctypes.data_as(C.POINTER(C.c_uint64)), rank, world, pp, C.byref(out))
+        if rc != LP_OK:
+            _raise(rc)
+        return self._take(out)
+
+    def analyze_range_dist_device(self, dev_ptr: int, length: int, halo_before: int, halo_after: int, prior_count=None,
+                                  options: int = 0) -> Result:
+        """Collective: this rank's piece of ONE log cut by line range; summaries exchanged and composed on the device."""
+        keep, pp = self._prior(prior_count)
+        out = C.c_void_p()
+        rc = self.L.lp_analyze_range_dist_device(self.h, dev_ptr, length, halo_before, halo_after, pp, options, C.byref(out))
+        if rc != LP_OK:
+            _raise(rc)
+        return self._take(out)
+
+    def analyze_range_dist_host_ptr(self, host_ptr: int, length: int, halo_before: int, halo_after: int, prior_count=None,
+                                    options: int = 0) -> Result:
+        keep, pp = self._prior(prior_count)
+        out = C.c_void_p()
+        rc = self.L.lp_analyze_range_dist(self.h, host_ptr, length, halo_before, halo_after, pp, options, C.byref(out))
         if rc != LP_OK:
             _raise(rc)
         return self._take(out)

@@ -191,7 +191,7 @@ struct lp_ctx {
         bool range = false;                 // line-range shard: events only for the lines between the halos
         uint32_t halo_before = 0, halo_after = 0;
     } pend;
-    DevBuf seq_tab_off, seq_tab, seq_T, prior_eff, any_flag, dist_mine, dist_all;
+    DevBuf seq_tab_off, seq_tab, seq_T, prior_eff, any_flag, dist_mine, dist_all, range_dev;
     void* nccl_comm = nullptr;              // ncclComm_t of lp_comm_init (NCCL is loaded at run time, see NcclApi)
     std::function<void()> after_unique;     // run_scan calls it once the unique records exist (the collective starts its exchange there)
     cudaEvent_t dist_ev[2] = {nullptr, nullptr};
@@ -801,7 +801,11 @@ void wait_for_stream(cudaStream_t st) {
 }
 
 // ---- phase 2: frequency ranks, scoring, ranking, result download (one synchronisation)
-struct RangeGlobal { long long line_base, n_global; const long long* seq_T; };   // seq_T: host array [n_seq]
+struct RangeGlobal {
+    long long line_base, n_global; const long long* seq_T;        // seq_T: host array [n_seq]
+    const long long* dev_range = nullptr;                         // or: {line_base, n_global, error} and seq_T composed on the device (k_range_compose)
+    const long long* dev_seq_T = nullptr;
+};
 
 lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* rgl = nullptr,
                      const unsigned long long* prior_dev = nullptr, const unsigned long long* flag_dev = nullptr,
@@ -825,7 +829,7 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
     const size_t o_ctr = take(sizeof(Counters)), o_line = take((size_t)mc * 4), o_pat = take((size_t)mc * 4), o_score = take((size_t)mc * 8),
                  o_rank = take((size_t)mc * 4), o_fac = take(want_factors ? (size_t)mc * 56 : 0),
                  o_delta = take((size_t)np * 8), o_nl = take((size_t)n_logs * 4), o_leb = take((size_t)(n_logs + 1) * 8),
-                 o_ss = take(want_spans ? (size_t)mc * 4 : 0), o_se = take(want_spans ? (size_t)mc * 4 : 0), o_flag = take(8);
+                 o_ss = take(want_spans ? (size_t)mc * 4 : 0), o_se = take(want_spans ? (size_t)mc * 4 : 0), o_flag = take(32);
     c->out_arena.ensure(off);
     uint8_t* const arena = c->out_arena.as<uint8_t>();
     uint32_t* const d_rank = reinterpret_cast<uint32_t*>(arena + o_rank);
@@ -850,7 +854,10 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
     sa.out_score = reinterpret_cast<double*>(arena + o_score);
     sa.out_factors = want_factors ? reinterpret_cast<double*>(arena + o_fac) : nullptr;
     sa.sort_key = c->sort_key.as<unsigned long long>();
-    if (rgl) {
+    if (rgl && rgl->dev_range) {
+        sa.range_dev = rgl->dev_range; sa.n_global = 1; sa.core_lo = c->pend.halo_before;       // (n_global is read from range_dev by the kernel)
+        if (c->n_seq) sa.seq_T = rgl->dev_seq_T;
+    } else if (rgl) {
         sa.line_base = rgl->line_base; sa.n_global = rgl->n_global; sa.core_lo = c->pend.halo_before;
         if (c->n_seq) {
             c->seq_T.ensure((size_t)c->n_seq * 8);
@@ -902,7 +909,7 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
     // the small items (counters, per-pattern counts, per-log line counts and event ranges, status word) are
     // packed behind the event columns by one tiny kernel, then the arena goes to the host in one copy
     k_pack_tail<<<1, 256, 0, st>>>(ctr, c->freq_delta.as<unsigned long long>(), np, c->n_lines.as<uint32_t>(), n_logs,
-                                   c->log_event_begin.as<unsigned long long>(), flag_dev, reinterpret_cast<Counters*>(arena + o_ctr),
+                                   c->log_event_begin.as<unsigned long long>(), flag_dev, rgl ? rgl->dev_range : nullptr, reinterpret_cast<Counters*>(arena + o_ctr),
                                    reinterpret_cast<unsigned long long*>(arena + o_delta), reinterpret_cast<uint32_t*>(arena + o_nl),
                                    reinterpret_cast<unsigned long long*>(arena + o_leb), reinterpret_cast<unsigned long long*>(arena + o_flag));
     c->launches += 1;
@@ -934,7 +941,13 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
     res->n_patterns = np;
     res->log_n_lines.resize(n_logs);
     for (uint32_t k = 0; k < n_logs; ++k) res->log_n_lines[k] = reinterpret_cast<uint32_t*>(hs + o_nl)[k];
-    if (rgl) res->log_n_lines[0] = (uint64_t)rgl->n_global;      // a shard reports the whole log's line count
+    if (rgl && rgl->dev_range) {
+        long long rw[3];
+        memcpy(rw, hs + o_flag + 8, sizeof rw);
+        if (rw[2] == 1) throw std::invalid_argument("halo_before exceeds the lines of the lower shards");
+        if (rw[2] == 2) throw std::invalid_argument("shard summaries come from a different pattern set");
+        res->log_n_lines[0] = (uint64_t)rw[1];
+    } else if (rgl) res->log_n_lines[0] = (uint64_t)rgl->n_global;      // a shard reports the whole log's line count
     res->log_event_begin.assign(reinterpret_cast<uint64_t*>(hs + o_leb), reinterpret_cast<uint64_t*>(hs + o_leb) + n_logs + 1);
     if (options & LP_OPT_LINE_OFFSETS) {
         res->has_offsets = true;
@@ -1127,7 +1140,7 @@ void lp_destroy(lp_ctx* c) {
                      &c->ev_log, &c->slot_key, &c->slot_key_alt, &c->ev_idx, &c->ev_idx_alt, &c->rank_in_slot, &c->freq_delta, &c->prior,
                      &c->out_arena, &c->sort_key, &c->sort_key_alt, &c->order, &c->order_alt,
                      &c->log_sorted, &c->log_sorted_alt, &c->log_event_begin, &c->n_unique, &c->d_lut,
-                     &c->f_bitmap, &c->f_key, &c->f_lits, &c->f_bytes, &c->f_bits, &c->f_gkeys, &c->fs_lists, &c->line_skip, &c->items, &c->ss_keys, &c->ss_idx, &c->seq_tab_off, &c->seq_tab, &c->seq_T, &c->prior_eff, &c->any_flag, &c->dist_mine, &c->dist_all};
+                     &c->f_bitmap, &c->f_key, &c->f_lits, &c->f_bytes, &c->f_bits, &c->f_gkeys, &c->fs_lists, &c->line_skip, &c->items, &c->ss_keys, &c->ss_idx, &c->seq_tab_off, &c->seq_tab, &c->seq_T, &c->prior_eff, &c->any_flag, &c->dist_mine, &c->dist_all, &c->range_dev};
     for (DevBuf* b : all) b->release();
     if (c->nccl_comm) nccl_comm_destroy(c->nccl_comm);
     c->stage.release();
@@ -1508,6 +1521,95 @@ int lp_range_score(lp_ctx* c, const uint64_t* summaries, uint32_t rank, uint32_t
             throw LimitFail("internal: estimates validated by lp_range_scan_device were exceeded in lp_range_score");
         }
     });
+}
+
+// One log cut by line range over the communicator of lp_comm_init, exchange on the device: this rank scans its piece
+// (core lines + halos), its summary [per-pattern counts of the core lines, status, core lines, chain tables] is
+// all-gathered over NVLink on the second stream, k_range_compose turns the gathered summaries into this shard's prior
+// counts, place in the log and sequence thresholds, and k_score waits for that. Nothing comes back to the host before
+// the events do. Collective: every rank calls it once per step; a rank whose scratch estimates were too small makes
+// all ranks repeat the step (they see it in the gathered status words). Same results as lp_range_scan_device +
+// lp_range_score, which remain for callers that run the exchange themselves.
+static int analyze_range_dist(lp_ctx* c, const uint8_t* text, bool on_host, size_t len, uint32_t halo_before, uint32_t halo_after,
+                              const uint64_t* prior_count, int options, lp_result** out) {
+    if (!c || !out) { g_last_error = "NULL argument"; return LP_ERR_INVALID; }
+    *out = nullptr;
+    return guarded(c, [&] {
+        std::lock_guard<std::mutex> lk(c->mu);
+        if (!c->loaded) throw std::invalid_argument("lp_load_patterns has not been called");
+        if (!c->nccl_comm) throw std::invalid_argument("lp_comm_init has not been called on this context");
+        if (on_host && len && !text) throw std::invalid_argument("text is NULL");
+        const uint8_t* d_text = on_host ? stage_host_log(c, text, len) : text;
+        struct DropHostSrc { lp_ctx* c; ~DropHostSrc() { c->host_src = nullptr; } } drop{c};
+        const uint32_t np = c->dp.n_pat, world = c->comm_world, rank = c->comm_rank, n_tab = c->h_seq_tab_off[c->n_seq];
+        const size_t words = (size_t)np + 3 + n_tab;
+        c->dist_mine.ensure(words * 8);
+        c->dist_all.ensure(words * 8 * world);
+        c->prior_eff.ensure((size_t)std::max<uint32_t>(np, 1) * 8);
+        c->any_flag.ensure(8);
+        c->seq_T.ensure((size_t)std::max<uint32_t>(c->n_seq, 1) * 8);
+        c->range_dev.ensure(32);
+        for (int k = 0; k < 2; ++k) if (!c->dist_ev[k]) CK(cudaEventCreateWithFlags(&c->dist_ev[k], cudaEventDisableTiming));
+        const unsigned long long* prior_in = nullptr;
+        if (prior_count && np) {
+            c->prior.ensure((size_t)np * 8);
+            CK(cudaMemcpyAsync(c->prior.p, prior_count, (size_t)np * 8, cudaMemcpyHostToDevice, c->stream));
+            prior_in = c->prior.as<unsigned long long>();
+        }
+        const uint64_t off[2] = {0, (uint64_t)len};
+        const RangeShard rg{halo_before, halo_after};
+        for (int round = 0;; ++round) {
+            if (round > 16) throw LimitFail("scratch estimates did not settle");
+            run_scan(c, d_text, len, off, 1, options, &rg);
+            unsigned long long* mine = c->dist_mine.as<unsigned long long>();
+            Counters* ctr = c->counters.as<Counters>();
+            CK(cudaMemsetAsync(mine, 0, words * 8, c->stream));
+            k_count_per_pattern<<<c->n_sm * 4, 256, 0, c->stream>>>(c->recs.as<unsigned long long>(), ctr, c->dp, mine, rg.halo_before, rg.halo_after);
+            k_publish_overflow<<<1, 128, 0, c->stream>>>(ctr, est_caps(c), mine, np, mine + np);
+            k_range_header<<<1, 32, 0, c->stream>>>(ctr, np, rg.halo_before, rg.halo_after, mine + np + 1);
+            if (n_tab)
+                k_range_tables<<<blocks_for(c->n_seq, 128), 128, 0, c->stream>>>(c->recs.as<unsigned long long>(), c->rx_begin.as<uint32_t>(), c->dp, ctr, c->n_seq,
+                                                                                  c->seq_tab_off.as<uint32_t>(), rg.halo_before, rg.halo_after, mine + np + 3);
+            CK(cudaEventRecord(c->dist_ev[0], c->stream));
+            CK(cudaStreamWaitEvent(c->copy_stream, c->dist_ev[0], 0));
+            nccl_check(nccl().AllGather(mine, c->dist_all.p, words, NCCL_UINT64, c->nccl_comm, c->copy_stream), "ncclAllGather");
+            k_range_compose<<<blocks_for(std::max<uint32_t>(std::max(np, c->n_seq), 1), 128), 128, 0, c->copy_stream>>>(
+                c->dist_all.as<unsigned long long>(), np, n_tab, rank, world, prior_in, rg.halo_before, c->n_seq, c->seq_tab_off.as<uint32_t>(), c->dp,
+                c->prior_eff.as<unsigned long long>(), c->any_flag.as<unsigned long long>(), c->range_dev.as<long long>(), c->seq_T.as<long long>());
+            CK(cudaEventRecord(c->dist_ev[1], c->copy_stream));
+            c->launches += 5;
+            std::unique_ptr<lp_result> res;
+            bool again = false;
+            unsigned long long flag = 0;
+            RangeGlobal rgl{0, 0, nullptr};
+            rgl.dev_range = c->range_dev.as<long long>(); rgl.dev_seq_T = c->seq_T.as<long long>();
+            try {
+                res.reset(run_score(c, nullptr, &rgl, c->prior_eff.as<unsigned long long>(), c->any_flag.as<unsigned long long>(), &flag, c->dist_ev[1]));
+            } catch (const Retry&) { again = true; }
+            if (again) {
+                CK(cudaMemcpy(&flag, c->any_flag.p, 8, cudaMemcpyDeviceToHost));
+                if (!flag) throw LimitFail("internal: a repeat was requested that the other ranks cannot see");
+                continue;
+            }
+            if ((flag & 16u) && (options & LP_OPT_STRICT_BUDGET)) throw std::overflow_error("backtracking verifier exceeded its step/stack budget");
+            if (flag & ~16ull) continue;                 // every rank sees the same words: all of them repeat
+            *out = res.release();
+            if (on_host) {
+                float ms = 0;
+                cudaEventElapsedTime(&ms, c->ev[5], c->ev[8]);
+                c->tm.h2d_ms = ms;
+            }
+            return;
+        }
+    });
+}
+int lp_analyze_range_dist_device(lp_ctx* c, const uint8_t* d_text, size_t len, uint32_t halo_before_lines, uint32_t halo_after_lines,
+                                 const uint64_t* prior_count, int options, lp_result** out) {
+    return analyze_range_dist(c, d_text, false, len, halo_before_lines, halo_after_lines, prior_count, options, out);
+}
+int lp_analyze_range_dist(lp_ctx* c, const uint8_t* text, size_t len, uint32_t halo_before_lines, uint32_t halo_after_lines,
+                          const uint64_t* prior_count, int options, lp_result** out) {
+    return analyze_range_dist(c, text, true, len, halo_before_lines, halo_after_lines, prior_count, options, out);
 }
 
 int lp_analyze_batch_device(lp_ctx* c, const uint8_t* d_logs, const uint64_t* offsets, size_t n_logs, const uint64_t* prior_count,

@@ -82,6 +82,7 @@ struct ScoreArgs {
     // count, the first own line, and the per-sequence chain thresholds composed over all shards
     long long line_base;
     long long n_global;
+    const long long* range_dev;      // {line_base, n_global} composed on the device from the gathered shard summaries (overrides the two above)
     uint32_t core_lo;
     const long long* seq_T;
 };
@@ -98,6 +99,7 @@ __global__ void __launch_bounds__(128) k_score(ScoreArgs a, DevPlan P, ScoreCfg 
     if (e >= a.m_cap) return;
     a.ev_idx[e] = e;
     if (e >= a.ctr->n_events) { a.sort_key[e] = ~0ull; a.ev_log[e] = a.n_logs; return; }      // padding sorts last
+    if (a.range_dev) { a.line_base = a.range_dev[0]; a.n_global = a.range_dev[1]; }
     const unsigned long long ek = a.ev_key[e];
     const uint32_t g = (uint32_t)(ek >> P.pb), p = (uint32_t)(ek & ((1ull << P.pb) - 1ull));
     const unsigned long long gmask = (1ull << P.gb) - 1ull;
@@ -323,6 +325,68 @@ __global__ void k_prior_prefix(const unsigned long long* __restrict__ all, uint3
         *any_flag = f;
     }
 }
+// Line-range shards with the exchange kept on the device. Every rank's summary, all-gathered into `all`, is
+// [n_pat core-line event counts, status word, core lines, n_pat, chain tables (k_range_tables)]; this kernel does for
+// one rank what lp_range_score does on the host: the counts seen before the shard's lines (window prior + lower
+// shards, per pattern id), the shard's place in the whole log, and per sequence the line where its last-but-one
+// event is first reachable when the shards are walked in order (ScoringService.java:296-305, 315-347).
+// range_out = {line_base, n_global, error}: error 1 = halo_before exceeds the lines of the lower shards, 2 = the
+// summaries come from different pattern sets.
+__global__ void k_range_header(const Counters* ctr, uint32_t n_pat, uint32_t halo_before, uint32_t halo_after, unsigned long long* __restrict__ dst) {
+    if (blockIdx.x || threadIdx.x) return;
+    const unsigned long long lines = ctr->total_nl + 1ull, halos = (unsigned long long)halo_before + halo_after;
+    dst[0] = lines > halos ? lines - halos : 0ull;
+    dst[1] = n_pat;
+}
+__global__ void k_range_compose(const unsigned long long* __restrict__ all, uint32_t n_pat, uint32_t n_tab, uint32_t rank, uint32_t world,
+                                const unsigned long long* __restrict__ prior_in, uint32_t halo_before, uint32_t n_seq,
+                                const uint32_t* __restrict__ tab_off, DevPlan P, unsigned long long* __restrict__ prior_out,
+                                unsigned long long* __restrict__ any_flag, long long* __restrict__ range_out, long long* __restrict__ seq_T) {
+    const uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
+    const size_t stride = (size_t)n_pat + 3 + n_tab;
+    if (t < n_pat) {
+        unsigned long long v = prior_in ? prior_in[t] : 0ull;
+        const int slot = P.pat_slot[t];
+        if (slot >= 0)
+            for (uint32_t j = P.slot_begin[slot]; j < P.slot_begin[slot + 1]; ++j) {
+                const uint32_t q = P.slot_pats[j];
+                for (uint32_t r = 0; r < rank; ++r) v += all[r * stride + q];
+            }
+        prior_out[t] = v;
+    }
+    if (t < n_seq) {
+        const uint32_t k = P.seq_ev_begin[t + 1] - P.seq_ev_begin[t];
+        long long T = -1;                                   // fewer than two events: the condition holds for every line
+        if (k >= 2) {
+            T = 0x7FFFFFFFFFFFFFFFll;                       // never reached
+            uint32_t state = 0;
+            long long core_base = 0;
+            for (uint32_t r = 0; r < world && state + 1 < k; ++r) {
+                const unsigned long long* s = all + r * stride;
+                const unsigned long long e = s[n_pat + 3 + tab_off[t] + state];
+                const uint32_t exit_state = (uint32_t)(e >> 32), at = (uint32_t)(e & 0xFFFFFFFFull);
+                if (exit_state + 1 >= k && at) { T = core_base + (long long)at - 1; break; }
+                state = exit_state;
+                core_base += (long long)s[n_pat + 1];
+            }
+        }
+        seq_T[t] = T;
+    }
+    if (t == 0) {
+        unsigned long long f = 0;
+        long long base = 0, n_global = 0, err = 0;
+        for (uint32_t r = 0; r < world; ++r) {
+            const unsigned long long* s = all + r * stride;
+            f |= s[n_pat];
+            if (s[n_pat + 2] != n_pat) err = 2;
+            if (r < rank) base += (long long)s[n_pat + 1];
+            n_global += (long long)s[n_pat + 1];
+        }
+        if (!err && base < (long long)halo_before) err = 1;
+        *any_flag = f;
+        range_out[0] = base - (long long)halo_before; range_out[1] = n_global; range_out[2] = err;
+    }
+}
 // Status word of a scan for the other ranks: non-zero exactly when check_estimates() on this rank will ask for a re-run.
 struct EstCaps { unsigned long long lines, cand, tasks, vm_tasks, recs, items, events; };
 // `counts` are this rank's per-pattern event counts: their sum is the number of events k_emit_events
@@ -348,9 +412,12 @@ __global__ void __launch_bounds__(128) k_publish_overflow(const Counters* ctr, E
 // Copies the small read-back items behind the event columns of the output arena (one block).
 __global__ void k_pack_tail(const Counters* ctr, const unsigned long long* __restrict__ freq_delta, uint32_t n_pat,
                             const uint32_t* __restrict__ n_lines, uint32_t n_logs, const unsigned long long* __restrict__ log_event_begin,
-                            const unsigned long long* flag, Counters* o_ctr, unsigned long long* __restrict__ o_delta,
+                            const unsigned long long* flag, const long long* range_dev, Counters* o_ctr, unsigned long long* __restrict__ o_delta,
                             uint32_t* __restrict__ o_nl, unsigned long long* __restrict__ o_leb, unsigned long long* o_flag) {
-    if (threadIdx.x == 0) { *o_ctr = *ctr; *o_flag = flag ? *flag : 0ull; }
+    if (threadIdx.x == 0) {     // o_flag: status word, then {line_base, n_global, error} of a line-range shard
+        *o_ctr = *ctr; o_flag[0] = flag ? *flag : 0ull;
+        for (int i = 0; i < 3; ++i) o_flag[1 + i] = range_dev ? (unsigned long long)range_dev[i] : 0ull;
+    }
     for (uint32_t p = threadIdx.x; p < n_pat; p += blockDim.x) o_delta[p] = freq_delta[p];
     for (uint32_t k = threadIdx.x; k < n_logs; k += blockDim.x) o_nl[k] = n_lines[k];
     // a single log: its events are all of them (k_log_event_begin is not launched)

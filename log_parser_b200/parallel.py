@@ -279,3 +279,17 @@ def analyze_range_sharded(engine, log: bytes, rank: int, world_size: int, prior_
     tb, te, before, after = split_line_ranges(log, world_size, engine.halo_lines(), end)[rank]
     summary = engine.scan(bytes(log[tb:te]), before, after)
     return engine.score(gather_summaries(summary, world_size, group), rank, world_size, prior_count)
+
+
+def analyze_range_dist(parser, log: bytes, rank: int, world_size: int, prior_count=None, options: int = 0):
+    """The same share of ONE log with the exchange inside the library (lp_analyze_range_dist_device over the
+    communicator of init_library_comm): the shard summaries are all-gathered over NVLink and composed on the
+    device, nothing returns to the host between the scan and the events. Returns None when the log has no lines."""
+    import torch
+
+    end = strip_trailing_separators(log)
+    if end == 0 and len(log) > 0:
+        return None
+    tb, te, before, after = split_line_ranges(log, world_size, max(1, parser.range_halo_lines()), end)[rank]
+    text = torch.from_numpy(np.frombuffer(bytes(log[tb:te]) or b"\0", dtype=np.uint8).copy()).cuda()
+    return parser.analyze_range_dist_device(text.data_ptr(), te - tb, before, after, prior_count, options)

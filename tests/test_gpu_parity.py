@@ -721,6 +721,91 @@ def test_library_nccl_batch_two_gpus(parser, tmp_path):
     np.testing.assert_array_equal(np.concatenate([p["score"] for p in parts]), whole.score)
 
 
+def _range_dist_worker(rank, world, port, path):
+    import os
+    import torch
+    import torch.distributed as dist
+    from log_parser_b200 import parallel
+
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    torch.cuda.set_device(rank)
+    dist.init_process_group("gloo", rank=rank, world_size=world)      # only carries the ncclUniqueId
+    wl = synth.make_patterns(40, 5152, scoring_heavy=True, noliteral=1)
+    log = synth.make_log(wl, 7000, 5151, hit_rate=0.05, symptom_rate=0.3, phase_rate=0.01, pool_blocks=1500) + b"\r\n\n\n"
+    prior = (np.arange(len(wl.patterns)) % 7).astype(np.uint64)
+    lp = binding.LogParser(ScoringConfig(), device=rank)
+    lp.load_patterns(wl.patterns)
+    parallel.init_library_comm(lp, rank, world)
+    for _ in range(3):       # the first steps repeat internally while the scratch estimates settle
+        r = parallel.analyze_range_dist(lp, log, rank, world, prior)
+    np.savez(os.path.join(path, f"r{rank}.npz"), line=np.array(r.line), pattern=np.array(r.pattern), score=np.array(r.score),
+             delta=np.array(r.freq_delta), n=np.array(r.log_n_lines))
+    dist.barrier()
+    dist.destroy_process_group()
+    lp.close()
+
+
+def test_line_range_dist_two_gpus(parser, tmp_path):
+    """lp_analyze_range_dist_device on two GPUs (skipped on a one-GPU box): one log cut by line range, summaries
+    all-gathered by NCCL inside the library and composed on the device; the shards concatenate to the whole-log result."""
+    import socket
+    import torch
+    import torch.multiprocessing as mp
+
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    wl = synth.make_patterns(40, 5152, scoring_heavy=True, noliteral=1)
+    log = synth.make_log(wl, 7000, 5151, hit_rate=0.05, symptom_rate=0.3, phase_rate=0.01, pool_blocks=1500) + b"\r\n\n\n"
+    prior = (np.arange(len(wl.patterns)) % 7).astype(np.uint64)
+    parser.load_patterns(wl.patterns)
+    whole = parser.analyze(log, prior_count=prior)
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    mp.spawn(_range_dist_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    parts = [np.load(os.path.join(tmp_path, f"r{r}.npz")) for r in range(2)]
+    np.testing.assert_array_equal(np.concatenate([p["line"] for p in parts]), whole.line)
+    np.testing.assert_array_equal(np.concatenate([p["pattern"] for p in parts]), whole.pattern)
+    np.testing.assert_array_equal(np.concatenate([p["score"] for p in parts]), whole.score)
+    np.testing.assert_array_equal(sum(p["delta"] for p in parts), whole.freq_delta)
+    assert all(int(p["n"][0]) == int(whole.log_n_lines[0]) for p in parts)
+
+
+def test_line_range_dist_single_rank_equals_whole_log(parser):
+    """lp_analyze_range_dist_device with a communicator of one rank (runs on a one-GPU box): summary built on the
+    device, all-gather, k_range_compose, k_score reading the shard's place and the sequence thresholds from device
+    memory; must give exactly lp_analyze's result, also from a host buffer and on a fresh context (repeat loop)."""
+    from log_parser_b200 import parallel
+
+    wl = synth.make_patterns(40, 5152, scoring_heavy=True, noliteral=1)
+    log = synth.make_log(wl, 7000, 5151, hit_rate=0.05, symptom_rate=0.3, phase_rate=0.01, pool_blocks=1500) + b"\n\n"
+    prior = (np.arange(len(wl.patterns)) % 6).astype(np.uint64)
+    parser.load_patterns(wl.patterns)
+    whole = parser.analyze(log, prior_count=prior, options=binding.OPT_FACTORS)
+    assert whole.n_events > 200 and (whole.factors[:, 4] > 1.0).any()
+    lp = binding.LogParser(ScoringConfig())
+    try:
+        lp.load_patterns(wl.patterns)
+        lp.comm_init(lp.comm_unique_id(), 0, 1)
+        for _ in range(3):
+            r = parallel.analyze_range_dist(lp, log, 0, 1, prior, options=binding.OPT_FACTORS)
+            np.testing.assert_array_equal(r.line, whole.line)
+            np.testing.assert_array_equal(r.pattern, whole.pattern)
+            np.testing.assert_array_equal(r.score, whole.score)
+            np.testing.assert_array_equal(r.rank, whole.rank)
+            np.testing.assert_array_equal(r.freq_delta, whole.freq_delta)
+            assert int(r.log_n_lines[0]) == int(whole.log_n_lines[0])
+        end = parallel.strip_trailing_separators(log)
+        host = np.frombuffer(log[:end], dtype=np.uint8).copy()
+        r = lp.analyze_range_dist_host_ptr(host.ctypes.data, end, 0, 0, prior)
+        np.testing.assert_array_equal(r.line, whole.line)
+        np.testing.assert_array_equal(r.score, whole.score)
+    finally:
+        lp.close()
+
+
 def test_library_nccl_single_rank_equals_batch(parser):
     """lp_analyze_batch_dist_device with a communicator of one rank: the exchange path (count after the
     unique pass, all-gather and prefix on the second stream, k_score waiting for it, the repeat loop on
