@@ -84,12 +84,15 @@ public class GpuAnalysisService {
         List<Pattern> patterns;
         long[] prior;
         LogParserB200.Columns c;
-        synchronized (this) {       // prior snapshot, device call and recording form one step, as one request does in the reference
+        // Not synchronized: the reference lets concurrent requests interleave their reads and records of the frequency
+        // state freely (FTS keeps a ConcurrentHashMap, AnalysisService is a shared singleton, AS:35). Here a request sees
+        // the counts at its start plus its own earlier events, and requests from different threads overlap on the GPU.
+        synchronized (this) {       // only the (pattern list, native plan) pair is read atomically against reload()
             patterns = flat;
-            prior = frequency.priorCounts(patterns);
-            c = gpu.analyze(logs, prior, 0);
-            frequency.apply(patterns, c.freqDelta());
         }
+        prior = frequency.priorCounts(patterns);
+        c = gpu.analyze(logs, prior, 0);
+        frequency.apply(patterns, c.freqDelta());
         String[] logLines = logs.split("\\r?\\n");          // only for the context strings of the response (AS:132-156)
         List<MatchedEvent> foundEvents = new ArrayList<>(c.line().length);
         for (int k = 0; k < c.line().length; k++) {         // discovery order, as AS:100-109 appends them

@@ -96,8 +96,19 @@ public final class LogParserB200 implements AutoCloseable {
             Map.of("CRITICAL", 5.0, "HIGH", 3.0, "MEDIUM", 2.0, "LOW", 1.5, "INFO", 1.0);
 
     private final MemorySegment ctx;
-    private MemorySegment hostBuf = MemorySegment.NULL;     // page-locked request buffer, grown on demand
-    private long hostCap = 0;
+    /** Page-locked request buffer of one calling thread, grown on demand (lp_host_alloc). */
+    private static final class HostBuf {
+        MemorySegment seg = MemorySegment.NULL;
+        long cap = 0;
+    }
+    // one buffer per worker thread: lp_analyze calls from different threads run on different workers of the context
+    // and overlap on the GPU, so the binding must not serialise them on a shared buffer
+    private final java.util.Queue<HostBuf> allBufs = new java.util.concurrent.ConcurrentLinkedQueue<>();
+    private final ThreadLocal<HostBuf> hostBufs = ThreadLocal.withInitial(() -> {
+        HostBuf b = new HostBuf();
+        allBufs.add(b);
+        return b;
+    });
     private int nPatterns = 0;
 
     public LogParserB200(ScoringProps p, int device) {
@@ -199,28 +210,29 @@ public final class LogParserB200 implements AutoCloseable {
      * inside the sliding frequency window at request start ({@link FrequencyBridge#priorCounts}); the library adds
      * the in-request rank itself, which is the read-before-record order of ScoringService.java:84-88.
      */
-    public synchronized Columns analyze(String logs, long[] priorInWindow, int options) {
+    public Columns analyze(String logs, long[] priorInWindow, int options) {
         byte[] utf8 = logs.getBytes(StandardCharsets.UTF_8);
+        HostBuf hb = hostBufs.get();
         try (Arena a = Arena.ofConfined()) {
             // the request bytes go through a page-locked buffer owned by the library: the host->device copy then runs
             // asynchronously, in pieces, underneath the scan of the pieces that have already landed
-            if (utf8.length > hostCap) {
-                if (!hostBuf.equals(MemorySegment.NULL)) {
-                    HOST_FREE.invokeExact(hostBuf);
+            if (utf8.length > hb.cap) {
+                if (!hb.seg.equals(MemorySegment.NULL)) {
+                    HOST_FREE.invokeExact(hb.seg);
                 }
-                hostCap = Math.max(1L << 20, utf8.length + (utf8.length >> 2));
-                MemorySegment p = (MemorySegment) HOST_ALLOC.invokeExact(hostCap);
+                hb.cap = Math.max(1L << 20, utf8.length + (utf8.length >> 2));
+                MemorySegment p = (MemorySegment) HOST_ALLOC.invokeExact(hb.cap);
                 if (p.equals(MemorySegment.NULL)) {
-                    hostCap = 0;
-                    hostBuf = MemorySegment.NULL;
+                    hb.cap = 0;
+                    hb.seg = MemorySegment.NULL;
                     throw new IllegalStateException("lp_host_alloc: " + lastError());
                 }
-                hostBuf = p.reinterpret(hostCap);
+                hb.seg = p.reinterpret(hb.cap);
             }
-            MemorySegment.copy(utf8, 0, hostBuf, JAVA_BYTE, 0, utf8.length);
+            MemorySegment.copy(utf8, 0, hb.seg, JAVA_BYTE, 0, utf8.length);
             MemorySegment prior = priorInWindow == null ? MemorySegment.NULL : a.allocateArray(JAVA_LONG, priorInWindow);
             MemorySegment out = a.allocate(ADDRESS);
-            int rc = (int) ANALYZE.invokeExact(ctx, hostBuf, (long) utf8.length, prior, options, out);
+            int rc = (int) ANALYZE.invokeExact(ctx, hb.seg, (long) utf8.length, prior, options, out);
             if (rc != 0) {
                 throw new IllegalStateException("lp_analyze: " + lastError());
             }
@@ -261,9 +273,12 @@ public final class LogParserB200 implements AutoCloseable {
     @Override
     public synchronized void close() {
         try {
-            if (!hostBuf.equals(MemorySegment.NULL)) {
-                HOST_FREE.invokeExact(hostBuf);
-                hostBuf = MemorySegment.NULL;
+            for (HostBuf b : allBufs) {
+                if (!b.seg.equals(MemorySegment.NULL)) {
+                    HOST_FREE.invokeExact(b.seg);
+                    b.seg = MemorySegment.NULL;
+                    b.cap = 0;
+                }
             }
             DESTROY.invokeExact(ctx);
         } catch (Throwable t) {

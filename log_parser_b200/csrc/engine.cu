@@ -160,6 +160,10 @@ struct lp_ctx {
     std::vector<uint32_t> lit_off8;   // literal -> offset in the 8-byte aligned device copy of the literal bytes
     bool calibrated = false;
     int recalibrations = 0;
+    double cal_rate = -1.0;                     // candidates per line on the first call after a calibration (recalibration trigger)
+    // what one worker learned from its first log serves the others: the owner context keeps the calibrated filter
+    struct SharedCal { std::mutex mu; uint64_t version = 0; std::vector<uint32_t> lit_gram_off, bitmap, table_key, table_begin, table_count, gram_lits; uint32_t table_bits = 0, f_mul = 0; } shared_cal;
+    uint64_t cal_seen = 0;                      // version of the owner's shared calibration this worker has adopted
     DevPlan dp{};
     DevBuf d_lut;
     ScoreCfg sc{};
@@ -510,7 +514,31 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     c->tm = lp_timings();
 
     const bool use_filter = !c->plan.lit_off.empty();
-    if (use_filter && !c->calibrated && len >= 4096) calibrate_filter(c, d_text, len);
+    if (use_filter && len >= 4096) {
+        lp_ctx::SharedCal& sh = c->owner->shared_cal;
+        std::unique_lock<std::mutex> lk(sh.mu);
+        if (sh.version > c->cal_seen && !(c->calibrated == false && c->recalibrations > 0)) {
+            // another worker of this context has already tuned the filter against a log: adopt its choice
+            lpx::Plan& pl = c->plan;
+            pl.lit_gram_off = sh.lit_gram_off; pl.bitmap = sh.bitmap; pl.table_key = sh.table_key; pl.table_begin = sh.table_begin;
+            pl.table_count = sh.table_count; pl.gram_lits = sh.gram_lits; pl.table_bits = sh.table_bits;
+            c->f_mul = sh.f_mul;
+            c->cal_seen = sh.version;
+            lk.unlock();
+            upload_filter(c);
+            c->calibrated = true;
+            c->cal_rate = -1.0;
+        } else if (!c->calibrated) {
+            lk.unlock();
+            calibrate_filter(c, d_text, len);
+            c->cal_rate = -1.0;
+            lk.lock();
+            const lpx::Plan& pl = c->plan;
+            sh.lit_gram_off = pl.lit_gram_off; sh.bitmap = pl.bitmap; sh.table_key = pl.table_key; sh.table_begin = pl.table_begin;
+            sh.table_count = pl.table_count; sh.gram_lits = pl.gram_lits; sh.table_bits = pl.table_bits; sh.f_mul = c->f_mul;
+            c->cal_seen = ++sh.version;
+        }
+    }
     const uint32_t n_always = (uint32_t)c->plan.always_list.size();
     const uint32_t n_always_vm = (uint32_t)c->plan.always_vm_list.size();
     const bool has_vm = c->plan.n_vm > 0;
@@ -975,7 +1003,13 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
     if (c->scan_mode == 0) c->tm.scan_bytes = c->pend.len + 2ull * h.total_nl + 36ull * ((c->pend.len + fs::TILE) / fs::TILE) + 4ull * h.n_cand;
     else c->tm.scan_bytes = c->pend.len + 4ull * ((c->pend.len + TILE_BYTES) / TILE_BYTES) + 4ull * h.n_cand;
     c->tm.dfa_scan_bytes = c->d_group_blob.empty() ? 0 : c->pend.len + 8ull * ((uint64_t)G + 1) + (uint64_t)G;
-    if (!c->plan.lit_off.empty() && (uint64_t)h.n_cand * 2 > (uint64_t)G + 1024 && c->recalibrations < 2) { c->calibrated = false; ++c->recalibrations; }
+    // The filter is tuned once, against the first log. It is tuned again (at most twice) only when logs arrive that
+    // produce several times the candidates per line of the log it was tuned on.
+    if (!c->plan.lit_off.empty() && c->calibrated && G > 0) {
+        const double rate = (double)h.n_cand / (double)G;
+        if (c->cal_rate < 0) c->cal_rate = rate;
+        else if (rate > 4.0 * c->cal_rate + 0.5 && c->recalibrations < 2) { c->calibrated = false; ++c->recalibrations; }
+    }
     c->pend.valid = false;
     res->hold = c->stage;          // ownership moves to the result; the next call draws a buffer from the pool
     res->pool = c->pool;
@@ -1164,6 +1198,8 @@ int lp_load_patterns(lp_ctx* c, const lp_pattern_desc* pats, size_t n, int64_t* 
         c->calibrated = false;
         c->recalibrations = 0;
         c->f_mul = fs::MUL1;
+        c->cal_seen = 0; c->cal_rate = -1.0;
+        { std::lock_guard<std::mutex> lc(c->shared_cal.mu); c->shared_cal.version = 0; }
         lpx::build_plan(in, c->plan, bad_pattern);
         upload_plan(c);
         // line-range shards: where each sequence's chain table sits in a shard summary
@@ -1177,7 +1213,7 @@ int lp_load_patterns(lp_ctx* c, const lp_pattern_desc* pats, size_t n, int64_t* 
         c->loaded = true;
         for (lp_ctx* e : c->extra) {       // the other workers get their own copy of the (small) tables
             std::lock_guard<std::mutex> le(e->mu);
-            e->loaded = false; e->calibrated = false; e->recalibrations = 0; e->f_mul = fs::MUL1;
+            e->loaded = false; e->calibrated = false; e->recalibrations = 0; e->f_mul = fs::MUL1; e->cal_seen = 0; e->cal_rate = -1.0;
             e->plan = c->plan;
             upload_plan(e);
             e->n_seq = c->n_seq; e->h_seq_tab_off = c->h_seq_tab_off;
