@@ -505,6 +505,27 @@ def main():
     lines_all = lines_per_gpu * (1 if by_lines else world)
     value = lines_all * args.steps / dev_s
 
+    # ---- N>1, by log: the same per-GPU batch through the non-collective call on every GPU at once, so that the cost of
+    # the exchange can be read off next to the weak-scaling value (the N=1 line of this bench is the single-log config
+    # C2, a different workload: a batch of 50 logs takes ~0.1 ms longer per step than one log of the same size)
+    alone = None
+    if world > 1 and not by_lines:
+        for i in range(3):
+            lp.analyze_batch_device(copies[i % len(copies)].data_ptr(), offsets)
+        barrier()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record(lib_stream)
+        for i in range(args.steps):
+            lp.analyze_batch_device(copies[i % len(copies)].data_ptr(), offsets)
+        a1.record(lib_stream)
+        barrier()
+        al = torch.tensor([a0.elapsed_time(a1) / 1e3], dtype=torch.float64, device=dev)
+        dist.all_reduce(al, op=dist.ReduceOp.MAX)
+        alone = {"what": "the same per-GPU batch through lp_analyze_batch_device on all GPUs at once, no exchange (max over ranks)",
+                 "ms_per_step": 1e3 * float(al[0]) / args.steps, "exchange_cost_ms_per_step": 1e3 * (dev_s - float(al[0])) / args.steps}
+        for i in range(2):
+            step_device(i)
+
     # ---- e2e: host buffer in, events out, through the host-buffer entry point (the call the JVM makes)
     e2e_steps = 0 if args.no_e2e else max(3, min(args.steps, 10))
     r2 = res
@@ -613,6 +634,7 @@ def main():
                     "host_buffer": "page-locked, from lp_host_alloc", "h2d_ceiling": h2d_ceiling,
                     "two_request_threads": e2e_two},
             "parity": parity,
+            "without_exchange": alone,
             "gpu_launches": int(launches), "clocks": clocks,
         }
         if not args.no_cpu_baseline:

@@ -905,9 +905,15 @@ lp_result* run_score(lp_ctx* c, const uint64_t* prior_count, const RangeGlobal* 
         small_sort(c, c->sort_key.as<unsigned long long>(), mc, 64, nullptr, d_rank, &ctr->n_events)) {
         // one log, few events: ranks by tile sort + counting (descending score, ties keep discovery order)
     } else if (!(options & LP_OPT_NO_RANK)) {
-        // stable sort by descending score (ties keep discovery order), then stably by log
-        sort_pairs<unsigned long long, uint32_t>(c, c->sort_key.as<unsigned long long>(), c->sort_key_alt.as<unsigned long long>(),
-                                                 c->ev_idx.as<uint32_t>(), c->order.as<uint32_t>(), mc, 64);
+        // stable sort by descending score (ties keep discovery order), then stably by log. The first step is the tile sort
+        // + counting rank when the events fit it (a device-wide radix sort of a few ten thousand 64-bit keys is eight
+        // passes of launch and look-back latency).
+        if (small_sort(c, c->sort_key.as<unsigned long long>(), mc, 64, nullptr, c->order_alt.as<uint32_t>(), &ctr->n_events)) {
+            k_invert_rank<<<blocks_for(mc, 256), 256, 0, st>>>(c->order_alt.as<uint32_t>(), ctr, mc, c->order.as<uint32_t>());
+            c->launches += 1;
+        } else
+            sort_pairs<unsigned long long, uint32_t>(c, c->sort_key.as<unsigned long long>(), c->sort_key_alt.as<unsigned long long>(),
+                                                     c->ev_idx.as<uint32_t>(), c->order.as<uint32_t>(), mc, 64);
         uint32_t* order = c->order.as<uint32_t>();
         if (n_logs > 1) {
             k_gather_u32<<<blocks_for(mc, 256), 256, 0, st>>>(c->ev_log.as<uint32_t>(), order, mc, c->log_sorted.as<uint32_t>());

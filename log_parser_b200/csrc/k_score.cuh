@@ -266,6 +266,13 @@ __global__ void k_write_rank(const uint32_t* __restrict__ order, const uint32_t*
     const uint32_t e = order[j];
     rank[e] = j - (uint32_t)log_begin[ev_log[e]];
 }
+// order[final position] = event, from the positions k_tile_rank gave the first *n_valid events; the padding behind them
+// keeps its place (its log index is n_logs, so the stable sort by log leaves it last)
+__global__ void k_invert_rank(const uint32_t* __restrict__ rank, const Counters* ctr, uint32_t n, uint32_t* __restrict__ order) {
+    const uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    if (j < ctr->n_events) order[rank[j]] = j; else order[j] = j;
+}
 __global__ void k_gather_u32(const uint32_t* __restrict__ src, const uint32_t* __restrict__ idx, uint32_t n, uint32_t* __restrict__ dst) {
     uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j < n) dst[j] = src[idx[j]];
