@@ -173,7 +173,7 @@ struct lp_ctx {
     DevBuf items, ss_keys, ss_idx;
     size_t est_items = 0;
     int occ_confirm = 0, occ_resolve = 0;
-    DevBuf cand, tasks, vm_tasks, vm_tasks_alt, vm_stack, recs, recs_alt, cub_tmp, rx_begin, ctx_flags;
+    DevBuf cand, tasks, group_hist, vm_tasks, vm_tasks_alt, vm_stack, recs, recs_alt, cub_tmp, rx_begin, ctx_flags;
     DevBuf ev_key, ev_key_alt, ev_log, slot_key, slot_key_alt, ev_idx, ev_idx_alt, rank_in_slot, freq_delta, prior;
     DevBuf out_arena, sort_key, sort_key_alt, order, order_alt, log_sorted, log_sorted_alt;
     DevBuf log_event_begin, n_unique;
@@ -332,6 +332,7 @@ void upload_plan(lp_ctx* c) {
     d.n_rx = pl.n_rx;
     d.rx_kind = upload(K, pl.rx_kind);
     d.rx_dfa_off = upload(K, pl.rx_dfa_off);
+    d.rx_dfa_len = upload(K, pl.rx_dfa_len);
     d.rx_ncls = upload(K, pl.rx_ncls);
     d.rx_start = upload(K, pl.rx_start);
     d.dfa_trans = upload(K, pl.dfa_trans);
@@ -577,6 +578,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     c->ctx_flags.ensure((line_cap / 4 + 2) * 4);
     c->cand.ensure(c->est_cand * 4);
     c->tasks.ensure(c->est_tasks * 8);
+    c->group_hist.ensure((size_t)(c->dp.n_rx + 1) * 4 * 4);      // histogram + cursors, for the DFA tasks and the bytecode tasks
     c->items.ensure(c->est_items * 8 * N_CLASSES);
     if (has_vm) { c->vm_tasks.ensure(c->est_vm_tasks * 8); c->vm_tasks_alt.ensure(c->est_vm_tasks * 8); }
     if (has_vm || !c->plan.always_vm_list.empty()) c->vm_stack.ensure((size_t)VM_POOL_STACKS * lpx::VM_STACK_WORDS * 4);
@@ -660,7 +662,6 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     CK(cudaMemcpyAsync(c->log_off.p, h_off, (n_logs + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
     CK(cudaMemsetAsync(c->recs.p, 0xFF, rec_cap * 8, st));            // padding sentinels sort last
     CK(cudaMemsetAsync(c->ev_key_alt.p, 0xFF, ev_cap * 8, st));
-    if (has_vm) CK(cudaMemsetAsync(c->vm_tasks.p, 0xFF, c->est_vm_tasks * 8, st));      // padding sorts behind the tasks
     if (!c->plan.ctx_any_in_groups) CK(cudaMemsetAsync(c->ctx_flags.p, 0, (line_cap / 4 + 2) * 4, st));   // else k_dfa_scan writes every byte
     k_scan_tiles<<<1, 1024, 0, st>>>(c->tile_counts.as<uint32_t>(), fused ? c->fs_lists.as<uint16_t>() : nullptr, n_tiles, n_logs, ctr);
     if (fused) {
@@ -716,13 +717,21 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         k_confirm<<<c->n_sm * c->occ_confirm, 256, 0, st>>>(ca, c->dp);
         k_resolve<<<c->n_sm * c->occ_resolve, 256, 0, st>>>(ra, c->dp);
         c->launches += 1;
+        // bytecode tasks are grouped by regex before they are interpreted (see k_group_count)
+        const uint32_t bins = c->dp.n_rx + 1;
+        uint32_t* const gh = c->group_hist.as<uint32_t>();
+        auto group_by_regex = [&](const unsigned long long* in, const unsigned int* n_ptr, uint32_t cap, uint32_t* hist, unsigned long long* out) {
+            k_group_count<<<c->n_sm * 2, 256, 0, st>>>(in, n_ptr, cap, c->dp.n_rx, hist);
+            k_group_scan<<<1, 1024, 0, st>>>(hist, bins, hist + bins);
+            k_group_scatter<<<c->n_sm * 2, 256, 0, st>>>(in, n_ptr, cap, c->dp.n_rx, hist + bins, out);
+            c->launches += 3;
+        };
+        if (has_vm) CK(cudaMemsetAsync(gh, 0, (size_t)bins * 4 * 4, st));
         k_verify<<<c->n_sm * 8, 256, 0, st>>>(va, c->dp);
         c->launches += 2;
         if (has_vm) {
-            // tasks grouped by regex (a stable sort on the regex bits only: two radix passes instead of six): the lanes
-            // of a warp then interpret the same program and stay together far longer than with tasks in arrival order
-            sort_keys<unsigned long long>(c, c->vm_tasks.as<unsigned long long>(), c->vm_tasks_alt.as<unsigned long long>(), va.vm_task_cap,
-                                          std::min<int>(64, 32 + bits_for(c->dp.n_rx)), 32);
+            // the lanes of a warp then interpret the same program and stay together far longer than with tasks in arrival order
+            group_by_regex(c->vm_tasks.as<unsigned long long>(), &ctr->n_vm_tasks, va.vm_task_cap, gh + 2 * bins, c->vm_tasks_alt.as<unsigned long long>());
             va.vm_tasks = c->vm_tasks_alt.as<unsigned long long>();
             k_verify_vm<<<vm_grid, vm_block, 0, st>>>(va, c->dp);
             c->launches += 1;
@@ -1176,7 +1185,7 @@ void lp_destroy(lp_ctx* c) {
     cudaStreamSynchronize(c->stream);
     for (auto& b : c->plan_bufs) b.release();
     DevBuf* all[] = {&c->text, &c->log_off, &c->tile_counts, &c->counters, &c->line_start, &c->line_end, &c->first_line, &c->n_lines,
-                     &c->cand, &c->tasks, &c->vm_tasks, &c->vm_tasks_alt, &c->vm_stack, &c->recs, &c->recs_alt, &c->cub_tmp, &c->rx_begin, &c->ctx_flags, &c->ev_key, &c->ev_key_alt,
+                     &c->cand, &c->tasks, &c->group_hist, &c->vm_tasks, &c->vm_tasks_alt, &c->vm_stack, &c->recs, &c->recs_alt, &c->cub_tmp, &c->rx_begin, &c->ctx_flags, &c->ev_key, &c->ev_key_alt,
                      &c->ev_log, &c->slot_key, &c->slot_key_alt, &c->ev_idx, &c->ev_idx_alt, &c->rank_in_slot, &c->freq_delta, &c->prior,
                      &c->out_arena, &c->sort_key, &c->sort_key_alt, &c->order, &c->order_alt,
                      &c->log_sorted, &c->log_sorted_alt, &c->log_event_begin, &c->n_unique, &c->d_lut,

@@ -381,6 +381,54 @@ __global__ void __launch_bounds__(256) k_resolve(ResolveArgs a, DevPlan P) {
 }
 
 // ------------------------------------------------------------------ K4: verify tasks
+// ------------------------------------------------------------------ tasks grouped by regex
+// k_verify_vm interprets per-regex bytecode: with tasks in arrival order the 32 lanes of a warp hold 32 different
+// programs and diverge at once. A counting sort on the regex id (histogram, scan, scatter: three tiny kernels; the
+// order inside a regex does not matter, the records are sorted later) puts neighbours on the same program; it
+// replaced a two-pass device radix sort. (For k_verify's table-driven walks the same grouping, even with the
+// automata of a block copied to shared memory, did not pay: 15 + 4 + 15 us of grouping for 72 -> 50 us of walking;
+// profiles/r02_scan_variants.jsonl.)
+__global__ void k_group_count(const unsigned long long* __restrict__ tasks, const unsigned int* n_ptr, uint32_t cap, uint32_t n_rx, uint32_t* __restrict__ hist) {
+    const uint32_t n = min(*n_ptr, cap);
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x)
+        atomicAdd(&hist[min((uint32_t)(tasks[t] >> 32), n_rx)], 1u);
+}
+// one block: hist[0..n_rx] -> exclusive prefix in place, a second copy as the scatter cursors
+__global__ void __launch_bounds__(1024) k_group_scan(uint32_t* __restrict__ hist, uint32_t n_bins, uint32_t* __restrict__ cursor) {
+    __shared__ uint32_t warp_tot[32];
+    __shared__ uint32_t carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (uint32_t base = 0; base < n_bins; base += 1024) {
+        const uint32_t i = base + threadIdx.x;
+        const uint32_t v = i < n_bins ? hist[i] : 0u;
+        uint32_t inc = v;
+        for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, inc, o); if ((threadIdx.x & 31) >= o) inc += y; }
+        if ((threadIdx.x & 31) == 31) warp_tot[threadIdx.x >> 5] = inc;
+        __syncthreads();
+        if (threadIdx.x < 32) {
+            const uint32_t w = warp_tot[threadIdx.x];
+            uint32_t wi = w;
+            for (int o = 1; o < 32; o <<= 1) { const uint32_t y = __shfl_up_sync(0xffffffffu, wi, o); if (threadIdx.x >= o) wi += y; }
+            warp_tot[threadIdx.x] = wi - w;
+        }
+        __syncthreads();
+        const uint32_t excl = carry + warp_tot[threadIdx.x >> 5] + inc - v;
+        if (i < n_bins) { hist[i] = excl; cursor[i] = excl; }
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = excl + v;
+        __syncthreads();
+    }
+}
+__global__ void k_group_scatter(const unsigned long long* __restrict__ tasks, const unsigned int* n_ptr, uint32_t cap, uint32_t n_rx,
+                                uint32_t* __restrict__ cursor, unsigned long long* __restrict__ out) {
+    const uint32_t n = min(*n_ptr, cap);
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < n; t += gridDim.x * blockDim.x) {
+        const unsigned long long task = tasks[t];
+        out[atomicAdd(&cursor[min((uint32_t)(task >> 32), n_rx)], 1u)] = task;
+    }
+}
+
 struct VerifyArgs {
     const uint8_t* text;
     uint64_t len;

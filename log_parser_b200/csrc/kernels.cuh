@@ -28,6 +28,7 @@ struct DevPlan {
     uint32_t n_rx;
     const uint8_t* rx_kind;
     const uint32_t* rx_dfa_off;
+    const uint32_t* rx_dfa_len;       // entries (u16) of the regex's whole-line automaton in dfa_trans
     const uint16_t* rx_ncls;
     const uint16_t* rx_start;
     const uint16_t* dfa_trans;

@@ -180,7 +180,7 @@ void build_plan(const std::vector<PlanPatternIn>& pats, Plan& pl, int64_t* bad) 
         Dfa dfa;
         bool is_dfa = pr.regular && build_dfa(*pr.root, dfa);
         pl.rx_kind.push_back(is_dfa ? RXK_DFA : RXK_VM);
-        pl.rx_dfa_off.push_back(0); pl.rx_ncls.push_back(0); pl.rx_start.push_back(0);
+        pl.rx_dfa_off.push_back(0); pl.rx_dfa_len.push_back(0); pl.rx_ncls.push_back(0); pl.rx_start.push_back(0);
         pl.rx_vm_off.push_back(0); pl.rx_vm_len.push_back(0); pl.rx_vm_slots.push_back(0);
         pl.rx_vm_caps.push_back(0); pl.rx_vm_set_base.push_back(0);
         pl.rx_cmap.resize((size_t)pl.n_rx * 256, 0);
@@ -190,6 +190,7 @@ void build_plan(const std::vector<PlanPatternIn>& pats, Plan& pl, int64_t* bad) 
         pl.rx_acmap.resize((size_t)pl.n_rx * 256, 0);
         if (is_dfa) {
             pl.rx_dfa_off[id] = (uint32_t)pl.dfa_trans.size();
+            pl.rx_dfa_len[id] = (uint32_t)dfa.trans.size();
             pl.rx_ncls[id] = dfa.n_classes;
             pl.rx_start[id] = dfa.start;
             pl.dfa_trans.insert(pl.dfa_trans.end(), dfa.trans.begin(), dfa.trans.end());

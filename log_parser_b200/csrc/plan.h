@@ -39,6 +39,7 @@ struct Plan {
     std::vector<uint8_t> rx_kind;         // RxKind
     std::vector<uint8_t> rx_always;       // 1: no usable literal -> every line is a candidate
     std::vector<uint32_t> rx_dfa_off;     // offset into dfa_trans (u16 units)
+    std::vector<uint32_t> rx_dfa_len;     // entries of the whole-line automaton
     std::vector<uint16_t> rx_ncls;
     std::vector<uint16_t> rx_start;
     std::vector<uint16_t> dfa_trans;
