@@ -635,6 +635,8 @@ def main():
                     "two_request_threads": e2e_two},
             "parity": parity,
             "without_exchange": alone,
+            "build": {"library": "log_parser_b200/liblogparser_b200.so", "mode": build.LAST_BUILD_MODE, "source_hash": build.source_hash(),
+                      "matches_sources": not build.stale()},
             "gpu_launches": int(launches), "clocks": clocks,
         }
         if not args.no_cpu_baseline:
