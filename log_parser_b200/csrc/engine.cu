@@ -577,7 +577,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     c->n_lines.ensure((size_t)n_logs * 4);
     c->ctx_flags.ensure((line_cap / 4 + 2) * 4);
     c->cand.ensure(c->est_cand * 4);
-    c->tasks.ensure(c->est_tasks * 8);
+    c->tasks.ensure(c->est_tasks * 16);
     c->group_hist.ensure((size_t)(c->dp.n_rx + 1) * 4 * 4);      // histogram + cursors, for the DFA tasks and the bytecode tasks
     c->items.ensure(c->est_items * 8 * N_CLASSES);
     if (has_vm) { c->vm_tasks.ensure(c->est_vm_tasks * 8); c->vm_tasks_alt.ensure(c->est_vm_tasks * 8); }
@@ -691,7 +691,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
 
     VerifyArgs va{};
     va.text = d_text; va.len = len; va.line_start = c->line_start.as<uint32_t>(); va.line_end = c->line_end.as<uint32_t>();
-    va.tasks = c->tasks.as<unsigned long long>(); va.task_cap = (uint32_t)std::min<size_t>(c->est_tasks, 0xFFFFFFFFu);
+    va.tasks = c->tasks.as<uint4>(); va.task_cap = (uint32_t)std::min<size_t>(c->est_tasks, 0xFFFFFFFFu);
     va.recs = c->recs.as<unsigned long long>(); va.rec_cap = (uint32_t)rec_cap; va.ctr = ctr; va.n_lines_total = (uint32_t)line_cap;
     va.first_line = c->first_line.as<uint32_t>(); va.n_lines = c->n_lines.as<uint32_t>(); va.n_logs = n_logs;
     va.vm_tasks = c->vm_tasks.as<unsigned long long>(); va.vm_task_cap = (uint32_t)std::min<size_t>(c->est_vm_tasks, 0xFFFFFFFFu);
@@ -705,7 +705,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         ra.tile_prefix = c->tile_counts.as<uint32_t>(); ra.n_tiles = n_tiles; ra.tile_bytes = tile_bytes;
         ra.span_counts = fused ? c->fs_lists.as<uint16_t>() : nullptr; ra.log_off = c->log_off.as<uint64_t>(); ra.n_logs = n_logs;
         ra.line_start = c->line_start.as<uint32_t>(); ra.line_end = c->line_end.as<uint32_t>(); ra.n_lines_total = (uint32_t)line_cap;
-        ra.tasks = c->tasks.as<unsigned long long>(); ra.task_cap = va.task_cap; ra.ctr = ctr;
+        ra.tasks = c->tasks.as<uint4>(); ra.task_cap = va.task_cap; ra.ctr = ctr;
         ra.vm_tasks = c->vm_tasks.as<unsigned long long>(); ra.vm_task_cap = va.vm_task_cap;
         ra.recs = c->recs.as<unsigned long long>(); ra.rec_cap = (uint32_t)rec_cap;
         // grids of exactly one resident wave (grid-stride kernels; a partial second wave would run alone at the end)
@@ -773,8 +773,13 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
 
     // ---- sort + unique the (regex, line) records; rec_cap slots are sorted, unused ones are sentinels
     {
-        sort_keys<unsigned long long>(c, c->recs.as<unsigned long long>(), c->recs_alt.as<unsigned long long>(), (uint32_t)rec_cap,
-                                      std::min<int>(64, (int)c->dp.gb + bits_for(c->dp.n_rx)));     // the all-ones padding has regex field 2^bits - 1 > n_rx - 1: it sorts last without an extra bit
+        // (the all-ones padding has regex field 2^bits - 1 > n_rx - 1: it sorts last without an extra bit)
+        const int rec_bits = std::min<int>(64, (int)c->dp.gb + bits_for(c->dp.n_rx));
+        // small requests (C1: one 10k-line log; a shard of a log cut over 8 GPUs): tile sort + counting rank, two launches
+        // instead of the device radix sort's six, which are pure launch and look-back latency at this size
+        if (rec_cap > 8 * (size_t)SS_TILE ||
+            !small_sort(c, c->recs.as<unsigned long long>(), (uint32_t)rec_cap, rec_bits, c->recs_alt.as<unsigned long long>(), nullptr, nullptr))
+            sort_keys<unsigned long long>(c, c->recs.as<unsigned long long>(), c->recs_alt.as<unsigned long long>(), (uint32_t)rec_cap, rec_bits);
         size_t tmp = 0;
         cub::DeviceSelect::Unique(nullptr, tmp, c->recs_alt.as<unsigned long long>(), c->recs.as<unsigned long long>(),
                                   &ctr->n_unique, (int)rec_cap, st);

@@ -273,7 +273,7 @@ struct ResolveArgs {
     const uint32_t* line_start;
     const uint32_t* line_end;
     uint32_t n_lines_total;
-    unsigned long long* tasks;
+    uint4* tasks;                    // {regex | flags, line, position, state}, see k_verify
     uint32_t task_cap;
     unsigned long long* vm_tasks;
     uint32_t vm_task_cap;
@@ -282,10 +282,22 @@ struct ResolveArgs {
     Counters* ctr;
 };
 constexpr uint32_t ANCHOR_BUDGET = 24;     // automaton steps an item may spend here before it is handed to k_verify
+constexpr uint32_t T_STAGE = 1024;         // tasks staged per block of k_resolve
+constexpr uint32_t VT_FWD = 1u << 30, VT_REV = 1u << 31;      // task.x flags: continue an anchored walk forwards / backwards (else: whole-line walk)
 __global__ void __launch_bounds__(256) k_resolve(ResolveArgs a, DevPlan P) {
-    __shared__ QStage s_rec, s_task;
-    if (threadIdx.x == 0) { s_rec.n = 0; s_task.n = 0; }
+    __shared__ QStage s_rec;
+    __shared__ uint4 s_tbuf[T_STAGE];        // tasks for k_verify, staged like the records (16-byte entries)
+    __shared__ uint32_t s_tn, s_tbase;
+    if (threadIdx.x == 0) { s_rec.n = 0; s_tn = 0; }
     __syncthreads();
+    auto put_task = [&](const uint4& t) {
+        const uint32_t idx = atomicAdd(&s_tn, 1u);
+        if (idx < T_STAGE) s_tbuf[idx] = t;
+        else {      // staging full: straight to the global queue
+            const uint32_t gi = atomicAdd(&a.ctr->n_tasks, 1u);
+            if (gi < a.task_cap) a.tasks[gi] = t; else atomicOr(&a.ctr->overflow, 2u);
+        }
+    };
     const uint32_t n0 = min(a.ctr->n_items[0], a.item_cap), n1 = min(a.ctr->n_items[1], a.item_cap),
                    n2 = min(a.ctr->n_items[2], a.item_cap), n3 = min(a.ctr->n_items[3], a.item_cap);
     const uint32_t c1 = (n0 + blockDim.x - 1) / blockDim.x, c2 = c1 + (n1 + blockDim.x - 1) / blockDim.x,
@@ -339,7 +351,7 @@ __global__ void __launch_bounds__(256) k_resolve(ResolveArgs a, DevPlan P) {
                 if (hit && (mode & 4u)) hit = ((mode & 64u) != 0) != (e2 < le && dev_word(a.text[e2]));
                 if (hit) stage_put(s_rec, a.ctr, &a.ctr->n_recs, a.recs, a.rec_cap, 4u, rec);
             } else if (cls == 3) {
-                if (P.rx_kind[r] == 0) stage_put(s_task, a.ctr, &a.ctr->n_tasks, a.tasks, a.task_cap, 2u, ((unsigned long long)r << 32) | g);
+                if (P.rx_kind[r] == 0) put_task(make_uint4(r, g, 0u, 0u));
                 else {
                     const uint32_t vi = atomicAdd(&a.ctr->n_vm_tasks, 1u);
                     if (vi < a.vm_task_cap) a.vm_tasks[vi] = ((unsigned long long)r << 32) | g;
@@ -370,14 +382,22 @@ __global__ void __launch_bounds__(256) k_resolve(ResolveArgs a, DevPlan P) {
                 }
                 const uint32_t st = w.st[0];
                 if (st == 1u) stage_put(s_rec, a.ctr, &a.ctr->n_recs, a.recs, a.rec_cap, 4u, rec);
-                else if (st > 1u) stage_put(s_task, a.ctr, &a.ctr->n_tasks, a.tasks, a.task_cap, 2u, ((unsigned long long)r << 32) | g);
+                else if (st > 1u)       // undecided: k_verify carries this walk on from where it stopped, in the state it stopped in
+                    put_task(make_uint4(r | (cls == 1 ? VT_FWD : VT_REV), g, cls == 1 ? min(le, s + ANCHOR_BUDGET) : (e2 - ls > ANCHOR_BUDGET ? e2 - ANCHOR_BUDGET : ls), st));
             }
         } while (false);
         // no barrier per chunk: a block handles a few chunks and its output fits the staging buffers
         // (entries beyond them go straight to the global queues)
     }
     stage_flush(s_rec, a.ctr, &a.ctr->n_recs, a.recs, a.rec_cap, 4u, true);
-    stage_flush(s_task, a.ctr, &a.ctr->n_tasks, a.tasks, a.task_cap, 2u, true);
+    const uint32_t staged = min(s_tn, T_STAGE);
+    if (staged) {
+        if (threadIdx.x == 0) s_tbase = atomicAdd(&a.ctr->n_tasks, staged);
+        __syncthreads();
+        for (uint32_t q = threadIdx.x; q < staged; q += blockDim.x) {
+            if (s_tbase + q < a.task_cap) a.tasks[s_tbase + q] = s_tbuf[q]; else atomicOr(&a.ctr->overflow, 2u);
+        }
+    }
 }
 
 // ------------------------------------------------------------------ K4: verify tasks
@@ -434,7 +454,7 @@ struct VerifyArgs {
     uint64_t len;
     const uint32_t* line_start;
     const uint32_t* line_end;
-    const unsigned long long* tasks;
+    const uint4* tasks;
     uint32_t task_cap;
     unsigned long long* recs;
     uint32_t rec_cap;
@@ -460,10 +480,31 @@ __global__ void __launch_bounds__(256) k_verify(VerifyArgs a, DevPlan P) {
     uint32_t t = blockIdx.x * blockDim.x + threadIdx.x;
     for (uint32_t it = 0; it < rounds; ++it, t += stride) {
         if (t < n) {
-            const unsigned long long task = a.tasks[t];
-            const uint32_t r = (uint32_t)(task >> 32), g = (uint32_t)task;
-            if (P.rx_kind[r] == 0 && dfa_walk(P, r, a.text, a.len, a.line_start[g], a.line_end[g]))
-                stage_put(sg, a.ctr, &a.ctr->n_recs, a.recs, a.rec_cap, 4u, ((unsigned long long)r << P.gb) | g);
+            const uint4 task = a.tasks[t];
+            const uint32_t r = task.x & ~(VT_FWD | VT_REV), g = task.y;
+            const uint32_t ls = a.line_start[g], le = a.line_end[g];
+            bool hit = false;
+            if (task.x & (VT_FWD | VT_REV)) {
+                // the anchored automaton of k_resolve, from the position and state its budget ran out in: the rest of the
+                // line (forwards) or the part before the occurrence (backwards), not the whole line from its start
+                const uint4 ad = __ldg(&P.anchor_desc[r]);
+                LineWalker<1, true> w;
+                w.nc[0] = ad.y; w.T[0] = P.dfa_trans + ad.x; w.cm[0] = P.rx_acmap + (size_t)r * 256; w.ff[0] = 0;
+                w.st[0] = task.w;
+                const uint32_t at = task.z;
+                if (task.x & VT_FWD) {
+                    const long tpos = tail_terminator(a.text, ls, le);
+                    if (tpos < 0 || (long)at > tpos) w.segment(a.text, a.len, at, le);
+                    else if (w.segment(a.text, a.len, at, (uint32_t)tpos)) { w.symbol(2); w.segment(a.text, a.len, (uint32_t)tpos, le); }
+                } else {
+                    w.segment_rev(a.text, a.len, ls, at);
+                }
+                w.symbol(1);
+                hit = w.st[0] == 1u;
+            } else if (P.rx_kind[r] == 0) {
+                hit = dfa_walk(P, r, a.text, a.len, ls, le);
+            }
+            if (hit) stage_put(sg, a.ctr, &a.ctr->n_recs, a.recs, a.rec_cap, 4u, ((unsigned long long)r << P.gb) | g);
         }
         stage_flush(sg, a.ctr, &a.ctr->n_recs, a.recs, a.rec_cap, 4u, false);
     }
