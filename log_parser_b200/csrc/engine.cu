@@ -151,9 +151,11 @@ struct lp_ctx {
     uint32_t n_group_record_rx = 0;
     DevBuf f_bitmap, f_key, f_lits, f_bytes;   // prefilter tables (re-uploaded by calibration)
     DevBuf line_skip;                          // per line: the always-on scan need not walk it (written by k_expand)
+    DevBuf scan_list;                           // lines the always-on scan walks (k_expand)
     DevBuf f_bits, f_gkeys, fs_lists;           // fused scan: first-stage bit table, exact gram keys, per-span newline counts and lists
     const uint8_t* d_byte_table = nullptr;
     int scan_mode = 0;                         // 0: fused single-pass scan (k_fscan); 1: k_filter_count + k_scan_tiles + k_lines (LP_SCAN_MODE=legacy)
+    uint32_t anchor_budget = ANCHOR_BUDGET;     // LP_ANCHOR_BUDGET
     uint32_t vm_blocks_per_sm = 12;            // k_verify_vm: blocks of 4 warps per SM (40 registers: 48 resident warps); the more warps, the fewer evaluations each one serialises (LP_VM_BLOCKS)
     uint32_t f_mul = fs::MUL1;                 // first-stage hash multiplier of k_fscan (pick_multiplier)
     int fscan_variant = 0;                     // first-stage lookup of k_fscan: 0 IMAD.HI hash, 1 IMAD+SHF hash, 2 byte table (LP_FSCAN_VARIANT)
@@ -611,6 +613,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         for (int w = 0; w < 8; ++w) fz.skip1[w] = c->plan.groups.empty() ? 0u : 0xFFFFFFFFu;
         for (const auto& g : c->plan.groups) for (int w = 0; w < 8; ++w) fz.skip1[w] &= g.skip1[w];
         c->line_skip.ensure(line_cap + 16);
+        c->scan_list.ensure((line_cap + 16) * 4);
     }
     auto launch_fscan = [&](uint32_t tile_begin, uint32_t tile_end) {
         fz.tile_begin = tile_begin; fz.tile_end = tile_end;
@@ -662,7 +665,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     CK(cudaMemcpyAsync(c->log_off.p, h_off, (n_logs + 1) * sizeof(uint64_t), cudaMemcpyHostToDevice, st));
     CK(cudaMemsetAsync(c->recs.p, 0xFF, rec_cap * 8, st));            // padding sentinels sort last
     CK(cudaMemsetAsync(c->ev_key_alt.p, 0xFF, ev_cap * 8, st));
-    if (!c->plan.ctx_any_in_groups) CK(cudaMemsetAsync(c->ctx_flags.p, 0, (line_cap / 4 + 2) * 4, st));   // else k_dfa_scan writes every byte
+    if (!c->plan.ctx_any_in_groups || fused) CK(cudaMemsetAsync(c->ctx_flags.p, 0, (line_cap / 4 + 2) * 4, st));   // else k_dfa_scan (walking every line) writes every byte
     k_scan_tiles<<<1, 1024, 0, st>>>(c->tile_counts.as<uint32_t>(), fused ? c->fs_lists.as<uint16_t>() : nullptr, n_tiles, n_logs, ctr);
     if (fused) {
         ExpandArgs ea{};
@@ -671,6 +674,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         ea.line_start = c->line_start.as<uint32_t>(); ea.line_end = c->line_end.as<uint32_t>();
         ea.first_line = c->first_line.as<uint32_t>(); ea.line_cap = (uint32_t)line_cap; ea.ctr = ctr;
         ea.line_skip = c->plan.groups.empty() ? nullptr : c->line_skip.as<uint8_t>();
+        ea.scan_list = c->plan.groups.empty() ? nullptr : c->scan_list.as<uint32_t>();
         for (int w = 0; w < 8; ++w) ea.skip1[w] = fz.skip1[w];
         k_expand<<<std::min<uint32_t>(n_tiles, (uint32_t)c->n_sm * 16), EX_THREADS, 0, st>>>(ea);
     } else {
@@ -705,7 +709,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         ra.tile_prefix = c->tile_counts.as<uint32_t>(); ra.n_tiles = n_tiles; ra.tile_bytes = tile_bytes;
         ra.span_counts = fused ? c->fs_lists.as<uint16_t>() : nullptr; ra.log_off = c->log_off.as<uint64_t>(); ra.n_logs = n_logs;
         ra.line_start = c->line_start.as<uint32_t>(); ra.line_end = c->line_end.as<uint32_t>(); ra.n_lines_total = (uint32_t)line_cap;
-        ra.tasks = c->tasks.as<uint4>(); ra.task_cap = va.task_cap; ra.ctr = ctr;
+        ra.tasks = c->tasks.as<uint4>(); ra.task_cap = va.task_cap; ra.ctr = ctr; ra.budget = c->anchor_budget;
         ra.vm_tasks = c->vm_tasks.as<unsigned long long>(); ra.vm_task_cap = va.vm_task_cap;
         ra.recs = c->recs.as<unsigned long long>(); ra.rec_cap = (uint32_t)rec_cap;
         // grids of exactly one resident wave (grid-stride kernels; a partial second wave would run alone at the end)
@@ -750,6 +754,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         da.n_groups = (uint32_t)std::min<size_t>(DS_MAXG, c->d_group_blob.size() - g0);
         for (int w = 0; w < 8; ++w) da.skip1[w] = 0xFFFFFFFFu;
         da.line_skip = fused ? c->line_skip.as<uint8_t>() : nullptr;      // the flags hold for every group (k_fscan used the intersection)
+        da.scan_list = fused ? c->scan_list.as<uint32_t>() : nullptr;
         for (uint32_t q = 0; q < da.n_groups; ++q) {
             for (int w = 0; w < 8; ++w) da.skip1[w] &= c->plan.groups[g0 + q].skip1[w];
             da.blob[q] = c->d_group_blob[g0 + q]; da.blob_words[q] = c->group_words[g0 + q];
@@ -1137,6 +1142,7 @@ static lp_ctx* create_worker(const lp_scoring_cfg* cfg, int device) {
     CK(cudaGetDeviceProperties(&prop, device));
     ctx->n_sm = prop.multiProcessorCount;
     if (const char* m = getenv("LP_SCAN_MODE")) ctx->scan_mode = strcmp(m, "legacy") == 0 ? 1 : 0;
+    if (const char* v = getenv("LP_ANCHOR_BUDGET")) ctx->anchor_budget = (uint32_t)std::max(1, std::min(4096, atoi(v)));
     if (const char* v = getenv("LP_VM_BLOCKS")) ctx->vm_blocks_per_sm = (uint32_t)std::max(1, std::min(16, atoi(v)));
     if (const char* v = getenv("LP_FSCAN_VARIANT")) ctx->fscan_variant = std::max(0, std::min(3, atoi(v)));
     std::vector<double> lut((size_t)cfg->max_window + 1);
@@ -1194,7 +1200,7 @@ void lp_destroy(lp_ctx* c) {
                      &c->ev_log, &c->slot_key, &c->slot_key_alt, &c->ev_idx, &c->ev_idx_alt, &c->rank_in_slot, &c->freq_delta, &c->prior,
                      &c->out_arena, &c->sort_key, &c->sort_key_alt, &c->order, &c->order_alt,
                      &c->log_sorted, &c->log_sorted_alt, &c->log_event_begin, &c->n_unique, &c->d_lut,
-                     &c->f_bitmap, &c->f_key, &c->f_lits, &c->f_bytes, &c->f_bits, &c->f_gkeys, &c->fs_lists, &c->line_skip, &c->items, &c->ss_keys, &c->ss_idx, &c->seq_tab_off, &c->seq_tab, &c->seq_T, &c->prior_eff, &c->any_flag, &c->dist_mine, &c->dist_all, &c->range_dev};
+                     &c->f_bitmap, &c->f_key, &c->f_lits, &c->f_bytes, &c->f_bits, &c->f_gkeys, &c->fs_lists, &c->scan_list, &c->line_skip, &c->items, &c->ss_keys, &c->ss_idx, &c->seq_tab_off, &c->seq_tab, &c->seq_T, &c->prior_eff, &c->any_flag, &c->dist_mine, &c->dist_all, &c->range_dev};
     for (DevBuf* b : all) b->release();
     if (c->nccl_comm) nccl_comm_destroy(c->nccl_comm);
     c->stage.release();

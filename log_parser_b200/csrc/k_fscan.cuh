@@ -382,12 +382,27 @@ struct ExpandArgs {
     uint32_t* line_start;
     uint32_t* line_end;
     uint8_t* line_skip;               // [line_cap] out (may be NULL): 1 = the always-on scan need not walk this line
+    uint32_t* scan_list;              // [line_cap] out (with line_skip): the lines it has to walk, compacted (any order)
     uint32_t skip1[8];
     uint32_t* first_line;             // [n_logs+1]
     uint32_t line_cap;
     Counters* ctr;
 };
 constexpr int EX_THREADS = 256;
+// Appends line g to the list of lines the always-on scan walks, one global atomic per warp. Called by every lane that is
+// active at the call site (`want` false: nothing to add). A warp of k_dfa_scan that takes 32 consecutive lines nearly
+// always holds a stack frame or two, so skipping inside it saved memory traffic but no time; with the list only the
+// lines that need it are dealt out.
+__device__ __forceinline__ void ex_append_scan(const ExpandArgs& a, uint32_t g, bool want) {
+    const unsigned act = __activemask();
+    const unsigned votes = __ballot_sync(act, want);
+    if (!votes) return;
+    const int lane = threadIdx.x & 31, leader = __ffs(votes) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(&a.ctr->n_scan, (unsigned)__popc(votes));
+    base = __shfl_sync(act, base, leader);
+    if (want) a.scan_list[base + __popc(votes & ((1u << lane) - 1u))] = g;
+}
 __global__ void __launch_bounds__(EX_THREADS) k_expand(ExpandArgs a) {
     __shared__ uint32_t s_warp[EX_THREADS / 32];
     __shared__ uint32_t s_pre[17];      // exclusive prefix of the 16 span counts; [16] = the tile's total
@@ -440,6 +455,7 @@ __global__ void __launch_bounds__(EX_THREADS) k_expand(ExpandArgs a) {
                     a.line_start[g + 1] = (uint32_t)(p + 1);
                     if (a.line_skip) a.line_skip[g + 1] = (uint8_t)((ent >> 14) & 1u);
                 } else atomicOr(&a.ctr->overflow, 64u);
+                if (a.scan_list) ex_append_scan(a, g + 1, g + 1 < a.line_cap && !((ent >> 14) & 1u));
             }
             if (events) {       // start of log j / end of log j-1 inside this tile: newlines before it = spans in front + a binary search in its span
                 uint32_t j = lower_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, base) + threadIdx.x;
@@ -455,6 +471,7 @@ __global__ void __launch_bounds__(EX_THREADS) k_expand(ExpandArgs a) {
                         if (j < a.n_logs) { a.line_start[nlb + j] = (uint32_t)b; if (a.line_skip) a.line_skip[nlb + j] = 0; }   // first line of a log: always walked
                         if (j > 0) a.line_end[nlb + j - 1] = (uint32_t)b;
                     } else atomicOr(&a.ctr->overflow, 64u);
+                    if (a.scan_list) ex_append_scan(a, nlb + j, nlb + j < a.line_cap && j < a.n_logs);
                 }
             }
             continue;
@@ -486,14 +503,17 @@ __global__ void __launch_bounds__(EX_THREADS) k_expand(ExpandArgs a) {
             if (inner) k = upper_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, p) - 1;
             const uint32_t g = excl + __popcll(nl & ((1ull << i) - 1ull)) + k;
             const bool cr = p > a.log_off[k] && a.text[p - 1] == '\r';
+            uint32_t sk = 0;
             if (g + 1 < a.line_cap) {
                 a.line_end[g] = (uint32_t)(p - (cr ? 1 : 0));
                 a.line_start[g + 1] = (uint32_t)(p + 1);
                 if (a.line_skip) {
                     const uint32_t nb = p + 1 < a.len ? a.text[p + 1] : 0u;
-                    a.line_skip[g + 1] = (uint8_t)((nb != '\n' && nb != 0u) ? ((a.skip1[nb >> 5] >> (nb & 31u)) & 1u) : 0u);
+                    sk = (nb != '\n' && nb != 0u) ? ((a.skip1[nb >> 5] >> (nb & 31u)) & 1u) : 0u;
+                    a.line_skip[g + 1] = (uint8_t)sk;
                 }
             } else atomicOr(&a.ctr->overflow, 64u);
+            if (a.scan_list) ex_append_scan(a, g + 1, g + 1 < a.line_cap && !sk);
         }
         if (events && pos <= a.len) {
             uint32_t j = lower_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, pos);
@@ -505,6 +525,7 @@ __global__ void __launch_bounds__(EX_THREADS) k_expand(ExpandArgs a) {
                     if (j < a.n_logs) { a.line_start[nlb + j] = (uint32_t)b; if (a.line_skip) a.line_skip[nlb + j] = 0; }
                     if (j > 0) a.line_end[nlb + j - 1] = (uint32_t)b;
                 } else atomicOr(&a.ctr->overflow, 64u);
+                if (a.scan_list) ex_append_scan(a, nlb + j, nlb + j < a.line_cap && j < a.n_logs);
                 ++j;
             }
         }

@@ -280,8 +280,9 @@ struct ResolveArgs {
     unsigned long long* recs;
     uint32_t rec_cap;
     Counters* ctr;
+    uint32_t budget;                 // anchored-walk steps per item (ANCHOR_BUDGET)
 };
-constexpr uint32_t ANCHOR_BUDGET = 24;     // automaton steps an item may spend here before it is handed to k_verify
+constexpr uint32_t ANCHOR_BUDGET = 12;     // default of ResolveArgs::budget: automaton steps an item may spend in k_resolve before it is handed to k_verify
 constexpr uint32_t T_STAGE = 1024;         // tasks staged per block of k_resolve
 constexpr uint32_t VT_FWD = 1u << 30, VT_REV = 1u << 31;      // task.x flags: continue an anchored walk forwards / backwards (else: whole-line walk)
 __global__ void __launch_bounds__(256) k_resolve(ResolveArgs a, DevPlan P) {
@@ -360,7 +361,7 @@ __global__ void __launch_bounds__(256) k_resolve(ResolveArgs a, DevPlan P) {
             } else {
                 // every match starts (class 1) / ends (class 2) with this literal: anchored automaton from the
                 // occurrence. Walks die or match within a few bytes; one that is still undecided after
-                // ANCHOR_BUDGET steps (".*" tails) goes to k_verify's walk of the whole line.
+                // `budget` steps (".*" tails) is handed to k_verify, which carries the same walk on.
                 const uint4 ad = __ldg(&P.anchor_desc[r]);
                 const uint32_t nc = ad.y;
                 const uint16_t* __restrict__ T = P.dfa_trans + ad.x;
@@ -369,21 +370,21 @@ __global__ void __launch_bounds__(256) k_resolve(ResolveArgs a, DevPlan P) {
                 w.nc[0] = nc; w.T[0] = T; w.cm[0] = cm; w.ff[0] = 0;
                 if (cls == 1) {
                     w.st[0] = s == ls ? (ad.z & 0xFFFFu) : dev_word(a.text[s - 1]) ? ad.w : (ad.z >> 16);
-                    const uint32_t stop = min(le, s + ANCHOR_BUDGET);
+                    const uint32_t stop = min(le, s + a.budget);
                     const long tpos = tail_terminator(a.text, ls, le);
                     if (tpos < 0 || (long)s > tpos || (long)stop <= tpos) w.segment(a.text, a.len, s, stop);
                     else if (w.segment(a.text, a.len, s, (uint32_t)tpos)) { w.symbol(2); w.segment(a.text, a.len, (uint32_t)tpos, stop); }
                     if (stop == le) w.symbol(1);
                 } else {
                     w.st[0] = e2 == le ? (ad.z & 0xFFFFu) : dev_word(a.text[e2]) ? ad.w : (ad.z >> 16);
-                    const uint32_t stop = e2 - ls > ANCHOR_BUDGET ? e2 - ANCHOR_BUDGET : ls;
+                    const uint32_t stop = e2 - ls > a.budget ? e2 - a.budget : ls;
                     w.segment_rev(a.text, a.len, stop, e2);
                     if (stop == ls) w.symbol(1);
                 }
                 const uint32_t st = w.st[0];
                 if (st == 1u) stage_put(s_rec, a.ctr, &a.ctr->n_recs, a.recs, a.rec_cap, 4u, rec);
                 else if (st > 1u)       // undecided: k_verify carries this walk on from where it stopped, in the state it stopped in
-                    put_task(make_uint4(r | (cls == 1 ? VT_FWD : VT_REV), g, cls == 1 ? min(le, s + ANCHOR_BUDGET) : (e2 - ls > ANCHOR_BUDGET ? e2 - ANCHOR_BUDGET : ls), st));
+                    put_task(make_uint4(r | (cls == 1 ? VT_FWD : VT_REV), g, cls == 1 ? min(le, s + a.budget) : (e2 - ls > a.budget ? e2 - a.budget : ls), st));
             }
         } while (false);
         // no barrier per chunk: a block handles a few chunks and its output fits the staging buffers
@@ -665,6 +666,8 @@ struct DfaScanArgs {
     int write_flags;             // 0 leave alone, 1 store every line's flag byte, 2 OR this launch's bits in
     uint32_t skip1[8];           // first bytes on which every group of this launch is decided without a hit: such lines are not walked
     const uint8_t* line_skip;    // [lines] 1 = k_fscan saw such a first byte while the text was in shared memory (NULL: look at the text here)
+    const uint32_t* scan_list;   // the lines to walk, compacted by k_expand (ctr->n_scan of them), or NULL: every line is visited;
+                                 // with the list the flag bytes of the other lines must have been cleared beforehand
     unsigned long long* recs;
     uint32_t rec_cap;
     uint32_t gb;
@@ -714,7 +717,10 @@ __global__ void __launch_bounds__(DS_THREADS) k_dfa_scan(DfaScanArgs a) {
 
     const uint32_t stride = gridDim.x * DS_THREADS;
     const uint32_t n_total = min(a.ctr->n_lines_total, a.n_lines_total);     // host passes the capacity
-    for (uint32_t g = blockIdx.x * DS_THREADS + threadIdx.x; g < n_total; g += stride) {
+    const uint32_t n_iter = a.scan_list ? min(a.ctr->n_scan, a.n_lines_total) : n_total;
+    for (uint32_t it = blockIdx.x * DS_THREADS + threadIdx.x; it < n_iter; it += stride) {
+        const uint32_t g = a.scan_list ? a.scan_list[it] : it;
+        if (g >= n_total) continue;
         const uint32_t k = a.n_logs == 1 ? 0 : upper_bound_dev<uint32_t>(a.first_line, a.n_logs + 1, g) - 1;
         const bool live = k < a.n_logs && g - a.first_line[k] < a.n_lines[k];
         uint32_t flags = 0;
@@ -722,7 +728,8 @@ __global__ void __launch_bounds__(DS_THREADS) k_dfa_scan(DfaScanArgs a) {
         uint32_t ls = 0, le = 0;
         if (live) {
             ls = a.line_start[g]; le = a.line_end[g];
-            if (a.line_skip) walk = a.line_skip[g] == 0;
+            if (a.scan_list) walk = true;
+            else if (a.line_skip) walk = a.line_skip[g] == 0;
             else if (le > ls) { const uint32_t b = a.text[ls]; walk = ((a.skip1[b >> 5] >> (b & 31u)) & 1u) == 0; }
         }
         if (walk) {
@@ -748,7 +755,7 @@ __global__ void __launch_bounds__(DS_THREADS) k_dfa_scan(DfaScanArgs a) {
         }
         // every line's flag byte is stored by the first launch (it doubles as the clearing pass); further
         // launches, when the groups do not fit one, add their bits (a line belongs to one thread)
-        if (a.write_flags == 1) a.ctx_flags[g] = (uint8_t)flags;
+        if (a.write_flags == 1 && (!a.scan_list || flags)) a.ctx_flags[g] = (uint8_t)flags;
         else if (a.write_flags == 2 && flags) a.ctx_flags[g] = (uint8_t)(a.ctx_flags[g] | flags);
     }
 }

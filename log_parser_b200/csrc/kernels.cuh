@@ -109,6 +109,7 @@ struct Counters {
     unsigned int n_items[4];       // (literal occurrence, regex) pairs per verification class, k_confirm -> k_resolve
     unsigned int n_budget;         // (line, regex) evaluations the backtracking verifier gave up on (step / stack budget)
     unsigned int vm_pool_next;     // deep backtracking stacks handed out so far in this call
+    unsigned int n_scan;           // lines the always-on scan has to walk (k_expand's list)
 };
 
 }  // namespace lpk
