@@ -666,7 +666,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     CK(cudaMemsetAsync(c->recs.p, 0xFF, rec_cap * 8, st));            // padding sentinels sort last
     CK(cudaMemsetAsync(c->ev_key_alt.p, 0xFF, ev_cap * 8, st));
     if (!c->plan.ctx_any_in_groups || fused) CK(cudaMemsetAsync(c->ctx_flags.p, 0, (line_cap / 4 + 2) * 4, st));   // else k_dfa_scan (walking every line) writes every byte
-    k_scan_tiles<<<1, 1024, 0, st>>>(c->tile_counts.as<uint32_t>(), fused ? c->fs_lists.as<uint16_t>() : nullptr, n_tiles, n_logs, ctr);
+    k_scan_tiles<<<1, 1024, n_tiles <= 16384 ? (size_t)n_tiles * 4 : 0, st>>>(c->tile_counts.as<uint32_t>(), fused ? c->fs_lists.as<uint16_t>() : nullptr, n_tiles, n_logs, ctr);
     if (fused) {
         ExpandArgs ea{};
         ea.text = d_text; ea.len = len; ea.n_tiles = n_tiles; ea.tile_prefix = c->tile_counts.as<uint32_t>(); ea.warp_counts = c->fs_lists.as<uint16_t>(); ea.nl_lists = c->fs_lists.as<uint16_t>() + (size_t)n_tiles * 16;
@@ -1173,6 +1173,7 @@ lp_ctx* lp_create(const lp_scoring_cfg* cfg, int device) {
         CK(cudaFuncSetAttribute(k_fscan<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs::SMEM_BYTES));
         CK(cudaFuncSetAttribute(k_fscan<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs::SMEM_BYTES));
         CK(cudaFuncSetAttribute(k_fscan<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fs::SMEM_BYTES));
+        CK(cudaFuncSetAttribute(k_scan_tiles, cudaFuncAttributeMaxDynamicSharedMemorySize, 16384 * 4));
         CK(cudaFuncSetAttribute(k_tile_sort, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sizeof(SsSorter::TempStorage)));
         CK(cudaFuncSetAttribute(k_dfa_scan<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
         CK(cudaFuncSetAttribute(k_dfa_scan<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024));
