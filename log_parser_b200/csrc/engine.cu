@@ -717,6 +717,9 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
             CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c->occ_confirm, k_confirm, 256, 0));
             CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&c->occ_resolve, k_resolve, 256, 0));
             c->occ_confirm = std::max(1, c->occ_confirm); c->occ_resolve = std::max(1, c->occ_resolve);
+            // (fewer blocks per SM measured slower for both, and k_resolve squeezed to 40 registers for 6 blocks much slower)
+            if (const char* v = getenv("LP_CONFIRM_BLOCKS")) c->occ_confirm = std::max(1, std::min(c->occ_confirm, atoi(v)));
+            if (const char* v = getenv("LP_RESOLVE_BLOCKS")) c->occ_resolve = std::max(1, std::min(c->occ_resolve, atoi(v)));
         }
         k_confirm<<<c->n_sm * c->occ_confirm, 256, 0, st>>>(ca, c->dp);
         k_resolve<<<c->n_sm * c->occ_resolve, 256, 0, st>>>(ra, c->dp);
