@@ -87,25 +87,48 @@ struct ScoreArgs {
     const long long* seq_T;
 };
 
-__device__ __forceinline__ bool list_any_in(const unsigned long long* __restrict__ keys, uint32_t b, uint32_t e, uint32_t r, uint32_t gb,
-                                            uint32_t lo, uint32_t hi /* [lo,hi) global lines */) {
+// lower_bound_dev by a group of SG consecutive lanes (all of them call it with the same arguments and get the same
+// answer): SG probes per round split the range into SG + 1 parts, so a list of 5*10^4 records is searched in 5
+// dependent loads instead of 16. k_score is such searches chained one after the other (70 % of its warp samples
+// wait on them); a whole warp per event made the chains shorter still but the kernel slower (32 times the warps).
+constexpr int SG = 8;
+template <class T>
+__device__ __forceinline__ uint32_t group_lower_bound(const T* __restrict__ a, uint32_t n, T v) {
+    const uint32_t lane = threadIdx.x & 31, sub = lane & (SG - 1), gbase = lane & ~(uint32_t)(SG - 1);
+    const unsigned gmask = ((1u << SG) - 1u) << gbase;
+    uint32_t lo = 0, hi = n;                    // the answer lies in [lo, hi]
+    while (hi - lo > SG) {
+        const uint32_t step = (hi - lo + SG) / (SG + 1);
+        const uint32_t idx = lo + (sub + 1) * step - 1;
+        const bool less = idx < hi && a[idx] < v;
+        const uint32_t k = __popc(__ballot_sync(gmask, less));        // the list is sorted: the first k probes are < v
+        const uint32_t nlo = lo + k * step, nhi = k < SG ? min(hi, lo + (k + 1) * step - 1) : hi;
+        lo = nlo; hi = nhi;
+    }
+    const uint32_t idx = lo + sub;
+    const bool less = idx < hi && a[idx] < v;
+    return lo + __popc(__ballot_sync(gmask, less));
+}
+__device__ __forceinline__ bool group_list_any_in(const unsigned long long* __restrict__ keys, uint32_t b, uint32_t e, uint32_t r, uint32_t gb,
+                                                  uint32_t lo, uint32_t hi /* [lo,hi) global lines */) {
     if (lo >= hi) return false;
-    const uint32_t i = b + lower_bound_dev<unsigned long long>(keys + b, e - b, ((unsigned long long)r << gb) | lo);
+    const uint32_t i = b + group_lower_bound<unsigned long long>(keys + b, e - b, ((unsigned long long)r << gb) | lo);
     return i < e && (uint32_t)(keys[i] & ((1ull << gb) - 1ull)) < hi;
 }
-
+// SG lanes per event: every lane of the group runs the same code on the same values (the searches are cooperative, see
+// group_lower_bound), its first lane writes. The arithmetic is the reference's, in its order (fp64, no contraction).
 __global__ void __launch_bounds__(128) k_score(ScoreArgs a, DevPlan P, ScoreCfg C) {
-    const uint32_t e = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t e = (blockIdx.x * blockDim.x + threadIdx.x) / SG;
+    const bool writer = (threadIdx.x & (SG - 1)) == 0;
     if (e >= a.m_cap) return;
-    a.ev_idx[e] = e;
-    if (e >= a.ctr->n_events) { a.sort_key[e] = ~0ull; a.ev_log[e] = a.n_logs; return; }      // padding sorts last
+    if (writer) a.ev_idx[e] = e;
+    if (e >= a.ctr->n_events) { if (writer) { a.sort_key[e] = ~0ull; a.ev_log[e] = a.n_logs; } return; }      // padding sorts last
     if (a.range_dev) { a.line_base = a.range_dev[0]; a.n_global = a.range_dev[1]; }
     const unsigned long long ek = a.ev_key[e];
     const uint32_t g = (uint32_t)(ek >> P.pb), p = (uint32_t)(ek & ((1ull << P.pb) - 1ull));
     const unsigned long long gmask = (1ull << P.gb) - 1ull;
     const uint32_t k = a.n_logs == 1 ? 0u : upper_bound_dev<uint32_t>(a.first_line, a.n_logs + 1, g) - 1;
-    a.ev_log[e] = k;
-    atomicAdd(&a.freq_delta[p], 1ull);        // FTS:41-56: one recordPatternMatch per event, applied by the host after the call
+    if (writer) { a.ev_log[e] = k; atomicAdd(&a.freq_delta[p], 1ull); }        // FTS:41-56: one recordPatternMatch per event, applied by the host after the call
     const uint32_t first = a.first_line[k];
     const long long N = a.n_lines[k];
     const long long i = (long long)g - first;
@@ -141,7 +164,7 @@ __global__ void __launch_bounds__(128) k_score(ScoreArgs a, DevPlan P, ScoreCfg 
                 const unsigned long long* kk = a.keys + b;
                 const uint32_t cnt = en - b;
                 const unsigned long long self = ((unsigned long long)r << P.gb) | g;
-                const uint32_t at = lower_bound_dev<unsigned long long>(kk, cnt, self);
+                const uint32_t at = group_lower_bound<unsigned long long>(kk, cnt, self);
                 long long best = -1;
                 if (at > 0) {
                     const long long l = (long long)(uint32_t)(kk[at - 1] & gmask) - first;
@@ -170,7 +193,7 @@ __global__ void __launch_bounds__(128) k_score(ScoreArgs a, DevPlan P, ScoreCfg 
                 if (eb == ee) continue;                                  // SS:233-235
                 const uint32_t rl = P.ev_rx[ee - 1];
                 const long long nlo = max(0ll, i - 5), nhi = min(N, i + 6);  // SS:275-277
-                if (!list_any_in(a.keys, a.rx_begin[rl], a.rx_begin[rl + 1], rl, P.gb, first + (uint32_t)nlo, first + (uint32_t)nhi)) continue;
+                if (!group_list_any_in(a.keys, a.rx_begin[rl], a.rx_begin[rl + 1], rl, P.gb, first + (uint32_t)nlo, first + (uint32_t)nhi)) continue;
                 bool ok = true;
                 long long T = -1;   // local line of the earliest feasible position of the previous event
                 if (a.seq_T) ok = a.seq_T[q] < i + a.line_base;
@@ -178,7 +201,7 @@ __global__ void __launch_bounds__(128) k_score(ScoreArgs a, DevPlan P, ScoreCfg 
                     const uint32_t r = P.ev_rx[j];
                     const uint32_t b = a.rx_begin[r], en = a.rx_begin[r + 1];
                     const unsigned long long want = ((unsigned long long)r << P.gb) | (uint32_t)(first + T + 1);
-                    const uint32_t at = b + lower_bound_dev<unsigned long long>(a.keys + b, en - b, want);
+                    const uint32_t at = b + group_lower_bound<unsigned long long>(a.keys + b, en - b, want);
                     if (at >= en) { ok = false; break; }
                     const long long l = (long long)(uint32_t)(a.keys[at] & gmask) - first;
                     if (l >= i) { ok = false; break; }     // must end strictly before the primary line
@@ -227,9 +250,9 @@ __global__ void __launch_bounds__(128) k_score(ScoreArgs a, DevPlan P, ScoreCfg 
                 const uint32_t q = P.slot_pats[j], rq = P.pat_primary[q];
                 const uint32_t b = a.rx_begin[rq], cnt2 = a.rx_begin[rq + 1] - b;
                 const unsigned long long want = ((unsigned long long)rq << P.gb) | g;
-                const uint32_t at = lower_bound_dev<unsigned long long>(a.keys + b, cnt2, want);
+                const uint32_t at = group_lower_bound<unsigned long long>(a.keys + b, cnt2, want);
                 earlier += at;
-                if (a.n_global) earlier -= lower_bound_dev<unsigned long long>(a.keys + b, cnt2, ((unsigned long long)rq << P.gb) | a.core_lo);
+                if (a.n_global) earlier -= group_lower_bound<unsigned long long>(a.keys + b, cnt2, ((unsigned long long)rq << P.gb) | a.core_lo);
                 if (q < p && at < cnt2 && a.keys[b + at] == want) earlier += 1;
             }
             const unsigned long long cnt = pr + earlier;
@@ -247,6 +270,7 @@ __global__ void __launch_bounds__(128) k_score(ScoreArgs a, DevPlan P, ScoreCfg 
     s = __dmul_rn(s, ctx);
     s = __dmul_rn(s, __dsub_rn(1.0, pen));
 
+    if (!writer) return;
     a.out_line[e] = (uint32_t)(i + a.line_base + 1);
     a.out_pat[e] = p;
     a.out_score[e] = s;
