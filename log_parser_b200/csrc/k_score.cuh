@@ -91,9 +91,9 @@ struct ScoreArgs {
 // answer): SG probes per round split the range into SG + 1 parts, so a list of 5*10^4 records is searched in 5
 // dependent loads instead of 16. k_score is such searches chained one after the other (70 % of its warp samples
 // wait on them); a whole warp per event made the chains shorter still but the kernel slower (32 times the warps).
-constexpr int SG = 8;
-template <class T>
+template <int SG, class T>
 __device__ __forceinline__ uint32_t group_lower_bound(const T* __restrict__ a, uint32_t n, T v) {
+    if constexpr (SG == 1) return lower_bound_dev<T>(a, n, v);
     const uint32_t lane = threadIdx.x & 31, sub = lane & (SG - 1), gbase = lane & ~(uint32_t)(SG - 1);
     const unsigned gmask = ((1u << SG) - 1u) << gbase;
     uint32_t lo = 0, hi = n;                    // the answer lies in [lo, hi]
@@ -109,16 +109,57 @@ __device__ __forceinline__ uint32_t group_lower_bound(const T* __restrict__ a, u
     const bool less = idx < hi && a[idx] < v;
     return lo + __popc(__ballot_sync(gmask, less));
 }
+template <int SG>
 __device__ __forceinline__ bool group_list_any_in(const unsigned long long* __restrict__ keys, uint32_t b, uint32_t e, uint32_t r, uint32_t gb,
                                                   uint32_t lo, uint32_t hi /* [lo,hi) global lines */) {
     if (lo >= hi) return false;
-    const uint32_t i = b + group_lower_bound<unsigned long long>(keys + b, e - b, ((unsigned long long)r << gb) | lo);
+    const uint32_t i = b + group_lower_bound<SG, unsigned long long>(keys + b, e - b, ((unsigned long long)r << gb) | lo);
     return i < e && (uint32_t)(keys[i] & ((1ull << gb) - 1ull)) < hi;
+}
+// context factor, CAS:46-117, accumulated in the reference's per-line order. The walk over the context lines is a
+// serial chain of fp64 additions that cannot be split between lanes without changing the rounding; it is done with
+// one thread per event (a warp of the block takes the block's events) so that a wide window (C4: +-500 lines) costs
+// its issue slots once per 32 events, not once per group.
+__device__ __forceinline__ double ctx_factor(const ScoreArgs& a, const DevPlan& P, const ScoreCfg& C, uint32_t g, uint32_t p) {
+    const uint32_t k = a.n_logs == 1 ? 0u : upper_bound_dev<uint32_t>(a.first_line, a.n_logs + 1, g) - 1;
+    const uint32_t first = a.first_line[k];
+    const long long N = a.n_lines[k];
+    const long long i = (long long)g - first;
+    long long b0 = i, a1 = i + 1;
+    if (P.pat_has_ctx[p]) { b0 = max(0ll, i - (long long)P.pat_before[p]); a1 = min(N, i + 1 + (long long)P.pat_after[p]); }
+    double score = 0.0;
+    int err = 0, stack = 0;
+    const uint8_t* __restrict__ fl = a.ctx_flags + first;
+    for (long long l = b0; l < a1; ++l) {
+        const uint32_t f = fl[l];
+        if (f & 1u) { ++err; score = __dadd_rn(score, 0.4); }
+        else if (f & 2u) { score = __dadd_rn(score, 0.2); }
+        if (f & 4u) { ++stack; score = __dadd_rn(score, 0.1); }
+        if (f & 8u) { score = __dadd_rn(score, 0.3); }
+    }
+    if (stack > 0) score = __dadd_rn(score, fmin(__dmul_rn((double)stack, 0.1), 0.5));
+    const int total = (int)(a1 - b0);
+    if (total > 10 && (double)(stack + err) > __dmul_rn((double)total, 0.7)) score = __dmul_rn(score, 0.8);
+    double ctx = __dadd_rn(1.0, score);
+    if (ctx > C.max_ctx) ctx = C.max_ctx;
+    if (total <= 0) ctx = 1.0;
+    return ctx;
 }
 // SG lanes per event: every lane of the group runs the same code on the same values (the searches are cooperative, see
 // group_lower_bound), its first lane writes. The arithmetic is the reference's, in its order (fp64, no contraction).
-__global__ void __launch_bounds__(128) k_score(ScoreArgs a, DevPlan P, ScoreCfg C) {
-    const uint32_t e = (blockIdx.x * blockDim.x + threadIdx.x) / SG;
+template <int SG, int SC_THREADS>
+__global__ void __launch_bounds__(SC_THREADS) k_score(ScoreArgs a, DevPlan P, ScoreCfg C) {
+    constexpr int SC_EVENTS = SC_THREADS / SG;       // events of one block
+    __shared__ double s_ctx[SG > 1 ? SC_EVENTS : 1];
+    if (SG > 1 && threadIdx.x < SC_EVENTS) {      // the block's context factors, one thread per event
+        const uint32_t e2 = blockIdx.x * SC_EVENTS + threadIdx.x;
+        if (e2 < a.m_cap && e2 < a.ctr->n_events) {
+            const unsigned long long ek2 = a.ev_key[e2];
+            s_ctx[threadIdx.x] = ctx_factor(a, P, C, (uint32_t)(ek2 >> P.pb), (uint32_t)(ek2 & ((1ull << P.pb) - 1ull)));
+        }
+    }
+    if (SG > 1) __syncthreads();
+    const uint32_t e = blockIdx.x * SC_EVENTS + threadIdx.x / SG;
     const bool writer = (threadIdx.x & (SG - 1)) == 0;
     if (e >= a.m_cap) return;
     if (writer) a.ev_idx[e] = e;
@@ -164,7 +205,7 @@ __global__ void __launch_bounds__(128) k_score(ScoreArgs a, DevPlan P, ScoreCfg 
                 const unsigned long long* kk = a.keys + b;
                 const uint32_t cnt = en - b;
                 const unsigned long long self = ((unsigned long long)r << P.gb) | g;
-                const uint32_t at = group_lower_bound<unsigned long long>(kk, cnt, self);
+                const uint32_t at = group_lower_bound<SG, unsigned long long>(kk, cnt, self);
                 long long best = -1;
                 if (at > 0) {
                     const long long l = (long long)(uint32_t)(kk[at - 1] & gmask) - first;
@@ -193,7 +234,7 @@ __global__ void __launch_bounds__(128) k_score(ScoreArgs a, DevPlan P, ScoreCfg 
                 if (eb == ee) continue;                                  // SS:233-235
                 const uint32_t rl = P.ev_rx[ee - 1];
                 const long long nlo = max(0ll, i - 5), nhi = min(N, i + 6);  // SS:275-277
-                if (!group_list_any_in(a.keys, a.rx_begin[rl], a.rx_begin[rl + 1], rl, P.gb, first + (uint32_t)nlo, first + (uint32_t)nhi)) continue;
+                if (!group_list_any_in<SG>(a.keys, a.rx_begin[rl], a.rx_begin[rl + 1], rl, P.gb, first + (uint32_t)nlo, first + (uint32_t)nhi)) continue;
                 bool ok = true;
                 long long T = -1;   // local line of the earliest feasible position of the previous event
                 if (a.seq_T) ok = a.seq_T[q] < i + a.line_base;
@@ -201,7 +242,7 @@ __global__ void __launch_bounds__(128) k_score(ScoreArgs a, DevPlan P, ScoreCfg 
                     const uint32_t r = P.ev_rx[j];
                     const uint32_t b = a.rx_begin[r], en = a.rx_begin[r + 1];
                     const unsigned long long want = ((unsigned long long)r << P.gb) | (uint32_t)(first + T + 1);
-                    const uint32_t at = b + group_lower_bound<unsigned long long>(a.keys + b, en - b, want);
+                    const uint32_t at = b + group_lower_bound<SG, unsigned long long>(a.keys + b, en - b, want);
                     if (at >= en) { ok = false; break; }
                     const long long l = (long long)(uint32_t)(a.keys[at] & gmask) - first;
                     if (l >= i) { ok = false; break; }     // must end strictly before the primary line
@@ -213,28 +254,7 @@ __global__ void __launch_bounds__(128) k_score(ScoreArgs a, DevPlan P, ScoreCfg 
         }
     }
 
-    // context factor, CAS:46-117, accumulated in the reference's per-line order
-    double ctx;
-    {
-        long long b0 = i, a1 = i + 1;
-        if (P.pat_has_ctx[p]) { b0 = max(0ll, i - (long long)P.pat_before[p]); a1 = min(N, i + 1 + (long long)P.pat_after[p]); }
-        double score = 0.0;
-        int err = 0, stack = 0;
-        const uint8_t* __restrict__ fl = a.ctx_flags + first;
-        for (long long l = b0; l < a1; ++l) {
-            const uint32_t f = fl[l];
-            if (f & 1u) { ++err; score = __dadd_rn(score, 0.4); }
-            else if (f & 2u) { score = __dadd_rn(score, 0.2); }
-            if (f & 4u) { ++stack; score = __dadd_rn(score, 0.1); }
-            if (f & 8u) { score = __dadd_rn(score, 0.3); }
-        }
-        if (stack > 0) score = __dadd_rn(score, fmin(__dmul_rn((double)stack, 0.1), 0.5));
-        const int total = (int)(a1 - b0);
-        if (total > 10 && (double)(stack + err) > __dmul_rn((double)total, 0.7)) score = __dmul_rn(score, 0.8);
-        ctx = __dadd_rn(1.0, score);
-        if (ctx > C.max_ctx) ctx = C.max_ctx;
-        if (total <= 0) ctx = 1.0;
-    }
+    const double ctx = SG > 1 ? s_ctx[threadIdx.x / SG] : ctx_factor(a, P, C, g, p);      // groups: computed above, one thread per event
 
     // frequency penalty, FTS:64-93 with the count read before this match is recorded (SS:84-88)
     double pen = 0.0;
@@ -250,9 +270,9 @@ __global__ void __launch_bounds__(128) k_score(ScoreArgs a, DevPlan P, ScoreCfg 
                 const uint32_t q = P.slot_pats[j], rq = P.pat_primary[q];
                 const uint32_t b = a.rx_begin[rq], cnt2 = a.rx_begin[rq + 1] - b;
                 const unsigned long long want = ((unsigned long long)rq << P.gb) | g;
-                const uint32_t at = group_lower_bound<unsigned long long>(a.keys + b, cnt2, want);
+                const uint32_t at = group_lower_bound<SG, unsigned long long>(a.keys + b, cnt2, want);
                 earlier += at;
-                if (a.n_global) earlier -= group_lower_bound<unsigned long long>(a.keys + b, cnt2, ((unsigned long long)rq << P.gb) | a.core_lo);
+                if (a.n_global) earlier -= group_lower_bound<SG, unsigned long long>(a.keys + b, cnt2, ((unsigned long long)rq << P.gb) | a.core_lo);
                 if (q < p && at < cnt2 && a.keys[b + at] == want) earlier += 1;
             }
             const unsigned long long cnt = pr + earlier;
