@@ -688,7 +688,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     k_lines<<<std::min<uint32_t>(n_tiles, (uint32_t)c->n_sm * 4), LN_TILE_THREADS, 0, st>>>(sa);
     }
     c->launches += 2;
-    k_log_meta<<<blocks_for(n_logs, 128), 128, 0, st>>>(c->first_line.as<uint32_t>(), c->line_start.as<uint32_t>(),
+    k_log_meta<<<std::min<uint32_t>(n_logs, (uint32_t)c->n_sm * 8), LM_THREADS, 0, st>>>(c->first_line.as<uint32_t>(), c->line_start.as<uint32_t>(),
                                                          c->line_end.as<uint32_t>(), n_logs, (uint32_t)line_cap, rg ? 1u : 0u, c->n_lines.as<uint32_t>());
     CK(cudaEventRecord(c->ev[9], st));
     c->launches += 2;

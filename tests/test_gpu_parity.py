@@ -75,6 +75,22 @@ def test_split_edge_cases(parser, oracle, log, n):
         assert (int(res.line_start[i]), int(res.line_end[i])) == (s, e)
 
 
+def test_long_tail_of_empty_lines_is_trimmed(parser, oracle):
+    """A log (and logs of a batch) ending in hundreds of thousands of blank lines: String.split drops them all
+    (AS:53); k_log_meta finds the last non-empty line 256 lines at a time, one block per log."""
+    pats = [PatternSpec(id="p", primary_regex="hit", confidence=0.7, severity="HIGH")]
+    parser.load_patterns(pats)
+    log = b"a\nhit 1\n\nhit 2" + b"\n" * 300_000
+    res = parser.analyze(log)
+    ora = oracle.analyze(ScoringConfig(), pats, log)
+    assert ora.n_lines == 4
+    _check(res, ora)
+    logs = [b"hit\r\n" + b"\r\n" * 70_000, b"x\n\n\nhit", b"\n" * 1000, b"hit" + b"\n" * 513]
+    batch = parser.analyze_batch(logs)
+    for k, one in enumerate(logs):
+        _check(batch, oracle.analyze(ScoringConfig(), pats, one), log_index=k)
+
+
 def test_all_factors_small(parser, oracle):
     log = b"\n".join([b"start", b"connect begin", b"WARN slow", b"boom OutOfMemoryError", b"retry", b"x", b"y", b"z", b"w", b"v"])
     pats = [PatternSpec(id="p1", primary_regex="OutOfMemoryError", confidence=0.8, severity="high", lines_before=2, lines_after=1,
