@@ -545,8 +545,8 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     const uint32_t n_always = (uint32_t)c->plan.always_list.size();
     const uint32_t n_always_vm = (uint32_t)c->plan.always_vm_list.size();
     const bool has_vm = c->plan.n_vm > 0;
-    // one thread per (line, regex) evaluation with a private 16 KB backtracking stack (620 MB of stacks, allocated only
-    // when such patterns exist; four times as many threads measured no faster: the kernel is bound by divergence)
+    // one lane per (line, regex) evaluation; the top of its backtracking stack is in local memory, deeper entries come
+    // from a pool (VM_POOL_STACKS x 16 KB, allocated only when such patterns exist)
     const uint32_t vm_grid = (uint32_t)c->n_sm * c->vm_blocks_per_sm, vm_block = 128;
 
     // first-call estimates (later calls reuse what earlier logs needed; an under-estimate costs one re-run)
