@@ -439,6 +439,11 @@ bool small_sort(lp_ctx* c, const unsigned long long* in, uint32_t n, int end_bit
                 const unsigned int* n_valid) {
     const uint32_t n_tiles = (n + SS_TILE - 1) / SS_TILE;
     if (n == 0 || n_tiles > SS_MAX_TILES) return false;
+    if (n <= TR_MAX) {       // a small request: ranks by counting, one launch
+        k_tiny_rank<<<(n + TR_ELEMS - 1) / TR_ELEMS, TR_THREADS, 0, c->stream>>>(in, n, out_sorted, out_rank, n_valid);
+        c->launches += 1;
+        return true;
+    }
     c->ss_keys.ensure((size_t)n_tiles * SS_TILE * 8);
     c->ss_idx.ensure((size_t)n_tiles * SS_TILE * 4);
     k_tile_sort<<<n_tiles, SS_THREADS, sizeof(SsSorter::TempStorage), c->stream>>>(in, n, end_bit, c->ss_keys.as<unsigned long long>(), c->ss_idx.as<uint32_t>());

@@ -71,6 +71,31 @@ __global__ void __launch_bounds__(128) k_tile_rank(const unsigned long long* __r
     if (out_sorted && r < n) out_sorted[r] = key;
     if (out_rank) { const uint32_t i = tile_idx[j]; if (i < *n_valid) out_rank[i] = r; }
 }
+// Up to TR_MAX keys (one small request: C1 has ~10^2 events): final positions by counting, in one launch. Every block
+// holds all keys in shared memory and ranks 64 of them, four lanes per key splitting the comparisons; stable (equal keys
+// keep their order). A tile sort of 64-bit keys is eleven block-wide radix passes whatever the number of keys (33 us).
+constexpr uint32_t TR_MAX = 2048;
+constexpr int TR_THREADS = 256, TR_PER = 4, TR_ELEMS = TR_THREADS / TR_PER;
+__global__ void __launch_bounds__(TR_THREADS) k_tiny_rank(const unsigned long long* __restrict__ in, uint32_t n, unsigned long long* __restrict__ out_sorted,
+                                                          uint32_t* __restrict__ out_rank, const unsigned int* __restrict__ n_valid) {
+    __shared__ unsigned long long s[TR_MAX];
+    for (uint32_t j = threadIdx.x; j < n; j += TR_THREADS) s[j] = in[j];
+    __syncthreads();
+    const uint32_t i = blockIdx.x * TR_ELEMS + threadIdx.x / TR_PER, part = threadIdx.x % TR_PER;
+    const unsigned long long key = i < n ? s[i] : 0ull;
+    uint32_t cnt = 0;
+    if (i < n)
+        for (uint32_t j = part; j < n; j += TR_PER) {
+            const unsigned long long v = s[j];
+            cnt += (v < key || (v == key && j < i)) ? 1u : 0u;
+        }
+    cnt += __shfl_xor_sync(0xffffffffu, cnt, 1);
+    cnt += __shfl_xor_sync(0xffffffffu, cnt, 2);
+    if (i < n && part == 0) {
+        if (out_sorted) out_sorted[cnt] = key;
+        if (out_rank && i < *n_valid) out_rank[i] = cnt;
+    }
+}
 __global__ void k_count_per_pattern(const unsigned long long* __restrict__ keys, const Counters* ctr, DevPlan P, unsigned long long* __restrict__ counts,
                                     uint32_t core_lo, uint32_t halo_after) {
     const uint32_t n = ctr->n_unique;

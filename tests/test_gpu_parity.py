@@ -4,6 +4,7 @@ order identical, scores <= 1e-9 relative (they are in fact compared for bit equa
 ranking identical."""
 import os
 import random
+import sys
 
 import numpy as np
 import pytest
@@ -89,6 +90,22 @@ def test_long_tail_of_empty_lines_is_trimmed(parser, oracle):
     batch = parser.analyze_batch(logs)
     for k, one in enumerate(logs):
         _check(batch, oracle.analyze(ScoringConfig(), pats, one), log_index=k)
+
+
+def test_scan_seams_against_oracle(oracle):
+    """Fixed-seed slice of scripts/fuzz_split_scan.py: texts whose lengths, literals, "\\r\\n" pairs and newline runs sit on
+    the seams of the scan pass (1 KiB spans, 16 KiB tiles, list overflow, lines longer than a tile), alone and in batches."""
+    import importlib.util
+
+    spec = importlib.util.spec_from_file_location("fuzz_split_scan", os.path.join(os.path.dirname(__file__), "..", "scripts", "fuzz_split_scan.py"))
+    fz = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(fz)
+    argv = sys.argv
+    try:
+        sys.argv = ["fuzz_split_scan.py", "1", "13"]
+        assert fz.main() == 0
+    finally:
+        sys.argv = argv
 
 
 def test_all_factors_small(parser, oracle):
