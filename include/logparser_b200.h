@@ -124,8 +124,18 @@ int lp_host_unregister(void* p);
 
 /* ---- lifecycle ------------------------------------------------------------------------- */
 /* Carries the scoring.* values into the library and binds it to one CUDA device
- * (replaces the @ConfigProperty injection of SS:38-51, CAS:24, FTS:27-34). NULL on failure. */
+ * (replaces the @ConfigProperty injection of SS:38-51, CAS:24, FTS:27-34). NULL on failure.
+ * device = -1: all visible devices, see lp_create_multi. */
 lp_ctx* lp_create(const lp_scoring_cfg* cfg, int device);
+/* One process driving several GPUs (the reference is ONE JVM): `lp_create(cfg, -1)` takes every visible device,
+ * lp_create_multi the listed ones (a device may be listed more than once). lp_load_patterns then loads every device,
+ * and lp_analyze_batch cuts a batch of two or more logs into contiguous blocks of logs, one per device, balanced by
+ * bytes: each block is copied and scanned on a host thread of its own, the per-pattern event counts of the blocks meet
+ * on the host (P x 8 bytes per device; FTS:41-93 is the only cross-request state), each block is scored with the
+ * counts of the blocks in front of it, and ONE result comes back in batch order: the same events, scores, per-log
+ * ranks and counts as on one device (LP_OPT_LINE_OFFSETS is not available there). Every other call runs on the first
+ * device. One process per GPU with lp_comm_init + lp_analyze_batch_dist is the other way to use several GPUs. */
+lp_ctx* lp_create_multi(const lp_scoring_cfg* cfg, const int* devices, size_t n_devices);
 void lp_destroy(lp_ctx* ctx);
 /* Thread-local message for the last failing call on this thread. */
 const char* lp_last_error(void);

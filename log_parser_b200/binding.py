@@ -88,7 +88,7 @@ EXPORTS = [
     "lp_result_free", "lp_get_timings", "lp_stream", "lp_split_lines_noalloc",
     "lp_counts_by_id", "lp_batch_scan_device_async", "lp_batch_score_gathered", "lp_comm_unique_id", "lp_comm_init",
     "lp_analyze_batch_dist_device", "lp_analyze_batch_dist", "lp_host_alloc", "lp_host_free", "lp_host_register",
-    "lp_host_unregister", "lp_range_halo_lines", "lp_range_summary_words", "lp_range_scan_device", "lp_range_score", "lp_analyze_range_dist_device", "lp_analyze_range_dist",
+    "lp_host_unregister", "lp_range_halo_lines", "lp_range_summary_words", "lp_range_scan_device", "lp_range_score", "lp_analyze_range_dist_device", "lp_analyze_range_dist", "lp_create_multi",
 ]
 
 _lib = None
@@ -106,6 +106,8 @@ def load_library() -> C.CDLL:
     vp, u8p, u64p = C.c_void_p, C.c_void_p, C.POINTER(C.c_uint64)
     L.lp_create.restype = vp
     L.lp_create.argtypes = [C.POINTER(ScoringCfg), C.c_int]
+    L.lp_create_multi.restype = vp
+    L.lp_create_multi.argtypes = [C.POINTER(ScoringCfg), C.POINTER(C.c_int), C.c_size_t]
     L.lp_destroy.argtypes = [vp]
     L.lp_last_error.restype = C.c_char_p
     L.lp_version.restype = C.c_char_p
@@ -247,7 +249,10 @@ def _view(ptr, n, dtype, owner):
 class LogParser:
     """One lp_ctx: scoring.* configuration + loaded pattern set bound to one CUDA device."""
 
-    def __init__(self, cfg: Optional[ScoringConfig] = None, device: int = 0, decay_lut: Optional[np.ndarray] = None):
+    def __init__(self, cfg: Optional[ScoringConfig] = None, device: int = 0, decay_lut: Optional[np.ndarray] = None,
+                 devices: Optional[Sequence[int]] = None):
+        """device = -1: every visible device; devices = [...]: lp_create_multi (one process driving several GPUs:
+        analyze_batch cuts a batch into one block of logs per device)."""
         self.L = load_library()
         cfg = cfg or ScoringConfig()
         self.cfg = cfg
@@ -259,7 +264,11 @@ class LogParser:
         sc = ScoringCfg(cfg.decay_constant, cfg.max_window, cfg.time_window_hours, cfg.early_bonus_threshold,
                         cfg.max_early_bonus, cfg.penalty_threshold, cfg.max_context_factor, cfg.frequency_threshold,
                         cfg.max_penalty, lut_p)
-        self.h = self.L.lp_create(C.byref(sc), device)
+        if devices is not None:
+            arr = (C.c_int * len(devices))(*[int(d) for d in devices])
+            self.h = self.L.lp_create_multi(C.byref(sc), arr, len(devices))
+        else:
+            self.h = self.L.lp_create(C.byref(sc), device)
         if not self.h:
             raise LpError(LP_ERR_CUDA, _last_error())
         self.n_patterns = 0

@@ -14,6 +14,7 @@
 #include <limits>
 #include <memory>
 #include <mutex>
+#include <thread>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -130,6 +131,7 @@ struct lp_result {
     uint64_t n_patterns = 0;
     std::vector<uint64_t> log_n_lines, log_event_begin;
     std::vector<uint32_t> line_start, line_end, zero_rank;
+    std::vector<unsigned long long> own;      // a result put together from several devices keeps its columns here
     uint64_t n_logs = 0, n_events = 0, total_lines = 0, budget_exceeded = 0;
     bool has_factors = false, has_offsets = false;
     ~lp_result() { if (hold.p) { if (pool) pool->give_back(hold); else hold.release(); } }
@@ -214,6 +216,9 @@ struct lp_ctx {
     // several threads overlap on the GPU (one's host->device copy under another's kernels). The two-phase, collective and
     // line-range calls keep state between calls and stay on the context itself.
     std::vector<lp_ctx*> extra;
+    // a multi-device context (lp_create(cfg, -1) / lp_create_multi): the contexts of the other devices; lp_analyze_batch
+    // cuts a batch into one block of logs per device
+    std::vector<lp_ctx*> shards;
     lp_ctx* owner = nullptr;                    // the context this worker belongs to (itself for the context)
     std::atomic<uint32_t> next_worker{0};
     std::atomic<lp_ctx*> last_used{nullptr};
@@ -1170,6 +1175,13 @@ static lp_ctx* create_worker(const lp_scoring_cfg* cfg, int device) {
 }
 
 lp_ctx* lp_create(const lp_scoring_cfg* cfg, int device) {
+    if (device == -1) {     // every visible device
+        int n = 0;
+        if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0) { g_last_error = "no CUDA device visible"; return nullptr; }
+        std::vector<int> all(n);
+        for (int i = 0; i < n; ++i) all[i] = i;
+        return lp_create_multi(cfg, all.data(), all.size());
+    }
     lp_ctx* c = nullptr;
     int rc = guarded(nullptr, [&] {
         if (!cfg) throw std::invalid_argument("cfg is NULL");
@@ -1200,9 +1212,23 @@ lp_ctx* lp_create(const lp_scoring_cfg* cfg, int device) {
     return rc == LP_OK ? c : nullptr;
 }
 
+lp_ctx* lp_create_multi(const lp_scoring_cfg* cfg, const int* devices, size_t n_devices) {
+    if (!devices || n_devices == 0) { g_last_error = "no devices given"; return nullptr; }
+    lp_ctx* c = lp_create(cfg, devices[0]);
+    if (!c) return nullptr;
+    for (size_t i = 1; i < n_devices; ++i) {
+        lp_ctx* d = devices[i] >= 0 ? lp_create(cfg, devices[i]) : nullptr;
+        if (!d) { if (devices[i] < 0) g_last_error = "device index out of range"; lp_destroy(c); return nullptr; }
+        c->shards.push_back(d);
+    }
+    return c;
+}
+
 static void nccl_comm_destroy(void* comm);
 void lp_destroy(lp_ctx* c) {
     if (!c) return;
+    for (lp_ctx* d : c->shards) lp_destroy(d);
+    c->shards.clear();
     for (lp_ctx* e : c->extra) lp_destroy(e);
     c->extra.clear();
     cudaSetDevice(c->device);
@@ -1229,6 +1255,10 @@ void lp_destroy(lp_ctx* c) {
 int lp_load_patterns(lp_ctx* c, const lp_pattern_desc* pats, size_t n, int64_t* bad_pattern) {
     if (bad_pattern) *bad_pattern = -1;
     if (!c) { g_last_error = "ctx is NULL"; return LP_ERR_INVALID; }
+    for (lp_ctx* d : c->shards) {       // a multi-device context: the other devices first (a failure leaves the message of the first one)
+        const int rc = lp_load_patterns(d, pats, n, bad_pattern);
+        if (rc != LP_OK) return rc;
+    }
     return guarded(c, [&] {
         if (n && !pats) throw std::invalid_argument("patterns is NULL");
         std::lock_guard<std::mutex> lk(c->mu);
@@ -1696,9 +1726,126 @@ int lp_analyze_batch_device(lp_ctx* c, const uint8_t* d_logs, const uint64_t* of
         *out = run_all(wl.w, [&] { return d_logs; }, offsets[n_logs], offsets, (uint32_t)n_logs, prior_count, options);
     });
 }
+// ---- one process, several GPUs (the reference is ONE JVM; lp_create(cfg, -1) / lp_create_multi)
+// A batch is cut into contiguous blocks of logs, one per device, balanced by bytes. Every block is copied to its device
+// and scanned on a host thread of its own; the per-pattern event counts of the blocks meet on the host (P x 8 bytes per
+// device: the only exchange, FTS:41-93 is the only cross-request state), every block is scored with the counts of the
+// blocks in front of it as its prior, and the results are put together in batch order. Same events, scores, per-log
+// ranks and counts as lp_analyze_batch on one device.
+namespace {
+lp_result* merge_results(std::vector<std::unique_ptr<lp_result>>& parts, uint32_t np) {
+    std::unique_ptr<lp_result> R(new lp_result());
+    uint64_t M = 0;
+    bool factors = true, spans = true;
+    for (auto& p : parts) { M += p->n_events; factors = factors && p->has_factors; spans = spans && p->span_start && p->span_end; }
+    const size_t w_u32 = (size_t)(M + 1) / 2 + 1;       // 8-byte words holding M uint32
+    size_t words = 3 * w_u32 + M + (factors ? 7 * M : 0) + (spans ? 2 * w_u32 : 0) + np + 1;
+    R->own.assign(words, 0ull);
+    unsigned long long* at = R->own.data();
+    uint32_t* line = reinterpret_cast<uint32_t*>(at); at += w_u32;
+    uint32_t* pat = reinterpret_cast<uint32_t*>(at); at += w_u32;
+    uint32_t* rank = reinterpret_cast<uint32_t*>(at); at += w_u32;
+    double* score = reinterpret_cast<double*>(at); at += M;
+    double* fac = nullptr;
+    if (factors) { fac = reinterpret_cast<double*>(at); at += 7 * M; }
+    uint32_t *ss = nullptr, *se = nullptr;
+    if (spans) { ss = reinterpret_cast<uint32_t*>(at); at += w_u32; se = reinterpret_cast<uint32_t*>(at); at += w_u32; }
+    uint64_t* delta = reinterpret_cast<uint64_t*>(at);
+    uint64_t e0 = 0;
+    R->log_event_begin.push_back(0);
+    for (auto& p : parts) {
+        const uint64_t m = p->n_events;
+        if (m) {
+            memcpy(line + e0, p->line, m * 4); memcpy(pat + e0, p->pattern, m * 4); memcpy(rank + e0, p->rank, m * 4);
+            memcpy(score + e0, p->score, m * 8);
+            if (fac) memcpy(fac + 7 * e0, p->factors, m * 56);
+            if (ss) { memcpy(ss + e0, p->span_start, m * 4); memcpy(se + e0, p->span_end, m * 4); }
+        }
+        for (uint32_t q = 0; q < np; ++q) delta[q] += p->freq_delta[q];
+        for (uint64_t k = 0; k < p->n_logs; ++k) {
+            R->log_n_lines.push_back(p->log_n_lines[k]);
+            R->log_event_begin.push_back(e0 + p->log_event_begin[k + 1]);
+        }
+        e0 += m;
+        R->n_logs += p->n_logs; R->total_lines += p->total_lines; R->budget_exceeded += p->budget_exceeded;
+    }
+    R->n_events = M; R->n_patterns = np;
+    R->line = line; R->pattern = pat; R->rank = rank; R->score = score; R->freq_delta = delta;
+    R->has_factors = factors; R->factors = fac; R->span_start = ss; R->span_end = se;
+    return R.release();
+}
+
+void analyze_batch_multi(lp_ctx* c, const uint8_t* logs, const uint64_t* offsets, size_t n_logs, const uint64_t* prior_count, int options,
+                         lp_result** out) {
+    if (options & LP_OPT_LINE_OFFSETS) throw std::invalid_argument("LP_OPT_LINE_OFFSETS is not available for a batch cut over several devices");
+    if (!c->loaded) throw std::invalid_argument("lp_load_patterns has not been called");
+    std::vector<lp_ctx*> devs{c};
+    devs.insert(devs.end(), c->shards.begin(), c->shards.end());
+    const size_t S = std::min(devs.size(), n_logs);
+    const uint64_t total = offsets[n_logs];
+    if (total && !logs) throw std::invalid_argument("logs is NULL");
+    std::vector<size_t> cut(S + 1, 0);        // block s = logs [cut[s], cut[s+1]): contiguous, at least one log each, balanced by bytes
+    cut[S] = n_logs;
+    for (size_t s = 1; s < S; ++s) {
+        size_t k = std::max(cut[s - 1] + 1, (size_t)(std::lower_bound(offsets, offsets + n_logs + 1, total / S * s) - offsets));
+        cut[s] = std::min(k, n_logs - (S - s));
+    }
+    const uint32_t np = c->dp.n_pat;
+    std::vector<std::unique_lock<std::mutex>> locks;      // held across both phases: a scan is pending on every device in between
+    for (size_t s = 0; s < S; ++s) locks.emplace_back(devs[s]->mu);
+    std::vector<std::vector<uint64_t>> counts(S, std::vector<uint64_t>(std::max<uint32_t>(np, 1), 0)), off(S);
+    std::vector<std::exception_ptr> err(S);
+    auto run_phase = [&](const std::function<void(size_t)>& body) {
+        std::vector<std::thread> th;
+        for (size_t s = 0; s < S; ++s)
+            th.emplace_back([&, s] {
+                try { CK(cudaSetDevice(devs[s]->device)); body(s); } catch (...) { err[s] = std::current_exception(); }
+            });
+        for (auto& t : th) t.join();
+        for (size_t s = 0; s < S; ++s) if (err[s]) std::rethrow_exception(err[s]);
+    };
+    run_phase([&](size_t s) {
+        lp_ctx* d = devs[s];
+        const uint64_t b0 = offsets[cut[s]], len = offsets[cut[s + 1]] - b0;
+        const uint32_t n = (uint32_t)(cut[s + 1] - cut[s]);
+        off[s].resize(n + 1);
+        for (uint32_t k = 0; k <= n; ++k) off[s][k] = offsets[cut[s] + k] - b0;
+        const uint8_t* dptr = stage_host_log(d, logs + b0, len);
+        struct DropHostSrc { lp_ctx* c; ~DropHostSrc() { c->host_src = nullptr; } } drop{d};
+        for (;;) {
+            try {
+                run_scan(d, dptr, len, off[s].data(), n, options);
+                per_pattern_counts(d, counts[s].data());
+                break;
+            } catch (const Retry&) { continue; }
+        }
+    });
+    std::vector<std::vector<uint64_t>> prior(S, std::vector<uint64_t>(std::max<uint32_t>(np, 1), 0));
+    std::vector<uint64_t> run(std::max<uint32_t>(np, 1), 0), by_id(std::max<uint32_t>(np, 1), 0);
+    for (uint32_t p = 0; p < np; ++p) run[p] = prior_count ? prior_count[p] : 0;
+    for (size_t s = 0; s < S; ++s) {
+        prior[s] = run;
+        lp_counts_by_id(c, counts[s].data(), by_id.data());       // counts are kept per pattern id (FTS:46-50)
+        for (uint32_t p = 0; p < np; ++p) run[p] += by_id[p];
+    }
+    std::vector<std::unique_ptr<lp_result>> parts(S);
+    run_phase([&](size_t s) {
+        try {
+            parts[s].reset(run_score(devs[s], prior[s].data()));
+        } catch (const Retry&) {
+            throw LimitFail("internal: estimates validated by the scan phase were exceeded in the score phase");
+        }
+    });
+    *out = merge_results(parts, np);
+    CK(cudaSetDevice(c->device));
+}
+}  // namespace
+
 int lp_analyze_batch(lp_ctx* c, const uint8_t* logs, const uint64_t* offsets, size_t n_logs, const uint64_t* prior_count, int options,
                      lp_result** out) {
     if (!c || !out) { g_last_error = "NULL argument"; return LP_ERR_INVALID; }
+    if (!c->shards.empty() && offsets && n_logs >= 2)
+        return guarded(c, [&] { analyze_batch_multi(c, logs, offsets, n_logs, prior_count, options, out); });
     return guarded(c, [&] {
         if (!offsets) throw std::invalid_argument("offsets is NULL");
         WorkerLock wl = pick_worker(c);

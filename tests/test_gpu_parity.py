@@ -839,6 +839,47 @@ def test_line_range_dist_single_rank_equals_whole_log(parser):
         lp.close()
 
 
+@pytest.mark.parametrize("layout", ["same-device", "all-devices"])
+def test_one_process_several_devices_equals_one_device(parser, layout):
+    """lp_create_multi / lp_create(cfg, -1): ONE process, a batch cut into one block of logs per device context, counts
+    exchanged on the host, one result in batch order; must equal lp_analyze_batch on a single device, repeatedly (the
+    estimates of every device settle) and with fewer logs than devices. "same-device" lists device 0 three times, so the
+    cut, the exchange and the merge run on a one-GPU box; "all-devices" takes what the box has."""
+    import torch
+
+    wl = synth.make_patterns(40, 4243, noliteral=1)
+    logs = [synth.make_log(wl, n, 800 + i, pool_blocks=400, hit_rate=0.06) for i, n in enumerate([700, 40, 1300, 5, 400, 900, 60])]
+    prior = (np.arange(len(wl.patterns)) % 9).astype(np.uint64)
+    parser.load_patterns(wl.patterns)
+    whole = parser.analyze_batch(logs, prior_count=prior, options=binding.OPT_FACTORS)
+    if layout == "same-device":
+        lp = binding.LogParser(ScoringConfig(), devices=[0, 0, 0])
+    else:
+        if torch.cuda.device_count() < 2:
+            pytest.skip("needs two GPUs")
+        lp = binding.LogParser(ScoringConfig(), device=-1)
+    try:
+        lp.load_patterns(wl.patterns)
+        for _ in range(3):
+            r = lp.analyze_batch(logs, prior_count=prior, options=binding.OPT_FACTORS)
+            np.testing.assert_array_equal(r.log_n_lines, whole.log_n_lines)
+            np.testing.assert_array_equal(r.log_event_begin, whole.log_event_begin)
+            np.testing.assert_array_equal(r.line, whole.line)
+            np.testing.assert_array_equal(r.pattern, whole.pattern)
+            np.testing.assert_array_equal(r.score, whole.score)
+            np.testing.assert_array_equal(r.factors, whole.factors)
+            np.testing.assert_array_equal(r.rank, whole.rank)
+            np.testing.assert_array_equal(r.freq_delta, whole.freq_delta)
+        two = lp.analyze_batch(logs[:2], prior_count=prior)           # fewer logs than devices
+        ref2 = parser.analyze_batch(logs[:2], prior_count=prior)
+        np.testing.assert_array_equal(two.line, ref2.line)
+        np.testing.assert_array_equal(two.score, ref2.score)
+        one = lp.analyze(logs[2], prior_count=prior)                   # a single log runs on the first device
+        np.testing.assert_array_equal(one.score, parser.analyze(logs[2], prior_count=prior).score)
+    finally:
+        lp.close()
+
+
 def test_library_nccl_single_rank_equals_batch(parser):
     """lp_analyze_batch_dist_device with a communicator of one rank: the exchange path (count after the
     unique pass, all-gather and prefix on the second stream, k_score waiting for it, the repeat loop on

@@ -36,6 +36,20 @@ def test_debug_hooks_are_not_in_the_product_library(lib):
     assert hasattr(binding.load_debug_library(), "lp_debug_rx_compile")
 
 
+def test_build_reuse_is_decided_by_content_not_by_file_times():
+    """build.stale(): the prebuilt library is reused exactly when the hash stored beside it equals the hash of the sources,
+    headers and compiler flags (a copy of the tree on a GPU box has meaningless file times)."""
+    from log_parser_b200 import build
+
+    build.build()
+    assert not build.stale()
+    assert build.source_hash() == open(build.SO + ".srchash").read().strip()
+    assert build.source_hash(flags=build.NVCC_FLAGS + ["-DX"]) != build.source_hash()
+    assert build.source_hash(sources=build.SOURCES[:-1]) != build.source_hash()
+    os.utime(os.path.join(build.CSRC, "engine.cu"))          # touching a source does not make the library stale
+    assert not build.stale()
+
+
 def test_version_and_error_string(lib):
     assert b"sm_100a" in lib.lp_version()
     assert isinstance(lib.lp_last_error(), bytes)
