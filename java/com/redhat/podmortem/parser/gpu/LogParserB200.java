@@ -111,6 +111,10 @@ public final class LogParserB200 implements AutoCloseable {
     });
     private int nPatterns = 0;
 
+    /**
+     * @param device CUDA device index, or -1 for every visible device: one context then owns a device context per GPU
+     *               and lp_analyze_batch cuts a batch of requests into one block per GPU (single requests run on the first).
+     */
     public LogParserB200(ScoringProps p, int device) {
         try (Arena a = Arena.ofConfined()) {
             MemorySegment cfg = a.allocate(CFG);
