@@ -845,8 +845,6 @@ def test_one_process_several_devices_equals_one_device(parser, layout):
     exchanged on the host, one result in batch order; must equal lp_analyze_batch on a single device, repeatedly (the
     estimates of every device settle) and with fewer logs than devices. "same-device" lists device 0 three times, so the
     cut, the exchange and the merge run on a one-GPU box; "all-devices" takes what the box has."""
-    import torch
-
     wl = synth.make_patterns(40, 4243, noliteral=1)
     logs = [synth.make_log(wl, n, 800 + i, pool_blocks=400, hit_rate=0.06) for i, n in enumerate([700, 40, 1300, 5, 400, 900, 60])]
     prior = (np.arange(len(wl.patterns)) % 9).astype(np.uint64)
@@ -855,9 +853,7 @@ def test_one_process_several_devices_equals_one_device(parser, layout):
     if layout == "same-device":
         lp = binding.LogParser(ScoringConfig(), devices=[0, 0, 0])
     else:
-        if torch.cuda.device_count() < 2:
-            pytest.skip("needs two GPUs")
-        lp = binding.LogParser(ScoringConfig(), device=-1)
+        lp = binding.LogParser(ScoringConfig(), device=-1)       # on a one-GPU box: one device context, the plain path
     try:
         lp.load_patterns(wl.patterns)
         for _ in range(3):
