@@ -612,6 +612,8 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
         c->fs_lists.ensure((size_t)n_tiles * 16 * 2 + (size_t)n_tiles * 16 * fs::WLIST * 2);
         fz.text = d_text; fz.len = len; fz.n_tiles = n_tiles;
         fz.warp_counts = c->fs_lists.as<uint16_t>();
+        fz.tile_counts = c->tile_counts.as<uint32_t>();
+        CK(cudaMemsetAsync(c->tile_counts.p, 0, (size_t)n_tiles * 4, st));
         fz.nl_lists = c->fs_lists.as<uint16_t>() + (size_t)n_tiles * 16;
         fz.mul = c->f_mul;
         { const uint32_t kk[8] = {1u, 1024u, 128u, 1u << 25, 1u << 26, 1u << 27, 1u << 28, 1u << 15}; for (int q = 0; q < 8; ++q) fz.k[q] = kk[q]; }
@@ -676,7 +678,7 @@ void run_scan(lp_ctx* c, const uint8_t* d_text, uint64_t len, const uint64_t* h_
     CK(cudaMemsetAsync(c->recs.p, 0xFF, rec_cap * 8, st));            // padding sentinels sort last
     CK(cudaMemsetAsync(c->ev_key_alt.p, 0xFF, ev_cap * 8, st));
     if (!c->plan.ctx_any_in_groups || fused) CK(cudaMemsetAsync(c->ctx_flags.p, 0, (line_cap / 4 + 2) * 4, st));   // else k_dfa_scan (walking every line) writes every byte
-    k_scan_tiles<<<1, 1024, n_tiles <= 16384 ? (size_t)n_tiles * 4 : 0, st>>>(c->tile_counts.as<uint32_t>(), fused ? c->fs_lists.as<uint16_t>() : nullptr, n_tiles, n_logs, ctr);
+    k_scan_tiles<<<1, 1024, n_tiles <= 16384 ? (size_t)n_tiles * 4 : 0, st>>>(c->tile_counts.as<uint32_t>(), nullptr, n_tiles, n_logs, ctr);
     if (fused) {
         ExpandArgs ea{};
         ea.text = d_text; ea.len = len; ea.n_tiles = n_tiles; ea.tile_prefix = c->tile_counts.as<uint32_t>(); ea.warp_counts = c->fs_lists.as<uint16_t>(); ea.nl_lists = c->fs_lists.as<uint16_t>() + (size_t)n_tiles * 16;

@@ -72,6 +72,7 @@ struct FscanArgs {
     uint64_t len;
     uint32_t n_tiles;                 // tiles of the whole text (the last one covers position `len`)
     uint32_t tile_begin, tile_end;    // this launch's tiles (a log arriving from the host is scanned piece by piece)
+    uint32_t* tile_counts;            // [n_tiles] out, zeroed before the first launch: newlines per tile, summed from the spans by reduction atomics
     uint16_t* warp_counts;            // [n_tiles][16] out: newlines per 1 KiB warp span; above fs::WLIST the span's list was not written
     uint16_t* nl_lists;               // [n_tiles][16][fs::WLIST] out: the newlines of each warp span, see k_expand
     const uint32_t* bit_table;        // fs::ROWS words (variants 0/1) or the 64 KiB byte table (variant 2)
@@ -332,7 +333,11 @@ __global__ void __launch_bounds__(fs::THREADS, 1) k_fscan(FscanArgs a) {
             }
             if (lane == 0) {
                 a.warp_counts[span] = (uint16_t)t0;
-                if (two) a.warp_counts[span + W] = (uint16_t)t1;
+                if (t0) atomicAdd(&a.tile_counts[span / fs::SPANS], t0);
+                if (two) {
+                    a.warp_counts[span + W] = (uint16_t)t1;
+                    if (t1) atomicAdd(&a.tile_counts[(span + W) / fs::SPANS], t1);
+                }
             }
         }
         // ---- phase B, first-stage hits: compacted into the warp's list, then checked by full warps (the hits of a
@@ -389,6 +394,7 @@ struct ExpandArgs {
     Counters* ctr;
 };
 constexpr int EX_THREADS = 256;
+constexpr int EX_SCAN_STAGE = 1536;      // a tile holds at most 16 x 64 listed newlines; the rest is room for the first lines of logs
 // Appends line g to the list of lines the always-on scan walks, one global atomic per warp. Called by every lane that is
 // active at the call site (`want` false: nothing to add). A warp of k_dfa_scan that takes 32 consecutive lines nearly
 // always holds a stack frame or two, so skipping inside it saved memory traffic but no time; with the list only the
@@ -407,7 +413,14 @@ __global__ void __launch_bounds__(EX_THREADS) k_expand(ExpandArgs a) {
     __shared__ uint32_t s_warp[EX_THREADS / 32];
     __shared__ uint32_t s_pre[17];      // exclusive prefix of the 16 span counts; [16] = the tile's total
     __shared__ uint32_t s_dense;
+    __shared__ uint32_t s_scan[EX_SCAN_STAGE], s_nscan, s_scan_base;      // the tile's lines for the always-on scan, published with one atomic
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) s_nscan = 0;
+    auto stage_scan = [&](uint32_t g) {
+        const uint32_t at = atomicAdd(&s_nscan, 1u);
+        if (at < EX_SCAN_STAGE) s_scan[at] = g;
+        else a.scan_list[atomicAdd(&a.ctr->n_scan, 1u)] = g;       // more than the stage holds (a tile of tiny logs): straight to the list
+    };
     for (uint32_t tile = blockIdx.x; tile < a.n_tiles; tile += gridDim.x) {
         const uint64_t base = (uint64_t)tile * fs::TILE, tile_end = base + fs::TILE;
         const uint32_t prefix = a.tile_prefix[tile];
@@ -455,7 +468,7 @@ __global__ void __launch_bounds__(EX_THREADS) k_expand(ExpandArgs a) {
                     a.line_start[g + 1] = (uint32_t)(p + 1);
                     if (a.line_skip) a.line_skip[g + 1] = (uint8_t)((ent >> 14) & 1u);
                 } else atomicOr(&a.ctr->overflow, 64u);
-                if (a.scan_list) ex_append_scan(a, g + 1, g + 1 < a.line_cap && !((ent >> 14) & 1u));
+                if (a.scan_list && g + 1 < a.line_cap && !((ent >> 14) & 1u)) stage_scan(g + 1);
             }
             if (events) {       // start of log j / end of log j-1 inside this tile: newlines before it = spans in front + a binary search in its span
                 uint32_t j = lower_bound_dev<uint64_t>(a.log_off, a.n_logs + 1, base) + threadIdx.x;
@@ -471,8 +484,17 @@ __global__ void __launch_bounds__(EX_THREADS) k_expand(ExpandArgs a) {
                         if (j < a.n_logs) { a.line_start[nlb + j] = (uint32_t)b; if (a.line_skip) a.line_skip[nlb + j] = 0; }   // first line of a log: always walked
                         if (j > 0) a.line_end[nlb + j - 1] = (uint32_t)b;
                     } else atomicOr(&a.ctr->overflow, 64u);
-                    if (a.scan_list) ex_append_scan(a, nlb + j, nlb + j < a.line_cap && j < a.n_logs);
+                    if (a.scan_list && nlb + j < a.line_cap && j < a.n_logs) stage_scan(nlb + j);
                 }
+            }
+            if (a.scan_list) {
+                __syncthreads();
+                const uint32_t staged = min(s_nscan, (uint32_t)EX_SCAN_STAGE);
+                if (threadIdx.x == 0 && staged) s_scan_base = atomicAdd(&a.ctr->n_scan, staged);
+                __syncthreads();
+                for (uint32_t q = threadIdx.x; q < staged; q += EX_THREADS) a.scan_list[s_scan_base + q] = s_scan[q];
+                __syncthreads();
+                if (threadIdx.x == 0) s_nscan = 0;
             }
             continue;
         }
