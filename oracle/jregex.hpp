@@ -10,7 +10,13 @@
 // vectors for this path). This engine is pinned instead by
 //   * the hand-derived vectors of SURVEY.md §8c (tests/test_oracle_golden.py),
 //   * differential tests against CPython `re` and the `regex` module on the shared
-//     syntax subset (tests/test_oracle_regex_diff.py).
+//     syntax subset (tests/test_oracle_regex_diff.py),
+//   * differential tests against PCRE2 10.42 where its dialect agrees with Java's, with the known
+//     dialect differences held as fixtures (tests/test_oracle_pcre2_diff.py, tests/golden/).
+// Known difference from the JDK, in this restatement and in the library alike: Pattern.Bound also
+// counts a non-spacing mark (category Mn) that follows a letter or digit as a word character
+// (Bound.check / hasBaseCharacter); here `\b` and `\B` look at the ASCII word class only, so a
+// line with a combining mark right at a `\b` position can be decided differently.
 //
 // Design: a leftmost, ordered-alternation backtracking matcher over Unicode code points
 // (the same observable behaviour as Matcher.find() on well-formed UTF-16), written as a
@@ -29,7 +35,7 @@ struct SyntaxError : std::runtime_error {
     int index;
     SyntaxError(const std::string& m, int idx) : std::runtime_error(m), index(idx) {}
 };
-// Valid Java syntax that this restatement does not model (\X, \G, \p{L}, (?u), (?U) ...).
+// Valid Java syntax that this restatement does not model (\X, \b{g}, \N{..}, \b under (?U), back-references under (?iu), CANON_EQ).
 struct Unsupported : std::runtime_error {
     int index;
     Unsupported(const std::string& m, int idx) : std::runtime_error(m), index(idx) {}
@@ -41,8 +47,8 @@ enum Flag : int {
     F_COMMENTS = 0x04,          // (?x)
     F_MULTILINE = 0x08,         // (?m)
     F_DOTALL = 0x20,            // (?s)
-    F_UNICODE_CASE = 0x40,      // (?u)   unsupported
-    F_UNICODE_CLASS = 0x100,    // (?U)   unsupported
+    F_UNICODE_CASE = 0x40,      // (?u)   simple case folding toLowerCase(toUpperCase(c))
+    F_UNICODE_CLASS = 0x100,    // (?U)   Unicode \w \d \s and POSIX classes; implies (?u)
 };
 
 struct Range {
