@@ -149,7 +149,9 @@ int lp_load_patterns(lp_ctx* ctx, const lp_pattern_desc* patterns, size_t n_patt
 
 /* ---- the hot path ------------------------------------------------------------------------ */
 /* Replaces AS:53-113 for one request: split, scan, score. `log` is host memory (UTF-8 of
- * PodFailureData.logs). prior_count[p] = matches of pattern p already inside the sliding
+ * PodFailureData.logs, i.e. what String.getBytes(UTF_8) produces: well-formed. The reference matches on the decoded
+ * String, where malformed input bytes have already become U+FFFD; here a malformed sequence matches no character
+ * class, so a caller holding raw bytes replaces malformed sequences by EF BF BD first). prior_count[p] = matches of pattern p already inside the sliding
  * frequency window at request start (FTS state stays on the JVM); NULL = all zero.
  * FrequencyTrackingService keys its counts by pattern id (FTS:46-50): patterns that carry the same id
  * share one count. Pass the id's count in the entry of every pattern with that id (the library reads

@@ -190,6 +190,26 @@ public:
         return set_node(std::move(s));
     }
     AstP assertion(AssertKind k) { AstP a = node(AstKind::Assert); a->assert_kind = k; return a; }
+    // (?U)\b / (?U)\B: Pattern.Bound with UNICODE_CHARACTER_CLASS asks CharPredicates.WORD() of the code points on both
+    // sides (a non-spacing mark is a word character there whatever precedes it). The automata keep one "previous byte
+    // is an ASCII word byte" bit, so this form goes to the backtracking engine, written with what it already has:
+    //   \b = (?<=\w)(?!\w) | (?<!\w)(?=\w)      \B = (?<=\w)(?=\w) | (?<!\w)(?!\w)
+    AstP unicode_word_boundary(bool negated) {
+        regular = false;
+        auto side = [&](bool behind, bool neg) {
+            AstP l = node(AstKind::Look); l->behind = behind; l->neg = neg;
+            l->kids.push_back(set_node(uni_get(UNI_PROP, "WORD")));
+            return l;
+        };
+        AstP alt = node(AstKind::Alt);
+        for (int after_word = 1; after_word >= 0; --after_word) {
+            AstP cat = node(AstKind::Cat);
+            cat->kids.push_back(side(true, !after_word));
+            cat->kids.push_back(side(false, negated ? !after_word : (bool)after_word));
+            alt->kids.push_back(std::move(cat));
+        }
+        return alt;
+    }
 
     // -------- expression / sequence
     AstP expr() {
@@ -533,10 +553,10 @@ public:
             case 'P': return set_node(posix(true));
             case 'b':
                 if (raw() == '{') nope("\\b{g}");
-                if (on(RXF_UNICODE_CLASS)) nope("(?U) with \\b (Unicode word boundaries)");
+                if (on(RXF_UNICODE_CLASS)) return unicode_word_boundary(false);
                 return assertion(AssertKind::WordB);
             case 'B':
-                if (on(RXF_UNICODE_CLASS)) nope("(?U) with \\B (Unicode word boundaries)");
+                if (on(RXF_UNICODE_CLASS)) return unicode_word_boundary(true);
                 return assertion(AssertKind::NotWordB);
             case 'A': return assertion(AssertKind::Begin);
             case 'z': return assertion(AssertKind::End);

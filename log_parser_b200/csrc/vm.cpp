@@ -190,8 +190,11 @@ FirstSet first_set(const Ast& a) {
             for (const auto& x : a.set) {
                 const uint32_t hi = std::min<uint32_t>(x.hi, 0x10FFFF);
                 if (x.lo > hi) continue;
-                // lead bytes are monotonic in the code point: every lead byte between the two ends can occur
-                for (uint32_t b = lead_byte(x.lo); b <= lead_byte(hi); ++b) fs_add(r, b);
+                // lead bytes are monotonic in the code point: every lead byte between the two ends can occur. 0x80..0xC1
+                // lie between the ASCII and the multi-byte lead bytes and are none: with them in the set, the search for
+                // the next start position would stop inside a character whose own lead byte no match begins with.
+                for (uint32_t b = lead_byte(x.lo); b <= lead_byte(hi); ++b)
+                    if (b < 0x80 || b >= 0xC2) fs_add(r, b);
             }
             return r;
         case AstKind::Group: case AstKind::Atomic: return first_set(*a.kids[0]);

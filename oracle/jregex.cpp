@@ -212,6 +212,13 @@ struct Parser {
     }
 
     NodeP mk(Kind k) { NodeP n(new Node()); n->kind = k; return n; }
+    // Pattern.Bound: isWord() is the ASCII word class, or CharPredicates.WORD() under UNICODE_CHARACTER_CLASS (the node
+    // then carries that set; a non-spacing mark belongs to it, whatever precedes the mark).
+    NodeP bound(Kind k) {
+        NodeP n = mk(k);
+        if (has(F_UNICODE_CLASS)) { n->flags = F_UNICODE_CLASS; n->set = table_get(UNI_PROP, "WORD"); n->set.normalize(); }
+        return n;
+    }
 
     NodeP parse_alt() {
         std::vector<NodeP> alts;
@@ -593,12 +600,10 @@ struct Parser {
             case 'P': return setnode(property(true));
             case 'b': {
                 if (raw_peek() == '{') unsup("\\b{g}");
-                if (has(F_UNICODE_CLASS)) unsup("\\b under (?U) (Unicode word boundaries are not modelled)");
-                return mk(N_WORDB);
+                return bound(N_WORDB);
             }
             case 'B':
-                if (has(F_UNICODE_CLASS)) unsup("\\B under (?U) (Unicode word boundaries are not modelled)");
-                return mk(N_NWORDB);
+                return bound(N_NWORDB);
             case 'A': return mk(N_BEGIN);
             case 'z': return mk(N_END);
             case 'Z': { NodeP n = mk(N_EOL); n->flags = flags & F_UNIX_LINES; return n; }
@@ -883,8 +888,9 @@ bool m(const Node* nd, int i, Ctx& cx, FR k) {
             return k(i);
         }
         case N_WORDB: case N_NWORDB: {
-            bool l = i > 0 && is_word(cx.t[i - 1]);
-            bool r = i < cx.n && is_word(cx.t[i]);
+            const bool uni = (nd->flags & F_UNICODE_CLASS) != 0;
+            bool l = i > 0 && (uni ? nd->set.has(cx.t[i - 1]) : is_word(cx.t[i - 1]));
+            bool r = i < cx.n && (uni ? nd->set.has(cx.t[i]) : is_word(cx.t[i]));
             bool b = l != r;
             return (nd->kind == N_WORDB ? b : !b) && k(i);
         }

@@ -35,7 +35,7 @@ struct SyntaxError : std::runtime_error {
     int index;
     SyntaxError(const std::string& m, int idx) : std::runtime_error(m), index(idx) {}
 };
-// Valid Java syntax that this restatement does not model (\X, \b{g}, \N{..}, \b under (?U), back-references under (?iu), CANON_EQ).
+// Valid Java syntax that this restatement does not model (\X, \b{g}, \N{..}, back-references under (?iu), CANON_EQ).
 struct Unsupported : std::runtime_error {
     int index;
     Unsupported(const std::string& m, int idx) : std::runtime_error(m), index(idx) {}

@@ -302,10 +302,32 @@ def test_deferred_leading_lookaround_vs_oracle_random(lib, oracle):
     (r"x.{0,40}y", "x" + "a" * 30 + "y"), (r"x.{0,40}y", "x" + "a" * 41 + "y"), (r"(?=.*\[edge1\])lost \d+", "lost 12 [edge1]"),
     (r"(?i)(a)\1", "aA"), (r"(?<=é)x", "éx"), (r"(?<=\bab|c)x", "abx"), (r"^(?:a|ab)*+c", "abac"), (r"(a*)*b", "aaaa"),
     (r"(?:^_??[^x]*){2}a", "  a:.Ec_11E"), (r"(\w+)\s\1$", "hello hello\r"), (r"(?<=\d{2,4})ms", "x1234ms"),
+    # a class that leaves out a whole block of UTF-8 lead bytes: the search for the next start position must not stop on the
+    # continuation byte of a character whose lead byte no match begins with (first_set in vm.cpp)
+    (r"(?!\u0434)\P{L}", "\u0434\u0434"), (r"(?!\u0434)\P{L}", "\u0434\u0434-"), (r"(?=.)[^\u0400-\u04ff]", "\u0436\u0436"), (r"(?>\P{IsCyrillic})x", "\u0436x"),
+    # (?U)\b / \B: CharPredicates.WORD() on both sides, a combining mark is a word character
+    (r"(?U)\b\u00e9", "a\u00e9 \u00e9"), (r"(?U)\b\u00e9", "a\u00e9"), (r"(?U)a\b", "a\u0301"), (r"(?U)a\B", "a\u0301"), (r"(?U)\B\W", "\u0434-"), (r"(?U)\B", ""),
+    (r"(?U)\b\d+\b", "x \u0663\u0664 y"), (r"(?U)\bx\b", "\u0434x\u0434"), (r"\bx\b", "\u0434x\u0434"),
 ])
 def test_backtracking_cases(lib, oracle, pat, text):
     d = binding.DebugRegex(pat)
     assert bool(d.match(text)) == oracle.Regex(pat).find(text)
+
+
+def test_multi_script_text_vs_oracle_random(lib, oracle):
+    """Unicode property classes, negated classes that leave out whole UTF-8 lead-byte blocks, (?U) classes and word
+    boundaries inside look-arounds, atomic groups, possessive repeats and back-references, on texts mixing 1- to 4-byte
+    characters and combining marks; automata and bytecode engine (forced for every other pattern). The generator is
+    scripts/fuzz_host_scripts.py, here with a fixed seed."""
+    import importlib.util
+
+    spec = importlib.util.spec_from_file_location("fuzz_host_scripts", os.path.join(ROOT, "scripts", "fuzz_host_scripts.py"))
+    fz = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(fz)
+    problems = []
+    checked, matched, bad = fz.check(random.Random(7), 600, report=lambda *a: problems.append(a))
+    assert bad == 0, problems[:5]
+    assert checked > 4000 and matched > 800
 
 
 @pytest.mark.parametrize("pat,flags", [
@@ -342,9 +364,9 @@ def test_syntax_errors_surface_like_java(lib):
     for bad in ["a{,2}", "(a", "[a", "*a", "a{3,2}", "\\k<x>", "(?<=a*)b"]:
         with pytest.raises(binding.PatternSyntaxError):
             binding.DebugRegex(bad)
-    for ok in ["\\G", "\\p{L}", "(?u)a", "(?U)\\w", "\\p{IsGreek}"]:        # legal Java the reference serves: accepted since round 2
+    for ok in ["\\G", "\\p{L}", "(?u)a", "(?U)\\w", "\\p{IsGreek}", "(?U)\\bx", "(?U)x\\B"]:        # legal Java the reference serves: accepted since round 2
         binding.DebugRegex(ok)
-    for unsup in ["\\X", "\\b{g}", "(?U)\\bx"]:
+    for unsup in ["\\X", "\\b{g}", "\\N{DIGIT ONE}", "(?iu)(a)\\1"]:
         with pytest.raises(binding.UnsupportedRegexError):
             binding.DebugRegex(unsup)
 

@@ -119,7 +119,7 @@ def test_syntax_errors(oracle, bad):
         oracle.Regex(bad)
 
 
-@pytest.mark.parametrize("pat", ["\\X", "\\b{g}", "\\N{DIGIT ONE}", "(?U)\\bx", "(?U)x\\B", "(?iu)(a)\\1"])
+@pytest.mark.parametrize("pat", ["\\X", "\\b{g}", "\\N{DIGIT ONE}", "(?iu)(a)\\1"])
 def test_declared_unsupported(oracle, pat):
     with pytest.raises(oracle.OracleUnsupported):
         oracle.Regex(pat)
@@ -181,6 +181,45 @@ def test_unicode_flags_cases(oracle, pat, text, exp):
 
     assert oracle.Regex(pat).find(text) == exp
     assert bool(binding.DebugRegex(pat).match(text)) == exp
+
+
+def test_unicode_word_boundary_vs_regex_module(oracle):
+    """(?U)\\b and (?U)\\B (Pattern.Bound with UNICODE_CHARACTER_CLASS: CharPredicates.WORD() on both sides) in three
+    formulations: the oracle asks the predicate at the position, the library lowers the boundary to look-arounds for its
+    backtracking engine (rx_parse.cpp unicode_word_boundary), and the `regex` module runs the look-arounds spelled out
+    with the word class written as a set. Texts carry combining marks, non-Latin letters and digits, joiners."""
+    from log_parser_b200 import binding
+
+    W = "[\\p{Alphabetic}\\p{M}\\p{Nd}\\p{Pc}\\u200c\\u200d]"
+    b_third = "(?:(?<=%s)(?!%s)|(?<!%s)(?=%s))" % (W, W, W, W)
+    nb_third = "(?:(?<=%s)(?=%s)|(?<!%s)(?!%s))" % (W, W, W, W)
+    alpha = "a\u00e9\u0301\u03a9\u0663_ -.x1\u200d\u0434"
+    atoms = ["a", "x", "\u00e9", "\u03a9", "\\w", "\\w+", "\\d+", "\\S*", ".", "[a\u0434]+", "\\W", "_", "1"]
+    rng = random.Random(11)
+    checked = matched = 0
+    for _ in range(700):
+        parts = []
+        for _k in range(rng.randint(1, 4)):
+            parts.append(rng.choice(["\\b", "\\B", "", ""]) + rng.choice(atoms) + rng.choice(["\\b", "\\B", "", ""]))
+        body = "".join(parts)
+        if "\\b" not in body and "\\B" not in body:
+            body = "\\b" + body
+        java = "(?U)" + body
+        third = rx.compile(body.replace("\\b", b_third).replace("\\B", nb_third).replace("\\w", W).replace("\\W", "[^" + W[1:])
+                           .replace("\\d", "\\p{Nd}").replace("\\S", "\\P{White_Space}"))
+        o = oracle.Regex(java)
+        d = binding.DebugRegex(java)
+        for _k in range(6):
+            t = "".join(rng.choice(alpha) for _ in range(rng.randint(0, 10)))
+            m = third.search(t)
+            assert o.find(t) == (m is not None), (java, t)
+            assert bool(d.match(t)) == (m is not None), (java, t)
+            checked += 1
+            if m is not None:
+                matched += 1
+                assert o.span(t) == m.span(), (java, t)
+                assert tuple(d.span(t)) == (len(t[:m.start()].encode()), len(t[:m.end()].encode())), (java, t)
+    assert checked > 4000 and matched > 400
 
 
 @pytest.mark.parametrize("bad", ["\\p{lu}", "\\p{IsFoo}", "\\p{InNowhere}", "\\p{sc=Nope}", "\\p{foo=bar}", "\\p{Latin}", "\\p{javaFoo}", "\\p{"])
