@@ -14,7 +14,7 @@ from oracle import oracle  # noqa: E402
 ALPHA = "aé́ΩдЖ٣_ -.x1‍€漢\U0001F600Z"
 ATOMS = [r"\p{L}", r"\P{L}", r"\p{Lu}", r"\P{Lu}", r"\p{IsCyrillic}", r"\P{IsCyrillic}", r"\p{InGreek}", r"\P{InGreek}", r"[^Ѐ-ӿ]",
          r"\p{Nd}", r"\P{Nd}", r"\p{M}", r"\P{M}", r"\p{IsAlphabetic}", r"\P{IsAlphabetic}", r"\p{So}", r"\P{So}", r"\p{IsHan}", r"[^\p{IsHan}a]",
-         r"\w", r"\W", r"\d", r"\D", r"\s", r"\S", ".", "a", "x", "é", "д", "Ж", "漢", "\U0001F600", r"[д-я]", r"[^a-zд]",
+         r"\w", r"\W", r"\d", r"\D", r"\s", r"\S", ".", "a", "x", "é", "д", "Ж", "漢", "Жx1", "éa", "xд", "1漢", "\U0001F600", r"[д-я]", r"[^a-zд]",
          r"[\p{L}&&[^\p{IsLatin}]]", r"\b", r"\B", "^", "$"]
 QUANT = ["", "", "", "+", "*", "?", "{2}", "+?", "*?", "*+", "++", "{1,2}"]
 
@@ -74,6 +74,10 @@ def check(rng: random.Random, n_patterns: int, report=print):
             if d.anchor and bool(d.match_anchored(t)) != want:
                 bad += 1
                 report("ANCHORED MISMATCH", repr(j), repr(t), "oracle", want)
+            local = d.match_local(t)                       # -2: not of the "literal with boundary conditions" form
+            if local != -2 and bool(local) != want:
+                bad += 1
+                report("BOUNDARY-FORM MISMATCH", repr(j), repr(t), "library", local, "oracle", want)
             if want:
                 matched += 1
                 try:
