@@ -12,6 +12,7 @@ from log_parser_b200 import binding  # noqa: E402
 from oracle import oracle  # noqa: E402
 
 ALPHA = "aé́ΩдЖ٣_ -.x1‍€漢\U0001F600Z"
+TERMINATORS = "\r\u0085\u2028"              # what a line of a "\n"-split log can still hold and `$`, `.`, (?m) care about
 ATOMS = [r"\p{L}", r"\P{L}", r"\p{Lu}", r"\P{Lu}", r"\p{IsCyrillic}", r"\P{IsCyrillic}", r"\p{InGreek}", r"\P{InGreek}", r"[^Ѐ-ӿ]",
          r"\p{Nd}", r"\P{Nd}", r"\p{M}", r"\P{M}", r"\p{IsAlphabetic}", r"\P{IsAlphabetic}", r"\p{So}", r"\P{So}", r"\p{IsHan}", r"[^\p{IsHan}a]",
          r"\w", r"\W", r"\d", r"\D", r"\s", r"\S", ".", "a", "x", "é", "д", "Ж", "漢", "Жx1", "éa", "xд", "1漢", "\U0001F600", r"[д-я]", r"[^a-zд]",
@@ -40,12 +41,23 @@ def piece(rng: random.Random, depth: int) -> str:
 
 
 def pattern(rng: random.Random) -> str:
-    body = "".join(piece(rng, 2) for _ in range(rng.randint(1, 3)))
-    return rng.choice(["", "", "(?U)", "(?i)", "(?iu)", "(?U)(?i)"]) + body
+    parts = [piece(rng, 2) for _ in range(rng.randint(1, 3))]
+    if rng.random() < 0.25:                   # a flag switched on or off part of the way, or for one group only
+        k = rng.randrange(len(parts))
+        parts[k] = rng.choice(["(?i)", "(?-i)", "(?u)", "(?m)", "(?s)", "(?d)", "(?U)", "(?-U)", "(?x) ", "(?iu)"]) + parts[k] if rng.random() < 0.5 \
+            else "(?" + rng.choice(["i", "iu", "s", "m", "U", "-i", "d", "x"]) + ":" + parts[k] + ")"
+    return rng.choice(["", "", "(?U)", "(?i)", "(?iu)", "(?U)(?i)", "(?m)", "(?s)", "(?d)", "(?dm)"]) + "".join(parts)
 
 
 def text(rng: random.Random, maxlen: int = 12) -> str:
-    return "".join(rng.choice(ALPHA) for _ in range(rng.randint(0, maxlen)))
+    t = "".join(rng.choice(ALPHA) for _ in range(rng.randint(0, maxlen)))
+    k = rng.random()
+    if k < 0.15:
+        t += rng.choice(TERMINATORS)
+    elif k < 0.25:
+        cut = rng.randint(0, len(t))
+        t = t[:cut] + rng.choice(TERMINATORS) + t[cut:]
+    return t
 
 
 def check(rng: random.Random, n_patterns: int, report=print):
