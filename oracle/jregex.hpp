@@ -13,6 +13,8 @@
 //     syntax subset (tests/test_oracle_regex_diff.py),
 //   * differential tests against PCRE2 10.42 where its dialect agrees with Java's, with the known
 //     dialect differences held as fixtures (tests/test_oracle_pcre2_diff.py, tests/golden/).
+// oracle/RegexPin.java replays tests/golden/regex_pin_corpus.tsv.gz (this engine's answers) on a real JDK where one
+// exists; tests/test_oracle_golden.py keeps this engine on the recorded answers.
 // Known difference from the JDK, in this restatement and in the library alike: Pattern.Bound also
 // counts a non-spacing mark (category Mn) that follows a letter or digit as a word character
 // (Bound.check / hasBaseCharacter); here `\b` and `\B` look at the ASCII word class only, so a

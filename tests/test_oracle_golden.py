@@ -211,3 +211,53 @@ def test_temporal_equivalence_bruteforce(oracle):
             near = any(has[k - 1][l] for l in range(max(0, i - 5), min(nl, i + 6)))
             exp = near and (k == 1 or (ok_chain and T < i))
             assert r.factors[idx, 4] == (2.0 if exp else 1.0)
+
+
+def _pin_corpus():
+    import base64
+    import gzip
+    import os
+
+    path = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "regex_pin_corpus.tsv.gz")
+    with gzip.open(path, "rt", encoding="ascii") as f:
+        for row in f:
+            if row.strip():
+                p, flags, t, found, s, e = row.rstrip("\n").split("\t")
+                yield base64.b64decode(p).decode("utf-8"), int(flags), base64.b64decode(t).decode("utf-8"), found == "1", int(s), int(e)
+
+
+def test_pin_corpus_is_what_the_oracle_and_the_library_answer(oracle):
+    """tests/golden/regex_pin_corpus.tsv.gz is the file oracle/RegexPin.java replays on a real JDK (none in this image):
+    ~5 000 (pattern, flags, text) cases with the first find() and its span. The restatement must keep giving the recorded
+    answers (otherwise the corpus is regenerated and the change explained), and the product's host compiler — automata or
+    bytecode engine, the tables the device walks — gives the same ones."""
+    from log_parser_b200 import binding
+
+    n = n_found = n_lib = 0
+    compiled = {}
+    for pat, flags, text, found, s, e in _pin_corpus():
+        key = (pat, flags)
+        if key not in compiled:
+            try:
+                d = binding.DebugRegex(pat, flags)
+            except binding.UnsupportedRegexError:
+                d = None                               # beyond the library's limits (e.g. look-behind spanning > 64 lengths)
+            compiled[key] = (oracle.Regex(pat, flags), d)
+        o, d = compiled[key]
+        sp = o.span(text)
+        assert (sp is not None) == found and (sp or (-1, -1)) == (s, e), (pat, flags, text)
+        n += 1
+        n_found += found
+        if d is None:
+            continue
+        got = d.match(text)
+        if got < 0:
+            continue                                   # backtracking budget
+        assert bool(got) == found, (pat, flags, text)
+        n_lib += 1
+        if found:
+            try:
+                assert tuple(d.span(text)) == (len(text[:s].encode()), len(text[:e].encode())), (pat, flags, text)
+            except binding.LpError:
+                pass
+    assert n > 4500 and n_found > 1200 and n_lib > 4400
