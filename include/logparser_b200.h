@@ -266,8 +266,8 @@ int lp_analyze_range_dist(lp_ctx* ctx, const uint8_t* text, size_t len, uint32_t
  *                 overflow flag back and returns only after `stream` has drained; the calling thread's
  *                 current device is the same after the call as before
  *   err/errlen    optional buffer for a message when the return value is not LP_OK
- * The first call on each device looks up the scratch array's address; issue it before starting
- * any stream capture. All calls on one device share that array and it keeps the previous call's
+ * The first call on each device looks up the scratch array's address, once. All calls on one device
+ * share that array and it keeps the previous call's
  * contents (the call clears what it needs): calls that can overlap on the GPU corrupt each other,
  * so keep them on one stream or otherwise serialised. */
 #define LP_NOALLOC_MAX_BYTES (1ull << 30)

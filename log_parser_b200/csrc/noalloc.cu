@@ -14,7 +14,7 @@
 //   * at most LP_NOALLOC_MAX_BYTES (1 GiB) of log per call; larger inputs are rejected with
 //     LP_ERR_LIMIT before anything is launched;
 //   * the first call on a given device resolves the scratch array's device address
-//     (cudaGetSymbolAddress). Make that first call outside of any CUDA stream capture;
+//     (cudaGetSymbolAddress), with that device current, once;
 //   * every call is synchronous: it reads the overflow flag back and waits for `stream` to drain
 //     before it returns (the caller's current device is left as it was);
 //   * all calls on one device share the one scratch array. Two calls whose kernels may overlap on
