@@ -1001,6 +1001,54 @@ def test_random_regexes_with_literals_through_the_pipeline(parser, oracle):
     assert checked >= 20 and n_events > 2000
 
 
+def test_multi_script_patterns_through_the_pipeline(parser, oracle):
+    """Unicode property classes, (?U) classes and word boundaries, (?iu) folding, negated classes that leave out whole
+    UTF-8 lead-byte blocks, inside look-arounds, atomic groups and back-references, on lines mixing 1- to 4-byte
+    characters, combining marks and Java's extra line terminators: every (line, pattern) event of the device pipeline
+    against the oracle's find() on that line. The generator is scripts/fuzz_host_scripts.py (its host-side run is
+    tests/test_library_cpu.py::test_multi_script_text_vs_oracle_random)."""
+    import importlib.util
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("fuzz_host_scripts", os.path.join(root, "scripts", "fuzz_host_scripts.py"))
+    fz = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(fz)
+    rng = random.Random(31)
+    words = ["ERRx", "\u0434\u0430\u0442\u0430", "\u0416x1", "\u00e9a", "timeout"]
+    checked = n_events = 0
+    for rnd_i in range(8):
+        pats, rxs = [], []
+        while len(pats) < 12:
+            a = fz.pattern(rng)
+            w = rng.choice(words)
+            j = [a, w + a, a + w, "(?U)\\b" + w + "\\b", "(?:" + a + "|" + w + ")", "(?iu)" + w + a][rng.randrange(6)]
+            try:
+                o = oracle.Regex(j)
+                binding.DebugRegex(j)
+            except Exception:
+                continue
+            pats.append(PatternSpec(id=f"p{len(pats)}", primary_regex=j, confidence=0.5, severity="LOW"))
+            rxs.append(o)
+        made = []
+        for _ in range(300):
+            made.append("".join(rng.choice(words) if rng.random() < 0.4 else fz.text(rng, 6) for _k in range(rng.randint(0, 3))))
+        log = ("\n".join(made) + "\n").encode()
+        lines = [log[s:e].decode() for s, e in oracle.split(log)]       # "\r" in front of a "\n" belongs to the separator
+        parser.load_patterns(pats)
+        res = parser.analyze(log, options=binding.OPT_NO_RANK)
+        assert res.n_lines == len(lines)
+        got = set(zip(res.line.tolist(), res.pattern.tolist()))
+        exp = set()
+        for i, ln in enumerate(lines):
+            for p, o in enumerate(rxs):
+                if o.find(ln):
+                    exp.add((i + 1, p))
+        assert got == exp, (rnd_i, sorted(got ^ exp)[:5], [(pats[p].primary_regex, lines[l - 1]) for l, p in sorted(got ^ exp)[:3]])
+        checked += 1
+        n_events += len(exp)
+    assert checked == 8 and n_events > 2000
+
+
 def test_concurrent_requests_from_threads(parser):
     """AnalysisService.analyze is called from several Quarkus worker threads at once (AS:35,50): calls on one
     shared context run on its workers (two by default, each with its own stream and scratch) and overlap on the
