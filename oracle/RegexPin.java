@@ -8,7 +8,9 @@
 //     java oracle/RegexPin.java [tests/golden/regex_pin_corpus.tsv.gz]
 // Exit status 0 = no unexpected disagreement. One class of disagreement is known and labelled as such: Pattern.Bound
 // counts a non-spacing mark that follows a letter or digit as a word character, the restatement and the library test
-// the ASCII word class only (DESIGN.md §3).
+// the ASCII word class only (DESIGN.md §3). A second one is labelled too: Pattern.Behind steps back in UTF-16 units
+// unless the pattern itself holds a supplementary character (BehindS), the restatement steps back in code points, so a
+// look-behind right after a character beyond the BMP can see half of it on the JDK.
 //
 // Line format, TAB separated: base64(pattern UTF-8), flags (Pattern.* bit values), base64(text UTF-8), found (0/1),
 // start, end of the first find() in code points (-1 -1 when not found).
@@ -57,10 +59,15 @@ public class RegexPin {
                 boolean mark = text.codePoints().anyMatch(c -> Character.getType(c) == Character.NON_SPACING_MARK);
                 boolean boundary = regex.contains("\\b") || regex.contains("\\B");
                 boolean unicodeClass = (flags & Pattern.UNICODE_CHARACTER_CLASS) != 0 || regex.contains("(?U");
+                boolean beyondBmp = text.codePoints().anyMatch(Character::isSupplementaryCodePoint);
+                boolean lookBehind = regex.contains("(?<=") || regex.contains("(?<!");
                 String label;
                 if (mark && boundary && !unicodeClass) {
                     known++;
                     label = "known (mark at a word boundary)";
+                } else if (beyondBmp && lookBehind) {
+                    known++;
+                    label = "known (look-behind next to a character beyond the BMP)";
                 } else {
                     unexpected++;
                     label = "UNEXPECTED";

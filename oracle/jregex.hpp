@@ -19,6 +19,9 @@
 // counts a non-spacing mark (category Mn) that follows a letter or digit as a word character
 // (Bound.check / hasBaseCharacter); here `\b` and `\B` look at the ASCII word class only, so a
 // line with a combining mark right at a `\b` position can be decided differently.
+// A second one: Pattern.Behind steps back in UTF-16 units unless the pattern itself contains a supplementary
+// character (then BehindS); here look-behind steps back in code points, so a look-behind right after a character
+// beyond the BMP can be decided differently.
 //
 // Design: a leftmost, ordered-alternation backtracking matcher over Unicode code points
 // (the same observable behaviour as Matcher.find() on well-formed UTF-16), written as a
