@@ -3,13 +3,25 @@ compiler extracted for it (rx_literal.cpp required_literals) - a missing literal
 where only lines holding a literal's 4-byte gram reach verification. Random patterns from both generators glued to words
 in several scripts, (?i) and (?iu) folding, literal lengths 1..4. Hunting tool.
 Usage: python scripts/fuzz_host_literals.py <seed> <rounds>"""
-import sys, random, importlib.util
-sys.path.insert(0, "."); sys.path.insert(0, "tests")
-from log_parser_b200 import binding
-from oracle import oracle
-from rxgen import Gen
-spec = importlib.util.spec_from_file_location("fz", "scripts/fuzz_host_scripts.py"); fz = importlib.util.module_from_spec(spec); spec.loader.exec_module(fz)
-def ascii_lower(b): return bytes(c + 32 if 65 <= c <= 90 else c for c in b)
+import importlib.util
+import random
+import sys
+
+sys.path.insert(0, ".")
+sys.path.insert(0, "tests")
+from log_parser_b200 import binding  # noqa: E402
+from oracle import oracle  # noqa: E402
+from rxgen import Gen  # noqa: E402
+
+spec = importlib.util.spec_from_file_location("fz", "scripts/fuzz_host_scripts.py")
+fz = importlib.util.module_from_spec(spec)
+spec.loader.exec_module(fz)
+
+
+def ascii_lower(b: bytes) -> bytes:      # icase literals are stored with ASCII letters in lower case; nothing else is folded
+    return bytes(c + 32 if 65 <= c <= 90 else c for c in b)
+
+
 WORDS = ["ERRx", "abc_1", "Exception", "x-1:E", "timeout ", "дата", "Жx1", "éa", "STRASSE", "straße", "İx", "Kelvin"]
 rng = random.Random(int(sys.argv[1])); rounds = int(sys.argv[2])
 n = matched = withlits = bad = 0
